@@ -1,0 +1,588 @@
+// extract.cu -- surface point and marching-cubes extraction from the hashed TSDF volume (sm_100a).
+//
+// Replaces volume.extract_point_cloud() / volume.extract_triangle_mesh() (+ compute_vertex_normals)
+// (/root/reference/CodeThatWorks/GoodColorReconstruction.py:285-286,305,536-542;
+//  CodeThatWorks/1camera-detectsSceneChanges.py:277-291); upstream semantics: SURVEY.md A.5.
+//
+// Design (not a port of upstream's serial scan + unordered_map welding):
+//   * units are processed in SORTED KEY ORDER (cub radix sort of packed keys) so output order is
+//     canonical and reproducible: (unit key, voxel x*256+y*16+z, edge axis);
+//   * one CTA per unit stages the unit's TSDF with its 1-voxel apron (neighbour units found through
+//     the spatial hash) in shared memory, weight==0 encoded as NaN;
+//   * every mesh vertex has exactly one OWNER (the voxel at the lower end of its edge + the axis), so
+//     welding needs no hash map: a count pass writes per-voxel vertex slots, an exclusive scan over
+//     units gives bases, the fill pass resolves any cube edge to owner -> index arithmetically;
+//   * compaction = per-thread popc over a z column + block scan (warp shuffles).
+#include "tsdf_internal.h"
+#include <cub/cub.cuh>
+
+#define MC_TABLE_QUAL __device__ __constant__ const
+#include "mc_tables.h"
+
+namespace {
+
+struct VolView {
+    B2RHash hash;
+    const int32_t* unit_keys;
+    const float* pool;
+    int64_t unit_stride;
+    int planes;
+    double voxel_length, unit_length;
+};
+
+__device__ __forceinline__ int find_unit(const VolView& V, int kx, int ky, int kz) {
+    if (!b2r_key_in_range(kx, ky, kz)) return -1;
+    return b2r_hash_find(V.hash, b2r_pack_key(kx, ky, kz));
+}
+
+// ---- shared-memory apron: A[(x-LO)][(y-LO)][(z-LO)] for x,y,z in [LO, 16] ----------------------
+template <int LO, bool RANGE_CHECK>
+__device__ __forceinline__ void stage_apron(const VolView& V, int unit, float* A, int* nb /*27*/) {
+    constexpr int D = 17 - LO;
+    const int kx = V.unit_keys[3 * unit], ky = V.unit_keys[3 * unit + 1], kz = V.unit_keys[3 * unit + 2];
+    if (threadIdx.x < 27) {
+        const int dx = threadIdx.x / 9 - 1, dy = (threadIdx.x / 3) % 3 - 1, dz = threadIdx.x % 3 - 1;
+        int id = -1;
+        if (dx == 0 && dy == 0 && dz == 0) id = unit;
+        else if (dx >= LO && dy >= LO && dz >= LO) id = find_unit(V, kx + dx, ky + dy, kz + dz);
+        nb[threadIdx.x] = id;
+    }
+    __syncthreads();
+    const float nanv = __int_as_float(0x7fc00000);
+    for (int c = threadIdx.x; c < D * D * D; c += blockDim.x) {
+        const int ax = c / (D * D), ay = (c / D) % D, az = c % D;
+        int x = ax + LO, y = ay + LO, z = az + LO;
+        int ox = 1, oy = 1, oz = 1;
+        if (x < 0) { x += 16; ox = 0; } else if (x >= 16) { x -= 16; ox = 2; }
+        if (y < 0) { y += 16; oy = 0; } else if (y >= 16) { y -= 16; oy = 2; }
+        if (z < 0) { z += 16; oz = 0; } else if (z >= 16) { z -= 16; oz = 2; }
+        const int u = nb[(ox * 3 + oy) * 3 + oz];
+        float f = nanv;
+        if (u >= 0) {
+            const float* base = V.pool + (int64_t)u * V.unit_stride + (x * 256 + y * 16 + z);
+            const float t = base[0], w = base[B2R_UNIT_VOX];
+            bool ok = (w != 0.0f);
+            if (RANGE_CHECK) ok = ok && (t < 0.98f) && (t >= -0.98f);
+            if (ok) f = t;
+        }
+        A[c] = f;
+    }
+    __syncthreads();
+}
+
+// block-wide exclusive scan of one int per thread (256 threads); returns exclusive prefix, sets total
+__device__ __forceinline__ int block_exclusive_scan(int v, int* total, int* ws /*>=9 ints*/) {
+    int incl = v;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    __syncthreads();
+    if (lane == 31) ws[warp] = incl;
+    __syncthreads();
+    int wbase = 0, tot = 0;
+    const int nw = blockDim.x >> 5;
+    for (int i = 0; i < nw; i++) { if (i < warp) wbase += ws[i]; tot += ws[i]; }
+    *total = tot;
+    return wbase + incl - v;
+}
+
+// f64 trilinear TSDF sample, SURVEY A.5 GetTSDFAt (reads global memory through the hash)
+__device__ double tsdf_at(const VolView& V, double px, double py, double pz) {
+    const double vl = V.voxel_length, hv = xdmul(0.5, vl);
+    const double q[3] = {xdsub(px, hv), xdsub(py, hv), xdsub(pz, hv)};
+    int k[3], idx[3];
+    double r[3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) k[i] = (int)floor(xddiv(q[i], V.unit_length));
+    const int u0 = find_unit(V, k[0], k[1], k[2]);
+    if (u0 < 0) return 0.0;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        const double g = xddiv(xdsub(q[i], xdmul((double)k[i], V.unit_length)), vl);
+        int f = (int)floor(g);
+        f = min(max(f, 0), 15);
+        idx[i] = f;
+        r[i] = xdsub(g, (double)f);
+    }
+    double f[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        int x = idx[0] + mc_shift[i][0], y = idx[1] + mc_shift[i][1], z = idx[2] + mc_shift[i][2];
+        int ux = k[0], uy = k[1], uz = k[2];
+        bool same = true;
+        if (x >= 16) { x -= 16; ux++; same = false; }
+        if (y >= 16) { y -= 16; uy++; same = false; }
+        if (z >= 16) { z -= 16; uz++; same = false; }
+        const int u = same ? u0 : find_unit(V, ux, uy, uz);
+        f[i] = (u >= 0) ? (double)V.pool[(int64_t)u * V.unit_stride + (x * 256 + y * 16 + z)] : 0.0;
+    }
+    const double a0 = xdsub(1.0, r[0]), a1 = xdsub(1.0, r[1]), a2 = xdsub(1.0, r[2]);
+    const double t04 = xdadd(xdmul(a2, f[0]), xdmul(r[2], f[4]));
+    const double t37 = xdadd(xdmul(a2, f[3]), xdmul(r[2], f[7]));
+    const double t15 = xdadd(xdmul(a2, f[1]), xdmul(r[2], f[5]));
+    const double t26 = xdadd(xdmul(a2, f[2]), xdmul(r[2], f[6]));
+    const double lo = xdadd(xdmul(a1, t04), xdmul(r[1], t37));
+    const double hi = xdadd(xdmul(a1, t15), xdmul(r[1], t26));
+    return xdadd(xdmul(a0, lo), xdmul(r[0], hi));
+}
+
+// ------------------------------------------------------------------------------------------------
+// surface points
+// ------------------------------------------------------------------------------------------------
+template <bool FILL>
+__global__ void __launch_bounds__(256) extract_points_kernel(const VolView V, const int32_t* order, int32_t* unit_counts,
+                                                             const int32_t* unit_offsets, double* xyz, double* rgb,
+                                                             double* nrm, int32_t* ids, int64_t capacity) {
+    constexpr int D = 17;
+    __shared__ float A[D * D * D];
+    __shared__ int nb[27];
+    __shared__ int ws[9];
+    const int pos = blockIdx.x;
+    const int unit = order[pos];
+    stage_apron<0, true>(V, unit, A, nb);
+    const int x = threadIdx.x >> 4, y = threadIdx.x & 15;
+    unsigned masks[16];
+    int cnt = 0;
+#pragma unroll
+    for (int z = 0; z < 16; z++) {
+        const float f0 = A[(x * D + y) * D + z];
+        unsigned m = 0;
+        if (f0 == f0) {
+            const float fx1 = A[((x + 1) * D + y) * D + z], fy1 = A[(x * D + y + 1) * D + z], fz1 = A[(x * D + y) * D + z + 1];
+            if (xfmul(f0, fx1) < 0.0f) m |= 1u;
+            if (xfmul(f0, fy1) < 0.0f) m |= 2u;
+            if (xfmul(f0, fz1) < 0.0f) m |= 4u;
+        }
+        masks[z] = m;
+        cnt += __popc(m);
+    }
+    int total;
+    int offs = block_exclusive_scan(cnt, &total, ws);
+    if (!FILL) {
+        if (threadIdx.x == 0) unit_counts[pos] = total;
+        return;
+    }
+    if (total == 0) return;
+    const int64_t base = (int64_t)unit_offsets[pos];
+    const int kx = V.unit_keys[3 * unit], ky = V.unit_keys[3 * unit + 1], kz = V.unit_keys[3 * unit + 2];
+    const double vl = V.voxel_length, hv = xdmul(0.5, vl);
+#pragma unroll 1
+    for (int z = 0; z < 16; z++) {
+        const unsigned m = masks[z];
+        if (!m) continue;
+        const int l[3] = {x, y, z};
+        const int kk[3] = {kx, ky, kz};
+        double p0[3];
+#pragma unroll
+        for (int i = 0; i < 3; i++) p0[i] = xdadd(xdadd(hv, xdmul(vl, (double)l[i])), xdmul((double)kk[i], V.unit_length));
+        const float f0 = A[(x * D + y) * D + z];
+        const float* v0 = V.pool + (int64_t)unit * V.unit_stride + (x * 256 + y * 16 + z);
+        for (int i = 0; i < 3; i++) {
+            if (!(m & (1u << i))) continue;
+            const int64_t o = base + offs;
+            offs++;
+            if (o >= capacity) continue;
+            int n[3] = {x, y, z};
+            n[i] += 1;
+            const float f1 = A[(n[0] * D + n[1]) * D + n[2]];
+            const float r0 = fabsf(f0), r1 = fabsf(f1);
+            double p[3] = {p0[0], p0[1], p0[2]};
+            const double p1i = xdadd(p0[i], vl);
+            p[i] = xddiv(xdadd(xdmul(p0[i], (double)r1), xdmul(p1i, (double)r0)), (double)xfadd(r0, r1));
+            xyz[3 * o] = p[0]; xyz[3 * o + 1] = p[1]; xyz[3 * o + 2] = p[2];
+            if (rgb && V.planes == 5) {
+                int ux = 1, uy = 1, uz = 1, lx = n[0], ly = n[1], lz = n[2];
+                if (lx >= 16) { lx -= 16; ux = 2; }
+                if (ly >= 16) { ly -= 16; uy = 2; }
+                if (lz >= 16) { lz -= 16; uz = 2; }
+                const int u1 = nb[(ux * 3 + uy) * 3 + uz];
+                const float* v1 = V.pool + (int64_t)u1 * V.unit_stride + (lx * 256 + ly * 16 + lz);
+#pragma unroll
+                for (int c = 0; c < 3; c++) {
+                    const float c0 = v0[(2 + c) * B2R_UNIT_VOX], c1 = v1[(2 + c) * B2R_UNIT_VOX];
+                    const float cc = xfdiv(xfdiv(xfadd(xfmul(c0, r1), xfmul(c1, r0)), xfadd(r0, r1)), 255.0f);
+                    rgb[3 * o + c] = (double)cc;
+                }
+            }
+            if (nrm) {
+                const double hg = xdmul(0.99, vl);
+                double g[3];
+                g[0] = xdsub(tsdf_at(V, xdadd(p[0], hg), p[1], p[2]), tsdf_at(V, xdsub(p[0], hg), p[1], p[2]));
+                g[1] = xdsub(tsdf_at(V, p[0], xdadd(p[1], hg), p[2]), tsdf_at(V, p[0], xdsub(p[1], hg), p[2]));
+                g[2] = xdsub(tsdf_at(V, p[0], p[1], xdadd(p[2], hg)), tsdf_at(V, p[0], p[1], xdsub(p[2], hg)));
+                const double len = sqrt(xdadd(xdadd(xdmul(g[0], g[0]), xdmul(g[1], g[1])), xdmul(g[2], g[2])));
+                if (len > 0.0) { g[0] = xddiv(g[0], len); g[1] = xddiv(g[1], len); g[2] = xddiv(g[2], len); }
+                nrm[3 * o] = g[0]; nrm[3 * o + 1] = g[1]; nrm[3 * o + 2] = g[2];
+            }
+            if (ids) { ids[4 * o] = kx * 16 + x; ids[4 * o + 1] = ky * 16 + y; ids[4 * o + 2] = kz * 16 + z; ids[4 * o + 3] = i; }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// marching cubes
+// ------------------------------------------------------------------------------------------------
+#define MD 18   // apron [-1, 16]
+#define MC 17   // cube origins [-1, 15]
+
+__device__ __forceinline__ float apron_m(const float* A, int x, int y, int z) { return A[((x + 1) * MD + (y + 1)) * MD + (z + 1)]; }
+
+__device__ __forceinline__ void stage_complete(const float* A, unsigned char* C) {
+    for (int c = threadIdx.x; c < MC * MC * MC; c += blockDim.x) {
+        const int x = c / (MC * MC) - 1, y = (c / MC) % MC - 1, z = c % MC - 1;
+        bool ok = true;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const float f = apron_m(A, x + mc_shift[i][0], y + mc_shift[i][1], z + mc_shift[i][2]);
+            ok = ok && (f == f);
+        }
+        C[c] = ok ? 1 : 0;
+    }
+    __syncthreads();
+}
+__device__ __forceinline__ bool cube_complete(const unsigned char* C, int x, int y, int z) { return C[((x + 1) * MC + (y + 1)) * MC + (z + 1)] != 0; }
+
+__device__ __forceinline__ unsigned owned_edge_mask(const float* A, const unsigned char* C, int x, int y, int z) {
+    const float f0 = apron_m(A, x, y, z);
+    if (!(f0 == f0)) return 0;
+    const bool s0 = f0 < 0.0f;
+    unsigned m = 0;
+    {   // axis 0: cubes (x, y-{0,1}, z-{0,1})
+        const float f1 = apron_m(A, x + 1, y, z);
+        if (f1 == f1 && ((f1 < 0.0f) != s0) &&
+            (cube_complete(C, x, y, z) || cube_complete(C, x, y - 1, z) || cube_complete(C, x, y, z - 1) || cube_complete(C, x, y - 1, z - 1))) m |= 1u;
+    }
+    {   // axis 1: cubes (x-{0,1}, y, z-{0,1})
+        const float f1 = apron_m(A, x, y + 1, z);
+        if (f1 == f1 && ((f1 < 0.0f) != s0) &&
+            (cube_complete(C, x, y, z) || cube_complete(C, x - 1, y, z) || cube_complete(C, x, y, z - 1) || cube_complete(C, x - 1, y, z - 1))) m |= 2u;
+    }
+    {   // axis 2: cubes (x-{0,1}, y-{0,1}, z)
+        const float f1 = apron_m(A, x, y, z + 1);
+        if (f1 == f1 && ((f1 < 0.0f) != s0) &&
+            (cube_complete(C, x, y, z) || cube_complete(C, x - 1, y, z) || cube_complete(C, x, y - 1, z) || cube_complete(C, x - 1, y - 1, z))) m |= 4u;
+    }
+    return m;
+}
+
+__device__ __forceinline__ int cube_case(const float* A, const unsigned char* C, int x, int y, int z) {
+    if (!cube_complete(C, x, y, z)) return 0;
+    int cube = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+        if (apron_m(A, x + mc_shift[i][0], y + mc_shift[i][1], z + mc_shift[i][2]) < 0.0f) cube |= 1 << i;
+    return cube;
+}
+
+// pass 1: per-voxel vertex slots + per-unit vertex / triangle counts
+__global__ void __launch_bounds__(256) mesh_count_kernel(const VolView V, const int32_t* order, uint32_t* vinfo,
+                                                         int32_t* unit_vcount, int32_t* unit_tcount) {
+    __shared__ float A[MD * MD * MD];
+    __shared__ unsigned char C[MC * MC * MC];
+    __shared__ int nb[27];
+    __shared__ int ws[9];
+    const int pos = blockIdx.x;
+    const int unit = order[pos];
+    stage_apron<-1, false>(V, unit, A, nb);
+    stage_complete(A, C);
+    const int x = threadIdx.x >> 4, y = threadIdx.x & 15;
+    unsigned masks[16];
+    int vc = 0, tc = 0;
+#pragma unroll
+    for (int z = 0; z < 16; z++) {
+        const unsigned m = owned_edge_mask(A, C, x, y, z);
+        masks[z] = m;
+        vc += __popc(m);
+        const int cube = cube_case(A, C, x, y, z);
+        tc += mc_num_tris[cube];
+    }
+    int vtot, ttot;
+    int voff = block_exclusive_scan(vc, &vtot, ws);
+    block_exclusive_scan(tc, &ttot, ws);
+    uint32_t* vi = vinfo + (int64_t)unit * B2R_UNIT_VOX + (x * 256 + y * 16);
+#pragma unroll
+    for (int z = 0; z < 16; z++) {
+        vi[z] = ((uint32_t)voff << 3) | masks[z];
+        voff += __popc(masks[z]);
+    }
+    if (threadIdx.x == 0) { unit_vcount[pos] = vtot; unit_tcount[pos] = ttot; }
+}
+
+__global__ void scatter_bases_kernel(const int32_t* order, const int32_t* scan, int32_t* by_unit, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) by_unit[order[i]] = scan[i];
+}
+
+// pass 2: emit vertices (owner voxels) and triangles (cubes)
+__global__ void __launch_bounds__(256) mesh_fill_kernel(const VolView V, const int32_t* order, const uint32_t* vinfo,
+                                                        const int32_t* vbase_by_unit, const int32_t* tbase,
+                                                        double* vtx, double* vcol, int32_t* tri, int32_t* ids,
+                                                        int64_t capV, int64_t capF) {
+    __shared__ float A[MD * MD * MD];
+    __shared__ unsigned char C[MC * MC * MC];
+    __shared__ int nb[27];
+    __shared__ int ws[9];
+    const int pos = blockIdx.x;
+    const int unit = order[pos];
+    stage_apron<-1, false>(V, unit, A, nb);
+    stage_complete(A, C);
+    const int x = threadIdx.x >> 4, y = threadIdx.x & 15;
+    const int kx = V.unit_keys[3 * unit], ky = V.unit_keys[3 * unit + 1], kz = V.unit_keys[3 * unit + 2];
+    const double vl = V.voxel_length, hv = xdmul(0.5, vl);
+    const int64_t vb = vbase_by_unit[unit];
+    const uint32_t* vi = vinfo + (int64_t)unit * B2R_UNIT_VOX + (x * 256 + y * 16);
+    // ---- vertices
+#pragma unroll 1
+    for (int z = 0; z < 16; z++) {
+        const uint32_t info = vi[z];
+        const unsigned m = info & 7u;
+        if (!m) continue;
+        int64_t o = vb + (info >> 3);
+        const float f0f = apron_m(A, x, y, z);
+        const float* v0 = V.pool + (int64_t)unit * V.unit_stride + (x * 256 + y * 16 + z);
+        const int e[3] = {kx * 16 + x, ky * 16 + y, kz * 16 + z};
+        for (int a = 0; a < 3; a++) {
+            if (!(m & (1u << a))) continue;
+            if (o < capV) {
+                int n[3] = {x, y, z};
+                n[a] += 1;
+                const float f1f = apron_m(A, n[0], n[1], n[2]);
+                const double f0 = fabs((double)f0f), f1 = fabs((double)f1f);
+                double pt[3];
+#pragma unroll
+                for (int i = 0; i < 3; i++) pt[i] = xdadd(hv, xdmul(vl, (double)e[i]));
+                pt[a] = xdadd(pt[a], xddiv(xdmul(f0, vl), xdadd(f0, f1)));
+                vtx[3 * o] = pt[0]; vtx[3 * o + 1] = pt[1]; vtx[3 * o + 2] = pt[2];
+                if (vcol && V.planes == 5) {
+                    int ux = 1, uy = 1, uz = 1, lx = n[0], ly = n[1], lz = n[2];
+                    if (lx >= 16) { lx -= 16; ux = 2; }
+                    if (ly >= 16) { ly -= 16; uy = 2; }
+                    if (lz >= 16) { lz -= 16; uz = 2; }
+                    const int u1 = nb[(ux * 3 + uy) * 3 + uz];
+                    const float* v1 = V.pool + (int64_t)u1 * V.unit_stride + (lx * 256 + ly * 16 + lz);
+#pragma unroll
+                    for (int c = 0; c < 3; c++) {
+                        const double c0 = xddiv((double)v0[(2 + c) * B2R_UNIT_VOX], 255.0), c1 = xddiv((double)v1[(2 + c) * B2R_UNIT_VOX], 255.0);
+                        vcol[3 * o + c] = xddiv(xdadd(xdmul(f1, c0), xdmul(f0, c1)), xdadd(f0, f1));
+                    }
+                }
+                if (ids) { ids[4 * o] = e[0]; ids[4 * o + 1] = e[1]; ids[4 * o + 2] = e[2]; ids[4 * o + 3] = a; }
+            }
+            o++;
+        }
+    }
+    // ---- triangles
+    int cases[16];
+    int tc = 0;
+#pragma unroll
+    for (int z = 0; z < 16; z++) { cases[z] = cube_case(A, C, x, y, z); tc += mc_num_tris[cases[z]]; }
+    int ttot;
+    int toff = block_exclusive_scan(tc, &ttot, ws);
+    if (ttot == 0) return;
+    int64_t to = (int64_t)tbase[pos] + toff;
+#pragma unroll 1
+    for (int z = 0; z < 16; z++) {
+        const int cube = cases[z];
+        const int nt = mc_num_tris[cube];
+        if (!nt) continue;
+        int vid[12];
+        const int em = mc_edge_table[cube];
+#pragma unroll 1
+        for (int i = 0; i < 12; i++) {
+            vid[i] = -1;
+            if (!(em & (1 << i))) continue;
+            int ox = x + mc_edge_shift[i][0], oy = y + mc_edge_shift[i][1], oz = z + mc_edge_shift[i][2];
+            const int axis = mc_edge_shift[i][3];
+            int ux = 1, uy = 1, uz = 1;
+            if (ox >= 16) { ox -= 16; ux = 2; }
+            if (oy >= 16) { oy -= 16; uy = 2; }
+            if (oz >= 16) { oz -= 16; uz = 2; }
+            const int u = nb[(ux * 3 + uy) * 3 + uz];
+            const uint32_t info = vinfo[(int64_t)u * B2R_UNIT_VOX + (ox * 256 + oy * 16 + oz)];
+            vid[i] = vbase_by_unit[u] + (int)(info >> 3) + __popc(info & ((1u << axis) - 1u));
+        }
+        for (int t = 0; t < nt; t++) {
+            if (to < capF) {
+                tri[3 * to] = vid[mc_tri_table[cube][3 * t]];
+                tri[3 * to + 1] = vid[mc_tri_table[cube][3 * t + 2]];
+                tri[3 * to + 2] = vid[mc_tri_table[cube][3 * t + 1]];
+            }
+            to++;
+        }
+    }
+}
+
+__global__ void pack_keys_kernel(const int32_t* unit_keys, int n, uint64_t* keys, int32_t* ids) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    keys[i] = b2r_pack_key(unit_keys[3 * i], unit_keys[3 * i + 1], unit_keys[3 * i + 2]);
+    ids[i] = i;
+}
+
+struct Scratch {
+    uint64_t *k_in, *k_out;
+    int32_t *id_in, *order;
+    int32_t *cnt_a, *cnt_b, *scan_a, *scan_b, *vbase_by_unit;
+    uint32_t* vinfo;
+    void* cub_tmp;
+    size_t cub_bytes;
+};
+
+size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
+
+int carve(b2r_tsdf* h, int n, bool mesh, Scratch* S) {
+    size_t sort_tmp = 0, scan_tmp = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp, (uint64_t*)nullptr, (uint64_t*)nullptr, (int32_t*)nullptr, (int32_t*)nullptr, n);
+    cub::DeviceScan::ExclusiveSum(nullptr, scan_tmp, (int32_t*)nullptr, (int32_t*)nullptr, n + 1);
+    const size_t cub_bytes = align_up(sort_tmp > scan_tmp ? sort_tmp : scan_tmp);
+    size_t total = 0;
+    auto take = [&](size_t bytes) { size_t o = total; total += align_up(bytes); return o; };
+    const size_t o_kin = take((size_t)n * 8), o_kout = take((size_t)n * 8), o_idin = take((size_t)n * 4), o_ord = take((size_t)n * 4);
+    const size_t o_ca = take((size_t)(n + 1) * 4), o_cb = take((size_t)(n + 1) * 4), o_sa = take((size_t)(n + 1) * 4), o_sb = take((size_t)(n + 1) * 4);
+    const size_t o_vb = take((size_t)n * 4);
+    const size_t o_cub = take(cub_bytes);
+    const size_t o_vi = mesh ? take((size_t)n * B2R_UNIT_VOX * 4) : 0;
+    int rc = b2r_tsdf_ensure_scratch(h, total);
+    if (rc != B2R_OK) return rc;
+    char* b = (char*)h->scratch;
+    S->k_in = (uint64_t*)(b + o_kin); S->k_out = (uint64_t*)(b + o_kout);
+    S->id_in = (int32_t*)(b + o_idin); S->order = (int32_t*)(b + o_ord);
+    S->cnt_a = (int32_t*)(b + o_ca); S->cnt_b = (int32_t*)(b + o_cb);
+    S->scan_a = (int32_t*)(b + o_sa); S->scan_b = (int32_t*)(b + o_sb);
+    S->vbase_by_unit = (int32_t*)(b + o_vb);
+    S->cub_tmp = b + o_cub; S->cub_bytes = cub_bytes;
+    S->vinfo = mesh ? (uint32_t*)(b + o_vi) : nullptr;
+    return B2R_OK;
+}
+
+VolView make_view(const b2r_tsdf* h) {
+    VolView V;
+    V.hash = h->hash; V.unit_keys = h->unit_keys; V.pool = h->pool;
+    V.unit_stride = (int64_t)h->planes * B2R_UNIT_VOX; V.planes = h->planes;
+    V.voxel_length = h->voxel_length; V.unit_length = h->unit_length;
+    return V;
+}
+
+int sorted_order(b2r_tsdf* h, int n, Scratch& S, cudaStream_t stream) {
+    pack_keys_kernel<<<(n + 255) / 256, 256, 0, stream>>>(h->unit_keys, n, S.k_in, S.id_in);
+    B2R_CHECK_LAUNCH();
+    size_t tmp = S.cub_bytes;
+    B2R_CUDA(cub::DeviceRadixSort::SortPairs(S.cub_tmp, tmp, S.k_in, S.k_out, S.id_in, S.order, n, 0, 63, stream));
+    return B2R_OK;
+}
+
+}  // namespace
+
+// volume.extract_point_cloud().  Outputs (DEVICE, f64): xyz/rgb/nrm [capacity*3]; ids (optional int32
+// [capacity*4]) = global voxel coordinate of the edge's lower end + axis (the canonical sort key).
+// Call with xyz == NULL (or too small a capacity) to get the required count in *count and
+// B2R_ERR_CAPACITY; a second call with enough room fills.  Synchronises `stream` to read counts.
+B2R_API int b2r_tsdf_extract_points(b2r_tsdf* h, double* xyz, double* rgb, double* nrm, int32_t* ids, int64_t capacity,
+                                    int64_t* count, cudaStream_t stream) {
+    if (!h || !count) return B2R_ERR_BAD_ARG;
+    B2RDeviceGuard g(h->device);
+    int64_t st[5];
+    int rc = b2r_tsdf_stats(h, st, stream);
+    if (rc != B2R_OK) return rc;
+    const int n = (int)st[0];
+    *count = 0;
+    if (n == 0) return B2R_OK;
+    Scratch S;
+    rc = carve(h, n, false, &S);
+    if (rc != B2R_OK) return rc;
+    rc = sorted_order(h, n, S, stream);
+    if (rc != B2R_OK) return rc;
+    const VolView V = make_view(h);
+    extract_points_kernel<false><<<n, 256, 0, stream>>>(V, S.order, S.cnt_a, nullptr, nullptr, nullptr, nullptr, nullptr, 0);
+    B2R_CHECK_LAUNCH();
+    B2R_CUDA(cudaMemsetAsync(S.cnt_a + n, 0, 4, stream));
+    size_t tmp = S.cub_bytes;
+    B2R_CUDA(cub::DeviceScan::ExclusiveSum(S.cub_tmp, tmp, S.cnt_a, S.scan_a, n + 1, stream));
+    int32_t total = 0;
+    B2R_CUDA(cudaMemcpyAsync(&total, S.scan_a + n, 4, cudaMemcpyDeviceToHost, stream));
+    B2R_CUDA(cudaStreamSynchronize(stream));
+    *count = total;
+    if (!xyz || capacity < total) { b2r_set_error("extract_points: need capacity %d", total); return B2R_ERR_CAPACITY; }
+    if (total == 0) return B2R_OK;
+    extract_points_kernel<true><<<n, 256, 0, stream>>>(V, S.order, nullptr, S.scan_a, xyz, h->planes == 5 ? rgb : nullptr, nrm, ids, capacity);
+    B2R_CHECK_LAUNCH();
+    return B2R_OK;
+}
+
+// volume.extract_triangle_mesh().  Outputs (DEVICE): vtx/vcol f64 [capV*3], tri int32 [capF*3],
+// ids optional int32 [capV*4] = global integer edge id (X,Y,Z,axis) of each vertex.
+// Same two-call capacity protocol as extract_points (nV/nF always written).
+B2R_API int b2r_tsdf_extract_mesh(b2r_tsdf* h, double* vtx, double* vcol, int32_t* tri, int32_t* ids, int64_t capV,
+                                  int64_t capF, int64_t* nV, int64_t* nF, cudaStream_t stream) {
+    if (!h || !nV || !nF) return B2R_ERR_BAD_ARG;
+    B2RDeviceGuard g(h->device);
+    int64_t st[5];
+    int rc = b2r_tsdf_stats(h, st, stream);
+    if (rc != B2R_OK) return rc;
+    const int n = (int)st[0];
+    *nV = 0; *nF = 0;
+    if (n == 0) return B2R_OK;
+    Scratch S;
+    rc = carve(h, n, true, &S);
+    if (rc != B2R_OK) return rc;
+    rc = sorted_order(h, n, S, stream);
+    if (rc != B2R_OK) return rc;
+    const VolView V = make_view(h);
+    mesh_count_kernel<<<n, 256, 0, stream>>>(V, S.order, S.vinfo, S.cnt_a, S.cnt_b);
+    B2R_CHECK_LAUNCH();
+    B2R_CUDA(cudaMemsetAsync(S.cnt_a + n, 0, 4, stream));
+    B2R_CUDA(cudaMemsetAsync(S.cnt_b + n, 0, 4, stream));
+    size_t tmp = S.cub_bytes;
+    B2R_CUDA(cub::DeviceScan::ExclusiveSum(S.cub_tmp, tmp, S.cnt_a, S.scan_a, n + 1, stream));
+    tmp = S.cub_bytes;
+    B2R_CUDA(cub::DeviceScan::ExclusiveSum(S.cub_tmp, tmp, S.cnt_b, S.scan_b, n + 1, stream));
+    int32_t tv = 0, tf = 0;
+    B2R_CUDA(cudaMemcpyAsync(&tv, S.scan_a + n, 4, cudaMemcpyDeviceToHost, stream));
+    B2R_CUDA(cudaMemcpyAsync(&tf, S.scan_b + n, 4, cudaMemcpyDeviceToHost, stream));
+    B2R_CUDA(cudaStreamSynchronize(stream));
+    *nV = tv; *nF = tf;
+    if (!vtx || !tri || capV < tv || capF < tf) { b2r_set_error("extract_mesh: need capacity V=%d F=%d", tv, tf); return B2R_ERR_CAPACITY; }
+    if (tv == 0) return B2R_OK;
+    scatter_bases_kernel<<<(n + 255) / 256, 256, 0, stream>>>(S.order, S.scan_a, S.vbase_by_unit, n);
+    B2R_CHECK_LAUNCH();
+    mesh_fill_kernel<<<n, 256, 0, stream>>>(V, S.order, S.vinfo, S.vbase_by_unit, S.scan_b, vtx, h->planes == 5 ? vcol : nullptr, tri, ids, capV, capF);
+    B2R_CHECK_LAUNCH();
+    return B2R_OK;
+}
+
+// ---- TriangleMesh.compute_vertex_normals() (GoodColorReconstruction.py:286) --------
+namespace {
+__global__ void tri_normals_accumulate_kernel(const double* vtx, const int32_t* tri, int64_t nF, double* out) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nF) return;
+    const int i0 = tri[3 * t], i1 = tri[3 * t + 1], i2 = tri[3 * t + 2];
+    const double ax = vtx[3 * i0], ay = vtx[3 * i0 + 1], az = vtx[3 * i0 + 2];
+    const double e1x = xdsub(vtx[3 * i1], ax), e1y = xdsub(vtx[3 * i1 + 1], ay), e1z = xdsub(vtx[3 * i1 + 2], az);
+    const double e2x = xdsub(vtx[3 * i2], ax), e2y = xdsub(vtx[3 * i2 + 1], ay), e2z = xdsub(vtx[3 * i2 + 2], az);
+    double nx = xdsub(xdmul(e1y, e2z), xdmul(e1z, e2y)), ny = xdsub(xdmul(e1z, e2x), xdmul(e1x, e2z)), nz = xdsub(xdmul(e1x, e2y), xdmul(e1y, e2x));
+    const double len = sqrt(xdadd(xdadd(xdmul(nx, nx), xdmul(ny, ny)), xdmul(nz, nz)));
+    if (len > 0.0) { nx = xddiv(nx, len); ny = xddiv(ny, len); nz = xddiv(nz, len); }
+    const int idx[3] = {i0, i1, i2};
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        atomicAdd(&out[3 * idx[k]], nx); atomicAdd(&out[3 * idx[k] + 1], ny); atomicAdd(&out[3 * idx[k] + 2], nz);
+    }
+}
+__global__ void normalize_kernel(double* n, int64_t nV) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nV) return;
+    const double x = n[3 * i], y = n[3 * i + 1], z = n[3 * i + 2];
+    const double len = sqrt(xdadd(xdadd(xdmul(x, x), xdmul(y, y)), xdmul(z, z)));
+    if (len > 0.0) { n[3 * i] = xddiv(x, len); n[3 * i + 1] = xddiv(y, len); n[3 * i + 2] = xddiv(z, len); }
+}
+}  // namespace
+
+B2R_API int b2r_mesh_vertex_normals(const double* vtx, int64_t nV, const int32_t* tri, int64_t nF, double* out, cudaStream_t stream) {
+    if (!vtx || !tri || !out || nV < 0 || nF < 0) return B2R_ERR_BAD_ARG;
+    if (nV == 0) return B2R_OK;
+    B2R_CUDA(cudaMemsetAsync(out, 0, (size_t)nV * 24, stream));
+    if (nF) tri_normals_accumulate_kernel<<<(unsigned)((nF + 255) / 256), 256, 0, stream>>>(vtx, tri, nF, out);
+    B2R_CHECK_LAUNCH();
+    normalize_kernel<<<(unsigned)((nV + 255) / 256), 256, 0, stream>>>(out, nV);
+    B2R_CHECK_LAUNCH();
+    return B2R_OK;
+}

@@ -1,0 +1,370 @@
+"""o3d.geometry look-alikes backed by libb2recon.so: Image, RGBDImage, PointCloud, TriangleMesh.
+
+Same names, argument meaning and error behaviour as the Open3D 0.19 legacy API the reference calls
+(SURVEY.md 8(b)); data lives in torch CUDA tensors, numpy views on demand.  Reference call sites:
+Depth2PC.py:51-93, GoodColorReconstruction.py:124-139, BetterVisualizer2CamWorksCOLOR.py:515-541,634-640.
+"""
+from __future__ import annotations
+
+import copy as _copy
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _lib
+from .camera import PinholeCameraIntrinsic
+from .utility import Vector3dVector, Vector3iVector
+
+_IDENTITY = np.eye(4, dtype=np.float64)
+
+
+class Image:
+    """o3d.geometry.Image(np.ndarray): HxW u16 (1ch/2B), HxWx3|4 u8, HxW f32 (1ch/4B)."""
+
+    def __init__(self, data=None):
+        if data is None:
+            self.tensor = torch.empty((0, 0), dtype=torch.uint8)
+            return
+        if isinstance(data, Image):
+            self.tensor = data.tensor
+            return
+        if isinstance(data, torch.Tensor):
+            t = data
+        else:
+            arr = np.ascontiguousarray(np.asarray(data))
+            if arr.dtype == np.uint16:
+                t = torch.from_numpy(arr.view(np.int16)).view(torch.uint16)
+            else:
+                t = torch.from_numpy(arr)
+        if t.dim() not in (2, 3):
+            raise RuntimeError("Image: expected HxW or HxWxC data")
+        self.tensor = t.to(_lib.default_device()).contiguous()
+
+    @property
+    def height(self):
+        return int(self.tensor.shape[0]) if self.tensor.dim() >= 2 else 0
+
+    @property
+    def width(self):
+        return int(self.tensor.shape[1]) if self.tensor.dim() >= 2 else 0
+
+    @property
+    def channels(self):
+        return int(self.tensor.shape[2]) if self.tensor.dim() == 3 else 1
+
+    @property
+    def bytes_per_channel(self):
+        return self.tensor.element_size()
+
+    def is_empty(self):
+        return self.tensor.numel() == 0
+
+    def __array__(self, dtype=None, copy=None):
+        t = self.tensor.detach().cpu()
+        a = t.view(torch.int16).numpy().view(np.uint16) if t.dtype == torch.uint16 else t.numpy()
+        return a.astype(dtype) if dtype is not None else a
+
+    def __repr__(self):
+        return "Image of size %dx%d, with %d channels." % (self.width, self.height, self.channels)
+
+
+class RGBDImage:
+    def __init__(self):
+        self.color = Image()
+        self.depth = Image()
+
+    @staticmethod
+    def create_from_color_and_depth(color, depth, depth_scale: float = 1000.0, depth_trunc: float = 3.0,
+                                    convert_rgb_to_intensity: bool = True) -> "RGBDImage":
+        """RGBDImage::CreateFromColorAndDepth (Depth2PC.py:60-66, RGBD_Odometry.py:15-18)."""
+        color = color if isinstance(color, Image) else Image(color)
+        depth = depth if isinstance(depth, Image) else Image(depth)
+        if color.height != depth.height or color.width != depth.width:
+            raise RuntimeError("[CreateFromColorAndDepth] Unsupported image format.")
+        lib = _lib.load()
+        out = RGBDImage()
+        dt = depth.tensor
+        n = dt.numel()
+        if dt.dim() != 2:
+            raise RuntimeError("[CreateFromColorAndDepth] Unsupported image format.")
+        if dt.dtype == torch.uint16:
+            _lib.require_cuda()
+            f = torch.empty(dt.shape, dtype=torch.float32, device=dt.device)
+            _lib.check(lib.b2r_depth_to_float(_lib.ptr(dt), n, float(depth_scale), float(depth_trunc), _lib.ptr(f), _lib.stream_ptr()))
+        elif dt.dtype == torch.float32:
+            f = dt / np.float32(depth_scale)          # ConvertDepthToFloatImage on an f32 image
+            f = torch.where(f >= np.float32(depth_trunc), torch.zeros_like(f), f)
+        elif dt.dtype == torch.uint8:
+            f = dt.to(torch.float32) / np.float32(255.0) / np.float32(depth_scale)
+            f = torch.where(f >= np.float32(depth_trunc), torch.zeros_like(f), f)
+        else:
+            raise RuntimeError("[CreateFromColorAndDepth] Unsupported image format.")
+        out.depth = Image(f)
+        ct = color.tensor
+        if convert_rgb_to_intensity:
+            if ct.dtype == torch.uint8 and ct.dim() == 3 and ct.shape[2] in (3, 4):
+                _lib.require_cuda()
+                g = torch.empty(ct.shape[:2], dtype=torch.float32, device=ct.device)
+                _lib.check(lib.b2r_rgb_to_intensity(_lib.ptr(ct), ct.shape[0] * ct.shape[1], int(ct.shape[2]), 0, _lib.ptr(g), _lib.stream_ptr()))
+                out.color = Image(g)
+            elif ct.dtype == torch.uint8 and ct.dim() == 2:
+                out.color = Image(ct.to(torch.float32) / np.float32(255.0))
+            elif ct.dtype == torch.float32 and ct.dim() == 2:
+                out.color = Image(ct.clone())
+            else:
+                raise RuntimeError("[CreateFloatImage] Unsupported image format.")
+        else:
+            out.color = color
+        return out
+
+    def __repr__(self):
+        return "RGBDImage of size \nColor image : %dx%d, with %d channels.\nDepth image : %dx%d, with %d channels." % (
+            self.color.width, self.color.height, self.color.channels, self.depth.width, self.depth.height, self.depth.channels)
+
+
+def _as_vec3d(v) -> Vector3dVector:
+    return v if isinstance(v, Vector3dVector) else Vector3dVector(v)
+
+
+def unproject(depth: torch.Tensor, intrinsic: PinholeCameraIntrinsic, *, depth_is_u16=False, depth_scale=1000.0,
+              depth_trunc=1000.0, color: Optional[torch.Tensor] = None, color_bgr=False, gray: Optional[torch.Tensor] = None,
+              color_intrinsic: Optional[PinholeCameraIntrinsic] = None, depth_to_color: Optional[np.ndarray] = None,
+              transforms=None, stride=1, dtype=torch.float64, valid_only=True, want_index=False, want_gather_index=False):
+    """Batched fused unprojection (b2r_unproject). depth: (B,H,W) or (H,W) device tensor.
+
+    ``transforms``: (B,4,4) camera->output matrices (default identity).  Returns a dict with ``xyz``
+    (B,cap,3), ``rgb`` or None, ``counts`` (B,) int32 device tensor, optional ``src_index``/``gather_index``.
+    """
+    dev = _lib.require_cuda()
+    lib = _lib.load()
+    if depth.dim() == 2:
+        depth = depth[None]
+    depth = depth.contiguous()
+    B, H, W = depth.shape
+    cap = ((W + stride - 1) // stride) * ((H + stride - 1) // stride)
+    f64 = dtype == torch.float64
+    if transforms is None:
+        transforms = np.tile(_IDENTITY, (B, 1, 1))
+    T = torch.as_tensor(np.ascontiguousarray(np.asarray(transforms, dtype=np.float64).reshape(B, 16)), device=dev)
+    xyz = torch.empty((B, cap, 3), dtype=dtype, device=dev)
+    has_col = color is not None or gray is not None
+    rgb = torch.empty((B, cap, 3), dtype=dtype, device=dev) if has_col else None
+    src = torch.empty((B, cap), dtype=torch.int32, device=dev) if want_index else None
+    gidx = torch.empty((B, cap), dtype=torch.int32, device=dev) if want_gather_index else None
+    counts = torch.empty((B,), dtype=torch.int32, device=dev)
+    scratch = torch.empty((int(lib.b2r_unproject_scratch_words(W, H, B, stride, 1 if f64 else 0)),), dtype=torch.int32, device=dev)
+    cch, Wc, Hc = 0, 0, 0
+    if color is not None:
+        color = color.contiguous()
+        if color.dim() == 3:
+            color = color[None]
+        cch, Hc, Wc = int(color.shape[3]), int(color.shape[1]), int(color.shape[2])
+    K = _lib.dbl4(*intrinsic.fxfycxcy())
+    Kc = _lib.dbl4(*color_intrinsic.fxfycxcy()) if color_intrinsic is not None else None
+    d2c = _lib.dbl16(depth_to_color) if depth_to_color is not None else None
+    rc = lib.b2r_unproject(_lib.ptr(depth), 1 if depth_is_u16 else 0, float(depth_scale), float(depth_trunc), W, H, B,
+                           _lib.ptr(color), cch, 1 if color_bgr else 0, Wc, Hc, _lib.ptr(gray.contiguous() if gray is not None else None),
+                           K, Kc, d2c, _lib.ptr(T), int(stride), 1 if f64 else 0, 1 if valid_only else 0,
+                           _lib.ptr(xyz), _lib.ptr(rgb), _lib.ptr(src), _lib.ptr(gidx), cap, _lib.ptr(counts), _lib.ptr(scratch),
+                           _lib.stream_ptr())
+    _lib.check(rc, "unproject")
+    return dict(xyz=xyz, rgb=rgb, counts=counts, src_index=src, gather_index=gidx, capacity=cap)
+
+
+class PointCloud:
+    def __init__(self, points=None):
+        self._points = _as_vec3d(points) if points is not None else Vector3dVector()
+        self._colors = Vector3dVector()
+        self._normals = Vector3dVector()
+        self.source_index = None    # int32 raster index per point (build extension; parity checks use it)
+
+    # attribute protocol of the legacy API: assignable Vector3dVector-s
+    points = property(lambda s: s._points, lambda s, v: setattr(s, "_points", _as_vec3d(v)))
+    colors = property(lambda s: s._colors, lambda s, v: setattr(s, "_colors", _as_vec3d(v)))
+    normals = property(lambda s: s._normals, lambda s, v: setattr(s, "_normals", _as_vec3d(v)))
+
+    def has_points(self):
+        return len(self._points) > 0
+
+    def has_colors(self):
+        return len(self._points) > 0 and len(self._colors) == len(self._points)
+
+    def has_normals(self):
+        return len(self._points) > 0 and len(self._normals) == len(self._points)
+
+    def is_empty(self):
+        return not self.has_points()
+
+    def clear(self):
+        self.__init__()
+        return self
+
+    # ---- factories ---------------------------------------------------------------------------------
+    @staticmethod
+    def create_from_rgbd_image(image: RGBDImage, intrinsic: PinholeCameraIntrinsic, extrinsic=_IDENTITY,
+                               project_valid_depth_only: bool = True, dtype=torch.float64) -> "PointCloud":
+        """PointCloud::CreateFromRGBDImage (Depth2PC.py:69-74)."""
+        d, c = image.depth.tensor, image.color.tensor
+        if d.dtype != torch.float32 or d.dim() != 2:
+            raise RuntimeError("[CreatePointCloudFromRGBDImage] Unsupported image format.")
+        pose = _lib.m4_inverse(np.asarray(extrinsic, dtype=np.float64))
+        kw = {}
+        if c.dtype == torch.uint8 and c.dim() == 3 and c.shape[2] == 3:
+            kw["color"] = c
+        elif c.dtype == torch.float32 and c.dim() == 2:
+            kw["gray"] = c
+        else:
+            raise RuntimeError("[CreatePointCloudFromRGBDImage] Unsupported image format.")
+        if tuple(c.shape[:2]) != tuple(d.shape):
+            raise RuntimeError("[CreatePointCloudFromRGBDImage] Unsupported image format.")
+        r = unproject(d, intrinsic, transforms=pose[None], dtype=dtype, valid_only=project_valid_depth_only, want_index=True, **kw)
+        n = int(r["counts"][0].item())
+        pcd = PointCloud()
+        pcd._points = Vector3dVector(r["xyz"][0, :n])
+        pcd._colors = Vector3dVector(r["rgb"][0, :n])
+        pcd.source_index = r["src_index"][0, :n]
+        return pcd
+
+    @staticmethod
+    def create_from_depth_image(depth: Image, intrinsic: PinholeCameraIntrinsic, extrinsic=_IDENTITY,
+                                depth_scale: float = 1000.0, depth_trunc: float = 1000.0, stride: int = 1,
+                                project_valid_depth_only: bool = True, dtype=torch.float64) -> "PointCloud":
+        """PointCloud::CreateFromDepthImage (Depth2PC.py:77-84)."""
+        depth = depth if isinstance(depth, Image) else Image(depth)
+        d = depth.tensor
+        if d.dim() != 2 or d.dtype not in (torch.uint16, torch.float32):
+            raise RuntimeError("[CreatePointCloudFromDepthImage] Unsupported image format.")
+        pose = _lib.m4_inverse(np.asarray(extrinsic, dtype=np.float64))
+        r = unproject(d, intrinsic, depth_is_u16=(d.dtype == torch.uint16), depth_scale=depth_scale, depth_trunc=depth_trunc,
+                      transforms=pose[None], stride=stride, dtype=dtype, valid_only=project_valid_depth_only, want_index=True)
+        n = int(r["counts"][0].item())
+        pcd = PointCloud()
+        pcd._points = Vector3dVector(r["xyz"][0, :n])
+        pcd.source_index = r["src_index"][0, :n]
+        return pcd
+
+    @staticmethod
+    def create_from_kinect_capture(depth_u16, color_bgra, depth_intrinsic: PinholeCameraIntrinsic,
+                                   color_intrinsic: PinholeCameraIntrinsic, depth_to_color: np.ndarray,
+                                   extrinsic=_IDENTITY, post_transform=None, depth_scale=1000.0, depth_trunc=3.0,
+                                   dtype=torch.float32) -> "PointCloud":
+        """Fused Azure-Kinect path (north_star subsystem 1): native-grid u16 depth + 720p BGRA colour ->
+        coloured cloud, with the colour-to-depth gather, BGRA swizzle, depth conversion and the output
+        transform (e.g. flip @ camera extrinsic, BetterVisualizer2CamWorksCOLOR.py:534,634-640) in one pass."""
+        depth = depth_u16 if isinstance(depth_u16, Image) else Image(depth_u16)
+        color = color_bgra if isinstance(color_bgra, Image) else Image(color_bgra)
+        T = _lib.m4_inverse(np.asarray(extrinsic, dtype=np.float64))
+        if post_transform is not None:
+            T = _lib.m4_mul(np.asarray(post_transform, dtype=np.float64), T)
+        r = unproject(depth.tensor, depth_intrinsic, depth_is_u16=True, depth_scale=depth_scale, depth_trunc=depth_trunc,
+                      color=color.tensor, color_bgr=True, color_intrinsic=color_intrinsic, depth_to_color=depth_to_color,
+                      transforms=T[None], dtype=dtype, want_index=True, want_gather_index=True)
+        n = int(r["counts"][0].item())
+        pcd = PointCloud()
+        pcd._points = Vector3dVector(r["xyz"][0, :n])
+        pcd._colors = Vector3dVector(r["rgb"][0, :n])
+        pcd.source_index = r["src_index"][0, :n]
+        pcd.gather_index = r["gather_index"][0, :n]
+        return pcd
+
+    # ---- transforms / merging ----------------------------------------------------------------------
+    def transform(self, T) -> "PointCloud":
+        """Geometry3D::Transform (Depth2PC.py:87-93). Returns self."""
+        if len(self._points):
+            _lib.require_cuda()
+            nrm = self._normals.tensor if self.has_normals() else None
+            _lib.check(_lib.load().b2r_transform_points(_lib.ptr(self._points.tensor), _lib.ptr(nrm), len(self._points), 1,
+                                                         _lib.dbl16(T), _lib.stream_ptr()))
+        return self
+
+    def __iadd__(self, o: "PointCloud") -> "PointCloud":
+        """PointCloud::operator+=: keep an attribute only if both sides carry it."""
+        if o.is_empty():
+            return self
+        old_n = len(self._points)
+        keep_n = (old_n == 0 or self.has_normals()) and o.has_normals()
+        keep_c = (old_n == 0 or self.has_colors()) and o.has_colors()
+        self._normals = Vector3dVector(torch.cat([self._normals.tensor[:old_n], o._normals.tensor])) if keep_n else Vector3dVector()
+        self._colors = Vector3dVector(torch.cat([self._colors.tensor[:old_n], o._colors.tensor])) if keep_c else Vector3dVector()
+        self._points = Vector3dVector(torch.cat([self._points.tensor, o._points.tensor]))
+        self.source_index = None
+        return self
+
+    def __add__(self, o: "PointCloud") -> "PointCloud":
+        r = _copy.deepcopy(self)
+        r += o
+        return r
+
+    def __deepcopy__(self, memo):
+        r = PointCloud()
+        r._points = Vector3dVector(self._points.tensor.clone())
+        r._colors = Vector3dVector(self._colors.tensor.clone())
+        r._normals = Vector3dVector(self._normals.tensor.clone())
+        r.source_index = None if self.source_index is None else self.source_index.clone()
+        return r
+
+    def __repr__(self):
+        return "PointCloud with %d points." % len(self._points)
+
+
+class TriangleMesh:
+    def __init__(self):
+        self._vertices = Vector3dVector()
+        self._vertex_colors = Vector3dVector()
+        self._vertex_normals = Vector3dVector()
+        self._triangles = Vector3iVector()
+        self.edge_ids = None   # int32 (V,4) global edge id per vertex (build extension for parity checks)
+
+    vertices = property(lambda s: s._vertices, lambda s, v: setattr(s, "_vertices", _as_vec3d(v)))
+    vertex_colors = property(lambda s: s._vertex_colors, lambda s, v: setattr(s, "_vertex_colors", _as_vec3d(v)))
+    vertex_normals = property(lambda s: s._vertex_normals, lambda s, v: setattr(s, "_vertex_normals", _as_vec3d(v)))
+    triangles = property(lambda s: s._triangles,
+                         lambda s, v: setattr(s, "_triangles", v if isinstance(v, Vector3iVector) else Vector3iVector(v)))
+
+    def has_vertices(self):
+        return len(self._vertices) > 0
+
+    def has_triangles(self):
+        return len(self._vertices) > 0 and len(self._triangles) > 0
+
+    def has_vertex_normals(self):
+        return len(self._vertices) > 0 and len(self._vertex_normals) == len(self._vertices)
+
+    def has_vertex_colors(self):
+        return len(self._vertices) > 0 and len(self._vertex_colors) == len(self._vertices)
+
+    def is_empty(self):
+        return not self.has_vertices()
+
+    def compute_vertex_normals(self, normalized: bool = True) -> "TriangleMesh":
+        """TriangleMesh::ComputeVertexNormals (GoodColorReconstruction.py:286)."""
+        nV, nF = len(self._vertices), len(self._triangles)
+        if nV == 0:
+            return self
+        _lib.require_cuda()
+        out = torch.empty((nV, 3), dtype=torch.float64, device=self._vertices.tensor.device)
+        _lib.check(_lib.load().b2r_mesh_vertex_normals(_lib.ptr(self._vertices.tensor), nV, _lib.ptr(self._triangles.tensor), nF,
+                                                        _lib.ptr(out), _lib.stream_ptr()))
+        self._vertex_normals = Vector3dVector(out)
+        return self
+
+    def transform(self, T) -> "TriangleMesh":
+        if len(self._vertices):
+            _lib.require_cuda()
+            nrm = self._vertex_normals.tensor if self.has_vertex_normals() else None
+            _lib.check(_lib.load().b2r_transform_points(_lib.ptr(self._vertices.tensor), _lib.ptr(nrm), len(self._vertices), 1,
+                                                         _lib.dbl16(T), _lib.stream_ptr()))
+        return self
+
+    def __deepcopy__(self, memo):
+        r = TriangleMesh()
+        r._vertices = Vector3dVector(self._vertices.tensor.clone())
+        r._vertex_colors = Vector3dVector(self._vertex_colors.tensor.clone())
+        r._vertex_normals = Vector3dVector(self._vertex_normals.tensor.clone())
+        r._triangles = Vector3iVector(self._triangles.tensor.clone())
+        return r
+
+    def __repr__(self):
+        return "TriangleMesh with %d points and %d triangles." % (len(self._vertices), len(self._triangles))

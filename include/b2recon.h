@@ -1,0 +1,158 @@
+/* b2recon.h -- C-ABI of libb2recon.so: the B200-native RGB-D reconstruction core.
+ *
+ * This is the drop-in boundary for the one hot path of mishn-0/AzureKinect3DReconstruction: the
+ * Open3D 0.19.0 legacy calls its scripts make (the scripts are pure call sites; the arithmetic is in
+ * open3d==0.19.0, pinned at /root/reference/pyproject.toml:15).  Every entry point names the reference
+ * call it replaces.  The reference binds this path through Open3D's pybind11 module; the ctypes binding
+ * a maintainer would add instead is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *  - All image / point / mesh pointers are DEVICE pointers (torch CUDA tensors) unless the name says
+ *    "_host".  4x4 matrices are row-major f64.  Intrinsics are (fx, fy, cx, cy) f64.
+ *  - Every call is asynchronous on `stream` unless it returns a count (then it synchronises `stream`).
+ *  - Return value: 0 = OK, <0 = error (codes below); b2r_last_error() gives the message (thread-local).
+ *  - The caller owns every buffer it passes; the library owns only what lives behind a handle.
+ *  - There is no CPU fallback: without a CUDA device every compute call fails with B2R_ERR_CUDA.
+ */
+#ifndef B2RECON_H
+#define B2RECON_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef __CUDA_RUNTIME_H__
+typedef struct CUstream_st* cudaStream_t;
+#endif
+
+#define B2R_OK 0
+#define B2R_ERR_BAD_ARG (-1)
+#define B2R_ERR_CUDA (-2)
+#define B2R_ERR_CAPACITY (-3) /* output / pool too small; the required size is reported */
+#define B2R_ERR_FORMAT (-4)   /* upstream utility::LogError("Unsupported image format.") conditions */
+#define B2R_ERR_SINGULAR (-5)
+#define B2R_ERR_RANGE (-6)
+
+#define B2R_COLOR_NONE 0   /* TSDFVolumeColorType.NoColor */
+#define B2R_COLOR_RGB8 1   /* TSDFVolumeColorType.RGB8    */
+#define B2R_COLOR_GRAY32 2 /* TSDFVolumeColorType.Gray32  */
+
+typedef struct b2r_tsdf b2r_tsdf;
+
+int b2r_version(void);
+const char* b2r_last_error(void);
+
+/* f64 pose algebra shared by every caller (host).  Upstream: Eigen Matrix4d::inverse(), SURVEY A.3. */
+int b2r_m4_inverse(const double* in16, double* out16);
+void b2r_m4_mul(const double* a16, const double* b16, double* out16);
+
+/* ---- a1: RGBDImage.create_from_color_and_depth pieces (Depth2PC.py:60-66,
+ *      GoodColorReconstruction.py:131-137, RGBD_Odometry.py:15-18).  Normally fused into consumers. */
+int b2r_depth_to_float(const uint16_t* depth, int64_t n, float depth_scale, float depth_trunc, float* out,
+                       cudaStream_t stream);
+int b2r_rgb_to_intensity(const uint8_t* rgb, int64_t n, int channels, int bgr, float* out, cudaStream_t stream);
+
+/* ---- a3/a4/a5/a6: PointCloud.create_from_rgbd_image / create_from_depth_image (+ fused a1 conversion,
+ *      BGRA swizzle, colour-to-depth gather and output transform), batched over B same-shaped frames.
+ *      Reference: Depth2PC.py:69-93, BetterVisualizer2CamWorksCOLOR.py:515-541,634-640,
+ *      InitialReconstruction-CUDA-2cam:639-646,743-755.
+ *  depth        u16 (depth_is_u16=1; scaled by depth_scale, zeroed at >= depth_trunc) or f32 metres
+ *  color        u8, 3 or 4 channels, same WxH as depth -- or, when color_K and d2c_host are given, a
+ *               Wc x Hc image in its own camera (gather). color_bgr=1 swaps channel 0 and 2. May be NULL.
+ *  gray         f32 intensity image (colour of a convert_rgb_to_intensity RGBDImage). May be NULL.
+ *  depth_K      HOST (fx,fy,cx,cy); color_K HOST or NULL; d2c_host HOST 16 f64 depth->colour or NULL
+ *  T_dev        DEVICE B*16 f64: camera -> output transform (= extrinsic^-1, optionally pre-multiplied
+ *               by the flip / per-camera pose)
+ *  out_f64      1: xyz/rgb are f64 and follow the upstream f64 chain exactly; 0: f32 throughput path
+ *  valid_only   project_valid_depth_only
+ *  xyz,rgb      [B][capacity][3]; src_index / gather_index (optional) [B][capacity] int32: raster index
+ *               of the source depth pixel / gathered colour texel (-1 = outside the colour image)
+ *  counts       DEVICE int32[B]; scratch DEVICE int32[b2r_unproject_scratch_words(...)]               */
+int64_t b2r_unproject_scratch_words(int W, int H, int B, int stride, int out_f64);
+int b2r_unproject(const void* depth, int depth_is_u16, float depth_scale, float depth_trunc, int W, int H, int B,
+                  const uint8_t* color, int color_channels, int color_bgr, int Wc, int Hc, const float* gray,
+                  const double* depth_K, const double* color_K, const double* d2c_host, const double* T_dev,
+                  int stride, int out_f64, int valid_only, void* xyz, void* rgb, int32_t* src_index,
+                  int32_t* gather_index, int64_t capacity, int32_t* counts, int32_t* scratch, cudaStream_t stream);
+
+/* pcd.transform(T) / mesh.transform(T)  (Depth2PC.py:87-93, bundlefusion_reconstruction.py:323-324) */
+int b2r_transform_points(void* xyz, void* normals, int64_t n, int is_f64, const double* T_host, cudaStream_t stream);
+
+/* ---- a7: ScalableTSDFVolume(voxel_length, sdf_trunc, color_type, volume_unit_resolution=16,
+ *      depth_sampling_stride=4)  (GoodColorReconstruction.py:111-115, bundlefusion_reconstruction.py:108-112).
+ *      capacity_units: size of the zeroed unit pool (80 KiB per RGB8 unit).  rank/world: this handle
+ *      keeps only the units whose key hashes to `rank`; 0/1 for a single GPU. */
+b2r_tsdf* b2r_tsdf_create(double voxel_length, double sdf_trunc, int color_type, int unit_resolution,
+                          int depth_sampling_stride, int64_t capacity_units, int rank, int world);
+void b2r_tsdf_destroy(b2r_tsdf* h);
+int b2r_tsdf_reset(b2r_tsdf* h, cudaStream_t stream); /* volume.reset(), bundlefusion_reconstruction.py:309 */
+double b2r_tsdf_voxel_length(b2r_tsdf* h);
+double b2r_tsdf_sdf_trunc(b2r_tsdf* h);
+int b2r_tsdf_color_type(b2r_tsdf* h);
+int64_t b2r_tsdf_capacity(b2r_tsdf* h);
+
+/* ---- a8+a9: volume.integrate(rgbd, intrinsic, extrinsic)  (GoodColorReconstruction.py:270,
+ *      BetterVisualizer2CamWorksCOLOR.py:319, capture_frames.py:157, WORKSkinda.py:546-551).
+ *      extrinsic: HOST 16 f64 world->camera.  Images as in b2r_unproject (aligned colour only). */
+int b2r_tsdf_integrate(b2r_tsdf* h, const void* depth, int depth_is_u16, float depth_scale, float depth_trunc,
+                       const uint8_t* color, int color_channels, int color_bgr, const float* gray, int W, int H,
+                       double fx, double fy, double cx, double cy, const double* extrinsic_host, cudaStream_t stream);
+/* n frames stored back to back (the reset + re-integrate loop, bundlefusion_reconstruction.py:309-315) */
+int b2r_tsdf_integrate_batch(b2r_tsdf* h, int n, const void* depth, int depth_is_u16, float depth_scale,
+                             float depth_trunc, const uint8_t* color, int color_channels, int color_bgr, int W,
+                             int H, double fx, double fy, double cx, double cy, const double* extrinsics_host,
+                             cudaStream_t stream);
+/* same with HOST images: H2D copies overlap fusion through an internal 3-deep device ring */
+int b2r_tsdf_integrate_host(b2r_tsdf* h, int n, const void* depth_host, int depth_is_u16, float depth_scale,
+                            float depth_trunc, const uint8_t* color_host, int color_channels, int color_bgr, int W,
+                            int H, double fx, double fy, double cx, double cy, const double* extrinsics_host,
+                            cudaStream_t stream);
+
+/* out[0]=units allocated, out[1]=error bits, out[2]=units touched by the last frame,
+ * out[3]=cumulative updated voxels (N_upd), out[4]=cumulative touched units.  Synchronises. */
+int b2r_tsdf_stats(b2r_tsdf* h, int64_t* out5_host, cudaStream_t stream);
+int64_t b2r_tsdf_num_units(b2r_tsdf* h, cudaStream_t stream);
+/* parity / checkpoint hooks: keys int32[n][3]; planes tsdf[n][4096], weight[n][4096], rgb[n][3][4096],
+ * voxel index x*256 + y*16 + z (upstream IndexOf) */
+int b2r_tsdf_export_keys(b2r_tsdf* h, int32_t* keys3, int64_t n, cudaStream_t stream);
+int b2r_tsdf_export_units(b2r_tsdf* h, int64_t first, int64_t count, float* tsdf, float* weight, float* rgb,
+                          cudaStream_t stream);
+int b2r_tsdf_import_units(b2r_tsdf* h, const int32_t* keys3, int64_t n, const float* tsdf, const float* weight,
+                          const float* rgb, cudaStream_t stream);
+
+/* ---- a10: volume.extract_point_cloud()  (GoodColorReconstruction.py:305,542).  f64 outputs.
+ *      Two-call protocol: xyz==NULL or capacity too small -> *count set, returns B2R_ERR_CAPACITY. */
+int b2r_tsdf_extract_points(b2r_tsdf* h, double* xyz, double* rgb, double* nrm, int32_t* ids4, int64_t capacity,
+                            int64_t* count_host, cudaStream_t stream);
+/* ---- a11: volume.extract_triangle_mesh()  (GoodColorReconstruction.py:285,536) */
+int b2r_tsdf_extract_mesh(b2r_tsdf* h, double* vtx, double* vcol, int32_t* tri, int32_t* ids4, int64_t capV,
+                          int64_t capF, int64_t* nV_host, int64_t* nF_host, cudaStream_t stream);
+/* mesh.compute_vertex_normals()  (GoodColorReconstruction.py:286) */
+int b2r_mesh_vertex_normals(const double* vtx, int64_t nV, const int32_t* tri, int64_t nF, double* out,
+                            cudaStream_t stream);
+
+/* ---- a12: o3d.pipelines.odometry.compute_rgbd_odometry  (RGBD_Odometry.py:26-35,
+ *      capture_frames.py:148-151, bundlefusion_reconstruction.py:224-227).
+ *      Images: f32 intensity + f32 depth (metres), W x H, DEVICE.  jac_kind 0 = colour term, 1 = hybrid.
+ *      iters_host[n_levels]: iterations per pyramid level, coarsest first ([20,10,5]).
+ *      out_T_host 16 f64 (source->target), out_info_host 36 f64, *success_host 0/1.  Synchronises. */
+int b2r_odometry(const float* src_gray, const float* src_depth, const float* tgt_gray, const float* tgt_depth, int W,
+                 int H, double fx, double fy, double cx, double cy, const double* init_host, int jac_kind,
+                 const int* iters_host, int n_levels, double depth_diff_max, double depth_min, double depth_max,
+                 double* out_T_host, double* out_info_host, int* success_host, cudaStream_t stream);
+
+/* ---- a13: registration_icp(..., TransformationEstimationPointToPlane(), ICPConvergenceCriteria(...))
+ *      (GoodColorReconstruction.py:194-198, BetterVisualizer2CamWorksCOLOR.py:255-259).
+ *      src_xyz N*3, tgt_xyz/tgt_nrm M*3 f64 DEVICE.  corr (optional) DEVICE int32[N]: target index or -1.
+ *      Returns iterations executed (>= 0) or an error code; synchronises. */
+int b2r_icp_point_to_plane(const double* src_xyz, int64_t N, const double* tgt_xyz, const double* tgt_nrm, int64_t M,
+                           double max_dist, const double* init_host, int max_iter, double rel_fitness,
+                           double rel_rmse, double* out_T_host, double* fitness_host, double* rmse_host,
+                           int32_t* corr, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2RECON_H */
