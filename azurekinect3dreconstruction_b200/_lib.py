@@ -45,6 +45,8 @@ SIGNATURES = {
     "b2r_tsdf_integrate_batch": (_i, [_vp, _i, _vp, _i, _f, _f, _vp, _i, _i, _i, _i, _d, _d, _d, _d, _pd, _vp]),
     "b2r_tsdf_integrate_host": (_i, [_vp, _i, _vp, _i, _f, _f, _vp, _i, _i, _i, _i, _d, _d, _d, _d, _pd, _vp]),
     "b2r_tsdf_stats": (_i, [_vp, _pi64, _vp]),
+    "b2r_tsdf_profile": (_i, [_vp, _i]),
+    "b2r_tsdf_profile_read": (_i, [_vp, _pd]),
     "b2r_tsdf_num_units": (_i64, [_vp, _vp]),
     "b2r_tsdf_export_keys": (_i, [_vp, _vp, _i64, _vp]),
     "b2r_tsdf_export_units": (_i, [_vp, _i64, _i64, _vp, _vp, _vp, _vp]),
@@ -53,6 +55,8 @@ SIGNATURES = {
     "b2r_tsdf_extract_mesh": (_i, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _pi64, _pi64, _vp]),
     "b2r_mesh_vertex_normals": (_i, [_vp, _i64, _vp, _i64, _vp, _vp]),
     "b2r_odometry": (_i, [_vp, _vp, _vp, _vp, _i, _i, _d, _d, _d, _d, _pd, _i, _pi, _i, _d, _d, _d, _pd, _pd, _pi, _vp]),
+    "b2r_image_filter": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "b2r_image_downsample": (_i, [_vp, _i, _i, _vp, _vp]),
     "b2r_icp_point_to_plane": (_i, [_vp, _i64, _vp, _vp, _i64, _d, _pd, _i, _d, _d, _pd, _pd, _pd, _vp, _vp]),
 }
 
@@ -113,7 +117,7 @@ def stream_ptr() -> C.c_void_p:
 def dbl16(m) -> "C.Array":
     a = np.ascontiguousarray(np.asarray(m, dtype=np.float64).reshape(-1))
     assert a.size % 16 == 0
-    return (C.c_double * a.size)(*a.tolist())
+    return (C.c_double * a.size).from_buffer_copy(a)
 
 
 def dbl4(fx, fy, cx, cy) -> "C.Array":

@@ -1,0 +1,388 @@
+// icp.cu -- point-to-plane ICP on sm_100a (north_star subsystem 4, second half).
+//
+// Replaces o3d.pipelines.registration.registration_icp(src, tgt, max_dist, init,
+//   TransformationEstimationPointToPlane(), ICPConvergenceCriteria(...))
+// (/root/reference/CodeThatWorks/GoodColorReconstruction.py:194-198,
+//  CodeThatWorks/BetterVisualizer2CamWorksCOLOR.py:255-259, azure-kinect-DK/Reconstruction/Reconstruction.py:129-133);
+// upstream semantics restated in SURVEY.md Appendix A.7.
+//
+// Design: upstream builds a FLANN kd-tree and loops on the host.  Here the target is binned once into a
+// uniform grid (cell = max_dist; cub radix sort of cell ids), and ONE kernel per ICP iteration does
+//   apply the previous update U to every source point -> exact 1-NN within max_dist over the <=27
+//   neighbouring cells -> residual + Jacobian row -> f64 reduction of JtJ/Jtr/err^2/count
+//   (warp shuffles -> shared memory -> per-block partials) -> the last block solves the 6x6 system,
+//   accumulates T <- U*T, evaluates fitness / inlier_rmse and the convergence test, all on the device.
+// The host only reads the final state.
+#include "common.cuh"
+#include "host_math.h"
+#include <cub/cub.cuh>
+#include <math.h>
+
+namespace {
+
+#define ICP_THREADS 256
+#define ICP_NV 30     // 21 JtJ + 6 Jtr + r2 + err2 + count
+
+struct IcpGrid {
+    double lo[3];
+    double cell;
+    int dim[3];
+};
+
+struct IcpState {
+    double T[16];          // accumulated transformation
+    double U[16];          // update to apply to the working cloud at the next launch
+    double fitness, rmse, prev_fitness, prev_rmse;
+    long long n_corr;
+    int done, iters, launches;
+    unsigned ticket;
+    double bounds[6];      // target min xyz, max xyz
+};
+
+__global__ void __launch_bounds__(1024) bounds_kernel(const double* __restrict__ p, long long M, IcpState* st) {
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    for (long long i = threadIdx.x; i < M; i += blockDim.x)
+#pragma unroll
+        for (int k = 0; k < 3; k++) { const double v = p[3 * i + k]; lo[k] = fmin(lo[k], v); hi[k] = fmax(hi[k], v); }
+    __shared__ double s[32][6];
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[k] = fmin(lo[k], __shfl_down_sync(0xffffffffu, lo[k], o));
+            hi[k] = fmax(hi[k], __shfl_down_sync(0xffffffffu, hi[k], o));
+        }
+    if ((threadIdx.x & 31) == 0)
+        for (int k = 0; k < 3; k++) { s[threadIdx.x >> 5][k] = lo[k]; s[threadIdx.x >> 5][3 + k] = hi[k]; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int)(blockDim.x >> 5); w++)
+            for (int k = 0; k < 3; k++) { s[0][k] = fmin(s[0][k], s[w][k]); s[0][3 + k] = fmax(s[0][3 + k], s[w][3 + k]); }
+        for (int k = 0; k < 6; k++) st->bounds[k] = s[0][k];
+    }
+}
+
+__device__ __forceinline__ int grid_coord(const IcpGrid& g, double v, int k) {
+    const int c = (int)floor(xddiv(xdsub(v, g.lo[k]), g.cell));
+    return min(max(c, 0), g.dim[k] - 1);
+}
+
+__global__ void cell_id_kernel(const double* __restrict__ p, int M, const IcpGrid g, unsigned* cid, int* idx) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= M) return;
+    const int a = grid_coord(g, p[3 * i], 0), b = grid_coord(g, p[3 * i + 1], 1), c = grid_coord(g, p[3 * i + 2], 2);
+    cid[i] = (unsigned)((a * g.dim[1] + b) * g.dim[2] + c);
+    idx[i] = i;
+}
+
+__global__ void cell_range_kernel(const unsigned* __restrict__ cid_sorted, int M, int* cell_start, int* cell_end) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= M) return;
+    const unsigned c = cid_sorted[i];
+    if (i == 0 || cid_sorted[i - 1] != c) cell_start[c] = i;
+    if (i == M - 1 || cid_sorted[i + 1] != c) cell_end[c] = i + 1;
+}
+
+__global__ void copy_points_kernel(const double* __restrict__ in, double* out, long long n3) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n3) out[i] = in[i];
+}
+
+__device__ bool icp_ldlt6(const double* A_in, const double* b_in, double* x) {
+    const int n = 6;
+    double A[36], L[36], D[6], y[6], z[6];
+    int perm[6];
+    for (int i = 0; i < 36; i++) { A[i] = A_in[i]; L[i] = 0.0; }
+    for (int i = 0; i < n; i++) perm[i] = i;
+    for (int k = 0; k < n; k++) {
+        int p = k;
+        double best = fabs(A[k * n + k]);
+        for (int i = k + 1; i < n; i++) if (fabs(A[i * n + i]) > best) { best = fabs(A[i * n + i]); p = i; }
+        if (p != k) {
+            for (int j = 0; j < n; j++) { double t = A[k * n + j]; A[k * n + j] = A[p * n + j]; A[p * n + j] = t; }
+            for (int j = 0; j < n; j++) { double t = A[j * n + k]; A[j * n + k] = A[j * n + p]; A[j * n + p] = t; }
+            for (int j = 0; j < k; j++) { double t = L[k * n + j]; L[k * n + j] = L[p * n + j]; L[p * n + j] = t; }
+            int t = perm[k]; perm[k] = perm[p]; perm[p] = t;
+        }
+        const double d = A[k * n + k];
+        D[k] = d;
+        L[k * n + k] = 1.0;
+        if (d == 0.0) {
+            for (int i = k + 1; i < n; i++) { D[i] = 0.0; L[i * n + i] = 1.0; L[i * n + k] = 0.0; }
+            break;
+        }
+        for (int i = k + 1; i < n; i++) L[i * n + k] = xddiv(A[i * n + k], d);
+        for (int i = k + 1; i < n; i++)
+            for (int j = k + 1; j < n; j++) A[i * n + j] = xdsub(A[i * n + j], xdmul(xdmul(L[i * n + k], d), L[j * n + k]));
+    }
+    for (int i = 0; i < n; i++) y[i] = b_in[perm[i]];
+    for (int i = 0; i < n; i++) { double s = y[i]; for (int j = 0; j < i; j++) s = xdsub(s, xdmul(L[i * n + j], z[j])); z[i] = s; }
+    for (int i = 0; i < n; i++) z[i] = (fabs(D[i]) > 2.2250738585072014e-308) ? xddiv(z[i], D[i]) : 0.0;
+    for (int i = n - 1; i >= 0; i--) { double s = z[i]; for (int j = i + 1; j < n; j++) s = xdsub(s, xdmul(L[j * n + i], y[j])); y[i] = s; }
+    bool ok = true;
+    for (int i = 0; i < n; i++) x[perm[i]] = y[i];
+    for (int i = 0; i < n; i++) ok = ok && isfinite(x[i]);
+    return ok;
+}
+
+__device__ void icp_vec6_to_m4(const double* x, double* T) {
+    const double ca = cos(x[0]), sa = sin(x[0]), cb = cos(x[1]), sb = sin(x[1]), cg = cos(x[2]), sg = sin(x[2]);
+    T[0] = cg * cb; T[1] = cg * sb * sa - sg * ca; T[2] = cg * sb * ca + sg * sa; T[3] = x[3];
+    T[4] = sg * cb; T[5] = sg * sb * sa + cg * ca; T[6] = sg * sb * ca - cg * sa; T[7] = x[4];
+    T[8] = -sb;     T[9] = cb * sa;                T[10] = cb * ca;               T[11] = x[5];
+    T[12] = 0; T[13] = 0; T[14] = 0; T[15] = 1;
+}
+
+}  // namespace
+
+namespace {
+
+struct IcpArgs {
+    double* pcd;                 // N*3 working copy of the source (transformed in place)
+    long long N;
+    const double* tgt;           // M*3
+    const double* nrm;           // M*3
+    const int* sorted_idx;       // M, target indices ordered by cell
+    const int* cell_start;
+    const int* cell_end;
+    IcpGrid g;
+    double max_dist;
+    int32_t* corr;               // N
+    double* partials;
+    IcpState* st;
+    int max_iter;
+    double rel_fitness, rel_rmse;
+};
+
+__global__ void __launch_bounds__(ICP_THREADS) icp_iter_kernel(const IcpArgs a) {
+    IcpState* st = a.st;
+    if (st->done) return;
+    __shared__ double sU[16];
+    if (threadIdx.x < 16) sU[threadIdx.x] = st->U[threadIdx.x];
+    __syncthreads();
+    double acc[ICP_NV];
+#pragma unroll
+    for (int i = 0; i < ICP_NV; i++) acc[i] = 0.0;
+    const double r2max = xdmul(a.max_dist, a.max_dist);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.N; i += (long long)gridDim.x * blockDim.x) {
+        // pcd.Transform(U)  (Geometry3D::Transform: homogeneous divide)
+        const double x = a.pcd[3 * i], y = a.pcd[3 * i + 1], z = a.pcd[3 * i + 2];
+        double h[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) h[r] = xdadd(xdadd(xdadd(xdmul(sU[4 * r], x), xdmul(sU[4 * r + 1], y)), xdmul(sU[4 * r + 2], z)), sU[4 * r + 3]);
+        const double s[3] = {xddiv(h[0], h[3]), xddiv(h[1], h[3]), xddiv(h[2], h[3])};
+        a.pcd[3 * i] = s[0]; a.pcd[3 * i + 1] = s[1]; a.pcd[3 * i + 2] = s[2];
+        // exact nearest neighbour within max_dist
+        int c0[3], c1[3];
+        bool any = true;
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            c0[k] = (int)floor(xddiv(xdsub(xdsub(s[k], a.max_dist), a.g.lo[k]), a.g.cell));
+            c1[k] = (int)floor(xddiv(xdsub(xdadd(s[k], a.max_dist), a.g.lo[k]), a.g.cell));
+            if (c1[k] < 0 || c0[k] >= a.g.dim[k]) any = false;
+            c0[k] = max(c0[k], 0); c1[k] = min(c1[k], a.g.dim[k] - 1);
+        }
+        int best = -1;
+        double bd = 0.0;
+        if (any) {
+            for (int ca = c0[0]; ca <= c1[0]; ca++)
+                for (int cb = c0[1]; cb <= c1[1]; cb++)
+                    for (int cc = c0[2]; cc <= c1[2]; cc++) {
+                        const int ci = (ca * a.g.dim[1] + cb) * a.g.dim[2] + cc;
+                        const int e = a.cell_end[ci];
+                        for (int q = a.cell_start[ci]; q < e; q++) {
+                            const int j = a.sorted_idx[q];
+                            const double dx = xdsub(a.tgt[3 * j], s[0]), dy = xdsub(a.tgt[3 * j + 1], s[1]), dz = xdsub(a.tgt[3 * j + 2], s[2]);
+                            const double d2 = xdadd(xdadd(xdmul(dx, dx), xdmul(dy, dy)), xdmul(dz, dz));
+                            if (d2 > r2max) continue;
+                            if (best < 0 || d2 < bd || (d2 == bd && j < best)) { bd = d2; best = j; }
+                        }
+                    }
+        }
+        a.corr[i] = best;
+        if (best >= 0) {
+            const double* t = a.tgt + 3 * best;
+            const double* n = a.nrm + 3 * best;
+            const double r = xdadd(xdadd(xdmul(xdsub(s[0], t[0]), n[0]), xdmul(xdsub(s[1], t[1]), n[1])), xdmul(xdsub(s[2], t[2]), n[2]));
+            const double J[6] = {xdsub(xdmul(s[1], n[2]), xdmul(s[2], n[1])), xdsub(xdmul(s[2], n[0]), xdmul(s[0], n[2])),
+                                 xdsub(xdmul(s[0], n[1]), xdmul(s[1], n[0])), n[0], n[1], n[2]};
+            int k = 0;
+#pragma unroll
+            for (int p = 0; p < 6; p++)
+#pragma unroll
+                for (int q = p; q < 6; q++) { acc[k] = xdadd(acc[k], xdmul(J[p], J[q])); k++; }
+#pragma unroll
+            for (int p = 0; p < 6; p++) acc[21 + p] = xdadd(acc[21 + p], xdmul(J[p], r));
+            acc[27] = xdadd(acc[27], xdmul(r, r));
+            acc[28] = xdadd(acc[28], bd);
+            acc[29] += 1.0;
+        }
+    }
+    __shared__ double sh[ICP_THREADS / 32][ICP_NV];
+    __shared__ bool is_last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < ICP_NV; i++) {
+        double v = acc[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v = xdadd(v, __shfl_down_sync(0xffffffffu, v, o));
+        if (lane == 0) sh[warp][i] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < ICP_NV) {
+        double v = 0.0;
+        for (int w = 0; w < ICP_THREADS / 32; w++) v = xdadd(v, sh[w][threadIdx.x]);
+        a.partials[(size_t)blockIdx.x * ICP_NV + threadIdx.x] = v;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = (atomicAdd(&st->ticket, 1u) == gridDim.x - 1);
+    __syncthreads();
+    if (!is_last) return;
+    __shared__ double tot[ICP_NV];
+    if (threadIdx.x < ICP_NV) {
+        double v = 0.0;
+        for (unsigned b = 0; b < gridDim.x; b++) v = xdadd(v, __ldcg(&a.partials[(size_t)b * ICP_NV + threadIdx.x]));
+        tot[threadIdx.x] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    st->ticket = 0;
+    const int k = st->launches;          // 0 = initial Evaluate, k >= 1 = k-th loop iteration
+    st->launches = k + 1;
+    const double n = tot[29];
+    const double fitness = a.N ? xddiv(n, (double)a.N) : 0.0;
+    const double rmse = n > 0.0 ? sqrt(xddiv(tot[28], n)) : 0.0;
+    if (k >= 1) {
+        double R[16];
+        for (int i = 0; i < 4; i++)
+            for (int j = 0; j < 4; j++) { double s = 0.0; for (int q = 0; q < 4; q++) s = xdadd(s, xdmul(sU[i * 4 + q], st->T[q * 4 + j])); R[i * 4 + j] = s; }
+        for (int i = 0; i < 16; i++) st->T[i] = R[i];
+        st->iters = k;
+    }
+    st->prev_fitness = st->fitness; st->prev_rmse = st->rmse;
+    st->fitness = fitness; st->rmse = rmse; st->n_corr = (long long)n;
+    bool done = false;
+    if (k >= 1 && fabs(xdsub(st->prev_fitness, fitness)) < a.rel_fitness && fabs(xdsub(st->prev_rmse, rmse)) < a.rel_rmse) done = true;
+    if (k >= a.max_iter) done = true;
+    if (done) { st->done = 1; return; }
+    // TransformationEstimationPointToPlane::ComputeTransformation for the next iteration
+    double U[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+    if (n > 0.0) {
+        double A[36], nb[6], x[6];
+        int q = 0;
+        for (int p = 0; p < 6; p++) for (int r = p; r < 6; r++) { A[p * 6 + r] = tot[q]; A[r * 6 + p] = tot[q]; q++; }
+        for (int p = 0; p < 6; p++) nb[p] = -tot[21 + p];
+        if (icp_ldlt6(A, nb, x)) icp_vec6_to_m4(x, U);
+    }
+    for (int i = 0; i < 16; i++) st->U[i] = U[i];
+}
+
+struct IcpWs { void* p = nullptr; size_t bytes = 0; };
+IcpWs g_icp_ws[16];
+
+int icp_get_ws(size_t bytes, void** out) {
+    int dev = 0;
+    B2R_CUDA(cudaGetDevice(&dev));
+    IcpWs& w = g_icp_ws[dev & 15];
+    if (w.bytes < bytes) {
+        if (w.p) { cudaDeviceSynchronize(); cudaFree(w.p); }
+        w.p = nullptr; w.bytes = 0;
+        B2R_CUDA(cudaMalloc(&w.p, bytes));
+        w.bytes = bytes;
+    }
+    *out = w.p;
+    return B2R_OK;
+}
+
+inline size_t al(size_t v) { return (v + 255) & ~(size_t)255; }
+
+}  // namespace
+
+// registration_icp with TransformationEstimationPointToPlane.  See include/b2recon.h.
+B2R_API int b2r_icp_point_to_plane(const double* src_xyz, int64_t N, const double* tgt_xyz, const double* tgt_nrm, int64_t M,
+                                   double max_dist, const double* init_host, int max_iter, double rel_fitness,
+                                   double rel_rmse, double* out_T_host, double* fitness_host, double* rmse_host,
+                                   int32_t* corr, cudaStream_t stream) {
+    if (!(max_dist > 0.0)) { b2r_set_error("[RegistrationICP] Invalid max_correspondence_distance."); return B2R_ERR_BAD_ARG; }
+    if (!tgt_nrm) { b2r_set_error("[RegistrationICP] TransformationEstimationPointToPlane requires target normals."); return B2R_ERR_FORMAT; }
+    if (!src_xyz || !tgt_xyz || !init_host || !out_T_host || !fitness_host || !rmse_host || N < 0 || M < 0 || max_iter < 0 ||
+        N > 0x7fffffff || M > 0x7fffffff) {
+        b2r_set_error("b2r_icp_point_to_plane: bad argument");
+        return B2R_ERR_BAD_ARG;
+    }
+    if (N == 0 || M == 0) {
+        memcpy(out_T_host, init_host, 128);
+        *fitness_host = 0.0; *rmse_host = 0.0;
+        return 0;
+    }
+    int nsm = 148;
+    cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, 0);
+    unsigned grid = (unsigned)((N + ICP_THREADS - 1) / ICP_THREADS);
+    if (grid > (unsigned)nsm * 4) grid = (unsigned)nsm * 4;
+    const size_t max_cells = (size_t)8 << 20;
+    size_t sort_tmp = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp, (unsigned*)nullptr, (unsigned*)nullptr, (int*)nullptr, (int*)nullptr, (int)M);
+    size_t total = 0;
+    auto take = [&](size_t b) { size_t o = total; total += al(b); return o; };
+    const size_t o_st = take(sizeof(IcpState)), o_pcd = take((size_t)N * 24), o_corr = take((size_t)N * 4);
+    const size_t o_cin = take((size_t)M * 4), o_cout = take((size_t)M * 4), o_iin = take((size_t)M * 4), o_iout = take((size_t)M * 4);
+    const size_t o_cs = take(max_cells * 4), o_ce = take(max_cells * 4);
+    const size_t o_part = take((size_t)grid * ICP_NV * 8), o_tmp = take(sort_tmp);
+    void* ws = nullptr;
+    int rc = icp_get_ws(total, &ws);
+    if (rc != B2R_OK) return rc;
+    char* b = (char*)ws;
+    IcpState* st = (IcpState*)(b + o_st);
+    IcpState h0;
+    memset(&h0, 0, sizeof(h0));
+    memcpy(h0.T, init_host, 128);
+    memcpy(h0.U, init_host, 128);
+    B2R_CUDA(cudaMemcpyAsync(st, &h0, sizeof(h0), cudaMemcpyHostToDevice, stream));
+    bounds_kernel<<<1, 1024, 0, stream>>>(tgt_xyz, (long long)M, st);
+    B2R_CHECK_LAUNCH();
+    IcpState h1;
+    B2R_CUDA(cudaMemcpyAsync(&h1, st, sizeof(h1), cudaMemcpyDeviceToHost, stream));
+    B2R_CUDA(cudaStreamSynchronize(stream));
+    IcpGrid g;
+    g.cell = max_dist;
+    for (int k = 0; k < 3; k++) g.lo[k] = h1.bounds[k];
+    for (;;) {
+        double n = 1.0;
+        for (int k = 0; k < 3; k++) { g.dim[k] = (int)fmax(1.0, floor((h1.bounds[3 + k] - g.lo[k]) / g.cell) + 1.0); n *= (double)g.dim[k]; }
+        if (n <= (double)max_cells) break;
+        g.cell *= 2.0;
+    }
+    const size_t ncells = (size_t)g.dim[0] * g.dim[1] * g.dim[2];
+    unsigned *cin = (unsigned*)(b + o_cin), *cout_ = (unsigned*)(b + o_cout);
+    int *iin = (int*)(b + o_iin), *iout = (int*)(b + o_iout);
+    int *cs = (int*)(b + o_cs), *ce = (int*)(b + o_ce);
+    cell_id_kernel<<<(unsigned)((M + 255) / 256), 256, 0, stream>>>(tgt_xyz, (int)M, g, cin, iin);
+    B2R_CHECK_LAUNCH();
+    size_t tmpb = sort_tmp;
+    B2R_CUDA(cub::DeviceRadixSort::SortPairs(b + o_tmp, tmpb, cin, cout_, iin, iout, (int)M, 0, 32, stream));
+    B2R_CUDA(cudaMemsetAsync(cs, 0, ncells * 4, stream));
+    B2R_CUDA(cudaMemsetAsync(ce, 0, ncells * 4, stream));
+    cell_range_kernel<<<(unsigned)((M + 255) / 256), 256, 0, stream>>>(cout_, (int)M, cs, ce);
+    copy_points_kernel<<<(unsigned)((N * 3 + 255) / 256), 256, 0, stream>>>(src_xyz, (double*)(b + o_pcd), (long long)N * 3);
+    B2R_CHECK_LAUNCH();
+    IcpArgs a;
+    a.pcd = (double*)(b + o_pcd); a.N = N; a.tgt = tgt_xyz; a.nrm = tgt_nrm; a.sorted_idx = iout; a.cell_start = cs; a.cell_end = ce;
+    a.g = g; a.max_dist = max_dist; a.corr = (int32_t*)(b + o_corr); a.partials = (double*)(b + o_part); a.st = st;
+    a.max_iter = max_iter; a.rel_fitness = rel_fitness; a.rel_rmse = rel_rmse;
+    for (int k = 0; k <= max_iter; k++) {
+        icp_iter_kernel<<<grid, ICP_THREADS, 0, stream>>>(a);
+        if ((k & 15) == 15) {     // cheap early exit: look at the done flag every 16 launches
+            B2R_CUDA(cudaMemcpyAsync(&h1, st, sizeof(h1), cudaMemcpyDeviceToHost, stream));
+            B2R_CUDA(cudaStreamSynchronize(stream));
+            if (h1.done) break;
+        }
+    }
+    B2R_CHECK_LAUNCH();
+    B2R_CUDA(cudaMemcpyAsync(&h1, st, sizeof(h1), cudaMemcpyDeviceToHost, stream));
+    if (corr) B2R_CUDA(cudaMemcpyAsync(corr, a.corr, (size_t)N * 4, cudaMemcpyDeviceToDevice, stream));
+    B2R_CUDA(cudaStreamSynchronize(stream));
+    memcpy(out_T_host, h1.T, 128);
+    *fitness_host = h1.fitness;
+    *rmse_host = h1.rmse;
+    return h1.iters;
+}

@@ -1,0 +1,523 @@
+// odometry.cu -- multi-scale RGB-D odometry (hybrid / colour term) on sm_100a (north_star subsystem 4).
+//
+// Replaces o3d.pipelines.odometry.compute_rgbd_odometry
+// (/root/reference/CodeThatWorks/RGBD_Odometry.py:22-35, CodeThatKindaWorks/capture_frames.py:148-151,
+//  CodeThatWorks/bundlefusionattemps/bundlefusion_reconstruction.py:118-129,224-227); upstream semantics
+// restated in SURVEY.md Appendix A.6.
+//
+// Design: the whole Gauss-Newton loop stays on the device -- no host round trip per iteration.
+//   corr_warp_kernel   forward-warps every source pixel; the per-target-pixel z-buffer is one 64-bit
+//                      atomicMin of (source depth bits << 32 | source raster index): nearest source depth
+//                      wins, ties go to the earlier raster index (= upstream's strict '<').
+//   reduce_kernel<M>   walks the target pixels, consumes (and clears) the z-buffer, builds the 1-2 Jacobian
+//                      rows per correspondence and reduces JtJ (21) + Jtr (6) + r^2 in f64: registers ->
+//                      warp shuffles -> shared memory -> per-block partials; the LAST block (atomic ticket)
+//                      adds the partials in block order (deterministic), solves the 6x6 system by pivoted
+//                      LDLT and left-multiplies the pose, all in one launch.
+// Image filters keep upstream's rounding points (f64 accumulate, f32 store after each separable pass).
+#include "common.cuh"
+#include "host_math.h"
+#include <math.h>
+
+namespace {
+
+#define OD_THREADS 256
+#define OD_NV 28            // 21 JtJ upper triangle + 6 Jtr + r2
+#define OD_EMPTY 0xFFFFFFFFFFFFFFFFull
+
+struct KLevel { double fx, fy, cx, cy; };
+
+// device-resident iteration state
+struct OdoState {
+    double pose[16];       // current source->target estimate
+    double scale[2];       // NormalizeIntensity factors (source, target)
+    double info[36];
+    double last_r2;
+    int failed;            // sticky: non-finite solve
+    int n_corr;            // correspondences of the last reduce
+    unsigned ticket;
+    int pad;
+};
+
+// ---- filters ---------------------------------------------------------------------------------------
+// kind: 0 Gaussian3, 1 Sobel3Dx ([-1,0,1] along x then [1,2,1] along y), 2 Sobel3Dy
+__device__ __forceinline__ void filter_taps(int kind, double* kh, double* kv) {
+    if (kind == 0) { kh[0] = 0.25; kh[1] = 0.5; kh[2] = 0.25; kv[0] = 0.25; kv[1] = 0.5; kv[2] = 0.25; }
+    else if (kind == 1) { kh[0] = -1.0; kh[1] = 0.0; kh[2] = 1.0; kv[0] = 1.0; kv[1] = 2.0; kv[2] = 1.0; }
+    else { kh[0] = 1.0; kh[1] = 2.0; kh[2] = 1.0; kv[0] = -1.0; kv[1] = 0.0; kv[2] = 1.0; }
+}
+
+__device__ __forceinline__ float pre_depth(float p, float dmin, float dmax) {
+    return (p < dmin || p > dmax || p <= 0.0f) ? __int_as_float(0x7fc00000) : p;
+}
+
+// out = Filter(in) with clamp-to-edge; PRE applies PreprocessDepth to the loads first
+template <bool PRE>
+__global__ void __launch_bounds__(OD_THREADS) filter3_kernel(const float* __restrict__ in, float* __restrict__ out, int W, int H,
+                                                              int kind, float dmin, float dmax) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= W * H) return;
+    const int v = idx / W, u = idx - v * W;
+    double kh[3], kv[3];
+    filter_taps(kind, kh, kv);
+    double acc = 0.0;
+#pragma unroll
+    for (int j = -1; j <= 1; j++) {
+        const int vs = min(max(v + j, 0), H - 1);
+        double t = 0.0;
+#pragma unroll
+        for (int i = -1; i <= 1; i++) {
+            const int us = min(max(u + i, 0), W - 1);
+            float p = in[vs * W + us];
+            if (PRE) p = pre_depth(p, dmin, dmax);
+            t = xdadd(t, xdmul((double)p, kh[i + 1]));
+        }
+        const float row = (float)t;                       // horizontal pass stored as f32
+        acc = xdadd(acc, xdmul((double)row, kv[j + 1]));
+    }
+    out[idx] = (float)acc;
+}
+
+__global__ void __launch_bounds__(OD_THREADS) downsample_kernel(const float* __restrict__ in, float* __restrict__ out, int W, int H) {
+    const int Wo = W / 2, Ho = H / 2;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= Wo * Ho) return;
+    const int y = idx / Wo, x = idx - y * Wo;
+    const float a = in[(2 * y) * W + 2 * x], b = in[(2 * y) * W + 2 * x + 1], c = in[(2 * y + 1) * W + 2 * x], d = in[(2 * y + 1) * W + 2 * x + 1];
+    out[idx] = xfdiv(xfadd(xfadd(xfadd(a, b), c), d), 4.0f);
+}
+
+__global__ void __launch_bounds__(OD_THREADS) scale_kernel(float* img, int n, const OdoState* st, int which) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n) return;
+    img[idx] = (float)xdmul(st->scale[which], (double)img[idx]);
+}
+
+__global__ void fill_u64_kernel(unsigned long long* p, int n) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx < n) p[idx] = OD_EMPTY;
+}
+
+// ---- correspondence (SURVEY A.6 ComputeCorrespondence) -------------------------------------------------
+__global__ void __launch_bounds__(OD_THREADS) corr_warp_kernel(const float* __restrict__ ds, const float* __restrict__ dt, int W, int H,
+                                                                const KLevel K, const OdoState* st, double depth_diff_max,
+                                                                unsigned long long* zbuf) {
+    __shared__ double sM[9], sKt[3];
+    if (threadIdx.x == 0) {
+        const double Km[9] = {K.fx, 0, K.cx, 0, K.fy, K.cy, 0, 0, 1};
+        const double Ki[9] = {xddiv(1.0, K.fx), 0, xddiv(-K.cx, K.fx), 0, xddiv(1.0, K.fy), xddiv(-K.cy, K.fy), 0, 0, 1};
+        double R[9], t[3], KR[9];
+        for (int i = 0; i < 3; i++) { for (int j = 0; j < 3; j++) R[i * 3 + j] = st->pose[i * 4 + j]; t[i] = st->pose[i * 4 + 3]; }
+        for (int i = 0; i < 3; i++)
+            for (int j = 0; j < 3; j++) { double s = 0; for (int k = 0; k < 3; k++) s = xdadd(s, xdmul(Km[i * 3 + k], R[k * 3 + j])); KR[i * 3 + j] = s; }
+        for (int i = 0; i < 3; i++)
+            for (int j = 0; j < 3; j++) { double s = 0; for (int k = 0; k < 3; k++) s = xdadd(s, xdmul(KR[i * 3 + k], Ki[k * 3 + j])); sM[i * 3 + j] = s; }
+        for (int i = 0; i < 3; i++) { double s = 0; for (int k = 0; k < 3; k++) s = xdadd(s, xdmul(Km[i * 3 + k], t[k])); sKt[i] = s; }
+    }
+    __syncthreads();
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= W * H) return;
+    const float dsf = ds[idx];
+    if (dsf != dsf) return;
+    const int vs = idx / W, us = idx - vs * W;
+    const double d = (double)dsf;
+    double q[3];
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+        q[i] = xdadd(xdadd(xdadd(xdmul(xdmul(d, sM[i * 3]), (double)us), xdmul(xdmul(d, sM[i * 3 + 1]), (double)vs)), xdmul(d, sM[i * 3 + 2])), sKt[i]);
+    const double zt = q[2];
+    const double uq = xdadd(xddiv(q[0], zt), 0.5), vq = xdadd(xddiv(q[1], zt), 0.5);
+    if (!(fabs(uq) < 1e9) || !(fabs(vq) < 1e9)) return;   // x86 (int) of NaN/huge = INT_MIN -> rejected upstream too
+    const int ut = (int)uq, vt = (int)vq;                 // truncation toward zero, like the C cast
+    if (ut < 0 || ut >= W || vt < 0 || vt >= H) return;
+    const float dtf = dt[vt * W + ut];
+    if (dtf != dtf) return;
+    if (!(fabs(xdsub(zt, (double)dtf)) <= depth_diff_max)) return;
+    const unsigned long long packed = ((unsigned long long)__float_as_uint(dsf) << 32) | (unsigned)idx;
+    atomicMin(&zbuf[vt * W + ut], packed);
+}
+
+// ---- 6x6 pivoted LDLT (same algorithm as the oracle) + pose update -----------------------------------------
+__device__ bool ldlt6_solve_dev(const double* A_in, const double* b_in, double* x) {
+    const int n = 6;
+    double A[36], L[36], D[6], y[6], z[6];
+    int perm[6];
+    for (int i = 0; i < 36; i++) { A[i] = A_in[i]; L[i] = 0.0; }
+    for (int i = 0; i < n; i++) perm[i] = i;
+    for (int k = 0; k < n; k++) {
+        int p = k;
+        double best = fabs(A[k * n + k]);
+        for (int i = k + 1; i < n; i++) if (fabs(A[i * n + i]) > best) { best = fabs(A[i * n + i]); p = i; }
+        if (p != k) {
+            for (int j = 0; j < n; j++) { double t = A[k * n + j]; A[k * n + j] = A[p * n + j]; A[p * n + j] = t; }
+            for (int j = 0; j < n; j++) { double t = A[j * n + k]; A[j * n + k] = A[j * n + p]; A[j * n + p] = t; }
+            for (int j = 0; j < k; j++) { double t = L[k * n + j]; L[k * n + j] = L[p * n + j]; L[p * n + j] = t; }
+            int t = perm[k]; perm[k] = perm[p]; perm[p] = t;
+        }
+        const double d = A[k * n + k];
+        D[k] = d;
+        L[k * n + k] = 1.0;
+        if (d == 0.0) {
+            for (int i = k + 1; i < n; i++) { D[i] = 0.0; L[i * n + i] = 1.0; L[i * n + k] = 0.0; }
+            break;
+        }
+        for (int i = k + 1; i < n; i++) L[i * n + k] = xddiv(A[i * n + k], d);
+        for (int i = k + 1; i < n; i++)
+            for (int j = k + 1; j < n; j++) A[i * n + j] = xdsub(A[i * n + j], xdmul(xdmul(L[i * n + k], d), L[j * n + k]));
+    }
+    for (int i = 0; i < n; i++) y[i] = b_in[perm[i]];
+    for (int i = 0; i < n; i++) { double s = y[i]; for (int j = 0; j < i; j++) s = xdsub(s, xdmul(L[i * n + j], z[j])); z[i] = s; }
+    for (int i = 0; i < n; i++) z[i] = (fabs(D[i]) > 2.2250738585072014e-308) ? xddiv(z[i], D[i]) : 0.0;
+    for (int i = n - 1; i >= 0; i--) { double s = z[i]; for (int j = i + 1; j < n; j++) s = xdsub(s, xdmul(L[j * n + i], y[j])); y[i] = s; }
+    bool ok = true;
+    for (int i = 0; i < n; i++) { x[perm[i]] = y[i]; }
+    for (int i = 0; i < n; i++) ok = ok && isfinite(x[i]);
+    return ok;
+}
+
+__device__ void vec6_to_m4_dev(const double* x, double* T) {
+    const double ca = cos(x[0]), sa = sin(x[0]), cb = cos(x[1]), sb = sin(x[1]), cg = cos(x[2]), sg = sin(x[2]);
+    T[0] = cg * cb; T[1] = cg * sb * sa - sg * ca; T[2] = cg * sb * ca + sg * sa; T[3] = x[3];
+    T[4] = sg * cb; T[5] = sg * sb * sa + cg * ca; T[6] = sg * sb * ca - cg * sa; T[7] = x[4];
+    T[8] = -sb;     T[9] = cb * sa;                T[10] = cb * ca;               T[11] = x[5];
+    T[12] = 0; T[13] = 0; T[14] = 0; T[15] = 1;
+}
+
+// expand 21 upper-triangle values + 6 Jtr into a full system, solve, pose <- dT * pose
+__device__ void solve_and_update(const double* tot, OdoState* st) {
+    double A[36], nb[6], x[6], dT[16], R[16];
+    int k = 0;
+    for (int a = 0; a < 6; a++) for (int b = a; b < 6; b++) { A[a * 6 + b] = tot[k]; A[b * 6 + a] = tot[k]; k++; }
+    for (int a = 0; a < 6; a++) nb[a] = -tot[21 + a];
+    st->last_r2 = tot[27];
+    if (!ldlt6_solve_dev(A, nb, x)) { st->failed = 1; return; }
+    vec6_to_m4_dev(x, dT);
+    for (int i = 0; i < 4; i++)
+        for (int j = 0; j < 4; j++) { double s = 0.0; for (int q = 0; q < 4; q++) s = xdadd(s, xdmul(dT[i * 4 + q], st->pose[q * 4 + j])); R[i * 4 + j] = s; }
+    for (int i = 0; i < 16; i++) st->pose[i] = R[i];
+}
+
+}  // namespace
+
+namespace {
+
+struct LevelImgs {
+    const float *sg, *sd, *tg, *td, *tgdx, *tgdy, *tddx, *tddy;
+    int W, H;
+};
+
+// MODE 0: colour-term Jacobian, 1: hybrid-term Jacobian, 2: intensity means (NormalizeIntensity),
+//      3: information matrix (CreateInformationMatrix)
+template <int MODE>
+__global__ void __launch_bounds__(OD_THREADS) reduce_kernel(const LevelImgs L, const KLevel K, OdoState* st, unsigned long long* zbuf,
+                                                             double* partials) {
+    constexpr int NV = (MODE == 2) ? 3 : (MODE == 3 ? 22 : OD_NV);
+    double acc[NV];
+#pragma unroll
+    for (int i = 0; i < NV; i++) acc[i] = 0.0;
+    const int W = L.W, N = L.W * L.H;
+    double R[9], t[3];
+    if (MODE <= 1) {
+#pragma unroll
+        for (int i = 0; i < 3; i++) { for (int j = 0; j < 3; j++) R[i * 3 + j] = st->pose[i * 4 + j]; t[i] = st->pose[i * 4 + 3]; }
+    }
+    const double inv_fx = xddiv(1.0, K.fx), inv_fy = xddiv(1.0, K.fy);
+    const double sI = sqrt(xdsub(1.0, 0.968)), sD = sqrt(0.968);
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < N; idx += gridDim.x * blockDim.x) {
+        const unsigned long long e = zbuf[idx];
+        if (e == OD_EMPTY) continue;
+        zbuf[idx] = OD_EMPTY;                               // consume: the buffer is clean for the next warp
+        const int src = (int)(e & 0xFFFFFFFFull);
+        const int vt = idx / W, ut = idx - vt * W;
+        const int vs = src / W, us = src - vs * W;
+        if (MODE == 2) {
+            acc[0] = xdadd(acc[0], (double)L.sg[src]);
+            acc[1] = xdadd(acc[1], (double)L.tg[idx]);
+            acc[2] += 1.0;
+            continue;
+        }
+        if (MODE == 3) {
+            const float zf = L.td[idx];
+            const double x = (double)(float)xdmul(xdmul(xdsub((double)ut, K.cx), (double)zf), inv_fx);
+            const double y = (double)(float)xdmul(xdmul(xdsub((double)vt, K.cy), (double)zf), inv_fy);
+            const double z = (double)zf;
+            const double g[3][6] = {{0, z, -y, 1, 0, 0}, {-z, 0, x, 0, 1, 0}, {y, -x, 0, 0, 0, 1}};
+#pragma unroll
+            for (int r = 0; r < 3; r++) {
+                int k = 0;
+#pragma unroll
+                for (int a = 0; a < 6; a++)
+#pragma unroll
+                    for (int b = a; b < 6; b++) { acc[k] = xdadd(acc[k], xdmul(g[r][a], g[r][b])); k++; }
+            }
+            acc[21] += 1.0;
+            continue;
+        }
+        // ---- Jacobian rows
+        const float zs = L.sd[src];
+        const double p0 = (double)(float)xdmul(xdmul(xdsub((double)us, K.cx), (double)zs), inv_fx);
+        const double p1 = (double)(float)xdmul(xdmul(xdsub((double)vs, K.cy), (double)zs), inv_fy);
+        const double p2 = (double)zs;
+        double P[3];
+#pragma unroll
+        for (int i = 0; i < 3; i++) P[i] = xdadd(xdadd(xdadd(xdmul(R[i * 3], p0), xdmul(R[i * 3 + 1], p1)), xdmul(R[i * 3 + 2], p2)), t[i]);
+        const double diff_photo = (double)xfsub(L.tg[idx], L.sg[src]);
+        const double dIdx = xdmul(0.125, (double)L.tgdx[idx]), dIdy = xdmul(0.125, (double)L.tgdy[idx]);
+        const double invz = xddiv(1.0, P[2]);
+        const double c0 = xdmul(xdmul(dIdx, K.fx), invz), c1 = xdmul(xdmul(dIdy, K.fy), invz);
+        const double c2 = xdmul(-xdadd(xdmul(c0, P[0]), xdmul(c1, P[1])), invz);
+        double J[6] = {xdadd(xdmul(-P[2], c1), xdmul(P[1], c2)), xdsub(xdmul(P[2], c0), xdmul(P[0], c2)),
+                       xdadd(xdmul(-P[1], c0), xdmul(P[0], c1)), c0, c1, c2};
+        double r = diff_photo;
+        if (MODE == 1) {
+#pragma unroll
+            for (int i = 0; i < 6; i++) J[i] = xdmul(sI, J[i]);
+            r = xdmul(sI, diff_photo);
+        }
+        {
+            int k = 0;
+#pragma unroll
+            for (int a = 0; a < 6; a++)
+#pragma unroll
+                for (int b = a; b < 6; b++) { acc[k] = xdadd(acc[k], xdmul(J[a], J[b])); k++; }
+#pragma unroll
+            for (int a = 0; a < 6; a++) acc[21 + a] = xdadd(acc[21 + a], xdmul(J[a], r));
+            acc[27] = xdadd(acc[27], xdmul(r, r));
+        }
+        if (MODE == 1) {
+            double dDdx = xdmul(0.125, (double)L.tddx[idx]), dDdy = xdmul(0.125, (double)L.tddy[idx]);
+            if (dDdx != dDdx) dDdx = 0.0;
+            if (dDdy != dDdy) dDdy = 0.0;
+            const double diff_geo = xdsub((double)L.td[idx], P[2]);
+            const double d0 = xdmul(xdmul(dDdx, K.fx), invz), d1 = xdmul(xdmul(dDdy, K.fy), invz);
+            const double d2 = xdmul(-xdadd(xdmul(d0, P[0]), xdmul(d1, P[1])), invz);
+            const double J1[6] = {xdmul(sD, xdsub(xdadd(xdmul(-P[2], d1), xdmul(P[1], d2)), P[1])),
+                                  xdmul(sD, xdadd(xdsub(xdmul(P[2], d0), xdmul(P[0], d2)), P[0])),
+                                  xdmul(sD, xdadd(xdmul(-P[1], d0), xdmul(P[0], d1))), xdmul(sD, d0), xdmul(sD, d1),
+                                  xdmul(sD, xdsub(d2, 1.0))};
+            const double r1 = xdmul(sD, diff_geo);
+            int k = 0;
+#pragma unroll
+            for (int a = 0; a < 6; a++)
+#pragma unroll
+                for (int b = a; b < 6; b++) { acc[k] = xdadd(acc[k], xdmul(J1[a], J1[b])); k++; }
+#pragma unroll
+            for (int a = 0; a < 6; a++) acc[21 + a] = xdadd(acc[21 + a], xdmul(J1[a], r1));
+            acc[27] = xdadd(acc[27], xdmul(r1, r1));
+        }
+    }
+    // ---- warp shuffle tree, then block tree through shared memory
+    __shared__ double sh[OD_THREADS / 32][NV];
+    __shared__ bool is_last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < NV; i++) {
+        double v = acc[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v = xdadd(v, __shfl_down_sync(0xffffffffu, v, o));
+        if (lane == 0) sh[warp][i] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < NV) {
+        double v = 0.0;
+        for (int w = 0; w < OD_THREADS / 32; w++) v = xdadd(v, sh[w][threadIdx.x]);
+        partials[(size_t)blockIdx.x * OD_NV + threadIdx.x] = v;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = (atomicAdd(&st->ticket, 1u) == gridDim.x - 1);
+    __syncthreads();
+    if (!is_last) return;
+    // ---- last block: deterministic sum over blocks, then finalise
+    __shared__ double tot[OD_NV];
+    if (threadIdx.x < NV) {
+        double v = 0.0;
+        for (unsigned b = 0; b < gridDim.x; b++) v = xdadd(v, __ldcg(&partials[(size_t)b * OD_NV + threadIdx.x]));
+        tot[threadIdx.x] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        st->ticket = 0;
+        if (MODE <= 1) {
+            solve_and_update(tot, st);
+        } else if (MODE == 2) {
+            st->n_corr = (int)tot[2];
+            st->scale[0] = xddiv(0.5, xddiv(tot[0], tot[2]));
+            st->scale[1] = xddiv(0.5, xddiv(tot[1], tot[2]));
+        } else {
+            int k = 0;
+            for (int a = 0; a < 6; a++) for (int b = a; b < 6; b++) { st->info[a * 6 + b] = tot[k]; st->info[b * 6 + a] = tot[k]; k++; }
+            st->n_corr = (int)tot[21];
+        }
+    }
+}
+
+// ---- per-device workspace (grow-only) ----------------------------------------------------------------------
+struct Workspace { void* p = nullptr; size_t bytes = 0; int device = -1; };
+Workspace g_ws[16];
+
+int get_ws(size_t bytes, void** out) {
+    int dev = 0;
+    B2R_CUDA(cudaGetDevice(&dev));
+    Workspace& w = g_ws[dev & 15];
+    if (w.bytes < bytes) {
+        if (w.p) { cudaDeviceSynchronize(); cudaFree(w.p); }
+        w.p = nullptr; w.bytes = 0;
+        B2R_CUDA(cudaMalloc(&w.p, bytes));
+        w.bytes = bytes;
+    }
+    *out = w.p;
+    return B2R_OK;
+}
+
+inline unsigned nblk(int n) { return (unsigned)((n + OD_THREADS - 1) / OD_THREADS); }
+
+}  // namespace
+
+// compute_rgbd_odometry.  See include/b2recon.h.
+B2R_API int b2r_odometry(const float* src_gray, const float* src_depth, const float* tgt_gray, const float* tgt_depth, int W,
+                         int H, double fx, double fy, double cx, double cy, const double* init_host, int jac_kind,
+                         const int* iters_host, int n_levels, double depth_diff_max, double depth_min, double depth_max,
+                         double* out_T_host, double* out_info_host, int* success_host, cudaStream_t stream) {
+    if (!src_gray || !src_depth || !tgt_gray || !tgt_depth || !init_host || !iters_host || !out_T_host || !out_info_host ||
+        !success_host || W < 4 || H < 4 || n_levels < 1 || n_levels > 8 || jac_kind < 0 || jac_kind > 1) {
+        b2r_set_error("b2r_odometry: bad argument");
+        return B2R_ERR_BAD_ARG;
+    }
+    int Wl[8], Hl[8];
+    size_t off[8], total_px = 0;
+    for (int l = 0; l < n_levels; l++) {
+        Wl[l] = l ? Wl[l - 1] / 2 : W; Hl[l] = l ? Hl[l - 1] / 2 : H;
+        if (Wl[l] < 2 || Hl[l] < 2) { b2r_set_error("b2r_odometry: image too small for %d levels", n_levels); return B2R_ERR_BAD_ARG; }
+        off[l] = total_px; total_px += ((size_t)Wl[l] * Hl[l] + 63) & ~(size_t)63;
+    }
+    const size_t N0 = (size_t)W * H;
+    int nsm = 148;
+    cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, 0);
+    const unsigned red_grid_max = (unsigned)nsm * 2;
+    // workspace: 8 pyramids + 1 temp image + zbuf + partials + state
+    const size_t bytes_imgs = (8 * total_px + N0) * sizeof(float);
+    const size_t o_z = (bytes_imgs + 255) & ~(size_t)255;
+    const size_t o_p = o_z + ((N0 * 8 + 255) & ~(size_t)255);
+    const size_t o_s = o_p + (((size_t)red_grid_max * OD_NV * 8 + 255) & ~(size_t)255);
+    const size_t total = o_s + sizeof(OdoState);
+    void* ws = nullptr;
+    int rc = get_ws(total, &ws);
+    if (rc != B2R_OK) return rc;
+    float* base = (float*)ws;
+    float* pyr[8];
+    for (int i = 0; i < 8; i++) pyr[i] = base + (size_t)i * total_px;     // sg, sd, tg, td, tgdx, tgdy, tddx, tddy
+    float* tmp = base + 8 * total_px;
+    unsigned long long* zbuf = (unsigned long long*)((char*)ws + o_z);
+    double* partials = (double*)((char*)ws + o_p);
+    OdoState* st = (OdoState*)((char*)ws + o_s);
+
+    OdoState h0;
+    memset(&h0, 0, sizeof(h0));
+    bool all_zero = true;
+    for (int i = 0; i < 16; i++) if (init_host[i] != 0.0) all_zero = false;
+    if (all_zero) b2r::m4_identity(h0.pose); else memcpy(h0.pose, init_host, sizeof(h0.pose));
+    h0.scale[0] = h0.scale[1] = 1.0;
+    B2R_CUDA(cudaMemcpyAsync(st, &h0, sizeof(h0), cudaMemcpyHostToDevice, stream));
+    fill_u64_kernel<<<nblk((int)N0), OD_THREADS, 0, stream>>>(zbuf, (int)N0);
+
+    // InitializeRGBDOdometry: Gaussian3 on grays; PreprocessDepth + Gaussian3 on depths
+    const float dmin = (float)depth_min, dmax = (float)depth_max;
+    filter3_kernel<false><<<nblk((int)N0), OD_THREADS, 0, stream>>>(src_gray, pyr[0], W, H, 0, 0.f, 0.f);
+    filter3_kernel<false><<<nblk((int)N0), OD_THREADS, 0, stream>>>(tgt_gray, pyr[2], W, H, 0, 0.f, 0.f);
+    filter3_kernel<true><<<nblk((int)N0), OD_THREADS, 0, stream>>>(src_depth, pyr[1], W, H, 0, dmin, dmax);
+    filter3_kernel<true><<<nblk((int)N0), OD_THREADS, 0, stream>>>(tgt_depth, pyr[3], W, H, 0, dmin, dmax);
+    B2R_CHECK_LAUNCH();
+
+    KLevel K[8];
+    K[0] = KLevel{fx, fy, cx, cy};
+    for (int l = 1; l < n_levels; l++) K[l] = KLevel{0.5 * K[l - 1].fx, 0.5 * K[l - 1].fy, 0.5 * K[l - 1].cx, 0.5 * K[l - 1].cy};
+    auto level = [&](int l) {
+        LevelImgs L;
+        L.sg = pyr[0] + off[l]; L.sd = pyr[1] + off[l]; L.tg = pyr[2] + off[l]; L.td = pyr[3] + off[l];
+        L.tgdx = pyr[4] + off[l]; L.tgdy = pyr[5] + off[l]; L.tddx = pyr[6] + off[l]; L.tddy = pyr[7] + off[l];
+        L.W = Wl[l]; L.H = Hl[l];
+        return L;
+    };
+    auto red_grid = [&](int n) { unsigned g = nblk(n); return g < red_grid_max ? g : red_grid_max; };
+
+    // NormalizeIntensity over the correspondences at the initial pose
+    {
+        const LevelImgs L = level(0);
+        corr_warp_kernel<<<nblk((int)N0), OD_THREADS, 0, stream>>>(L.sd, L.td, W, H, K[0], st, depth_diff_max, zbuf);
+        reduce_kernel<2><<<red_grid((int)N0), OD_THREADS, 0, stream>>>(L, K[0], st, zbuf, partials);
+        scale_kernel<<<nblk((int)N0), OD_THREADS, 0, stream>>>(pyr[0], (int)N0, st, 0);
+        scale_kernel<<<nblk((int)N0), OD_THREADS, 0, stream>>>(pyr[2], (int)N0, st, 1);
+        B2R_CHECK_LAUNCH();
+    }
+    // pyramids: colour = Downsample(Gaussian3(prev)), depth = Downsample(prev)
+    for (int l = 1; l < n_levels; l++) {
+        const int n_prev = Wl[l - 1] * Hl[l - 1], n_cur = Wl[l] * Hl[l];
+        for (int img = 0; img < 4; img++) {
+            const float* prev = pyr[img] + off[l - 1];
+            if (img == 0 || img == 2) {
+                filter3_kernel<false><<<nblk(n_prev), OD_THREADS, 0, stream>>>(prev, tmp, Wl[l - 1], Hl[l - 1], 0, 0.f, 0.f);
+                downsample_kernel<<<nblk(n_cur), OD_THREADS, 0, stream>>>(tmp, pyr[img] + off[l], Wl[l - 1], Hl[l - 1]);
+            } else {
+                downsample_kernel<<<nblk(n_cur), OD_THREADS, 0, stream>>>(prev, pyr[img] + off[l], Wl[l - 1], Hl[l - 1]);
+            }
+        }
+    }
+    // Sobel of the target colour and depth pyramids
+    for (int l = 0; l < n_levels; l++) {
+        const int n = Wl[l] * Hl[l];
+        filter3_kernel<false><<<nblk(n), OD_THREADS, 0, stream>>>(pyr[2] + off[l], pyr[4] + off[l], Wl[l], Hl[l], 1, 0.f, 0.f);
+        filter3_kernel<false><<<nblk(n), OD_THREADS, 0, stream>>>(pyr[2] + off[l], pyr[5] + off[l], Wl[l], Hl[l], 2, 0.f, 0.f);
+        filter3_kernel<false><<<nblk(n), OD_THREADS, 0, stream>>>(pyr[3] + off[l], pyr[6] + off[l], Wl[l], Hl[l], 1, 0.f, 0.f);
+        filter3_kernel<false><<<nblk(n), OD_THREADS, 0, stream>>>(pyr[3] + off[l], pyr[7] + off[l], Wl[l], Hl[l], 2, 0.f, 0.f);
+    }
+    B2R_CHECK_LAUNCH();
+    // coarse-to-fine Gauss-Newton, 2 launches per iteration, no host sync
+    for (int l = n_levels - 1; l >= 0; l--) {
+        const LevelImgs L = level(l);
+        const int n = Wl[l] * Hl[l];
+        const int n_it = iters_host[n_levels - 1 - l];
+        for (int it = 0; it < n_it; it++) {
+            corr_warp_kernel<<<nblk(n), OD_THREADS, 0, stream>>>(L.sd, L.td, L.W, L.H, K[l], st, depth_diff_max, zbuf);
+            if (jac_kind == 0) reduce_kernel<0><<<red_grid(n), OD_THREADS, 0, stream>>>(L, K[l], st, zbuf, partials);
+            else reduce_kernel<1><<<red_grid(n), OD_THREADS, 0, stream>>>(L, K[l], st, zbuf, partials);
+        }
+        B2R_CHECK_LAUNCH();
+    }
+    // CreateInformationMatrix at the final pose
+    {
+        const LevelImgs L = level(0);
+        corr_warp_kernel<<<nblk((int)N0), OD_THREADS, 0, stream>>>(L.sd, L.td, W, H, K[0], st, depth_diff_max, zbuf);
+        reduce_kernel<3><<<red_grid((int)N0), OD_THREADS, 0, stream>>>(L, K[0], st, zbuf, partials);
+        B2R_CHECK_LAUNCH();
+    }
+    OdoState h1;
+    B2R_CUDA(cudaMemcpyAsync(&h1, st, sizeof(h1), cudaMemcpyDeviceToHost, stream));
+    B2R_CUDA(cudaStreamSynchronize(stream));
+    bool ok = !h1.failed;
+    for (int i = 0; i < 16; i++) ok = ok && std::isfinite(h1.pose[i]);
+    if (ok) {
+        memcpy(out_T_host, h1.pose, sizeof(h1.pose));
+        memcpy(out_info_host, h1.info, sizeof(h1.info));
+        *success_host = 1;
+    } else {
+        b2r::m4_identity(out_T_host);
+        for (int i = 0; i < 36; i++) out_info_host[i] = (i % 7 == 0) ? 1.0 : 0.0;
+        *success_host = 0;
+    }
+    return B2R_OK;
+}
+
+// Building blocks exposed for the parity tests of the image kernels (not part of the reference-facing API).
+B2R_API int b2r_image_filter(const float* in, int W, int H, int kind, float* out, cudaStream_t stream) {
+    if (!in || !out || kind < 0 || kind > 2) return B2R_ERR_BAD_ARG;
+    filter3_kernel<false><<<nblk(W * H), OD_THREADS, 0, stream>>>(in, out, W, H, kind, 0.f, 0.f);
+    B2R_CHECK_LAUNCH();
+    return B2R_OK;
+}
+B2R_API int b2r_image_downsample(const float* in, int W, int H, float* out, cudaStream_t stream) {
+    if (!in || !out) return B2R_ERR_BAD_ARG;
+    downsample_kernel<<<nblk((W / 2) * (H / 2)), OD_THREADS, 0, stream>>>(in, out, W, H);
+    B2R_CHECK_LAUNCH();
+    return B2R_OK;
+}

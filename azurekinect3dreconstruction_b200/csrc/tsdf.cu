@@ -160,11 +160,12 @@ struct FuseParams {
     int64_t unit_stride;     // floats per unit
     int32_t* counters;
     int touched_word;
+    int cap_units;
 };
 
 template <int COLOR>
 __global__ void __launch_bounds__(256) tsdf_fuse_kernel(const FuseParams P) {
-    const int T = min(P.counters[P.touched_word], INT_MAX / 4);
+    const int T = min(P.counters[P.touched_word], P.cap_units);
     const int nwork = T * 4;
     const int tid = threadIdx.x;
     const int zq = tid & 3, y = (tid >> 2) & 15, xl = tid >> 6;
@@ -283,6 +284,8 @@ static void tsdf_free(b2r_tsdf* h) {
         cudaFree(h->stage_depth[i]); cudaFree(h->stage_color[i]);
     }
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    for (int i = 0; i < h->prof_cap; i++) cudaEventDestroy(h->prof_ev[i]);
+    delete[] h->prof_ev;
     delete h;
 }
 
@@ -418,8 +421,11 @@ static int tsdf_integrate_impl(b2r_tsdf* h, const void* depth, int depth_is_u16,
     P.frame_id = h->frame_id; P.rank = h->rank; P.world = h->world;
     P.hash = h->hash; P.slot_stamp = h->slot_stamp; P.unit_keys = h->unit_keys; P.touched = h->touched[buf];
     P.counters = h->counters; P.touched_word = tw; P.cap_units = (int)h->cap_units;
+    const bool prof = h->profile && h->prof_n + 3 <= h->prof_cap;
+    if (prof) cudaEventRecord(h->prof_ev[h->prof_n], stream);
     tsdf_pack_alloc_kernel<<<(unsigned)((npx + 255) / 256), 256, 0, stream>>>(P);
     B2R_CHECK_LAUNCH();
+    if (prof) cudaEventRecord(h->prof_ev[h->prof_n + 1], stream);
 
     FuseParams F;
     memset(&F, 0, sizeof(F));
@@ -433,11 +439,12 @@ static int tsdf_integrate_impl(b2r_tsdf* h, const void* depth, int depth_is_u16,
     F.unit_length = h->unit_length;
     F.touched = h->touched[buf]; F.hash_vals = h->hash.vals; F.unit_keys = h->unit_keys;
     F.pool = h->pool; F.unit_stride = (int64_t)h->planes * B2R_UNIT_VOX;
-    F.counters = h->counters; F.touched_word = tw;
+    F.counters = h->counters; F.touched_word = tw; F.cap_units = (int)h->cap_units;
     if (h->color_type == 0) tsdf_fuse_kernel<0><<<h->fuse_grid, 256, 0, stream>>>(F);
     else if (h->color_type == 1) tsdf_fuse_kernel<1><<<h->fuse_grid, 256, 0, stream>>>(F);
     else tsdf_fuse_kernel<2><<<h->fuse_grid, 256, 0, stream>>>(F);
     B2R_CHECK_LAUNCH();
+    if (prof) { cudaEventRecord(h->prof_ev[h->prof_n + 2], stream); h->prof_n += 3; }
     return B2R_OK;
 }
 
@@ -626,5 +633,37 @@ B2R_API int b2r_tsdf_import_units(b2r_tsdf* h, const int32_t* keys3, int64_t n, 
     dim3 grid(4, (unsigned)n);
     tsdf_import_planes_kernel<<<grid, 256, 0, stream>>>(h->pool, (int64_t)h->planes * B2R_UNIT_VOX, h->planes, ids, (int)n, tsdf, weight, rgb);
     B2R_CHECK_LAUNCH();
+    return B2R_OK;
+}
+
+// Per-kernel timing for the roofline line of bench.py: enable (max_frames > 0) / disable (0).
+B2R_API int b2r_tsdf_profile(b2r_tsdf* h, int max_frames) {
+    if (!h || max_frames < 0) return B2R_ERR_BAD_ARG;
+    B2RDeviceGuard g(h->device);
+    const int need = max_frames * 3;
+    if (need > h->prof_cap) {
+        cudaEvent_t* ev = new cudaEvent_t[need];
+        for (int i = 0; i < h->prof_cap; i++) ev[i] = h->prof_ev[i];
+        for (int i = h->prof_cap; i < need; i++) B2R_CUDA(cudaEventCreate(&ev[i]));
+        delete[] h->prof_ev;
+        h->prof_ev = ev; h->prof_cap = need;
+    }
+    h->profile = max_frames > 0; h->prof_n = 0;
+    return B2R_OK;
+}
+// out[0] = frames timed, out[1] = total ms in K1 (pack+alloc), out[2] = total ms in K2 (fuse). Synchronises.
+B2R_API int b2r_tsdf_profile_read(b2r_tsdf* h, double* out3) {
+    if (!h || !out3) return B2R_ERR_BAD_ARG;
+    B2RDeviceGuard g(h->device);
+    B2R_CUDA(cudaDeviceSynchronize());
+    double k1 = 0.0, k2 = 0.0;
+    for (int i = 0; i + 3 <= h->prof_n; i += 3) {
+        float a = 0.f, b = 0.f;
+        B2R_CUDA(cudaEventElapsedTime(&a, h->prof_ev[i], h->prof_ev[i + 1]));
+        B2R_CUDA(cudaEventElapsedTime(&b, h->prof_ev[i + 1], h->prof_ev[i + 2]));
+        k1 += a; k2 += b;
+    }
+    out3[0] = h->prof_n / 3; out3[1] = k1; out3[2] = k2;
+    h->prof_n = 0;
     return B2R_OK;
 }

@@ -42,6 +42,10 @@ struct b2r_tsdf {
     // extraction scratch
     void* scratch;
     size_t scratch_bytes;
+    // optional per-kernel timing (b2r_tsdf_profile): 3 events per frame (before K1, between, after K2)
+    int profile;
+    cudaEvent_t* prof_ev;
+    int prof_cap, prof_n;
 };
 
 struct B2RDeviceGuard {

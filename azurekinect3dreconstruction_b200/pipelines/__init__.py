@@ -1,0 +1,2 @@
+"""o3d.pipelines look-alike: integration (TSDF), odometry, registration."""
+from . import integration, odometry, registration  # noqa: F401

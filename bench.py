@@ -1,0 +1,309 @@
+#!/usr/bin/env python3
+"""bench.py -- BASELINE.json metric: TSDF-integrated depth frames/sec (640x576) on 1/2/4/8 B200 + % HBM roofline.
+
+Workload (BASELINE.json configs[2], SURVEY.md 8(d) "C3"): ScalableTSDFVolume integration of a 300-frame
+synthetic orbit trajectory, NFOV 640x576 u16 depth + aligned u8 RGB, 4 mm voxels, sdf_trunc 2 cm, 16^3
+units, depth_sampling_stride 4.  One STEP = volume.reset() + integrate all frames of the trajectory.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--frames F] [--impl reference]
+
+* value   : frames/s with the frames resident in HBM (device-timed, CUDA events, max over ranks).
+* e2e     : the same through the public Python API with HOST (pinned) frames: H2D copies inside the timed
+            region (overlapped by the library's 3-deep ring) and a D2H read of the volume stats per step.
+* roofline: tsdf_fuse_kernel, algorithmic bytes (40 B x updated voxels + 7 B x W x H per frame)
+            over its CUDA-event duration, against MEASURED_PEAKS.json hbm_gbs.
+* cpu_baseline: the CPU oracle (port of Open3D 0.19 legacy semantics; Open3D itself cannot be installed
+            here) on a bounded sample of the same frames, all host threads.
+* N > 1   : the volume is sharded by unit-key hash; every rank sees every frame (resident in its
+            HBM) and integrates only its own units; no data-path collective; strong scaling.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+VOXEL, TRUNC = 0.004, 0.02
+DEPTH_SCALE, DEPTH_TRUNC = 1000.0, 3.0
+RECORD_BYTES = 20          # tsdf f32 + weight f32 + rgb 3 x f32 (SURVEY 8(d) canonical record R)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--frames", type=int, default=300)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--ref-frames", type=int, default=6, help="frames per step of the CPU reference arm")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_config(args, extra=None):
+    cfg = {"workload": "configs[2]: ScalableTSDFVolume.integrate over a %d-frame synthetic orbit, NFOV 640x576 u16 depth + "
+                       "aligned u8 RGB, voxel 4 mm, sdf_trunc 2 cm, unit 16^3, stride 4; step = reset + all frames" % args.frames,
+           "frames_per_step": args.frames, "voxel_length": VOXEL, "sdf_trunc": TRUNC, "color_type": "RGB8",
+           "l2_policy": "inputs (%.0f MB of frames) and the touched voxel pool are larger than the 126 MB L2" % (args.frames * 1.84)}
+    if extra:
+        cfg.update(extra)
+    return cfg
+
+
+def make_frames(n_frames, device, trajectory_len=None):
+    """Render the trajectory (torch, on `device`). Returns depth (n,H,W) uint16, rgb (n,H,W,3) uint8, extrinsics (n,4,4)."""
+    import torch
+    from azurekinect3dreconstruction_b200 import synthetic as syn
+    kin = syn.SyntheticKinect(seed=0, dropout=0.02, noise_sigma_mm=1.0, device=str(device))
+    poses = syn.orbit_trajectory(trajectory_len or n_frames)[:n_frames]
+    H, W = kin.depth_intr["height"], kin.depth_intr["width"]
+    depth = torch.empty((n_frames, H, W), dtype=torch.int16, device=device)
+    rgb = torch.empty((n_frames, H, W, 3), dtype=torch.uint8, device=device)
+    for i, p in enumerate(poses):
+        d, c = kin.render_depth_aligned_rgb(p)
+        depth[i] = d.view(torch.int16)
+        rgb[i] = c
+    E = np.stack([np.linalg.inv(p) for p in poses])
+    return depth.view(torch.uint16), rgb, E, kin.depth_intr
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index):
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            out, _ = self.p.communicate(timeout=5)
+        except Exception:
+            self.p.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def hbm_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def cpu_reference(depth_np, rgb_np, E, intr, n_frames, steps, warmup):
+    """Times the CPU oracle (Open3D-legacy port, OpenMP over units, all host threads). Returns (frames/s, ms/step, cores)."""
+    from oracle import o3r
+    Kt = (intr["fx"], intr["fy"], intr["cx"], intr["cy"])
+    vol = o3r.TSDF(VOXEL, TRUNC, 1, 16, 4, parallel_units=True)
+    times = []
+    for s in range(warmup + steps):
+        vol.reset()
+        t0 = time.perf_counter()
+        for i in range(n_frames):
+            # RGBDImage conversion is part of the path the GPU arm fuses (a1), so it is timed here too
+            d = o3r.depth_to_float(depth_np[i], DEPTH_SCALE, DEPTH_TRUNC)
+            vol.integrate(d, Kt, E[i], rgb=rgb_np[i])
+        dt = time.perf_counter() - t0
+        if s >= warmup:
+            times.append(dt)
+    total = sum(times)
+    return n_frames * len(times) / total, 1e3 * total / len(times), o3r.num_threads()
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the path.  Open3D 0.19 cannot be installed or
+    compiled here (no sources under /root/reference, no network), so this is the oracle port, all host threads,
+    on a bounded sample (the first --ref-frames frames of the same trajectory per step)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import torch
+    nf = max(1, min(args.ref_frames, args.frames))
+    depth, rgb, E, intr = make_frames(nf, torch.device("cpu"), args.frames)
+    depth_np = depth.view(torch.int16).numpy().view(np.uint16)
+    rgb_np = rgb.numpy()
+    fps, ms, cores = cpu_reference(depth_np, rgb_np, E, intr, nf, args.steps, args.warmup)
+    line = {"metric": "tsdf_integrated_depth_frames_per_sec_640x576", "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
+            "config": workload_config(args, {"sample": "first %d frames of the trajectory per step" % nf}),
+            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
+                             "sample": "reset + first %d frames of the %d-frame trajectory per step, OpenMP over volume units" % (nf, args.frames)},
+            "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference(args)
+    import torch
+    import torch.distributed as dist
+    import azurekinect3dreconstruction_b200 as o3d
+    from azurekinect3dreconstruction_b200 import _lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n_gpus = world
+
+    depth, rgb, E, intr = make_frames(args.frames, dev)
+    F, H, W = depth.shape
+    K = o3d.camera.PinholeCameraIntrinsic(W, H, intr["fx"], intr["fy"], intr["cx"], intr["cy"])
+    TT = o3d.pipelines.integration.TSDFVolumeColorType
+    cap = int(os.environ.get("B2R_BENCH_CAPACITY_UNITS", "40000"))
+    vol = o3d.pipelines.integration.ScalableTSDFVolume(VOXEL, TRUNC, TT.RGB8, capacity_units=cap, rank=rank, world=world)
+    lib = _lib.load()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device():
+        vol.reset()
+        vol.integrate_raw(depth, rgb, K, E, DEPTH_SCALE, DEPTH_TRUNC)
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    # ---- device-resident arm ------------------------------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    ms = timed(step_device, args.steps)
+    clocks = sampler.stop() if sampler else None
+    st = vol.stats()
+    fps = args.frames * args.steps / (ms * 1e-3)
+
+    # ---- per-kernel pass for the roofline (same workload, CUDA events around each kernel) ---------------
+    _lib.check(lib.b2r_tsdf_profile(vol._h, args.frames))
+    before = vol.stats()
+    vol.reset()
+    upd0 = 0
+    vol.integrate_raw(depth, rgb, K, E, DEPTH_SCALE, DEPTH_TRUNC)
+    prof = (C.c_double * 3)()
+    _lib.check(lib.b2r_tsdf_profile_read(vol._h, prof))
+    _lib.check(lib.b2r_tsdf_profile(vol._h, 0))
+    st1 = vol.stats()
+    n_upd_step = st1["updated_voxels"] - upd0
+    n_timed = max(1.0, prof[0])
+    fuse_ms = prof[2] / n_timed
+    pack_ms = prof[1] / n_timed
+    algo_bytes = RECORD_BYTES * 2.0 * n_upd_step / args.frames + 7.0 * W * H
+    peak, peak_src = hbm_peak()
+    achieved = algo_bytes / (fuse_ms * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "fuse_kernel_traffic.json")
+    if os.path.exists(tpath):
+        try:
+            with open(tpath) as f:
+                traffic = json.load(f).get("dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+    roofline = {"kernel": "tsdf_fuse_kernel<RGB8>", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": algo_bytes, "avg_launch_ms": fuse_ms, "pack_alloc_kernel_avg_ms": pack_ms,
+                "updated_voxels_per_frame": n_upd_step / args.frames, "touched_units_per_frame": st1["touched_units"] / args.frames,
+                "kernel_share_of_step": (prof[2]) / max(1e-9, ms / args.steps)}
+
+    # ---- end-to-end arm: host (pinned) frames through the public API -----------------------------------
+    depth_h = depth.view(torch.int16).cpu().pin_memory().view(torch.uint16)
+    rgb_h = rgb.cpu().pin_memory()
+    d2h_bytes = 5 * 8
+
+    def step_e2e():
+        vol.reset()
+        vol.integrate_raw(depth_h, rgb_h, K, E, DEPTH_SCALE, DEPTH_TRUNC)
+        vol.stats()            # D2H read of the step's result (units allocated / voxels updated)
+
+    for _ in range(3):
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+    fps_e2e = args.frames * args.steps / (ms_e2e * 1e-3)
+    h2d_bytes = int(depth_h.numel() * 2 + rgb_h.numel())
+
+    # ---- CPU baseline (rank 0, bounded sample) ---------------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        nf = max(1, min(args.ref_frames, args.frames))
+        dn = depth_h[:nf].view(torch.int16).numpy().view(np.uint16)
+        cn = rgb_h[:nf].numpy()
+        cfps, cms, cores = cpu_reference(dn, cn, E[:nf], intr, nf, 2, 1)
+        cpu = {"value": cfps, "unit": "frames/s", "cores": cores, "kind": "port",
+               "sample": "reset + first %d frames of the trajectory, 2 timed passes, OpenMP over volume units" % nf}
+
+    if rank == 0:
+        line = {"metric": "tsdf_integrated_depth_frames_per_sec_640x576", "value": fps, "unit": "frames/s", "n_gpus": n_gpus,
+                "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": workload_config(args, {"sharding": "unit-key hash over %d rank(s)" % world, "units_allocated_rank0": st["num_units"]}),
+                "roofline": roofline, "cpu_baseline": cpu,
+                "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
+                        "ms_per_step": ms_e2e / args.steps},
+                "gpu_launches": args.steps * args.frames * 2, "clocks": clocks}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

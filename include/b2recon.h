@@ -114,6 +114,10 @@ int b2r_tsdf_integrate_host(b2r_tsdf* h, int n, const void* depth_host, int dept
  * out[3]=cumulative updated voxels (N_upd), out[4]=cumulative touched units.  Synchronises. */
 int b2r_tsdf_stats(b2r_tsdf* h, int64_t* out5_host, cudaStream_t stream);
 int64_t b2r_tsdf_num_units(b2r_tsdf* h, cudaStream_t stream);
+/* per-kernel CUDA-event timing for the roofline line of bench.py: enable for up to max_frames frames
+ * (0 = off); read: out3 = {frames timed, total ms pack+alloc kernel, total ms fuse kernel} */
+int b2r_tsdf_profile(b2r_tsdf* h, int max_frames);
+int b2r_tsdf_profile_read(b2r_tsdf* h, double* out3_host);
 /* parity / checkpoint hooks: keys int32[n][3]; planes tsdf[n][4096], weight[n][4096], rgb[n][3][4096],
  * voxel index x*256 + y*16 + z (upstream IndexOf) */
 int b2r_tsdf_export_keys(b2r_tsdf* h, int32_t* keys3, int64_t n, cudaStream_t stream);
@@ -142,6 +146,11 @@ int b2r_odometry(const float* src_gray, const float* src_depth, const float* tgt
                  int H, double fx, double fy, double cx, double cy, const double* init_host, int jac_kind,
                  const int* iters_host, int n_levels, double depth_diff_max, double depth_min, double depth_max,
                  double* out_T_host, double* out_info_host, int* success_host, cudaStream_t stream);
+
+/* image building blocks of a12, exposed for parity tests (Image::Filter Gaussian3/Sobel3Dx/Sobel3Dy =
+ * kind 0/1/2, Image::Downsample) */
+int b2r_image_filter(const float* in, int W, int H, int kind, float* out, cudaStream_t stream);
+int b2r_image_downsample(const float* in, int W, int H, float* out, cudaStream_t stream);
 
 /* ---- a13: registration_icp(..., TransformationEstimationPointToPlane(), ICPConvergenceCriteria(...))
  *      (GoodColorReconstruction.py:194-198, BetterVisualizer2CamWorksCOLOR.py:255-259).

@@ -1,0 +1,267 @@
+"""ctypes wrapper of the CPU oracle (oracle/liboracle.so).  TEST INFRASTRUCTURE ONLY.
+
+Importable from tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs --
+never from the product package.  PARITY UNPINNED vs real Open3D (see oracle.cpp header).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_DIR = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_DIR, "liboracle.so")
+_lib = None
+
+_vp, _i, _i64, _d = C.c_void_p, C.c_int, C.c_int64, C.c_double
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    src = os.path.join(_DIR, "oracle.cpp")
+    if not os.path.exists(_LIB) or (os.path.exists(src) and os.path.getmtime(src) > os.path.getmtime(_LIB)):
+        subprocess.run(["make", "-C", _DIR], check=True, capture_output=True)
+    L = C.CDLL(_LIB)
+    L.o3r_depth_u16_to_f32.argtypes = [_vp, _i64, _d, _d, _vp]
+    L.o3r_rgb_to_intensity.argtypes = [_vp, _i64, _vp]
+    L.o3r_unproject.restype = _i64
+    L.o3r_unproject.argtypes = [_vp, _i, _i, _vp, _vp, _d, _d, _d, _d, _vp, _i, _i, _vp, _vp, _vp]
+    L.o3r_transform_points.argtypes = [_vp, _i64, _vp, _vp]
+    L.o3r_color_gather_index.argtypes = [_vp, _i, _i, _d, _d, _d, _d, _d, _d, _i, _i, _d, _d, _d, _d, _vp, _vp]
+    L.o3r_tsdf_create.restype = _vp
+    L.o3r_tsdf_create.argtypes = [_d, _d, _i, _i, _i]
+    L.o3r_tsdf_destroy.argtypes = [_vp]
+    L.o3r_tsdf_reset.argtypes = [_vp]
+    L.o3r_tsdf_set_parallel_units.argtypes = [_vp, _i]
+    for n in ("o3r_tsdf_num_units", "o3r_tsdf_last_updated", "o3r_tsdf_last_touched", "o3r_tsdf_extract_points"):
+        getattr(L, n).restype = _i64
+        getattr(L, n).argtypes = [_vp]
+    L.o3r_tsdf_integrate.argtypes = [_vp, _vp, _vp, _vp, _i, _i, _d, _d, _d, _d, _vp]
+    L.o3r_tsdf_export_keys.argtypes = [_vp, _vp]
+    L.o3r_tsdf_export_unit.argtypes = [_vp, _vp, _vp, _vp, _vp]
+    L.o3r_tsdf_import_unit.argtypes = [_vp, _vp, _vp, _vp, _vp]
+    L.o3r_tsdf_extract_points_copy.argtypes = [_vp, _vp, _vp, _vp]
+    L.o3r_tsdf_extract_mesh.restype = _i64
+    L.o3r_tsdf_extract_mesh.argtypes = [_vp, C.POINTER(C.c_int64)]
+    L.o3r_tsdf_extract_mesh_copy.argtypes = [_vp, _vp, _vp, _vp]
+    L.o3r_mesh_vertex_normals.argtypes = [_vp, _i64, _vp, _i64, _vp]
+    L.o3r_odometry.argtypes = [_vp, _vp, _vp, _vp, _i, _i, _d, _d, _d, _d, _vp, _i, _vp, _i, _d, _d, _d, _vp, _vp, _vp]
+    L.o3r_filter.argtypes = [_vp, _i, _i, _i, _vp]
+    L.o3r_downsample.argtypes = [_vp, _i, _i, _vp]
+    L.o3r_correspondence.restype = _i64
+    L.o3r_correspondence.argtypes = [_vp, _vp, _i, _i, _d, _d, _d, _d, _vp, _d, _vp, _i64]
+    L.o3r_icp_point_to_plane.argtypes = [_vp, _i64, _vp, _vp, _i64, _d, _vp, _i, _d, _d, _vp, C.POINTER(C.c_double), C.POINTER(C.c_double), _vp]
+    L.o3r_m4_inverse.argtypes = [_vp, _vp]
+    L.o3r_solve6.argtypes = [_vp, _vp, _vp]
+    L.o3r_vec6_to_m4.argtypes = [_vp, _vp]
+    _lib = L
+    return L
+
+
+def _f64(a):
+    return np.ascontiguousarray(np.asarray(a, dtype=np.float64))
+
+
+def num_threads() -> int:
+    return int(lib().o3r_num_threads())
+
+
+def depth_to_float(depth_u16, depth_scale=1000.0, depth_trunc=3.0):
+    d = np.ascontiguousarray(depth_u16, dtype=np.uint16)
+    out = np.empty(d.shape, np.float32)
+    lib().o3r_depth_u16_to_f32(_p(d), d.size, depth_scale, depth_trunc, _p(out))
+    return out
+
+
+def rgb_to_intensity(rgb):
+    c = np.ascontiguousarray(rgb, dtype=np.uint8)
+    out = np.empty(c.shape[:2], np.float32)
+    lib().o3r_rgb_to_intensity(_p(c), out.size, _p(out))
+    return out
+
+
+def unproject(depth_f32, K, extrinsic=None, rgb=None, gray=None, stride=1, valid_only=True):
+    """K = (fx, fy, cx, cy). Returns (xyz (N,3) f64, col (N,3) f64 or None, src_index (N,) i32)."""
+    d = np.ascontiguousarray(depth_f32, dtype=np.float32)
+    H, W = d.shape
+    E = _f64(np.eye(4) if extrinsic is None else extrinsic)
+    cap = ((W + stride - 1) // stride) * ((H + stride - 1) // stride)
+    xyz = np.empty((cap, 3), np.float64)
+    has_c = rgb is not None or gray is not None
+    col = np.empty((cap, 3), np.float64) if has_c else None
+    idx = np.empty((cap,), np.int32)
+    rgb_c = np.ascontiguousarray(rgb, dtype=np.uint8) if rgb is not None else None
+    gray_c = np.ascontiguousarray(gray, dtype=np.float32) if gray is not None else None
+    n = lib().o3r_unproject(_p(d), W, H, _p(rgb_c), _p(gray_c), K[0], K[1], K[2], K[3], _p(E), stride, 1 if valid_only else 0,
+                            _p(xyz), _p(col), _p(idx))
+    if n < 0:
+        raise RuntimeError("oracle unproject failed")
+    return xyz[:n], (col[:n] if has_c else None), idx[:n]
+
+
+def transform_points(xyz, T, normals=None):
+    p = _f64(xyz).copy()
+    n = _f64(normals).copy() if normals is not None else None
+    lib().o3r_transform_points(_p(p), p.shape[0], _p(_f64(T)), _p(n))
+    return (p, n) if normals is not None else p
+
+
+def color_gather_index(depth_u16, Kd, Wc, Hc, Kc, d2c, depth_scale=1000.0, depth_trunc=3.0):
+    d = np.ascontiguousarray(depth_u16, dtype=np.uint16)
+    H, W = d.shape
+    out = np.empty((H, W), np.int32)
+    lib().o3r_color_gather_index(_p(d), W, H, depth_scale, depth_trunc, Kd[0], Kd[1], Kd[2], Kd[3], Wc, Hc, Kc[0], Kc[1], Kc[2], Kc[3],
+                                 _p(_f64(d2c)), _p(out))
+    return out
+
+
+class TSDF:
+    def __init__(self, voxel_length, sdf_trunc, color_type=1, res=16, stride=4, parallel_units=False):
+        self.h = lib().o3r_tsdf_create(voxel_length, sdf_trunc, color_type, res, stride)
+        self.res, self.color_type = res, color_type
+        if parallel_units:
+            lib().o3r_tsdf_set_parallel_units(self.h, 1)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().o3r_tsdf_destroy(self.h)
+            self.h = None
+
+    def reset(self):
+        lib().o3r_tsdf_reset(self.h)
+
+    def integrate(self, depth_f32, K, extrinsic, rgb=None, gray=None):
+        d = np.ascontiguousarray(depth_f32, dtype=np.float32)
+        H, W = d.shape
+        c = np.ascontiguousarray(rgb, dtype=np.uint8) if rgb is not None else None
+        g = np.ascontiguousarray(gray, dtype=np.float32) if gray is not None else None
+        rc = lib().o3r_tsdf_integrate(self.h, _p(d), _p(c), _p(g), W, H, K[0], K[1], K[2], K[3], _p(_f64(extrinsic)))
+        if rc != 0:
+            raise RuntimeError("[ScalableTSDFVolume::Integrate] Unsupported image format." if rc == -1 else "singular extrinsic")
+
+    def num_units(self):
+        return int(lib().o3r_tsdf_num_units(self.h))
+
+    def last_updated(self):
+        return int(lib().o3r_tsdf_last_updated(self.h))
+
+    def last_touched(self):
+        return int(lib().o3r_tsdf_last_touched(self.h))
+
+    def keys(self):
+        k = np.empty((self.num_units(), 3), np.int32)
+        lib().o3r_tsdf_export_keys(self.h, _p(k))
+        return k
+
+    def unit(self, key):
+        n = self.res ** 3
+        t, w, c = np.empty(n, np.float32), np.empty(n, np.float32), np.empty((n, 3), np.float64)
+        k = np.ascontiguousarray(key, dtype=np.int32)
+        if lib().o3r_tsdf_export_unit(self.h, _p(k), _p(t), _p(w), _p(c)) != 0:
+            return None
+        return t, w, c
+
+    def import_unit(self, key, tsdf, weight, rgb=None):
+        k = np.ascontiguousarray(key, dtype=np.int32)
+        t = np.ascontiguousarray(tsdf, dtype=np.float32)
+        w = np.ascontiguousarray(weight, dtype=np.float32)
+        c = _f64(rgb) if rgb is not None else None
+        lib().o3r_tsdf_import_unit(self.h, _p(k), _p(t), _p(w), _p(c))
+
+    def extract_points(self):
+        n = int(lib().o3r_tsdf_extract_points(self.h))
+        xyz, nrm, ids = np.empty((n, 3)), np.empty((n, 3)), np.empty((n, 4), np.int32)
+        rgb = np.empty((n, 3)) if self.color_type else None
+        lib().o3r_tsdf_extract_points_copy(_p(xyz), _p(rgb), _p(nrm), _p(ids))
+        return xyz, rgb, nrm, ids
+
+    def extract_mesh(self):
+        nF = C.c_int64(0)
+        nV = int(lib().o3r_tsdf_extract_mesh(self.h, C.byref(nF)))
+        vtx, ids = np.empty((nV, 3)), np.empty((nV, 4), np.int32)
+        vcol = np.empty((nV, 3)) if self.color_type else None
+        tri = np.empty((int(nF.value), 3), np.int32)
+        lib().o3r_tsdf_extract_mesh_copy(_p(vtx), _p(vcol), _p(tri), _p(ids))
+        return vtx, vcol, tri, ids
+
+
+def mesh_vertex_normals(vtx, tri):
+    v, t = _f64(vtx), np.ascontiguousarray(tri, dtype=np.int32)
+    out = np.empty_like(v)
+    lib().o3r_mesh_vertex_normals(_p(v), v.shape[0], _p(t), t.shape[0], _p(out))
+    return out
+
+
+def odometry(src_gray, src_depth, tgt_gray, tgt_depth, K, init=None, jac_kind=1, iters=(20, 10, 5), depth_diff_max=0.03,
+             depth_min=0.0, depth_max=4.0):
+    a = [np.ascontiguousarray(x, dtype=np.float32) for x in (src_gray, src_depth, tgt_gray, tgt_depth)]
+    H, W = a[0].shape
+    init = _f64(np.eye(4) if init is None else init)
+    it = np.ascontiguousarray(iters, dtype=np.int32)
+    T, info, dbg = np.empty((4, 4)), np.empty((6, 6)), np.zeros(len(iters), np.int32)
+    ok = lib().o3r_odometry(_p(a[0]), _p(a[1]), _p(a[2]), _p(a[3]), W, H, K[0], K[1], K[2], K[3], _p(init), jac_kind, _p(it), len(iters),
+                            depth_diff_max, depth_min, depth_max, _p(T), _p(info), _p(dbg))
+    return bool(ok), T, info, dbg
+
+
+def image_filter(img, kind):
+    a = np.ascontiguousarray(img, dtype=np.float32)
+    out = np.empty_like(a)
+    lib().o3r_filter(_p(a), a.shape[1], a.shape[0], kind, _p(out))
+    return out
+
+
+def image_downsample(img):
+    a = np.ascontiguousarray(img, dtype=np.float32)
+    out = np.empty((a.shape[0] // 2, a.shape[1] // 2), np.float32)
+    lib().o3r_downsample(_p(a), a.shape[1], a.shape[0], _p(out))
+    return out
+
+
+def correspondence(ds, dt, K, E, depth_diff_max=0.03):
+    a, b = np.ascontiguousarray(ds, dtype=np.float32), np.ascontiguousarray(dt, dtype=np.float32)
+    H, W = a.shape
+    out = np.empty((W * H, 4), np.int32)
+    n = lib().o3r_correspondence(_p(a), _p(b), W, H, K[0], K[1], K[2], K[3], _p(_f64(E)), depth_diff_max, _p(out), W * H)
+    return out[:n]
+
+
+def icp_point_to_plane(src, tgt, tgt_nrm, max_dist, init=None, max_iter=30, rel_fitness=1e-6, rel_rmse=1e-6):
+    s, t = _f64(src), _f64(tgt)
+    n = _f64(tgt_nrm) if tgt_nrm is not None else None
+    init = _f64(np.eye(4) if init is None else init)
+    T = np.empty((4, 4))
+    fit, rmse = C.c_double(0), C.c_double(0)
+    corr = np.empty((s.shape[0],), np.int32)
+    it = lib().o3r_icp_point_to_plane(_p(s), s.shape[0], _p(t), _p(n), t.shape[0], max_dist, _p(init), max_iter, rel_fitness, rel_rmse,
+                                      _p(T), C.byref(fit), C.byref(rmse), _p(corr))
+    if it < 0:
+        raise RuntimeError("[RegistrationICP] invalid arguments (%d)" % it)
+    return T, float(fit.value), float(rmse.value), corr, int(it)
+
+
+def m4_inverse(m):
+    out = np.empty((4, 4))
+    if lib().o3r_m4_inverse(_p(_f64(m)), _p(out)) != 0:
+        raise RuntimeError("singular")
+    return out
+
+
+def solve6(A, b):
+    x = np.empty(6)
+    rc = lib().o3r_solve6(_p(_f64(A)), _p(_f64(b)), _p(x))
+    return x if rc == 0 else None
+
+
+def vec6_to_m4(x):
+    T = np.empty((4, 4))
+    lib().o3r_vec6_to_m4(_p(_f64(x)), _p(T))
+    return T

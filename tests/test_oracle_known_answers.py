@@ -1,0 +1,355 @@
+"""Pins the CPU oracle with analytic known answers: the reference has no tests or golden
+vectors and Open3D cannot be installed here, so these closed-form cases are what anchors the oracle.
+CPU only (no GPU marker)."""
+import math
+
+import numpy as np
+import pytest
+
+K = (100.0, 110.0, 31.5, 23.5)
+W, H = 64, 48
+
+
+def plane_depth(D):
+    return np.full((H, W), D, np.float32)
+
+
+def test_depth_conversion_semantics(o3r):
+    d = np.array([[0, 999, 1000, 2999, 3000, 65535]], np.uint16)
+    f = o3r.depth_to_float(d, 1000.0, 3.0)
+    assert f.tolist() == [[0.0, np.float32(999) / np.float32(1000), 1.0, np.float32(2999) / np.float32(1000), 0.0, 0.0]]
+
+
+def test_intensity_weights(o3r):
+    rgb = np.array([[[255, 0, 0], [0, 255, 0], [0, 0, 255], [255, 255, 255]]], np.uint8)
+    g = o3r.rgb_to_intensity(rgb)
+    np.testing.assert_allclose(g[0], [0.299, 0.587, 0.114, 1.0], rtol=1e-6)
+
+
+def test_unproject_plane_closed_form(o3r):
+    D = 1.25
+    xyz, col, idx = o3r.unproject(plane_depth(D), K)
+    assert xyz.shape == (W * H, 3)
+    assert np.array_equal(idx, np.arange(W * H, dtype=np.int32))          # raster order, all valid
+    v, u = np.divmod(np.arange(W * H), W)
+    np.testing.assert_allclose(xyz[:, 0], (u - K[2]) * D / K[0], rtol=0, atol=1e-15)
+    np.testing.assert_allclose(xyz[:, 1], (v - K[3]) * D / K[1], rtol=0, atol=1e-15)
+    assert np.all(xyz[:, 2] == D)
+
+
+def test_unproject_compaction_and_extrinsic(o3r):
+    rng = np.random.default_rng(0)
+    d = plane_depth(2.0)
+    d[rng.random((H, W)) < 0.3] = 0.0
+    rgb = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+    th = 0.3
+    E = np.eye(4)
+    E[:3, :3] = [[math.cos(th), 0, math.sin(th)], [0, 1, 0], [-math.sin(th), 0, math.cos(th)]]
+    E[:3, 3] = [0.1, -0.2, 0.3]
+    xyz, col, idx = o3r.unproject(d, K, E, rgb=rgb)
+    valid = np.flatnonzero(d.reshape(-1) > 0)
+    assert np.array_equal(idx, valid.astype(np.int32))
+    v, u = np.divmod(valid, W)
+    cam = np.stack([(u - K[2]) * 2.0 / K[0], (v - K[3]) * 2.0 / K[1], np.full(valid.size, 2.0), np.ones(valid.size)], 1)
+    ref = (np.linalg.inv(E) @ cam.T).T[:, :3]
+    np.testing.assert_allclose(xyz, ref, atol=1e-13)
+    np.testing.assert_array_equal(col, rgb.reshape(-1, 3)[valid] / 255.0)
+    # stride + keep-invalid variants
+    xyz4, _, idx4 = o3r.unproject(d, K, stride=4, valid_only=False)
+    assert xyz4.shape[0] == (W // 4) * (H // 4)
+    assert np.isnan(xyz4[d[::4, ::4].reshape(-1) == 0]).all()
+    # empty image
+    xyz0, _, idx0 = o3r.unproject(np.zeros((H, W), np.float32), K)
+    assert xyz0.shape == (0, 3) and idx0.size == 0
+
+
+def test_transform_homogeneous(o3r):
+    p = np.array([[1.0, 2.0, 3.0]])
+    T = np.diag([1.0, -1.0, -1.0, 1.0])
+    np.testing.assert_array_equal(o3r.transform_points(p, T), [[1.0, -2.0, -3.0]])
+    T2 = np.eye(4)
+    T2[3, 3] = 2.0
+    np.testing.assert_array_equal(o3r.transform_points(p, T2), [[0.5, 1.0, 1.5]])
+
+
+def test_block_keys_single_pixel(o3r):
+    vl, trunc = 0.004, 0.02
+    ul = vl * 16
+    d = np.zeros((H, W), np.float32)
+    d[8, 12] = 1.0            # a stride-4 sample position
+    d[9, 13] = 1.0            # not sampled
+    vol = o3r.TSDF(vl, trunc, 0)
+    vol.integrate(d, K, np.eye(4))
+    p = np.array([(12 - K[2]) * 1.0 / K[0], (8 - K[3]) * 1.0 / K[1], 1.0])
+    lo, hi = np.floor((p - trunc) / ul).astype(int), np.floor((p + trunc) / ul).astype(int)
+    want = {(a, b, c) for a in range(lo[0], hi[0] + 1) for b in range(lo[1], hi[1] + 1) for c in range(lo[2], hi[2] + 1)}
+    assert {tuple(k) for k in vol.keys().tolist()} == want and 1 <= len(want) <= 8
+
+
+def test_tsdf_plane_closed_form(o3r):
+    """One frame of a fronto-parallel plane at depth D, identity pose: every updated voxel holds
+    tsdf = min(1, (D - z) * mult / trunc), weight 1; n identical frames leave tsdf unchanged, weight n."""
+    vl, trunc, D = 0.01, 0.04, 1.0
+    vol = o3r.TSDF(vl, trunc, 0)
+    d = plane_depth(D)
+    vol.integrate(d, K, np.eye(4))
+    keys = vol.keys()
+    assert len(keys) > 0
+    checked = 0
+    for key in keys:
+        t, w, _ = vol.unit(key)
+        t, w = t.reshape(16, 16, 16), w.reshape(16, 16, 16)
+        ii = np.arange(16)
+        x = (np.float32(0.005) + np.float32(vl) * ii.astype(np.float32)).astype(np.float64) + key[0] * vl * 16
+        y = (np.float32(0.005) + np.float32(vl) * ii.astype(np.float32)).astype(np.float64) + key[1] * vl * 16
+        z = 0.005 + vl * ii + key[2] * vl * 16
+        X, Y, Z = np.meshgrid(x, y, z, indexing="ij")
+        uf = X * K[0] / Z + K[2] + 0.5
+        vf = Y * K[1] / Z + K[3] + 0.5
+        inside = (Z > 0) & (uf >= 1e-4) & (uf < W - 1e-4) & (vf >= 1e-4) & (vf < H - 1e-4)
+        u, v = np.where(inside, uf, 0).astype(int), np.where(inside, vf, 0).astype(int)
+        mult = np.sqrt(((u - K[2]) / K[0]) ** 2 + ((v - K[3]) / K[1]) ** 2 + 1)
+        sdf = (D - Z) * mult
+        upd = inside & (sdf > -trunc)
+        # keep clear of decision boundaries where f32 vs f64 rounding may differ
+        safe = (np.abs(uf - np.round(uf)) > 1e-3) & (np.abs(vf - np.round(vf)) > 1e-3) & (np.abs(sdf + trunc) > 1e-5)
+        ref = np.minimum(1.0, sdf / trunc)
+        m = upd & safe
+        assert np.all(w[m] == 1.0)
+        np.testing.assert_allclose(t[m], ref[m], atol=2e-5)
+        assert np.all(w[~upd & safe] == 0.0)
+        checked += int(m.sum())
+    assert checked > 1000
+    before = {tuple(k): vol.unit(k) for k in keys}
+    vol.integrate(d, K, np.eye(4))
+    vol.integrate(d, K, np.eye(4))
+    for k, (t0, w0, _) in before.items():
+        t1, w1, _ = vol.unit(k)
+        assert np.array_equal(w1, w0 * 3.0)
+        np.testing.assert_allclose(t1, t0, atol=1e-6)
+
+
+def test_tsdf_color_average(o3r):
+    vol = o3r.TSDF(0.01, 0.04, 1)
+    d = plane_depth(1.0)
+    a = np.full((H, W, 3), 100, np.uint8)
+    b = np.full((H, W, 3), 200, np.uint8)
+    vol.integrate(d, K, np.eye(4), rgb=a)
+    vol.integrate(d, K, np.eye(4), rgb=b)
+    t, w, c = vol.unit(vol.keys()[0])
+    m = w == 2
+    assert m.any() and np.allclose(c[m], 150.0)
+    with pytest.raises(RuntimeError):
+        vol.integrate(d, K, np.eye(4))          # RGB8 volume without colour -> upstream LogError
+
+
+def sphere_volume(o3r, r=0.1, vl=0.01, color_type=0):
+    """Analytic sphere SDF written straight into units (weights 1): |p| - r, truncated at 4 voxels."""
+    vol = o3r.TSDF(vl, 4 * vl, color_type)
+    ul = vl * 16
+    n = int(math.ceil((r + 5 * vl) / ul))
+    for kx in range(-n, n):
+        for ky in range(-n, n):
+            for kz in range(-n, n):
+                i = np.arange(16)
+                x = 0.5 * vl + vl * i + kx * ul
+                y = 0.5 * vl + vl * i + ky * ul
+                z = 0.5 * vl + vl * i + kz * ul
+                X, Y, Z = np.meshgrid(x, y, z, indexing="ij")
+                sdf = np.sqrt(X * X + Y * Y + Z * Z) - r
+                t = np.clip(sdf / (4 * vl), -1, 1).astype(np.float32)
+                w = np.ones_like(t)
+                rgb = np.stack([np.full(t.shape, 255.0 * 0.25), 128 + 100 * X / r, np.full(t.shape, 10.0)], -1).reshape(-1, 3) if color_type else None
+                vol.import_unit((kx, ky, kz), t.reshape(-1), w.reshape(-1), rgb)
+    return vol
+
+
+def test_marching_cubes_sphere(o3r):
+    r, vl = 0.1, 0.01
+    vol = sphere_volume(o3r, r, vl)
+    vtx, _, tri, ids = vol.extract_mesh()
+    V, F = len(vtx), len(tri)
+    assert V > 500 and F > 1000
+    e = np.sort(np.concatenate([tri[:, [0, 1]], tri[:, [1, 2]], tri[:, [2, 0]]]), axis=1)
+    ue, cnt = np.unique(e, axis=0, return_counts=True)
+    assert np.all(cnt == 2)                         # closed 2-manifold: every edge shared by 2 triangles
+    assert V - len(ue) + F == 2                     # Euler characteristic of a sphere
+    assert len(np.unique(ids, axis=0)) == V         # welded: one vertex per global edge id
+    rad = np.linalg.norm(vtx, axis=1)
+    assert np.abs(rad - r).max() < 0.15 * vl        # linear interpolation of a (nearly) linear field
+    a, b, c = vtx[tri[:, 0]], vtx[tri[:, 1]], vtx[tri[:, 2]]
+    n = np.cross(b - a, c - a)
+    area = 0.5 * np.linalg.norm(n, axis=1).sum()
+    assert abs(area - 4 * math.pi * r * r) / (4 * math.pi * r * r) < 0.02
+    # upstream winding (i, i+2, i+1): for an inside-negative SDF the triangle normals point OUTWARD
+    cen = (a + b + c) / 3
+    assert np.all((n * cen).sum(1) > 0)
+    vn = o3r.mesh_vertex_normals(vtx, tri)
+    assert np.all((vn * vtx).sum(1) / rad > 0.95)
+
+
+def test_surface_points_sphere(o3r):
+    r, vl = 0.1, 0.01
+    vol = sphere_volume(o3r, r, vl, color_type=1)
+    xyz, rgb, nrm, ids = vol.extract_points()
+    assert len(xyz) > 500
+    rad = np.linalg.norm(xyz, axis=1)
+    assert np.abs(rad - r).max() < 0.15 * vl
+    assert np.all((nrm * xyz).sum(1) / rad > 0.97)   # gradient of |p| - r is radial
+    np.testing.assert_allclose(rgb[:, 0], 0.25, atol=1e-6)
+    np.testing.assert_allclose(rgb[:, 1], (128 + 100 * xyz[:, 0] / r) / 255.0, atol=2e-3)
+    # every point has a unique (voxel, axis) id and lies on that voxel edge
+    assert len(np.unique(ids, axis=0)) == len(ids)
+    p0 = 0.5 * vl + vl * ids[:, :3]
+    off = xyz - p0
+    ax = ids[:, 3]
+    along = off[np.arange(len(ids)), ax]
+    assert np.all((along >= -1e-12) & (along <= vl + 1e-12))
+    off[np.arange(len(ids)), ax] = 0
+    assert np.abs(off).max() < 1e-12
+
+
+def test_missing_neighbour_units_block_cubes(o3r):
+    """A single allocated unit: cubes that need a corner from a missing +x/+y/+z unit are skipped."""
+    vl = 0.01
+    vol = o3r.TSDF(vl, 0.04, 0)
+    i = np.arange(16)
+    X, Y, Z = np.meshgrid(i, i, i, indexing="ij")
+    t = np.clip((X - 7.5) / 4.0, -1, 1).astype(np.float32)       # plane between x=7 and x=8
+    vol.import_unit((0, 0, 0), t.reshape(-1), np.ones(4096, np.float32))
+    vtx, _, tri, ids = vol.extract_mesh()
+    assert len(tri) == 2 * 15 * 15                                   # cubes at y=15 or z=15 are incomplete
+    assert np.allclose(vtx[:, 0], 0.5 * vl + vl * 7.5)
+    xyz, _, _, pid = vol.extract_points()
+    assert len(xyz) == 16 * 16 and np.all(pid[:, 3] == 0)
+
+
+def test_linear_algebra_helpers(o3r):
+    rng = np.random.default_rng(1)
+    for _ in range(20):
+        M = np.eye(4)
+        q, _ = np.linalg.qr(rng.normal(size=(3, 3)))
+        M[:3, :3] = q
+        M[:3, 3] = rng.normal(size=3)
+        np.testing.assert_allclose(o3r.m4_inverse(M), np.linalg.inv(M), atol=1e-13)
+        J = rng.normal(size=(50, 6))
+        A, b = J.T @ J, rng.normal(size=6)
+        np.testing.assert_allclose(o3r.solve6(A, b), np.linalg.solve(A, b), rtol=1e-9, atol=1e-12)
+    x = np.array([0.1, -0.2, 0.3, 1.0, 2.0, 3.0])
+    T = o3r.vec6_to_m4(x)
+    ca, sa, cb, sb, cg, sg = math.cos(.1), math.sin(.1), math.cos(-.2), math.sin(-.2), math.cos(.3), math.sin(.3)
+    Rx = np.array([[1, 0, 0], [0, ca, -sa], [0, sa, ca]])
+    Ry = np.array([[cb, 0, sb], [0, 1, 0], [-sb, 0, cb]])
+    Rz = np.array([[cg, -sg, 0], [sg, cg, 0], [0, 0, 1]])
+    np.testing.assert_allclose(T[:3, :3], Rz @ Ry @ Rx, atol=1e-15)
+    assert T[:3, 3].tolist() == [1.0, 2.0, 3.0]
+    assert np.allclose(o3r.solve6(np.zeros((6, 6)), np.zeros(6)), 0)     # zero system -> zero update (Eigen LDLT behaviour)
+
+
+def test_filters_and_downsample(o3r):
+    rng = np.random.default_rng(2)
+    img = rng.random((9, 11)).astype(np.float32)
+    g = o3r.image_filter(img, 0)
+    pad = np.pad(img.astype(np.float64), 1, mode="edge")
+    k = np.array([0.25, 0.5, 0.25])
+    h = sum(k[i] * pad[:, i:i + 11] for i in range(3))
+    ref = sum(k[j] * h[j:j + 9, :] for j in range(3))
+    np.testing.assert_allclose(g, ref, atol=1e-6)
+    ramp = np.tile(np.arange(11, dtype=np.float32), (9, 1))
+    dx, dy = o3r.image_filter(ramp, 1), o3r.image_filter(ramp, 2)
+    assert np.all(dx[:, 1:-1] == 8.0) and np.all(dy == 0.0)          # [-1,0,1] x [1,2,1] on a unit ramp
+    ds = o3r.image_downsample(img)
+    assert ds.shape == (4, 5)
+    np.testing.assert_allclose(ds[1, 2], img[2:4, 4:6].mean(), rtol=1e-6)
+    nan_img = img.copy()
+    nan_img[4, 4] = np.nan
+    assert np.isnan(o3r.image_filter(nan_img, 0)[3:6, 3:6]).all()       # NaN spreads to the 3x3 neighbourhood
+
+
+def render_pair(small_kinect, motion):
+    """Two aligned intensity+depth pairs: target = camera 0, source = camera moved by `motion` (so that
+    the source->target transform equals `motion`)."""
+    import torch
+    from azurekinect3dreconstruction_b200 import synthetic as syn
+    pose_t = syn.orbit_trajectory(5)[2]
+    pose_s = pose_t @ motion
+    out = []
+    for pose in (pose_s, pose_t):
+        dep, rgb = small_kinect.render_depth_aligned_rgb(pose)
+        d = dep.view(torch.int16).numpy().view(np.uint16)
+        out.append((rgb.numpy(), d))
+    return out
+
+
+@pytest.mark.parametrize("jac", [0, 1])
+def test_odometry_recovers_known_motion(o3r, jac):
+    from azurekinect3dreconstruction_b200 import synthetic as syn
+    kin = syn.SyntheticKinect(depth_intrinsics=dict(width=160, height=144, fx=126.05, fy=126.025, cx=79.95, cy=71.975), seed=0)
+    motion = syn.make_pose(syn.rot_y(math.radians(0.5)) @ syn.rot_x(math.radians(-0.3)), (0.01, -0.004, 0.006))
+    (rs, ds), (rt, dt) = render_pair(kin, motion)
+    Kd = (126.05, 126.025, 79.95, 71.975)
+    gs, gt = o3r.rgb_to_intensity(rs), o3r.rgb_to_intensity(rt)
+    fs, ft = o3r.depth_to_float(ds, 1000.0, 3.0), o3r.depth_to_float(dt, 1000.0, 3.0)
+    ok, T, info, dbg = o3r.odometry(gs, fs, gt, ft, Kd, jac_kind=jac)
+    assert ok and dbg[0] > 1000
+    dR = T[:3, :3] @ motion[:3, :3].T
+    ang = math.degrees(math.acos(min(1.0, (np.trace(dR) - 1) / 2)))
+    # 1 mm depth quantisation + 160x144 pixels: expect ~1 mm / 0.1 degree accuracy
+    tol_t, tol_a = (0.006, 0.4) if jac == 0 else (0.003, 0.15)
+    assert np.linalg.norm(T[:3, 3] - motion[:3, 3]) < tol_t and ang < tol_a
+    assert np.allclose(info, info.T) and np.all(np.linalg.eigvalsh(info) > 0)
+    assert info[3, 3] == info[4, 4] == info[5, 5] and info[3, 3] > 1000      # = number of correspondences
+
+
+def test_odometry_identical_pair_is_identity(o3r):
+    """bundlefusion_reconstruction.py:224-225 passes the same rgbd as source and target."""
+    from azurekinect3dreconstruction_b200 import synthetic as syn
+    kin = syn.SyntheticKinect(depth_intrinsics=dict(width=160, height=144, fx=126.05, fy=126.025, cx=79.95, cy=71.975), seed=0)
+    (rs, ds), _ = render_pair(kin, np.eye(4))
+    g, f = o3r.rgb_to_intensity(rs), o3r.depth_to_float(ds, 1000.0, 3.0)
+    ok, T, info, _ = o3r.odometry(g, f, g, f, (126.05, 126.025, 79.95, 71.975))
+    assert ok
+    np.testing.assert_allclose(T, np.eye(4), atol=1e-9)
+
+
+def test_hybrid_jacobian_matches_finite_differences(o3r):
+    """Gauss-Newton step direction check: one iteration from identity reduces the true pose error."""
+    from azurekinect3dreconstruction_b200 import synthetic as syn
+    kin = syn.SyntheticKinect(depth_intrinsics=dict(width=160, height=144, fx=126.05, fy=126.025, cx=79.95, cy=71.975), seed=0)
+    motion = syn.make_pose(syn.rot_y(math.radians(0.3)), (0.006, 0.0, 0.0))
+    (rs, ds), (rt, dt) = render_pair(kin, motion)
+    Kd = (126.05, 126.025, 79.95, 71.975)
+    a = (o3r.rgb_to_intensity(rs), o3r.depth_to_float(ds), o3r.rgb_to_intensity(rt), o3r.depth_to_float(dt))
+    errs = []
+    for n in (1, 3, 8):
+        ok, T, _, _ = o3r.odometry(*a, Kd, jac_kind=1, iters=(n,))
+        errs.append(np.linalg.norm(T[:3, 3] - motion[:3, 3]))
+    assert errs[0] < 0.006 and errs[2] <= errs[0]
+
+
+def test_icp_recovers_inverse_motion(o3r):
+    rng = np.random.default_rng(3)
+    # target: points on a bumpy surface with exact normals
+    u, v = rng.random(4000) * 2 - 1, rng.random(4000) * 2 - 1
+    z = 0.2 * np.sin(2 * u) * np.cos(1.5 * v) + 0.1 * u * v
+    tgt = np.stack([u, v, z], 1)
+    nz = np.stack([-(0.4 * np.cos(2 * u) * np.cos(1.5 * v) + 0.1 * v), -(-0.3 * np.sin(2 * u) * np.sin(1.5 * v) + 0.1 * u), np.ones_like(u)], 1)
+    nrm = nz / np.linalg.norm(nz, axis=1, keepdims=True)
+    from azurekinect3dreconstruction_b200 import synthetic as syn
+    M = syn.make_pose(syn.rot_z(math.radians(1.0)) @ syn.rot_x(math.radians(0.7)), (0.01, -0.008, 0.012))
+    src = o3r.transform_points(tgt[::2], M)
+    T, fit, rmse, corr, it = o3r.icp_point_to_plane(src, tgt, nrm, 0.05, max_iter=60)
+    assert fit > 0.99 and rmse < 2e-3 and 1 <= it <= 60
+    np.testing.assert_allclose(T @ M, np.eye(4), atol=2e-3)
+    assert (corr >= 0).mean() > 0.99
+    # exact-NN check against brute force at the final pose
+    fin = o3r.transform_points(src, T)
+    d2 = ((fin[:200, None, :] - tgt[None, :, :]) ** 2).sum(-1)
+    assert np.array_equal(corr[:200], d2.argmin(1).astype(np.int32))
+    with pytest.raises(RuntimeError):
+        o3r.icp_point_to_plane(src, tgt, nrm, 0.0)
+    with pytest.raises(RuntimeError):
+        o3r.icp_point_to_plane(src, tgt, None, 0.05)
+    # nothing within reach: identity update, fitness 0
+    T0, fit0, rmse0, _, _ = o3r.icp_point_to_plane(src + 100.0, tgt, nrm, 0.05, max_iter=5)
+    assert fit0 == 0.0 and rmse0 == 0.0 and np.array_equal(T0, np.eye(4))
