@@ -347,7 +347,7 @@ def test_extract_triangle_mesh_parity(o3r, frames, small_kinect, color_type):
 
 
 def test_extract_analytic_sphere_and_empty(o3r):
-    from tests.test_oracle_known_answers import sphere_volume
+    from _helpers import sphere_volume
     r, vl = 0.1, 0.01
     ref = sphere_volume(o3r, r, vl, color_type=1)
     vol = o3d.pipelines.integration.ScalableTSDFVolume(vl, 4 * vl, o3d.pipelines.integration.TSDFVolumeColorType.RGB8, capacity_units=256)
