@@ -13,6 +13,7 @@ pytestmark = pytest.mark.gpu
 
 import azurekinect3dreconstruction_b200 as o3d
 from azurekinect3dreconstruction_b200 import synthetic as syn
+from _helpers import image_normals
 
 I4 = np.eye(4)
 
@@ -423,8 +424,10 @@ def test_icp_parity(o3r, frames, small_kinect):
     Kt = K_of(intr)
     src, _, _ = o3r.unproject(o3r.depth_to_float(ds), Kt, stride=2)
     tgt, _, _ = o3r.unproject(o3r.depth_to_float(dt), Kt, stride=2)
-    # target normals: cross product of image-space neighbours is out of scope; use a smooth analytic proxy
-    nrm = -tgt / np.linalg.norm(tgt, axis=1, keepdims=True)
+    # target normals from the organised depth grid (test-side helper; normal estimation is row f1, out of scope).
+    # NB radial "towards the camera" normals would leave rotation about the origin unobservable.
+    nrm = image_normals(o3r.depth_to_float(dt), Kt, stride=2)
+    assert nrm.shape == tgt.shape
     init = np.linalg.inv(pt) @ ps
     init[:3, 3] += [0.004, -0.003, 0.002]
     s, t = o3d.geometry.PointCloud(src), o3d.geometry.PointCloud(tgt)
