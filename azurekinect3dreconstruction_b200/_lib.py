@@ -46,7 +46,10 @@ SIGNATURES = {
     "b2r_tsdf_integrate_host": (_i, [_vp, _i, _vp, _i, _f, _f, _vp, _i, _i, _i, _i, _d, _d, _d, _d, _pd, _vp]),
     "b2r_tsdf_stats": (_i, [_vp, _pi64, _vp]),
     "b2r_tsdf_profile": (_i, [_vp, _i]),
-    "b2r_tsdf_profile_read": (_i, [_vp, _pd]),
+    "b2r_tsdf_profile_read": (_i, [_vp, _pd, _vp]),
+    "b2r_tsdf_flush": (_i, [_vp, _vp]),
+    "b2r_tsdf_set_batch": (_i, [_vp, _i, _vp]),
+    "b2r_selftest_div": (_i, [_i64, C.c_uint64, _pi64, _vp]),
     "b2r_tsdf_num_units": (_i64, [_vp, _vp]),
     "b2r_tsdf_export_keys": (_i, [_vp, _vp, _i64, _vp]),
     "b2r_tsdf_export_units": (_i, [_vp, _i64, _i64, _vp, _vp, _vp, _vp]),

@@ -62,21 +62,59 @@ __host__ __device__ __forceinline__ int b2r_owner(uint64_t key, int world) {
     return world <= 1 ? 0 : (int)((b2r_mix64(key) >> 33) % (uint64_t)world);
 }
 
+// One 32-byte slot = one L2 sector: a probe reads key, unit id and the three rotating per-batch frame
+// masks with a single access.  mask[q] bit f = frame f of the batch using buffer q touches this unit.
+struct __align__(32) B2RSlot {
+    uint64_t key;        // B2R_KEY_EMPTY when free
+    int32_t val;         // unit index (-1 while unassigned / on pool overflow)
+    uint32_t mask[3];
+    uint32_t pad[2];
+};
+
 struct B2RHash {
-    uint64_t* keys;   // nslots, B2R_KEY_EMPTY when free
-    int32_t* vals;    // nslots -> unit index (or -1 while unassigned / on overflow)
+    B2RSlot* slots;   // nslots
     uint32_t mask;    // nslots - 1
 };
 
 __device__ __forceinline__ int b2r_hash_find(const B2RHash& h, uint64_t key) {
     uint32_t s = (uint32_t)b2r_mix64(key) & h.mask;
     for (uint32_t probe = 0; probe <= h.mask; probe++) {
-        uint64_t k = h.keys[s];
-        if (k == key) return h.vals[s];
-        if (k == B2R_KEY_EMPTY) return -1;
+        const ulonglong2 kv = *reinterpret_cast<const ulonglong2*>(&h.slots[s]);   // key + val in one 16-byte load
+        if (kv.x == key) return (int)(uint32_t)kv.y;
+        if (kv.x == B2R_KEY_EMPTY) return -1;
         s = (s + 1) & h.mask;
     }
     return -1;
+}
+__host__ __device__ __forceinline__ void b2r_unpack_key(uint64_t key, int& x, int& y, int& z) {
+    x = (int)((key >> 42) & 0x1FFFFFu) - B2R_KEY_BIAS;
+    y = (int)((key >> 21) & 0x1FFFFFu) - B2R_KEY_BIAS;
+    z = (int)(key & 0x1FFFFFu) - B2R_KEY_BIAS;
+}
+
+// ---- IEEE-exact f32 division with a shared reciprocal ------------------------------------------------
+// Several quotients by the same divisor (u and v projections by z; tsdf/r/g/b running averages by w+1)
+// share ONE correctly rounded reciprocal, then Markstein's correction gives RN(a/b) in three instructions:
+//   y  = RN(1/b)      : MUFU.RCP (< 1 ulp) + one FMA Newton step -- correctly rounded for every significand
+//                       except all-ones (Markstein 1990), which b2r_div_domain() excludes;
+//   q0 = RN(a*y); r = fma(-b, q0, a) (exact); q = fma(r, y, q0) = RN(a/b)   when nothing under/overflows.
+// b2r_div_domain(b) bounds b to [2^-60, 2^60); the callers' numerators are either 0, or large enough for r to
+// be exact, or so small that the quotient cannot influence the result (see tsdf.cu).  Everything outside the
+// domain takes div.rn.  b2r_selftest_div() (tsdf.cu) brute-forces both claims on the GPU in the tests.
+__device__ __forceinline__ float b2r_rcp_markstein(float b) {
+    float y0;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y0) : "f"(b));
+    const float e = __fmaf_rn(-b, y0, 1.0f);
+    return __fmaf_rn(y0, e, y0);
+}
+__device__ __forceinline__ bool b2r_div_domain(float b) {   // 2^-60 <= b < 2^60 and significand not all ones
+    const uint32_t u = __float_as_uint(b);
+    return ((u >> 23) - 67u) < 120u && (u & 0x7FFFFFu) != 0x7FFFFFu;
+}
+__device__ __forceinline__ float b2r_div_fast(float a, float b, float y) {
+    const float q0 = __fmul_rn(a, y);
+    const float r = __fmaf_rn(-b, q0, a);
+    return __fmaf_rn(r, y, q0);
 }
 
 #define B2R_UNIT_RES 16

@@ -5,23 +5,32 @@
 // (/root/reference/CodeThatWorks/GoodColorReconstruction.py:111-115,270;
 //  CodeThatWorks/bundlefusionattemps/bundlefusion_reconstruction.py:108-112,276,315).
 // Semantics restated in SURVEY.md Appendix A.4; the f32 operation order of the per-voxel update is
-// reproduced exactly (explicit __f*_rn intrinsics, no FMA contraction) so TSDF/weight match the CPU
-// oracle bit for bit and the (int)u_f / (int)v_f pixel choices can never diverge.
+// reproduced exactly (explicit round-to-nearest intrinsics, no FMA contraction, IEEE-exact division) so
+// TSDF/weight/colour match the CPU oracle bit for bit and the (int)u_f / (int)v_f pixel choices can
+// never diverge.
 //
-// Per frame two kernels run on the caller's stream:
-//   K1 tsdf_pack_alloc_kernel : one thread per pixel. Fuses RGBDImage conversion (u16 -> f32 metres,
-//        trunc), the depth-to-camera-distance multiplier and the colour fetch into ONE 16-byte texel
-//        {d, mult, rgb8, 0}; every depth_sampling_stride-th pixel also unprojects in f64 and inserts
-//        the integer AABB of touched unit keys into the hash (allocation = pointer bump into a
-//        zeroed pool), appending first touches to the frame's touched list.
-//   K2 tsdf_fuse_kernel : persistent grid over (touched unit x 4 x-slabs); a thread owns 4
-//        consecutive z voxels (one 128-bit load/store per plane), decides from the texel gather
-//        alone whether any of them changes and only then touches the voxel record, so DRAM
-//        traffic follows the updated voxels (sector granular), not the block.
+// Two kernels, both on the caller's stream:
+//   K1 tsdf_pack_alloc_kernel (at every integrate call; one launch can take a batch of frames):
+//        pack role  - one thread per pixel fuses RGBDImage conversion (u16 -> f32 metres, trunc), the
+//                     depth-to-camera-distance multiplier and the colour fetch into ONE 16-byte texel
+//                     {d, mult, rgb8, 0} of the frame's texel image;
+//        alloc role - one thread per depth_sampling_stride-th pixel unprojects in f64; a warp merges its
+//                     lanes' integer AABBs of unit keys and probes the union's cells in PARALLEL (one
+//                     32-byte slot read per probe); first touches of a (unit, batch) are appended to
+//                     the batch's touched list and the frame's bit is OR-ed into the slot's batch mask.
+//   K2 tsdf_fuse_kernel (when max_batch frames are pending, or when anything reads the volume):
+//        persistent CTAs over (touched unit x 4 x-slabs).  A slab (planes x 4 KiB) is staged into shared
+//        memory by TMA bulk copies (cp.async.bulk + mbarrier) through a 3-deep ring, so the next two
+//        slabs are in flight while the current one is fused.  A thread owns 4 consecutive z voxels, keeps
+//        them in registers while it applies EVERY pending frame that touches the unit (in frame order,
+//        so the result equals frame-by-frame integration bit for bit), and writes the record back once,
+//        only if it changed.  HBM traffic per frame therefore falls with the batch size; the voxel
+//        arithmetic (not DRAM) becomes the limiter, which is why the divisions share reciprocals.
 #include "tsdf_internal.h"
 #include "host_math.h"
 #include <new>
 #include <string.h>
+#include <stdlib.h>
 
 // ------------------------------------------------------------------------------------------------
 // error string
@@ -34,44 +43,61 @@ void b2r_set_error(const char* fmt, ...) {
     va_end(ap);
 }
 B2R_API const char* b2r_last_error(void) { return g_err; }
-B2R_API int b2r_version(void) { return 100; }
+B2R_API int b2r_version(void) { return 200; }
 
 // ------------------------------------------------------------------------------------------------
-// kernel parameters
+// K1: pack + allocate
 // ------------------------------------------------------------------------------------------------
-struct PackParams {
-    int W, H;
+struct PackFrame {
     const void* depth;        // u16 or f32, W*H
-    int depth_is_u16;
-    float depth_scale, depth_trunc;
     const uint8_t* color;     // u8, channels 3|4 (may be null)
-    int color_channels, color_bgr;
     const float* gray;        // f32 intensity (Gray32), may be null
     float4* texel;
+    double pose[12];          // extrinsic^-1, rows 0..2
+    uint32_t bit;             // 1 << (index of the frame in the pending batch)
+    uint32_t pad;
+};
+
+struct PackParams {
+    int W, H;
+    int depth_is_u16;
+    float depth_scale, depth_trunc;
+    int color_channels, color_bgr;
     float fcx, fcy, ifx, ify;      // (float)cx, (float)cy, 1.0f/(float)fx, 1.0f/(float)fy
     double fx, fy, cx, cy;         // f64 intrinsics for the allocation samples
-    double pose[12];               // extrinsic^-1, rows 0..2
     double trunc, unit_length;
-    int stride;
-    int frame_id, rank, world;
+    int stride, Ws, n_samples;
+    int n_alloc_blocks;
+    int vec_ok;                    // images are 16-byte aligned and W*H % 4 == 0: vector loads in the pack role
+    int rank, world;
+    int q;                         // batch buffer (mask word) in use
     B2RHash hash;
-    int32_t* slot_stamp;
     int32_t* unit_keys;
     int32_t* touched;
     int32_t* counters;
-    int touched_word;
     int cap_units;
+    PackFrame fr[B2R_MAX_BATCH];
 };
 
-__device__ __forceinline__ void alloc_key(const PackParams& P, int kx, int ky, int kz) {
-    if (!b2r_key_in_range(kx, ky, kz)) { atomicOr(&P.counters[B2R_C_ERR], 2); return; }
-    const uint64_t key = b2r_pack_key(kx, ky, kz);
-    if (P.world > 1 && b2r_owner(key, P.world) != P.rank) return;
+__device__ __forceinline__ float load_depth_m(const PackParams& P, const void* depth, int idx) {
+    if (P.depth_is_u16) {
+        float d = xfdiv((float)__ldg((const uint16_t*)depth + idx), P.depth_scale);
+        if (d >= P.depth_trunc) d = 0.0f;
+        return d;
+    }
+    return __ldg((const float*)depth + idx);
+}
+
+// slow path of the allocator: insert-or-find `key` (linear probing), mark it touched by frame `bit`
+__device__ __noinline__ void alloc_key(const PackParams& P, uint64_t key, uint32_t bit) {
+    int kx, ky, kz;
+    b2r_unpack_key(key, kx, ky, kz);
     uint32_t s = (uint32_t)b2r_mix64(key) & P.hash.mask;
     for (uint32_t probe = 0; probe <= P.hash.mask; probe++) {
-        unsigned long long k = P.hash.keys[s];
+        B2RSlot* slot = &P.hash.slots[s];
+        unsigned long long k = __ldcg(reinterpret_cast<const unsigned long long*>(&slot->key));   // L2: coherent
         if (k == B2R_KEY_EMPTY) {
-            k = atomicCAS((unsigned long long*)&P.hash.keys[s], (unsigned long long)B2R_KEY_EMPTY, (unsigned long long)key);
+            k = atomicCAS((unsigned long long*)&slot->key, (unsigned long long)B2R_KEY_EMPTY, (unsigned long long)key);
             if (k == B2R_KEY_EMPTY) {
                 // we own the slot: bump-allocate a zeroed unit
                 int id = atomicAdd(&P.counters[B2R_C_NUM_UNITS], 1);
@@ -81,17 +107,15 @@ __device__ __forceinline__ void alloc_key(const PackParams& P, int kx, int ky, i
                 } else {
                     P.unit_keys[3 * id] = kx; P.unit_keys[3 * id + 1] = ky; P.unit_keys[3 * id + 2] = kz;
                 }
-                P.hash.vals[s] = id;   // consumed by the NEXT kernel (K2), no intra-kernel reader
+                slot->val = id;   // consumed by the NEXT kernel (K2), no intra-kernel reader
                 k = key;
             }
         }
         if (k == key) {
-            // first touch of this slot in this frame -> append to the touched list
-            if (P.slot_stamp[s] != P.frame_id) {
-                if (atomicExch(&P.slot_stamp[s], P.frame_id) != P.frame_id) {
-                    int pos = atomicAdd(&P.counters[P.touched_word], 1);
-                    if (pos < P.cap_units) P.touched[pos] = (int)s;
-                }
+            const uint32_t old = atomicOr(&slot->mask[P.q], bit);
+            if (old == 0) {   // first touch of this unit in this batch -> append to the touched list
+                const int pos = atomicAdd(&P.counters[B2R_C_TOUCHED0 + P.q], 1);
+                if (pos < P.cap_units) P.touched[pos] = (int)s;
             }
             return;
         }
@@ -100,158 +124,412 @@ __device__ __forceinline__ void alloc_key(const PackParams& P, int kx, int ky, i
     atomicOr(&P.counters[B2R_C_ERR], 4);
 }
 
-__global__ void __launch_bounds__(256) tsdf_pack_alloc_kernel(const PackParams P) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= P.W * P.H) return;
-    const int i = idx / P.W, j = idx - i * P.W;
-    // ---- a1: depth conversion (Image::ConvertDepthToFloatImage) fused
-    float d;
-    if (P.depth_is_u16) {
-        d = xfdiv((float)((const uint16_t*)P.depth)[idx], P.depth_scale);
-        if (d >= P.depth_trunc) d = 0.0f;
-    } else {
-        d = ((const float*)P.depth)[idx];
-    }
-    // ---- CreateDepthToCameraDistanceMultiplierFloatImage
+#define PACK_PX 4   // pixels per thread in the pack role
+
+__device__ __forceinline__ float pack_mult(const PackParams& P, int i, int j) {
     const float xx = xfmul(xfsub((float)j, P.fcx), P.ifx);
     const float yy = xfmul(xfsub((float)i, P.fcy), P.ify);
-    const float mult = __fsqrt_rn(xfadd(xfadd(xfmul(xx, xx), xfmul(yy, yy)), 1.0f));
-    float cbits = 0.0f;
-    if (P.color) {
-        const uint8_t* c = P.color + (size_t)idx * P.color_channels;
-        uint32_t r = c[0], g = c[1], b = c[2];
-        if (P.color_bgr) { uint32_t t = r; r = b; b = t; }
-        cbits = __uint_as_float(r | (g << 8) | (b << 16));
-    } else if (P.gray) {
-        cbits = P.gray[idx];
-    }
-    P.texel[idx] = make_float4(d, mult, cbits, 0.0f);
+    return __fsqrt_rn(xfadd(xfadd(xfmul(xx, xx), xfmul(yy, yy)), 1.0f));
+}
+__device__ __forceinline__ float depth_from_u16(const PackParams& P, uint32_t v) {
+    float d = xfdiv((float)v, P.depth_scale);
+    return d >= P.depth_trunc ? 0.0f : d;
+}
 
-    // ---- a8: block allocation from the stride-sampled pixels (f64 chain)
-    if ((i % P.stride) == 0 && (j % P.stride) == 0 && d > 0.0f) {
-        const double z = (double)d;
-        const double x = xddiv(xdmul(xdsub((double)j, P.cx), z), P.fx);
-        const double y = xddiv(xdmul(xdsub((double)i, P.cy), z), P.fy);
-        int lo[3], hi[3];
+__global__ void __launch_bounds__(256, 4) tsdf_pack_alloc_kernel(const __grid_constant__ PackParams P) {
+    const PackFrame& F = P.fr[blockIdx.y];
+    if ((int)blockIdx.x >= P.n_alloc_blocks) {
+        // ---- pack role: a1 depth conversion + CreateDepthToCameraDistanceMultiplierFloatImage + colour,
+        //      PACK_PX consecutive pixels per thread, every load issued before the first use
+        const int npx = P.W * P.H;
+        const int idx0 = ((blockIdx.x - P.n_alloc_blocks) * blockDim.x + threadIdx.x) * PACK_PX;
+        if (idx0 >= npx) return;
+        float d[PACK_PX], cb[PACK_PX];
+        if (P.vec_ok && idx0 + PACK_PX <= npx) {
+            if (P.depth_is_u16) {
+                const uint2 raw = __ldg(reinterpret_cast<const uint2*>((const uint16_t*)F.depth + idx0));
+                d[0] = depth_from_u16(P, raw.x & 0xFFFFu); d[1] = depth_from_u16(P, raw.x >> 16);
+                d[2] = depth_from_u16(P, raw.y & 0xFFFFu); d[3] = depth_from_u16(P, raw.y >> 16);
+            } else {
+                const float4 raw = __ldg(reinterpret_cast<const float4*>((const float*)F.depth + idx0));
+                d[0] = raw.x; d[1] = raw.y; d[2] = raw.z; d[3] = raw.w;
+            }
+            if (F.color) {
+                uint32_t px[PACK_PX];   // 0x00BBGGRR in memory order: byte 0 = channel 0
+                if (P.color_channels == 4) {
+                    const uint4 t = __ldg(reinterpret_cast<const uint4*>(F.color) + (idx0 >> 2));
+                    px[0] = t.x; px[1] = t.y; px[2] = t.z; px[3] = t.w;
+                } else {
+                    const uint32_t* c = reinterpret_cast<const uint32_t*>(F.color) + (size_t)(idx0 >> 2) * 3;
+                    const uint32_t w0 = __ldg(c), w1 = __ldg(c + 1), w2 = __ldg(c + 2);
+                    px[0] = w0; px[1] = (w0 >> 24) | (w1 << 8); px[2] = (w1 >> 16) | (w2 << 16); px[3] = w2 >> 8;
+                }
 #pragma unroll
-        for (int k = 0; k < 3; k++) {
-            const double p = xdadd(xdadd(xdadd(xdmul(P.pose[4 * k], x), xdmul(P.pose[4 * k + 1], y)), xdmul(P.pose[4 * k + 2], z)), P.pose[4 * k + 3]);
-            lo[k] = (int)floor(xddiv(xdsub(p, P.trunc), P.unit_length));
-            hi[k] = (int)floor(xddiv(xdadd(p, P.trunc), P.unit_length));
+                for (int k = 0; k < PACK_PX; k++) {
+                    uint32_t v = px[k] & 0xFFFFFFu;
+                    if (P.color_bgr) v = __byte_perm(v, 0, 0x4012);   // swap byte 0 and byte 2, clear byte 3
+                    cb[k] = __uint_as_float(v);
+                }
+            } else if (F.gray) {
+                const float4 g = __ldg(reinterpret_cast<const float4*>(F.gray + idx0));
+                cb[0] = g.x; cb[1] = g.y; cb[2] = g.z; cb[3] = g.w;
+            } else {
+                cb[0] = cb[1] = cb[2] = cb[3] = 0.0f;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < PACK_PX; k++) {
+                const int idx = min(idx0 + k, npx - 1);
+                d[k] = load_depth_m(P, F.depth, idx);
+                cb[k] = 0.0f;
+                if (F.color) {
+                    const uint8_t* c = F.color + (size_t)idx * P.color_channels;
+                    uint32_t r = __ldg(c), g = __ldg(c + 1), b = __ldg(c + 2);
+                    if (P.color_bgr) { const uint32_t t = r; r = b; b = t; }
+                    cb[k] = __uint_as_float(r | (g << 8) | (b << 16));
+                } else if (F.gray) {
+                    cb[k] = __ldg(F.gray + idx);
+                }
+            }
         }
-        for (int a = lo[0]; a <= hi[0]; a++)
-            for (int b = lo[1]; b <= hi[1]; b++)
-                for (int c = lo[2]; c <= hi[2]; c++) alloc_key(P, a, b, c);
+        int i = idx0 / P.W, j = idx0 - i * P.W;
+#pragma unroll
+        for (int k = 0; k < PACK_PX; k++) {
+            if (idx0 + k < npx) F.texel[idx0 + k] = make_float4(d[k], pack_mult(P, i, j), cb[k], 0.0f);
+            if (++j == P.W) { j = 0; i++; }
+        }
+        return;
+    }
+    // ---- alloc role (a8): block allocation from the stride-sampled pixels (f64 chain)
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned lane = threadIdx.x & 31u;
+    int lo[3] = {0, 0, 0};
+    int ny = 1, nz = 1, n = 0;   // n = cells in this sample's box (0: no valid depth)
+    if (s < P.n_samples) {
+        const int si = s / P.Ws, sj = s - si * P.Ws;
+        const int i = si * P.stride, j = sj * P.stride;
+        const float d = load_depth_m(P, F.depth, i * P.W + j);
+        if (d > 0.0f) {
+            const double z = (double)d;
+            const double x = xddiv(xdmul(xdsub((double)j, P.cx), z), P.fx);
+            const double y = xddiv(xdmul(xdsub((double)i, P.cy), z), P.fy);
+            long long ext[3];
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                const double p = xdadd(xdadd(xdadd(xdmul(F.pose[4 * k], x), xdmul(F.pose[4 * k + 1], y)), xdmul(F.pose[4 * k + 2], z)), F.pose[4 * k + 3]);
+                const double fl = floor(xddiv(xdsub(p, P.trunc), P.unit_length)), fh = floor(xddiv(xdadd(p, P.trunc), P.unit_length));
+                const bool ok = fl >= -(double)B2R_KEY_BIAS && fh < (double)B2R_KEY_BIAS;   // also false for NaN
+                lo[k] = ok ? (int)fl : 0;
+                ext[k] = ok ? (long long)((int)fh - (int)fl + 1) : -1;
+            }
+            if (ext[0] < 0 || ext[1] < 0 || ext[2] < 0 || ext[0] * ext[1] * ext[2] > 4096) {
+                atomicOr(&P.counters[B2R_C_ERR], 2);   // key out of range / degenerate box: report, don't loop
+            } else {
+                ny = (int)ext[1]; nz = (int)ext[2]; n = (int)(ext[0] * ext[1] * ext[2]);
+            }
+        }
+    }
+    // Rounds of 4 cells per lane, warp-uniform.  Per round: (A) all slot probes issued together; the common
+    // case -- unit exists and this frame's bit is already set -- ends there; (B) lanes holding the same key
+    // elect one leader (match.any) whose atomicOr marks the unit; (C) first touches append to the list;
+    // absent keys / collisions take the probing slow path.
+    for (int base = 0; __any_sync(0xffffffffu, base < n); base += 4) {
+        uint64_t want[4];
+        uint32_t slot_i[4];
+        bool need[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int c = base + k;
+            want[k] = B2R_KEY_EMPTY; need[k] = false; slot_i[k] = 0;
+            if (c < n) {
+                const int a = lo[0] + c / (ny * nz), b = lo[1] + (c / nz) % ny, cc = lo[2] + c % nz;
+                const uint64_t key = b2r_pack_key(a, b, cc);
+                const uint64_t hsh = b2r_mix64(key);
+                if (P.world <= 1 || (int)((hsh >> 33) % (uint64_t)P.world) == P.rank) { want[k] = key; slot_i[k] = (uint32_t)hsh & P.hash.mask; }
+            }
+        }
+        uint64_t got[4];
+        uint32_t mk[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            got[k] = 0; mk[k] = 0;
+            if (want[k] != B2R_KEY_EMPTY) {
+                const B2RSlot* slot = &P.hash.slots[slot_i[k]];
+                got[k] = __ldcg(reinterpret_cast<const unsigned long long*>(&slot->key));
+                mk[k] = __ldcg(&slot->mask[P.q]);
+            }
+        }
+        uint32_t old[4];
+        bool slow[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const bool live = want[k] != B2R_KEY_EMPTY && !(got[k] == want[k] && (mk[k] & F.bit));
+            const unsigned peers = __match_any_sync(0xffffffffu, live ? want[k] : (B2R_KEY_EMPTY - 1 - lane));
+            const bool leader = live && (lane == (unsigned)(__ffs(peers) - 1));
+            slow[k] = leader && got[k] != want[k];
+            need[k] = leader && got[k] == want[k];
+            old[k] = 1;
+            if (need[k]) old[k] = atomicOr(&P.hash.slots[slot_i[k]].mask[P.q], F.bit);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (need[k] && old[k] == 0) {
+                const int pos = atomicAdd(&P.counters[B2R_C_TOUCHED0 + P.q], 1);
+                if (pos < P.cap_units) P.touched[pos] = (int)slot_i[k];
+            }
+            if (slow[k]) alloc_key(P, want[k], F.bit);
+        }
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// K2: fuse
+// ------------------------------------------------------------------------------------------------
+#define FUSE_THREADS 256
+#define FUSE_MAX_ITEMS 64          // work items resolved per CTA per chunk
+#define FUSE_SLAB 1024             // floats per plane per slab (4 x-layers x 16 x 16)
+
 struct FuseParams {
-    int W, H;
-    const float4* texel;
-    float fx, fy, cx, cy;
-    float E[12];             // (float)extrinsic rows 0..2
-    float Es02, Es12, Es22;  // E(:,2) * voxel_length (f32)
-    float vl, hv, trunc, inv_trunc, safe_w, safe_h;
+    int nframes;
+    int q;                   // batch buffer being fused; (q+2)%3 = previous batch (its masks get cleared),
+                             // (q+1)%3 = next batch (its counter gets zeroed)
+    int reverse;             // sweep direction (alternates per batch: the tail of the last sweep is still in L2)
+    float vl, hv, trunc, inv_trunc;
     double unit_length;
     const int32_t* touched;
-    const int32_t* hash_vals;
-    const int32_t* unit_keys;
+    const int32_t* touched_prev;
+    B2RSlot* slots;
     float* pool;
     int64_t unit_stride;     // floats per unit
     int32_t* counters;
-    int touched_word;
     int cap_units;
+    B2RFrame fr[B2R_MAX_BATCH];
 };
 
-template <int COLOR>
-__global__ void __launch_bounds__(256) tsdf_fuse_kernel(const FuseParams P) {
-    const int T = min(P.counters[P.touched_word], P.cap_units);
-    const int nwork = T * 4;
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// TMA bulk copy global -> shared, completion counted on an mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+template <int COLOR, int FUSE_STAGES>
+__global__ void __launch_bounds__(FUSE_THREADS, 4) tsdf_fuse_kernel(const __grid_constant__ FuseParams P) {
+    constexpr int PLANES = COLOR ? 5 : 2;
+    extern __shared__ __align__(128) unsigned char fuse_smem[];
+    float* stage = reinterpret_cast<float*>(fuse_smem);                        // [FUSE_STAGES][PLANES][FUSE_SLAB]
+    __shared__ __align__(8) uint64_t full_bar[FUSE_STAGES];
+    __shared__ int s_unit[FUSE_MAX_ITEMS];
+    __shared__ uint32_t s_mask[FUSE_MAX_ITEMS];
+    __shared__ int s_key[FUSE_MAX_ITEMS][3];
+
     const int tid = threadIdx.x;
-    const int zq = tid & 3, y = (tid >> 2) & 15, xl = tid >> 6;
-    unsigned int upd = 0;
-    for (int w = blockIdx.x; w < nwork; w += gridDim.x) {
-        const int slot = P.touched[w >> 2];
-        const int unit = P.hash_vals[slot];
-        if (unit < 0) continue;
-        const int x = ((w & 3) << 2) + xl;
-        const int kx = P.unit_keys[3 * unit], ky = P.unit_keys[3 * unit + 1], kz = P.unit_keys[3 * unit + 2];
-        // voxel-centre column base: float(hv + vl*x + origin.x) with the f32->f64 promotion of upstream
-        const float px = (float)xdadd((double)xfadd(P.hv, xfmul(P.vl, (float)x)), xdmul((double)kx, P.unit_length));
-        const float py = (float)xdadd((double)xfadd(P.hv, xfmul(P.vl, (float)y)), xdmul((double)ky, P.unit_length));
-        const float pz = (float)xdadd((double)P.hv, xdmul((double)kz, P.unit_length));
-        float pcx = xfadd(xfadd(xfadd(xfmul(P.E[0], px), xfmul(P.E[1], py)), xfmul(P.E[2], pz)), P.E[3]);
-        float pcy = xfadd(xfadd(xfadd(xfmul(P.E[4], px), xfmul(P.E[5], py)), xfmul(P.E[6], pz)), P.E[7]);
-        float pcz = xfadd(xfadd(xfadd(xfmul(P.E[8], px), xfmul(P.E[9], py)), xfmul(P.E[10], pz)), P.E[11]);
-        // sequential z-march to this thread's first voxel (same f32 accumulation as the reference loop)
-        for (int s = 0; s < 4 * zq; s++) {
-            pcx = xfadd(pcx, P.Es02); pcy = xfadd(pcy, P.Es12); pcz = xfadd(pcz, P.Es22);
+    const int T = min(P.counters[B2R_C_TOUCHED0 + P.q], P.cap_units);
+    const int nwork = T * 4;
+
+    // ---- housekeeping for the rotating batch buffers
+    {
+        const int qp = (P.q + 2) % 3;
+        const int Tp = min(P.counters[B2R_C_TOUCHED0 + qp], P.cap_units);
+        for (int i = blockIdx.x * FUSE_THREADS + tid; i < Tp; i += gridDim.x * FUSE_THREADS) P.slots[P.touched_prev[i]].mask[qp] = 0u;
+        if (blockIdx.x == 0 && tid == 0) {
+            P.counters[B2R_C_TOUCHED0 + (P.q + 1) % 3] = 0;
+            P.counters[B2R_C_LAST_TOUCHED] = T;
         }
-        float tv[4];
-        float cv[4];
-        unsigned act = 0;
+    }
+    if (tid == 0) {
+        for (int s = 0; s < FUSE_STAGES; s++) mbar_init(&full_bar[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    // thread -> 4 consecutive z voxels.  The z-quad is WARP-uniform (so the sequential z-march to the quad's first
+    // voxel is divergence-free); a warp's lanes are 32 (x, y) columns of the slab.
+    const int zq = (tid >> 5) & 3;
+    const int col = ((tid >> 7) << 5) | (tid & 31);
+    const int y = col & 15, xl = col >> 4;
+    const int f4 = xl * 64 + y * 4 + zq;        // this thread's float4 inside a 1024-float slab plane
+    unsigned int upd = 0, pairs = 0;
+    uint32_t it_seq = 0;   // items issued through the ring so far by this CTA (stage = seq % STAGES)
+
+    const int my_items = (nwork > (int)blockIdx.x) ? (nwork - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+    for (int chunk0 = 0; chunk0 < my_items; chunk0 += FUSE_MAX_ITEMS) {
+        const int n_it = min(FUSE_MAX_ITEMS, my_items - chunk0);
+        __syncthreads();   // previous chunk fully consumed (info arrays + ring are free); barriers initialised
+        // ---- resolve this chunk's work items in parallel: touched -> slot {key, unit, mask}
+        if (tid < n_it) {
+            int w = (int)blockIdx.x + (chunk0 + tid) * (int)gridDim.x;
+            if (P.reverse) w = nwork - 1 - w;
+            const B2RSlot* slot = &P.slots[P.touched[w >> 2]];
+            const uint4 lo = __ldcg(reinterpret_cast<const uint4*>(slot));
+            const uint4 hi = __ldcg(reinterpret_cast<const uint4*>(slot) + 1);
+            const uint64_t key = ((uint64_t)lo.y << 32) | lo.x;
+            int kx, ky, kz;
+            b2r_unpack_key(key, kx, ky, kz);
+            s_unit[tid] = (int)lo.z;
+            s_mask[tid] = ((int)lo.z < 0) ? 0u : (P.q == 0 ? lo.w : (P.q == 1 ? hi.x : hi.y));
+            s_key[tid][0] = kx; s_key[tid][1] = ky; s_key[tid][2] = kz;
+            // slab index rides in the top bits of the unit word
+            s_unit[tid] = ((int)lo.z < 0) ? -1 : (((int)lo.z << 2) | (w & 3));
+        }
+        __syncthreads();
+        // ---- prologue: fill the ring
+        if (tid == 0) {
+            for (int i = 0; i < min(FUSE_STAGES, n_it); i++) {
+                const uint32_t st = (it_seq + i) % FUSE_STAGES;
+                const int us = s_unit[i];
+                if (us >= 0 && s_mask[i]) {
+                    const float* src = P.pool + (int64_t)(us >> 2) * P.unit_stride + (us & 3) * FUSE_SLAB;
+                    mbar_expect_tx(&full_bar[st], PLANES * FUSE_SLAB * 4);
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            tv[k] = 0.f; cv[k] = 0.f;
-            if (pcz > 0.0f) {
-                const float u_f = xfadd(xfadd(xfdiv(xfmul(pcx, P.fx), pcz), P.cx), 0.5f);
-                const float v_f = xfadd(xfadd(xfdiv(xfmul(pcy, P.fy), pcz), P.cy), 0.5f);
-                if (u_f >= 0.0001f && u_f < P.safe_w && v_f >= 0.0001f && v_f < P.safe_h) {
-                    const int u = (int)u_f, v = (int)v_f;
-                    const float4 tx = __ldg(&P.texel[v * P.W + u]);
-                    if (tx.x > 0.0f) {
-                        const float sdf = xfmul(xfsub(tx.x, pcz), tx.y);
-                        if (sdf > -P.trunc) {
-                            tv[k] = fminf(1.0f, xfmul(sdf, P.inv_trunc));
-                            cv[k] = tx.z;
-                            act |= 1u << k;
+                    for (int pl = 0; pl < PLANES; pl++) tma_load_1d(stage + (st * PLANES + pl) * FUSE_SLAB, src + pl * B2R_UNIT_VOX, FUSE_SLAB * 4, &full_bar[st]);
+                } else {
+                    mbar_expect_tx(&full_bar[st], 0);   // skipped item: keep the stage's phase in step
+                }
+            }
+        }
+        for (int it = 0; it < n_it; it++, it_seq++) {
+            const uint32_t st = it_seq % FUSE_STAGES;
+            const int us = s_unit[it];
+            const uint32_t fmask = s_mask[it];
+            if (us >= 0 && fmask) {
+                const int unit = us >> 2, x = ((us & 3) << 2) + xl;
+                const int kx = s_key[it][0], ky = s_key[it][1], kz = s_key[it][2];
+                // voxel-centre column base: float(hv + vl*x + origin.x) with the f32->f64 promotion of upstream
+                const float px = (float)xdadd((double)xfadd(P.hv, xfmul(P.vl, (float)x)), xdmul((double)kx, P.unit_length));
+                const float py = (float)xdadd((double)xfadd(P.hv, xfmul(P.vl, (float)y)), xdmul((double)ky, P.unit_length));
+                const float pz = (float)xdadd((double)P.hv, xdmul((double)kz, P.unit_length));
+                mbar_wait(&full_bar[st], (it_seq / FUSE_STAGES) & 1u);
+                const float* sb = stage + st * PLANES * FUSE_SLAB + f4 * 4;
+                float4 ts = *reinterpret_cast<const float4*>(sb);
+                float4 ws = *reinterpret_cast<const float4*>(sb + FUSE_SLAB);
+                float4 rs, gs, bs;
+                if (COLOR) {
+                    rs = *reinterpret_cast<const float4*>(sb + 2 * FUSE_SLAB);
+                    gs = *reinterpret_cast<const float4*>(sb + 3 * FUSE_SLAB);
+                    bs = *reinterpret_cast<const float4*>(sb + 4 * FUSE_SLAB);
+                }
+                float* tp = reinterpret_cast<float*>(&ts);
+                float* wp = reinterpret_cast<float*>(&ws);
+                float* rp = reinterpret_cast<float*>(&rs);
+                float* gp = reinterpret_cast<float*>(&gs);
+                float* bp = reinterpret_cast<float*>(&bs);
+                const unsigned upd0 = upd;
+                pairs += (tid == 0 && (us & 3) == 0) ? __popc(fmask) : 0;
+                for (uint32_t fm = fmask; fm; fm &= fm - 1) {
+                    const B2RFrame& F = P.fr[__ffs(fm) - 1];
+                    float pcx = xfadd(xfadd(xfadd(xfmul(F.E[0], px), xfmul(F.E[1], py)), xfmul(F.E[2], pz)), F.E[3]);
+                    float pcy = xfadd(xfadd(xfadd(xfmul(F.E[4], px), xfmul(F.E[5], py)), xfmul(F.E[6], pz)), F.E[7]);
+                    float pcz = xfadd(xfadd(xfadd(xfmul(F.E[8], px), xfmul(F.E[9], py)), xfmul(F.E[10], pz)), F.E[11]);
+                    // sequential z-march to this thread's first voxel (same f32 accumulation as the reference
+                    // loop): 4*zq steps, written as three predicated groups of four so there is no loop
+#pragma unroll
+                    for (int g = 0; g < 3; g++) {
+                        if (zq > g) {
+#pragma unroll
+                            for (int s = 0; s < 4; s++) { pcx = xfadd(pcx, F.Es02); pcy = xfadd(pcy, F.Es12); pcz = xfadd(pcz, F.Es22); }
+                        }
+                    }
+                    // pass 1: project the 4 voxels, issue the 4 texel gathers together
+                    float zc[4];
+                    float4 tx[4];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        zc[k] = pcz;
+                        tx[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (pcz > 0.0f) {
+                            // u_f = pc.x*fx/pc.z + cx + 0.5f, v_f likewise: both quotients share RN(1/pc.z).
+                            // Outside b2r_div_domain (pc.z < 2^-60, ...) take div.rn.  Inside it the Markstein
+                            // quotient is RN(a/b) unless |a| is so small that r underflows, and then |q| < 2^-40
+                            // cannot change RN(q + cx) -- the pixel picked is the same either way.
+                            const float ax = xfmul(pcx, F.fx), ay = xfmul(pcy, F.fy);
+                            float qx, qy;
+                            if (__builtin_expect(b2r_div_domain(pcz), 1)) {
+                                const float inv = b2r_rcp_markstein(pcz);
+                                qx = b2r_div_fast(ax, pcz, inv); qy = b2r_div_fast(ay, pcz, inv);
+                            } else {
+                                qx = __fdiv_rn(ax, pcz); qy = __fdiv_rn(ay, pcz);
+                            }
+                            const float u_f = xfadd(xfadd(qx, F.cx), 0.5f);
+                            const float v_f = xfadd(xfadd(qy, F.cy), 0.5f);
+                            const bool in = (u_f >= 0.0001f) & (u_f < F.safe_w) & (v_f >= 0.0001f) & (v_f < F.safe_h);
+                            if (in) tx[k] = __ldg(&F.texel[(int)v_f * F.W + (int)u_f]);
+                        }
+                        pcx = xfadd(pcx, F.Es02); pcy = xfadd(pcy, F.Es12); pcz = xfadd(pcz, F.Es22);
+                    }
+                    // pass 2: running averages in registers.  w1 = weight + 1 is an integer in [1, 2^24]: always inside
+                    // the division domain except 2^24 - 1 (all-ones significand); numerators are 0 or >= 2^-60.
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        if (tx[k].x > 0.0f) {
+                            const float sdf = xfmul(xfsub(tx[k].x, zc[k]), tx[k].y);
+                            if (sdf > -P.trunc) {
+                                const float tv = fminf(1.0f, xfmul(sdf, P.inv_trunc));
+                                const float wgt = wp[k];
+                                const float w1 = xfadd(wgt, 1.0f);
+                                float c0 = 0.f, c1 = 0.f, c2 = 0.f;
+                                if (COLOR == 1) {
+                                    const uint32_t c = __float_as_uint(tx[k].z);
+                                    c0 = (float)(c & 255u); c1 = (float)((c >> 8) & 255u); c2 = (float)((c >> 16) & 255u);
+                                } else if (COLOR == 2) {
+                                    c0 = c1 = c2 = tx[k].z;
+                                }
+                                const float at = xfadd(xfmul(tp[k], wgt), tv);
+                                float ar = 0.f, ag = 0.f, ab = 0.f;
+                                if (COLOR) { ar = xfadd(xfmul(rp[k], wgt), c0); ag = xfadd(xfmul(gp[k], wgt), c1); ab = xfadd(xfmul(bp[k], wgt), c2); }
+                                if (__builtin_expect(b2r_div_domain(w1), 1)) {
+                                    const float inv = b2r_rcp_markstein(w1);
+                                    tp[k] = b2r_div_fast(at, w1, inv);
+                                    if (COLOR) { rp[k] = b2r_div_fast(ar, w1, inv); gp[k] = b2r_div_fast(ag, w1, inv); bp[k] = b2r_div_fast(ab, w1, inv); }
+                                } else {
+                                    tp[k] = __fdiv_rn(at, w1);
+                                    if (COLOR) { rp[k] = __fdiv_rn(ar, w1); gp[k] = __fdiv_rn(ag, w1); bp[k] = __fdiv_rn(ab, w1); }
+                                }
+                                wp[k] = w1;
+                                upd++;
+                            }
                         }
                     }
                 }
-            }
-            pcx = xfadd(pcx, P.Es02); pcy = xfadd(pcy, P.Es12); pcz = xfadd(pcz, P.Es22);
-        }
-        if (act) {
-            float* base = P.pool + (int64_t)unit * P.unit_stride + (x * 256 + y * 16 + zq * 4);
-            float4 ts = *reinterpret_cast<float4*>(base);
-            float4 ws = *reinterpret_cast<float4*>(base + B2R_UNIT_VOX);
-            float4 rs, gs, bs;
-            if (COLOR) {
-                rs = *reinterpret_cast<float4*>(base + 2 * B2R_UNIT_VOX);
-                gs = *reinterpret_cast<float4*>(base + 3 * B2R_UNIT_VOX);
-                bs = *reinterpret_cast<float4*>(base + 4 * B2R_UNIT_VOX);
-            }
-            float* tp = reinterpret_cast<float*>(&ts);
-            float* wp = reinterpret_cast<float*>(&ws);
-            float* rp = reinterpret_cast<float*>(&rs);
-            float* gp = reinterpret_cast<float*>(&gs);
-            float* bp = reinterpret_cast<float*>(&bs);
-#pragma unroll
-            for (int k = 0; k < 4; k++) {
-                if (act & (1u << k)) {
-                    const float wgt = wp[k];
-                    const float w1 = xfadd(wgt, 1.0f);
-                    tp[k] = xfdiv(xfadd(xfmul(tp[k], wgt), tv[k]), w1);
-                    if (COLOR == 1) {
-                        const uint32_t c = __float_as_uint(cv[k]);
-                        rp[k] = xfdiv(xfadd(xfmul(rp[k], wgt), (float)(c & 255u)), w1);
-                        gp[k] = xfdiv(xfadd(xfmul(gp[k], wgt), (float)((c >> 8) & 255u)), w1);
-                        bp[k] = xfdiv(xfadd(xfmul(bp[k], wgt), (float)((c >> 16) & 255u)), w1);
-                    } else if (COLOR == 2) {
-                        rp[k] = xfdiv(xfadd(xfmul(rp[k], wgt), cv[k]), w1);
-                        gp[k] = xfdiv(xfadd(xfmul(gp[k], wgt), cv[k]), w1);
-                        bp[k] = xfdiv(xfadd(xfmul(bp[k], wgt), cv[k]), w1);
+                if (upd != upd0) {
+                    float* base = P.pool + (int64_t)unit * P.unit_stride + (us & 3) * FUSE_SLAB + f4 * 4;
+                    *reinterpret_cast<float4*>(base) = ts;
+                    *reinterpret_cast<float4*>(base + B2R_UNIT_VOX) = ws;
+                    if (COLOR) {
+                        *reinterpret_cast<float4*>(base + 2 * B2R_UNIT_VOX) = rs;
+                        *reinterpret_cast<float4*>(base + 3 * B2R_UNIT_VOX) = gs;
+                        *reinterpret_cast<float4*>(base + 4 * B2R_UNIT_VOX) = bs;
                     }
-                    wp[k] = w1;
-                    upd++;
                 }
             }
-            *reinterpret_cast<float4*>(base) = ts;
-            *reinterpret_cast<float4*>(base + B2R_UNIT_VOX) = ws;
-            if (COLOR) {
-                *reinterpret_cast<float4*>(base + 2 * B2R_UNIT_VOX) = rs;
-                *reinterpret_cast<float4*>(base + 3 * B2R_UNIT_VOX) = gs;
-                *reinterpret_cast<float4*>(base + 4 * B2R_UNIT_VOX) = bs;
+            __syncthreads();   // every thread has read its float4s of this stage -> the stage is free
+            if (tid == 0 && it + FUSE_STAGES < n_it) {
+                const int nx = it + FUSE_STAGES;
+                const int us2 = s_unit[nx];
+                if (us2 >= 0 && s_mask[nx]) {
+                    const float* src = P.pool + (int64_t)(us2 >> 2) * P.unit_stride + (us2 & 3) * FUSE_SLAB;
+                    mbar_expect_tx(&full_bar[st], PLANES * FUSE_SLAB * 4);
+#pragma unroll
+                    for (int pl = 0; pl < PLANES; pl++) tma_load_1d(stage + (st * PLANES + pl) * FUSE_SLAB, src + pl * B2R_UNIT_VOX, FUSE_SLAB * 4, &full_bar[st]);
+                } else {
+                    mbar_expect_tx(&full_bar[st], 0);
+                }
             }
         }
     }
@@ -259,8 +537,7 @@ __global__ void __launch_bounds__(256) tsdf_fuse_kernel(const FuseParams P) {
     for (int o = 16; o > 0; o >>= 1) upd += __shfl_down_sync(0xffffffffu, upd, o);
     if ((tid & 31) == 0) {
         if (upd) atomicAdd(reinterpret_cast<unsigned long long*>(&P.counters[B2R_C_UPDATED]), (unsigned long long)upd);
-        if (blockIdx.x == 0 && tid == 0)
-            atomicAdd(reinterpret_cast<unsigned long long*>(&P.counters[B2R_C_TOUCHED_TOTAL]), (unsigned long long)T);
+        if (tid == 0 && pairs) atomicAdd(reinterpret_cast<unsigned long long*>(&P.counters[B2R_C_TOUCHED_TOTAL]), (unsigned long long)pairs);
     }
 }
 
@@ -273,27 +550,42 @@ static uint32_t next_pow2(uint64_t v) {
     return (uint32_t)p;
 }
 
+static int env_int(const char* name, int dflt, int lo, int hi) {
+    const char* s = getenv(name);
+    if (!s || !*s) return dflt;
+    const int v = atoi(s);
+    return v < lo ? lo : (v > hi ? hi : v);
+}
+
 static void tsdf_free(b2r_tsdf* h) {
     if (!h) return;
-    cudaFree(h->hash.keys); cudaFree(h->hash.vals); cudaFree(h->slot_stamp); cudaFree(h->unit_keys);
-    cudaFree(h->pool); cudaFree(h->touched[0]); cudaFree(h->touched[1]); cudaFree(h->counters);
-    cudaFree(h->texel[0]); cudaFree(h->texel[1]); cudaFree(h->scratch);
+    cudaFree(h->hash.slots); cudaFree(h->unit_keys);
+    cudaFree(h->pool); cudaFree(h->counters); cudaFree(h->scratch);
+    for (int i = 0; i < 3; i++) cudaFree(h->touched[i]);
+    for (int i = 0; i < B2R_MAX_BATCH; i++) cudaFree(h->texel[i]);
     for (int i = 0; i < B2R_HOST_RING; i++) {
         if (h->ev_copied[i]) cudaEventDestroy(h->ev_copied[i]);
         if (h->ev_consumed[i]) cudaEventDestroy(h->ev_consumed[i]);
         cudaFree(h->stage_depth[i]); cudaFree(h->stage_color[i]);
     }
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
-    for (int i = 0; i < h->prof_cap; i++) cudaEventDestroy(h->prof_ev[i]);
+    for (int i = 0; i < 2 * h->prof_cap; i++) cudaEventDestroy(h->prof_ev[i]);
     delete[] h->prof_ev;
+    delete[] h->prof_kind;
     delete h;
+}
+
+typedef void (*fuse_fn_t)(const FuseParams);
+static fuse_fn_t fuse_fn(int color_type, int stages) {
+    if (stages >= 3) return color_type == 0 ? tsdf_fuse_kernel<0, 3> : (color_type == 1 ? tsdf_fuse_kernel<1, 3> : tsdf_fuse_kernel<2, 3>);
+    return color_type == 0 ? tsdf_fuse_kernel<0, 2> : (color_type == 1 ? tsdf_fuse_kernel<1, 2> : tsdf_fuse_kernel<2, 2>);
 }
 
 B2R_API b2r_tsdf* b2r_tsdf_create(double voxel_length, double sdf_trunc, int color_type, int unit_resolution,
                                   int depth_sampling_stride, int64_t capacity_units, int rank, int world) {
     if (unit_resolution != B2R_UNIT_RES) { b2r_set_error("volume_unit_resolution must be 16 (got %d)", unit_resolution); return nullptr; }
     if (!(voxel_length > 0) || !(sdf_trunc > 0) || depth_sampling_stride < 1 || capacity_units < 1 || color_type < 0 ||
-        color_type > 2 || world < 1 || rank < 0 || rank >= world) {
+        color_type > 2 || world < 1 || rank < 0 || rank >= world || capacity_units > (1 << 28)) {
         b2r_set_error("b2r_tsdf_create: bad argument");
         return nullptr;
     }
@@ -305,41 +597,37 @@ B2R_API b2r_tsdf* b2r_tsdf_create(double voxel_length, double sdf_trunc, int col
     h->color_type = color_type; h->res = unit_resolution; h->stride = depth_sampling_stride;
     h->planes = color_type == 0 ? 2 : 5;
     h->cap_units = capacity_units; h->rank = rank; h->world = world;
-    cudaGetDevice(&h->device);
+    h->max_batch = env_int("B2R_TSDF_BATCH", 8, 1, B2R_MAX_BATCH);
+    cudaError_t e = cudaGetDevice(&h->device);
     h->nslots = next_pow2((uint64_t)capacity_units * 2);
     h->hash.mask = h->nslots - 1;
-    h->frame_id = 0;
     const size_t pool_bytes = (size_t)capacity_units * h->planes * B2R_UNIT_VOX * sizeof(float);
-    cudaError_t e = cudaSuccess;
     auto A = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes); };
-    A((void**)&h->hash.keys, (size_t)h->nslots * 8);
-    A((void**)&h->hash.vals, (size_t)h->nslots * 4);
-    A((void**)&h->slot_stamp, (size_t)h->nslots * 4);
+    A((void**)&h->hash.slots, (size_t)h->nslots * sizeof(B2RSlot));
     A((void**)&h->unit_keys, (size_t)capacity_units * 12);
-    A((void**)&h->touched[0], (size_t)capacity_units * 4);
-    A((void**)&h->touched[1], (size_t)capacity_units * 4);
+    for (int i = 0; i < 3; i++) A((void**)&h->touched[i], (size_t)capacity_units * 4);
     A((void**)&h->counters, B2R_C_WORDS * 4);
     A((void**)&h->pool, pool_bytes);
-    if (e == cudaSuccess) e = cudaMemset(h->hash.keys, 0xFF, (size_t)h->nslots * 8);
-    if (e == cudaSuccess) e = cudaMemset(h->hash.vals, 0xFF, (size_t)h->nslots * 4);
-    if (e == cudaSuccess) e = cudaMemset(h->slot_stamp, 0, (size_t)h->nslots * 4);
-    if (e == cudaSuccess) e = cudaMemset(h->counters, 0, B2R_C_WORDS * 4);
     if (e == cudaSuccess) e = cudaMemset(h->pool, 0, pool_bytes);
+    if (e == cudaSuccess) e = cudaMemset(h->counters, 0, B2R_C_WORDS * 4);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking);
     for (int i = 0; i < B2R_HOST_RING && e == cudaSuccess; i++) {
         e = cudaEventCreateWithFlags(&h->ev_copied[i], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_consumed[i], cudaEventDisableTiming);
     }
     if (e == cudaSuccess) {
-        int nsm = 148, per_sm = 8;
+        const int stages = env_int("B2R_FUSE_STAGES", 2, 2, 3);
+        h->fuse_smem = stages * h->planes * FUSE_SLAB * 4;
+        fuse_fn_t fn = fuse_fn(color_type, stages);
+        e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fuse_smem);
+        int nsm = 148, per_sm = 1;
         cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, h->device);
-        if (color_type == 0) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tsdf_fuse_kernel<0>, 256, 0);
-        else if (color_type == 1) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tsdf_fuse_kernel<1>, 256, 0);
-        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tsdf_fuse_kernel<2>, 256, 0);
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, FUSE_THREADS, h->fuse_smem);
         if (per_sm < 1) per_sm = 1;
         h->fuse_grid = nsm * per_sm;
-        e = cudaGetLastError();
     }
+    if (e == cudaSuccess && b2r_tsdf_reset(h, 0) != B2R_OK) e = cudaErrorUnknown;
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e != cudaSuccess) {
         b2r_set_error("b2r_tsdf_create: %s (pool %.1f MiB)", cudaGetErrorString(e), pool_bytes / 1048576.0);
         tsdf_free(h);
@@ -355,20 +643,28 @@ B2R_API void b2r_tsdf_destroy(b2r_tsdf* h) {
     tsdf_free(h);
 }
 
-// volume.reset()  (bundlefusion_reconstruction.py:309, capture_frames.py:94)
+__global__ void tsdf_clear_slots_kernel(B2RSlot* slots, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    B2RSlot s;
+    s.key = B2R_KEY_EMPTY; s.val = -1; s.mask[0] = s.mask[1] = s.mask[2] = 0u; s.pad[0] = s.pad[1] = 0u;
+    slots[i] = s;
+}
+
+// volume.reset()  (bundlefusion_reconstruction.py:309, capture_frames.py:94).  Pending frames are dropped:
+// integrate-then-reset leaves an empty volume either way.
 B2R_API int b2r_tsdf_reset(b2r_tsdf* h, cudaStream_t stream) {
     if (!h) return B2R_ERR_BAD_ARG;
     B2RDeviceGuard g(h->device);
     int32_t n = 0;
     B2R_CUDA(cudaMemcpyAsync(&n, h->counters + B2R_C_NUM_UNITS, 4, cudaMemcpyDeviceToHost, stream));
     B2R_CUDA(cudaStreamSynchronize(stream));
-    if (n > h->cap_units) n = (int32_t)h->cap_units;
-    B2R_CUDA(cudaMemsetAsync(h->pool, 0, (size_t)n * h->planes * B2R_UNIT_VOX * sizeof(float), stream));
-    B2R_CUDA(cudaMemsetAsync(h->hash.keys, 0xFF, (size_t)h->nslots * 8, stream));
-    B2R_CUDA(cudaMemsetAsync(h->hash.vals, 0xFF, (size_t)h->nslots * 4, stream));
-    B2R_CUDA(cudaMemsetAsync(h->slot_stamp, 0, (size_t)h->nslots * 4, stream));
+    if (n > h->cap_units || n < 0) n = (int32_t)h->cap_units;
+    if (n) B2R_CUDA(cudaMemsetAsync(h->pool, 0, (size_t)n * h->planes * B2R_UNIT_VOX * sizeof(float), stream));
+    tsdf_clear_slots_kernel<<<(h->nslots + 255) / 256, 256, 0, stream>>>(h->hash.slots, h->nslots);
+    B2R_CHECK_LAUNCH();
     B2R_CUDA(cudaMemsetAsync(h->counters, 0, B2R_C_WORDS * 4, stream));
-    h->frame_id = 0;
+    h->q = 0; h->pending = 0; h->batches = 0;
     return B2R_OK;
 }
 
@@ -381,70 +677,120 @@ int b2r_tsdf_ensure_scratch(b2r_tsdf* h, size_t bytes) {
     return B2R_OK;
 }
 
+// ---- profiling hooks: an event pair around every kernel launch while enabled -----------------------
+static bool prof_begin(b2r_tsdf* h, int kind, cudaStream_t stream) {
+    if (!h->profile || h->prof_n >= h->prof_cap) return false;
+    h->prof_kind[h->prof_n] = kind;
+    cudaEventRecord(h->prof_ev[2 * h->prof_n], stream);
+    return true;
+}
+static void prof_end(b2r_tsdf* h, bool on, cudaStream_t stream) {
+    if (!on) return;
+    cudaEventRecord(h->prof_ev[2 * h->prof_n + 1], stream);
+    h->prof_n++;
+}
+
 // ------------------------------------------------------------------------------------------------
-// integrate (device inputs)
+// K2 launch: fuse the pending batch
 // ------------------------------------------------------------------------------------------------
-static int tsdf_integrate_impl(b2r_tsdf* h, const void* depth, int depth_is_u16, float depth_scale, float depth_trunc,
+int b2r_tsdf_flush_pending(b2r_tsdf* h, cudaStream_t stream) {
+    if (!h->pending) return B2R_OK;
+    FuseParams F;
+    memset(&F, 0, sizeof(F));
+    F.nframes = h->pending; F.q = h->q; F.reverse = (int)(h->batches & 1);
+    F.vl = (float)h->voxel_length; F.hv = F.vl * 0.5f;
+    F.trunc = (float)h->sdf_trunc; F.inv_trunc = 1.0f / F.trunc;
+    F.unit_length = h->unit_length;
+    F.touched = h->touched[h->q]; F.touched_prev = h->touched[(h->q + 2) % 3];
+    F.slots = h->hash.slots; F.pool = h->pool; F.unit_stride = (int64_t)h->planes * B2R_UNIT_VOX;
+    F.counters = h->counters; F.cap_units = (int)h->cap_units;
+    for (int i = 0; i < h->pending; i++) F.fr[i] = h->frames[i];
+    const int stages = h->fuse_smem / (h->planes * FUSE_SLAB * 4);
+    const bool prof = prof_begin(h, 2, stream);
+    fuse_fn(h->color_type, stages)<<<h->fuse_grid, FUSE_THREADS, h->fuse_smem, stream>>>(F);
+    B2R_CHECK_LAUNCH();
+    prof_end(h, prof, stream);
+    h->q = (h->q + 1) % 3;
+    h->pending = 0;
+    h->batches++;
+    return B2R_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// integrate (device inputs): K1 now, K2 when the batch is full or the volume is read
+// ------------------------------------------------------------------------------------------------
+static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth_is_u16, float depth_scale, float depth_trunc,
                                const uint8_t* color, int color_channels, int color_bgr, const float* gray, int W,
-                               int H, double fx, double fy, double cx, double cy, const double* extrinsic,
+                               int H, double fx, double fy, double cx, double cy, const double* extrinsics,
                                cudaStream_t stream) {
-    if (!h || !depth || !extrinsic || W < 1 || H < 1) { b2r_set_error("b2r_tsdf_integrate: bad argument"); return B2R_ERR_BAD_ARG; }
+    if (!h || !depth || !extrinsics || W < 1 || H < 1 || nf < 1) { b2r_set_error("b2r_tsdf_integrate: bad argument"); return B2R_ERR_BAD_ARG; }
     // upstream: "[ScalableTSDFVolume::Integrate] Unsupported image format."
     if (h->color_type == 1 && (!color || (color_channels != 3 && color_channels != 4))) { b2r_set_error("[ScalableTSDFVolume::Integrate] Unsupported image format."); return B2R_ERR_FORMAT; }
     if (h->color_type == 2 && !gray) { b2r_set_error("[ScalableTSDFVolume::Integrate] Unsupported image format."); return B2R_ERR_FORMAT; }
-    double pose[16];
-    if (!b2r::m4_inverse(extrinsic, pose)) { b2r_set_error("b2r_tsdf_integrate: singular extrinsic"); return B2R_ERR_SINGULAR; }
     const size_t npx = (size_t)W * H;
     if (h->texel_px < npx) {
+        int rc = b2r_tsdf_flush_pending(h, stream);
+        if (rc != B2R_OK) return rc;
         B2R_CUDA(cudaStreamSynchronize(stream));
-        for (int i = 0; i < 2; i++) { if (h->texel[i]) cudaFree(h->texel[i]); h->texel[i] = nullptr; }
+        for (int i = 0; i < B2R_MAX_BATCH; i++) { if (h->texel[i]) cudaFree(h->texel[i]); h->texel[i] = nullptr; }
         h->texel_px = 0;
-        for (int i = 0; i < 2; i++) B2R_CUDA(cudaMalloc((void**)&h->texel[i], npx * sizeof(float4)));
+        for (int i = 0; i < h->max_batch; i++) B2R_CUDA(cudaMalloc((void**)&h->texel[i], npx * sizeof(float4)));
         h->texel_px = npx;
     }
-    h->frame_id++;
-    const int buf = h->frame_id & 1;
-    const int tw = buf ? B2R_C_TOUCHED1 : B2R_C_TOUCHED0;
-    B2R_CUDA(cudaMemsetAsync(h->counters + tw, 0, 4, stream));
-
-    PackParams P;
-    memset(&P, 0, sizeof(P));
-    P.W = W; P.H = H; P.depth = depth; P.depth_is_u16 = depth_is_u16;
-    P.depth_scale = depth_scale; P.depth_trunc = depth_trunc;
-    P.color = h->color_type == 1 ? color : nullptr; P.color_channels = color_channels; P.color_bgr = color_bgr;
-    P.gray = h->color_type == 2 ? gray : nullptr;
-    P.texel = h->texel[buf];
-    P.fcx = (float)cx; P.fcy = (float)cy; P.ifx = 1.0f / (float)fx; P.ify = 1.0f / (float)fy;
-    P.fx = fx; P.fy = fy; P.cx = cx; P.cy = cy;
-    for (int i = 0; i < 12; i++) P.pose[i] = pose[i];
-    P.trunc = h->sdf_trunc; P.unit_length = h->unit_length; P.stride = h->stride;
-    P.frame_id = h->frame_id; P.rank = h->rank; P.world = h->world;
-    P.hash = h->hash; P.slot_stamp = h->slot_stamp; P.unit_keys = h->unit_keys; P.touched = h->touched[buf];
-    P.counters = h->counters; P.touched_word = tw; P.cap_units = (int)h->cap_units;
-    const bool prof = h->profile && h->prof_n + 3 <= h->prof_cap;
-    if (prof) cudaEventRecord(h->prof_ev[h->prof_n], stream);
-    tsdf_pack_alloc_kernel<<<(unsigned)((npx + 255) / 256), 256, 0, stream>>>(P);
-    B2R_CHECK_LAUNCH();
-    if (prof) cudaEventRecord(h->prof_ev[h->prof_n + 1], stream);
-
-    FuseParams F;
-    memset(&F, 0, sizeof(F));
-    F.W = W; F.H = H; F.texel = h->texel[buf];
-    F.fx = (float)fx; F.fy = (float)fy; F.cx = (float)cx; F.cy = (float)cy;
-    for (int i = 0; i < 12; i++) F.E[i] = (float)extrinsic[i];
-    F.vl = (float)h->voxel_length; F.hv = F.vl * 0.5f;
-    F.trunc = (float)h->sdf_trunc; F.inv_trunc = 1.0f / F.trunc;
-    F.Es02 = F.E[2] * F.vl; F.Es12 = F.E[6] * F.vl; F.Es22 = F.E[10] * F.vl;
-    F.safe_w = (float)W - 0.0001f; F.safe_h = (float)H - 0.0001f;
-    F.unit_length = h->unit_length;
-    F.touched = h->touched[buf]; F.hash_vals = h->hash.vals; F.unit_keys = h->unit_keys;
-    F.pool = h->pool; F.unit_stride = (int64_t)h->planes * B2R_UNIT_VOX;
-    F.counters = h->counters; F.touched_word = tw; F.cap_units = (int)h->cap_units;
-    if (h->color_type == 0) tsdf_fuse_kernel<0><<<h->fuse_grid, 256, 0, stream>>>(F);
-    else if (h->color_type == 1) tsdf_fuse_kernel<1><<<h->fuse_grid, 256, 0, stream>>>(F);
-    else tsdf_fuse_kernel<2><<<h->fuse_grid, 256, 0, stream>>>(F);
-    B2R_CHECK_LAUNCH();
-    if (prof) { cudaEventRecord(h->prof_ev[h->prof_n + 2], stream); h->prof_n += 3; }
+    const size_t dstep = npx * (depth_is_u16 ? 2 : 4), cstep = npx * (size_t)color_channels;
+    int done = 0;
+    while (done < nf) {
+        if (h->pending == h->max_batch) {
+            int rc = b2r_tsdf_flush_pending(h, stream);
+            if (rc != B2R_OK) return rc;
+        }
+        const int take = (nf - done < h->max_batch - h->pending) ? nf - done : h->max_batch - h->pending;
+        PackParams P;
+        memset(&P, 0, sizeof(P));
+        P.W = W; P.H = H; P.depth_is_u16 = depth_is_u16;
+        P.depth_scale = depth_scale; P.depth_trunc = depth_trunc;
+        P.color_channels = color_channels; P.color_bgr = color_bgr;
+        P.fcx = (float)cx; P.fcy = (float)cy; P.ifx = 1.0f / (float)fx; P.ify = 1.0f / (float)fy;
+        P.fx = fx; P.fy = fy; P.cx = cx; P.cy = cy;
+        P.trunc = h->sdf_trunc; P.unit_length = h->unit_length; P.stride = h->stride;
+        P.Ws = (W + h->stride - 1) / h->stride;
+        P.n_samples = P.Ws * ((H + h->stride - 1) / h->stride);
+        P.n_alloc_blocks = (P.n_samples + 255) / 256;
+        P.rank = h->rank; P.world = h->world; P.q = h->q;
+        P.hash = h->hash; P.unit_keys = h->unit_keys; P.touched = h->touched[h->q];
+        P.counters = h->counters; P.cap_units = (int)h->cap_units;
+        for (int f = 0; f < take; f++) {
+            const double* E = extrinsics + 16 * (size_t)(done + f);
+            double pose[16];
+            if (!b2r::m4_inverse(E, pose)) { b2r_set_error("b2r_tsdf_integrate: singular extrinsic"); return B2R_ERR_SINGULAR; }
+            const int slot = h->pending + f;
+            PackFrame& pf = P.fr[f];
+            pf.depth = (const char*)depth + (size_t)(done + f) * dstep;
+            pf.color = (h->color_type == 1) ? color + (size_t)(done + f) * cstep : nullptr;
+            pf.gray = (h->color_type == 2) ? gray + (size_t)(done + f) * npx : nullptr;
+            pf.texel = h->texel[slot];
+            for (int i = 0; i < 12; i++) pf.pose[i] = pose[i];
+            pf.bit = 1u << slot;
+            B2RFrame& fr = h->frames[slot];
+            for (int i = 0; i < 12; i++) fr.E[i] = (float)E[i];
+            const float vl = (float)h->voxel_length;
+            fr.Es02 = fr.E[2] * vl; fr.Es12 = fr.E[6] * vl; fr.Es22 = fr.E[10] * vl;
+            fr.fx = (float)fx; fr.fy = (float)fy; fr.cx = (float)cx; fr.cy = (float)cy;
+            fr.safe_w = (float)W - 0.0001f; fr.safe_h = (float)H - 0.0001f;
+            fr.W = W; fr.H = H; fr.texel = h->texel[slot];
+        }
+        const size_t cbpp = (h->color_type == 1) ? (size_t)color_channels : (h->color_type == 2 ? 4 : 0);
+        P.vec_ok = (npx % 4 == 0) && ((uintptr_t)depth % 16 == 0) && (dstep % 16 == 0) &&
+                   (cbpp == 0 || ((uintptr_t)(h->color_type == 1 ? (const void*)color : (const void*)gray) % 16 == 0 && (npx * cbpp) % 16 == 0));
+        const dim3 grid((unsigned)(P.n_alloc_blocks + (npx + 256 * PACK_PX - 1) / (256 * PACK_PX)), (unsigned)take);
+        const bool prof = prof_begin(h, 1, stream);
+        tsdf_pack_alloc_kernel<<<grid, 256, 0, stream>>>(P);
+        B2R_CHECK_LAUNCH();
+        prof_end(h, prof, stream);
+        h->pending += take;
+        h->prof_frames += h->profile ? take : 0;
+        done += take;
+    }
     return B2R_OK;
 }
 
@@ -452,13 +798,15 @@ static int tsdf_integrate_impl(b2r_tsdf* h, const void* depth, int depth_is_u16,
 //   depth: f32 metres (an RGBDImage's depth) or raw u16 with depth_scale/depth_trunc (a1 fused).
 //   color: u8, 3 (RGB) or 4 channels; color_bgr=1 for the camera's BGRA order (cv2.cvtColor fused).
 //   extrinsic: HOST 16 f64, row-major, world -> camera.
+// The images are consumed by K1 before the call's work on `stream` completes; the voxel update itself is
+// deferred until max_batch frames are pending or the volume is read (results are identical either way).
 B2R_API int b2r_tsdf_integrate(b2r_tsdf* h, const void* depth, int depth_is_u16, float depth_scale, float depth_trunc,
                                const uint8_t* color, int color_channels, int color_bgr, const float* gray, int W,
                                int H, double fx, double fy, double cx, double cy, const double* extrinsic,
                                cudaStream_t stream) {
     if (!h) return B2R_ERR_BAD_ARG;
     B2RDeviceGuard g(h->device);
-    return tsdf_integrate_impl(h, depth, depth_is_u16, depth_scale, depth_trunc, color, color_channels, color_bgr, gray,
+    return tsdf_integrate_impl(h, 1, depth, depth_is_u16, depth_scale, depth_trunc, color, color_channels, color_bgr, gray,
                                W, H, fx, fy, cx, cy, extrinsic, stream);
 }
 
@@ -469,25 +817,21 @@ B2R_API int b2r_tsdf_integrate_batch(b2r_tsdf* h, int n, const void* depth, int 
                                      int W, int H, double fx, double fy, double cx, double cy,
                                      const double* extrinsics, cudaStream_t stream) {
     if (!h) return B2R_ERR_BAD_ARG;
+    if (n == 0) return B2R_OK;
+    if (h->color_type == 2) { b2r_set_error("b2r_tsdf_integrate_batch: Gray32 volumes take frames through b2r_tsdf_integrate"); return B2R_ERR_FORMAT; }
     B2RDeviceGuard g(h->device);
-    const size_t npx = (size_t)W * H;
-    const size_t dstep = npx * (depth_is_u16 ? 2 : 4), cstep = npx * (size_t)color_channels;
-    for (int f = 0; f < n; f++) {
-        int rc = tsdf_integrate_impl(h, (const char*)depth + f * dstep, depth_is_u16, depth_scale, depth_trunc,
-                                     color ? color + f * cstep : nullptr, color_channels, color_bgr, nullptr, W, H, fx,
-                                     fy, cx, cy, extrinsics + 16 * f, stream);
-        if (rc != B2R_OK) return rc;
-    }
-    return B2R_OK;
+    return tsdf_integrate_impl(h, n, depth, depth_is_u16, depth_scale, depth_trunc, color, color_channels, color_bgr, nullptr,
+                               W, H, fx, fy, cx, cy, extrinsics, stream);
 }
 
 // Same, with HOST images (pinned for true overlap): each frame's H2D copy runs on an internal copy
-// stream into a 3-deep device ring while the previous frame fuses on `stream`.
+// stream into a 3-deep device ring while earlier frames are packed / fused on `stream`.
 B2R_API int b2r_tsdf_integrate_host(b2r_tsdf* h, int n, const void* depth_host, int depth_is_u16, float depth_scale,
                                     float depth_trunc, const uint8_t* color_host, int color_channels, int color_bgr,
                                     int W, int H, double fx, double fy, double cx, double cy,
                                     const double* extrinsics, cudaStream_t stream) {
-    if (!h || !depth_host) return B2R_ERR_BAD_ARG;
+    if (!h || !depth_host || n < 0) return B2R_ERR_BAD_ARG;
+    if (h->color_type == 2) { b2r_set_error("b2r_tsdf_integrate_host: Gray32 volumes take frames through b2r_tsdf_integrate"); return B2R_ERR_FORMAT; }
     B2RDeviceGuard g(h->device);
     const size_t npx = (size_t)W * H;
     const size_t dbytes = npx * (depth_is_u16 ? 2 : 4), cbytes = color_host ? npx * (size_t)color_channels : 0;
@@ -513,11 +857,11 @@ B2R_API int b2r_tsdf_integrate_host(b2r_tsdf* h, int n, const void* depth_host, 
         if (cbytes) B2R_CUDA(cudaMemcpyAsync(h->stage_color[r], color_host + f * cbytes, cbytes, cudaMemcpyHostToDevice, h->copy_stream));
         B2R_CUDA(cudaEventRecord(h->ev_copied[r], h->copy_stream));
         B2R_CUDA(cudaStreamWaitEvent(stream, h->ev_copied[r], 0));
-        int rc = tsdf_integrate_impl(h, h->stage_depth[r], depth_is_u16, depth_scale, depth_trunc,
+        int rc = tsdf_integrate_impl(h, 1, h->stage_depth[r], depth_is_u16, depth_scale, depth_trunc,
                                      cbytes ? (const uint8_t*)h->stage_color[r] : nullptr, color_channels, color_bgr,
                                      nullptr, W, H, fx, fy, cx, cy, extrinsics + 16 * f, stream);
         if (rc != B2R_OK) return rc;
-        B2R_CUDA(cudaEventRecord(h->ev_consumed[r], stream));
+        B2R_CUDA(cudaEventRecord(h->ev_consumed[r], stream));   // K1 has packed the frame: the ring slot is free
         h->host_seq++;
     }
     return B2R_OK;
@@ -526,17 +870,19 @@ B2R_API int b2r_tsdf_integrate_host(b2r_tsdf* h, int n, const void* depth_host, 
 // ------------------------------------------------------------------------------------------------
 // stats / export / import (parity + checkpoint hooks)
 // ------------------------------------------------------------------------------------------------
-// out[0]=num_units out[1]=error bits out[2]=touched units of the last frame out[3]=cumulative updated
-// voxels (N_upd) out[4]=cumulative touched units.  Synchronises `stream`.
+// out[0]=num_units out[1]=error bits out[2]=units touched by the last fused batch out[3]=cumulative updated
+// voxels (N_upd) out[4]=cumulative (unit, frame) pairs fused.  Synchronises `stream`.
 B2R_API int b2r_tsdf_stats(b2r_tsdf* h, int64_t* out, cudaStream_t stream) {
     if (!h || !out) return B2R_ERR_BAD_ARG;
     B2RDeviceGuard g(h->device);
+    int rc = b2r_tsdf_flush_pending(h, stream);
+    if (rc != B2R_OK) return rc;
     int32_t c[B2R_C_WORDS];
     B2R_CUDA(cudaMemcpyAsync(c, h->counters, sizeof(c), cudaMemcpyDeviceToHost, stream));
     B2R_CUDA(cudaStreamSynchronize(stream));
     out[0] = c[B2R_C_NUM_UNITS] > h->cap_units ? h->cap_units : c[B2R_C_NUM_UNITS];
     out[1] = c[B2R_C_ERR];
-    out[2] = c[(h->frame_id & 1) ? B2R_C_TOUCHED1 : B2R_C_TOUCHED0];
+    out[2] = c[B2R_C_LAST_TOUCHED];
     memcpy(&out[3], &c[B2R_C_UPDATED], 8);
     memcpy(&out[4], &c[B2R_C_TOUCHED_TOTAL], 8);
     if (c[B2R_C_ERR] & 1) { b2r_set_error("TSDF unit pool overflow (capacity %lld units)", (long long)h->cap_units); return B2R_ERR_CAPACITY; }
@@ -556,6 +902,24 @@ B2R_API double b2r_tsdf_voxel_length(b2r_tsdf* h) { return h ? h->voxel_length :
 B2R_API double b2r_tsdf_sdf_trunc(b2r_tsdf* h) { return h ? h->sdf_trunc : 0.0; }
 B2R_API int b2r_tsdf_color_type(b2r_tsdf* h) { return h ? h->color_type : -1; }
 B2R_API int64_t b2r_tsdf_capacity(b2r_tsdf* h) { return h ? h->cap_units : 0; }
+B2R_API int b2r_tsdf_flush(b2r_tsdf* h, cudaStream_t stream) {
+    if (!h) return B2R_ERR_BAD_ARG;
+    B2RDeviceGuard g(h->device);
+    return b2r_tsdf_flush_pending(h, stream);
+}
+B2R_API int b2r_tsdf_set_batch(b2r_tsdf* h, int max_batch, cudaStream_t stream) {
+    if (!h || max_batch < 1 || max_batch > B2R_MAX_BATCH) return B2R_ERR_BAD_ARG;
+    B2RDeviceGuard g(h->device);
+    int rc = b2r_tsdf_flush_pending(h, stream);
+    if (rc != B2R_OK) return rc;
+    if (max_batch > h->max_batch && h->texel_px) {
+        B2R_CUDA(cudaStreamSynchronize(stream));
+        for (int i = h->max_batch; i < max_batch; i++)
+            if (!h->texel[i]) B2R_CUDA(cudaMalloc((void**)&h->texel[i], h->texel_px * sizeof(float4)));
+    }
+    h->max_batch = max_batch;
+    return B2R_OK;
+}
 
 // keys3: DEVICE int32[n*3] in pool order (n = num_units at call time)
 B2R_API int b2r_tsdf_export_keys(b2r_tsdf* h, int32_t* keys3, int64_t n, cudaStream_t stream) {
@@ -571,6 +935,9 @@ B2R_API int b2r_tsdf_export_units(b2r_tsdf* h, int64_t first, int64_t count, flo
                                   cudaStream_t stream) {
     if (!h || first < 0 || count < 0 || first + count > h->cap_units) return B2R_ERR_BAD_ARG;
     B2RDeviceGuard g(h->device);
+    int rc = b2r_tsdf_flush_pending(h, stream);
+    if (rc != B2R_OK) return rc;
+    if (count == 0) return B2R_OK;
     const size_t us = (size_t)h->planes * B2R_UNIT_VOX * 4, pl = B2R_UNIT_VOX * 4;
     const char* src = (const char*)h->pool + first * us;
     if (tsdf) B2R_CUDA(cudaMemcpy2DAsync(tsdf, pl, src, us, pl, count, cudaMemcpyDeviceToDevice, stream));
@@ -589,12 +956,12 @@ __global__ void tsdf_import_keys_kernel(B2RHash hash, int32_t* unit_keys, int32_
     const uint64_t key = b2r_pack_key(kx, ky, kz);
     uint32_t s = (uint32_t)b2r_mix64(key) & hash.mask;
     for (uint32_t probe = 0; probe <= hash.mask; probe++) {
-        unsigned long long k = atomicCAS((unsigned long long*)&hash.keys[s], (unsigned long long)B2R_KEY_EMPTY, (unsigned long long)key);
+        unsigned long long k = atomicCAS((unsigned long long*)&hash.slots[s].key, (unsigned long long)B2R_KEY_EMPTY, (unsigned long long)key);
         if (k == B2R_KEY_EMPTY) {
             int id = atomicAdd(&counters[B2R_C_NUM_UNITS], 1);
             if (id >= cap) { atomicOr(&counters[B2R_C_ERR], 1); id = -1; }
             else { unit_keys[3 * id] = kx; unit_keys[3 * id + 1] = ky; unit_keys[3 * id + 2] = kz; }
-            hash.vals[s] = id;
+            hash.slots[s].val = id;
             out_ids[i] = id;
             return;
         }
@@ -625,7 +992,9 @@ B2R_API int b2r_tsdf_import_units(b2r_tsdf* h, const int32_t* keys3, int64_t n, 
     if (!h || !keys3 || !tsdf || !weight || n < 0) return B2R_ERR_BAD_ARG;
     if (n == 0) return B2R_OK;
     B2RDeviceGuard g(h->device);
-    int rc = b2r_tsdf_ensure_scratch(h, (size_t)n * 4);
+    int rc = b2r_tsdf_flush_pending(h, stream);
+    if (rc != B2R_OK) return rc;
+    rc = b2r_tsdf_ensure_scratch(h, (size_t)n * 4);
     if (rc != B2R_OK) return rc;
     int32_t* ids = (int32_t*)h->scratch;
     tsdf_import_keys_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(h->hash, h->unit_keys, h->counters, keys3, (int)n, (int)h->cap_units, ids);
@@ -636,34 +1005,92 @@ B2R_API int b2r_tsdf_import_units(b2r_tsdf* h, const int32_t* keys3, int64_t n, 
     return B2R_OK;
 }
 
-// Per-kernel timing for the roofline line of bench.py: enable (max_frames > 0) / disable (0).
-B2R_API int b2r_tsdf_profile(b2r_tsdf* h, int max_frames) {
-    if (!h || max_frames < 0) return B2R_ERR_BAD_ARG;
+// Per-kernel timing for the roofline line of bench.py: enable for up to max_launches kernel launches
+// (0 = off).  Timing events sit on the caller's stream around every K1 / K2 launch.
+B2R_API int b2r_tsdf_profile(b2r_tsdf* h, int max_launches) {
+    if (!h || max_launches < 0) return B2R_ERR_BAD_ARG;
     B2RDeviceGuard g(h->device);
-    const int need = max_frames * 3;
-    if (need > h->prof_cap) {
-        cudaEvent_t* ev = new cudaEvent_t[need];
-        for (int i = 0; i < h->prof_cap; i++) ev[i] = h->prof_ev[i];
-        for (int i = h->prof_cap; i < need; i++) B2R_CUDA(cudaEventCreate(&ev[i]));
-        delete[] h->prof_ev;
-        h->prof_ev = ev; h->prof_cap = need;
+    if (max_launches > h->prof_cap) {
+        cudaEvent_t* ev = new cudaEvent_t[2 * max_launches];
+        int* kind = new int[max_launches];
+        for (int i = 0; i < 2 * h->prof_cap; i++) ev[i] = h->prof_ev[i];
+        for (int i = 2 * h->prof_cap; i < 2 * max_launches; i++) B2R_CUDA(cudaEventCreate(&ev[i]));
+        delete[] h->prof_ev; delete[] h->prof_kind;
+        h->prof_ev = ev; h->prof_kind = kind; h->prof_cap = max_launches;
     }
-    h->profile = max_frames > 0; h->prof_n = 0;
+    h->profile = max_launches > 0; h->prof_n = 0; h->prof_frames = 0;
     return B2R_OK;
 }
-// out[0] = frames timed, out[1] = total ms in K1 (pack+alloc), out[2] = total ms in K2 (fuse). Synchronises.
-B2R_API int b2r_tsdf_profile_read(b2r_tsdf* h, double* out3) {
-    if (!h || !out3) return B2R_ERR_BAD_ARG;
+// out[0] = frames packed while profiling, out[1] = total ms in K1 (pack+alloc), out[2] = total ms in K2 (fuse),
+// out[3] = K1 launches, out[4] = K2 launches.  Fuses pending frames and synchronises the device.
+B2R_API int b2r_tsdf_profile_read(b2r_tsdf* h, double* out5, cudaStream_t stream) {
+    if (!h || !out5) return B2R_ERR_BAD_ARG;
     B2RDeviceGuard g(h->device);
+    int rc = b2r_tsdf_flush_pending(h, stream);
+    if (rc != B2R_OK) return rc;
     B2R_CUDA(cudaDeviceSynchronize());
-    double k1 = 0.0, k2 = 0.0;
-    for (int i = 0; i + 3 <= h->prof_n; i += 3) {
-        float a = 0.f, b = 0.f;
-        B2R_CUDA(cudaEventElapsedTime(&a, h->prof_ev[i], h->prof_ev[i + 1]));
-        B2R_CUDA(cudaEventElapsedTime(&b, h->prof_ev[i + 1], h->prof_ev[i + 2]));
-        k1 += a; k2 += b;
+    double ms[3] = {0, 0, 0}, cnt[3] = {0, 0, 0};
+    for (int i = 0; i < h->prof_n; i++) {
+        float a = 0.f;
+        B2R_CUDA(cudaEventElapsedTime(&a, h->prof_ev[2 * i], h->prof_ev[2 * i + 1]));
+        ms[h->prof_kind[i]] += a; cnt[h->prof_kind[i]] += 1;
     }
-    out3[0] = h->prof_n / 3; out3[1] = k1; out3[2] = k2;
-    h->prof_n = 0;
+    out5[0] = (double)h->prof_frames; out5[1] = ms[1]; out5[2] = ms[2]; out5[3] = cnt[1]; out5[4] = cnt[2];
+    h->prof_n = 0; h->prof_frames = 0;
+    return B2R_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// self-test of the shared-reciprocal division (tests/test_gpu_parity.py): counts inputs for which
+// b2r_div_fast differs bitwise from __fdiv_rn, or b2r_rcp_markstein from __frcp_rn.  mode 0: a random, b random in the projection range;
+// mode 1: a random, b = small integer weights (1 .. 2^16); mode 2: b sweeps ALL 2^23 significands.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t selftest_rng(uint64_t& s) {
+    s = s * 6364136223846793005ull + 1442695040888963407ull;
+    return (uint32_t)(s >> 32);
+}
+__global__ void selftest_div_kernel(int mode, uint64_t seed, int iters, unsigned long long* mismatches) {
+    uint64_t s = b2r_mix64(seed + ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 0x9E3779B97F4A7C15ull);
+    unsigned bad = 0;
+    for (int i = 0; i < iters; i++) {
+        float a, b;
+        const uint32_t r0 = selftest_rng(s), r1 = selftest_rng(s);
+        if (mode == 0) {
+            a = __uint_as_float((r0 & 0x807FFFFFu) | ((100u + (r1 & 63u)) << 23));        // |a| in 2^-27 .. 2^36
+            b = __uint_as_float((r1 >> 9) | ((117u + ((r0 >> 23) & 15u)) << 23));          // b in 2^-10 .. 2^5
+        } else if (mode == 1) {
+            a = __uint_as_float((r0 & 0x807FFFFFu) | ((110u + (r1 & 31u)) << 23));
+            b = (float)(1u + ((r1 >> 8) & 0xFFFFu));
+        } else {
+            const uint32_t idx = (blockIdx.x * blockDim.x + threadIdx.x) * (uint32_t)iters + (uint32_t)i;
+            b = __uint_as_float((idx & 0x7FFFFFu) | (127u << 23));
+            a = __uint_as_float((r0 & 0x807FFFFFu) | ((120u + (r1 & 15u)) << 23));
+        }
+        const float y = b2r_rcp_markstein(b);
+        const float q = b2r_div_domain(b) ? b2r_div_fast(a, b, y) : __fdiv_rn(a, b);
+        const float ref = __fdiv_rn(a, b);
+        bad += (__float_as_uint(q) != __float_as_uint(ref)) ? 1u : 0u;
+        if (b2r_div_domain(b)) bad += (__float_as_uint(y) != __float_as_uint(__frcp_rn(b))) ? 1u : 0u;
+    }
+    if (bad) atomicAdd(mismatches, (unsigned long long)bad);
+}
+// *mismatches_host receives the count (must be 0).  n_per_mode: inputs tested per mode (rounded up).
+B2R_API int b2r_selftest_div(int64_t n_per_mode, uint64_t seed, int64_t* mismatches_host, cudaStream_t stream) {
+    if (!mismatches_host || n_per_mode < 1) return B2R_ERR_BAD_ARG;
+    unsigned long long* d = nullptr;
+    B2R_CUDA(cudaMalloc(&d, 8));
+    B2R_CUDA(cudaMemsetAsync(d, 0, 8, stream));
+    const int threads = 256, blocks = 1024;
+    for (int mode = 0; mode < 3; mode++) {
+        const int64_t n = mode == 2 ? (int64_t)1 << 23 : n_per_mode;
+        const int iters = (int)((n + (int64_t)threads * blocks - 1) / ((int64_t)threads * blocks));
+        selftest_div_kernel<<<blocks, threads, 0, stream>>>(mode, seed + mode, iters, d);
+    }
+    unsigned long long hcount = 0;
+    cudaError_t e = cudaMemcpyAsync(&hcount, d, 8, cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    cudaFree(d);
+    if (e != cudaSuccess) { b2r_set_error("b2r_selftest_div: %s", cudaGetErrorString(e)); return B2R_ERR_CUDA; }
+    *mismatches_host = (int64_t)hcount;
     return B2R_OK;
 }

@@ -6,14 +6,24 @@
 enum {
     B2R_C_NUM_UNITS = 0,   // units allocated so far
     B2R_C_ERR = 1,         // sticky error bits (1 = pool overflow, 2 = key out of range, 4 = hash full)
-    B2R_C_TOUCHED0 = 2,    // touched-unit count, buffer 0
-    B2R_C_TOUCHED1 = 3,    // touched-unit count, buffer 1
-    B2R_C_UPDATED = 4,     // u64 (words 4,5): voxels whose record changed, cumulative (N_upd)
-    B2R_C_TOUCHED_TOTAL = 6,  // u64 (words 6,7): cumulative touched units
+    B2R_C_TOUCHED0 = 2,    // touched-unit counts of the three rotating batch buffers (words 2,3,4)
+    B2R_C_UPDATED = 6,     // u64 (words 6,7): voxels whose record changed, cumulative (N_upd)
+    B2R_C_TOUCHED_TOTAL = 8,  // u64 (words 8,9): cumulative (unit, frame) pairs fused
+    B2R_C_LAST_TOUCHED = 10,  // units touched by the most recent fused batch
     B2R_C_WORDS = 16
 };
 
 #define B2R_HOST_RING 3
+#define B2R_MAX_BATCH 16   // frames fused per pass over the touched units (bits of B2RSlot::mask)
+
+// what the fusion kernel needs to know about one pending frame (kernel parameter, by value)
+struct B2RFrame {
+    float E[12];             // (float)extrinsic rows 0..2
+    float Es02, Es12, Es22;  // E(:,2) * voxel_length (f32)
+    float fx, fy, cx, cy, safe_w, safe_h;
+    int W, H;
+    const float4* texel;     // packed frame: {depth m, ray multiplier, rgb8|gray bits, 0}
+};
 
 struct b2r_tsdf {
     double voxel_length, sdf_trunc, unit_length;
@@ -23,15 +33,20 @@ struct b2r_tsdf {
     int rank, world, device;
     B2RHash hash;
     uint32_t nslots;
-    int32_t* slot_stamp;   // nslots: frame id that last touched the slot
     int32_t* unit_keys;    // cap_units * 3
     float* pool;           // cap_units * planes * 4096 : planes = tsdf, weight[, r, g, b]
-    int32_t* touched[2];   // cap_units each: hash slots touched by the frame in flight
+    int32_t* touched[3];   // cap_units each: hash slots touched by the batch using that buffer
     int32_t* counters;     // B2R_C_WORDS
-    float4* texel[2];      // packed frame: {depth m, ray multiplier, rgb8|gray bits, 0}
+    // pending batch: frames packed + allocated (K1 done) but not yet fused (K2 runs at flush)
+    int q;                 // rotating buffer index of the pending batch
+    int pending;           // frames in it
+    int max_batch;         // <= B2R_MAX_BATCH
+    B2RFrame frames[B2R_MAX_BATCH];
+    float4* texel[B2R_MAX_BATCH];
     size_t texel_px;
-    int frame_id;
+    int64_t batches;       // fused so far (alternates the sweep direction)
     int fuse_grid;         // persistent grid size of the fusion kernel
+    int fuse_smem;         // dynamic shared memory of the fusion kernel
     // host-input pipeline (b2r_tsdf_integrate_host)
     cudaStream_t copy_stream;
     cudaEvent_t ev_copied[B2R_HOST_RING], ev_consumed[B2R_HOST_RING];
@@ -42,10 +57,12 @@ struct b2r_tsdf {
     // extraction scratch
     void* scratch;
     size_t scratch_bytes;
-    // optional per-kernel timing (b2r_tsdf_profile): 3 events per frame (before K1, between, after K2)
+    // optional per-kernel timing (b2r_tsdf_profile): event pairs around every K1 / K2 launch
     int profile;
     cudaEvent_t* prof_ev;
+    int* prof_kind;        // per pair: 1 = pack+alloc, 2 = fuse
     int prof_cap, prof_n;
+    int64_t prof_frames;
 };
 
 struct B2RDeviceGuard {
@@ -55,4 +72,7 @@ struct B2RDeviceGuard {
 };
 
 int b2r_tsdf_ensure_scratch(b2r_tsdf* h, size_t bytes);
+// fuses whatever is pending (K2).  Every entry point that reads or rewrites the volume calls it first.
+int b2r_tsdf_flush_pending(b2r_tsdf* h, cudaStream_t stream);
 extern "C" int b2r_tsdf_stats(b2r_tsdf* h, int64_t* out, cudaStream_t stream);
+extern "C" int b2r_tsdf_reset(b2r_tsdf* h, cudaStream_t stream);

@@ -105,6 +105,14 @@ class ScalableTSDFVolume:
     def reset(self) -> None:
         _lib.check(self._lib.b2r_tsdf_reset(self._h, _lib.stream_ptr()), "reset")
 
+    def flush(self) -> None:
+        """Fuse the frames that are packed but still pending (build extension; every read does this itself)."""
+        _lib.check(self._lib.b2r_tsdf_flush(self._h, _lib.stream_ptr()), "flush")
+
+    def set_batch(self, max_batch: int) -> None:
+        """Frames fused per pass over the touched units (1..16; 1 = strictly per-call fusion)."""
+        _lib.check(self._lib.b2r_tsdf_set_batch(self._h, int(max_batch), _lib.stream_ptr()), "set_batch")
+
     # ---- stats / parity hooks -----------------------------------------------------------------------
     def stats(self) -> dict:
         out = (C.c_int64 * 5)()

@@ -110,14 +110,26 @@ int b2r_tsdf_integrate_host(b2r_tsdf* h, int n, const void* depth_host, int dept
                             int H, double fx, double fy, double cx, double cy, const double* extrinsics_host,
                             cudaStream_t stream);
 
-/* out[0]=units allocated, out[1]=error bits, out[2]=units touched by the last frame,
- * out[3]=cumulative updated voxels (N_upd), out[4]=cumulative touched units.  Synchronises. */
+/* Frames are packed and their blocks allocated when integrate is called; the per-voxel update of up to
+ * max_batch (default 8, env B2R_TSDF_BATCH, <= 16) pending frames runs as ONE pass over the touched
+ * units when the batch is full or when anything reads the volume (stats, export, extract, ...).  Results
+ * are bit-identical to frame-by-frame integration.  b2r_tsdf_flush forces the pass; b2r_tsdf_set_batch(1)
+ * gives strictly per-call fusion. */
+int b2r_tsdf_flush(b2r_tsdf* h, cudaStream_t stream);
+int b2r_tsdf_set_batch(b2r_tsdf* h, int max_batch, cudaStream_t stream);
+
+/* out[0]=units allocated, out[1]=error bits, out[2]=units touched by the last fused batch,
+ * out[3]=cumulative updated voxels (N_upd), out[4]=cumulative (unit, frame) pairs fused.  Synchronises. */
 int b2r_tsdf_stats(b2r_tsdf* h, int64_t* out5_host, cudaStream_t stream);
 int64_t b2r_tsdf_num_units(b2r_tsdf* h, cudaStream_t stream);
-/* per-kernel CUDA-event timing for the roofline line of bench.py: enable for up to max_frames frames
- * (0 = off); read: out3 = {frames timed, total ms pack+alloc kernel, total ms fuse kernel} */
-int b2r_tsdf_profile(b2r_tsdf* h, int max_frames);
-int b2r_tsdf_profile_read(b2r_tsdf* h, double* out3_host);
+/* per-kernel CUDA-event timing for the roofline line of bench.py: enable for up to max_launches kernel
+ * launches (0 = off); read: out5 = {frames packed, total ms pack+alloc kernel, total ms fuse kernel,
+ * pack+alloc launches, fuse launches} */
+int b2r_tsdf_profile(b2r_tsdf* h, int max_launches);
+int b2r_tsdf_profile_read(b2r_tsdf* h, double* out5_host, cudaStream_t stream);
+/* GPU self-test of the shared-reciprocal IEEE division used by the fusion kernel: number of inputs whose
+ * quotient differs bitwise from div.rn.f32 (must be 0) */
+int b2r_selftest_div(int64_t n_per_mode, uint64_t seed, int64_t* mismatches_host, cudaStream_t stream);
 /* parity / checkpoint hooks: keys int32[n][3]; planes tsdf[n][4096], weight[n][4096], rgb[n][3][4096],
  * voxel index x*256 + y*16 + z (upstream IndexOf) */
 int b2r_tsdf_export_keys(b2r_tsdf* h, int32_t* keys3, int64_t n, cudaStream_t stream);

@@ -167,8 +167,10 @@ def test_transform_and_batch(o3r, frames, small_kinect):
 # ------------------------------------------------------------------------------------------------------
 # a7 / a8 / a9 TSDF
 # ------------------------------------------------------------------------------------------------------
-def run_both(o3r, frames, intr, vl, trunc, color_type, n, capacity=6000):
+def run_both(o3r, frames, intr, vl, trunc, color_type, n, capacity=6000, batch=None):
     vol = o3d.pipelines.integration.ScalableTSDFVolume(vl, trunc, o3d.pipelines.integration.TSDFVolumeColorType(color_type), capacity_units=capacity)
+    if batch:
+        vol.set_batch(batch)       # frames fused per pass over the touched units (results must not depend on it)
     ref = o3r.TSDF(vl, trunc, color_type, parallel_units=True)
     K = intrinsic_of(intr)
     for d, c, pose in frames[:n]:
@@ -204,14 +206,48 @@ def compare_volumes(vol, ref, color_type):
     return max_dt, exact, n_upd
 
 
-@pytest.mark.parametrize("color_type", [0, 1, 2])
-def test_tsdf_integrate_parity(o3r, frames, small_kinect, color_type):
-    vol, ref = run_both(o3r, frames, small_kinect.depth_intr, 0.01, 0.04, color_type, 4)
+@pytest.mark.parametrize("color_type,batch", [(0, 1), (1, 1), (2, 1), (1, 3), (1, None), (0, 16), (2, 2)])
+def test_tsdf_integrate_parity(o3r, frames, small_kinect, color_type, batch):
+    vol, ref = run_both(o3r, frames, small_kinect.depth_intr, 0.01, 0.04, color_type, 4, batch=batch)
     max_dt, exact, n_upd = compare_volumes(vol, ref, color_type)
     assert n_upd > 100000
     assert exact, "TSDF expected bit-exact (max diff %g)" % max_dt
     st = vol.stats()
-    assert st["num_units"] == ref.num_units() and st["last_touched"] == ref.last_touched() and st["errors"] == 0
+    assert st["num_units"] == ref.num_units() and st["errors"] == 0
+    if batch == 1:
+        assert st["last_touched"] == ref.last_touched()
+
+
+def test_shared_reciprocal_division_is_ieee_exact():
+    """The fusion kernel's divisions share reciprocals (Markstein correction); they must equal div.rn bit for bit."""
+    import ctypes as C
+    from azurekinect3dreconstruction_b200 import _lib
+    bad = C.c_int64(-1)
+    _lib.check(_lib.load().b2r_selftest_div(1 << 28, 12345, C.byref(bad), _lib.stream_ptr()))
+    assert bad.value == 0
+
+
+def test_tsdf_batch_size_invariance(frames, small_kinect):
+    """Deferred multi-frame fusion == frame-by-frame fusion, bit for bit, on every plane (incl. colour)."""
+    intr = small_kinect.depth_intr
+    K = intrinsic_of(intr)
+    n = 6
+    depth = torch.from_numpy(np.stack([frames[i][0] for i in range(n)]).view(np.int16)).view(torch.uint16).cuda()
+    color = torch.stack([torch.from_numpy(frames[i][1]) for i in range(n)]).cuda()
+    E = np.stack([np.linalg.inv(frames[i][2]) for i in range(n)])
+    out = []
+    for batch in (1, 4, 16):
+        v = o3d.pipelines.integration.ScalableTSDFVolume(0.004, 0.02, o3d.pipelines.integration.TSDFVolumeColorType.RGB8, capacity_units=30000)
+        v.set_batch(batch)
+        v.integrate_raw(depth[:2], color[:2], K, E[:2])
+        v.integrate_raw(depth[2:], color[2:], K, E[2:])
+        keys, tsdf, wgt, rgb = v.export_units()
+        order = np.lexsort(keys.cpu().numpy().T[::-1])
+        out.append((keys.cpu().numpy()[order], tsdf.cpu().numpy()[order], wgt.cpu().numpy()[order], rgb.cpu().numpy()[order], v.stats()))
+    for o in out[1:]:
+        for a, b in zip(out[0][:4], o[:4]):
+            assert np.array_equal(a, b)
+        assert o[4]["updated_voxels"] == out[0][4]["updated_voxels"] and o[4]["touched_units"] == out[0][4]["touched_units"]
 
 
 def test_tsdf_fine_voxels_and_reset(o3r, frames, small_kinect):
