@@ -126,6 +126,17 @@ __device__ __noinline__ void alloc_key(const PackParams& P, uint64_t key, uint32
 
 #define PACK_PX 4   // pixels per thread in the pack role
 
+// 8-bit colours ride in the texel as one 0x00BBGGRR word
+__device__ __forceinline__ void pack_rgb(uint32_t r, uint32_t g, uint32_t b, float& z, float& w) {
+    z = __uint_as_float(r | (g << 8) | (b << 16));
+    w = 0.0f;
+}
+// byte n of c -> float, without the quarter-rate I2F: 0x4B0000nn is the float 8388608 + nn
+template <int N>
+__device__ __forceinline__ float byte_to_float(uint32_t c) {
+    return __fadd_rn(__uint_as_float(__byte_perm(c, 0x4B000000u, 0x7540 | N)), -8388608.0f);
+}
+
 __device__ __forceinline__ float pack_mult(const PackParams& P, int i, int j) {
     const float xx = xfmul(xfsub((float)j, P.fcx), P.ifx);
     const float yy = xfmul(xfsub((float)i, P.fcy), P.ify);
@@ -144,7 +155,9 @@ __global__ void __launch_bounds__(256, 4) tsdf_pack_alloc_kernel(const __grid_co
         const int npx = P.W * P.H;
         const int idx0 = ((blockIdx.x - P.n_alloc_blocks) * blockDim.x + threadIdx.x) * PACK_PX;
         if (idx0 >= npx) return;
-        float d[PACK_PX], cb[PACK_PX];
+        float d[PACK_PX], cb[PACK_PX], cw[PACK_PX];
+#pragma unroll
+        for (int k = 0; k < PACK_PX; k++) cw[k] = 0.0f;
         if (P.vec_ok && idx0 + PACK_PX <= npx) {
             if (P.depth_is_u16) {
                 const uint2 raw = __ldg(reinterpret_cast<const uint2*>((const uint16_t*)F.depth + idx0));
@@ -168,7 +181,7 @@ __global__ void __launch_bounds__(256, 4) tsdf_pack_alloc_kernel(const __grid_co
                 for (int k = 0; k < PACK_PX; k++) {
                     uint32_t v = px[k] & 0xFFFFFFu;
                     if (P.color_bgr) v = __byte_perm(v, 0, 0x4012);   // swap byte 0 and byte 2, clear byte 3
-                    cb[k] = __uint_as_float(v);
+                    pack_rgb(v & 255u, (v >> 8) & 255u, v >> 16, cb[k], cw[k]);
                 }
             } else if (F.gray) {
                 const float4 g = __ldg(reinterpret_cast<const float4*>(F.gray + idx0));
@@ -186,7 +199,7 @@ __global__ void __launch_bounds__(256, 4) tsdf_pack_alloc_kernel(const __grid_co
                     const uint8_t* c = F.color + (size_t)idx * P.color_channels;
                     uint32_t r = __ldg(c), g = __ldg(c + 1), b = __ldg(c + 2);
                     if (P.color_bgr) { const uint32_t t = r; r = b; b = t; }
-                    cb[k] = __uint_as_float(r | (g << 8) | (b << 16));
+                    pack_rgb(r, g, b, cb[k], cw[k]);
                 } else if (F.gray) {
                     cb[k] = __ldg(F.gray + idx);
                 }
@@ -195,7 +208,7 @@ __global__ void __launch_bounds__(256, 4) tsdf_pack_alloc_kernel(const __grid_co
         int i = idx0 / P.W, j = idx0 - i * P.W;
 #pragma unroll
         for (int k = 0; k < PACK_PX; k++) {
-            if (idx0 + k < npx) F.texel[idx0 + k] = make_float4(d[k], pack_mult(P, i, j), cb[k], 0.0f);
+            if (idx0 + k < npx) F.texel[idx0 + k] = make_float4(d[k], pack_mult(P, i, j), cb[k], cw[k]);
             if (++j == P.W) { j = 0; i++; }
         }
         return;
@@ -359,12 +372,8 @@ __global__ void __launch_bounds__(FUSE_THREADS, 4) tsdf_fuse_kernel(const __grid
         for (int s = 0; s < FUSE_STAGES; s++) mbar_init(&full_bar[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    // thread -> 4 consecutive z voxels.  The z-quad is WARP-uniform (so the sequential z-march to the quad's first
-    // voxel is divergence-free); a warp's lanes are 32 (x, y) columns of the slab.
-    const int zq = (tid >> 5) & 3;
-    const int col = ((tid >> 7) << 5) | (tid & 31);
-    const int y = col & 15, xl = col >> 4;
-    const int f4 = xl * 64 + y * 4 + zq;        // this thread's float4 inside a 1024-float slab plane
+    const int zq = tid & 3, y = (tid >> 2) & 15, xl = tid >> 6;
+    const int f4 = tid;                          // this thread's float4 inside a 1024-float slab plane: 4 consecutive z voxels
     unsigned int upd = 0, pairs = 0;
     uint32_t it_seq = 0;   // items issued through the ring so far by this CTA (stage = seq % STAGES)
 
@@ -486,7 +495,7 @@ __global__ void __launch_bounds__(FUSE_THREADS, 4) tsdf_fuse_kernel(const __grid
                                 float c0 = 0.f, c1 = 0.f, c2 = 0.f;
                                 if (COLOR == 1) {
                                     const uint32_t c = __float_as_uint(tx[k].z);
-                                    c0 = (float)(c & 255u); c1 = (float)((c >> 8) & 255u); c2 = (float)((c >> 16) & 255u);
+                                    c0 = byte_to_float<0>(c); c1 = byte_to_float<1>(c); c2 = byte_to_float<2>(c);
                                 } else if (COLOR == 2) {
                                     c0 = c1 = c2 = tx[k].z;
                                 }
@@ -835,7 +844,9 @@ B2R_API int b2r_tsdf_integrate_host(b2r_tsdf* h, int n, const void* depth_host, 
     B2RDeviceGuard g(h->device);
     const size_t npx = (size_t)W * H;
     const size_t dbytes = npx * (depth_is_u16 ? 2 : 4), cbytes = color_host ? npx * (size_t)color_channels : 0;
-    if (h->stage_depth_bytes < dbytes || h->stage_color_bytes < cbytes) {
+    // a ring slot stages one chunk of up to max_batch frames: two large copies and ONE K1 launch per chunk
+    const size_t need_d = dbytes * h->max_batch, need_c = cbytes ? cbytes * h->max_batch : 16;
+    if (h->stage_depth_bytes < need_d || h->stage_color_bytes < need_c) {
         B2R_CUDA(cudaStreamSynchronize(stream));
         B2R_CUDA(cudaStreamSynchronize(h->copy_stream));
         for (int i = 0; i < B2R_HOST_RING; i++) {
@@ -844,25 +855,30 @@ B2R_API int b2r_tsdf_integrate_host(b2r_tsdf* h, int n, const void* depth_host, 
         }
         h->stage_depth_bytes = h->stage_color_bytes = 0;
         for (int i = 0; i < B2R_HOST_RING; i++) {
-            B2R_CUDA(cudaMalloc(&h->stage_depth[i], dbytes));
-            B2R_CUDA(cudaMalloc(&h->stage_color[i], cbytes ? cbytes : 16));
+            B2R_CUDA(cudaMalloc(&h->stage_depth[i], need_d));
+            B2R_CUDA(cudaMalloc(&h->stage_color[i], need_c));
         }
-        h->stage_depth_bytes = dbytes; h->stage_color_bytes = cbytes ? cbytes : 16;
+        h->stage_depth_bytes = need_d; h->stage_color_bytes = need_c;
         h->host_seq = 0;
     }
-    for (int f = 0; f < n; f++) {
+    int f = 0;
+    while (f < n) {
+        int room = h->max_batch - h->pending;
+        if (room <= 0) room = h->max_batch;
+        const int take = n - f < room ? n - f : room;
         const int r = (int)(h->host_seq % B2R_HOST_RING);
         if (h->host_seq >= B2R_HOST_RING) B2R_CUDA(cudaStreamWaitEvent(h->copy_stream, h->ev_consumed[r], 0));
-        B2R_CUDA(cudaMemcpyAsync(h->stage_depth[r], (const char*)depth_host + f * dbytes, dbytes, cudaMemcpyHostToDevice, h->copy_stream));
-        if (cbytes) B2R_CUDA(cudaMemcpyAsync(h->stage_color[r], color_host + f * cbytes, cbytes, cudaMemcpyHostToDevice, h->copy_stream));
+        B2R_CUDA(cudaMemcpyAsync(h->stage_depth[r], (const char*)depth_host + (size_t)f * dbytes, dbytes * take, cudaMemcpyHostToDevice, h->copy_stream));
+        if (cbytes) B2R_CUDA(cudaMemcpyAsync(h->stage_color[r], color_host + (size_t)f * cbytes, cbytes * take, cudaMemcpyHostToDevice, h->copy_stream));
         B2R_CUDA(cudaEventRecord(h->ev_copied[r], h->copy_stream));
         B2R_CUDA(cudaStreamWaitEvent(stream, h->ev_copied[r], 0));
-        int rc = tsdf_integrate_impl(h, 1, h->stage_depth[r], depth_is_u16, depth_scale, depth_trunc,
+        int rc = tsdf_integrate_impl(h, take, h->stage_depth[r], depth_is_u16, depth_scale, depth_trunc,
                                      cbytes ? (const uint8_t*)h->stage_color[r] : nullptr, color_channels, color_bgr,
-                                     nullptr, W, H, fx, fy, cx, cy, extrinsics + 16 * f, stream);
+                                     nullptr, W, H, fx, fy, cx, cy, extrinsics + 16 * (size_t)f, stream);
         if (rc != B2R_OK) return rc;
-        B2R_CUDA(cudaEventRecord(h->ev_consumed[r], stream));   // K1 has packed the frame: the ring slot is free
+        B2R_CUDA(cudaEventRecord(h->ev_consumed[r], stream));   // K1 has packed the chunk: the ring slot is free
         h->host_seq++;
+        f += take;
     }
     return B2R_OK;
 }

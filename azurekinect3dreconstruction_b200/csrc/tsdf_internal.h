@@ -22,7 +22,7 @@ struct B2RFrame {
     float Es02, Es12, Es22;  // E(:,2) * voxel_length (f32)
     float fx, fy, cx, cy, safe_w, safe_h;
     int W, H;
-    const float4* texel;     // packed frame: {depth m, ray multiplier, rgb8|gray bits, 0}
+    const float4* texel;     // packed frame: {depth m, ray multiplier, rgb8 | gray f32 bits, 0}
 };
 
 struct b2r_tsdf {
