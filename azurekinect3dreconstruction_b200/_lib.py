@@ -28,6 +28,7 @@ SIGNATURES = {
     "b2r_last_error": (C.c_char_p, []),
     "b2r_m4_inverse": (_i, [_pd, _pd]),
     "b2r_m4_mul": (None, [_pd, _pd, _pd]),
+    "b2r_unit_owner": (_i, [_i, _i, _i, _i]),
     "b2r_depth_to_float": (_i, [_vp, _i64, _f, _f, _vp, _vp]),
     "b2r_rgb_to_intensity": (_i, [_vp, _i64, _i, _i, _vp, _vp]),
     "b2r_unproject_scratch_words": (_i64, [_i, _i, _i, _i, _i]),
@@ -56,6 +57,7 @@ SIGNATURES = {
     "b2r_tsdf_import_units": (_i, [_vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     "b2r_tsdf_extract_points": (_i, [_vp, _vp, _vp, _vp, _vp, _i64, _pi64, _vp]),
     "b2r_tsdf_extract_mesh": (_i, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _pi64, _pi64, _vp]),
+    "b2r_tsdf_extract_mesh_sharded": (_i, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _pi64, _pi64, _pi64, _vp]),
     "b2r_mesh_vertex_normals": (_i, [_vp, _i64, _vp, _i64, _vp, _vp]),
     "b2r_odometry": (_i, [_vp, _vp, _vp, _vp, _i, _i, _d, _d, _d, _d, _pd, _i, _pi, _i, _d, _d, _d, _pd, _pd, _pi, _vp]),
     "b2r_image_filter": (_i, [_vp, _i, _i, _i, _vp, _vp]),

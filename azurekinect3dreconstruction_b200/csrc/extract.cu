@@ -316,12 +316,12 @@ __global__ void scatter_bases_kernel(const int32_t* order, const int32_t* scan, 
 __global__ void __launch_bounds__(256) mesh_fill_kernel(const VolView V, const int32_t* order, const uint32_t* vinfo,
                                                         const int32_t* vbase_by_unit, const int32_t* tbase,
                                                         double* vtx, double* vcol, int32_t* tri, int32_t* ids,
-                                                        int64_t capV, int64_t capF) {
+                                                        int64_t capV, int64_t capF, int pos0, int64_t v0, int64_t t0) {
     __shared__ float A[MD * MD * MD];
     __shared__ unsigned char C[MC * MC * MC];
     __shared__ int nb[27];
     __shared__ int ws[9];
-    const int pos = blockIdx.x;
+    const int pos = blockIdx.x + pos0;   // a sharded handle fills its own contiguous range of the (owner, key) order
     const int unit = order[pos];
     stage_apron<-1, false>(V, unit, A, nb);
     stage_complete(A, C);
@@ -336,7 +336,7 @@ __global__ void __launch_bounds__(256) mesh_fill_kernel(const VolView V, const i
         const uint32_t info = vi[z];
         const unsigned m = info & 7u;
         if (!m) continue;
-        int64_t o = vb + (info >> 3);
+        int64_t o = vb + (info >> 3) - v0;   // compact output; vertex ids inside triangles stay global
         const float f0f = apron_m(A, x, y, z);
         const float* v0 = V.pool + (int64_t)unit * V.unit_stride + (x * 256 + y * 16 + z);
         const int e[3] = {kx * 16 + x, ky * 16 + y, kz * 16 + z};
@@ -378,7 +378,7 @@ __global__ void __launch_bounds__(256) mesh_fill_kernel(const VolView V, const i
     int ttot;
     int toff = block_exclusive_scan(tc, &ttot, ws);
     if (ttot == 0) return;
-    int64_t to = (int64_t)tbase[pos] + toff;
+    int64_t to = (int64_t)tbase[pos] + toff - t0;
 #pragma unroll 1
     for (int z = 0; z < 16; z++) {
         const int cube = cases[z];
@@ -433,11 +433,14 @@ int carve(b2r_tsdf* h, int n, bool mesh, Scratch* S) {
     size_t sort_tmp = 0, scan_tmp = 0;
     cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp, (uint64_t*)nullptr, (uint64_t*)nullptr, (int32_t*)nullptr, (int32_t*)nullptr, n);
     cub::DeviceScan::ExclusiveSum(nullptr, scan_tmp, (int32_t*)nullptr, (int32_t*)nullptr, n + 1);
+    size_t sort2_tmp = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, sort2_tmp, (uint32_t*)nullptr, (uint32_t*)nullptr, (int32_t*)nullptr, (int32_t*)nullptr, n);
+    if (sort2_tmp > sort_tmp) sort_tmp = sort2_tmp;
     const size_t cub_bytes = align_up(sort_tmp > scan_tmp ? sort_tmp : scan_tmp);
     size_t total = 0;
     auto take = [&](size_t bytes) { size_t o = total; total += align_up(bytes); return o; };
     const size_t o_kin = take((size_t)n * 8), o_kout = take((size_t)n * 8), o_idin = take((size_t)n * 4), o_ord = take((size_t)n * 4);
-    const size_t o_ca = take((size_t)(n + 1) * 4), o_cb = take((size_t)(n + 1) * 4), o_sa = take((size_t)(n + 1) * 4), o_sb = take((size_t)(n + 1) * 4);
+    const size_t o_ca = take((size_t)(n + 65) * 4), o_cb = take((size_t)(n + 1) * 4), o_sa = take((size_t)(n + 1) * 4), o_sb = take((size_t)(n + 1) * 4);
     const size_t o_vb = take((size_t)n * 4);
     const size_t o_cub = take(cub_bytes);
     const size_t o_vi = mesh ? take((size_t)n * B2R_UNIT_VOX * 4) : 0;
@@ -462,11 +465,40 @@ VolView make_view(const b2r_tsdf* h) {
     return V;
 }
 
-int sorted_order(b2r_tsdf* h, int n, Scratch& S, cudaStream_t stream) {
+__global__ void owner_of_sorted_kernel(const int32_t* order, const int32_t* unit_keys, int n, int world, uint32_t* owner, int32_t* id_out, int32_t* hist) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int u = order[i];
+    const int o = b2r_owner(b2r_pack_key(unit_keys[3 * u], unit_keys[3 * u + 1], unit_keys[3 * u + 2]), world);
+    owner[i] = (uint32_t)o; id_out[i] = u;
+    atomicAdd(&hist[o], 1);
+}
+
+// Canonical unit order: by packed key; for a sharded handle (world > 1) by (owner rank, packed key), so that
+// the units -- and therefore the vertices -- of one rank are a contiguous range of the global numbering.
+// own[0], own[1]: the range of positions owned by h->rank (the whole range when world == 1).
+int sorted_order(b2r_tsdf* h, int n, Scratch& S, int* own, cudaStream_t stream) {
     pack_keys_kernel<<<(n + 255) / 256, 256, 0, stream>>>(h->unit_keys, n, S.k_in, S.id_in);
     B2R_CHECK_LAUNCH();
     size_t tmp = S.cub_bytes;
     B2R_CUDA(cub::DeviceRadixSort::SortPairs(S.cub_tmp, tmp, S.k_in, S.k_out, S.id_in, S.order, n, 0, 63, stream));
+    own[0] = 0; own[1] = n;
+    if (h->world <= 1) return B2R_OK;
+    // second, stable pass by owner (keys reuse the k_in buffer as uint32, values go order -> id_in -> order)
+    uint32_t* ow_in = reinterpret_cast<uint32_t*>(S.k_in);
+    uint32_t* ow_out = ow_in + n;
+    int32_t* hist = S.cnt_a;   // free until the count pass
+    B2R_CUDA(cudaMemsetAsync(hist, 0, 64 * 4, stream));
+    owner_of_sorted_kernel<<<(n + 255) / 256, 256, 0, stream>>>(S.order, h->unit_keys, n, h->world, ow_in, S.id_in, hist);
+    B2R_CHECK_LAUNCH();
+    tmp = S.cub_bytes;
+    B2R_CUDA(cub::DeviceRadixSort::SortPairs(S.cub_tmp, tmp, ow_in, ow_out, S.id_in, S.order, n, 0, 8, stream));
+    int32_t hh[64];
+    B2R_CUDA(cudaMemcpyAsync(hh, hist, 64 * 4, cudaMemcpyDeviceToHost, stream));
+    B2R_CUDA(cudaStreamSynchronize(stream));
+    int a = 0;
+    for (int r = 0; r < h->rank; r++) a += hh[r];
+    own[0] = a; own[1] = a + hh[h->rank];
     return B2R_OK;
 }
 
@@ -489,21 +521,25 @@ B2R_API int b2r_tsdf_extract_points(b2r_tsdf* h, double* xyz, double* rgb, doubl
     Scratch S;
     rc = carve(h, n, false, &S);
     if (rc != B2R_OK) return rc;
-    rc = sorted_order(h, n, S, stream);
+    int own[2];
+    rc = sorted_order(h, n, S, own, stream);
     if (rc != B2R_OK) return rc;
+    const int n_own = own[1] - own[0];
+    if (n_own == 0) return B2R_OK;
+    const int32_t* order = S.order + own[0];   // a sharded handle emits the points of its own units only
     const VolView V = make_view(h);
-    extract_points_kernel<false><<<n, 256, 0, stream>>>(V, S.order, S.cnt_a, nullptr, nullptr, nullptr, nullptr, nullptr, 0);
+    extract_points_kernel<false><<<n_own, 256, 0, stream>>>(V, order, S.cnt_a, nullptr, nullptr, nullptr, nullptr, nullptr, 0);
     B2R_CHECK_LAUNCH();
-    B2R_CUDA(cudaMemsetAsync(S.cnt_a + n, 0, 4, stream));
+    B2R_CUDA(cudaMemsetAsync(S.cnt_a + n_own, 0, 4, stream));
     size_t tmp = S.cub_bytes;
-    B2R_CUDA(cub::DeviceScan::ExclusiveSum(S.cub_tmp, tmp, S.cnt_a, S.scan_a, n + 1, stream));
+    B2R_CUDA(cub::DeviceScan::ExclusiveSum(S.cub_tmp, tmp, S.cnt_a, S.scan_a, n_own + 1, stream));
     int32_t total = 0;
-    B2R_CUDA(cudaMemcpyAsync(&total, S.scan_a + n, 4, cudaMemcpyDeviceToHost, stream));
+    B2R_CUDA(cudaMemcpyAsync(&total, S.scan_a + n_own, 4, cudaMemcpyDeviceToHost, stream));
     B2R_CUDA(cudaStreamSynchronize(stream));
     *count = total;
     if (!xyz || capacity < total) { b2r_set_error("extract_points: need capacity %d", total); return B2R_ERR_CAPACITY; }
     if (total == 0) return B2R_OK;
-    extract_points_kernel<true><<<n, 256, 0, stream>>>(V, S.order, nullptr, S.scan_a, xyz, h->planes == 5 ? rgb : nullptr, nrm, ids, capacity);
+    extract_points_kernel<true><<<n_own, 256, 0, stream>>>(V, order, nullptr, S.scan_a, xyz, h->planes == 5 ? rgb : nullptr, nrm, ids, capacity);
     B2R_CHECK_LAUNCH();
     return B2R_OK;
 }
@@ -511,8 +547,12 @@ B2R_API int b2r_tsdf_extract_points(b2r_tsdf* h, double* xyz, double* rgb, doubl
 // volume.extract_triangle_mesh().  Outputs (DEVICE): vtx/vcol f64 [capV*3], tri int32 [capF*3],
 // ids optional int32 [capV*4] = global integer edge id (X,Y,Z,axis) of each vertex.
 // Same two-call capacity protocol as extract_points (nV/nF always written).
-B2R_API int b2r_tsdf_extract_mesh(b2r_tsdf* h, double* vtx, double* vcol, int32_t* tri, int32_t* ids, int64_t capV,
-                                  int64_t capF, int64_t* nV, int64_t* nF, cudaStream_t stream) {
+// Sharded form (handle created with world > 1 and holding the FULL volume: its own units plus the other ranks'
+// units imported as ghosts): emits the vertices owned by this rank's units and the triangles of their cubes.
+// Triangle vertex ids are GLOBAL in the (owner rank, unit key, voxel, axis) order, so the rank-order
+// concatenation of all ranks' outputs is the complete welded mesh; *vertex_base = this rank's first global id.
+B2R_API int b2r_tsdf_extract_mesh_sharded(b2r_tsdf* h, double* vtx, double* vcol, int32_t* tri, int32_t* ids, int64_t capV,
+                                          int64_t capF, int64_t* nV, int64_t* nF, int64_t* vertex_base, cudaStream_t stream) {
     if (!h || !nV || !nF) return B2R_ERR_BAD_ARG;
     B2RDeviceGuard g(h->device);
     int64_t st[5];
@@ -524,9 +564,12 @@ B2R_API int b2r_tsdf_extract_mesh(b2r_tsdf* h, double* vtx, double* vcol, int32_
     Scratch S;
     rc = carve(h, n, true, &S);
     if (rc != B2R_OK) return rc;
-    rc = sorted_order(h, n, S, stream);
+    int own[2];
+    rc = sorted_order(h, n, S, own, stream);
     if (rc != B2R_OK) return rc;
     const VolView V = make_view(h);
+    // the count pass covers EVERY unit the handle holds (own + imported ghosts): it fixes the global vertex
+    // numbering, which a cube needs for edges owned by a neighbouring unit of another rank
     mesh_count_kernel<<<n, 256, 0, stream>>>(V, S.order, S.vinfo, S.cnt_a, S.cnt_b);
     B2R_CHECK_LAUNCH();
     B2R_CUDA(cudaMemsetAsync(S.cnt_a + n, 0, 4, stream));
@@ -535,18 +578,28 @@ B2R_API int b2r_tsdf_extract_mesh(b2r_tsdf* h, double* vtx, double* vcol, int32_
     B2R_CUDA(cub::DeviceScan::ExclusiveSum(S.cub_tmp, tmp, S.cnt_a, S.scan_a, n + 1, stream));
     tmp = S.cub_bytes;
     B2R_CUDA(cub::DeviceScan::ExclusiveSum(S.cub_tmp, tmp, S.cnt_b, S.scan_b, n + 1, stream));
-    int32_t tv = 0, tf = 0;
-    B2R_CUDA(cudaMemcpyAsync(&tv, S.scan_a + n, 4, cudaMemcpyDeviceToHost, stream));
-    B2R_CUDA(cudaMemcpyAsync(&tf, S.scan_b + n, 4, cudaMemcpyDeviceToHost, stream));
+    int32_t v01[2] = {0, 0}, t01[2] = {0, 0};
+    B2R_CUDA(cudaMemcpyAsync(&v01[0], S.scan_a + own[0], 4, cudaMemcpyDeviceToHost, stream));
+    B2R_CUDA(cudaMemcpyAsync(&v01[1], S.scan_a + own[1], 4, cudaMemcpyDeviceToHost, stream));
+    B2R_CUDA(cudaMemcpyAsync(&t01[0], S.scan_b + own[0], 4, cudaMemcpyDeviceToHost, stream));
+    B2R_CUDA(cudaMemcpyAsync(&t01[1], S.scan_b + own[1], 4, cudaMemcpyDeviceToHost, stream));
     B2R_CUDA(cudaStreamSynchronize(stream));
+    const int32_t tv = v01[1] - v01[0], tf = t01[1] - t01[0];
     *nV = tv; *nF = tf;
+    if (vertex_base) *vertex_base = v01[0];
     if (!vtx || !tri || capV < tv || capF < tf) { b2r_set_error("extract_mesh: need capacity V=%d F=%d", tv, tf); return B2R_ERR_CAPACITY; }
-    if (tv == 0) return B2R_OK;
+    if (tv == 0 || own[1] == own[0]) return B2R_OK;
     scatter_bases_kernel<<<(n + 255) / 256, 256, 0, stream>>>(S.order, S.scan_a, S.vbase_by_unit, n);
     B2R_CHECK_LAUNCH();
-    mesh_fill_kernel<<<n, 256, 0, stream>>>(V, S.order, S.vinfo, S.vbase_by_unit, S.scan_b, vtx, h->planes == 5 ? vcol : nullptr, tri, ids, capV, capF);
+    mesh_fill_kernel<<<own[1] - own[0], 256, 0, stream>>>(V, S.order, S.vinfo, S.vbase_by_unit, S.scan_b, vtx, h->planes == 5 ? vcol : nullptr, tri, ids,
+                                                        capV, capF, own[0], (int64_t)v01[0], (int64_t)t01[0]);
     B2R_CHECK_LAUNCH();
     return B2R_OK;
+}
+
+B2R_API int b2r_tsdf_extract_mesh(b2r_tsdf* h, double* vtx, double* vcol, int32_t* tri, int32_t* ids, int64_t capV,
+                                  int64_t capF, int64_t* nV, int64_t* nF, cudaStream_t stream) {
+    return b2r_tsdf_extract_mesh_sharded(h, vtx, vcol, tri, ids, capV, capF, nV, nF, nullptr, stream);
 }
 
 // ---- TriangleMesh.compute_vertex_normals() (GoodColorReconstruction.py:286) --------

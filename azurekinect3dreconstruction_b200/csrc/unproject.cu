@@ -396,3 +396,8 @@ B2R_API int b2r_rgb_to_intensity(const uint8_t* rgb, int64_t n, int channels, in
 // host helpers shared with the Python shim so pose algebra is done once, in f64, the same way everywhere
 B2R_API int b2r_m4_inverse(const double* in, double* out) { return b2r::m4_inverse(in, out) ? B2R_OK : B2R_ERR_SINGULAR; }
 B2R_API void b2r_m4_mul(const double* a, const double* b, double* out) { b2r::m4_mul(a, b, out); }
+// shard owner of a volume unit: the rank whose handle allocates and fuses unit (kx,ky,kz)
+B2R_API int b2r_unit_owner(int kx, int ky, int kz, int world) {
+    if (world < 1 || !b2r_key_in_range(kx, ky, kz)) return -1;
+    return b2r_owner(b2r_pack_key(kx, ky, kz), world);
+}

@@ -1,2 +1,2 @@
 """o3d.pipelines look-alike: integration (TSDF), odometry, registration."""
-from . import integration, odometry, registration  # noqa: F401
+from . import integration, odometry, registration, sharded  # noqa: F401

@@ -143,7 +143,7 @@ class ScalableTSDFVolume:
 
     def import_units(self, keys, tsdf, weight, rgb=None) -> None:
         dev = _lib.require_cuda()
-        keys = torch.as_tensor(np.asarray(keys), dtype=torch.int32).to(dev).contiguous()
+        keys = (keys if torch.is_tensor(keys) else torch.as_tensor(np.asarray(keys))).to(dev, dtype=torch.int32).contiguous()
         tsdf = torch.as_tensor(tsdf, dtype=torch.float32).to(dev).contiguous()
         weight = torch.as_tensor(weight, dtype=torch.float32).to(dev).contiguous()
         if rgb is not None:

@@ -1,0 +1,175 @@
+"""Multi-GPU form of the TSDF path; one process per GPU, torch.distributed for the plumbing.
+
+The reference is single-process (its only "many streams, one volume" precedent is
+CodeThatKindaWorks/BetterVisualizerD2camerasWORKSkinda.py:533-570).  Here the volume is sharded by unit key:
+``owner(key) = mix64(key) >> 33 mod world`` (csrc/common.cuh b2r_owner).  Every rank sees every frame and
+allocates / fuses only the units it owns -- integration needs NO collective.  Extraction needs one exchange,
+because marching-cubes cubes and surface-point normals straddle unit borders:
+
+  1. all-gather-v of the ranks' units (keys + voxel planes) over NCCL/NVLink -> every rank holds the full volume
+     in a scratch handle (own units + ghosts);
+  2. every rank extracts what ITS units own (b2r_tsdf_extract_mesh_sharded: vertices of its units' edges,
+     triangles of its units' cubes; vertex ids are global in (owner rank, key, voxel, axis) order, so no
+     cross-rank welding is needed);
+  3. all-gather-v of the parts; the rank-order concatenation is the complete mesh / cloud.
+
+Odometry and ICP pairs are independent: one pair per GPU ("replicas only"), no collective.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional
+
+import numpy as np
+import torch
+
+from .. import _lib
+from ..geometry import PointCloud, TriangleMesh
+from ..utility import Vector3dVector, Vector3iVector
+from .integration import ScalableTSDFVolume, TSDFVolumeColorType
+
+_M64 = (1 << 64) - 1
+_BIAS = 1 << 20
+
+
+def mix64(x: int) -> int:
+    x &= _M64
+    x ^= x >> 30
+    x = (x * 0xBF58476D1CE4E5B9) & _M64
+    x ^= x >> 27
+    x = (x * 0x94D049BB133111EB) & _M64
+    x ^= x >> 31
+    return x
+
+
+def unit_owner(key, world: int) -> int:
+    """Python mirror of b2r_unit_owner (host-side routing / tests)."""
+    kx, ky, kz = (int(v) for v in key)
+    packed = ((kx + _BIAS) << 42) | ((ky + _BIAS) << 21) | (kz + _BIAS)
+    return 0 if world <= 1 else (mix64(packed) >> 33) % world
+
+
+class Comm:
+    """Variable-length all-gather over a torch.distributed group (NCCL on GPUs, gloo on CPU tensors)."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+
+    def all_gather_v(self, t: torch.Tensor) -> List[torch.Tensor]:
+        n = torch.tensor([t.shape[0]], dtype=torch.int64, device=t.device)
+        counts = [torch.zeros_like(n) for _ in range(self.world)]
+        self.dist.all_gather(counts, n, group=self.group)
+        counts = [int(c.item()) for c in counts]
+        m = max(counts + [1])
+        pad = torch.zeros((m,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        pad[:t.shape[0]] = t
+        out = [torch.empty_like(pad) for _ in range(self.world)]
+        self.dist.all_gather(out, pad, group=self.group)
+        return [o[:c] for o, c in zip(out, counts)]
+
+
+class LocalComm:
+    """In-process stand-in used to emulate `world` ranks on one GPU (tests): the caller runs a phase for every
+    rank, then hands the per-rank tensors to `exchange`, which returns what all_gather_v would."""
+
+    def __init__(self, rank: int, world: int):
+        self.rank, self.world = rank, world
+
+
+# ---- the three phases (local -> collective -> local -> collective -> local) ------------------------------
+def phase_export(vol: ScalableTSDFVolume):
+    keys, tsdf, wgt, rgb = vol.export_units()
+    return [keys.contiguous(), tsdf, wgt] + ([rgb] if rgb is not None else [])
+
+
+def phase_extract(vol: ScalableTSDFVolume, gathered: List[List[torch.Tensor]], what: str = "mesh"):
+    """gathered[i] = list over ranks of tensor i of phase_export.  Returns this rank's part."""
+    cat = [torch.cat(g) for g in gathered]
+    total = int(cat[0].shape[0])
+    tmp = ScalableTSDFVolume(vol.voxel_length, vol.sdf_trunc, vol.color_type, capacity_units=max(total, 1) + 16,
+                             rank=vol.rank, world=vol.world)
+    if total:
+        tmp.import_units(cat[0], cat[1], cat[2], cat[3] if len(cat) > 3 else None)
+    if what == "points":
+        pc = tmp.extract_point_cloud()
+        dev = _lib.require_cuda()
+        e = lambda: torch.empty((0, 3), dtype=torch.float64, device=dev)
+        parts = [pc.points.tensor if len(pc.points) else e(), pc.normals.tensor if len(pc.points) else e()]
+        if vol.color_type != TSDFVolumeColorType.NoColor:
+            parts.append(pc.colors.tensor if len(pc.points) else e())
+        return parts
+    return _extract_mesh_part(tmp)
+
+
+def _extract_mesh_part(tmp: ScalableTSDFVolume):
+    lib, dev = _lib.load(), _lib.require_cuda()
+    nV, nF, vb = C.c_int64(0), C.c_int64(0), C.c_int64(0)
+    rc = lib.b2r_tsdf_extract_mesh_sharded(tmp._h, None, None, None, None, 0, 0, C.byref(nV), C.byref(nF), C.byref(vb), _lib.stream_ptr())
+    if rc not in (_lib.OK, _lib.ERR_CAPACITY):
+        _lib.check(rc, "extract_mesh_sharded")
+    v, f = int(nV.value), int(nF.value)
+    has_c = tmp.color_type != TSDFVolumeColorType.NoColor
+    vtx = torch.empty((v, 3), dtype=torch.float64, device=dev)
+    vcol = torch.empty((v, 3), dtype=torch.float64, device=dev) if has_c else None
+    tri = torch.empty((f, 3), dtype=torch.int32, device=dev)
+    if v:
+        _lib.check(lib.b2r_tsdf_extract_mesh_sharded(tmp._h, _lib.ptr(vtx), _lib.ptr(vcol), _lib.ptr(tri) if f else _lib.ptr(torch.empty((1, 3), dtype=torch.int32, device=dev)),
+                                                      None, v, max(f, 1), C.byref(nV), C.byref(nF), C.byref(vb), _lib.stream_ptr()), "extract_mesh_sharded")
+    return [vtx, tri] + ([vcol] if has_c else [])
+
+
+def merge_mesh_parts(parts: List[List[torch.Tensor]]) -> TriangleMesh:
+    """parts[i] = list over ranks of tensor i of _extract_mesh_part.  Triangle ids are already global and the
+    global vertex order is rank-major, so the mesh is the plain rank-order concatenation."""
+    mesh = TriangleMesh()
+    vtx, tri = torch.cat(parts[0]), torch.cat(parts[1])
+    if vtx.shape[0] == 0:
+        return mesh
+    mesh.vertices = Vector3dVector(vtx)
+    mesh.triangles = Vector3iVector(tri)
+    if len(parts) > 2:
+        mesh.vertex_colors = Vector3dVector(torch.cat(parts[2]))
+    return mesh
+
+
+def merge_point_parts(parts: List[List[torch.Tensor]]) -> PointCloud:
+    pcd = PointCloud()
+    pts = torch.cat(parts[0])
+    if pts.shape[0] == 0:
+        return pcd
+    pcd.points = Vector3dVector(pts)
+    pcd.normals = Vector3dVector(torch.cat(parts[1]))
+    if len(parts) > 2:
+        pcd.colors = Vector3dVector(torch.cat(parts[2]))
+    return pcd
+
+
+class ShardedTSDFVolume:
+    """One shard of a ScalableTSDFVolume per rank; same integrate / extract calls, collective extraction."""
+
+    def __init__(self, voxel_length: float, sdf_trunc: float, color_type, *, group=None, capacity_units: Optional[int] = None):
+        self.comm = Comm(group)
+        self.local = ScalableTSDFVolume(voxel_length, sdf_trunc, color_type, capacity_units=capacity_units,
+                                        rank=self.comm.rank, world=self.comm.world)
+
+    def integrate(self, image, intrinsic, extrinsic) -> None:
+        self.local.integrate(image, intrinsic, extrinsic)          # every rank gets every frame; no collective
+
+    def integrate_raw(self, *a, **k) -> None:
+        self.local.integrate_raw(*a, **k)
+
+    def reset(self) -> None:
+        self.local.reset()
+
+    def _gather(self, tensors):
+        return [self.comm.all_gather_v(t) for t in tensors]
+
+    def extract_triangle_mesh(self) -> TriangleMesh:
+        part = phase_extract(self.local, self._gather(phase_export(self.local)), "mesh")
+        return merge_mesh_parts(self._gather(part))
+
+    def extract_point_cloud(self) -> PointCloud:
+        part = phase_extract(self.local, self._gather(phase_export(self.local)), "points")
+        return merge_point_parts(self._gather(part))

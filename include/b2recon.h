@@ -48,6 +48,9 @@ const char* b2r_last_error(void);
 int b2r_m4_inverse(const double* in16, double* out16);
 void b2r_m4_mul(const double* a16, const double* b16, double* out16);
 
+/* multi-GPU sharding rule (host): rank that owns volume unit (kx,ky,kz) among `world` ranks; -1 if out of range */
+int b2r_unit_owner(int kx, int ky, int kz, int world);
+
 /* ---- a1: RGBDImage.create_from_color_and_depth pieces (Depth2PC.py:60-66,
  *      GoodColorReconstruction.py:131-137, RGBD_Odometry.py:15-18).  Normally fused into consumers. */
 int b2r_depth_to_float(const uint16_t* depth, int64_t n, float depth_scale, float depth_trunc, float* out,
@@ -145,6 +148,13 @@ int b2r_tsdf_extract_points(b2r_tsdf* h, double* xyz, double* rgb, double* nrm, 
 /* ---- a11: volume.extract_triangle_mesh()  (GoodColorReconstruction.py:285,536) */
 int b2r_tsdf_extract_mesh(b2r_tsdf* h, double* vtx, double* vcol, int32_t* tri, int32_t* ids4, int64_t capV,
                           int64_t capF, int64_t* nV_host, int64_t* nF_host, cudaStream_t stream);
+/* Multi-GPU form: on a handle created with world > 1 that holds the full volume (own units + the
+ * other ranks' units imported as ghosts), a10/a11 emit only what this rank's units own; triangle vertex ids
+ * are global in (owner rank, unit key, voxel, axis) order, so concatenating the ranks' outputs in rank order
+ * gives the complete welded mesh.  *vertex_base_host = this rank's first global vertex id. */
+int b2r_tsdf_extract_mesh_sharded(b2r_tsdf* h, double* vtx, double* vcol, int32_t* tri, int32_t* ids, int64_t capV,
+                                  int64_t capF, int64_t* nV_host, int64_t* nF_host, int64_t* vertex_base_host,
+                                  cudaStream_t stream);
 /* mesh.compute_vertex_normals()  (GoodColorReconstruction.py:286) */
 int b2r_mesh_vertex_normals(const double* vtx, int64_t nV, const int32_t* tri, int64_t nF, double* out,
                             cudaStream_t stream);

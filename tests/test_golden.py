@@ -1,0 +1,123 @@
+"""Committed golden fixtures (tests/golden/hotpath_v1.npz, made by tools/make_golden.py from the CPU oracle).
+
+* not-gpu: the oracle still reproduces them (pins the oracle against accidental change);
+* gpu: the CUDA path, through the C-ABI shim, reproduces them from the stored INPUTS (no renderer involved).
+The reference itself holds no golden vectors and Open3D is not importable: parity vs real
+Open3D stays unpinned.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+G = np.load(os.path.join(os.path.dirname(__file__), "golden", "hotpath_v1.npz"))
+W, H = int(G["intr"][0]), int(G["intr"][1])
+K = tuple(float(v) for v in G["intr"][2:6])
+VOXEL, TRUNC = float(G["voxel"][0]), float(G["voxel"][1])
+
+
+def canon_mesh(vtx, tri):
+    o = np.lexsort(vtx.T[::-1])
+    inv = np.empty_like(o)
+    inv[o] = np.arange(len(o))
+    t = inv[tri]
+    return vtx[o], t[np.lexsort(t.T[::-1])].astype(np.int32)
+
+
+# ---------------------------------------------------------------------------------------------- oracle vs golden
+def test_oracle_reproduces_golden_unprojection(o3r):
+    d0 = o3r.depth_to_float(G["depth"][0])
+    assert np.array_equal(d0, G["a1_depth_f32"])
+    assert np.array_equal(o3r.rgb_to_intensity(G["rgb"][0]), G["a1_intensity"])
+    xyz, col, idx = o3r.unproject(d0, K, extrinsic=np.linalg.inv(G["poses"][0]), rgb=G["rgb"][0])
+    assert np.array_equal(idx, G["a3_index"]) and np.array_equal(xyz, G["a3_xyz"]) and np.array_equal(col, G["a3_rgb"])
+
+
+def oracle_volume(o3r):
+    vol = o3r.TSDF(VOXEL, TRUNC, 1, parallel_units=True)
+    for i in range(3):
+        vol.integrate(o3r.depth_to_float(G["depth"][i]), K, np.linalg.inv(G["poses"][i]), rgb=G["rgb"][i])
+    return vol
+
+
+def test_oracle_reproduces_golden_tsdf_and_extraction(o3r):
+    vol = oracle_volume(o3r)
+    keys = vol.keys()
+    keys = keys[np.lexsort(keys.T[::-1])]
+    assert np.array_equal(keys, G["a8_keys"])
+    for n, k in enumerate(keys):
+        t, w, _ = vol.unit(k)
+        assert float(t.astype(np.float64).sum()) == G["a9_tsdf_sum"][n] and float(w.astype(np.float64).sum()) == G["a9_weight_sum"][n]
+    for j, n in enumerate(G["a9_sel"]):
+        t, w, c = vol.unit(keys[n])
+        assert np.array_equal(t, G["a9_tsdf"][j]) and np.array_equal(w, G["a9_weight"][j])
+        assert np.array_equal(c.astype(np.float32), G["a9_rgb"][j])
+    pts, _, nrm, _ = vol.extract_points()
+    o = np.lexsort(pts.T[::-1])
+    assert np.array_equal(pts[o], G["a10_xyz"]) and np.allclose(nrm[o], G["a10_nrm"], atol=1e-12)
+    vtx, _, tri, _ = vol.extract_mesh()
+    v, t = canon_mesh(vtx, tri)
+    assert np.array_equal(v, G["a11_vtx"]) and np.array_equal(t, G["a11_tri"])
+
+
+def test_oracle_reproduces_golden_odometry_and_icp(o3r):
+    g = [o3r.rgb_to_intensity(G["rgb"][i]) for i in range(2)]
+    d = [o3r.depth_to_float(G["depth"][i]) for i in range(2)]
+    for jac in (0, 1):
+        ok, T, info, _ = o3r.odometry(g[1], d[1], g[0], d[0], K, jac_kind=jac)
+        assert int(ok) == int(G["a12_ok_%d" % jac][0])
+        assert np.abs(T - G["a12_T_%d" % jac]).max() <= 1e-9           # OpenMP reduction order may differ
+        assert np.abs(info - G["a12_info_%d" % jac]).max() <= 1e-6 * np.abs(info).max()
+    T, fit, rmse, corr, it = o3r.icp_point_to_plane(G["a13_src"], G["a13_tgt"], G["a13_nrm"], 0.05, G["a13_init"], max_iter=30)
+    assert it == int(G["a13_iters"][0]) and np.abs(T - G["a13_T"]).max() <= 1e-9
+    assert np.array_equal(corr, G["a13_corr"]) and abs(fit - G["a13_fit"][0]) <= 1e-12
+
+
+# ---------------------------------------------------------------------------------------------- CUDA vs golden
+@pytest.mark.gpu
+def test_cuda_reproduces_golden():
+    import azurekinect3dreconstruction_b200 as o3d
+    Ko = o3d.camera.PinholeCameraIntrinsic(W, H, *K)
+    mk = lambda i, intensity=False: o3d.geometry.RGBDImage.create_from_color_and_depth(
+        o3d.geometry.Image(G["rgb"][i]), o3d.geometry.Image(G["depth"][i]), 1000.0, 3.0, intensity)
+    # a1 / a3
+    rgbd = mk(0)
+    assert np.array_equal(np.asarray(rgbd.depth), G["a1_depth_f32"])
+    pcd = o3d.geometry.PointCloud.create_from_rgbd_image(rgbd, Ko, np.linalg.inv(G["poses"][0]))
+    assert np.array_equal(pcd.source_index.cpu().numpy(), G["a3_index"])
+    assert np.array_equal(np.asarray(pcd.points), G["a3_xyz"]) and np.array_equal(np.asarray(pcd.colors), G["a3_rgb"])
+    # a8 / a9
+    vol = o3d.pipelines.integration.ScalableTSDFVolume(VOXEL, TRUNC, o3d.pipelines.integration.TSDFVolumeColorType.RGB8, capacity_units=2048)
+    for i in range(3):
+        vol.integrate(mk(i), Ko, np.linalg.inv(G["poses"][i]))
+    keys, tsdf, wgt, rgb = vol.export_units()
+    keys = keys.cpu().numpy()
+    o = np.lexsort(keys.T[::-1])
+    assert np.array_equal(keys[o], G["a8_keys"])                       # block allocation: bit-exact
+    tsdf, wgt, rgb = tsdf.cpu().numpy()[o], wgt.cpu().numpy()[o], rgb.cpu().numpy()[o]
+    assert np.array_equal(tsdf.astype(np.float64).sum(1), G["a9_tsdf_sum"]) and np.array_equal(wgt.astype(np.float64).sum(1), G["a9_weight_sum"])
+    for j, n in enumerate(G["a9_sel"]):
+        assert np.array_equal(tsdf[n], G["a9_tsdf"][j]) and np.array_equal(wgt[n], G["a9_weight"][j])
+        assert np.abs(rgb[n].T - G["a9_rgb"][j]).max() < 1e-3          # f32 running mean vs the oracle's f64
+    # a10 / a11
+    pc = vol.extract_point_cloud()
+    pts = np.asarray(pc.points)
+    o = np.lexsort(pts.T[::-1])
+    assert pts.shape == G["a10_xyz"].shape and np.abs(pts[o] - G["a10_xyz"]).max() <= 1e-4 * VOXEL
+    mesh = vol.extract_triangle_mesh()
+    v, t = canon_mesh(np.asarray(mesh.vertices), np.asarray(mesh.triangles))
+    assert np.array_equal(t, G["a11_tri"]) and np.abs(v - G["a11_vtx"]).max() <= 1e-4 * VOXEL
+    # a12
+    for jac, J in ((0, o3d.pipelines.odometry.RGBDOdometryJacobianFromColorTerm()), (1, o3d.pipelines.odometry.RGBDOdometryJacobianFromHybridTerm())):
+        ok, T, info = o3d.pipelines.odometry.compute_rgbd_odometry(mk(1, True), mk(0, True), Ko, np.eye(4), J, o3d.pipelines.odometry.OdometryOption())
+        assert int(ok) == int(G["a12_ok_%d" % jac][0])
+        assert np.abs(T[:3, 3] - G["a12_T_%d" % jac][:3, 3]).max() <= 1e-6
+        R = T[:3, :3] @ G["a12_T_%d" % jac][:3, :3].T
+        assert np.arccos(np.clip((np.trace(R) - 1) / 2, -1, 1)) <= 1e-6
+    # a13
+    s, tg = o3d.geometry.PointCloud(G["a13_src"]), o3d.geometry.PointCloud(G["a13_tgt"])
+    tg.normals = o3d.utility.Vector3dVector(G["a13_nrm"])
+    res = o3d.pipelines.registration.registration_icp(s, tg, 0.05, G["a13_init"], o3d.pipelines.registration.TransformationEstimationPointToPlane(),
+                                                       o3d.pipelines.registration.ICPConvergenceCriteria(max_iteration=30))
+    assert np.abs(res.transformation - G["a13_T"]).max() <= 1e-6 and abs(res.fitness - G["a13_fit"][0]) <= 1e-9

@@ -1,0 +1,79 @@
+"""Host-side logic of the multi-GPU path on CPU: world_size-2 gloo process group.
+The kernels are exercised on the GPU in test_gpu_parity.py::test_sharded_extraction_equals_single."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from azurekinect3dreconstruction_b200 import _lib
+from azurekinect3dreconstruction_b200.pipelines import sharded
+
+
+def free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        comm = sharded.Comm()
+        assert (comm.rank, comm.world) == (rank, world)
+        # ragged gather (rank 0: 3 rows, rank 1: 0 rows) of a 2-D int tensor and a 1-D float tensor
+        a = torch.arange(6, dtype=torch.int32).reshape(3, 2) + 100 * rank if rank == 0 else torch.zeros((0, 2), dtype=torch.int32)
+        got = comm.all_gather_v(a)
+        assert [g.shape[0] for g in got] == [3, 0] and torch.equal(got[0], torch.arange(6, dtype=torch.int32).reshape(3, 2))
+        b = torch.full((rank + 2,), float(rank), dtype=torch.float64)
+        got = comm.all_gather_v(b)
+        assert [g.shape[0] for g in got] == [2, 3] and float(got[1].sum()) == 3.0
+        # mesh merge: each rank contributes vertices [base, base+n) in rank-major global numbering
+        n = 4 + rank
+        base = 0 if rank == 0 else 4
+        vtx = torch.arange(3 * n, dtype=torch.float64).reshape(n, 3) + 1000 * rank
+        tri = torch.tensor([[base, base + 1, (base + n) % 9]], dtype=torch.int32)      # may reference the other rank
+        parts = [comm.all_gather_v(vtx), comm.all_gather_v(tri)]
+        mesh = sharded.merge_mesh_parts(parts)
+        V, F = np.asarray(mesh.vertices), np.asarray(mesh.triangles)
+        assert V.shape == (9, 3) and F.shape == (2, 3) and V[4, 0] == 1000.0 and F[1, 0] == 4
+        # every unit key has exactly one owner; the two ranks partition a key block evenly enough
+        keys = [(x, y, z) for x in range(-6, 6) for y in range(-3, 3) for z in range(-6, 6)]
+        mine = sum(1 for k in keys if sharded.unit_owner(k, world) == rank)
+        cnt = torch.tensor([mine], dtype=torch.int64)
+        dist.all_reduce(cnt)
+        assert int(cnt.item()) == len(keys) and 0.35 * len(keys) < mine < 0.65 * len(keys)
+        q.put((rank, "ok"))
+    except Exception as e:  # pragma: no cover
+        q.put((rank, repr(e)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gloo_world2_gather_merge_and_ownership():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(60)
+    assert res == {0: "ok", 1: "ok"}, res
+
+
+def test_unit_owner_python_mirror_matches_library():
+    lib = _lib.load()
+    rng = np.random.default_rng(5)
+    for world in (1, 2, 3, 4, 8):
+        for k in rng.integers(-5000, 5000, size=(200, 3)):
+            assert lib.b2r_unit_owner(int(k[0]), int(k[1]), int(k[2]), world) == sharded.unit_owner(k, world)
+    assert lib.b2r_unit_owner(1 << 21, 0, 0, 4) == -1
