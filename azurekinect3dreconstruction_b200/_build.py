@@ -43,12 +43,15 @@ def _stale(target: str, deps) -> bool:
 def build_cuda(force: bool = False, verbose: bool = False) -> str:
     srcs = [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
     deps = srcs + [os.path.join(CSRC, h) for h in HEADERS] + [os.path.abspath(__file__)]
-    if not force and not _stale(LIB, deps):
+    if not force and not _stale(LIB, deps) and not os.environ.get("B2R_LIB_OUT"):
         return LIB
     env = dict(os.environ)
     # the image exports CC/CXX pointing at a wrapper without libgomp specs; use the system compiler
     ccbin = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
-    cmd = [_nvcc(), "-ccbin", ccbin] + NVCC_FLAGS + ["-I", CSRC, "-o", LIB] + srcs
+    # tuning experiments: B2R_EXTRA_DEFS="-DFUSE_MIN_CTAS=2" B2R_LIB_OUT=/path/variant.so (load it with B2R_LIB=...)
+    extra = os.environ.get("B2R_EXTRA_DEFS", "").split()
+    out = os.environ.get("B2R_LIB_OUT", LIB)
+    cmd = [_nvcc(), "-ccbin", ccbin] + NVCC_FLAGS + extra + ["-I", CSRC, "-o", out] + srcs
     res = subprocess.run(cmd, env=env, capture_output=True, text=True)
     log = os.path.join(PKG, "csrc", "build.log")
     with open(log, "w") as f:

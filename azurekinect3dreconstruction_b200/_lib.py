@@ -13,7 +13,7 @@ import numpy as np
 import torch
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libb2recon.so")
+LIB_PATH = os.environ.get("B2R_LIB") or os.path.join(_PKG, "libb2recon.so")   # B2R_LIB: a tuning variant built by _build.py
 
 OK, ERR_BAD_ARG, ERR_CUDA, ERR_CAPACITY, ERR_FORMAT, ERR_SINGULAR, ERR_RANGE = 0, -1, -2, -3, -4, -5, -6
 

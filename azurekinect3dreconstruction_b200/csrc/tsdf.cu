@@ -299,6 +299,9 @@ __global__ void __launch_bounds__(256, 4) tsdf_pack_alloc_kernel(const __grid_co
 // K2: fuse
 // ------------------------------------------------------------------------------------------------
 #define FUSE_THREADS 256
+#ifndef FUSE_MIN_CTAS
+#define FUSE_MIN_CTAS 4   // 64 registers/thread: 32 resident warps per SM (measured best; 3 and 5 are slower)
+#endif
 #define FUSE_MAX_ITEMS 64          // work items resolved per CTA per chunk
 #define FUSE_SLAB 1024             // floats per plane per slab (4 x-layers x 16 x 16)
 
@@ -345,7 +348,7 @@ __device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem
 }
 
 template <int COLOR, int FUSE_STAGES>
-__global__ void __launch_bounds__(FUSE_THREADS, 4) tsdf_fuse_kernel(const __grid_constant__ FuseParams P) {
+__global__ void __launch_bounds__(FUSE_THREADS, FUSE_MIN_CTAS) tsdf_fuse_kernel(const __grid_constant__ FuseParams P) {
     constexpr int PLANES = COLOR ? 5 : 2;
     extern __shared__ __align__(128) unsigned char fuse_smem[];
     float* stage = reinterpret_cast<float*>(fuse_smem);                        // [FUSE_STAGES][PLANES][FUSE_SLAB]
