@@ -19,6 +19,13 @@
 #include "host_math.h"
 
 #define UNP_THREADS 128
+#include <type_traits>
+#include <string.h>
+
+static bool host_div_domain(float b) {   // same test as b2r_div_domain, on the host
+    uint32_t u; memcpy(&u, &b, 4);
+    return ((u >> 23) - 67u) < 120u && (u & 0x7FFFFFu) != 0x7FFFFFu;
+}
 
 struct UnprojParams {
     int W, H, B;               // depth image size, batch
@@ -32,6 +39,8 @@ struct UnprojParams {
     float gfx, gfy, gcx, gcy;  // depth intrinsics (f32) for the gather chain
     float Fx, Fy, Cx, Cy;      // colour intrinsics (f32)
     float d2c[12];             // depth -> colour rigid transform (f32)
+    float rgfx, rgfy, r255;    // RN(1/gfx), RN(1/gfy), RN(1/255): constant divisors go through the Markstein quotient
+    float rscale; int scale_fast;   // RN(1/depth_scale) and whether depth_scale is inside the Markstein domain
     const double* T;           // DEVICE B*16: camera -> output transform (extrinsic^-1, optionally pre-multiplied)
     int valid_only;
     void* xyz; void* rgb; int32_t* src_index; int32_t* gather_index;
@@ -60,7 +69,7 @@ __device__ __forceinline__ void load_depths(const UnprojParams& P, int b, int s0
 #pragma unroll
         for (int k = 0; k < 8; k++) {
             const uint32_t v = (w[k >> 1] >> ((k & 1) * 16)) & 0xFFFFu;
-            float dd = xfdiv((float)v, P.depth_scale);
+            float dd = P.scale_fast ? b2r_div_fast((float)v, P.depth_scale, P.rscale) : xfdiv((float)v, P.depth_scale);
             if (dd >= P.depth_trunc) dd = 0.0f;
             d[k] = dd; pix[k] = s0 + k;
         }
@@ -247,6 +256,190 @@ __global__ void __launch_bounds__(UNP_THREADS) unproject_fill_kernel(const Unpro
         for (int t = threadIdx.x; t < total; t += UNP_THREADS) P.gather_index[obase + t] = s_gidx[t];
 }
 
+// ---- f32 throughput path -------------------------------------------------------------------------------
+// Same integer results (validity, raster order, gather indices) and the same IEEE-rounded camera-space
+// x, y, colours as the generic kernel, but: constant divisors (fx, fy, 255) use a host-computed RN(1/b) + the
+// Markstein correction (3 instructions, bit-identical to div.rn for these operand ranges), the u/v projection
+// shares one reciprocal, all 8 colour gathers of a thread are in flight together, the output transform uses
+// FMAs (f32 mode promises a few ulp, not bit parity), and the compacted chunk leaves shared memory as
+// 128-bit stores whose alignment phase matches the global destination.
+// CMODE: 0 no colour, 1 f32 gray, 3 / 4 u8 channels.  GATHER: colour lives in its own camera.
+template <int CMODE, bool GATHER>
+__global__ void __launch_bounds__(UNP_THREADS) unproject_fill_f32_kernel(const __grid_constant__ UnprojParams P) {
+    constexpr int PPT = 8, CHUNK = UNP_THREADS * PPT;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float* s_xyz = reinterpret_cast<float*>(smem_raw);            // CHUNK*3 + 4
+    float* s_rgb = s_xyz + CHUNK * 3 + 4;                          // CHUNK*3 + 4
+    int32_t* s_idx = reinterpret_cast<int32_t*>(s_rgb + CHUNK * 3 + 4);   // CHUNK + 4
+    int32_t* s_gidx = s_idx + CHUNK + 4;                           // CHUNK + 4
+    __shared__ int ws[UNP_THREADS / 32];
+
+    const int b = blockIdx.y, chunk = blockIdx.x;
+    const int s0 = (chunk * UNP_THREADS + threadIdx.x) * PPT;
+    float d[PPT]; int pix[PPT];
+    const bool fast_u16 = P.scale_fast && P.stride == 1 && P.depth_is_u16 && ((P.W * P.H) % 8 == 0) && s0 + 8 <= P.n_samples;
+    if (fast_u16) {
+        // RN(v / depth_scale) through the host-computed RN(1/depth_scale) + Markstein correction (== div.rn here)
+        const uint4 raw = __ldg(reinterpret_cast<const uint4*>((const uint16_t*)P.depth + (size_t)b * P.W * P.H + s0));
+        const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const uint32_t v = (w[k >> 1] >> ((k & 1) * 16)) & 0xFFFFu;
+            float dd = b2r_div_fast((float)v, P.depth_scale, P.rscale);
+            if (dd >= P.depth_trunc) dd = 0.0f;
+            d[k] = dd; pix[k] = s0 + k;
+        }
+    } else {
+        load_depths<PPT>(P, b, s0, d, pix);
+    }
+    unsigned m = 0;
+#pragma unroll
+    for (int k = 0; k < PPT; k++)
+        if (pix[k] >= 0 && (d[k] > 0.0f || !P.valid_only)) m |= 1u << k;
+    const int cnt = __popc(m);
+    int incl = cnt;
+    for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, o); if ((threadIdx.x & 31) >= o) incl += t; }
+    if ((threadIdx.x & 31) == 31) ws[threadIdx.x >> 5] = incl;
+    const int64_t off = (int64_t)P.chunk_offsets[b * P.n_chunks + chunk];
+    __syncthreads();
+    int wbase = 0, total = 0;
+#pragma unroll
+    for (int i = 0; i < UNP_THREADS / 32; i++) { if (i < (int)(threadIdx.x >> 5)) wbase += ws[i]; total += ws[i]; }
+    int rank = wbase + incl - cnt;
+    const int64_t obase = (int64_t)b * P.capacity + off;
+    const int ph3 = (int)((obase * 3) & 3), ph1 = (int)(obase & 3);     // alignment phase of the destinations (floats / ints)
+
+    const double* Td = P.T + (size_t)b * 16;
+    float T[12];
+#pragma unroll
+    for (int i = 0; i < 12; i++) T[i] = (float)__ldg(Td + i);
+    const float nanv = __int_as_float(0x7fc00000);
+    // pass 1: camera-space point + gather index.  (i, j) of the first pixel by one division, then incremental
+    // when the thread's pixels are consecutive (stride 1).
+    float X[PPT], Y[PPT];
+    int gi[PPT];
+    int ci = 0, cj = 0;
+    if (P.stride == 1 && pix[0] >= 0) { ci = pix[0] / P.W; cj = pix[0] - ci * P.W; }
+#pragma unroll
+    for (int k = 0; k < PPT; k++) {
+        int i = ci, j = cj;
+        if (P.stride == 1) { if (++cj == P.W) { cj = 0; ci++; } }
+        X[k] = Y[k] = nanv; gi[k] = -1;
+        if (!(m & (1u << k)) || !(d[k] > 0.0f)) continue;
+        const int p = pix[k];
+        if (P.stride != 1) { i = p / P.W; j = p - i * P.W; }
+        const float z = d[k];
+        X[k] = b2r_div_fast(xfmul(xfsub((float)j, P.gcx), z), P.gfx, P.rgfx);
+        Y[k] = b2r_div_fast(xfmul(xfsub((float)i, P.gcy), z), P.gfy, P.rgfy);
+        gi[k] = p;
+        if (GATHER) {
+            gi[k] = -1;
+            const float Xc = xfadd(xfadd(xfadd(xfmul(P.d2c[0], X[k]), xfmul(P.d2c[1], Y[k])), xfmul(P.d2c[2], z)), P.d2c[3]);
+            const float Yc = xfadd(xfadd(xfadd(xfmul(P.d2c[4], X[k]), xfmul(P.d2c[5], Y[k])), xfmul(P.d2c[6], z)), P.d2c[7]);
+            const float Zc = xfadd(xfadd(xfadd(xfmul(P.d2c[8], X[k]), xfmul(P.d2c[9], Y[k])), xfmul(P.d2c[10], z)), P.d2c[11]);
+            if (Zc > 0.0f) {
+                float qu, qv;
+                const float au = xfmul(Xc, P.Fx), av = xfmul(Yc, P.Fy);
+                if (__builtin_expect(b2r_div_domain(Zc), 1)) { const float inv = b2r_rcp_markstein(Zc); qu = b2r_div_fast(au, Zc, inv); qv = b2r_div_fast(av, Zc, inv); }
+                else { qu = xfdiv(au, Zc); qv = xfdiv(av, Zc); }
+                const float uf = xfadd(xfadd(qu, P.Cx), 0.5f), vf = xfadd(xfadd(qv, P.Cy), 0.5f);
+                const int uc = (int)floorf(uf), vc = (int)floorf(vf);
+                if ((unsigned)uc < (unsigned)P.Wc && (unsigned)vc < (unsigned)P.Hc) gi[k] = vc * P.Wc + uc;
+            }
+        }
+    }
+    // pass 2: all colour gathers in flight together
+    uint32_t cw[PPT];
+    const size_t cbase = (size_t)b * (GATHER ? (size_t)P.Wc * P.Hc : (size_t)P.W * P.H);
+#pragma unroll
+    for (int k = 0; k < PPT; k++) {
+        cw[k] = 0;
+        if (CMODE != 0 && (m & (1u << k))) {
+            if (CMODE == 4) { if (gi[k] >= 0) cw[k] = __ldg(reinterpret_cast<const uint32_t*>(P.color) + cbase + gi[k]); }
+            else if (CMODE == 3) { if (gi[k] >= 0) { const uint8_t* c = P.color + (cbase + gi[k]) * 3; cw[k] = (uint32_t)__ldg(c) | ((uint32_t)__ldg(c + 1) << 8) | ((uint32_t)__ldg(c + 2) << 16); } }
+            else cw[k] = __float_as_uint(__ldg(P.gray + (size_t)b * P.W * P.H + pix[k]));
+        }
+    }
+    // pass 3: output transform, stage in shared memory at the destination's alignment phase
+    const uint32_t sel = P.color_bgr ? 0x4012u : 0x4210u;   // PRMT selector: swap bytes 0 and 2 (BGR) or keep; byte 3 cleared
+#pragma unroll
+    for (int k = 0; k < PPT; k++) {
+        if (!(m & (1u << k))) continue;
+        float ox = nanv, oy = nanv, oz = nanv;
+        if (d[k] > 0.0f) {
+            const float z = d[k];
+            ox = __fmaf_rn(T[0], X[k], __fmaf_rn(T[1], Y[k], __fmaf_rn(T[2], z, T[3])));
+            oy = __fmaf_rn(T[4], X[k], __fmaf_rn(T[5], Y[k], __fmaf_rn(T[6], z, T[7])));
+            oz = __fmaf_rn(T[8], X[k], __fmaf_rn(T[9], Y[k], __fmaf_rn(T[10], z, T[11])));
+        }
+        float* q = s_xyz + ph3 + 3 * rank;
+        q[0] = ox; q[1] = oy; q[2] = oz;
+        if (P.src_index) s_idx[ph1 + rank] = pix[k];
+        if (P.gather_index) s_gidx[ph1 + rank] = gi[k];
+        if (CMODE != 0) {
+            float r = 0.f, g = 0.f, bl = 0.f;
+            if (CMODE >= 3) {
+                if (gi[k] >= 0) {
+                    const uint32_t c = __byte_perm(cw[k], 0, sel);
+                    r = b2r_div_fast((float)(c & 255u), 255.0f, P.r255);
+                    g = b2r_div_fast((float)((c >> 8) & 255u), 255.0f, P.r255);
+                    bl = b2r_div_fast((float)(c >> 16), 255.0f, P.r255);
+                }
+            } else {
+                r = g = bl = __uint_as_float(cw[k]);
+            }
+            float* qc = s_rgb + ph3 + 3 * rank;
+            qc[0] = r; qc[1] = g; qc[2] = bl;
+        }
+        rank++;
+    }
+    __syncthreads();
+    // ---- write-out: scalar head up to 16-byte alignment, 128-bit body (fully unrolled), scalar tail
+    if (off + total > P.capacity) total = (int)max((int64_t)0, P.capacity - off);
+    auto copy_out = [&](float* g, const float* s, int n, int ph, auto max_vec) {   // g[t] = s[ph + t]; (g + t) is 16B-aligned when (ph + t) % 4 == 0
+        constexpr int ITERS = (decltype(max_vec)::value + UNP_THREADS - 1) / UNP_THREADS;
+        const int head = min(n, (4 - ph) & 3);
+        if ((int)threadIdx.x < head) g[threadIdx.x] = s[ph + threadIdx.x];
+        const int nv = (n - head) >> 2;
+        const float4* sv = reinterpret_cast<const float4*>(s + ph + head);
+        float4* gv = reinterpret_cast<float4*>(g + head);
+#pragma unroll
+        for (int it = 0; it < ITERS; it++) {
+            const int t = threadIdx.x + it * UNP_THREADS;
+            if (t < nv) gv[t] = sv[t];
+        }
+        const int t = head + (nv << 2) + threadIdx.x;
+        if (t < n) g[t] = s[ph + t];
+    };
+    copy_out(reinterpret_cast<float*>(P.xyz) + obase * 3, s_xyz, total * 3, ph3, std::integral_constant<int, CHUNK * 3 / 4>());
+    if (CMODE != 0) copy_out(reinterpret_cast<float*>(P.rgb) + obase * 3, s_rgb, total * 3, ph3, std::integral_constant<int, CHUNK * 3 / 4>());
+    if (P.src_index) copy_out(reinterpret_cast<float*>(P.src_index) + obase, reinterpret_cast<const float*>(s_idx), total, ph1, std::integral_constant<int, CHUNK / 4>());
+    if (P.gather_index) copy_out(reinterpret_cast<float*>(P.gather_index) + obase, reinterpret_cast<const float*>(s_gidx), total, ph1, std::integral_constant<int, CHUNK / 4>());
+}
+
+template <int CMODE, bool GATHER>
+static int launch_fill_f32_t(const UnprojParams& P, cudaStream_t stream) {
+    constexpr int CHUNK = UNP_THREADS * 8;
+    const size_t smem = (size_t)(CHUNK * 3 + 4) * 4 * 2 + (size_t)(CHUNK + 4) * 4 * 2;
+    static bool attr_set = false;
+    if (!attr_set) {
+        B2R_CUDA(cudaFuncSetAttribute(unproject_fill_f32_kernel<CMODE, GATHER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    dim3 grid(P.n_chunks, P.B);
+    unproject_fill_f32_kernel<CMODE, GATHER><<<grid, UNP_THREADS, smem, stream>>>(P);
+    B2R_CHECK_LAUNCH();
+    return B2R_OK;
+}
+
+static int launch_fill_f32(const UnprojParams& P, cudaStream_t stream) {
+    const int cmode = (P.rgb && P.color) ? P.color_channels : ((P.rgb && P.gray) ? 1 : 0);
+    if (cmode == 4) return P.gather ? launch_fill_f32_t<4, true>(P, stream) : launch_fill_f32_t<4, false>(P, stream);
+    if (cmode == 3) return P.gather ? launch_fill_f32_t<3, true>(P, stream) : launch_fill_f32_t<3, false>(P, stream);
+    if (cmode == 1) return launch_fill_f32_t<1, false>(P, stream);
+    return launch_fill_f32_t<0, false>(P, stream);
+}
+
 template <typename OutT, int PPT>
 static int launch_fill(const UnprojParams& P, cudaStream_t stream) {
     constexpr int CHUNK = UNP_THREADS * PPT;
@@ -300,6 +493,8 @@ B2R_API int b2r_unproject(const void* depth, int depth_is_u16, float depth_scale
     }
     P.fx = depth_K[0]; P.fy = depth_K[1]; P.cx = depth_K[2]; P.cy = depth_K[3];
     P.gfx = (float)depth_K[0]; P.gfy = (float)depth_K[1]; P.gcx = (float)depth_K[2]; P.gcy = (float)depth_K[3];
+    P.rgfx = 1.0f / P.gfx; P.rgfy = 1.0f / P.gfy; P.r255 = 1.0f / 255.0f;   // host IEEE division: correctly rounded reciprocals
+    P.rscale = 1.0f / depth_scale; P.scale_fast = host_div_domain(depth_scale) ? 1 : 0;
     if (P.gather) {
         P.Fx = (float)color_K[0]; P.Fy = (float)color_K[1]; P.Cx = (float)color_K[2]; P.Cy = (float)color_K[3];
         for (int i = 0; i < 12; i++) P.d2c[i] = (float)d2c_host[i];
@@ -315,7 +510,7 @@ B2R_API int b2r_unproject(const void* depth, int depth_is_u16, float depth_scale
     unproject_scan_kernel<<<B, 1024, 0, stream>>>(P);
     B2R_CHECK_LAUNCH();
     if (out_f64) return launch_fill<double, 4>(P, stream);
-    return launch_fill<float, 8>(P, stream);
+    return launch_fill_f32(P, stream);
 }
 
 // ---- a5: pcd.transform(T) on device arrays (f64 or f32 points, optional normals) ---------------

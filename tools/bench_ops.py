@@ -1,0 +1,179 @@
+#!/usr/bin/env python3
+"""Secondary measurements for the SURVEY 8(a) rows that are not the headline metric (bench.py is the contract):
+unprojection (configs[0]/[1]), extraction (configs[2] tail), odometry + ICP (configs[3]).  CUDA-event timing,
+warm-up first, inputs larger than L2 where the op streams.  Prints one JSON object.
+
+    python tools/bench_ops.py [--frames 64] [--pairs 20] [--cpu]
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import azurekinect3dreconstruction_b200 as o3d  # noqa: E402
+from azurekinect3dreconstruction_b200 import geometry, synthetic as syn  # noqa: E402
+
+
+def ev_time(fn, iters=5, warm=2):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--frames", type=int, default=64)
+    ap.add_argument("--batch", type=int, default=256)
+    ap.add_argument("--pairs", type=int, default=20)
+    ap.add_argument("--only-unproject", action="store_true")
+    ap.add_argument("--cpu", action="store_true", help="also time the CPU oracle on bounded samples")
+    a = ap.parse_args()
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+    out = {"hbm_peak_gbs": peak}
+    kin = syn.SyntheticKinect(seed=0, dropout=0.02, noise_sigma_mm=1.0, device="cuda")
+    poses = syn.orbit_trajectory(300)
+    di, ci = kin.depth_intr, kin.color_intr
+    Kd = o3d.camera.PinholeCameraIntrinsic(di["width"], di["height"], di["fx"], di["fy"], di["cx"], di["cy"])
+    Kc = o3d.camera.PinholeCameraIntrinsic(ci["width"], ci["height"], ci["fx"], ci["fy"], ci["cx"], ci["cy"])
+    H, W = di["height"], di["width"]
+
+    # ---- a1+a3..a6: unprojection, batch of B Kinect captures (native depth + 720p BGRA, colour gathered to depth)
+    nsrc = 8
+    caps = [kin.render_pose(poses[i * 30], want_transformed_depth=False) for i in range(nsrc)]
+    B = a.batch
+    depth = torch.stack([torch.from_numpy(np.ascontiguousarray(caps[i % nsrc].depth).view(np.int16)).to(dev) for i in range(B)]).contiguous().view(torch.uint16)
+    color = torch.stack([torch.as_tensor(caps[i % nsrc].color).to(dev) for i in range(B)]).contiguous()
+    d2c = kin.d2c
+    flip = np.diag([1.0, -1.0, -1.0, 1.0])
+    T = np.stack([flip @ poses[(i * 30) % 300] for i in range(B)])
+
+    def unp_gather(b=B):
+        return geometry.unproject(depth[:b], Kd, depth_is_u16=True, depth_scale=1000.0, depth_trunc=3.0, color=color[:b], color_bgr=True,
+                                  color_intrinsic=Kc, depth_to_color=d2c, transforms=T[:b], dtype=torch.float32)
+    r = unp_gather()
+    n_valid = float(r["counts"].sum().item()) / B
+    ms = ev_time(unp_gather, iters=5)
+    algo = 2.0 * W * H + 4.0 * n_valid + 24.0 * n_valid
+    out["unproject_kinect_gather_f32"] = {"batch": B, "ms_per_launch_sequence": ms, "frames_per_s": B / (ms * 1e-3), "valid_points_per_frame": n_valid,
+                                          "algorithmic_bytes_per_frame": algo, "achieved_gbs": algo * B / (ms * 1e-3) / 1e9,
+                                          "frac_of_measured_hbm": algo * B / (ms * 1e-3) / 1e9 / peak}
+    ms1 = ev_time(lambda: unp_gather(1), iters=50, warm=5)
+    ms2 = ev_time(lambda: unp_gather(2), iters=50, warm=5)
+    out["unproject_kinect_gather_f32"]["latency_ms_B1"] = ms1
+    out["two_camera_fusion_config2"] = {"ms_per_tick_B2": ms2, "ticks_per_s": 1e3 / ms2, "sensor_rate_hz": 30}
+    # aligned colour, f64 output (bit-exact upstream chain)
+    dal, cal = [], []
+    for i in range(nsrc):
+        d, c = kin.render_depth_aligned_rgb(poses[i * 30])
+        dal.append(d.view(torch.int16).to(dev)); cal.append(c.to(dev))
+    Bd = min(B, 64)
+    d64 = torch.stack([dal[i % nsrc] for i in range(Bd)]).contiguous().view(torch.uint16)
+    c64 = torch.stack([cal[i % nsrc] for i in range(Bd)]).contiguous()
+
+    def unp_f64():
+        return geometry.unproject(d64, Kd, depth_is_u16=True, depth_scale=1000.0, depth_trunc=3.0,
+                                  color=c64, dtype=torch.float64)
+    ms = ev_time(unp_f64, iters=5)
+    out["unproject_aligned_f64"] = {"batch": Bd, "ms": ms, "frames_per_s": Bd / (ms * 1e-3)}
+    del depth, color, r
+    torch.cuda.empty_cache()
+    if a.only_unproject:
+        print(json.dumps(out, indent=1))
+        return
+
+    # ---- a10/a11: extraction after integrating --frames frames at 4 mm / 2 cm
+    TT = o3d.pipelines.integration.TSDFVolumeColorType
+    vol = o3d.pipelines.integration.ScalableTSDFVolume(0.004, 0.02, TT.RGB8, capacity_units=40000)
+    F = a.frames
+    fr = [kin.render_depth_aligned_rgb(poses[i]) for i in range(F)]
+    dd = torch.stack([f[0].view(torch.int16).to(dev) for f in fr]).contiguous().view(torch.uint16)
+    cc = torch.stack([f[1].to(dev) for f in fr]).contiguous()
+    E = np.stack([np.linalg.inv(poses[i]) for i in range(F)])
+    vol.integrate_raw(dd, cc, Kd, E, 1000.0, 3.0)
+    units = vol.num_units()
+    mesh = vol.extract_triangle_mesh()
+    V, Fc = len(mesh.vertices), len(mesh.triangles)
+    ms_mesh = ev_time(lambda: vol.extract_triangle_mesh(), iters=3, warm=1)
+    pc = vol.extract_point_cloud()
+    Kp = len(pc.points)
+    ms_pts = ev_time(lambda: vol.extract_point_cloud(), iters=3, warm=1)
+    ms_nrm = ev_time(lambda: mesh.compute_vertex_normals(), iters=3, warm=1)
+    nvox = units * 4096.0
+    algo_mesh = 8.0 * nvox + 24.0 * V + 24.0 * V + 12.0 * Fc
+    algo_pts = 8.0 * nvox + 24.0 * Kp + 36.0 * Kp
+    out["extract_triangle_mesh"] = {"units": units, "vertices": V, "triangles": Fc, "ms": ms_mesh, "algorithmic_bytes": algo_mesh,
+                                    "achieved_gbs": algo_mesh / (ms_mesh * 1e-3) / 1e9, "frac_of_measured_hbm": algo_mesh / (ms_mesh * 1e-3) / 1e9 / peak,
+                                    "note": "two-call protocol: count + fill passes both inside ms (f64 outputs)"}
+    out["extract_point_cloud"] = {"points": Kp, "ms": ms_pts, "algorithmic_bytes": algo_pts, "achieved_gbs": algo_pts / (ms_pts * 1e-3) / 1e9}
+    out["compute_vertex_normals"] = {"ms": ms_nrm}
+
+    # ---- a12/a13: odometry + ICP over consecutive pairs
+    mk = lambda i: o3d.geometry.RGBDImage.create_from_color_and_depth(o3d.geometry.Image(cc[i]), o3d.geometry.Image(dd[i]), 1000.0, 3.0, True)
+    imgs = [mk(i) for i in range(min(F, a.pairs + 1))]
+    opt = o3d.pipelines.odometry.OdometryOption(iteration_number_per_pyramid_level=o3d.utility.IntVector([20, 10, 5]), max_depth_diff=0.03, min_depth=0.0, max_depth=4.0)
+    J = o3d.pipelines.odometry.RGBDOdometryJacobianFromHybridTerm()
+    res = []
+
+    def odo():
+        res.clear()
+        for i in range(len(imgs) - 1):
+            res.append(o3d.pipelines.odometry.compute_rgbd_odometry(imgs[i + 1], imgs[i], Kd, np.eye(4), J, opt))
+    t0 = time.perf_counter(); odo(); torch.cuda.synchronize(); t_first = time.perf_counter() - t0
+    t0 = time.perf_counter(); odo(); torch.cuda.synchronize(); t_odo = time.perf_counter() - t0
+    errs = []
+    for i, (ok, T_, _) in enumerate(res):
+        gt = np.linalg.inv(poses[i]) @ poses[i + 1]
+        errs.append(float(np.linalg.norm(T_[:3, 3] - gt[:3, 3])))
+    out["rgbd_odometry_hybrid"] = {"pairs": len(res), "ms_per_pair": 1e3 * t_odo / max(1, len(res)), "pairs_per_s": len(res) / t_odo, "all_ok": all(r[0] for r in res),
+                                   "median_translation_error_m_vs_ground_truth": float(np.median(errs)), "first_call_s": t_first}
+    from _helpers import image_normals
+    p_src = o3d.geometry.PointCloud.create_from_depth_image(o3d.geometry.Image(dd[1]), Kd, depth_scale=1000.0, depth_trunc=3.0, stride=4)
+    p_tgt = o3d.geometry.PointCloud.create_from_depth_image(o3d.geometry.Image(dd[0]), Kd, depth_scale=1000.0, depth_trunc=3.0, stride=4)
+    d0 = (dd[0]).cpu().numpy().astype(np.float32) / 1000.0
+    d0[d0 >= 3.0] = 0
+    p_tgt.normals = o3d.utility.Vector3dVector(image_normals(d0, (di["fx"], di["fy"], di["cx"], di["cy"]), stride=4))
+    crit = o3d.pipelines.registration.ICPConvergenceCriteria(max_iteration=100)
+    est = o3d.pipelines.registration.TransformationEstimationPointToPlane()
+    icp = lambda: o3d.pipelines.registration.registration_icp(p_src, p_tgt, 0.03, np.eye(4), est, crit)
+    r_icp = icp()
+    t0 = time.perf_counter(); r_icp = icp(); torch.cuda.synchronize(); t_icp = time.perf_counter() - t0
+    out["icp_point_to_plane"] = {"source_points": len(p_src.points), "target_points": len(p_tgt.points), "iterations": int(r_icp.num_iterations), "ms": 1e3 * t_icp,
+                                 "fitness": float(r_icp.fitness), "inlier_rmse": float(r_icp.inlier_rmse)}
+
+    if a.cpu:   # bounded CPU-oracle samples (reported baseline only)
+        from oracle import o3r
+        Kt = (di["fx"], di["fy"], di["cx"], di["cy"])
+        dn = (dd[0]).cpu().numpy()
+        cn = cc[0].cpu().numpy()
+        t0 = time.perf_counter(); o3r.unproject(o3r.depth_to_float(dn), Kt, rgb=cn); t_u = time.perf_counter() - t0
+        g = [o3r.rgb_to_intensity(cc[i].cpu().numpy()) for i in range(2)]
+        df = [o3r.depth_to_float((dd[i]).cpu().numpy()) for i in range(2)]
+        t0 = time.perf_counter(); o3r.odometry(g[1], df[1], g[0], df[0], Kt, jac_kind=1); t_o = time.perf_counter() - t0
+        cv = o3r.TSDF(0.004, 0.02, 1, parallel_units=True)
+        nf = min(F, 8)
+        for i in range(nf):
+            cv.integrate(o3r.depth_to_float((dd[i]).cpu().numpy()), Kt, E[i], rgb=cc[i].cpu().numpy())
+        t0 = time.perf_counter(); vtx, _, tri, _ = cv.extract_mesh(); t_m = time.perf_counter() - t0
+        out["cpu_oracle"] = {"cores": o3r.num_threads(), "unproject_one_frame_ms": 1e3 * t_u, "odometry_one_pair_ms": 1e3 * t_o,
+                             "extract_mesh_ms": 1e3 * t_m, "extract_mesh_units": cv.num_units(), "extract_mesh_vertices": int(len(vtx)), "kind": "port"}
+    print(json.dumps(out, indent=1))
+
+
+if __name__ == "__main__":
+    main()
