@@ -40,7 +40,9 @@ struct UnprojParams {
     float Fx, Fy, Cx, Cy;      // colour intrinsics (f32)
     float d2c[12];             // depth -> colour rigid transform (f32)
     float rgfx, rgfy, r255;    // RN(1/gfx), RN(1/gfy), RN(1/255): constant divisors go through the Markstein quotient
-    float rscale; int scale_fast;   // RN(1/depth_scale) and whether depth_scale is inside the Markstein domain
+    float rscale; int scale_fast;
+    int u16_count_fast;        // depth_scale > 0: the integer validity test below is equivalent
+    uint32_t u16_vmax;         // largest raw u16 depth that survives the conversion (RN(v/scale) < trunc); valid <=> 1 <= v <= vmax   // RN(1/depth_scale) and whether depth_scale is inside the Markstein domain
     const double* T;           // DEVICE B*16: camera -> output transform (extrinsic^-1, optionally pre-multiplied)
     int valid_only;
     void* xyz; void* rgb; int32_t* src_index; int32_t* gather_index;
@@ -90,11 +92,22 @@ template <int PPT>
 __global__ void __launch_bounds__(UNP_THREADS) unproject_count_kernel(const UnprojParams P) {
     const int b = blockIdx.y, chunk = blockIdx.x;
     const int s0 = (chunk * UNP_THREADS + threadIdx.x) * PPT;
-    float d[PPT]; int pix[PPT];
-    load_depths<PPT>(P, b, s0, d, pix);
     int c = 0;
+    if (PPT == 8 && P.u16_count_fast && P.stride == 1 && P.depth_is_u16 && ((P.W * P.H) % 8 == 0) && s0 + 8 <= P.n_samples) {
+        // integer-only validity: RN(v/scale) is monotone in v, so "0 < d < trunc" is "1 <= v <= vmax" (vmax from the host)
+        const uint4 raw = __ldg(reinterpret_cast<const uint4*>((const uint16_t*)P.depth + (size_t)b * P.W * P.H + s0));
+        const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
 #pragma unroll
-    for (int k = 0; k < PPT; k++) c += (pix[k] >= 0 && (d[k] > 0.0f || !P.valid_only)) ? 1 : 0;
+        for (int k = 0; k < 8; k++) {
+            const uint32_t v = (w[k >> 1] >> ((k & 1) * 16)) & 0xFFFFu;
+            c += (!P.valid_only || (v - 1u) < P.u16_vmax) ? 1 : 0;
+        }
+    } else {
+        float d[PPT]; int pix[PPT];
+        load_depths<PPT>(P, b, s0, d, pix);
+#pragma unroll
+        for (int k = 0; k < PPT; k++) c += (pix[k] >= 0 && (d[k] > 0.0f || !P.valid_only)) ? 1 : 0;
+    }
     for (int o = 16; o > 0; o >>= 1) c += __shfl_down_sync(0xffffffffu, c, o);
     __shared__ int ws[UNP_THREADS / 32];
     if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = c;
@@ -264,13 +277,13 @@ __global__ void __launch_bounds__(UNP_THREADS) unproject_fill_kernel(const Unpro
 // FMAs (f32 mode promises a few ulp, not bit parity), and the compacted chunk leaves shared memory as
 // 128-bit stores whose alignment phase matches the global destination.
 // CMODE: 0 no colour, 1 f32 gray, 3 / 4 u8 channels.  GATHER: colour lives in its own camera.
-template <int CMODE, bool GATHER>
+template <int CMODE, bool GATHER, bool WANT_IDX>
 __global__ void __launch_bounds__(UNP_THREADS) unproject_fill_f32_kernel(const __grid_constant__ UnprojParams P) {
     constexpr int PPT = 8, CHUNK = UNP_THREADS * PPT;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* s_xyz = reinterpret_cast<float*>(smem_raw);            // CHUNK*3 + 4
-    float* s_rgb = s_xyz + CHUNK * 3 + 4;                          // CHUNK*3 + 4
-    int32_t* s_idx = reinterpret_cast<int32_t*>(s_rgb + CHUNK * 3 + 4);   // CHUNK + 4
+    float* s_rgb = s_xyz + CHUNK * 3 + 4;                          // CHUNK*3 + 4 (absent when CMODE == 0)
+    int32_t* s_idx = reinterpret_cast<int32_t*>(s_rgb + (CMODE != 0 ? CHUNK * 3 + 4 : 0));   // CHUNK + 4 (WANT_IDX only)
     int32_t* s_gidx = s_idx + CHUNK + 4;                           // CHUNK + 4
     __shared__ int ws[UNP_THREADS / 32];
 
@@ -318,16 +331,17 @@ __global__ void __launch_bounds__(UNP_THREADS) unproject_fill_f32_kernel(const _
     // when the thread's pixels are consecutive (stride 1).
     float X[PPT], Y[PPT];
     int gi[PPT];
+    // rows_ok: the thread's 8 consecutive pixels never straddle a row (stride 1, W % 8 == 0): one division per thread
+    const bool rows_ok = P.stride == 1 && (P.W & 7) == 0 && pix[0] >= 0;
     int ci = 0, cj = 0;
-    if (P.stride == 1 && pix[0] >= 0) { ci = pix[0] / P.W; cj = pix[0] - ci * P.W; }
+    if (rows_ok) { ci = pix[0] / P.W; cj = pix[0] - ci * P.W; }
 #pragma unroll
     for (int k = 0; k < PPT; k++) {
-        int i = ci, j = cj;
-        if (P.stride == 1) { if (++cj == P.W) { cj = 0; ci++; } }
+        int i = ci, j = cj + k;
         X[k] = Y[k] = nanv; gi[k] = -1;
         if (!(m & (1u << k)) || !(d[k] > 0.0f)) continue;
         const int p = pix[k];
-        if (P.stride != 1) { i = p / P.W; j = p - i * P.W; }
+        if (!rows_ok) { i = p / P.W; j = p - i * P.W; }
         const float z = d[k];
         X[k] = b2r_div_fast(xfmul(xfsub((float)j, P.gcx), z), P.gfx, P.rgfx);
         Y[k] = b2r_div_fast(xfmul(xfsub((float)i, P.gcy), z), P.gfy, P.rgfy);
@@ -374,8 +388,7 @@ __global__ void __launch_bounds__(UNP_THREADS) unproject_fill_f32_kernel(const _
         }
         float* q = s_xyz + ph3 + 3 * rank;
         q[0] = ox; q[1] = oy; q[2] = oz;
-        if (P.src_index) s_idx[ph1 + rank] = pix[k];
-        if (P.gather_index) s_gidx[ph1 + rank] = gi[k];
+        if (WANT_IDX) { s_idx[ph1 + rank] = pix[k]; s_gidx[ph1 + rank] = gi[k]; }
         if (CMODE != 0) {
             float r = 0.f, g = 0.f, bl = 0.f;
             if (CMODE >= 3) {
@@ -413,23 +426,28 @@ __global__ void __launch_bounds__(UNP_THREADS) unproject_fill_f32_kernel(const _
     };
     copy_out(reinterpret_cast<float*>(P.xyz) + obase * 3, s_xyz, total * 3, ph3, std::integral_constant<int, CHUNK * 3 / 4>());
     if (CMODE != 0) copy_out(reinterpret_cast<float*>(P.rgb) + obase * 3, s_rgb, total * 3, ph3, std::integral_constant<int, CHUNK * 3 / 4>());
-    if (P.src_index) copy_out(reinterpret_cast<float*>(P.src_index) + obase, reinterpret_cast<const float*>(s_idx), total, ph1, std::integral_constant<int, CHUNK / 4>());
-    if (P.gather_index) copy_out(reinterpret_cast<float*>(P.gather_index) + obase, reinterpret_cast<const float*>(s_gidx), total, ph1, std::integral_constant<int, CHUNK / 4>());
+    if (WANT_IDX && P.src_index) copy_out(reinterpret_cast<float*>(P.src_index) + obase, reinterpret_cast<const float*>(s_idx), total, ph1, std::integral_constant<int, CHUNK / 4>());
+    if (WANT_IDX && P.gather_index) copy_out(reinterpret_cast<float*>(P.gather_index) + obase, reinterpret_cast<const float*>(s_gidx), total, ph1, std::integral_constant<int, CHUNK / 4>());
+}
+
+template <int CMODE, bool GATHER, bool WANT_IDX>
+static int launch_fill_f32_t2(const UnprojParams& P, cudaStream_t stream) {
+    constexpr int CHUNK = UNP_THREADS * 8;
+    const size_t smem = (size_t)(CHUNK * 3 + 4) * 4 * (CMODE != 0 ? 2 : 1) + (WANT_IDX ? (size_t)(CHUNK + 4) * 4 * 2 : 0);
+    static bool attr_set = false;
+    if (!attr_set) {
+        B2R_CUDA(cudaFuncSetAttribute(unproject_fill_f32_kernel<CMODE, GATHER, WANT_IDX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    dim3 grid(P.n_chunks, P.B);
+    unproject_fill_f32_kernel<CMODE, GATHER, WANT_IDX><<<grid, UNP_THREADS, smem, stream>>>(P);
+    B2R_CHECK_LAUNCH();
+    return B2R_OK;
 }
 
 template <int CMODE, bool GATHER>
 static int launch_fill_f32_t(const UnprojParams& P, cudaStream_t stream) {
-    constexpr int CHUNK = UNP_THREADS * 8;
-    const size_t smem = (size_t)(CHUNK * 3 + 4) * 4 * 2 + (size_t)(CHUNK + 4) * 4 * 2;
-    static bool attr_set = false;
-    if (!attr_set) {
-        B2R_CUDA(cudaFuncSetAttribute(unproject_fill_f32_kernel<CMODE, GATHER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
-    }
-    dim3 grid(P.n_chunks, P.B);
-    unproject_fill_f32_kernel<CMODE, GATHER><<<grid, UNP_THREADS, smem, stream>>>(P);
-    B2R_CHECK_LAUNCH();
-    return B2R_OK;
+    return (P.src_index || P.gather_index) ? launch_fill_f32_t2<CMODE, GATHER, true>(P, stream) : launch_fill_f32_t2<CMODE, GATHER, false>(P, stream);
 }
 
 static int launch_fill_f32(const UnprojParams& P, cudaStream_t stream) {
@@ -495,6 +513,16 @@ B2R_API int b2r_unproject(const void* depth, int depth_is_u16, float depth_scale
     P.gfx = (float)depth_K[0]; P.gfy = (float)depth_K[1]; P.gcx = (float)depth_K[2]; P.gcy = (float)depth_K[3];
     P.rgfx = 1.0f / P.gfx; P.rgfy = 1.0f / P.gfy; P.r255 = 1.0f / 255.0f;   // host IEEE division: correctly rounded reciprocals
     P.rscale = 1.0f / depth_scale; P.scale_fast = host_div_domain(depth_scale) ? 1 : 0;
+    P.u16_vmax = 0; P.u16_count_fast = (depth_is_u16 && depth_scale > 0.0f) ? 1 : 0;
+    if (P.u16_count_fast) {   // binary search of the monotone predicate RN((float)v / scale) < trunc (IEEE float division, as on the device)
+        uint32_t lo = 0, hi = 65535;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi + 1) >> 1;
+            volatile float q = (float)mid / depth_scale;
+            if (q < depth_trunc) lo = mid; else hi = mid - 1;
+        }
+        P.u16_vmax = lo;
+    }
     if (P.gather) {
         P.Fx = (float)color_K[0]; P.Fy = (float)color_K[1]; P.Cx = (float)color_K[2]; P.Cy = (float)color_K[3];
         for (int i = 0; i < 12; i++) P.d2c[i] = (float)d2c_host[i];
