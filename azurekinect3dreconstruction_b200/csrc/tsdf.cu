@@ -242,55 +242,72 @@ __global__ void __launch_bounds__(256, 4) tsdf_pack_alloc_kernel(const __grid_co
             }
         }
     }
-    // Rounds of 4 cells per lane, warp-uniform.  Per round: (A) all slot probes issued together; the common
-    // case -- unit exists and this frame's bit is already set -- ends there; (B) lanes holding the same key
-    // elect one leader (match.any) whose atomicOr marks the unit; (C) first touches append to the list;
-    // absent keys / collisions take the probing slow path.
-    for (int base = 0; __any_sync(0xffffffffu, base < n); base += 4) {
-        uint64_t want[4];
-        uint32_t slot_i[4];
-        bool need[4];
+    // Neighbouring samples mostly share a box.  Keep one box per RUN of equal boxes (run heads), lay the heads'
+    // cells end to end, and deal the cells out to the 256 threads of the block: ~1 cell per thread instead of
+    // 8-27 per sample.  Per cell: (A) one slot probe -- the common case (unit exists, this frame's bit already
+    // set) ends there; (B) lanes holding the same key elect a leader (match.any) whose atomicOr marks the unit;
+    // (C) first touches append to the touched list; absent keys / collisions take the probing slow path.
+    __shared__ int s_lo[256][3];
+    __shared__ int s_dim[256][2];     // ny, nz of the head's box
+    __shared__ int s_start[257];      // first cell of head h in the block's cell sequence
+    __shared__ int s_n[256];
+    __shared__ int s_warp[2][8];
+    const int t = threadIdx.x, warp = t >> 5;
+    s_lo[t][0] = lo[0]; s_lo[t][1] = lo[1]; s_lo[t][2] = lo[2]; s_dim[t][0] = ny; s_dim[t][1] = nz; s_n[t] = n;
+    __syncthreads();
+    bool head = n > 0;
+    if (head && t > 0)
+        head = !(s_lo[t - 1][0] == lo[0] && s_lo[t - 1][1] == lo[1] && s_lo[t - 1][2] == lo[2] && s_dim[t - 1][0] == ny && s_dim[t - 1][1] == nz && s_n[t - 1] == n);
+    // block scans: heads before me, cells before me
+    int hc = head ? 1 : 0, cc_ = head ? n : 0;
+    int hi_ = hc, ci_ = cc_;
+    for (int o = 1; o < 32; o <<= 1) {
+        const int a1 = __shfl_up_sync(0xffffffffu, hi_, o), a2 = __shfl_up_sync(0xffffffffu, ci_, o);
+        if ((int)lane >= o) { hi_ += a1; ci_ += a2; }
+    }
+    if (lane == 31) { s_warp[0][warp] = hi_; s_warp[1][warp] = ci_; }
+    __syncthreads();   // also: everyone has read its left neighbour's box
+    int hbase = 0, cbase = 0, nheads = 0, ncells = 0;
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const int c = base + k;
-            want[k] = B2R_KEY_EMPTY; need[k] = false; slot_i[k] = 0;
-            if (c < n) {
-                const int a = lo[0] + c / (ny * nz), b = lo[1] + (c / nz) % ny, cc = lo[2] + c % nz;
-                const uint64_t key = b2r_pack_key(a, b, cc);
-                const uint64_t hsh = b2r_mix64(key);
-                if (P.world <= 1 || (int)((hsh >> 33) % (uint64_t)P.world) == P.rank) { want[k] = key; slot_i[k] = (uint32_t)hsh & P.hash.mask; }
-            }
+    for (int w = 0; w < 8; w++) { if (w < warp) { hbase += s_warp[0][w]; cbase += s_warp[1][w]; } nheads += s_warp[0][w]; ncells += s_warp[1][w]; }
+    const int my_h = hbase + hi_ - hc, my_c = cbase + ci_ - cc_;
+    __syncthreads();   // s_lo / s_dim are about to be overwritten in head order
+    if (head) { s_lo[my_h][0] = lo[0]; s_lo[my_h][1] = lo[1]; s_lo[my_h][2] = lo[2]; s_dim[my_h][0] = ny; s_dim[my_h][1] = nz; s_start[my_h] = my_c; }
+    if (t == 0) s_start[nheads] = ncells;
+    __syncthreads();
+    for (int c0 = 0; c0 < ncells; c0 += 256) {      // block-uniform trip count: every lane reaches the match.any
+        const int c = c0 + t;
+        uint64_t want = B2R_KEY_EMPTY;
+        uint32_t slot_i = 0;
+        if (c < ncells) {
+            int lo_h = 0, hi_h = nheads - 1;          // last head whose start <= c
+            while (lo_h < hi_h) { const int mid = (lo_h + hi_h + 1) >> 1; if (s_start[mid] <= c) lo_h = mid; else hi_h = mid - 1; }
+            const int r = c - s_start[lo_h], dy = s_dim[lo_h][0], dz = s_dim[lo_h][1];
+            const int a = s_lo[lo_h][0] + r / (dy * dz), b = s_lo[lo_h][1] + (r / dz) % dy, cz = s_lo[lo_h][2] + r % dz;
+            const uint64_t key = b2r_pack_key(a, b, cz);
+            const uint64_t hsh = b2r_mix64(key);
+            if (P.world <= 1 || (int)((hsh >> 33) % (uint64_t)P.world) == P.rank) { want = key; slot_i = (uint32_t)hsh & P.hash.mask; }
         }
-        uint64_t got[4];
-        uint32_t mk[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            got[k] = 0; mk[k] = 0;
-            if (want[k] != B2R_KEY_EMPTY) {
-                const B2RSlot* slot = &P.hash.slots[slot_i[k]];
-                got[k] = __ldcg(reinterpret_cast<const unsigned long long*>(&slot->key));
-                mk[k] = __ldcg(&slot->mask[P.q]);
-            }
+        uint64_t got = 0;
+        uint32_t mk = 0;
+        if (want != B2R_KEY_EMPTY) {
+            const B2RSlot* slot = &P.hash.slots[slot_i];
+            got = __ldcg(reinterpret_cast<const unsigned long long*>(&slot->key));
+            mk = __ldcg(&slot->mask[P.q]);
         }
-        uint32_t old[4];
-        bool slow[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const bool live = want[k] != B2R_KEY_EMPTY && !(got[k] == want[k] && (mk[k] & F.bit));
-            const unsigned peers = __match_any_sync(0xffffffffu, live ? want[k] : (B2R_KEY_EMPTY - 1 - lane));
-            const bool leader = live && (lane == (unsigned)(__ffs(peers) - 1));
-            slow[k] = leader && got[k] != want[k];
-            need[k] = leader && got[k] == want[k];
-            old[k] = 1;
-            if (need[k]) old[k] = atomicOr(&P.hash.slots[slot_i[k]].mask[P.q], F.bit);
-        }
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            if (need[k] && old[k] == 0) {
-                const int pos = atomicAdd(&P.counters[B2R_C_TOUCHED0 + P.q], 1);
-                if (pos < P.cap_units) P.touched[pos] = (int)slot_i[k];
+        const bool live = want != B2R_KEY_EMPTY && !(got == want && (mk & F.bit));
+        const unsigned peers = __match_any_sync(0xffffffffu, live ? want : (B2R_KEY_EMPTY - 1 - lane));
+        const bool leader = live && (lane == (unsigned)(__ffs(peers) - 1));
+        if (leader) {
+            if (got == want) {
+                const uint32_t old = atomicOr(&P.hash.slots[slot_i].mask[P.q], F.bit);
+                if (old == 0) {
+                    const int pos = atomicAdd(&P.counters[B2R_C_TOUCHED0 + P.q], 1);
+                    if (pos < P.cap_units) P.touched[pos] = (int)slot_i;
+                }
+            } else {
+                alloc_key(P, want, F.bit);
             }
-            if (slow[k]) alloc_key(P, want[k], F.bit);
         }
     }
 }
