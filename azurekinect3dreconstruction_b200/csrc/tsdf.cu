@@ -626,7 +626,7 @@ B2R_API b2r_tsdf* b2r_tsdf_create(double voxel_length, double sdf_trunc, int col
     h->color_type = color_type; h->res = unit_resolution; h->stride = depth_sampling_stride;
     h->planes = color_type == 0 ? 2 : 5;
     h->cap_units = capacity_units; h->rank = rank; h->world = world;
-    h->max_batch = env_int("B2R_TSDF_BATCH", 8, 1, B2R_MAX_BATCH);
+    h->max_batch = env_int("B2R_TSDF_BATCH", 16, 1, B2R_MAX_BATCH);
     cudaError_t e = cudaGetDevice(&h->device);
     h->nslots = next_pow2((uint64_t)capacity_units * 2);
     h->hash.mask = h->nslots - 1;
