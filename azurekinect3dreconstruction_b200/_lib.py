@@ -50,6 +50,7 @@ SIGNATURES = {
     "b2r_tsdf_profile_read": (_i, [_vp, _pd, _vp]),
     "b2r_tsdf_flush": (_i, [_vp, _vp]),
     "b2r_tsdf_set_batch": (_i, [_vp, _i, _vp]),
+    "b2r_selftest_u8_div255": (_i, []),
     "b2r_selftest_div": (_i, [_i64, C.c_uint64, _pi64, _vp]),
     "b2r_tsdf_num_units": (_i64, [_vp, _vp]),
     "b2r_tsdf_export_keys": (_i, [_vp, _vp, _i64, _vp]),

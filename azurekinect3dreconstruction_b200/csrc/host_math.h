@@ -48,4 +48,18 @@ inline void m4_identity(double* r) {
     for (int i = 0; i < 16; i++) r[i] = (i % 5 == 0) ? 1.0 : 0.0;
 }
 
+// a6 colour-to-depth gather constants (the chain is defined in unproject.cu / oracle.cpp "a6"): folded in f64,
+// rounded once to f32.  dK, cK = {fx, fy, cx, cy}; d2c = row-major rigid transform (>= 12 doubles).
+// out16 = {ax, bx, ay, by, M[3][4]} with M = [[Fx,0,Cx+0.5],[0,Fy,Cy+0.5],[0,0,1]] * [R|t].
+inline void gather_constants(const double* dK, const double* cK, const double* d2c, float* out16) {
+    out16[0] = (float)(1.0 / dK[0]); out16[1] = (float)(-dK[2] / dK[0]);
+    out16[2] = (float)(1.0 / dK[1]); out16[3] = (float)(-dK[3] / dK[1]);
+    const double cu = cK[2] + 0.5, cv = cK[3] + 0.5;
+    for (int j = 0; j < 4; j++) {
+        out16[4 + j] = (float)(cK[0] * d2c[j] + cu * d2c[8 + j]);
+        out16[8 + j] = (float)(cK[1] * d2c[4 + j] + cv * d2c[8 + j]);
+        out16[12 + j] = (float)d2c[8 + j];
+    }
+}
+
 }  // namespace b2r

@@ -131,11 +131,13 @@ def _as_vec3d(v) -> Vector3dVector:
 def unproject(depth: torch.Tensor, intrinsic: PinholeCameraIntrinsic, *, depth_is_u16=False, depth_scale=1000.0,
               depth_trunc=1000.0, color: Optional[torch.Tensor] = None, color_bgr=False, gray: Optional[torch.Tensor] = None,
               color_intrinsic: Optional[PinholeCameraIntrinsic] = None, depth_to_color: Optional[np.ndarray] = None,
-              transforms=None, stride=1, dtype=torch.float64, valid_only=True, want_index=False, want_gather_index=False):
+              transforms=None, stride=1, dtype=torch.float64, valid_only=True, want_index=False, want_gather_index=False, out=None):
     """Batched fused unprojection (b2r_unproject). depth: (B,H,W) or (H,W) device tensor.
 
-    ``transforms``: (B,4,4) camera->output matrices (default identity).  Returns a dict with ``xyz``
-    (B,cap,3), ``rgb`` or None, ``counts`` (B,) int32 device tensor, optional ``src_index``/``gather_index``.
+    ``transforms``: (B,4,4) camera->output matrices (default identity), numpy or an f64 device tensor.  Returns a dict
+    with ``xyz`` (B,cap,3), ``rgb`` or None, ``counts`` (B,) int32 device tensor, optional ``src_index``/``gather_index``.
+    ``out``: a dict returned by an earlier call with the same shapes / options -- its buffers (and its device copy of
+    the transforms unless new ones are given) are reused, so a streaming caller allocates nothing per tick.
     """
     dev = _lib.require_cuda()
     lib = _lib.load()
@@ -145,16 +147,27 @@ def unproject(depth: torch.Tensor, intrinsic: PinholeCameraIntrinsic, *, depth_i
     B, H, W = depth.shape
     cap = ((W + stride - 1) // stride) * ((H + stride - 1) // stride)
     f64 = dtype == torch.float64
-    if transforms is None:
-        transforms = np.tile(_IDENTITY, (B, 1, 1))
-    T = torch.as_tensor(np.ascontiguousarray(np.asarray(transforms, dtype=np.float64).reshape(B, 16)), device=dev)
-    xyz = torch.empty((B, cap, 3), dtype=dtype, device=dev)
     has_col = color is not None or gray is not None
-    rgb = torch.empty((B, cap, 3), dtype=dtype, device=dev) if has_col else None
-    src = torch.empty((B, cap), dtype=torch.int32, device=dev) if want_index else None
-    gidx = torch.empty((B, cap), dtype=torch.int32, device=dev) if want_gather_index else None
-    counts = torch.empty((B,), dtype=torch.int32, device=dev)
-    scratch = torch.empty((int(lib.b2r_unproject_scratch_words(W, H, B, stride, 1 if f64 else 0)),), dtype=torch.int32, device=dev)
+    if out is not None and transforms is None:
+        T = out["_T"]
+    elif isinstance(transforms, torch.Tensor) and transforms.is_cuda:
+        T = transforms.to(torch.float64).reshape(B, 16).contiguous()
+    else:
+        if transforms is None:
+            transforms = np.tile(_IDENTITY, (B, 1, 1))
+        T = torch.as_tensor(np.ascontiguousarray(np.asarray(transforms, dtype=np.float64).reshape(B, 16)), device=dev)
+    if out is not None:
+        xyz, rgb, src, gidx, counts, scratch = out["xyz"], out["rgb"], out["src_index"], out["gather_index"], out["counts"], out["_scratch"]
+        if tuple(xyz.shape) != (B, cap, 3) or xyz.dtype != dtype or (rgb is None) == has_col or (src is None) == bool(want_index) \
+                or (gidx is None) == bool(want_gather_index):
+            raise ValueError("unproject(out=...): buffers do not match this call's shapes / options")
+    else:
+        xyz = torch.empty((B, cap, 3), dtype=dtype, device=dev)
+        rgb = torch.empty((B, cap, 3), dtype=dtype, device=dev) if has_col else None
+        src = torch.empty((B, cap), dtype=torch.int32, device=dev) if want_index else None
+        gidx = torch.empty((B, cap), dtype=torch.int32, device=dev) if want_gather_index else None
+        counts = torch.empty((B,), dtype=torch.int32, device=dev)
+        scratch = torch.empty((int(lib.b2r_unproject_scratch_words(W, H, B, stride, 1 if f64 else 0)),), dtype=torch.int32, device=dev)
     cch, Wc, Hc = 0, 0, 0
     if color is not None:
         color = color.contiguous()
@@ -170,7 +183,7 @@ def unproject(depth: torch.Tensor, intrinsic: PinholeCameraIntrinsic, *, depth_i
                            _lib.ptr(xyz), _lib.ptr(rgb), _lib.ptr(src), _lib.ptr(gidx), cap, _lib.ptr(counts), _lib.ptr(scratch),
                            _lib.stream_ptr())
     _lib.check(rc, "unproject")
-    return dict(xyz=xyz, rgb=rgb, counts=counts, src_index=src, gather_index=gidx, capacity=cap)
+    return dict(xyz=xyz, rgb=rgb, counts=counts, src_index=src, gather_index=gidx, capacity=cap, _T=T, _scratch=scratch)
 
 
 class PointCloud:

@@ -72,7 +72,9 @@ int b2r_rgb_to_intensity(const uint8_t* rgb, int64_t n, int channels, int bgr, f
  *  valid_only   project_valid_depth_only
  *  xyz,rgb      [B][capacity][3]; src_index / gather_index (optional) [B][capacity] int32: raster index
  *               of the source depth pixel / gathered colour texel (-1 = outside the colour image)
- *  counts       DEVICE int32[B]; scratch DEVICE int32[b2r_unproject_scratch_words(...)]               */
+ *  counts       DEVICE int32[B]; scratch DEVICE int32[b2r_unproject_scratch_words(...)], 8-byte aligned
+ *  The f32 path is ONE kernel (tiles in raster order by ticket, offsets by decoupled look-back); the f64 path is
+ *  count -> scan -> fill.  The gather chain (a6) is the f32 FMA chain defined in oracle/oracle.cpp "a6".  */
 int64_t b2r_unproject_scratch_words(int W, int H, int B, int stride, int out_f64);
 int b2r_unproject(const void* depth, int depth_is_u16, float depth_scale, float depth_trunc, int W, int H, int B,
                   const uint8_t* color, int color_channels, int color_bgr, int Wc, int Hc, const float* gray,
@@ -130,6 +132,8 @@ int64_t b2r_tsdf_num_units(b2r_tsdf* h, cudaStream_t stream);
  * pack+alloc launches, fuse launches} */
 int b2r_tsdf_profile(b2r_tsdf* h, int max_launches);
 int b2r_tsdf_profile_read(b2r_tsdf* h, double* out5_host, cudaStream_t stream);
+/* Host-only: bytes c for which the f32 unprojection path's two-term constant misrounds c/255 (must return 0). */
+int b2r_selftest_u8_div255(void);
 /* GPU self-test of the shared-reciprocal IEEE division used by the fusion kernel: number of inputs whose
  * quotient differs bitwise from div.rn.f32 (must be 0) */
 int b2r_selftest_div(int64_t n_per_mode, uint64_t seed, int64_t* mismatches_host, cudaStream_t stream);

