@@ -131,6 +131,7 @@ def hbm_peak():
 def cpu_reference(depth_np, rgb_np, E, intr, n_frames, steps, warmup):
     """Times the CPU oracle (Open3D-legacy port, OpenMP over units, all host threads). Returns (frames/s, ms/step, cores)."""
     from oracle import o3r
+    o3r.set_num_threads(os.cpu_count() or 1)       # all host cores, also under torchrun (which exports OMP_NUM_THREADS=1)
     Kt = (intr["fx"], intr["fy"], intr["cx"], intr["cy"])
     vol = o3r.TSDF(VOXEL, TRUNC, 1, 16, 4, parallel_units=True)
     times = []
@@ -327,5 +328,27 @@ def main():
     return 0
 
 
+def _main_with_clean_stdout():
+    """The contract is ONE JSON line on stdout: libraries (NCCL prints its version banner to stdout) are kept off it by
+    pointing fd 1 at stderr for the duration of the run and printing the line to the saved descriptor."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    real = os.fdopen(saved, "w")
+    import builtins
+    _print = builtins.print
+
+    def print_json(*a, **k):
+        k.setdefault("file", real)
+        _print(*a, **k)
+        real.flush()
+    builtins.print = print_json
+    try:
+        return main()
+    finally:
+        builtins.print = _print
+        sys.stdout.flush()
+
+
 if __name__ == "__main__":
-    sys.exit(main())
+    sys.exit(_main_with_clean_stdout())

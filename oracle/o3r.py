@@ -74,6 +74,13 @@ def num_threads() -> int:
     return int(lib().o3r_num_threads())
 
 
+def set_num_threads(n: int) -> None:
+    L = lib()
+    L.o3r_set_num_threads.argtypes = [C.c_int]
+    L.o3r_set_num_threads.restype = None
+    L.o3r_set_num_threads(int(n))
+
+
 def depth_to_float(depth_u16, depth_scale=1000.0, depth_trunc=3.0):
     d = np.ascontiguousarray(depth_u16, dtype=np.uint16)
     out = np.empty(d.shape, np.float32)

@@ -1208,6 +1208,14 @@ O3R_API int o3r_m4_inverse(const double* in, double* out) {
 }
 O3R_API int o3r_solve6(const double* A, const double* b, double* x) { return ldlt6_solve(A, b, x) ? 0 : -1; }
 O3R_API void o3r_vec6_to_m4(const double* x, double* T) { M4 m = vec6_to_m4(x); std::memcpy(T, m.m, sizeof(m.m)); }
+// torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU reference arm of bench.py asks for all host cores explicitly
+O3R_API void o3r_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
 O3R_API int o3r_num_threads() {
 #ifdef _OPENMP
     return omp_get_max_threads();
