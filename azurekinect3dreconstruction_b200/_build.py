@@ -14,7 +14,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libb2recon.so")
-SOURCES = ["tsdf.cu", "unproject.cu", "extract.cu", "odometry.cu", "icp.cu"]
+SOURCES = ["tsdf.cu", "unproject.cu", "extract.cu", "odometry.cu", "icp.cu", "pointcloud.cu"]
 HEADERS = ["common.cuh", "host_math.h", "tsdf_internal.h", "mc_tables.h"]
 
 NVCC_FLAGS = [
@@ -66,7 +66,7 @@ def build_cuda(force: bool = False, verbose: bool = False) -> str:
 def build_oracle(force: bool = False) -> str:
     odir = os.path.join(ROOT, "oracle")
     lib = os.path.join(odir, "liboracle.so")
-    deps = [os.path.join(odir, "oracle.cpp"), os.path.join(odir, "mc_tables.h"), os.path.join(odir, "Makefile")]
+    deps = [os.path.join(odir, "oracle.cpp"), os.path.join(odir, "oracle_pcd.cpp"), os.path.join(odir, "mc_tables.h"), os.path.join(odir, "Makefile")]
     if force or _stale(lib, deps):
         res = subprocess.run(["make", "-C", odir] + (["-B"] if force else []), capture_output=True, text=True)
         if res.returncode != 0:

@@ -63,6 +63,16 @@ SIGNATURES = {
     "b2r_odometry": (_i, [_vp, _vp, _vp, _vp, _i, _i, _d, _d, _d, _d, _pd, _i, _pi, _i, _d, _d, _d, _pd, _pd, _pi, _vp]),
     "b2r_image_filter": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "b2r_image_downsample": (_i, [_vp, _i, _i, _vp, _vp]),
+    "b2r_knn_create": (_vp, [_vp, _i64, _d, _i, _vp]),
+    "b2r_knn_destroy": (None, [_vp]),
+    "b2r_knn_info": (_i, [_vp, _pd, _pi64]),
+    "b2r_knn_search": (_i, [_vp, _vp, _i64, _i, _d, _vp, _vp, _vp, _vp]),
+    "b2r_pcd_estimate_normals": (_i, [_vp, _vp, _i, _d, _vp, _i, _vp, _vp]),
+    "b2r_pcd_orient_normals": (_i, [_vp, _i64, _pd, _vp, _vp]),
+    "b2r_pcd_statistical_outlier": (_i, [_vp, _i, _d, _vp, _vp, _pi64, _vp, _vp]),
+    "b2r_pcd_gather_rows": (_i, [_vp, _vp, _i64, _i, _i, _vp, _vp]),
+    "b2r_pcd_voxel_down_sample": (_i, [_vp, _vp, _vp, _i64, _d, _vp, _vp, _vp, _vp, _i64, _pi64, _vp]),
+    "b2r_pcd_bounds": (_i, [_vp, _i64, _pd, _vp]),
     "b2r_icp_point_to_plane": (_i, [_vp, _i64, _vp, _vp, _i64, _d, _pd, _i, _d, _d, _pd, _pd, _pd, _vp, _vp]),
 }
 

@@ -186,6 +186,50 @@ def unproject(depth: torch.Tensor, intrinsic: PinholeCameraIntrinsic, *, depth_i
     return dict(xyz=xyz, rgb=rgb, counts=counts, src_index=src, gather_index=gidx, capacity=cap, _T=T, _scratch=scratch)
 
 
+class KDTreeSearchParamKNN:
+    """o3d.geometry.KDTreeSearchParamKNN(knn=30)"""
+    def __init__(self, knn: int = 30):
+        self.knn = int(knn)
+
+
+class KDTreeSearchParamRadius:
+    """o3d.geometry.KDTreeSearchParamRadius(radius) -- served as a hybrid search with the library's largest list (128)."""
+    def __init__(self, radius: float):
+        self.radius = float(radius)
+
+
+class KDTreeSearchParamHybrid:
+    """o3d.geometry.KDTreeSearchParamHybrid(radius, max_nn)  (GoodColorReconstruction.py:150)"""
+    def __init__(self, radius: float, max_nn: int):
+        self.radius = float(radius)
+        self.max_nn = int(max_nn)
+
+
+def _search_k_radius(param):
+    if param is None or isinstance(param, KDTreeSearchParamKNN):
+        return (param.knn if param is not None else 30), -1.0
+    if isinstance(param, KDTreeSearchParamHybrid):
+        return param.max_nn, param.radius
+    if isinstance(param, KDTreeSearchParamRadius):
+        return 128, param.radius
+    raise TypeError("search_param must be a KDTreeSearchParam{KNN,Radius,Hybrid}")
+
+
+class _Knn:
+    """Owns a b2r_knn handle (uniform-grid index of a device point array)."""
+    def __init__(self, xyz: torch.Tensor, cell: float, k_hint: int):
+        self._h = _lib.load().b2r_knn_create(_lib.ptr(xyz), int(xyz.shape[0]), float(cell), int(k_hint), _lib.stream_ptr())
+        if not self._h:
+            raise RuntimeError(_lib.last_error())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            _lib.load().b2r_knn_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+
 class PointCloud:
     def __init__(self, points=None):
         self._points = _as_vec3d(points) if points is not None else Vector3dVector()
@@ -281,6 +325,129 @@ class PointCloud:
         pcd.source_index = r["src_index"][0, :n]
         pcd.gather_index = r["gather_index"][0, :n]
         return pcd
+
+    # ---- conditioning on either side of ICP ---------------------------------------------
+    def _xyz64(self) -> torch.Tensor:
+        dev = _lib.require_cuda()
+        t = self._points.tensor
+        if t.dtype != torch.float64 or not t.is_cuda or not t.is_contiguous():
+            t = t.to(device=dev, dtype=torch.float64).contiguous()
+            self._points = Vector3dVector(t)
+        return t
+
+    @staticmethod
+    def _attr64(v: Vector3dVector, dev) -> torch.Tensor:
+        return v.tensor.to(device=dev, dtype=torch.float64).contiguous()
+
+    def get_min_bound(self) -> np.ndarray:
+        return self._bounds()[:3]
+
+    def get_max_bound(self) -> np.ndarray:
+        return self._bounds()[3:]
+
+    def _bounds(self) -> np.ndarray:
+        if self.is_empty():
+            return np.zeros(6)
+        xyz = self._xyz64()
+        out = (C.c_double * 6)()
+        _lib.check(_lib.load().b2r_pcd_bounds(_lib.ptr(xyz), len(xyz), out, _lib.stream_ptr()))
+        return np.array(list(out))
+
+    def select_by_index(self, indices, invert: bool = False) -> "PointCloud":
+        """PointCloud::SelectByIndex (device gather; indices: list / ndarray / int tensor)."""
+        xyz = self._xyz64()
+        dev = xyz.device
+        idx = torch.as_tensor(np.asarray(indices) if not isinstance(indices, torch.Tensor) else indices).to(device=dev, dtype=torch.int32).contiguous()
+        if invert:
+            m = torch.ones(len(xyz), dtype=torch.bool, device=dev)
+            m[idx.long()] = False
+            idx = torch.nonzero(m).reshape(-1).to(torch.int32).contiguous()
+        lib = _lib.load()
+        out = PointCloud()
+
+        def take(t):
+            dst = torch.empty((len(idx), 3), dtype=torch.float64, device=dev)
+            _lib.check(lib.b2r_pcd_gather_rows(_lib.ptr(t), _lib.ptr(idx), len(idx), 3, 0, _lib.ptr(dst), _lib.stream_ptr()))
+            return Vector3dVector(dst)
+        out._points = take(xyz)
+        if self.has_colors():
+            out._colors = take(self._attr64(self._colors, dev))
+        if self.has_normals():
+            out._normals = take(self._attr64(self._normals, dev))
+        return out
+
+    def remove_statistical_outlier(self, nb_neighbors: int, std_ratio: float, print_progress: bool = False):
+        """PointCloud::RemoveStatisticalOutliers -> (inlier cloud, inlier indices)  (GoodColorReconstruction.py:144)."""
+        if nb_neighbors < 1 or not std_ratio > 0:
+            raise RuntimeError("[RemoveStatisticalOutliers] Illegal input parameters, number of neighbors and standard deviation ratio must be positive.")
+        if self.is_empty():
+            return PointCloud(), []
+        xyz = self._xyz64()
+        n = len(xyz)
+        knn = _Knn(xyz, -1.0, nb_neighbors)
+        try:
+            keep = torch.empty((n,), dtype=torch.uint8, device=xyz.device)
+            idx = torch.empty((n,), dtype=torch.int32, device=xyz.device)
+            m = C.c_int64(0)
+            _lib.check(_lib.load().b2r_pcd_statistical_outlier(knn._h, int(nb_neighbors), float(std_ratio), _lib.ptr(keep), _lib.ptr(idx),
+                                                              C.byref(m), None, _lib.stream_ptr()))
+        finally:
+            knn.close()
+        idx = idx[:m.value].contiguous()
+        return self.select_by_index(idx), idx
+
+    def voxel_down_sample(self, voxel_size: float) -> "PointCloud":
+        """PointCloud::VoxelDownSample (GoodColorReconstruction.py:147); output in ascending voxel-index order."""
+        if not voxel_size > 0:
+            raise RuntimeError("[VoxelDownSample] voxel_size <= 0.")
+        out = PointCloud()
+        if self.is_empty():
+            return out
+        xyz = self._xyz64()
+        dev, n = xyz.device, len(xyz)
+        col = self._attr64(self._colors, dev) if self.has_colors() else None
+        nrm = self._attr64(self._normals, dev) if self.has_normals() else None
+        o_xyz = torch.empty((n, 3), dtype=torch.float64, device=dev)
+        o_col = torch.empty((n, 3), dtype=torch.float64, device=dev) if col is not None else None
+        o_nrm = torch.empty((n, 3), dtype=torch.float64, device=dev) if nrm is not None else None
+        o_key = torch.empty((n, 3), dtype=torch.int32, device=dev)
+        m = C.c_int64(0)
+        _lib.check(_lib.load().b2r_pcd_voxel_down_sample(_lib.ptr(xyz), _lib.ptr(col), _lib.ptr(nrm), n, float(voxel_size), _lib.ptr(o_xyz),
+                                                        _lib.ptr(o_col), _lib.ptr(o_nrm), _lib.ptr(o_key), n, C.byref(m), _lib.stream_ptr()))
+        out._points = Vector3dVector(o_xyz[:m.value])
+        if col is not None:
+            out._colors = Vector3dVector(o_col[:m.value])
+        if nrm is not None:
+            out._normals = Vector3dVector(o_nrm[:m.value])
+        out.voxel_index = o_key[:m.value]
+        return out
+
+    def estimate_normals(self, search_param=None, fast_normal_computation: bool = True) -> None:
+        """PointCloud::EstimateNormals (GoodColorReconstruction.py:150, BetterVisualizer2CamWorksCOLOR.py:537).
+        Only the fast (closed-form) eigen solver is provided -- upstream's default."""
+        if self.is_empty():
+            return
+        k, radius = _search_k_radius(search_param)
+        xyz = self._xyz64()
+        has = self.has_normals()
+        nrm = self._attr64(self._normals, xyz.device).clone() if has else torch.zeros_like(xyz)
+        knn = _Knn(xyz, radius if radius > 0 else -1.0, k)
+        try:
+            _lib.check(_lib.load().b2r_pcd_estimate_normals(knn._h, _lib.ptr(xyz), int(k), float(radius), _lib.ptr(nrm), 1 if has else 0, None,
+                                                           _lib.stream_ptr()))
+        finally:
+            knn.close()
+        self._normals = Vector3dVector(nrm)
+
+    def orient_normals_towards_camera_location(self, camera_location=(0.0, 0.0, 0.0)) -> None:
+        """PointCloud::OrientNormalsTowardsCameraLocation (GoodColorReconstruction.py:151)."""
+        if not self.has_normals():
+            raise RuntimeError("[OrientNormalsTowardsCameraLocation] No normals in the PointCloud. Call EstimateNormals() first.")
+        xyz = self._xyz64()
+        nrm = self._attr64(self._normals, xyz.device)
+        cam = (C.c_double * 3)(*[float(v) for v in np.asarray(camera_location, dtype=np.float64).reshape(3)])
+        _lib.check(_lib.load().b2r_pcd_orient_normals(_lib.ptr(xyz), len(xyz), cam, _lib.ptr(nrm), _lib.stream_ptr()))
+        self._normals = Vector3dVector(nrm)
 
     # ---- transforms / merging ----------------------------------------------------------------------
     def transform(self, T) -> "PointCloud":

@@ -187,6 +187,40 @@ int b2r_icp_point_to_plane(const double* src_xyz, int64_t N, const double* tgt_x
                            double rel_rmse, double* out_T_host, double* fitness_host, double* rmse_host,
                            int32_t* corr, cudaStream_t stream);
 
+/* ---- f1: point-cloud conditioning on either side of ICP.  All arrays DEVICE f64 [n][3] unless noted.
+ *      Reference: pcd.remove_statistical_outlier(20, 2.0) / voxel_down_sample(v) / estimate_normals(Hybrid(r, max_nn)) /
+ *      orient_normals_towards_camera_location -- GoodColorReconstruction.py:141-153,
+ *      BetterVisualizer2CamWorksCOLOR.py:531,537,643.  Exact neighbour search through a uniform grid (pointcloud.cu). */
+typedef struct b2r_knn b2r_knn;
+/* index of n points.  cell > 0: grid cell edge (the search radius for hybrid queries); cell <= 0: chosen for k_hint-NN
+ * queries.  Synchronises.  NULL on error. */
+b2r_knn* b2r_knn_create(const double* xyz, int64_t n, double cell, int k_hint, cudaStream_t stream);
+void b2r_knn_destroy(b2r_knn* h);
+int b2r_knn_info(const b2r_knn* h, double* cell, int64_t* n_cells);
+/* KDTreeFlann::SearchKNN (radius <= 0) / SearchHybrid (radius > 0, at most k with d2 < radius^2).  query NULL = every
+ * indexed point (itself first).  idx [nq][k] ascending (distance, index), -1 padded; d2 optional [nq][k]; counts [nq]. */
+int b2r_knn_search(const b2r_knn* h, const double* query, int64_t nq, int k, double radius, int32_t* idx, double* d2,
+                   int32_t* counts, cudaStream_t stream);
+/* PointCloud::EstimateNormals(param, fast_normal_computation=true); radius <= 0: KNN(k), else Hybrid(radius, k).
+ * normals in/out; has_normals=1 orients along the existing normals; cov_out optional [n][6] (xx,xy,xz,yy,yz,zz). */
+int b2r_pcd_estimate_normals(const b2r_knn* h, const double* xyz, int k, double radius, double* normals, int has_normals,
+                             double* cov_out, cudaStream_t stream);
+/* PointCloud::OrientNormalsTowardsCameraLocation(cam) */
+int b2r_pcd_orient_normals(const double* xyz, int64_t n, const double* cam3_host, double* normals, cudaStream_t stream);
+/* PointCloud::RemoveStatisticalOutliers: keep u8[n], inlier_idx int32[n] (first *n_inliers_host valid, ascending),
+ * avg_out optional f64[n].  Synchronises. */
+int b2r_pcd_statistical_outlier(const b2r_knn* h, int nb_neighbors, double std_ratio, uint8_t* keep, int32_t* inlier_idx,
+                                int64_t* n_inliers_host, double* avg_out, cudaStream_t stream);
+/* select_by_index: dst[r][:] = src[idx[r]][:], rows of `width` f64 (or int32 when is_i32) */
+int b2r_pcd_gather_rows(const void* src, const int32_t* idx, int64_t m, int width, int is_i32, void* dst, cudaStream_t stream);
+/* PointCloud::VoxelDownSample(voxel): outputs in ascending voxel-index order, `capacity` rows (n always suffices);
+ * col / nrm / out_key optional.  *m_host = voxels.  Synchronises. */
+int b2r_pcd_voxel_down_sample(const double* xyz, const double* col, const double* nrm, int64_t n, double voxel, double* out_xyz,
+                              double* out_col, double* out_nrm, int32_t* out_key, int64_t capacity, int64_t* m_host,
+                              cudaStream_t stream);
+/* get_min_bound / get_max_bound: out6_host = {min xyz, max xyz}.  Synchronises. */
+int b2r_pcd_bounds(const double* xyz, int64_t n, double* out6_host, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

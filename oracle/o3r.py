@@ -26,8 +26,8 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    src = os.path.join(_DIR, "oracle.cpp")
-    if not os.path.exists(_LIB) or (os.path.exists(src) and os.path.getmtime(src) > os.path.getmtime(_LIB)):
+    srcs = [os.path.join(_DIR, f) for f in ("oracle.cpp", "oracle_pcd.cpp")]
+    if not os.path.exists(_LIB) or any(os.path.exists(f) and os.path.getmtime(f) > os.path.getmtime(_LIB) for f in srcs):
         subprocess.run(["make", "-C", _DIR], check=True, capture_output=True)
     L = C.CDLL(_LIB)
     L.o3r_depth_u16_to_f32.argtypes = [_vp, _i64, _d, _d, _vp]
@@ -59,6 +59,13 @@ def lib():
     L.o3r_correspondence.restype = _i64
     L.o3r_correspondence.argtypes = [_vp, _vp, _i, _i, _d, _d, _d, _d, _vp, _d, _vp, _i64]
     L.o3r_icp_point_to_plane.argtypes = [_vp, _i64, _vp, _vp, _i64, _d, _vp, _i, _d, _d, _vp, C.POINTER(C.c_double), C.POINTER(C.c_double), _vp]
+    L.o3r_pcd_search.argtypes = [_vp, _i64, _vp, _i64, _i, _d, _vp, _vp, _vp]
+    L.o3r_pcd_estimate_normals.argtypes = [_vp, _i64, _i, _d, _vp, _i, _vp]
+    L.o3r_pcd_orient_normals.argtypes = [_vp, _i64, _vp, _vp]
+    L.o3r_pcd_statistical_outlier.restype = _i64
+    L.o3r_pcd_statistical_outlier.argtypes = [_vp, _i64, _i, _d, _vp, _vp]
+    L.o3r_pcd_voxel_down_sample.restype = _i64
+    L.o3r_pcd_voxel_down_sample.argtypes = [_vp, _vp, _vp, _i64, _d, _vp, _vp, _vp, _vp]
     L.o3r_m4_inverse.argtypes = [_vp, _vp]
     L.o3r_solve6.argtypes = [_vp, _vp, _vp]
     L.o3r_vec6_to_m4.argtypes = [_vp, _vp]
@@ -272,3 +279,55 @@ def vec6_to_m4(x):
     T = np.empty((4, 4))
     lib().o3r_vec6_to_m4(_p(_f64(x)), _p(T))
     return T
+
+
+# ---- f1: point-cloud conditioning (oracle_pcd.cpp) ------------------------------------------------------------
+def pcd_search(pts, query=None, k=20, radius=-1.0):
+    """Exact brute-force neighbours: (idx [nq,k] -1 padded, d2 [nq,k], counts [nq]); query None = the points themselves."""
+    p = _f64(pts)
+    q = p if query is None else _f64(query)
+    nq = len(q)
+    idx = np.empty((nq, k), np.int32)
+    d2 = np.empty((nq, k), np.float64)
+    cnt = np.empty((nq,), np.int32)
+    lib().o3r_pcd_search(_p(p), len(p), _p(q), nq, int(k), float(radius), _p(idx), _p(d2), _p(cnt))
+    return idx, d2, cnt
+
+
+def pcd_estimate_normals(pts, k=30, radius=-1.0, normals=None):
+    """PointCloud::EstimateNormals (fast). Returns (normals [n,3], covariances [n,6])."""
+    p = _f64(pts)
+    has = normals is not None
+    nrm = _f64(normals).copy() if has else np.zeros_like(p)
+    cov = np.empty((len(p), 6), np.float64)
+    lib().o3r_pcd_estimate_normals(_p(p), len(p), int(k), float(radius), _p(nrm), 1 if has else 0, _p(cov))
+    return nrm, cov
+
+
+def pcd_orient_normals(pts, normals, camera=(0.0, 0.0, 0.0)):
+    p = _f64(pts)
+    nrm = _f64(normals).copy()
+    cam = _f64(camera)
+    lib().o3r_pcd_orient_normals(_p(p), len(p), _p(cam), _p(nrm))
+    return nrm
+
+
+def pcd_statistical_outlier(pts, nb_neighbors=20, std_ratio=2.0):
+    """PointCloud::RemoveStatisticalOutliers. Returns (keep mask [n] bool, mean neighbour distance [n])."""
+    p = _f64(pts)
+    keep = np.empty((len(p),), np.uint8)
+    avg = np.empty((len(p),), np.float64)
+    lib().o3r_pcd_statistical_outlier(_p(p), len(p), int(nb_neighbors), float(std_ratio), _p(keep), _p(avg))
+    return keep.astype(bool), avg
+
+
+def pcd_voxel_down_sample(pts, voxel, colors=None, normals=None):
+    """PointCloud::VoxelDownSample in ascending voxel-index order. Returns (pts, colors|None, normals|None, keys [m,3])."""
+    p = _f64(pts)
+    c = None if colors is None else _f64(colors)
+    nr = None if normals is None else _f64(normals)
+    n = len(p)
+    op = np.empty((n, 3)); oc = np.empty((n, 3)) if c is not None else None; on = np.empty((n, 3)) if nr is not None else None
+    ok = np.empty((n, 3), np.int32)
+    m = lib().o3r_pcd_voxel_down_sample(_p(p), _p(c), _p(nr), n, float(voxel), _p(op), _p(oc), _p(on), _p(ok))
+    return op[:m].copy(), (oc[:m].copy() if oc is not None else None), (on[:m].copy() if on is not None else None), ok[:m].copy()

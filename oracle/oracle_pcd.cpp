@@ -1,0 +1,278 @@
+// oracle_pcd.cpp -- TEST INFRASTRUCTURE, NOT PRODUCT CODE (same rules as oracle.cpp: only tests/, smoke() and the
+// CPU legs of the benchmarks may load liboracle.so).
+//
+// CPU restatement of the point-cloud conditioning calls the reference scripts make on either side of ICP
+// (SURVEY.md 8(f) row f1), as Open3D 0.19.0's legacy geometry::PointCloud implements them:
+//   remove_statistical_outlier(20, 2.0)         CodeThatWorks/GoodColorReconstruction.py:144,
+//                                               CodeThatWorks/BetterVisualizer2CamWorksCOLOR.py:531
+//   voxel_down_sample(voxel)                    GoodColorReconstruction.py:147, BetterVisualizer2CamWorksCOLOR.py:643
+//   estimate_normals(KDTreeSearchParamHybrid)   GoodColorReconstruction.py:150, BetterVisualizer2CamWorksCOLOR.py:537
+//   orient_normals_towards_camera_location      GoodColorReconstruction.py:151
+// PARITY UNPINNED (as for oracle.cpp): the upstream C++ is not in /root/reference; the semantics are restated from the
+// published algorithms (PointCloud::VoxelDownSample / RemoveStatisticalOutliers, EstimateNormals.cpp: cumulant
+// covariance + the closed-form symmetric 3x3 eigen solver of Eberly's "A Robust Eigensolver for 3x3 Symmetric
+// Matrices").  Neighbour search is BRUTE FORCE here (obviously exact); ties in distance go to the lower index.
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <map>
+#include <tuple>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#define O3R_API extern "C" __attribute__((visibility("default")))
+
+namespace {
+
+struct Nb { double d2; int32_t i; };
+inline bool nb_less(const Nb& a, const Nb& b) { return a.d2 < b.d2 || (a.d2 == b.d2 && a.i < b.i); }
+
+// k nearest (radius <= 0) or hybrid: within radius (d2 <= r*r is NOT what nanoflann's radius search keeps: it keeps
+// d2 < r*r ... upstream SearchHybrid passes radius*radius to a kNN result set bounded by that worst distance, which
+// admits d2 < r2 only) and at most k, ascending (d2, index).
+void search(const double* pts, int64_t n, const double* q, int k, double radius, std::vector<Nb>& out) {
+    out.clear();
+    const double r2 = radius > 0.0 ? radius * radius : INFINITY;
+    std::vector<Nb> all;
+    all.reserve(256);
+    for (int64_t j = 0; j < n; j++) {
+        const double dx = pts[3 * j] - q[0], dy = pts[3 * j + 1] - q[1], dz = pts[3 * j + 2] - q[2];
+        const double d2 = dx * dx + dy * dy + dz * dz;
+        if (d2 < r2) all.push_back({d2, (int32_t)j});
+    }
+    const size_t kk = std::min<size_t>((size_t)k, all.size());
+    std::partial_sort(all.begin(), all.begin() + kk, all.end(), nb_less);
+    out.assign(all.begin(), all.begin() + kk);
+}
+
+struct V3 { double x, y, z; };
+inline V3 cross(const V3& a, const V3& b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+inline double dot(const V3& a, const V3& b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+
+// A = {a00, a01, a02, a11, a12, a22}
+V3 eigenvector0(const double* A, double e) {
+    const V3 r0{A[0] - e, A[1], A[2]}, r1{A[1], A[3] - e, A[4]}, r2{A[2], A[4], A[5] - e};
+    const V3 c01 = cross(r0, r1), c02 = cross(r0, r2), c12 = cross(r1, r2);
+    const double d0 = dot(c01, c01), d1 = dot(c02, c02), d2 = dot(c12, c12);
+    double dmax = d0; int imax = 0;
+    if (d1 > dmax) { dmax = d1; imax = 1; }
+    if (d2 > dmax) { imax = 2; }
+    if (imax == 0) { const double s = std::sqrt(d0); return {c01.x / s, c01.y / s, c01.z / s}; }
+    if (imax == 1) { const double s = std::sqrt(d1); return {c02.x / s, c02.y / s, c02.z / s}; }
+    const double s = std::sqrt(d2); return {c12.x / s, c12.y / s, c12.z / s};
+}
+
+V3 eigenvector1(const double* A, const V3& e0, double eval1) {
+    V3 U;
+    if (std::fabs(e0.x) > std::fabs(e0.y)) { const double inv = 1.0 / std::sqrt(e0.x * e0.x + e0.z * e0.z); U = {-e0.z * inv, 0.0, e0.x * inv}; }
+    else { const double inv = 1.0 / std::sqrt(e0.y * e0.y + e0.z * e0.z); U = {0.0, e0.z * inv, -e0.y * inv}; }
+    const V3 V = cross(e0, U);
+    const V3 AU{A[0] * U.x + A[1] * U.y + A[2] * U.z, A[1] * U.x + A[3] * U.y + A[4] * U.z, A[2] * U.x + A[4] * U.y + A[5] * U.z};
+    const V3 AV{A[0] * V.x + A[1] * V.y + A[2] * V.z, A[1] * V.x + A[3] * V.y + A[4] * V.z, A[2] * V.x + A[4] * V.y + A[5] * V.z};
+    double m00 = dot(U, AU) - eval1, m01 = dot(U, AV), m11 = dot(V, AV) - eval1;
+    const double a00 = std::fabs(m00), a01 = std::fabs(m01), a11 = std::fabs(m11);
+    if (a00 >= a11) {
+        if (std::max(a00, a01) > 0.0) {
+            if (a00 >= a01) { m01 /= m00; m00 = 1.0 / std::sqrt(1.0 + m01 * m01); m01 *= m00; }
+            else { m00 /= m01; m01 = 1.0 / std::sqrt(1.0 + m00 * m00); m00 *= m01; }
+            return {m01 * U.x - m00 * V.x, m01 * U.y - m00 * V.y, m01 * U.z - m00 * V.z};
+        }
+        return U;
+    }
+    if (std::max(a11, a01) > 0.0) {
+        if (a11 >= a01) { m01 /= m11; m11 = 1.0 / std::sqrt(1.0 + m01 * m01); m01 *= m11; }
+        else { m11 /= m01; m01 = 1.0 / std::sqrt(1.0 + m11 * m11); m11 *= m01; }
+        return {m11 * U.x - m01 * V.x, m11 * U.y - m01 * V.y, m11 * U.z - m01 * V.z};
+    }
+    return U;
+}
+
+// eigenvector of the smallest eigenvalue of the symmetric matrix C = {c00, c01, c02, c11, c12, c22}
+V3 fast_eigen3x3(const double* C) {
+    double A[6];
+    double maxc = C[0];
+    for (int i = 1; i < 6; i++) maxc = std::max(maxc, C[i]);
+    if (maxc == 0.0) return {0.0, 0.0, 0.0};
+    for (int i = 0; i < 6; i++) A[i] = C[i] / maxc;
+    const double norm = A[1] * A[1] + A[2] * A[2] + A[4] * A[4];
+    if (norm > 0.0) {
+        const double q = (A[0] + A[3] + A[5]) / 3.0;
+        const double b00 = A[0] - q, b11 = A[3] - q, b22 = A[5] - q;
+        const double p = std::sqrt((b00 * b00 + b11 * b11 + b22 * b22 + norm * 2.0) / 6.0);
+        const double c00 = b11 * b22 - A[4] * A[4];
+        const double c01 = A[1] * b22 - A[4] * A[2];
+        const double c02 = A[1] * A[4] - b11 * A[2];
+        const double det = (b00 * c00 - A[1] * c01 + A[2] * c02) / (p * p * p);
+        const double half_det = std::min(std::max(det * 0.5, -1.0), 1.0);
+        const double angle = std::acos(half_det) / 3.0;
+        const double two_thirds_pi = 2.09439510239319549;
+        const double beta2 = std::cos(angle) * 2.0;
+        const double beta0 = std::cos(angle + two_thirds_pi) * 2.0;
+        const double beta1 = -(beta0 + beta2);
+        const double e0 = q + p * beta0, e1 = q + p * beta1, e2 = q + p * beta2;
+        if (half_det >= 0.0) {
+            const V3 v2 = eigenvector0(A, e2);
+            if (e2 < e0 && e2 < e1) return v2;
+            const V3 v1 = eigenvector1(A, v2, e1);
+            if (e1 < e0 && e1 < e2) return v1;
+            return cross(v1, v2);
+        }
+        const V3 v0 = eigenvector0(A, e0);
+        if (e0 < e1 && e0 < e2) return v0;
+        const V3 v1 = eigenvector1(A, v0, e1);
+        if (e1 < e0 && e1 < e2) return v1;
+        return cross(v0, v1);
+    }
+    if (C[0] < C[3] && C[0] < C[5]) return {1.0, 0.0, 0.0};
+    if (C[3] < C[0] && C[3] < C[5]) return {0.0, 1.0, 0.0};
+    return {0.0, 0.0, 1.0};
+}
+
+}  // namespace
+
+// exact neighbour search: idx[nq][k] (-1 padded), d2[nq][k], counts[nq]
+O3R_API void o3r_pcd_search(const double* pts, int64_t n, const double* q, int64_t nq, int k, double radius, int32_t* idx,
+                            double* d2, int32_t* counts) {
+#pragma omp parallel
+    {
+        std::vector<Nb> nb;
+#pragma omp for schedule(dynamic, 64)
+        for (int64_t i = 0; i < nq; i++) {
+            search(pts, n, q + 3 * i, k, radius, nb);
+            counts[i] = (int32_t)nb.size();
+            for (int j = 0; j < k; j++) {
+                idx[i * k + j] = j < (int)nb.size() ? nb[j].i : -1;
+                if (d2) d2[i * k + j] = j < (int)nb.size() ? nb[j].d2 : -1.0;
+            }
+        }
+    }
+}
+
+// PointCloud::EstimateNormals(search_param, fast_normal_computation = true).  radius <= 0: KNN(k); else Hybrid(radius, k).
+// normals: in/out [n][3]; has_normals: existing normals orient the result.  cov_out (optional) [n][6].
+O3R_API void o3r_pcd_estimate_normals(const double* pts, int64_t n, int k, double radius, double* normals, int has_normals,
+                                      double* cov_out) {
+#pragma omp parallel
+    {
+        std::vector<Nb> nb;
+#pragma omp for schedule(dynamic, 64)
+        for (int64_t i = 0; i < n; i++) {
+            search(pts, n, pts + 3 * i, k, radius, nb);
+            double C[6] = {1.0, 0.0, 0.0, 1.0, 0.0, 1.0};        // identity when fewer than 3 neighbours
+            if (nb.size() >= 3) {
+                double c[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+                for (const Nb& e : nb) {
+                    const double x = pts[3 * e.i], y = pts[3 * e.i + 1], z = pts[3 * e.i + 2];
+                    c[0] += x; c[1] += y; c[2] += z;
+                    c[3] += x * x; c[4] += x * y; c[5] += x * z; c[6] += y * y; c[7] += y * z; c[8] += z * z;
+                }
+                const double m = (double)nb.size();
+                for (int j = 0; j < 9; j++) c[j] /= m;
+                C[0] = c[3] - c[0] * c[0]; C[3] = c[6] - c[1] * c[1]; C[5] = c[8] - c[2] * c[2];
+                C[1] = c[4] - c[0] * c[1]; C[2] = c[5] - c[0] * c[2]; C[4] = c[7] - c[1] * c[2];
+            }
+            if (cov_out) std::memcpy(cov_out + 6 * i, C, sizeof(C));
+            V3 nrm = fast_eigen3x3(C);
+            const double nn = std::sqrt(dot(nrm, nrm));
+            const V3 old{normals[3 * i], normals[3 * i + 1], normals[3 * i + 2]};
+            if (nn == 0.0) nrm = has_normals ? old : V3{0.0, 0.0, 1.0};
+            if (has_normals && dot(nrm, old) < 0.0) { nrm.x = -nrm.x; nrm.y = -nrm.y; nrm.z = -nrm.z; }
+            normals[3 * i] = nrm.x; normals[3 * i + 1] = nrm.y; normals[3 * i + 2] = nrm.z;
+        }
+    }
+}
+
+// PointCloud::OrientNormalsTowardsCameraLocation
+O3R_API void o3r_pcd_orient_normals(const double* pts, int64_t n, const double* cam, double* normals) {
+    for (int64_t i = 0; i < n; i++) {
+        V3 ref{cam[0] - pts[3 * i], cam[1] - pts[3 * i + 1], cam[2] - pts[3 * i + 2]};
+        double* nm = normals + 3 * i;
+        const double nn = std::sqrt(nm[0] * nm[0] + nm[1] * nm[1] + nm[2] * nm[2]);
+        if (nn == 0.0) {
+            const double rn = std::sqrt(dot(ref, ref));
+            if (rn == 0.0) { nm[0] = 0.0; nm[1] = 0.0; nm[2] = 1.0; }
+            else { nm[0] = ref.x / rn; nm[1] = ref.y / rn; nm[2] = ref.z / rn; }
+        } else if (nm[0] * ref.x + nm[1] * ref.y + nm[2] * ref.z < 0.0) {
+            nm[0] = -nm[0]; nm[1] = -nm[1]; nm[2] = -nm[2];
+        }
+    }
+}
+
+// PointCloud::RemoveStatisticalOutliers(nb_neighbors, std_ratio): keep[i] = 1 for inliers; avg (optional) = mean
+// neighbour distance per point (the point itself is its own first neighbour, as upstream's KNN search returns it).
+O3R_API int64_t o3r_pcd_statistical_outlier(const double* pts, int64_t n, int nb_neighbors, double std_ratio, uint8_t* keep,
+                                            double* avg_out) {
+    if (n == 0) return 0;
+    std::vector<double> avg((size_t)n);
+    int64_t valid = 0;
+#pragma omp parallel
+    {
+        std::vector<Nb> nb;
+#pragma omp for schedule(dynamic, 64) reduction(+ : valid)
+        for (int64_t i = 0; i < n; i++) {
+            search(pts, n, pts + 3 * i, nb_neighbors, -1.0, nb);
+            double mean = -1.0;
+            if (!nb.empty()) {
+                valid++;
+                double s = 0.0;
+                for (const Nb& e : nb) s += std::sqrt(e.d2);
+                mean = s / (double)nb.size();
+            }
+            avg[i] = mean;
+        }
+    }
+    double sum = 0.0;
+    for (int64_t i = 0; i < n; i++) if (avg[i] > 0.0) sum += avg[i];
+    const double cloud_mean = sum / (double)valid;
+    double sq = 0.0;
+    for (int64_t i = 0; i < n; i++) if (avg[i] > 0.0) sq += (avg[i] - cloud_mean) * (avg[i] - cloud_mean);
+    const double std_dev = std::sqrt(sq / (double)(valid - 1));
+    const double thr = cloud_mean + std_ratio * std_dev;
+    int64_t kept = 0;
+    for (int64_t i = 0; i < n; i++) {
+        keep[i] = (avg[i] > 0.0 && avg[i] < thr) ? 1 : 0;
+        kept += keep[i];
+        if (avg_out) avg_out[i] = avg[i];
+    }
+    return kept;
+}
+
+// PointCloud::VoxelDownSample(voxel).  Output in ascending voxel-index order (upstream's order is that of an
+// unordered_map: implementation-defined; comparisons are on the canonical order).  col / nrm may be null.
+// Returns the number of output points; out_* sized by the caller to n.  out_key (optional) [m][3].
+O3R_API int64_t o3r_pcd_voxel_down_sample(const double* pts, const double* col, const double* nrm, int64_t n, double voxel,
+                                          double* out_pts, double* out_col, double* out_nrm, int32_t* out_key) {
+    if (n == 0) return 0;
+    double mn[3] = {pts[0], pts[1], pts[2]};
+    for (int64_t i = 1; i < n; i++)
+        for (int a = 0; a < 3; a++) mn[a] = std::min(mn[a], pts[3 * i + a]);
+    for (int a = 0; a < 3; a++) mn[a] -= voxel * 0.5;
+    struct Acc { double p[3] = {0, 0, 0}, c[3] = {0, 0, 0}, nn[3] = {0, 0, 0}; int64_t num = 0; };
+    std::map<std::tuple<int, int, int>, Acc> vox;
+    for (int64_t i = 0; i < n; i++) {
+        int k[3];
+        for (int a = 0; a < 3; a++) k[a] = (int)std::floor((pts[3 * i + a] - mn[a]) / voxel);
+        Acc& A = vox[std::make_tuple(k[0], k[1], k[2])];
+        for (int a = 0; a < 3; a++) A.p[a] += pts[3 * i + a];
+        if (nrm && !std::isnan(nrm[3 * i]) && !std::isnan(nrm[3 * i + 1]) && !std::isnan(nrm[3 * i + 2]))
+            for (int a = 0; a < 3; a++) A.nn[a] += nrm[3 * i + a];
+        if (col) for (int a = 0; a < 3; a++) A.c[a] += col[3 * i + a];
+        A.num++;
+    }
+    int64_t m = 0;
+    for (const auto& kv : vox) {
+        const Acc& A = kv.second;
+        const double d = (double)A.num;
+        for (int a = 0; a < 3; a++) {
+            out_pts[3 * m + a] = A.p[a] / d;
+            if (col) out_col[3 * m + a] = A.c[a] / d;
+            if (nrm) out_nrm[3 * m + a] = A.nn[a] / d;
+        }
+        if (out_key) { out_key[3 * m] = std::get<0>(kv.first); out_key[3 * m + 1] = std::get<1>(kv.first); out_key[3 * m + 2] = std::get<2>(kv.first); }
+        m++;
+    }
+    return m;
+}

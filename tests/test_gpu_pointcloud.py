@@ -1,0 +1,195 @@
+"""GPU parity tests for the point-cloud conditioning row: exact neighbour search, estimate_normals,
+orient_normals_towards_camera_location, remove_statistical_outlier, voxel_down_sample -- the CUDA path through the C-ABI
+vs the brute-force CPU oracle (oracle/oracle_pcd.cpp) on identical inputs.
+Bars: neighbour indices, inlier masks, voxel sets: bit-exact; covariances, mean distances, voxel averages: bit-exact f64
+(same summation order); normals: |n . n_ref| >= 1 - 1e-9 (the eigen solver calls acos / cos, whose last bit differs
+between glibc and CUDA)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+import azurekinect3dreconstruction_b200 as o3d
+from azurekinect3dreconstruction_b200 import _lib, synthetic as syn
+from azurekinect3dreconstruction_b200.geometry import _Knn
+
+
+def intrinsic_of(intr):
+    return o3d.camera.PinholeCameraIntrinsic(intr["width"], intr["height"], intr["fx"], intr["fy"], intr["cx"], intr["cy"])
+
+
+@pytest.fixture(scope="module")
+def cloud(small_kinect):
+    """One unprojected synthetic frame (about 22 k coloured points, a surface sampled as a depth camera samples it)."""
+    pose = syn.orbit_trajectory(4, yaw_sweep_deg=10.0)[2]
+    d, c = small_kinect.render_depth_aligned_rgb(pose)
+    rgbd = o3d.geometry.RGBDImage.create_from_color_and_depth(o3d.geometry.Image(c), o3d.geometry.Image(d), 1000.0, 3.0, False)
+    return o3d.geometry.PointCloud.create_from_rgbd_image(rgbd, intrinsic_of(small_kinect.depth_intr))
+
+
+def dev(a, dtype=torch.float64):
+    return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype).cuda().contiguous()
+
+
+def gpu_search(xyz, k, radius, cell, query=None):
+    t = dev(xyz)
+    knn = _Knn(t, cell, k)
+    nq = len(xyz) if query is None else len(query)
+    q = None if query is None else dev(query)
+    idx = torch.empty((nq, k), dtype=torch.int32, device="cuda")
+    d2 = torch.empty((nq, k), dtype=torch.float64, device="cuda")
+    cnt = torch.empty((nq,), dtype=torch.int32, device="cuda")
+    _lib.check(_lib.load().b2r_knn_search(knn._h, _lib.ptr(q), nq, k, float(radius), _lib.ptr(idx), _lib.ptr(d2), _lib.ptr(cnt), _lib.stream_ptr()))
+    torch.cuda.synchronize()
+    knn.close()
+    return idx.cpu().numpy(), d2.cpu().numpy(), cnt.cpu().numpy()
+
+
+@pytest.mark.parametrize("k,radius,cell", [(20, -1.0, -1.0), (30, 0.04, 0.04), (30, 0.1, 0.1), (8, -1.0, 0.5), (40, 0.05, 0.02)])
+def test_knn_search_exact(o3r, cloud, k, radius, cell):
+    xyz = np.asarray(cloud.points)
+    idx, d2, cnt = gpu_search(xyz, k, radius, cell)
+    ridx, rd2, rcnt = o3r.pcd_search(xyz, None, k, radius)
+    assert np.array_equal(cnt, rcnt)
+    assert np.array_equal(idx, ridx)                       # neighbour sets AND order: bit-exact
+    assert np.array_equal(d2, rd2)
+    assert (idx[:, 0] == np.arange(len(xyz))).all()        # a point is its own first neighbour
+
+
+def test_knn_random_cloud_duplicates_and_external_queries(o3r):
+    rng = np.random.default_rng(5)
+    pts = rng.uniform(-1, 1, (6000, 3))
+    pts[100:110] = pts[100]                                # exact duplicates: ties resolved by index
+    pts = np.r_[pts, [[5.0, 5.0, 5.0]]]                    # an isolated point far away (forces many rings)
+    q = rng.uniform(-1.5, 1.5, (500, 3))                   # queries outside the grid too
+    for k, r in ((12, -1.0), (16, 0.3)):
+        idx, d2, cnt = gpu_search(pts, k, r, -1.0 if r < 0 else r, query=q)
+        ridx, rd2, rcnt = o3r.pcd_search(pts, q, k, r)
+        assert np.array_equal(cnt, rcnt) and np.array_equal(idx, ridx) and np.array_equal(d2, rd2)
+    idx, _, _ = gpu_search(pts, 12, -1.0, -1.0)
+    ridx, _, _ = o3r.pcd_search(pts, None, 12, -1.0)
+    assert np.array_equal(idx, ridx)
+    # fewer points than k
+    few = pts[:5]
+    idx, _, cnt = gpu_search(few, 8, -1.0, -1.0)
+    assert (cnt == 5).all() and (idx[:, 5:] == -1).all()
+
+
+@pytest.mark.parametrize("k,radius", [(30, 0.04), (30, -1.0), (30, 0.1)])
+def test_estimate_normals_parity(o3r, cloud, k, radius):
+    xyz = np.asarray(cloud.points)
+    t = dev(xyz)
+    knn = _Knn(t, radius if radius > 0 else -1.0, k)
+    nrm = torch.zeros_like(t)
+    cov = torch.empty((len(xyz), 6), dtype=torch.float64, device="cuda")
+    _lib.check(_lib.load().b2r_pcd_estimate_normals(knn._h, _lib.ptr(t), k, float(radius), _lib.ptr(nrm), 0, _lib.ptr(cov), _lib.stream_ptr()))
+    torch.cuda.synchronize()
+    knn.close()
+    rn, rcov = o3r.pcd_estimate_normals(xyz, k, radius)
+    assert np.array_equal(cov.cpu().numpy(), rcov)         # same neighbours, same summation order: bit-exact f64
+    n = nrm.cpu().numpy()
+    dots = np.einsum("ij,ij->i", n, rn)
+    assert np.abs(np.abs(dots) - 1.0).max() <= 1e-9
+    assert (dots > 0).mean() > 0.999                       # same branch of the solver, same sign
+    assert np.abs(np.linalg.norm(n, axis=1) - 1.0).max() < 1e-12
+    # the public call (what the reference scripts do), then orientation towards the camera: exact given equal inputs
+    pcd = o3d.geometry.PointCloud(t.clone())
+    pcd.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(radius, k) if radius > 0 else o3d.geometry.KDTreeSearchParamKNN(k))
+    assert np.array_equal(np.asarray(pcd.normals), n)
+    pcd.orient_normals_towards_camera_location(np.array([0.0, 0.0, 0.0]))
+    assert np.array_equal(np.asarray(pcd.normals), o3r.pcd_orient_normals(xyz, n))
+    assert (np.einsum("ij,ij->i", np.asarray(pcd.normals), -xyz) >= 0).all()
+    # a second estimate keeps the orientation of the existing normals (has_normals path)
+    before = np.asarray(pcd.normals).copy()
+    pcd.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(radius, k) if radius > 0 else o3d.geometry.KDTreeSearchParamKNN(k))
+    assert (np.einsum("ij,ij->i", np.asarray(pcd.normals), before) > 0).all()
+
+
+def test_estimate_normals_plane_known_answer():
+    rng = np.random.default_rng(2)
+    xy = rng.uniform(-1, 1, (5000, 2))
+    pts = np.c_[xy, 0.3 * xy[:, 0] + 0.1 * xy[:, 1] + 1.0]
+    pcd = o3d.geometry.PointCloud(dev(pts))
+    pcd.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(0.2, 30))
+    ref = np.array([0.3, 0.1, -1.0]) / np.linalg.norm([0.3, 0.1, -1.0])
+    assert np.abs(np.abs(np.asarray(pcd.normals) @ ref) - 1.0).max() < 1e-9
+    lonely = o3d.geometry.PointCloud(dev([[0.0, 0, 0], [10.0, 0, 0]]))      # fewer than 3 neighbours -> (0, 0, 1)
+    lonely.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(0.1, 30))
+    assert np.array_equal(np.asarray(lonely.normals), [[0, 0, 1.0], [0, 0, 1.0]])
+
+
+def test_remove_statistical_outlier_parity(o3r, cloud):
+    xyz = np.asarray(cloud.points)
+    rng = np.random.default_rng(9)
+    xyz = np.r_[xyz, rng.uniform(-2, 2, (40, 3)) + [0, 0, 2.0]]          # floating outliers
+    pcd = o3d.geometry.PointCloud(dev(xyz))
+    pcd.colors = o3d.utility.Vector3dVector(dev(rng.uniform(0, 1, xyz.shape)))
+    t = pcd.points.tensor
+    knn = _Knn(t, -1.0, 20)
+    keep = torch.empty((len(xyz),), dtype=torch.uint8, device="cuda")
+    idx = torch.empty((len(xyz),), dtype=torch.int32, device="cuda")
+    avg = torch.empty((len(xyz),), dtype=torch.float64, device="cuda")
+    m = C.c_int64(0)
+    _lib.check(_lib.load().b2r_pcd_statistical_outlier(knn._h, 20, 2.0, _lib.ptr(keep), _lib.ptr(idx), C.byref(m), _lib.ptr(avg), _lib.stream_ptr()))
+    knn.close()
+    rkeep, ravg = o3r.pcd_statistical_outlier(xyz, 20, 2.0)
+    assert np.array_equal(avg.cpu().numpy(), ravg)                         # mean neighbour distance: bit-exact
+    assert np.array_equal(keep.cpu().numpy().astype(bool), rkeep)          # inlier mask: bit-exact
+    assert m.value == int(rkeep.sum()) and np.array_equal(idx[:m.value].cpu().numpy(), np.nonzero(rkeep)[0])
+    assert rkeep[-40:].sum() < 10 and rkeep[:-40].mean() > 0.9
+    inl, ind = pcd.remove_statistical_outlier(nb_neighbors=20, std_ratio=2.0)                # the reference's call
+    assert np.array_equal(np.asarray(inl.points), xyz[rkeep]) and np.array_equal(np.asarray(ind.cpu()), np.nonzero(rkeep)[0])
+    assert np.array_equal(np.asarray(inl.colors), np.asarray(pcd.colors)[rkeep])
+    with pytest.raises(RuntimeError):
+        pcd.remove_statistical_outlier(0, 2.0)
+    with pytest.raises(RuntimeError):
+        pcd.remove_statistical_outlier(20, 0.0)
+
+
+@pytest.mark.parametrize("voxel", [0.01, 0.02, 0.25])
+def test_voxel_down_sample_parity(o3r, cloud, voxel):
+    xyz, col = np.asarray(cloud.points), np.asarray(cloud.colors)
+    nrm, _ = o3r.pcd_estimate_normals(xyz[:2000], 10, -1.0)
+    nrm = np.r_[nrm, np.tile([[0.0, 0.0, 1.0]], (len(xyz) - 2000, 1))]
+    nrm[5] = np.nan                                                        # upstream skips NaN normals in the sum
+    pcd = o3d.geometry.PointCloud(dev(xyz))
+    pcd.colors = o3d.utility.Vector3dVector(dev(col))
+    pcd.normals = o3d.utility.Vector3dVector(dev(nrm))
+    down = pcd.voxel_down_sample(voxel)
+    rp, rc, rn, rk = o3r.pcd_voxel_down_sample(xyz, voxel, col, nrm)
+    assert len(down.points) == len(rp) < len(xyz)
+    assert np.array_equal(down.voxel_index.cpu().numpy(), rk)              # voxel set (and canonical order): bit-exact
+    assert np.array_equal(np.asarray(down.points), rp)                     # sequential sums in input order: bit-exact
+    assert np.array_equal(np.asarray(down.colors), rc) and np.array_equal(np.asarray(down.normals), rn)
+    plain = o3d.geometry.PointCloud(dev(xyz)).voxel_down_sample(voxel)     # no colours / normals
+    assert np.array_equal(np.asarray(plain.points), rp) and not plain.has_colors() and not plain.has_normals()
+    with pytest.raises(RuntimeError):
+        pcd.voxel_down_sample(0.0)
+    assert np.array_equal(pcd.get_min_bound(), xyz.min(0)) and np.array_equal(pcd.get_max_bound(), xyz.max(0))
+
+
+def test_preprocess_then_icp_like_the_reference(o3r, small_kinect):
+    """GoodColorReconstruction.py:141-153 + 194-198: outlier removal -> voxel_down_sample -> estimate_normals ->
+    orient -> point-to-plane ICP between two consecutive frames recovers the relative motion."""
+    poses = syn.orbit_trajectory(30, yaw_sweep_deg=30.0)
+    K = intrinsic_of(small_kinect.depth_intr)
+    clouds = []
+    for p in (poses[0], poses[1]):
+        d, c = small_kinect.render_depth_aligned_rgb(p)
+        rgbd = o3d.geometry.RGBDImage.create_from_color_and_depth(o3d.geometry.Image(c), o3d.geometry.Image(d), 1000.0, 3.0, False)
+        pcd = o3d.geometry.PointCloud.create_from_rgbd_image(rgbd, K)
+        pcd, _ = pcd.remove_statistical_outlier(nb_neighbors=20, std_ratio=2.0)
+        pcd = pcd.voxel_down_sample(0.03)
+        pcd.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(radius=0.1, max_nn=30))
+        pcd.orient_normals_towards_camera_location(np.array([0, 0, 0]))
+        clouds.append(pcd)
+    src, tgt = clouds[1], clouds[0]
+    res = o3d.pipelines.registration.registration_icp(src, tgt, 0.06, np.eye(4), o3d.pipelines.registration.TransformationEstimationPointToPlane(),
+                                                      o3d.pipelines.registration.ICPConvergenceCriteria(max_iteration=50))
+    gt = np.linalg.inv(poses[0]) @ poses[1]
+    assert res.fitness > 0.8
+    assert np.linalg.norm(res.transformation[:3, 3] - gt[:3, 3]) < 5e-3
+    assert np.abs(res.transformation[:3, :3] - gt[:3, :3]).max() < 5e-3
