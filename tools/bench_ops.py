@@ -165,6 +165,28 @@ def main():
     out["icp_point_to_plane"] = {"source_points": len(p_src.points), "target_points": len(p_tgt.points), "iterations": int(r_icp.num_iterations), "ms": 1e3 * t_icp,
                                  "fitness": float(r_icp.fitness), "inlier_rmse": float(r_icp.inlier_rmse)}
 
+    # ---- f1: per-frame conditioning chain of the reference (GoodColorReconstruction.py:141-153) on one full NFOV frame
+    rgbd0 = o3d.geometry.RGBDImage.create_from_color_and_depth(o3d.geometry.Image(cc[0]), o3d.geometry.Image(dd[0]), 1000.0, 3.0, False)
+    full = o3d.geometry.PointCloud.create_from_rgbd_image(rgbd0, Kd)
+    nfull = len(full.points)
+
+    def t_wall(fn, iters=3):
+        fn(); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(iters):
+            r_ = fn()
+        torch.cuda.synchronize()
+        return 1e3 * (time.perf_counter() - t0) / iters, r_
+    ms_out, (inl, _) = t_wall(lambda: full.remove_statistical_outlier(nb_neighbors=20, std_ratio=2.0))
+    ms_vox, down = t_wall(lambda: inl.voxel_down_sample(0.01))
+    ms_nrm, _ = t_wall(lambda: down.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(radius=0.1, max_nn=30)))
+    ms_nrm2, _ = t_wall(lambda: down.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(radius=0.02, max_nn=30)))
+    ms_ori, _ = t_wall(lambda: down.orient_normals_towards_camera_location(np.array([0.0, 0.0, 0.0])))
+    out["pointcloud_conditioning_f1"] = {"input_points": nfull, "remove_statistical_outlier_20_2.0_ms": ms_out, "inliers": len(inl.points),
+                                         "voxel_down_sample_1cm_ms": ms_vox, "voxels": len(down.points),
+                                         "estimate_normals_hybrid_r0.1_nn30_ms": ms_nrm, "estimate_normals_hybrid_r0.02_nn30_ms": ms_nrm2,
+                                         "orient_normals_ms": ms_ori, "timing": "wall clock around the public call incl. index build and result allocation"}
+
     if a.cpu:   # bounded CPU-oracle samples (reported baseline only)
         from oracle import o3r
         Kt = (di["fx"], di["fy"], di["cx"], di["cy"])
