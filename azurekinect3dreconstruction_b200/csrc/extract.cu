@@ -226,83 +226,95 @@ __global__ void __launch_bounds__(256) extract_points_kernel(const VolView V, co
 
 __device__ __forceinline__ float apron_m(const float* A, int x, int y, int z) { return A[((x + 1) * MD + (y + 1)) * MD + (z + 1)]; }
 
-__device__ __forceinline__ void stage_complete(const float* A, unsigned char* C) {
-    for (int c = threadIdx.x; c < MC * MC * MC; c += blockDim.x) {
-        const int x = c / (MC * MC) - 1, y = (c / MC) % MC - 1, z = c % MC - 1;
-        bool ok = true;
+// ---- bit-parallel classification ----------------------------------------------------------------------------
+// Per (x, y) column of the staged apron (x, y in [-1, 16]) two 18-bit words over z in [-1, 16] (bit z + 1):
+//   VAL: the voxel has weight != 0;   NEG: it is valid and its TSDF is negative.
+// Per cube column (origins x, y in [-1, 15]) the word CC: bit z + 1 set iff all 8 corners of cube (x, y, z) are valid
+// (upstream skips a cube as soon as one corner has weight 0).  Edge ownership, cube activity and cube cases are then
+// AND / XOR / shift expressions over these words -- a thread classifies its 16-voxel z column in a few dozen integer
+// instructions and only loops over the (few) voxels that own a vertex and the (few) cubes that emit triangles.
+#define MCOLS (MD * MD)        // 324 voxel columns
+#define CCOLS (MC * MC)        // 289 cube columns
+
+__device__ __forceinline__ void stage_bits(const float* A, uint32_t* NEG, uint32_t* VAL, uint32_t* CC) {
+    for (int c = threadIdx.x; c < MCOLS; c += blockDim.x) {
+        const float* col = A + c * MD;
+        uint32_t n = 0, v = 0;
 #pragma unroll
-        for (int i = 0; i < 8; i++) {
-            const float f = apron_m(A, x + mc_shift[i][0], y + mc_shift[i][1], z + mc_shift[i][2]);
-            ok = ok && (f == f);
+        for (int z = 0; z < MD; z++) {
+            const float f = col[z];
+            v |= (f == f) ? (1u << z) : 0u;
+            n |= (f < 0.0f) ? (1u << z) : 0u;
         }
-        C[c] = ok ? 1 : 0;
+        NEG[c] = n; VAL[c] = v;
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < CCOLS; c += blockDim.x) {
+        const int cx = c / MC, cy = c - cx * MC;                       // cube origin (cx - 1, cy - 1)
+        const int b = cx * MD + cy;
+        const uint32_t v4 = VAL[b] & VAL[b + MD] & VAL[b + 1] & VAL[b + MD + 1];
+        CC[c] = v4 & (v4 >> 1);
     }
     __syncthreads();
 }
-__device__ __forceinline__ bool cube_complete(const unsigned char* C, int x, int y, int z) { return C[((x + 1) * MC + (y + 1)) * MC + (z + 1)] != 0; }
 
-__device__ __forceinline__ unsigned owned_edge_mask(const float* A, const unsigned char* C, int x, int y, int z) {
-    const float f0 = apron_m(A, x, y, z);
-    if (!(f0 == f0)) return 0;
-    const bool s0 = f0 < 0.0f;
-    unsigned m = 0;
-    {   // axis 0: cubes (x, y-{0,1}, z-{0,1})
-        const float f1 = apron_m(A, x + 1, y, z);
-        if (f1 == f1 && ((f1 < 0.0f) != s0) &&
-            (cube_complete(C, x, y, z) || cube_complete(C, x, y - 1, z) || cube_complete(C, x, y, z - 1) || cube_complete(C, x, y - 1, z - 1))) m |= 1u;
-    }
-    {   // axis 1: cubes (x-{0,1}, y, z-{0,1})
-        const float f1 = apron_m(A, x, y + 1, z);
-        if (f1 == f1 && ((f1 < 0.0f) != s0) &&
-            (cube_complete(C, x, y, z) || cube_complete(C, x - 1, y, z) || cube_complete(C, x, y, z - 1) || cube_complete(C, x - 1, y, z - 1))) m |= 2u;
-    }
-    {   // axis 2: cubes (x-{0,1}, y-{0,1}, z)
-        const float f1 = apron_m(A, x, y, z + 1);
-        if (f1 == f1 && ((f1 < 0.0f) != s0) &&
-            (cube_complete(C, x, y, z) || cube_complete(C, x - 1, y, z) || cube_complete(C, x, y - 1, z) || cube_complete(C, x - 1, y - 1, z))) m |= 4u;
-    }
-    return m;
+// Masks of thread (x, y), bit z for z in [0, 15]: m[a] = voxel (x, y, z) owns the vertex on its +axis-a edge;
+// act = cube (x, y, z) is complete and its corners do not all share a sign.  nn[4] = NEG words of the cube's columns
+// (x, y), (x+1, y), (x, y+1), (x+1, y+1) for the cube-case bits.
+__device__ __forceinline__ void column_masks(const uint32_t* NEG, const uint32_t* VAL, const uint32_t* CC, int x, int y, uint32_t* m,
+                                             uint32_t* act, uint32_t* nn) {
+    const int c0 = (x + 1) * MD + (y + 1);
+    const uint32_t n0 = NEG[c0], v0 = VAL[c0], nx = NEG[c0 + MD], vx = VAL[c0 + MD], ny = NEG[c0 + 1], vy = VAL[c0 + 1], nxy = NEG[c0 + MD + 1];
+    const int q = (x + 1) * MC + (y + 1);
+    const uint32_t c11 = CC[q], c01 = CC[q - MC], c10 = CC[q - 1], c00 = CC[q - MC - 1];
+    const uint32_t C0 = c11 | c10, C1 = c11 | c01, C2 = c11 | c01 | c10 | c00;
+    m[0] = (((n0 ^ nx) & v0 & vx & (C0 | (C0 << 1))) >> 1) & 0xFFFFu;      // cubes (x, y-{0,1}, z-{0,1})
+    m[1] = (((n0 ^ ny) & v0 & vy & (C1 | (C1 << 1))) >> 1) & 0xFFFFu;      // cubes (x-{0,1}, y, z-{0,1})
+    m[2] = (((n0 ^ (n0 >> 1)) & v0 & (v0 >> 1) & C2) >> 1) & 0xFFFFu;      // cubes (x-{0,1}, y-{0,1}, z)
+    uint32_t any = n0 | nx | ny | nxy, all = n0 & nx & ny & nxy;
+    any |= any >> 1; all &= all >> 1;
+    *act = ((c11 & any & ~all) >> 1) & 0xFFFFu;
+    nn[0] = n0; nn[1] = nx; nn[2] = ny; nn[3] = nxy;
 }
 
-__device__ __forceinline__ int cube_case(const float* A, const unsigned char* C, int x, int y, int z) {
-    if (!cube_complete(C, x, y, z)) return 0;
+// marching-cubes case of cube (x, y, z): bit i = corner mc_shift[i] is negative (Bourke corner order:
+// (0,0,0) (1,0,0) (1,1,0) (0,1,0) (0,0,1) (1,0,1) (1,1,1) (0,1,1))
+__device__ __forceinline__ int cube_case_bits(const uint32_t* nn, int z) {
     int cube = 0;
 #pragma unroll
-    for (int i = 0; i < 8; i++)
-        if (apron_m(A, x + mc_shift[i][0], y + mc_shift[i][1], z + mc_shift[i][2]) < 0.0f) cube |= 1 << i;
+    for (int i = 0; i < 8; i++) {
+        const uint32_t w = nn[mc_shift[i][0] + 2 * mc_shift[i][1]];
+        cube |= (int)((w >> (z + 1 + mc_shift[i][2])) & 1u) << i;
+    }
     return cube;
 }
 
-// pass 1: per-voxel vertex slots + per-unit vertex / triangle counts
+// pass 1: per-voxel vertex slots (written only where a vertex is owned) + per-unit vertex / triangle counts
 __global__ void __launch_bounds__(256) mesh_count_kernel(const VolView V, const int32_t* order, uint32_t* vinfo,
                                                          int32_t* unit_vcount, int32_t* unit_tcount) {
     __shared__ float A[MD * MD * MD];
-    __shared__ unsigned char C[MC * MC * MC];
+    __shared__ uint32_t NEG[MCOLS], VAL[MCOLS], CC[CCOLS];
     __shared__ int nb[27];
     __shared__ int ws[9];
     const int pos = blockIdx.x;
     const int unit = order[pos];
     stage_apron<-1, false>(V, unit, A, nb);
-    stage_complete(A, C);
+    stage_bits(A, NEG, VAL, CC);
     const int x = threadIdx.x >> 4, y = threadIdx.x & 15;
-    unsigned masks[16];
-    int vc = 0, tc = 0;
-#pragma unroll
-    for (int z = 0; z < 16; z++) {
-        const unsigned m = owned_edge_mask(A, C, x, y, z);
-        masks[z] = m;
-        vc += __popc(m);
-        const int cube = cube_case(A, C, x, y, z);
-        tc += mc_num_tris[cube];
-    }
+    uint32_t m[3], act, nn[4];
+    column_masks(NEG, VAL, CC, x, y, m, &act, nn);
+    const int vc = __popc(m[0]) + __popc(m[1]) + __popc(m[2]);
+    int tc = 0;
+    for (uint32_t a = act; a; a &= a - 1) tc += mc_num_tris[cube_case_bits(nn, __ffs(a) - 1)];
     int vtot, ttot;
     int voff = block_exclusive_scan(vc, &vtot, ws);
     block_exclusive_scan(tc, &ttot, ws);
     uint32_t* vi = vinfo + (int64_t)unit * B2R_UNIT_VOX + (x * 256 + y * 16);
-#pragma unroll
-    for (int z = 0; z < 16; z++) {
-        vi[z] = ((uint32_t)voff << 3) | masks[z];
-        voff += __popc(masks[z]);
+    for (uint32_t mm = m[0] | m[1] | m[2]; mm; mm &= mm - 1) {
+        const int z = __ffs(mm) - 1;
+        const uint32_t bits = ((m[0] >> z) & 1u) | (((m[1] >> z) & 1u) << 1) | (((m[2] >> z) & 1u) << 2);
+        vi[z] = ((uint32_t)voff << 3) | bits;
+        voff += __popc(bits);
     }
     if (threadIdx.x == 0) { unit_vcount[pos] = vtot; unit_tcount[pos] = ttot; }
 }
@@ -318,30 +330,30 @@ __global__ void __launch_bounds__(256) mesh_fill_kernel(const VolView V, const i
                                                         double* vtx, double* vcol, int32_t* tri, int32_t* ids,
                                                         int64_t capV, int64_t capF, int pos0, int64_t v0, int64_t t0) {
     __shared__ float A[MD * MD * MD];
-    __shared__ unsigned char C[MC * MC * MC];
+    __shared__ uint32_t NEG[MCOLS], VAL[MCOLS], CC[CCOLS];
     __shared__ int nb[27];
     __shared__ int ws[9];
     const int pos = blockIdx.x + pos0;   // a sharded handle fills its own contiguous range of the (owner, key) order
     const int unit = order[pos];
     stage_apron<-1, false>(V, unit, A, nb);
-    stage_complete(A, C);
+    stage_bits(A, NEG, VAL, CC);
     const int x = threadIdx.x >> 4, y = threadIdx.x & 15;
+    uint32_t m[3], act, nn[4];
+    column_masks(NEG, VAL, CC, x, y, m, &act, nn);
     const int kx = V.unit_keys[3 * unit], ky = V.unit_keys[3 * unit + 1], kz = V.unit_keys[3 * unit + 2];
     const double vl = V.voxel_length, hv = xdmul(0.5, vl);
     const int64_t vb = vbase_by_unit[unit];
     const uint32_t* vi = vinfo + (int64_t)unit * B2R_UNIT_VOX + (x * 256 + y * 16);
-    // ---- vertices
-#pragma unroll 1
-    for (int z = 0; z < 16; z++) {
+    // ---- vertices: only the voxels of this column that own one
+    for (uint32_t mm = m[0] | m[1] | m[2]; mm; mm &= mm - 1) {
+        const int z = __ffs(mm) - 1;
         const uint32_t info = vi[z];
-        const unsigned m = info & 7u;
-        if (!m) continue;
         int64_t o = vb + (info >> 3) - v0;   // compact output; vertex ids inside triangles stay global
         const float f0f = apron_m(A, x, y, z);
-        const float* v0 = V.pool + (int64_t)unit * V.unit_stride + (x * 256 + y * 16 + z);
+        const float* v0p = V.pool + (int64_t)unit * V.unit_stride + (x * 256 + y * 16 + z);
         const int e[3] = {kx * 16 + x, ky * 16 + y, kz * 16 + z};
         for (int a = 0; a < 3; a++) {
-            if (!(m & (1u << a))) continue;
+            if (!((m[a] >> z) & 1u)) continue;
             if (o < capV) {
                 int n[3] = {x, y, z};
                 n[a] += 1;
@@ -361,7 +373,7 @@ __global__ void __launch_bounds__(256) mesh_fill_kernel(const VolView V, const i
                     const float* v1 = V.pool + (int64_t)u1 * V.unit_stride + (lx * 256 + ly * 16 + lz);
 #pragma unroll
                     for (int c = 0; c < 3; c++) {
-                        const double c0 = xddiv((double)v0[(2 + c) * B2R_UNIT_VOX], 255.0), c1 = xddiv((double)v1[(2 + c) * B2R_UNIT_VOX], 255.0);
+                        const double c0 = xddiv((double)v0p[(2 + c) * B2R_UNIT_VOX], 255.0), c1 = xddiv((double)v1[(2 + c) * B2R_UNIT_VOX], 255.0);
                         vcol[3 * o + c] = xddiv(xdadd(xdmul(f1, c0), xdmul(f0, c1)), xdadd(f0, f1));
                     }
                 }
@@ -370,18 +382,16 @@ __global__ void __launch_bounds__(256) mesh_fill_kernel(const VolView V, const i
             o++;
         }
     }
-    // ---- triangles
-    int cases[16];
+    // ---- triangles: only the active cubes of this column
     int tc = 0;
-#pragma unroll
-    for (int z = 0; z < 16; z++) { cases[z] = cube_case(A, C, x, y, z); tc += mc_num_tris[cases[z]]; }
+    for (uint32_t a = act; a; a &= a - 1) tc += mc_num_tris[cube_case_bits(nn, __ffs(a) - 1)];
     int ttot;
     int toff = block_exclusive_scan(tc, &ttot, ws);
     if (ttot == 0) return;
     int64_t to = (int64_t)tbase[pos] + toff - t0;
-#pragma unroll 1
-    for (int z = 0; z < 16; z++) {
-        const int cube = cases[z];
+    for (uint32_t a = act; a; a &= a - 1) {
+        const int z = __ffs(a) - 1;
+        const int cube = cube_case_bits(nn, z);
         const int nt = mc_num_tris[cube];
         if (!nt) continue;
         int vid[12];

@@ -25,6 +25,25 @@
 #include <math.h>
 #include <string.h>
 
+// Temporaries come from the stream-ordered pool (cudaMallocAsync): with the release threshold raised once, repeated calls
+// reuse the same blocks instead of paying cudaMalloc / cudaFree (hundreds of microseconds each) per call.
+static cudaError_t pcd_alloc(void** p, size_t bytes, cudaStream_t stream) {
+    static bool pool_ready = false;
+    if (!pool_ready) {
+        int dev = 0;
+        cudaMemPool_t pool;
+        if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+            uint64_t keep = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+        pool_ready = true;
+    }
+    return cudaMallocAsync(p, bytes ? bytes : 1, stream);
+}
+template <typename T>
+static cudaError_t pcd_alloc(T** p, size_t bytes, cudaStream_t stream) { return pcd_alloc(reinterpret_cast<void**>(p), bytes, stream); }
+static void pcd_free(void* p, cudaStream_t stream) { if (p) cudaFreeAsync(p, stream); }
+
 namespace {
 
 #define PCD_KEY_EMPTY 0xFFFFFFFFFFFFFFFFull
@@ -186,7 +205,8 @@ static GridView view_of(const b2r_knn* h) {
 
 B2R_API void b2r_knn_destroy(b2r_knn* h) {
     if (!h) return;
-    cudaFree(h->pts); cudaFree(h->order); cudaFree(h->slots);
+    cudaStream_t stream = 0;
+    pcd_free(h->pts, stream); pcd_free(h->order, stream); pcd_free(h->slots, stream);
     delete h;
 }
 
@@ -205,12 +225,12 @@ B2R_API b2r_knn* b2r_knn_create(const double* xyz, int64_t n, double cell, int k
     size_t tmp_bytes = 0;
     auto fail = [&](const char* what, cudaError_t e) -> b2r_knn* {
         if (e != cudaSuccess) b2r_set_error("b2r_knn_create: %s: %s", what, cudaGetErrorString(e));
-        cudaFree(mm_dev); cudaFree(k_in); cudaFree(k_out); cudaFree(id_in); cudaFree(count_dev); cudaFree(tmp);
+        pcd_free(mm_dev, stream); pcd_free(k_in, stream); pcd_free(k_out, stream); pcd_free(id_in, stream); pcd_free(count_dev, stream); pcd_free(tmp, stream);
         b2r_knn_destroy(h);
         return nullptr;
     };
     cudaError_t e;
-    if ((e = cudaMalloc(&mm_dev, 6 * sizeof(double))) != cudaSuccess) return fail("alloc", e);
+    if ((e = pcd_alloc(&mm_dev, 6 * sizeof(double), stream)) != cudaSuccess) return fail("alloc", e);
     if (device_bounds(xyz, n, mm_dev, stream) != B2R_OK) return fail("bounds", cudaGetLastError());
     double mm[6];
     if ((e = cudaMemcpyAsync(mm, mm_dev, sizeof(mm), cudaMemcpyDeviceToHost, stream)) != cudaSuccess) return fail("bounds copy", e);
@@ -227,12 +247,12 @@ B2R_API b2r_knn* b2r_knn_create(const double* xyz, int64_t n, double cell, int k
         cell = sqrt(target_occ * area / (double)n);
         if (!(cell > 0.0)) cell = 1.0;
     }
-    if ((e = cudaMalloc(&k_in, n * 8)) != cudaSuccess || (e = cudaMalloc(&k_out, n * 8)) != cudaSuccess ||
-        (e = cudaMalloc(&id_in, n * 4)) != cudaSuccess || (e = cudaMalloc(&h->order, n * 4)) != cudaSuccess ||
-        (e = cudaMalloc(&count_dev, 4)) != cudaSuccess)
+    if ((e = pcd_alloc(&k_in, n * 8, stream)) != cudaSuccess || (e = pcd_alloc(&k_out, n * 8, stream)) != cudaSuccess ||
+        (e = pcd_alloc(&id_in, n * 4, stream)) != cudaSuccess || (e = pcd_alloc(&h->order, n * 4, stream)) != cudaSuccess ||
+        (e = pcd_alloc(&count_dev, 4, stream)) != cudaSuccess)
         return fail("alloc", e);
     cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k_in, k_out, id_in, h->order, (int)n, 0, 63, stream);
-    if ((e = cudaMalloc(&tmp, tmp_bytes)) != cudaSuccess) return fail("alloc", e);
+    if ((e = pcd_alloc(&tmp, tmp_bytes, stream)) != cudaSuccess) return fail("alloc", e);
     const unsigned grid = (unsigned)((n + 255) / 256);
     int32_t n_cells = 0;
     for (int attempt = 0; attempt < 4; attempt++) {
@@ -260,14 +280,14 @@ B2R_API b2r_knn* b2r_knn_create(const double* xyz, int64_t n, double cell, int k
     uint32_t nslots = 64;
     while (nslots < 2u * (uint32_t)n_cells) nslots <<= 1;
     h->nslots = nslots;
-    if ((e = cudaMalloc(&h->slots, (size_t)nslots * sizeof(CellSlot))) != cudaSuccess || (e = cudaMalloc(&h->pts, n * 24)) != cudaSuccess) return fail("alloc", e);
+    if ((e = pcd_alloc(&h->slots, (size_t)nslots * sizeof(CellSlot), stream)) != cudaSuccess || (e = pcd_alloc(&h->pts, n * 24, stream)) != cudaSuccess) return fail("alloc", e);
     clear_slots_kernel<<<(nslots + 255) / 256, 256, 0, stream>>>(h->slots, nslots);
     insert_heads_kernel<<<grid, 256, 0, stream>>>(k_out, n, h->slots, nslots - 1);
     insert_tails_kernel<<<grid, 256, 0, stream>>>(k_out, n, h->slots, nslots - 1);
     gather_points_kernel<<<grid, 256, 0, stream>>>(xyz, h->order, n, h->pts);
     if ((e = cudaGetLastError()) != cudaSuccess) return fail("launch", e);
     if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) return fail("sync", e);
-    cudaFree(mm_dev); cudaFree(k_in); cudaFree(k_out); cudaFree(id_in); cudaFree(count_dev); cudaFree(tmp);
+    pcd_free(mm_dev, stream); pcd_free(k_in, stream); pcd_free(k_out, stream); pcd_free(id_in, stream); pcd_free(count_dev, stream); pcd_free(tmp, stream);
     return h;
 }
 
@@ -619,9 +639,9 @@ B2R_API int b2r_pcd_statistical_outlier(const b2r_knn* h, int nb_neighbors, doub
     double *avg = avg_out, *st = nullptr;
     void* tmp = nullptr;
     int32_t* nsel = nullptr;
-    B2R_CUDA(cudaMalloc(&st, 4 * sizeof(double)));
-    B2R_CUDA(cudaMalloc(&nsel, 4));
-    if (!avg) B2R_CUDA(cudaMalloc(&avg, n * sizeof(double)));
+    B2R_CUDA(pcd_alloc(&st, 4 * sizeof(double), stream));
+    B2R_CUDA(pcd_alloc(&nsel, 4, stream));
+    if (!avg) B2R_CUDA(pcd_alloc(&avg, n * sizeof(double), stream));
     const unsigned grid = (unsigned)((n + 127) / 128);
     if (nb_neighbors <= 32) mean_distance_kernel<32><<<grid, 128, 0, stream>>>(G, nb_neighbors, avg);
     else mean_distance_kernel<128><<<grid, 128, 0, stream>>>(G, nb_neighbors, avg);
@@ -635,7 +655,7 @@ B2R_API int b2r_pcd_statistical_outlier(const b2r_knn* h, int nb_neighbors, doub
     cub::DeviceSelect::Flagged(nullptr, b2, counting, keep, inlier_idx, nsel, (int)n, stream);
     size_t tmp_bytes = b0 > b1 ? b0 : b1;
     if (b2 > tmp_bytes) tmp_bytes = b2;
-    B2R_CUDA(cudaMalloc(&tmp, tmp_bytes));
+    B2R_CUDA(pcd_alloc(&tmp, tmp_bytes, stream));
     B2R_CUDA(cub::DeviceReduce::Sum(tmp, tmp_bytes, it_pos, st, (int)n, stream));
     stat_mean_kernel<<<1, 1, 0, stream>>>(st, n);
     B2R_CUDA(cub::DeviceReduce::Sum(tmp, tmp_bytes, it_sq, st + 1, (int)n, stream));
@@ -646,8 +666,8 @@ B2R_API int b2r_pcd_statistical_outlier(const b2r_knn* h, int nb_neighbors, doub
     B2R_CUDA(cudaMemcpyAsync(&m, nsel, 4, cudaMemcpyDeviceToHost, stream));
     B2R_CUDA(cudaStreamSynchronize(stream));
     *n_inliers_host = m;
-    cudaFree(st); cudaFree(nsel); cudaFree(tmp);
-    if (!avg_out) cudaFree(avg);
+    pcd_free(st, stream); pcd_free(nsel, stream); pcd_free(tmp, stream);
+    if (!avg_out) pcd_free(avg, stream);
     return B2R_OK;
 }
 
@@ -735,12 +755,12 @@ B2R_API int b2r_pcd_voxel_down_sample(const double* xyz, const double* col, cons
     int32_t *id_in = nullptr, *order = nullptr, *seg = nullptr, *cnt = nullptr;
     void* tmp = nullptr;
     int rc = B2R_OK;
-    auto cleanup = [&]() { cudaFree(mm); cudaFree(k_in); cudaFree(k_out); cudaFree(id_in); cudaFree(order); cudaFree(seg); cudaFree(cnt); cudaFree(tmp); };
+    auto cleanup = [&]() { pcd_free(mm, stream); pcd_free(k_in, stream); pcd_free(k_out, stream); pcd_free(id_in, stream); pcd_free(order, stream); pcd_free(seg, stream); pcd_free(cnt, stream); pcd_free(tmp, stream); };
 #define PCD_TRY(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { b2r_set_error("b2r_pcd_voxel_down_sample: %s", cudaGetErrorString(e_)); cleanup(); return B2R_ERR_CUDA; } } while (0)
-    PCD_TRY(cudaMalloc(&mm, 6 * sizeof(double)));
-    PCD_TRY(cudaMalloc(&k_in, n * 8)); PCD_TRY(cudaMalloc(&k_out, n * 8));
-    PCD_TRY(cudaMalloc(&id_in, n * 4)); PCD_TRY(cudaMalloc(&order, n * 4)); PCD_TRY(cudaMalloc(&seg, n * 4));
-    PCD_TRY(cudaMalloc(&cnt, 8));
+    PCD_TRY(pcd_alloc(&mm, 6 * sizeof(double), stream));
+    PCD_TRY(pcd_alloc(&k_in, n * 8, stream)); PCD_TRY(pcd_alloc(&k_out, n * 8, stream));
+    PCD_TRY(pcd_alloc(&id_in, n * 4, stream)); PCD_TRY(pcd_alloc(&order, n * 4, stream)); PCD_TRY(pcd_alloc(&seg, n * 4, stream));
+    PCD_TRY(pcd_alloc(&cnt, 8, stream));
     PCD_TRY(cudaMemsetAsync(cnt, 0, 8, stream));
     if ((rc = device_bounds(xyz, n, mm, stream)) != B2R_OK) { cleanup(); return rc; }
     const unsigned grid = (unsigned)((n + 255) / 256);
@@ -751,7 +771,7 @@ B2R_API int b2r_pcd_voxel_down_sample(const double* xyz, const double* col, cons
     cub::DeviceRadixSort::SortPairs(nullptr, b0, k_in, k_out, id_in, order, (int)n, 0, 63, stream);
     cub::DeviceSelect::If(nullptr, b1, counting, seg, cnt, (int)n, is_head, stream);
     size_t tmp_bytes = b0 > b1 ? b0 : b1;
-    PCD_TRY(cudaMalloc(&tmp, tmp_bytes));
+    PCD_TRY(pcd_alloc(&tmp, tmp_bytes, stream));
     PCD_TRY(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, k_in, k_out, id_in, order, (int)n, 0, 63, stream));
     PCD_TRY(cub::DeviceSelect::If(tmp, tmp_bytes, counting, seg, cnt, (int)n, is_head, stream));
     int32_t hc[2] = {0, 0};
@@ -772,12 +792,12 @@ B2R_API int b2r_pcd_voxel_down_sample(const double* xyz, const double* col, cons
 B2R_API int b2r_pcd_bounds(const double* xyz, int64_t n, double* out6_host, cudaStream_t stream) {
     if (!xyz || !out6_host || n < 1) return B2R_ERR_BAD_ARG;
     double* mm = nullptr;
-    B2R_CUDA(cudaMalloc(&mm, 6 * sizeof(double)));
+    B2R_CUDA(pcd_alloc(&mm, 6 * sizeof(double), stream));
     int rc = device_bounds(xyz, n, mm, stream);
     if (rc == B2R_OK) {
         B2R_CUDA(cudaMemcpyAsync(out6_host, mm, 6 * sizeof(double), cudaMemcpyDeviceToHost, stream));
         B2R_CUDA(cudaStreamSynchronize(stream));
     }
-    cudaFree(mm);
+    pcd_free(mm, stream);
     return rc;
 }
