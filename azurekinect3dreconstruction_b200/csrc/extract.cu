@@ -49,23 +49,44 @@ __device__ __forceinline__ void stage_apron(const VolView& V, int unit, float* A
     }
     __syncthreads();
     const float nanv = __int_as_float(0x7fc00000);
-    for (int c = threadIdx.x; c < D * D * D; c += blockDim.x) {
-        const int ax = c / (D * D), ay = (c / D) % D, az = c % D;
-        int x = ax + LO, y = ay + LO, z = az + LO;
-        int ox = 1, oy = 1, oz = 1;
+    auto keep = [&](float t, float w) -> float {
+        bool ok = (w != 0.0f);
+        if (RANGE_CHECK) ok = ok && (t < 0.98f) && (t >= -0.98f);
+        return ok ? t : nanv;
+    };
+    // interior rows: every (x, y) column holds z = 0..15 of ONE unit, contiguous in both planes -> four 128-bit loads each
+    for (int i = threadIdx.x; i < D * D * 4; i += blockDim.x) {
+        const int c = i >> 2, part = i & 3;
+        const int ax = c / D, ay = c - ax * D;
+        int x = ax + LO, y = ay + LO, ox = 1, oy = 1;
         if (x < 0) { x += 16; ox = 0; } else if (x >= 16) { x -= 16; ox = 2; }
         if (y < 0) { y += 16; oy = 0; } else if (y >= 16) { y -= 16; oy = 2; }
-        if (z < 0) { z += 16; oz = 0; } else if (z >= 16) { z -= 16; oz = 2; }
-        const int u = nb[(ox * 3 + oy) * 3 + oz];
+        const int u = nb[(ox * 3 + oy) * 3 + 1];
+        float* dst = A + c * D + (0 - LO) + part * 4;
+        if (u >= 0) {
+            const float* base = V.pool + (int64_t)u * V.unit_stride + (x * 256 + y * 16 + part * 4);
+            const float4 t = __ldg(reinterpret_cast<const float4*>(base));
+            const float4 w = __ldg(reinterpret_cast<const float4*>(base + B2R_UNIT_VOX));
+            dst[0] = keep(t.x, w.x); dst[1] = keep(t.y, w.y); dst[2] = keep(t.z, w.z); dst[3] = keep(t.w, w.w);
+        } else {
+            dst[0] = nanv; dst[1] = nanv; dst[2] = nanv; dst[3] = nanv;
+        }
+    }
+    // caps: z = 16 (and z = -1 when the apron extends below) come from the units above / below
+    constexpr int NCAP = (LO < 0) ? 2 : 1;
+    for (int i = threadIdx.x; i < D * D * NCAP; i += blockDim.x) {
+        const int c = i / NCAP, top = (NCAP == 1) ? 1 : (i - c * NCAP);
+        const int ax = c / D, ay = c - ax * D;
+        int x = ax + LO, y = ay + LO, ox = 1, oy = 1;
+        if (x < 0) { x += 16; ox = 0; } else if (x >= 16) { x -= 16; ox = 2; }
+        if (y < 0) { y += 16; oy = 0; } else if (y >= 16) { y -= 16; oy = 2; }
+        const int u = nb[(ox * 3 + oy) * 3 + (top ? 2 : 0)];
         float f = nanv;
         if (u >= 0) {
-            const float* base = V.pool + (int64_t)u * V.unit_stride + (x * 256 + y * 16 + z);
-            const float t = base[0], w = base[B2R_UNIT_VOX];
-            bool ok = (w != 0.0f);
-            if (RANGE_CHECK) ok = ok && (t < 0.98f) && (t >= -0.98f);
-            if (ok) f = t;
+            const float* base = V.pool + (int64_t)u * V.unit_stride + (x * 256 + y * 16 + (top ? 0 : 15));
+            f = keep(__ldg(base), __ldg(base + B2R_UNIT_VOX));
         }
-        A[c] = f;
+        A[c * D + (top ? 16 - LO : 0)] = f;
     }
     __syncthreads();
 }
@@ -128,6 +149,7 @@ __device__ double tsdf_at(const VolView& V, double px, double py, double pz) {
 // ------------------------------------------------------------------------------------------------
 // surface points
 // ------------------------------------------------------------------------------------------------
+#define POINTS_CAP 2048
 template <bool FILL>
 __global__ void __launch_bounds__(256) extract_points_kernel(const VolView V, const int32_t* order, int32_t* unit_counts,
                                                              const int32_t* unit_offsets, double* xyz, double* rgb,
@@ -165,29 +187,44 @@ __global__ void __launch_bounds__(256) extract_points_kernel(const VolView V, co
     const int64_t base = (int64_t)unit_offsets[pos];
     const int kx = V.unit_keys[3 * unit], ky = V.unit_keys[3 * unit + 1], kz = V.unit_keys[3 * unit + 2];
     const double vl = V.voxel_length, hv = xdmul(0.5, vl);
-#pragma unroll 1
-    for (int z = 0; z < 16; z++) {
-        const unsigned m = masks[z];
-        if (!m) continue;
-        const int l[3] = {x, y, z};
-        const int kk[3] = {kx, ky, kz};
-        double p0[3];
+    // Few voxels carry a surface point: compact (voxel, axis) items into a shared list in output order, then consecutive
+    // threads take consecutive items -- full warps on the six f64 trilinear samples of each normal.
+    __shared__ uint16_t plist[POINTS_CAP];      // x << 10 | y << 6 | z << 2 | axis
+    for (int lbase = 0; lbase < total; lbase += POINTS_CAP) {
+        int li = offs - lbase;
 #pragma unroll
-        for (int i = 0; i < 3; i++) p0[i] = xdadd(xdadd(hv, xdmul(vl, (double)l[i])), xdmul((double)kk[i], V.unit_length));
-        const float f0 = A[(x * D + y) * D + z];
-        const float* v0 = V.pool + (int64_t)unit * V.unit_stride + (x * 256 + y * 16 + z);
-        for (int i = 0; i < 3; i++) {
-            if (!(m & (1u << i))) continue;
-            const int64_t o = base + offs;
-            offs++;
+        for (int z = 0; z < 16; z++) {
+            const unsigned m = masks[z];
+#pragma unroll
+            for (int i = 0; i < 3; i++)
+                if (m & (1u << i)) {
+                    if (li >= 0 && li < POINTS_CAP) plist[li] = (uint16_t)((x << 10) | (y << 6) | (z << 2) | i);
+                    li++;
+                }
+        }
+        __syncthreads();
+        const int cnt = min(POINTS_CAP, total - lbase);
+        for (int t = threadIdx.x; t < cnt; t += blockDim.x) {
+            const int64_t o = base + lbase + t;
             if (o >= capacity) continue;
-            int n[3] = {x, y, z};
+            const int it = plist[t];
+            const int px = it >> 10, py = (it >> 6) & 15, pz = (it >> 2) & 15, i = it & 3;
+            const int l[3] = {px, py, pz};
+            const int kk[3] = {kx, ky, kz};
+            double p0[3];
+#pragma unroll
+            for (int a = 0; a < 3; a++) p0[a] = xdadd(xdadd(hv, xdmul(vl, (double)l[a])), xdmul((double)kk[a], V.unit_length));
+            const float f0 = A[(px * D + py) * D + pz];
+            const float* v0 = V.pool + (int64_t)unit * V.unit_stride + (px * 256 + py * 16 + pz);
+            int n[3] = {px, py, pz};
             n[i] += 1;
             const float f1 = A[(n[0] * D + n[1]) * D + n[2]];
             const float r0 = fabsf(f0), r1 = fabsf(f1);
             double p[3] = {p0[0], p0[1], p0[2]};
-            const double p1i = xdadd(p0[i], vl);
-            p[i] = xddiv(xdadd(xdmul(p0[i], (double)r1), xdmul(p1i, (double)r0)), (double)xfadd(r0, r1));
+            const double p0i = i == 0 ? p0[0] : (i == 1 ? p0[1] : p0[2]);
+            const double p1i = xdadd(p0i, vl);
+            const double pi = xddiv(xdadd(xdmul(p0i, (double)r1), xdmul(p1i, (double)r0)), (double)xfadd(r0, r1));
+            if (i == 0) p[0] = pi; else if (i == 1) p[1] = pi; else p[2] = pi;
             xyz[3 * o] = p[0]; xyz[3 * o + 1] = p[1]; xyz[3 * o + 2] = p[2];
             if (rgb && V.planes == 5) {
                 int ux = 1, uy = 1, uz = 1, lx = n[0], ly = n[1], lz = n[2];
@@ -213,8 +250,9 @@ __global__ void __launch_bounds__(256) extract_points_kernel(const VolView V, co
                 if (len > 0.0) { g[0] = xddiv(g[0], len); g[1] = xddiv(g[1], len); g[2] = xddiv(g[2], len); }
                 nrm[3 * o] = g[0]; nrm[3 * o + 1] = g[1]; nrm[3 * o + 2] = g[2];
             }
-            if (ids) { ids[4 * o] = kx * 16 + x; ids[4 * o + 1] = ky * 16 + y; ids[4 * o + 2] = kz * 16 + z; ids[4 * o + 3] = i; }
+            if (ids) { ids[4 * o] = kx * 16 + px; ids[4 * o + 1] = ky * 16 + py; ids[4 * o + 2] = kz * 16 + pz; ids[4 * o + 3] = i; }
         }
+        __syncthreads();
     }
 }
 
@@ -324,13 +362,20 @@ __global__ void scatter_bases_kernel(const int32_t* order, const int32_t* scan, 
     if (i < n) by_unit[order[i]] = scan[i];
 }
 
-// pass 2: emit vertices (owner voxels) and triangles (cubes)
+// pass 2: emit vertices (owner voxels) and triangles (cubes).
+// Only ~1 % of the voxels own a vertex or an active cube, so the classified columns are first COMPACTED into shared-memory
+// work lists (block scans give every item its slot = its output rank), then consecutive threads process consecutive
+// items: full warps on the f64 interpolation instead of one or two live lanes per warp, and consecutive output rows.
+#define FILL_CAP 2048          // items per round (a unit holds at most 3 * 4096 vertices / 4096 cubes: processed in rounds)
 __global__ void __launch_bounds__(256) mesh_fill_kernel(const VolView V, const int32_t* order, const uint32_t* vinfo,
                                                         const int32_t* vbase_by_unit, const int32_t* tbase,
                                                         double* vtx, double* vcol, int32_t* tri, int32_t* ids,
                                                         int64_t capV, int64_t capF, int pos0, int64_t v0, int64_t t0) {
     __shared__ float A[MD * MD * MD];
     __shared__ uint32_t NEG[MCOLS], VAL[MCOLS], CC[CCOLS];
+    __shared__ uint16_t vlist[FILL_CAP];       // x << 10 | y << 6 | z << 2 | axis
+    __shared__ uint16_t clist[FILL_CAP];       // x << 8 | y << 4 | z
+    __shared__ uint16_t ctoff[FILL_CAP];       // triangle offset of the cube inside the unit (< 5 * 4096)
     __shared__ int nb[27];
     __shared__ int ws[9];
     const int pos = blockIdx.x + pos0;   // a sharded handle fills its own contiguous range of the (owner, key) order
@@ -342,82 +387,110 @@ __global__ void __launch_bounds__(256) mesh_fill_kernel(const VolView V, const i
     column_masks(NEG, VAL, CC, x, y, m, &act, nn);
     const int kx = V.unit_keys[3 * unit], ky = V.unit_keys[3 * unit + 1], kz = V.unit_keys[3 * unit + 2];
     const double vl = V.voxel_length, hv = xdmul(0.5, vl);
-    const int64_t vb = vbase_by_unit[unit];
-    const uint32_t* vi = vinfo + (int64_t)unit * B2R_UNIT_VOX + (x * 256 + y * 16);
-    // ---- vertices: only the voxels of this column that own one
-    for (uint32_t mm = m[0] | m[1] | m[2]; mm; mm &= mm - 1) {
-        const int z = __ffs(mm) - 1;
-        const uint32_t info = vi[z];
-        int64_t o = vb + (info >> 3) - v0;   // compact output; vertex ids inside triangles stay global
-        const float f0f = apron_m(A, x, y, z);
-        const float* v0p = V.pool + (int64_t)unit * V.unit_stride + (x * 256 + y * 16 + z);
-        const int e[3] = {kx * 16 + x, ky * 16 + y, kz * 16 + z};
-        for (int a = 0; a < 3; a++) {
-            if (!((m[a] >> z) & 1u)) continue;
-            if (o < capV) {
-                int n[3] = {x, y, z};
-                n[a] += 1;
-                const float f1f = apron_m(A, n[0], n[1], n[2]);
-                const double f0 = fabs((double)f0f), f1 = fabs((double)f1f);
-                double pt[3];
+    const int64_t vb = (int64_t)vbase_by_unit[unit] - v0;   // compact output; vertex ids inside triangles stay global
+
+    // ---- vertices: rank inside the unit = (x, y) column order, then z, then axis -- the numbering of the count pass
+    int vtot;
+    const int voff = block_exclusive_scan(__popc(m[0]) + __popc(m[1]) + __popc(m[2]), &vtot, ws);
+    for (int base = 0; base < vtot; base += FILL_CAP) {
+        int li = voff - base;
+        for (uint32_t mm = m[0] | m[1] | m[2]; mm; mm &= mm - 1) {
+            const int z = __ffs(mm) - 1;
 #pragma unroll
-                for (int i = 0; i < 3; i++) pt[i] = xdadd(hv, xdmul(vl, (double)e[i]));
-                pt[a] = xdadd(pt[a], xddiv(xdmul(f0, vl), xdadd(f0, f1)));
-                vtx[3 * o] = pt[0]; vtx[3 * o + 1] = pt[1]; vtx[3 * o + 2] = pt[2];
-                if (vcol && V.planes == 5) {
-                    int ux = 1, uy = 1, uz = 1, lx = n[0], ly = n[1], lz = n[2];
-                    if (lx >= 16) { lx -= 16; ux = 2; }
-                    if (ly >= 16) { ly -= 16; uy = 2; }
-                    if (lz >= 16) { lz -= 16; uz = 2; }
-                    const int u1 = nb[(ux * 3 + uy) * 3 + uz];
-                    const float* v1 = V.pool + (int64_t)u1 * V.unit_stride + (lx * 256 + ly * 16 + lz);
-#pragma unroll
-                    for (int c = 0; c < 3; c++) {
-                        const double c0 = xddiv((double)v0p[(2 + c) * B2R_UNIT_VOX], 255.0), c1 = xddiv((double)v1[(2 + c) * B2R_UNIT_VOX], 255.0);
-                        vcol[3 * o + c] = xddiv(xdadd(xdmul(f1, c0), xdmul(f0, c1)), xdadd(f0, f1));
-                    }
+            for (int a = 0; a < 3; a++)
+                if ((m[a] >> z) & 1u) {
+                    if (li >= 0 && li < FILL_CAP) vlist[li] = (uint16_t)((x << 10) | (y << 6) | (z << 2) | a);
+                    li++;
                 }
-                if (ids) { ids[4 * o] = e[0]; ids[4 * o + 1] = e[1]; ids[4 * o + 2] = e[2]; ids[4 * o + 3] = a; }
-            }
-            o++;
         }
+        __syncthreads();
+        const int cnt = min(FILL_CAP, vtot - base);
+        for (int t = threadIdx.x; t < cnt; t += blockDim.x) {
+            const int64_t o = vb + base + t;
+            if (o >= capV) continue;
+            const int it = vlist[t];
+            const int px = it >> 10, py = (it >> 6) & 15, pz = (it >> 2) & 15, a = it & 3;
+            int n[3] = {px, py, pz};
+            n[a] += 1;
+            const float f0f = apron_m(A, px, py, pz), f1f = apron_m(A, n[0], n[1], n[2]);
+            const double f0 = fabs((double)f0f), f1 = fabs((double)f1f);
+            const int e[3] = {kx * 16 + px, ky * 16 + py, kz * 16 + pz};
+            double pt[3];
+#pragma unroll
+            for (int i = 0; i < 3; i++) pt[i] = xdadd(hv, xdmul(vl, (double)e[i]));
+            const double step = xddiv(xdmul(f0, vl), xdadd(f0, f1));
+            if (a == 0) pt[0] = xdadd(pt[0], step); else if (a == 1) pt[1] = xdadd(pt[1], step); else pt[2] = xdadd(pt[2], step);
+            vtx[3 * o] = pt[0]; vtx[3 * o + 1] = pt[1]; vtx[3 * o + 2] = pt[2];
+            if (vcol && V.planes == 5) {
+                int ux = 1, uy = 1, uz = 1, lx = n[0], ly = n[1], lz = n[2];
+                if (lx >= 16) { lx -= 16; ux = 2; }
+                if (ly >= 16) { ly -= 16; uy = 2; }
+                if (lz >= 16) { lz -= 16; uz = 2; }
+                const int u1 = nb[(ux * 3 + uy) * 3 + uz];
+                const float* p0 = V.pool + (int64_t)unit * V.unit_stride + (px * 256 + py * 16 + pz);
+                const float* p1 = V.pool + (int64_t)u1 * V.unit_stride + (lx * 256 + ly * 16 + lz);
+#pragma unroll
+                for (int c = 0; c < 3; c++) {
+                    const double c0 = xddiv((double)p0[(2 + c) * B2R_UNIT_VOX], 255.0), c1 = xddiv((double)p1[(2 + c) * B2R_UNIT_VOX], 255.0);
+                    vcol[3 * o + c] = xddiv(xdadd(xdmul(f1, c0), xdmul(f0, c1)), xdadd(f0, f1));
+                }
+            }
+            if (ids) { ids[4 * o] = e[0]; ids[4 * o + 1] = e[1]; ids[4 * o + 2] = e[2]; ids[4 * o + 3] = a; }
+        }
+        __syncthreads();
     }
-    // ---- triangles: only the active cubes of this column
+
+    // ---- triangles: the active cubes, compacted the same way
     int tc = 0;
     for (uint32_t a = act; a; a &= a - 1) tc += mc_num_tris[cube_case_bits(nn, __ffs(a) - 1)];
-    int ttot;
-    int toff = block_exclusive_scan(tc, &ttot, ws);
+    int ttot, ctot;
+    const int toff = block_exclusive_scan(tc, &ttot, ws);
     if (ttot == 0) return;
-    int64_t to = (int64_t)tbase[pos] + toff - t0;
-    for (uint32_t a = act; a; a &= a - 1) {
-        const int z = __ffs(a) - 1;
-        const int cube = cube_case_bits(nn, z);
-        const int nt = mc_num_tris[cube];
-        if (!nt) continue;
-        int vid[12];
-        const int em = mc_edge_table[cube];
+    const int coff = block_exclusive_scan(__popc(act), &ctot, ws);
+    const int64_t tb = (int64_t)tbase[pos] - t0;
+    for (int base = 0; base < ctot; base += FILL_CAP) {
+        int li = coff - base, to = toff;
+        for (uint32_t a = act; a; a &= a - 1) {
+            const int z = __ffs(a) - 1;
+            if (li >= 0 && li < FILL_CAP) { clist[li] = (uint16_t)((x << 8) | (y << 4) | z); ctoff[li] = (uint16_t)to; }
+            to += mc_num_tris[cube_case_bits(nn, z)];
+            li++;
+        }
+        __syncthreads();
+        const int cnt = min(FILL_CAP, ctot - base);
+        for (int t = threadIdx.x; t < cnt; t += blockDim.x) {
+            const int it = clist[t];
+            const int px = it >> 8, py = (it >> 4) & 15, pz = it & 15;
+            const int c0 = (px + 1) * MD + (py + 1);
+            const uint32_t cn[4] = {NEG[c0], NEG[c0 + MD], NEG[c0 + 1], NEG[c0 + MD + 1]};
+            const int cube = cube_case_bits(cn, pz);
+            const int nt = mc_num_tris[cube];
+            if (!nt) continue;
+            int vid[12];
+            const int em = mc_edge_table[cube];
 #pragma unroll 1
-        for (int i = 0; i < 12; i++) {
-            vid[i] = -1;
-            if (!(em & (1 << i))) continue;
-            int ox = x + mc_edge_shift[i][0], oy = y + mc_edge_shift[i][1], oz = z + mc_edge_shift[i][2];
-            const int axis = mc_edge_shift[i][3];
-            int ux = 1, uy = 1, uz = 1;
-            if (ox >= 16) { ox -= 16; ux = 2; }
-            if (oy >= 16) { oy -= 16; uy = 2; }
-            if (oz >= 16) { oz -= 16; uz = 2; }
-            const int u = nb[(ux * 3 + uy) * 3 + uz];
-            const uint32_t info = vinfo[(int64_t)u * B2R_UNIT_VOX + (ox * 256 + oy * 16 + oz)];
-            vid[i] = vbase_by_unit[u] + (int)(info >> 3) + __popc(info & ((1u << axis) - 1u));
-        }
-        for (int t = 0; t < nt; t++) {
-            if (to < capF) {
-                tri[3 * to] = vid[mc_tri_table[cube][3 * t]];
-                tri[3 * to + 1] = vid[mc_tri_table[cube][3 * t + 2]];
-                tri[3 * to + 2] = vid[mc_tri_table[cube][3 * t + 1]];
+            for (int i = 0; i < 12; i++) {
+                vid[i] = -1;
+                if (!(em & (1 << i))) continue;
+                int ox = px + mc_edge_shift[i][0], oy = py + mc_edge_shift[i][1], oz = pz + mc_edge_shift[i][2];
+                const int axis = mc_edge_shift[i][3];
+                int ux = 1, uy = 1, uz = 1;
+                if (ox >= 16) { ox -= 16; ux = 2; }
+                if (oy >= 16) { oy -= 16; uy = 2; }
+                if (oz >= 16) { oz -= 16; uz = 2; }
+                const int u = nb[(ux * 3 + uy) * 3 + uz];
+                const uint32_t info = vinfo[(int64_t)u * B2R_UNIT_VOX + (ox * 256 + oy * 16 + oz)];
+                vid[i] = vbase_by_unit[u] + (int)(info >> 3) + __popc(info & ((1u << axis) - 1u));
             }
-            to++;
+            int64_t to2 = tb + ctoff[t];
+            for (int k = 0; k < nt; k++, to2++) {
+                if (to2 >= capF) break;
+                tri[3 * to2] = vid[mc_tri_table[cube][3 * k]];
+                tri[3 * to2 + 1] = vid[mc_tri_table[cube][3 * k + 2]];
+                tri[3 * to2 + 2] = vid[mc_tri_table[cube][3 * k + 1]];
+            }
         }
+        __syncthreads();
     }
 }
 
@@ -454,6 +527,7 @@ int carve(b2r_tsdf* h, int n, bool mesh, Scratch* S) {
     const size_t o_vb = take((size_t)n * 4);
     const size_t o_cub = take(cub_bytes);
     const size_t o_vi = mesh ? take((size_t)n * B2R_UNIT_VOX * 4) : 0;
+    if (!mesh || h->scratch_bytes < total) h->mesh_gen = 0;   // the scratch is about to be reused / reallocated
     int rc = b2r_tsdf_ensure_scratch(h, total);
     if (rc != B2R_OK) return rc;
     char* b = (char*)h->scratch;
@@ -575,32 +649,41 @@ B2R_API int b2r_tsdf_extract_mesh_sharded(b2r_tsdf* h, double* vtx, double* vcol
     rc = carve(h, n, true, &S);
     if (rc != B2R_OK) return rc;
     int own[2];
-    rc = sorted_order(h, n, S, own, stream);
-    if (rc != B2R_OK) return rc;
-    const VolView V = make_view(h);
-    // the count pass covers EVERY unit the handle holds (own + imported ghosts): it fixes the global vertex
-    // numbering, which a cube needs for edges owned by a neighbouring unit of another rank
-    mesh_count_kernel<<<n, 256, 0, stream>>>(V, S.order, S.vinfo, S.cnt_a, S.cnt_b);
-    B2R_CHECK_LAUNCH();
-    B2R_CUDA(cudaMemsetAsync(S.cnt_a + n, 0, 4, stream));
-    B2R_CUDA(cudaMemsetAsync(S.cnt_b + n, 0, 4, stream));
-    size_t tmp = S.cub_bytes;
-    B2R_CUDA(cub::DeviceScan::ExclusiveSum(S.cub_tmp, tmp, S.cnt_a, S.scan_a, n + 1, stream));
-    tmp = S.cub_bytes;
-    B2R_CUDA(cub::DeviceScan::ExclusiveSum(S.cub_tmp, tmp, S.cnt_b, S.scan_b, n + 1, stream));
     int32_t v01[2] = {0, 0}, t01[2] = {0, 0};
-    B2R_CUDA(cudaMemcpyAsync(&v01[0], S.scan_a + own[0], 4, cudaMemcpyDeviceToHost, stream));
-    B2R_CUDA(cudaMemcpyAsync(&v01[1], S.scan_a + own[1], 4, cudaMemcpyDeviceToHost, stream));
-    B2R_CUDA(cudaMemcpyAsync(&t01[0], S.scan_b + own[0], 4, cudaMemcpyDeviceToHost, stream));
-    B2R_CUDA(cudaMemcpyAsync(&t01[1], S.scan_b + own[1], 4, cudaMemcpyDeviceToHost, stream));
-    B2R_CUDA(cudaStreamSynchronize(stream));
+    const VolView V = make_view(h);
+    if (h->mesh_gen == h->generation && h->mesh_n == n) {
+        // second call of the two-call protocol on an unchanged volume: order, vertex slots and scans are still in scratch
+        own[0] = h->mesh_own[0]; own[1] = h->mesh_own[1];
+        v01[0] = h->mesh_v01[0]; v01[1] = h->mesh_v01[1]; t01[0] = h->mesh_t01[0]; t01[1] = h->mesh_t01[1];
+    } else {
+        rc = sorted_order(h, n, S, own, stream);
+        if (rc != B2R_OK) return rc;
+        // the count pass covers EVERY unit the handle holds (own + imported ghosts): it fixes the global vertex
+        // numbering, which a cube needs for edges owned by a neighbouring unit of another rank
+        mesh_count_kernel<<<n, 256, 0, stream>>>(V, S.order, S.vinfo, S.cnt_a, S.cnt_b);
+        B2R_CHECK_LAUNCH();
+        B2R_CUDA(cudaMemsetAsync(S.cnt_a + n, 0, 4, stream));
+        B2R_CUDA(cudaMemsetAsync(S.cnt_b + n, 0, 4, stream));
+        size_t tmp = S.cub_bytes;
+        B2R_CUDA(cub::DeviceScan::ExclusiveSum(S.cub_tmp, tmp, S.cnt_a, S.scan_a, n + 1, stream));
+        tmp = S.cub_bytes;
+        B2R_CUDA(cub::DeviceScan::ExclusiveSum(S.cub_tmp, tmp, S.cnt_b, S.scan_b, n + 1, stream));
+        scatter_bases_kernel<<<(n + 255) / 256, 256, 0, stream>>>(S.order, S.scan_a, S.vbase_by_unit, n);
+        B2R_CHECK_LAUNCH();
+        B2R_CUDA(cudaMemcpyAsync(&v01[0], S.scan_a + own[0], 4, cudaMemcpyDeviceToHost, stream));
+        B2R_CUDA(cudaMemcpyAsync(&v01[1], S.scan_a + own[1], 4, cudaMemcpyDeviceToHost, stream));
+        B2R_CUDA(cudaMemcpyAsync(&t01[0], S.scan_b + own[0], 4, cudaMemcpyDeviceToHost, stream));
+        B2R_CUDA(cudaMemcpyAsync(&t01[1], S.scan_b + own[1], 4, cudaMemcpyDeviceToHost, stream));
+        B2R_CUDA(cudaStreamSynchronize(stream));
+        h->mesh_gen = h->generation; h->mesh_n = n;
+        h->mesh_own[0] = own[0]; h->mesh_own[1] = own[1];
+        h->mesh_v01[0] = v01[0]; h->mesh_v01[1] = v01[1]; h->mesh_t01[0] = t01[0]; h->mesh_t01[1] = t01[1];
+    }
     const int32_t tv = v01[1] - v01[0], tf = t01[1] - t01[0];
     *nV = tv; *nF = tf;
     if (vertex_base) *vertex_base = v01[0];
     if (!vtx || !tri || capV < tv || capF < tf) { b2r_set_error("extract_mesh: need capacity V=%d F=%d", tv, tf); return B2R_ERR_CAPACITY; }
     if (tv == 0 || own[1] == own[0]) return B2R_OK;
-    scatter_bases_kernel<<<(n + 255) / 256, 256, 0, stream>>>(S.order, S.scan_a, S.vbase_by_unit, n);
-    B2R_CHECK_LAUNCH();
     mesh_fill_kernel<<<own[1] - own[0], 256, 0, stream>>>(V, S.order, S.vinfo, S.vbase_by_unit, S.scan_b, vtx, h->planes == 5 ? vcol : nullptr, tri, ids,
                                                         capV, capF, own[0], (int64_t)v01[0], (int64_t)t01[0]);
     B2R_CHECK_LAUNCH();

@@ -621,6 +621,7 @@ B2R_API b2r_tsdf* b2r_tsdf_create(double voxel_length, double sdf_trunc, int col
     b2r_tsdf* h = new (std::nothrow) b2r_tsdf();
     if (!h) return nullptr;
     memset(h, 0, sizeof(*h));
+    h->generation = 1;   // mesh_gen == 0 never matches: the extraction cache starts invalid
     h->voxel_length = voxel_length; h->sdf_trunc = sdf_trunc;
     h->unit_length = voxel_length * unit_resolution;
     h->color_type = color_type; h->res = unit_resolution; h->stride = depth_sampling_stride;
@@ -694,6 +695,7 @@ B2R_API int b2r_tsdf_reset(b2r_tsdf* h, cudaStream_t stream) {
     B2R_CHECK_LAUNCH();
     B2R_CUDA(cudaMemsetAsync(h->counters, 0, B2R_C_WORDS * 4, stream));
     h->q = 0; h->pending = 0; h->batches = 0;
+    h->generation++;
     return B2R_OK;
 }
 
@@ -756,6 +758,7 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
     // upstream: "[ScalableTSDFVolume::Integrate] Unsupported image format."
     if (h->color_type == 1 && (!color || (color_channels != 3 && color_channels != 4))) { b2r_set_error("[ScalableTSDFVolume::Integrate] Unsupported image format."); return B2R_ERR_FORMAT; }
     if (h->color_type == 2 && !gray) { b2r_set_error("[ScalableTSDFVolume::Integrate] Unsupported image format."); return B2R_ERR_FORMAT; }
+    h->generation++;
     const size_t npx = (size_t)W * H;
     if (h->texel_px < npx) {
         int rc = b2r_tsdf_flush_pending(h, stream);
@@ -1030,6 +1033,7 @@ B2R_API int b2r_tsdf_import_units(b2r_tsdf* h, const int32_t* keys3, int64_t n, 
     B2RDeviceGuard g(h->device);
     int rc = b2r_tsdf_flush_pending(h, stream);
     if (rc != B2R_OK) return rc;
+    h->generation++;
     rc = b2r_tsdf_ensure_scratch(h, (size_t)n * 4);
     if (rc != B2R_OK) return rc;
     int32_t* ids = (int32_t*)h->scratch;
