@@ -173,3 +173,87 @@ class ShardedTSDFVolume:
     def extract_point_cloud(self) -> PointCloud:
         part = phase_extract(self.local, self._gather(phase_export(self.local)), "points")
         return merge_point_parts(self._gather(part))
+
+
+# ---- host-frame ingest at world > 1: upload 1/world per rank over PCIe, exchange over NVLink -----------------------
+def superchunk_plan(n_frames: int, world: int, per: int):
+    """Frames are consumed in super-chunks of world * per; inside super-chunk i rank r uploads the `per` consecutive
+    frames starting at i * world * per + r * per, so the rank-major all-gather buffer is in GLOBAL FRAME ORDER (fusion
+    order decides the running averages bit for bit).  Returns [(first_frame, n_valid, [(f0, f1) per rank])]."""
+    S = world * per
+    plan = []
+    for f_start in range(0, n_frames, S):
+        n_valid = min(S, n_frames - f_start)
+        ranges = []
+        for r in range(world):
+            f0 = min(f_start + r * per, f_start + n_valid)
+            ranges.append((f0, min(f0 + per, f_start + n_valid)))
+        plan.append((f_start, n_valid, ranges))
+    return plan
+
+
+class HostFrameExchange:
+    """north_star: "each frame's depth/color/pose is broadcast and each rank integrates only its own blocks".
+    When the frames start in HOST memory, pushing every frame through every GPU's PCIe link would cap the job at one
+    link's bandwidth whatever the GPU count.  Instead rank r copies only its 1/world share host->device (pinned,
+    asynchronous, on a copy stream), and one NCCL all-gather per super-chunk hands every rank all frames over
+    NVLink/NVSwitch; the next super-chunk's upload overlaps the current gather + integration (double buffering).
+    `consume(depth, color, first_frame, n_valid)` receives device tensors in global frame order."""
+
+    def __init__(self, frame_shape, color_channels: int, per: int = 8, group=None, device=None):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.per, (self.H, self.W), self.ch = int(per), frame_shape, int(color_channels)
+        self.device = device
+        cuda = device is not None and torch.device(device).type == "cuda"
+        S = self.per * self.world
+        mk = lambda n, shape, dt: [torch.zeros((n,) + shape, dtype=dt, device=device) for _ in range(2)]
+        self.ld, self.lc = mk(self.per, (self.H, self.W), torch.int16), mk(self.per, (self.H, self.W, self.ch), torch.uint8)
+        self.gd, self.gc = mk(S, (self.H, self.W), torch.int16), mk(S, (self.H, self.W, self.ch), torch.uint8)
+        self.copy_stream = torch.cuda.Stream(device=device) if cuda else None
+        self.uploaded = [torch.cuda.Event() for _ in range(2)] if cuda else None
+        self.consumed = [torch.cuda.Event() for _ in range(2)] if cuda else None
+        self.bytes_uploaded = 0
+
+    def _upload(self, slot, depth_h, color_h, f0, f1):
+        n = f1 - f0
+        if self.copy_stream is None:
+            if n > 0:
+                self.ld[slot][:n].copy_(depth_h[f0:f1].view(torch.int16)); self.lc[slot][:n].copy_(color_h[f0:f1])
+        else:
+            with torch.cuda.stream(self.copy_stream):
+                self.copy_stream.wait_event(self.consumed[slot])       # the gather that read this slot two rounds ago
+                if n > 0:
+                    self.ld[slot][:n].copy_(depth_h[f0:f1].view(torch.int16), non_blocking=True)
+                    self.lc[slot][:n].copy_(color_h[f0:f1], non_blocking=True)
+                self.uploaded[slot].record(self.copy_stream)
+        self.bytes_uploaded += n * self.H * self.W * (2 + self.ch)
+
+    def run(self, depth_h: torch.Tensor, color_h: torch.Tensor, consume) -> None:
+        """depth_h (F,H,W) uint16, color_h (F,H,W,ch) uint8 -- pinned host tensors (identical on every rank)."""
+        plan = superchunk_plan(int(depth_h.shape[0]), self.world, self.per)
+        if not plan:
+            return
+        self._upload(0, depth_h, color_h, *plan[0][2][self.rank])
+        for i, (f_start, n_valid, _) in enumerate(plan):
+            slot = i & 1
+            if i + 1 < len(plan):
+                self._upload(slot ^ 1, depth_h, color_h, *plan[i + 1][2][self.rank])
+            if self.copy_stream is not None:
+                torch.cuda.current_stream().wait_event(self.uploaded[slot])
+            self.dist.all_gather_into_tensor(self.gd[slot].view(torch.uint8).reshape(-1), self.ld[slot].view(torch.uint8).reshape(-1), group=self.group)
+            self.dist.all_gather_into_tensor(self.gc[slot].reshape(-1), self.lc[slot].reshape(-1), group=self.group)
+            if self.copy_stream is not None:
+                self.consumed[slot].record(torch.cuda.current_stream())
+            consume(self.gd[slot][:n_valid].view(torch.uint16), self.gc[slot][:n_valid], f_start, n_valid)
+
+
+def integrate_host_frames(vol: ScalableTSDFVolume, depth_h: torch.Tensor, color_h: torch.Tensor, intrinsic, extrinsics,
+                          depth_scale: float = 1000.0, depth_trunc: float = 3.0, exchange: Optional[HostFrameExchange] = None) -> None:
+    """integrate_raw for HOST frames on a sharded volume: PCIe carries each frame once per JOB (not once per rank)."""
+    if exchange is None or exchange.world == 1:
+        vol.integrate_raw(depth_h, color_h, intrinsic, extrinsics, depth_scale, depth_trunc)
+        return
+    E = np.asarray(extrinsics, dtype=np.float64).reshape(-1, 4, 4)
+    exchange.run(depth_h, color_h, lambda d, c, f0, n: vol.integrate_raw(d, c, intrinsic, E[f0:f0 + n], depth_scale, depth_trunc))

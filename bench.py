@@ -292,9 +292,19 @@ def main():
     rgb_h = rgb.cpu().pin_memory()
     d2h_bytes = 5 * 8
 
+    # world > 1: every rank needs every frame, but PCIe carries each frame only ONCE per job -- rank r uploads its
+    # 1/world share and one NCCL all-gather per super-chunk distributes it over NVLink (pipelines/sharded.py)
+    exchange = None
+    if world > 1:
+        from azurekinect3dreconstruction_b200.pipelines import sharded
+        exchange = sharded.HostFrameExchange((H, W), 3, per=int(os.environ.get("B2R_EXCHANGE_PER", "8")), device=dev)
+
     def step_e2e():
         vol.reset()
-        vol.integrate_raw(depth_h, rgb_h, K, E, DEPTH_SCALE, DEPTH_TRUNC)
+        if exchange is None:
+            vol.integrate_raw(depth_h, rgb_h, K, E, DEPTH_SCALE, DEPTH_TRUNC)
+        else:
+            sharded.integrate_host_frames(vol, depth_h, rgb_h, K, E, DEPTH_SCALE, DEPTH_TRUNC, exchange=exchange)
         vol.stats()            # fuses what is pending + D2H read of the step's result (units allocated / voxels updated)
 
     for _ in range(3):
@@ -319,8 +329,11 @@ def main():
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": workload_config(args, {"sharding": "unit-key hash over %d rank(s)" % world, "units_allocated_rank0": st["num_units"]}),
                 "roofline": roofline, "cpu_baseline": cpu,
-                "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-                        "ms_per_step": ms_e2e / args.steps},
+                "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes * world,
+                        "ms_per_step": ms_e2e / args.steps,
+                        "ingest": ("host frames -> one GPU over PCIe (3-deep staged ring)" if world == 1 else
+                                   "each rank uploads 1/%d of the frames over its PCIe link; NCCL all-gather over NVLink hands every rank all frames "
+                                   "(h2d_bytes_per_step is the whole job's)" % world)},
                 "gpu_launches": args.steps * n_launches_step, "clocks": clocks}
         print(json.dumps(line))
     if world > 1:

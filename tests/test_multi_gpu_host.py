@@ -50,6 +50,18 @@ def _worker(rank, world, port, q):
         cnt = torch.tensor([mine], dtype=torch.int64)
         dist.all_reduce(cnt)
         assert int(cnt.item()) == len(keys) and 0.35 * len(keys) < mine < 0.65 * len(keys)
+        # host-frame exchange: each rank uploads its share, the all-gather returns every frame in global order
+        F, H, W = 11, 4, 6                                                       # ragged: 11 frames, super-chunks of 2 x 3
+        depth = (torch.arange(F * H * W, dtype=torch.int32) % 60000).to(torch.int16).reshape(F, H, W).view(torch.uint16)
+        color = (torch.arange(F * H * W * 3, dtype=torch.int64) % 251).to(torch.uint8).reshape(F, H, W, 3)
+        ex = sharded.HostFrameExchange((H, W), 3, per=3, device=None)
+        seen = []
+        ex.run(depth, color, lambda d, c, f0, n: seen.append((f0, n, d.clone(), c.clone())))
+        assert [(f0, n) for f0, n, _, _ in seen] == [(0, 6), (6, 5)]
+        got_d = torch.cat([d.view(torch.int16) for _, _, d, _ in seen])
+        got_c = torch.cat([c for _, _, _, c in seen])
+        assert torch.equal(got_d, depth.view(torch.int16)) and torch.equal(got_c, color)
+        assert ex.bytes_uploaded == (6 if rank == 0 else 5) * H * W * 5          # rank 0: frames 0-2, 6-8; rank 1: 3-5, 9-10
         q.put((rank, "ok"))
     except Exception as e:  # pragma: no cover
         q.put((rank, repr(e)))
@@ -77,3 +89,19 @@ def test_unit_owner_python_mirror_matches_library():
         for k in rng.integers(-5000, 5000, size=(200, 3)):
             assert lib.b2r_unit_owner(int(k[0]), int(k[1]), int(k[2]), world) == sharded.unit_owner(k, world)
     assert lib.b2r_unit_owner(1 << 21, 0, 0, 4) == -1
+
+
+def test_superchunk_plan_keeps_global_frame_order():
+    for F, world, per in ((300, 8, 8), (11, 2, 3), (5, 4, 2), (64, 8, 8), (1, 2, 4)):
+        plan = sharded.superchunk_plan(F, world, per)
+        covered = []
+        for f_start, n_valid, ranges in plan:
+            assert len(ranges) == world and 0 < n_valid <= world * per
+            slot = 0
+            for r, (f0, f1) in enumerate(ranges):
+                assert 0 <= f1 - f0 <= per
+                if f1 > f0:
+                    assert f0 - f_start == r * per                              # slot index in the gathered buffer == frame index
+                covered += list(range(f0, f1))
+            assert covered[-n_valid:] == list(range(f_start, f_start + n_valid))
+        assert covered == list(range(F))
