@@ -87,39 +87,83 @@ __global__ void copy_points_kernel(const double* __restrict__ in, double* out, l
     if (i < n3) out[i] = in[i];
 }
 
+// Every loop is fully unrolled and the pivot row / column exchange is written as predicated swaps over STATIC indices, so
+// the 36 + 36 + 24 doubles live in registers instead of dynamically indexed local memory (this runs on ONE thread at the
+// end of every Gauss-Newton iteration: its latency is on the critical path every ICP iteration).  Same operations, same
+// order, same results as the loop form the oracle uses.
 __device__ bool icp_ldlt6(const double* A_in, const double* b_in, double* x) {
-    const int n = 6;
+    constexpr int n = 6;
     double A[36], L[36], D[6], y[6], z[6];
     int perm[6];
+#pragma unroll
     for (int i = 0; i < 36; i++) { A[i] = A_in[i]; L[i] = 0.0; }
-    for (int i = 0; i < n; i++) perm[i] = i;
+#pragma unroll
+    for (int i = 0; i < n; i++) { perm[i] = i; D[i] = 0.0; }
+    bool stopped = false;
+#pragma unroll
     for (int k = 0; k < n; k++) {
+        if (stopped) continue;
         int p = k;
         double best = fabs(A[k * n + k]);
+#pragma unroll
         for (int i = k + 1; i < n; i++) if (fabs(A[i * n + i]) > best) { best = fabs(A[i * n + i]); p = i; }
-        if (p != k) {
-            for (int j = 0; j < n; j++) { double t = A[k * n + j]; A[k * n + j] = A[p * n + j]; A[p * n + j] = t; }
-            for (int j = 0; j < n; j++) { double t = A[j * n + k]; A[j * n + k] = A[j * n + p]; A[j * n + p] = t; }
-            for (int j = 0; j < k; j++) { double t = L[k * n + j]; L[k * n + j] = L[p * n + j]; L[p * n + j] = t; }
-            int t = perm[k]; perm[k] = perm[p]; perm[p] = t;
+#pragma unroll
+        for (int i = k + 1; i < n; i++) {
+            if (i == p) {
+#pragma unroll
+                for (int j = 0; j < n; j++) { const double t = A[k * n + j]; A[k * n + j] = A[i * n + j]; A[i * n + j] = t; }
+#pragma unroll
+                for (int j = 0; j < n; j++) { const double t = A[j * n + k]; A[j * n + k] = A[j * n + i]; A[j * n + i] = t; }
+#pragma unroll
+                for (int j = 0; j < k; j++) { const double t = L[k * n + j]; L[k * n + j] = L[i * n + j]; L[i * n + j] = t; }
+                const int t = perm[k]; perm[k] = perm[i]; perm[i] = t;
+            }
         }
         const double d = A[k * n + k];
         D[k] = d;
         L[k * n + k] = 1.0;
         if (d == 0.0) {
+#pragma unroll
             for (int i = k + 1; i < n; i++) { D[i] = 0.0; L[i * n + i] = 1.0; L[i * n + k] = 0.0; }
-            break;
+            stopped = true;
+            continue;
         }
+#pragma unroll
         for (int i = k + 1; i < n; i++) L[i * n + k] = xddiv(A[i * n + k], d);
+#pragma unroll
         for (int i = k + 1; i < n; i++)
+#pragma unroll
             for (int j = k + 1; j < n; j++) A[i * n + j] = xdsub(A[i * n + j], xdmul(xdmul(L[i * n + k], d), L[j * n + k]));
     }
-    for (int i = 0; i < n; i++) y[i] = b_in[perm[i]];
-    for (int i = 0; i < n; i++) { double s = y[i]; for (int j = 0; j < i; j++) s = xdsub(s, xdmul(L[i * n + j], z[j])); z[i] = s; }
+#pragma unroll
+    for (int i = 0; i < n; i++) {
+        double v = 0.0;
+#pragma unroll
+        for (int j = 0; j < n; j++) if (perm[i] == j) v = b_in[j];
+        y[i] = v;
+    }
+#pragma unroll
+    for (int i = 0; i < n; i++) {
+        double s = y[i];
+#pragma unroll
+        for (int j = 0; j < i; j++) s = xdsub(s, xdmul(L[i * n + j], z[j]));
+        z[i] = s;
+    }
+#pragma unroll
     for (int i = 0; i < n; i++) z[i] = (fabs(D[i]) > 2.2250738585072014e-308) ? xddiv(z[i], D[i]) : 0.0;
-    for (int i = n - 1; i >= 0; i--) { double s = z[i]; for (int j = i + 1; j < n; j++) s = xdsub(s, xdmul(L[j * n + i], y[j])); y[i] = s; }
+#pragma unroll
+    for (int i = n - 1; i >= 0; i--) {
+        double s = z[i];
+#pragma unroll
+        for (int j = i + 1; j < n; j++) s = xdsub(s, xdmul(L[j * n + i], y[j]));
+        y[i] = s;
+    }
     bool ok = true;
-    for (int i = 0; i < n; i++) x[perm[i]] = y[i];
+#pragma unroll
+    for (int i = 0; i < n; i++)
+#pragma unroll
+        for (int j = 0; j < n; j++) if (perm[i] == j) x[j] = y[i];
+#pragma unroll
     for (int i = 0; i < n; i++) ok = ok && isfinite(x[i]);
     return ok;
 }
@@ -238,10 +282,26 @@ __global__ void __launch_bounds__(ICP_THREADS) icp_iter_kernel(const IcpArgs a) 
     if (threadIdx.x == 0) is_last = (atomicAdd(&st->ticket, 1u) == gridDim.x - 1);
     __syncthreads();
     if (!is_last) return;
+    // fixed tree over the blocks' partials: warp w sums blocks w, w + 8, ... (four loads in flight), then the warp sums in order
     __shared__ double tot[ICP_NV];
+    __shared__ double part[ICP_THREADS / 32][ICP_NV];
+    if (lane < ICP_NV) {
+        constexpr int NW = ICP_THREADS / 32;
+        double v0 = 0.0, v1 = 0.0, v2 = 0.0, v3 = 0.0;
+        unsigned b = warp;
+        for (; b + 3 * NW < gridDim.x; b += 4 * NW) {
+            const double a0 = __ldcg(&a.partials[(size_t)b * ICP_NV + lane]), a1 = __ldcg(&a.partials[(size_t)(b + NW) * ICP_NV + lane]);
+            const double a2 = __ldcg(&a.partials[(size_t)(b + 2 * NW) * ICP_NV + lane]), a3 = __ldcg(&a.partials[(size_t)(b + 3 * NW) * ICP_NV + lane]);
+            v0 = xdadd(v0, a0); v1 = xdadd(v1, a1); v2 = xdadd(v2, a2); v3 = xdadd(v3, a3);
+        }
+        for (; b < gridDim.x; b += NW) v0 = xdadd(v0, __ldcg(&a.partials[(size_t)b * ICP_NV + lane]));
+        part[warp][lane] = xdadd(xdadd(v0, v1), xdadd(v2, v3));
+    }
+    __syncthreads();
     if (threadIdx.x < ICP_NV) {
         double v = 0.0;
-        for (unsigned b = 0; b < gridDim.x; b++) v = xdadd(v, __ldcg(&a.partials[(size_t)b * ICP_NV + threadIdx.x]));
+#pragma unroll
+        for (int w = 0; w < ICP_THREADS / 32; w++) v = xdadd(v, part[w][threadIdx.x]);
         tot[threadIdx.x] = v;
     }
     __syncthreads();

@@ -138,39 +138,83 @@ __global__ void __launch_bounds__(OD_THREADS) corr_warp_kernel(const float* __re
 }
 
 // ---- 6x6 pivoted LDLT (same algorithm as the oracle) + pose update -----------------------------------------
+// Every loop is fully unrolled and the pivot row / column exchange is written as predicated swaps over STATIC indices, so
+// the 36 + 36 + 24 doubles live in registers instead of dynamically indexed local memory (this runs on ONE thread at the
+// end of every Gauss-Newton iteration: its latency is on the critical path 35 times per pair).  Same operations, same
+// order, same results as the loop form the oracle uses.
 __device__ bool ldlt6_solve_dev(const double* A_in, const double* b_in, double* x) {
-    const int n = 6;
+    constexpr int n = 6;
     double A[36], L[36], D[6], y[6], z[6];
     int perm[6];
+#pragma unroll
     for (int i = 0; i < 36; i++) { A[i] = A_in[i]; L[i] = 0.0; }
-    for (int i = 0; i < n; i++) perm[i] = i;
+#pragma unroll
+    for (int i = 0; i < n; i++) { perm[i] = i; D[i] = 0.0; }
+    bool stopped = false;
+#pragma unroll
     for (int k = 0; k < n; k++) {
+        if (stopped) continue;
         int p = k;
         double best = fabs(A[k * n + k]);
+#pragma unroll
         for (int i = k + 1; i < n; i++) if (fabs(A[i * n + i]) > best) { best = fabs(A[i * n + i]); p = i; }
-        if (p != k) {
-            for (int j = 0; j < n; j++) { double t = A[k * n + j]; A[k * n + j] = A[p * n + j]; A[p * n + j] = t; }
-            for (int j = 0; j < n; j++) { double t = A[j * n + k]; A[j * n + k] = A[j * n + p]; A[j * n + p] = t; }
-            for (int j = 0; j < k; j++) { double t = L[k * n + j]; L[k * n + j] = L[p * n + j]; L[p * n + j] = t; }
-            int t = perm[k]; perm[k] = perm[p]; perm[p] = t;
+#pragma unroll
+        for (int i = k + 1; i < n; i++) {
+            if (i == p) {
+#pragma unroll
+                for (int j = 0; j < n; j++) { const double t = A[k * n + j]; A[k * n + j] = A[i * n + j]; A[i * n + j] = t; }
+#pragma unroll
+                for (int j = 0; j < n; j++) { const double t = A[j * n + k]; A[j * n + k] = A[j * n + i]; A[j * n + i] = t; }
+#pragma unroll
+                for (int j = 0; j < k; j++) { const double t = L[k * n + j]; L[k * n + j] = L[i * n + j]; L[i * n + j] = t; }
+                const int t = perm[k]; perm[k] = perm[i]; perm[i] = t;
+            }
         }
         const double d = A[k * n + k];
         D[k] = d;
         L[k * n + k] = 1.0;
         if (d == 0.0) {
+#pragma unroll
             for (int i = k + 1; i < n; i++) { D[i] = 0.0; L[i * n + i] = 1.0; L[i * n + k] = 0.0; }
-            break;
+            stopped = true;
+            continue;
         }
+#pragma unroll
         for (int i = k + 1; i < n; i++) L[i * n + k] = xddiv(A[i * n + k], d);
+#pragma unroll
         for (int i = k + 1; i < n; i++)
+#pragma unroll
             for (int j = k + 1; j < n; j++) A[i * n + j] = xdsub(A[i * n + j], xdmul(xdmul(L[i * n + k], d), L[j * n + k]));
     }
-    for (int i = 0; i < n; i++) y[i] = b_in[perm[i]];
-    for (int i = 0; i < n; i++) { double s = y[i]; for (int j = 0; j < i; j++) s = xdsub(s, xdmul(L[i * n + j], z[j])); z[i] = s; }
+#pragma unroll
+    for (int i = 0; i < n; i++) {
+        double v = 0.0;
+#pragma unroll
+        for (int j = 0; j < n; j++) if (perm[i] == j) v = b_in[j];
+        y[i] = v;
+    }
+#pragma unroll
+    for (int i = 0; i < n; i++) {
+        double s = y[i];
+#pragma unroll
+        for (int j = 0; j < i; j++) s = xdsub(s, xdmul(L[i * n + j], z[j]));
+        z[i] = s;
+    }
+#pragma unroll
     for (int i = 0; i < n; i++) z[i] = (fabs(D[i]) > 2.2250738585072014e-308) ? xddiv(z[i], D[i]) : 0.0;
-    for (int i = n - 1; i >= 0; i--) { double s = z[i]; for (int j = i + 1; j < n; j++) s = xdsub(s, xdmul(L[j * n + i], y[j])); y[i] = s; }
+#pragma unroll
+    for (int i = n - 1; i >= 0; i--) {
+        double s = z[i];
+#pragma unroll
+        for (int j = i + 1; j < n; j++) s = xdsub(s, xdmul(L[j * n + i], y[j]));
+        y[i] = s;
+    }
     bool ok = true;
-    for (int i = 0; i < n; i++) { x[perm[i]] = y[i]; }
+#pragma unroll
+    for (int i = 0; i < n; i++)
+#pragma unroll
+        for (int j = 0; j < n; j++) if (perm[i] == j) x[j] = y[i];
+#pragma unroll
     for (int i = 0; i < n; i++) ok = ok && isfinite(x[i]);
     return ok;
 }
@@ -329,10 +373,27 @@ __global__ void __launch_bounds__(OD_THREADS) reduce_kernel(const LevelImgs L, c
     __syncthreads();
     if (!is_last) return;
     // ---- last block: deterministic sum over blocks, then finalise
+    // (a fixed tree: warp w sums blocks w, w + 8, ... with four loads in flight, then the 8 warp sums are added in order --
+    //  run-to-run deterministic, and ~8x shorter than one thread per value walking all blocks with dependent adds)
     __shared__ double tot[OD_NV];
+    __shared__ double part[OD_THREADS / 32][OD_NV];
+    if (lane < NV) {
+        constexpr int NW = OD_THREADS / 32;
+        double v0 = 0.0, v1 = 0.0, v2 = 0.0, v3 = 0.0;
+        unsigned b = warp;
+        for (; b + 3 * NW < gridDim.x; b += 4 * NW) {
+            const double a0 = __ldcg(&partials[(size_t)b * OD_NV + lane]), a1 = __ldcg(&partials[(size_t)(b + NW) * OD_NV + lane]);
+            const double a2 = __ldcg(&partials[(size_t)(b + 2 * NW) * OD_NV + lane]), a3 = __ldcg(&partials[(size_t)(b + 3 * NW) * OD_NV + lane]);
+            v0 = xdadd(v0, a0); v1 = xdadd(v1, a1); v2 = xdadd(v2, a2); v3 = xdadd(v3, a3);
+        }
+        for (; b < gridDim.x; b += NW) v0 = xdadd(v0, __ldcg(&partials[(size_t)b * OD_NV + lane]));
+        part[warp][lane] = xdadd(xdadd(v0, v1), xdadd(v2, v3));
+    }
+    __syncthreads();
     if (threadIdx.x < NV) {
         double v = 0.0;
-        for (unsigned b = 0; b < gridDim.x; b++) v = xdadd(v, __ldcg(&partials[(size_t)b * OD_NV + threadIdx.x]));
+#pragma unroll
+        for (int w = 0; w < OD_THREADS / 32; w++) v = xdadd(v, part[w][threadIdx.x]);
         tot[threadIdx.x] = v;
     }
     __syncthreads();
@@ -370,6 +431,15 @@ int get_ws(size_t bytes, void** out) {
     return B2R_OK;
 }
 
+struct OdoGraphKey { int W, H, jac, n_levels, iters[8]; double k[7]; void* ws; };
+struct OdoGraph { OdoGraphKey key; cudaGraphExec_t exec = nullptr; cudaStream_t cap_stream = nullptr; };
+OdoGraph g_odo_graph[16];
+bool odo_graph_enabled() {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("B2R_ODO_GRAPH"); on = (e && e[0] == '0') ? 0 : 1; }
+    return on == 1;
+}
+
 inline unsigned nblk(int n) { return (unsigned)((n + OD_THREADS - 1) / OD_THREADS); }
 
 }  // namespace
@@ -395,8 +465,9 @@ B2R_API int b2r_odometry(const float* src_gray, const float* src_depth, const fl
     int nsm = 148;
     cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, 0);
     const unsigned red_grid_max = (unsigned)nsm * 2;
-    // workspace: 8 pyramids + 1 temp image + zbuf + partials + state
-    const size_t bytes_imgs = (8 * total_px + N0) * sizeof(float);
+    // workspace: 8 pyramids + 1 temp image + 4 staged inputs + zbuf + partials + state
+    const size_t N0p = (N0 + 63) & ~(size_t)63;
+    const size_t bytes_imgs = (8 * total_px + N0p + 4 * N0p) * sizeof(float);
     const size_t o_z = (bytes_imgs + 255) & ~(size_t)255;
     const size_t o_p = o_z + ((N0 * 8 + 255) & ~(size_t)255);
     const size_t o_s = o_p + (((size_t)red_grid_max * OD_NV * 8 + 255) & ~(size_t)255);
@@ -408,6 +479,8 @@ B2R_API int b2r_odometry(const float* src_gray, const float* src_depth, const fl
     float* pyr[8];
     for (int i = 0; i < 8; i++) pyr[i] = base + (size_t)i * total_px;     // sg, sd, tg, td, tgdx, tgdy, tddx, tddy
     float* tmp = base + 8 * total_px;
+    float* stage[4];
+    for (int i = 0; i < 4; i++) stage[i] = tmp + (size_t)(i + 1) * N0p;
     unsigned long long* zbuf = (unsigned long long*)((char*)ws + o_z);
     double* partials = (double*)((char*)ws + o_p);
     OdoState* st = (OdoState*)((char*)ws + o_s);
@@ -419,15 +492,20 @@ B2R_API int b2r_odometry(const float* src_gray, const float* src_depth, const fl
     if (all_zero) b2r::m4_identity(h0.pose); else memcpy(h0.pose, init_host, sizeof(h0.pose));
     h0.scale[0] = h0.scale[1] = 1.0;
     B2R_CUDA(cudaMemcpyAsync(st, &h0, sizeof(h0), cudaMemcpyHostToDevice, stream));
-    fill_u64_kernel<<<nblk((int)N0), OD_THREADS, 0, stream>>>(zbuf, (int)N0);
+    // Everything between the state upload and the result read-back is ~105 small dependent launches with fixed
+    // parameters (the iteration counts are fixed; upstream has no convergence break): it is captured ONCE into a CUDA
+    // graph per (shape, intrinsics, options, workspace) and replayed; the inputs are first copied into staging images
+    // inside the workspace so the graph's pointers never change.  B2R_ODO_GRAPH=0 launches the kernels directly.
+    auto enqueue = [&](cudaStream_t s, const float* in_sg, const float* in_sd, const float* in_tg, const float* in_td) -> bool {
+    fill_u64_kernel<<<nblk((int)N0), OD_THREADS, 0, s>>>(zbuf, (int)N0);
 
     // InitializeRGBDOdometry: Gaussian3 on grays; PreprocessDepth + Gaussian3 on depths
     const float dmin = (float)depth_min, dmax = (float)depth_max;
-    filter3_kernel<false><<<nblk((int)N0), OD_THREADS, 0, stream>>>(src_gray, pyr[0], W, H, 0, 0.f, 0.f);
-    filter3_kernel<false><<<nblk((int)N0), OD_THREADS, 0, stream>>>(tgt_gray, pyr[2], W, H, 0, 0.f, 0.f);
-    filter3_kernel<true><<<nblk((int)N0), OD_THREADS, 0, stream>>>(src_depth, pyr[1], W, H, 0, dmin, dmax);
-    filter3_kernel<true><<<nblk((int)N0), OD_THREADS, 0, stream>>>(tgt_depth, pyr[3], W, H, 0, dmin, dmax);
-    B2R_CHECK_LAUNCH();
+    filter3_kernel<false><<<nblk((int)N0), OD_THREADS, 0, s>>>(in_sg, pyr[0], W, H, 0, 0.f, 0.f);
+    filter3_kernel<false><<<nblk((int)N0), OD_THREADS, 0, s>>>(in_tg, pyr[2], W, H, 0, 0.f, 0.f);
+    filter3_kernel<true><<<nblk((int)N0), OD_THREADS, 0, s>>>(in_sd, pyr[1], W, H, 0, dmin, dmax);
+    filter3_kernel<true><<<nblk((int)N0), OD_THREADS, 0, s>>>(in_td, pyr[3], W, H, 0, dmin, dmax);
+    if (cudaGetLastError() != cudaSuccess) return false;
 
     KLevel K[8];
     K[0] = KLevel{fx, fy, cx, cy};
@@ -444,11 +522,11 @@ B2R_API int b2r_odometry(const float* src_gray, const float* src_depth, const fl
     // NormalizeIntensity over the correspondences at the initial pose
     {
         const LevelImgs L = level(0);
-        corr_warp_kernel<<<nblk((int)N0), OD_THREADS, 0, stream>>>(L.sd, L.td, W, H, K[0], st, depth_diff_max, zbuf);
-        reduce_kernel<2><<<red_grid((int)N0), OD_THREADS, 0, stream>>>(L, K[0], st, zbuf, partials);
-        scale_kernel<<<nblk((int)N0), OD_THREADS, 0, stream>>>(pyr[0], (int)N0, st, 0);
-        scale_kernel<<<nblk((int)N0), OD_THREADS, 0, stream>>>(pyr[2], (int)N0, st, 1);
-        B2R_CHECK_LAUNCH();
+        corr_warp_kernel<<<nblk((int)N0), OD_THREADS, 0, s>>>(L.sd, L.td, W, H, K[0], st, depth_diff_max, zbuf);
+        reduce_kernel<2><<<red_grid((int)N0), OD_THREADS, 0, s>>>(L, K[0], st, zbuf, partials);
+        scale_kernel<<<nblk((int)N0), OD_THREADS, 0, s>>>(pyr[0], (int)N0, st, 0);
+        scale_kernel<<<nblk((int)N0), OD_THREADS, 0, s>>>(pyr[2], (int)N0, st, 1);
+        if (cudaGetLastError() != cudaSuccess) return false;
     }
     // pyramids: colour = Downsample(Gaussian3(prev)), depth = Downsample(prev)
     for (int l = 1; l < n_levels; l++) {
@@ -456,41 +534,78 @@ B2R_API int b2r_odometry(const float* src_gray, const float* src_depth, const fl
         for (int img = 0; img < 4; img++) {
             const float* prev = pyr[img] + off[l - 1];
             if (img == 0 || img == 2) {
-                filter3_kernel<false><<<nblk(n_prev), OD_THREADS, 0, stream>>>(prev, tmp, Wl[l - 1], Hl[l - 1], 0, 0.f, 0.f);
-                downsample_kernel<<<nblk(n_cur), OD_THREADS, 0, stream>>>(tmp, pyr[img] + off[l], Wl[l - 1], Hl[l - 1]);
+                filter3_kernel<false><<<nblk(n_prev), OD_THREADS, 0, s>>>(prev, tmp, Wl[l - 1], Hl[l - 1], 0, 0.f, 0.f);
+                downsample_kernel<<<nblk(n_cur), OD_THREADS, 0, s>>>(tmp, pyr[img] + off[l], Wl[l - 1], Hl[l - 1]);
             } else {
-                downsample_kernel<<<nblk(n_cur), OD_THREADS, 0, stream>>>(prev, pyr[img] + off[l], Wl[l - 1], Hl[l - 1]);
+                downsample_kernel<<<nblk(n_cur), OD_THREADS, 0, s>>>(prev, pyr[img] + off[l], Wl[l - 1], Hl[l - 1]);
             }
         }
     }
     // Sobel of the target colour and depth pyramids
     for (int l = 0; l < n_levels; l++) {
         const int n = Wl[l] * Hl[l];
-        filter3_kernel<false><<<nblk(n), OD_THREADS, 0, stream>>>(pyr[2] + off[l], pyr[4] + off[l], Wl[l], Hl[l], 1, 0.f, 0.f);
-        filter3_kernel<false><<<nblk(n), OD_THREADS, 0, stream>>>(pyr[2] + off[l], pyr[5] + off[l], Wl[l], Hl[l], 2, 0.f, 0.f);
-        filter3_kernel<false><<<nblk(n), OD_THREADS, 0, stream>>>(pyr[3] + off[l], pyr[6] + off[l], Wl[l], Hl[l], 1, 0.f, 0.f);
-        filter3_kernel<false><<<nblk(n), OD_THREADS, 0, stream>>>(pyr[3] + off[l], pyr[7] + off[l], Wl[l], Hl[l], 2, 0.f, 0.f);
+        filter3_kernel<false><<<nblk(n), OD_THREADS, 0, s>>>(pyr[2] + off[l], pyr[4] + off[l], Wl[l], Hl[l], 1, 0.f, 0.f);
+        filter3_kernel<false><<<nblk(n), OD_THREADS, 0, s>>>(pyr[2] + off[l], pyr[5] + off[l], Wl[l], Hl[l], 2, 0.f, 0.f);
+        filter3_kernel<false><<<nblk(n), OD_THREADS, 0, s>>>(pyr[3] + off[l], pyr[6] + off[l], Wl[l], Hl[l], 1, 0.f, 0.f);
+        filter3_kernel<false><<<nblk(n), OD_THREADS, 0, s>>>(pyr[3] + off[l], pyr[7] + off[l], Wl[l], Hl[l], 2, 0.f, 0.f);
     }
-    B2R_CHECK_LAUNCH();
+    if (cudaGetLastError() != cudaSuccess) return false;
     // coarse-to-fine Gauss-Newton, 2 launches per iteration, no host sync
     for (int l = n_levels - 1; l >= 0; l--) {
         const LevelImgs L = level(l);
         const int n = Wl[l] * Hl[l];
         const int n_it = iters_host[n_levels - 1 - l];
         for (int it = 0; it < n_it; it++) {
-            corr_warp_kernel<<<nblk(n), OD_THREADS, 0, stream>>>(L.sd, L.td, L.W, L.H, K[l], st, depth_diff_max, zbuf);
-            if (jac_kind == 0) reduce_kernel<0><<<red_grid(n), OD_THREADS, 0, stream>>>(L, K[l], st, zbuf, partials);
-            else reduce_kernel<1><<<red_grid(n), OD_THREADS, 0, stream>>>(L, K[l], st, zbuf, partials);
+            corr_warp_kernel<<<nblk(n), OD_THREADS, 0, s>>>(L.sd, L.td, L.W, L.H, K[l], st, depth_diff_max, zbuf);
+            if (jac_kind == 0) reduce_kernel<0><<<red_grid(n), OD_THREADS, 0, s>>>(L, K[l], st, zbuf, partials);
+            else reduce_kernel<1><<<red_grid(n), OD_THREADS, 0, s>>>(L, K[l], st, zbuf, partials);
         }
-        B2R_CHECK_LAUNCH();
+        if (cudaGetLastError() != cudaSuccess) return false;
     }
     // CreateInformationMatrix at the final pose
     {
         const LevelImgs L = level(0);
-        corr_warp_kernel<<<nblk((int)N0), OD_THREADS, 0, stream>>>(L.sd, L.td, W, H, K[0], st, depth_diff_max, zbuf);
-        reduce_kernel<3><<<red_grid((int)N0), OD_THREADS, 0, stream>>>(L, K[0], st, zbuf, partials);
-        B2R_CHECK_LAUNCH();
+        corr_warp_kernel<<<nblk((int)N0), OD_THREADS, 0, s>>>(L.sd, L.td, W, H, K[0], st, depth_diff_max, zbuf);
+        reduce_kernel<3><<<red_grid((int)N0), OD_THREADS, 0, s>>>(L, K[0], st, zbuf, partials);
+        if (cudaGetLastError() != cudaSuccess) return false;
     }
+        return true;
+    };
+    OdoGraphKey key;
+    memset(&key, 0, sizeof(key));
+    key.W = W; key.H = H; key.jac = jac_kind; key.n_levels = n_levels;
+    for (int l = 0; l < n_levels; l++) key.iters[l] = iters_host[l];
+    key.k[0] = fx; key.k[1] = fy; key.k[2] = cx; key.k[3] = cy; key.k[4] = depth_diff_max; key.k[5] = depth_min; key.k[6] = depth_max;
+    key.ws = ws;
+    bool launched = false;
+    if (odo_graph_enabled()) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        OdoGraph& G = g_odo_graph[dev & 15];
+        if (!G.exec || memcmp(&G.key, &key, sizeof(key)) != 0) {
+            if (G.exec) { cudaGraphExecDestroy(G.exec); G.exec = nullptr; }
+            if (!G.cap_stream) cudaStreamCreateWithFlags(&G.cap_stream, cudaStreamNonBlocking);
+            cudaGraph_t graph = nullptr;
+            if (G.cap_stream && cudaStreamBeginCapture(G.cap_stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+                const bool ok = enqueue(G.cap_stream, stage[0], stage[1], stage[2], stage[3]);
+                const cudaError_t e = cudaStreamEndCapture(G.cap_stream, &graph);
+                if (ok && e == cudaSuccess && graph && cudaGraphInstantiate(&G.exec, graph, 0) == cudaSuccess) G.key = key;
+                else G.exec = nullptr;
+                if (graph) cudaGraphDestroy(graph);
+            }
+            cudaGetLastError();   // a failed capture must not poison the direct path below
+        }
+        if (G.exec) {
+            const size_t nb = N0 * sizeof(float);
+            B2R_CUDA(cudaMemcpyAsync(stage[0], src_gray, nb, cudaMemcpyDeviceToDevice, stream));
+            B2R_CUDA(cudaMemcpyAsync(stage[1], src_depth, nb, cudaMemcpyDeviceToDevice, stream));
+            B2R_CUDA(cudaMemcpyAsync(stage[2], tgt_gray, nb, cudaMemcpyDeviceToDevice, stream));
+            B2R_CUDA(cudaMemcpyAsync(stage[3], tgt_depth, nb, cudaMemcpyDeviceToDevice, stream));
+            B2R_CUDA(cudaGraphLaunch(G.exec, stream));
+            launched = true;
+        }
+    }
+    if (!launched && !enqueue(stream, src_gray, src_depth, tgt_gray, tgt_depth)) { B2R_CHECK_LAUNCH(); return B2R_ERR_CUDA; }
     OdoState h1;
     B2R_CUDA(cudaMemcpyAsync(&h1, st, sizeof(h1), cudaMemcpyDeviceToHost, stream));
     B2R_CUDA(cudaStreamSynchronize(stream));
