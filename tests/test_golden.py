@@ -121,3 +121,46 @@ def test_cuda_reproduces_golden():
     res = o3d.pipelines.registration.registration_icp(s, tg, 0.05, G["a13_init"], o3d.pipelines.registration.TransformationEstimationPointToPlane(),
                                                        o3d.pipelines.registration.ICPConvergenceCriteria(max_iteration=30))
     assert np.abs(res.transformation - G["a13_T"]).max() <= 1e-6 and abs(res.fitness - G["a13_fit"][0]) <= 1e-9
+
+
+# ---------------------------------------------------------------------------------------------- v2: a6 + f1
+G2 = np.load(os.path.join(os.path.dirname(__file__), "golden", "hotpath_v2.npz"))
+
+
+def test_oracle_reproduces_golden_v2_gather_and_pointcloud(o3r):
+    Kc = tuple(float(v) for v in G2["a6_Kc"][2:6])
+    gi = o3r.color_gather_index(G2["a6_depth"], K, int(G2["a6_Kc"][0]), int(G2["a6_Kc"][1]), Kc, G2["a6_d2c"])
+    assert np.array_equal(gi.astype(np.int32), G2["a6_gather_index"])          # the a6 chain is defined by the oracle: pinned here
+    xyz = G2["f1_xyz"]
+    idx, d2, _ = o3r.pcd_search(xyz, None, 12, -1.0)
+    assert np.array_equal(idx, G2["f1_knn_idx"]) and np.array_equal(d2, G2["f1_knn_d2"])
+    hidx, _, hcnt = o3r.pcd_search(xyz, None, 16, 0.08)
+    assert np.array_equal(hidx, G2["f1_hybrid_idx"]) and np.array_equal(hcnt, G2["f1_hybrid_cnt"])
+    nrm, cov = o3r.pcd_estimate_normals(xyz, 16, 0.08)
+    assert np.array_equal(cov, G2["f1_cov"]) and np.abs(nrm - G2["f1_normals"]).max() <= 1e-12
+    keep, avg = o3r.pcd_statistical_outlier(xyz, 12, 2.0)
+    assert np.array_equal(keep, G2["f1_keep"]) and np.array_equal(avg, G2["f1_avg"])
+    vp, vc, _, vk = o3r.pcd_voxel_down_sample(xyz, 0.05, G2["f1_rgb"])
+    assert np.array_equal(vk, G2["f1_voxel_key"]) and np.array_equal(vp, G2["f1_voxel_xyz"]) and np.array_equal(vc, G2["f1_voxel_rgb"])
+
+
+@pytest.mark.gpu
+def test_cuda_reproduces_golden_v2():
+    import azurekinect3dreconstruction_b200 as o3d
+    Kd = o3d.camera.PinholeCameraIntrinsic(W, H, *K)
+    Kc = o3d.camera.PinholeCameraIntrinsic(int(G2["a6_Kc"][0]), int(G2["a6_Kc"][1]), *[float(v) for v in G2["a6_Kc"][2:6]])
+    for dt in (torch.float64, torch.float32):                                   # generic (f64) and single-pass (f32) kernels
+        pcd = o3d.geometry.PointCloud.create_from_kinect_capture(G2["a6_depth"], G2["a6_color"], Kd, Kc, G2["a6_d2c"], dtype=dt)
+        src = pcd.source_index.cpu().numpy()
+        assert np.array_equal(pcd.gather_index.cpu().numpy(), G2["a6_gather_index"].reshape(-1)[src])
+    xyz = G2["f1_xyz"]
+    pcd = o3d.geometry.PointCloud(xyz)
+    pcd.colors = o3d.utility.Vector3dVector(G2["f1_rgb"])
+    down = pcd.voxel_down_sample(0.05)
+    assert np.array_equal(down.voxel_index.cpu().numpy(), G2["f1_voxel_key"])
+    assert np.array_equal(np.asarray(down.points), G2["f1_voxel_xyz"]) and np.array_equal(np.asarray(down.colors), G2["f1_voxel_rgb"])
+    inl, ind = pcd.remove_statistical_outlier(12, 2.0)
+    assert np.array_equal(ind.cpu().numpy(), np.nonzero(G2["f1_keep"])[0])
+    pcd.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(0.08, 16))
+    dots = np.einsum("ij,ij->i", np.asarray(pcd.normals), G2["f1_normals"])
+    assert np.abs(np.abs(dots) - 1.0).max() <= 1e-9

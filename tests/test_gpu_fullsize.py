@@ -1,0 +1,160 @@
+"""Full-size (BASELINE.json configs) GPU checks through size-independent properties -- the CPU oracle is too slow to run at
+these sizes inside the test budget, so the CUDA path is checked against invariants of the domain instead:
+unprojection: count == number of valid pixels, raster order, re-projection onto the source pixel; TSDF: results independent
+of the fusion batch size and of the ingest path (device / pinned host), union of 2 shards == single volume, reset + replay
+idempotent; mesh: indices in range, no degenerate triangle, interior edges shared by exactly two triangles, every vertex
+inside its voxel edge; extraction repeatable (cached second call) and invariant under export -> import."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+import azurekinect3dreconstruction_b200 as o3d
+from azurekinect3dreconstruction_b200 import synthetic as syn
+from azurekinect3dreconstruction_b200.geometry import unproject
+
+TT = o3d.pipelines.integration.TSDFVolumeColorType
+
+
+@pytest.fixture(scope="module")
+def nfov():
+    kin = syn.SyntheticKinect(seed=0, dropout=0.02, noise_sigma_mm=1.0, device="cuda")
+    poses = syn.orbit_trajectory(300)[:12]
+    fr = [kin.render_depth_aligned_rgb(p) for p in poses]
+    depth = torch.stack([f[0].view(torch.int16) for f in fr]).contiguous().view(torch.uint16)
+    rgb = torch.stack([f[1] for f in fr]).contiguous()
+    di = kin.depth_intr
+    K = o3d.camera.PinholeCameraIntrinsic(di["width"], di["height"], di["fx"], di["fy"], di["cx"], di["cy"])
+    E = np.stack([np.linalg.inv(p) for p in poses])
+    return kin, depth, rgb, K, E
+
+
+def test_unprojection_full_nfov_and_wfov_properties(nfov):
+    kin, depth, rgb, K, E = nfov
+    r = unproject(depth[:4], K, depth_is_u16=True, depth_scale=1000.0, depth_trunc=3.0, color=rgb[:4], dtype=torch.float32, want_index=True)
+    d = depth[:4].view(torch.int16).to(torch.int32) & 0xFFFF
+    valid = (d > 0) & (d.float() / 1000.0 < 3.0)
+    fx, fy, cx, cy = K.fxfycxcy()
+    lut = torch.as_tensor(np.arange(256, dtype=np.float32) / np.float32(255.0), device="cuda")
+    for b in range(4):
+        n = int(r["counts"][b])
+        assert n == int(valid[b].sum())                                   # count == valid pixels
+        idx = r["src_index"][b, :n].long()
+        assert bool((idx[1:] > idx[:-1]).all())                           # raster order
+        assert bool(valid[b].reshape(-1)[idx].all())
+        xyz = r["xyz"][b, :n].double()
+        u = xyz[:, 0] * fx / xyz[:, 2] + cx
+        v = xyz[:, 1] * fy / xyz[:, 2] + cy
+        assert float((u - (idx % K.width).double()).abs().max()) < 1e-3 and float((v - (idx // K.width).double()).abs().max()) < 1e-3
+        assert float((xyz[:, 2] - d[b].reshape(-1)[idx].double() / 1000.0).abs().max()) < 1e-6
+        col = r["rgb"][b, :n]
+        assert torch.equal(col, lut[rgb[b].reshape(-1, 3)[idx].long()])     # exactly rounded c / 255 (numpy division; torch's CUDA scalar division multiplies by 1/255)
+    # WFOV 1024 x 1024 (config 5 frame shape), depth only
+    g = torch.Generator(device="cuda").manual_seed(1)
+    dw = torch.randint(0, 2300, (2, 1024, 1024), device="cuda", generator=g, dtype=torch.int32)
+    dw = torch.where(dw < 300, torch.zeros_like(dw), dw).to(torch.int16).view(torch.uint16)
+    Kw = o3d.camera.PinholeCameraIntrinsic(1024, 1024, 504.2, 504.2, 511.5, 511.5)
+    rw = unproject(dw, Kw, depth_is_u16=True, depth_scale=1000.0, depth_trunc=3.0, dtype=torch.float32, want_index=True)
+    for b in range(2):
+        n = int(rw["counts"][b])
+        assert n == int((dw[b].view(torch.int16) != 0).sum())
+        idx = rw["src_index"][b, :n].long()
+        assert bool((idx[1:] > idx[:-1]).all())
+
+
+def volume_state(vol):
+    keys, tsdf, wgt, rgb = vol.export_units()
+    keys = keys.cpu().numpy()
+    o = np.lexsort(keys.T[::-1])
+    o_t = torch.as_tensor(o, device=tsdf.device)
+    return keys[o], tsdf[o_t], wgt[o_t], rgb[o_t]
+
+
+def same_state(a, b):
+    return np.array_equal(a[0], b[0]) and torch.equal(a[1], b[1]) and torch.equal(a[2], b[2]) and torch.equal(a[3], b[3])
+
+
+def test_tsdf_full_size_invariances(nfov):
+    kin, depth, rgb, K, E = nfov
+    def run(batch, host=False, world=1, rank=0):
+        vol = o3d.pipelines.integration.ScalableTSDFVolume(0.004, 0.02, TT.RGB8, capacity_units=12000, rank=rank, world=world)
+        vol.set_batch(batch)
+        if host:
+            dh = depth.view(torch.int16).cpu().pin_memory().view(torch.uint16)
+            ch = rgb.cpu().pin_memory()
+            vol.integrate_raw(dh, ch, K, E, 1000.0, 3.0)
+        else:
+            vol.integrate_raw(depth, rgb, K, E, 1000.0, 3.0)
+        return vol
+    ref_vol = run(16)
+    ref = volume_state(ref_vol)
+    assert len(ref[0]) > 2000 and int(ref_vol.stats()["errors"]) == 0
+    assert same_state(ref, volume_state(run(1)))                          # fusion batch size does not change a bit
+    assert same_state(ref, volume_state(run(5)))
+    assert same_state(ref, volume_state(run(16, host=True)))              # nor does the ingest path
+    # reset + replay is idempotent
+    ref_vol.reset()
+    assert ref_vol.num_units() == 0
+    ref_vol.integrate_raw(depth, rgb, K, E, 1000.0, 3.0)
+    assert same_state(ref, volume_state(ref_vol))
+    # union of two shards == the single volume, shards disjoint
+    s0, s1 = volume_state(run(16, world=2, rank=0)), volume_state(run(16, world=2, rank=1))
+    k0 = {tuple(k) for k in s0[0].tolist()}
+    k1 = {tuple(k) for k in s1[0].tolist()}
+    assert not (k0 & k1) and (k0 | k1) == {tuple(k) for k in ref[0].tolist()}
+    keys = np.concatenate([s0[0], s1[0]])
+    o = np.lexsort(keys.T[::-1])
+    o_t = torch.as_tensor(o, device="cuda")
+    merged = (keys[o], torch.cat([s0[1], s1[1]])[o_t], torch.cat([s0[2], s1[2]])[o_t], torch.cat([s0[3], s1[3]])[o_t])
+    assert same_state(ref, merged)
+
+
+def test_mesh_full_size_properties(nfov):
+    kin, depth, rgb, K, E = nfov
+    vl = 0.004
+    vol = o3d.pipelines.integration.ScalableTSDFVolume(vl, 0.02, TT.RGB8, capacity_units=12000)
+    vol.integrate_raw(depth, rgb, K, E, 1000.0, 3.0)
+    mesh = vol.extract_triangle_mesh(with_ids=True)
+    V, F = mesh.vertices.tensor, mesh.triangles.tensor.long()
+    nV, nF = V.shape[0], F.shape[0]
+    assert nV > 100000 and nF > 200000
+    assert int(F.min()) >= 0 and int(F.max()) < nV
+    assert bool(((F[:, 0] != F[:, 1]) & (F[:, 1] != F[:, 2]) & (F[:, 0] != F[:, 2])).all())     # no degenerate triangle
+    assert int(torch.unique(F.reshape(-1)).numel()) == nV                                          # every vertex is used (welded, none orphaned)
+    # every vertex lies on its voxel edge: id = (global voxel xyz, axis) -> position within [centre, centre + voxel] along the axis
+    ids = mesh.edge_ids.long()
+    base = (ids[:, :3].double() + 0.5) * vl
+    off = V - base
+    axis = ids[:, 3]
+    along = off.gather(1, axis[:, None]).squeeze(1)
+    assert float(along.min()) >= -1e-12 and float(along.max()) <= vl * (1 + 1e-9)
+    other = off.clone()
+    other.scatter_(1, axis[:, None], 0.0)
+    assert float(other.abs().max()) <= 1e-12
+    assert int(torch.unique(ids, dim=0).shape[0]) == nV                                            # one vertex per edge
+    # manifoldness: an undirected edge belongs to at most two triangles; where it has two they traverse it in opposite directions
+    e = torch.cat([F[:, [0, 1]], F[:, [1, 2]], F[:, [2, 0]]])
+    lo, hi = torch.minimum(e[:, 0], e[:, 1]), torch.maximum(e[:, 0], e[:, 1])
+    code = lo * nV + hi
+    uniq, cnt = torch.unique(code, return_counts=True)
+    assert int(cnt.max()) <= 2
+    assert float((cnt == 2).double().mean()) > 0.97                                                # the rest are the open borders of the scan
+    dirsum = torch.zeros_like(uniq, dtype=torch.int64)
+    pos = torch.searchsorted(uniq, code)
+    dirsum.scatter_add_(0, pos, torch.where(e[:, 0] < e[:, 1], 1, -1))
+    assert bool((dirsum[cnt == 2] == 0).all())                                                     # consistent orientation
+    # repeatability (second call runs from the cached count pass) and export -> import invariance
+    again = vol.extract_triangle_mesh()
+    assert torch.equal(again.vertices.tensor, V) and torch.equal(again.triangles.tensor.long(), F)
+    keys, tsdf, wgt, col = vol.export_units()
+    clone = o3d.pipelines.integration.ScalableTSDFVolume(vl, 0.02, TT.RGB8, capacity_units=12000)
+    clone.import_units(keys, tsdf, wgt, col)
+    m2 = clone.extract_triangle_mesh()
+    assert torch.equal(m2.vertices.tensor, V) and torch.equal(m2.triangles.tensor.long(), F)
+    assert torch.equal(m2.vertex_colors.tensor, mesh.vertex_colors.tensor)
+    pc = vol.extract_point_cloud()
+    pc2 = clone.extract_point_cloud()
+    assert len(pc.points) > 100000 and torch.equal(pc.points.tensor, pc2.points.tensor) and torch.equal(pc.normals.tensor, pc2.normals.tensor)
+    nn = torch.linalg.norm(pc.normals.tensor, dim=1)
+    assert float((nn - 1).abs().max()) < 1e-9

@@ -86,8 +86,33 @@ def main():
     out.update(a13_src=src, a13_tgt=tgt, a13_nrm=nrm, a13_init=init, a13_T=T, a13_fit=np.array([fit, rmse]), a13_iters=np.array([it]),
                a13_corr=corr)
     path = os.path.join(ROOT, "tests", "golden", "hotpath_v1.npz")
+    if "--only-v2" not in sys.argv:
+        np.savez_compressed(path, **out)
+        print(path, os.path.getsize(path), "bytes;", len(keys), "units,", len(vtx), "vertices,", len(tri), "triangles")
+    make_v2(kin, poses, depth, rgb, K)
+
+
+def make_v2(kin, poses, depth, rgb, K):
+    """tests/golden/hotpath_v2.npz: the rows added after v1 -- a6 (colour-to-depth gather on a native Kinect capture) and
+    f1 (neighbour search, normals, outlier removal, voxel down-sampling) on the unprojected first frame."""
+    cdict = dict(width=160, height=90, fx=605.6 / 8, fy=605.9 / 8, cx=637.7 / 8, cy=364.3 / 8)
+    kin2 = syn.SyntheticKinect(depth_intrinsics=INTR, color_intrinsics=cdict, seed=7, dropout=0.02)
+    cap = kin2.render_pose(poses[1], want_transformed_depth=False)
+    Kc = (cdict["fx"], cdict["fy"], cdict["cx"], cdict["cy"])
+    gi = o3r.color_gather_index(cap.depth, K, cdict["width"], cdict["height"], Kc, kin2.d2c)
+    out = dict(a6_depth=np.ascontiguousarray(cap.depth), a6_color=np.ascontiguousarray(cap.color), a6_Kc=np.array([cdict["width"], cdict["height"], *Kc]),
+               a6_d2c=kin2.d2c, a6_gather_index=gi.astype(np.int32))
+    xyz, col, _ = o3r.unproject(o3r.depth_to_float(depth[0]), K, rgb=rgb[0])
+    idx, d2, cnt = o3r.pcd_search(xyz, None, 12, -1.0)
+    hidx, _, hcnt = o3r.pcd_search(xyz, None, 16, 0.08)
+    nrm, cov = o3r.pcd_estimate_normals(xyz, 16, 0.08)
+    keep, avg = o3r.pcd_statistical_outlier(xyz, 12, 2.0)
+    vp, vc, _, vk = o3r.pcd_voxel_down_sample(xyz, 0.05, col)
+    out.update(f1_xyz=xyz, f1_rgb=col, f1_knn_idx=idx, f1_knn_d2=d2, f1_hybrid_idx=hidx, f1_hybrid_cnt=hcnt, f1_cov=cov, f1_normals=nrm,
+               f1_keep=keep, f1_avg=avg, f1_voxel_xyz=vp, f1_voxel_rgb=vc, f1_voxel_key=vk)
+    path = os.path.join(ROOT, "tests", "golden", "hotpath_v2.npz")
     np.savez_compressed(path, **out)
-    print(path, os.path.getsize(path), "bytes;", len(keys), "units,", len(vtx), "vertices,", len(tri), "triangles")
+    print(path, os.path.getsize(path), "bytes;", len(xyz), "points,", int((gi >= 0).sum()), "gathered texels,", len(vp), "voxels")
 
 
 if __name__ == "__main__":
