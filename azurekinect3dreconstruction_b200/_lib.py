@@ -52,6 +52,7 @@ SIGNATURES = {
     "b2r_tsdf_set_batch": (_i, [_vp, _i, _vp]),
     "b2r_selftest_u8_div255": (_i, []),
     "b2r_selftest_div": (_i, [_i64, C.c_uint64, _pi64, _vp]),
+    "b2r_selftest_ddiv": (_i, [_d, _i64, C.c_uint64, _pi64, _vp]),
     "b2r_tsdf_num_units": (_i64, [_vp, _vp]),
     "b2r_tsdf_export_keys": (_i, [_vp, _vp, _i64, _vp]),
     "b2r_tsdf_export_units": (_i, [_vp, _i64, _i64, _vp, _vp, _vp, _vp]),

@@ -10,14 +10,17 @@
 // never diverge.
 //
 // Two kernels, both on the caller's stream:
-//   K1 tsdf_pack_alloc_kernel (at every integrate call; one launch can take a batch of frames):
-//        pack role  - one thread per pixel fuses RGBDImage conversion (u16 -> f32 metres, trunc), the
-//                     depth-to-camera-distance multiplier and the colour fetch into ONE 16-byte texel
-//                     {d, mult, rgb8, 0} of the frame's texel image;
-//        alloc role - one thread per depth_sampling_stride-th pixel unprojects in f64; a warp merges its
-//                     lanes' integer AABBs of unit keys and probes the union's cells in PARALLEL (one
-//                     32-byte slot read per probe); first touches of a (unit, batch) are appended to
-//                     the batch's touched list and the frame's bit is OR-ed into the slot's batch mask.
+//   K1 tsdf_pack_alloc_kernel (at every integrate call; one launch can take a batch of frames; the two roles are
+//      dealt out evenly over the launch order so the latency-bound one runs beside the bandwidth-bound one):
+//        pack role  - a CTA stages 2048 pixels of depth, colour and the cached depth-to-camera-distance multiplier
+//                     image by three TMA bulk copies, fuses the RGBDImage conversion (u16 -> f32 metres, trunc) and
+//                     writes ONE 16-byte texel {d, mult, rgb8, 0} per pixel, 512 contiguous bytes per warp store;
+//        alloc role - one thread per depth_sampling_stride-th pixel unprojects in f64 (divisions by fx, fy and the
+//                     unit length through host-rounded reciprocals, exact); runs of equal key boxes are merged, the
+//                     run heads write their cells' keys into a shared list and the block probes them in parallel
+//                     (one 32-byte slot read per cell, all of a thread's probes in flight together); first touches
+//                     of a (unit, batch) are appended to the batch's touched list (one counter atomic per warp) and
+//                     the frame's bit is OR-ed into the slot's batch mask.
 //   K2 tsdf_fuse_kernel (when max_batch frames are pending, or when anything reads the volume):
 //        persistent CTAs over (touched unit x 4 x-slabs).  A slab (planes x 4 KiB) is staged into shared
 //        memory by TMA bulk copies (cp.async.bulk + mbarrier) through a 3-deep ring, so the next two
@@ -48,6 +51,31 @@ B2R_API int b2r_version(void) { return 200; }
 // ------------------------------------------------------------------------------------------------
 // K1: pack + allocate
 // ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// TMA bulk copy global -> shared, completion counted on an mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
 struct PackFrame {
     const void* depth;        // u16 or f32, W*H
     const uint8_t* color;     // u8, channels 3|4 (may be null)
@@ -68,7 +96,11 @@ struct PackParams {
     double trunc, unit_length;
     int stride, Ws, n_samples;
     int n_alloc_blocks;
-    int vec_ok;                    // images are 16-byte aligned and W*H % 4 == 0: vector loads in the pack role
+    const float* mult;             // cached multiplier image (pack_mult of every pixel)
+    float rscale; int scale_fast;  // RN(1/depth_scale); depth_scale inside b2r_div_domain
+    double rfx, rfy, runit;        // RN(1/fx), RN(1/fy), RN(1/unit_length)
+    int ddiv_fast;                 // all three f64 divisors qualify for the shared-reciprocal division
+    int tma_ok;                    // every tile of every image is a 16-byte aligned multiple of 16 bytes: TMA staging in the pack role
     int rank, world;
     int q;                         // batch buffer (mask word) in use
     B2RHash hash;
@@ -79,13 +111,28 @@ struct PackParams {
     PackFrame fr[B2R_MAX_BATCH];
 };
 
+// u16 -> metres.  0x4B00vvvv is the float 8388608 + v, so the conversion is one LOP + one FADD (the I2F unit runs
+// at quarter rate); the division shares RN(1/depth_scale) when the host found the divisor inside b2r_div_domain.
+__device__ __forceinline__ float depth_from_u16(const PackParams& P, uint32_t v) {
+    const float fv = __fadd_rn(__uint_as_float(0x4B000000u | v), -8388608.0f);
+    const float d = P.scale_fast ? b2r_div_fast(fv, P.depth_scale, P.rscale) : xfdiv(fv, P.depth_scale);
+    return d >= P.depth_trunc ? 0.0f : d;
+}
 __device__ __forceinline__ float load_depth_m(const PackParams& P, const void* depth, int idx) {
-    if (P.depth_is_u16) {
-        float d = xfdiv((float)__ldg((const uint16_t*)depth + idx), P.depth_scale);
-        if (d >= P.depth_trunc) d = 0.0f;
-        return d;
-    }
+    if (P.depth_is_u16) return depth_from_u16(P, (uint32_t)__ldg((const uint16_t*)depth + idx));
     return __ldg((const float*)depth + idx);
+}
+// f64 division by one of the call's constants (fx, fy, unit_length): q0 = RN(a*y), r = a - b*q0 (exact), RN(q0 + r*y)
+// == RN(a/b) when y = RN(1/b) (computed with an IEEE division on the host) and b's significand is not all ones
+// (Markstein); b2r_selftest_ddiv brute-forces it in the tests.  Non-finite a gives NaN instead of +-inf: both fail
+// the key-range test below in the same way.
+__device__ __forceinline__ double ddiv_const(double a, double b, double y, int fast) {
+    if (fast) {
+        const double q0 = __dmul_rn(a, y);
+        const double r = __fma_rn(-b, q0, a);
+        return __fma_rn(r, y, q0);
+    }
+    return xddiv(a, b);
 }
 
 // slow path of the allocator: insert-or-find `key` (linear probing), mark it touched by frame `bit`
@@ -124,97 +171,149 @@ __device__ __noinline__ void alloc_key(const PackParams& P, uint64_t key, uint32
     atomicOr(&P.counters[B2R_C_ERR], 4);
 }
 
-#define PACK_PX 4   // pixels per thread in the pack role
+#define PACK_PX 8       // pixels per thread in the pack role
+#define PACK_TILE (256 * PACK_PX)   // pixels per CTA of the pack role
+#define K1_DYN_SMEM (PACK_TILE * 12) // dynamic shared memory: the pack role's staged tile; the alloc role's cell list aliases it
+#define ALLOC_CELLS 2048 // cell keys staged per window of the alloc role
+#ifndef ALLOC_IT
+#define ALLOC_IT 2       // cells per thread whose slot probes are in flight together (2 measured best; 4 spills)
+#endif
+#ifndef PACK_MIN_CTAS
+#define PACK_MIN_CTAS 5
+#endif
 
 // 8-bit colours ride in the texel as one 0x00BBGGRR word
-__device__ __forceinline__ void pack_rgb(uint32_t r, uint32_t g, uint32_t b, float& z, float& w) {
-    z = __uint_as_float(r | (g << 8) | (b << 16));
-    w = 0.0f;
-}
 // byte n of c -> float, without the quarter-rate I2F: 0x4B0000nn is the float 8388608 + nn
 template <int N>
 __device__ __forceinline__ float byte_to_float(uint32_t c) {
     return __fadd_rn(__uint_as_float(__byte_perm(c, 0x4B000000u, 0x7540 | N)), -8388608.0f);
 }
 
-__device__ __forceinline__ float pack_mult(const PackParams& P, int i, int j) {
-    const float xx = xfmul(xfsub((float)j, P.fcx), P.ifx);
-    const float yy = xfmul(xfsub((float)i, P.fcy), P.ify);
-    return __fsqrt_rn(xfadd(xfadd(xfmul(xx, xx), xfmul(yy, yy)), 1.0f));
-}
-__device__ __forceinline__ float depth_from_u16(const PackParams& P, uint32_t v) {
-    float d = xfdiv((float)v, P.depth_scale);
-    return d >= P.depth_trunc ? 0.0f : d;
+// CreateDepthToCameraDistanceMultiplierFloatImage: depends on the intrinsics only, so it is computed
+// once per (W, H, fx, fy, cx, cy) and cached in the handle; every frame's pack reads it back (L2 resident).
+__global__ void tsdf_mult_kernel(float* __restrict__ mult, int W, int H, float fcx, float fcy, float ifx, float ify) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= W * H) return;
+    const int i = idx / W, j = idx - i * W;
+    const float xx = xfmul(xfsub((float)j, fcx), ifx);
+    const float yy = xfmul(xfsub((float)i, fcy), ify);
+    mult[idx] = __fsqrt_rn(xfadd(xfadd(xfmul(xx, xx), xfmul(yy, yy)), 1.0f));
 }
 
-__global__ void __launch_bounds__(256, 4) tsdf_pack_alloc_kernel(const __grid_constant__ PackParams P) {
-    const PackFrame& F = P.fr[blockIdx.y];
-    if ((int)blockIdx.x >= P.n_alloc_blocks) {
-        // ---- pack role: a1 depth conversion + CreateDepthToCameraDistanceMultiplierFloatImage + colour,
-        //      PACK_PX consecutive pixels per thread, every load issued before the first use
+#ifdef B2R_K1_TRACE
+__device__ unsigned long long g_k1_trace[4 * 8192];
+__device__ __forceinline__ unsigned long long k1_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+struct K1Trace {
+    unsigned long long t0; int role;
+    __device__ K1Trace(int r) : t0(k1_now()), role(r) {}
+    __device__ ~K1Trace() {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const unsigned L = blockIdx.y * gridDim.x + blockIdx.x;
+            unsigned sm; asm("mov.u32 %0, %smid;" : "=r"(sm));
+            if (L < 8192) { g_k1_trace[4 * L] = t0; g_k1_trace[4 * L + 1] = k1_now(); g_k1_trace[4 * L + 2] = sm; g_k1_trace[4 * L + 3] = role; }
+        }
+    }
+};
+B2R_API int b2r_debug_k1_trace(unsigned long long* out, int n) {
+    return cudaMemcpyFromSymbol(out, g_k1_trace, sizeof(unsigned long long) * 4 * (size_t)n) == cudaSuccess ? 0 : -1;
+}
+#endif
+__global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(const __grid_constant__ PackParams P) {
+    // The two roles are dealt out evenly over the launch order (CTAs start in linear block order): the latency-bound
+    // allocation CTAs then run beside the bandwidth-bound pack CTAs from the first wave to the last, instead of each
+    // frame's allocation starting only when its row of the grid comes up.  Position L takes allocation block A(L) =
+    // floor(L * n_alloc_total / n_total) when A(L + 1) > A(L), else pack block L - A(L).
+    const unsigned L = blockIdx.y * gridDim.x + blockIdx.x;
+    const unsigned n_total = gridDim.x * gridDim.y, n_alloc_total = (unsigned)P.n_alloc_blocks * gridDim.y;
+    const unsigned A0 = (unsigned)(((unsigned long long)L * n_alloc_total) / n_total);
+    const unsigned A1 = (unsigned)(((unsigned long long)(L + 1) * n_alloc_total) / n_total);
+    const bool role_pack = A1 == A0;
+    const unsigned n_role = role_pack ? gridDim.x - (unsigned)P.n_alloc_blocks : (unsigned)P.n_alloc_blocks;
+    const unsigned ridx = role_pack ? L - A0 : A0;
+    const int fidx = (int)(ridx / n_role), bidx = (int)(ridx - (unsigned)fidx * n_role);
+    const PackFrame& F = P.fr[fidx];
+#ifdef B2R_K1_TRACE
+    K1Trace trace_(role_pack ? 1 : 0);
+#endif
+    if (role_pack) {
+        // ---- pack role: a1 depth conversion + the cached CreateDepthToCameraDistanceMultiplierFloatImage + colour.
+        //      A warp owns 32 * PACK_PX consecutive pixels; in step k lane l takes pixel 32 k + l, so every 16-byte
+        //      texel store of the warp lands in 512 contiguous bytes (4 full lines per request instead of 32 partial
+        //      ones -- the store REQUEST rate, not the bytes, bounded the thread-contiguous layout).  All loads of the
+        //      PACK_PX steps are issued before the first use.
         const int npx = P.W * P.H;
-        const int idx0 = ((blockIdx.x - P.n_alloc_blocks) * blockDim.x + threadIdx.x) * PACK_PX;
-        if (idx0 >= npx) return;
-        float d[PACK_PX], cb[PACK_PX], cw[PACK_PX];
-#pragma unroll
-        for (int k = 0; k < PACK_PX; k++) cw[k] = 0.0f;
-        if (P.vec_ok && idx0 + PACK_PX <= npx) {
-            if (P.depth_is_u16) {
-                const uint2 raw = __ldg(reinterpret_cast<const uint2*>((const uint16_t*)F.depth + idx0));
-                d[0] = depth_from_u16(P, raw.x & 0xFFFFu); d[1] = depth_from_u16(P, raw.x >> 16);
-                d[2] = depth_from_u16(P, raw.y & 0xFFFFu); d[3] = depth_from_u16(P, raw.y >> 16);
-            } else {
-                const float4 raw = __ldg(reinterpret_cast<const float4*>((const float*)F.depth + idx0));
-                d[0] = raw.x; d[1] = raw.y; d[2] = raw.z; d[3] = raw.w;
+        const int lane = threadIdx.x & 31;
+        const int base = (bidx * (int)(blockDim.x >> 5) + (int)(threadIdx.x >> 5)) * (32 * PACK_PX) + lane;
+        if (base - lane >= npx) return;
+        uint32_t dv[PACK_PX], cv[PACK_PX];
+        float m[PACK_PX];
+        const bool full = base - lane + 32 * PACK_PX <= npx;
+        if (P.tma_ok) {
+            // The tile's depth, colour and multiplier bytes arrive by three TMA bulk copies (one elected thread, one
+            // mbarrier): the LDG form of the same reads was bounded by the requests an SM may have in flight, not by
+            // HBM.  Dynamic shared memory: [depth | colour or gray | multiplier], PACK_TILE pixels each.
+            extern __shared__ __align__(128) unsigned char k1_smem[];
+            __shared__ __align__(8) uint64_t tile_bar;
+            const int tile0 = bidx * PACK_TILE;
+            const int tpx = min(PACK_TILE, npx - tile0);
+            const uint32_t dbytes = P.depth_is_u16 ? 2u : 4u;
+            const uint32_t cbytes = F.color ? (uint32_t)P.color_channels : (F.gray ? 4u : 0u);
+            unsigned char* s_d = k1_smem;
+            unsigned char* s_c = k1_smem + PACK_TILE * 4;
+            float* s_m = reinterpret_cast<float*>(k1_smem + PACK_TILE * 8);
+            if (threadIdx.x == 0) {
+                mbar_init(&tile_bar, 1);
+                asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+                mbar_expect_tx(&tile_bar, (uint32_t)tpx * (dbytes + cbytes + 4u));
+                tma_load_1d(s_d, (const unsigned char*)F.depth + (size_t)tile0 * dbytes, (uint32_t)tpx * dbytes, &tile_bar);
+                if (cbytes) tma_load_1d(s_c, (F.color ? (const unsigned char*)F.color : (const unsigned char*)F.gray) + (size_t)tile0 * cbytes, (uint32_t)tpx * cbytes, &tile_bar);
+                tma_load_1d(s_m, P.mult + tile0, (uint32_t)tpx * 4u, &tile_bar);
             }
-            if (F.color) {
-                uint32_t px[PACK_PX];   // 0x00BBGGRR in memory order: byte 0 = channel 0
-                if (P.color_channels == 4) {
-                    const uint4 t = __ldg(reinterpret_cast<const uint4*>(F.color) + (idx0 >> 2));
-                    px[0] = t.x; px[1] = t.y; px[2] = t.z; px[3] = t.w;
-                } else {
-                    const uint32_t* c = reinterpret_cast<const uint32_t*>(F.color) + (size_t)(idx0 >> 2) * 3;
-                    const uint32_t w0 = __ldg(c), w1 = __ldg(c + 1), w2 = __ldg(c + 2);
-                    px[0] = w0; px[1] = (w0 >> 24) | (w1 << 8); px[2] = (w1 >> 16) | (w2 << 16); px[3] = w2 >> 8;
-                }
+            __syncthreads();                 // the barrier's initialisation is visible to the waiters
+            mbar_wait(&tile_bar, 0);
+            const int l0 = (threadIdx.x >> 5) * (32 * PACK_PX) + lane;
 #pragma unroll
-                for (int k = 0; k < PACK_PX; k++) {
-                    uint32_t v = px[k] & 0xFFFFFFu;
-                    if (P.color_bgr) v = __byte_perm(v, 0, 0x4012);   // swap byte 0 and byte 2, clear byte 3
-                    pack_rgb(v & 255u, (v >> 8) & 255u, v >> 16, cb[k], cw[k]);
-                }
-            } else if (F.gray) {
-                const float4 g = __ldg(reinterpret_cast<const float4*>(F.gray + idx0));
-                cb[0] = g.x; cb[1] = g.y; cb[2] = g.z; cb[3] = g.w;
-            } else {
-                cb[0] = cb[1] = cb[2] = cb[3] = 0.0f;
+            for (int k = 0; k < PACK_PX; k++) {
+                const int li = min(l0 + 32 * k, tpx - 1);
+                dv[k] = P.depth_is_u16 ? (uint32_t)reinterpret_cast<const uint16_t*>(s_d)[li] : reinterpret_cast<const uint32_t*>(s_d)[li];
+                m[k] = s_m[li];
+                if (cbytes == 4u) cv[k] = reinterpret_cast<const uint32_t*>(s_c)[li];
+                else if (cbytes == 3u) cv[k] = (uint32_t)s_c[3 * li] | ((uint32_t)s_c[3 * li + 1] << 8) | ((uint32_t)s_c[3 * li + 2] << 16);
+                else cv[k] = 0u;
             }
         } else {
 #pragma unroll
-            for (int k = 0; k < PACK_PX; k++) {
-                const int idx = min(idx0 + k, npx - 1);
-                d[k] = load_depth_m(P, F.depth, idx);
-                cb[k] = 0.0f;
-                if (F.color) {
-                    const uint8_t* c = F.color + (size_t)idx * P.color_channels;
-                    uint32_t r = __ldg(c), g = __ldg(c + 1), b = __ldg(c + 2);
-                    if (P.color_bgr) { const uint32_t t = r; r = b; b = t; }
-                    pack_rgb(r, g, b, cb[k], cw[k]);
-                } else if (F.gray) {
-                    cb[k] = __ldg(F.gray + idx);
+        for (int k = 0; k < PACK_PX; k++) {
+            const int idx = full ? base + 32 * k : min(base + 32 * k, npx - 1);
+            dv[k] = P.depth_is_u16 ? (uint32_t)__ldg((const uint16_t*)F.depth + idx) : __float_as_uint(__ldg((const float*)F.depth + idx));
+            m[k] = __ldg(P.mult + idx);
+            if (F.color) {
+                if (P.color_channels == 4) {
+                    cv[k] = __ldg(reinterpret_cast<const uint32_t*>(F.color) + idx);      // 0x..BBGGRR in memory order: byte 0 = channel 0
+                } else {
+                    const uint8_t* q = F.color + (size_t)idx * 3;
+                    cv[k] = (uint32_t)__ldg(q) | ((uint32_t)__ldg(q + 1) << 8) | ((uint32_t)__ldg(q + 2) << 16);
                 }
+            } else if (F.gray) {
+                cv[k] = __float_as_uint(__ldg(F.gray + idx));
+            } else {
+                cv[k] = 0u;
             }
         }
-        int i = idx0 / P.W, j = idx0 - i * P.W;
+        }
+        const uint32_t sel = P.color_bgr ? 0x4012u : 0x4210u;   // swap byte 0 and byte 2 for BGR; byte 3 cleared
 #pragma unroll
         for (int k = 0; k < PACK_PX; k++) {
-            if (idx0 + k < npx) F.texel[idx0 + k] = make_float4(d[k], pack_mult(P, i, j), cb[k], cw[k]);
-            if (++j == P.W) { j = 0; i++; }
+            const int idx = base + 32 * k;
+            const float d = P.depth_is_u16 ? depth_from_u16(P, dv[k]) : __uint_as_float(dv[k]);
+            const uint32_t c = F.color ? __byte_perm(cv[k], 0, sel) : cv[k];
+            if (full || idx < npx) F.texel[idx] = make_float4(d, m[k], __uint_as_float(c), 0.0f);
         }
         return;
     }
     // ---- alloc role (a8): block allocation from the stride-sampled pixels (f64 chain)
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    const int s = bidx * (int)blockDim.x + (int)threadIdx.x;
     const unsigned lane = threadIdx.x & 31u;
     int lo[3] = {0, 0, 0};
     int ny = 1, nz = 1, n = 0;   // n = cells in this sample's box (0: no valid depth)
@@ -224,13 +323,14 @@ __global__ void __launch_bounds__(256, 4) tsdf_pack_alloc_kernel(const __grid_co
         const float d = load_depth_m(P, F.depth, i * P.W + j);
         if (d > 0.0f) {
             const double z = (double)d;
-            const double x = xddiv(xdmul(xdsub((double)j, P.cx), z), P.fx);
-            const double y = xddiv(xdmul(xdsub((double)i, P.cy), z), P.fy);
+            const double x = ddiv_const(xdmul(xdsub((double)j, P.cx), z), P.fx, P.rfx, P.ddiv_fast);
+            const double y = ddiv_const(xdmul(xdsub((double)i, P.cy), z), P.fy, P.rfy, P.ddiv_fast);
             long long ext[3];
 #pragma unroll
             for (int k = 0; k < 3; k++) {
                 const double p = xdadd(xdadd(xdadd(xdmul(F.pose[4 * k], x), xdmul(F.pose[4 * k + 1], y)), xdmul(F.pose[4 * k + 2], z)), F.pose[4 * k + 3]);
-                const double fl = floor(xddiv(xdsub(p, P.trunc), P.unit_length)), fh = floor(xddiv(xdadd(p, P.trunc), P.unit_length));
+                const double fl = floor(ddiv_const(xdsub(p, P.trunc), P.unit_length, P.runit, P.ddiv_fast));
+                const double fh = floor(ddiv_const(xdadd(p, P.trunc), P.unit_length, P.runit, P.ddiv_fast));
                 const bool ok = fl >= -(double)B2R_KEY_BIAS && fh < (double)B2R_KEY_BIAS;   // also false for NaN
                 lo[k] = ok ? (int)fl : 0;
                 ext[k] = ok ? (long long)((int)fh - (int)fl + 1) : -1;
@@ -242,71 +342,92 @@ __global__ void __launch_bounds__(256, 4) tsdf_pack_alloc_kernel(const __grid_co
             }
         }
     }
-    // Neighbouring samples mostly share a box.  Keep one box per RUN of equal boxes (run heads), lay the heads'
-    // cells end to end, and deal the cells out to the 256 threads of the block: ~1 cell per thread instead of
-    // 8-27 per sample.  Per cell: (A) one slot probe -- the common case (unit exists, this frame's bit already
-    // set) ends there; (B) lanes holding the same key elect a leader (match.any) whose atomicOr marks the unit;
-    // (C) first touches append to the touched list; absent keys / collisions take the probing slow path.
+    // Neighbouring samples mostly share a box.  Keep one box per RUN of equal boxes (run heads) and let every head
+    // write its cells' keys, end to end, into a shared list; then the 256 threads take the cells ALLOC_IT at a time:
+    // (A) the slot probes of all of a thread's cells are issued together -- the common case (unit exists, this frame's
+    // bit already set) ends there; (B) lanes holding the same key elect a leader (match.any) whose atomicOr marks the
+    // unit; (C) the atomics' results are consumed only after all of them are in flight, and first touches are appended
+    // to the touched list with one counter atomic per warp.  Absent keys / collisions take the probing slow path.
     __shared__ int s_lo[256][3];
-    __shared__ int s_dim[256][2];     // ny, nz of the head's box
-    __shared__ int s_start[257];      // first cell of head h in the block's cell sequence
     __shared__ int s_n[256];
+    __shared__ int s_dim[256][2];     // ny, nz of the box
     __shared__ int s_warp[2][8];
+    extern __shared__ __align__(128) unsigned char k1_smem[];
+    uint64_t* s_cell = reinterpret_cast<uint64_t*>(k1_smem);    // ALLOC_CELLS * 8 <= K1_DYN_SMEM
     const int t = threadIdx.x, warp = t >> 5;
     s_lo[t][0] = lo[0]; s_lo[t][1] = lo[1]; s_lo[t][2] = lo[2]; s_dim[t][0] = ny; s_dim[t][1] = nz; s_n[t] = n;
     __syncthreads();
     bool head = n > 0;
     if (head && t > 0)
         head = !(s_lo[t - 1][0] == lo[0] && s_lo[t - 1][1] == lo[1] && s_lo[t - 1][2] == lo[2] && s_dim[t - 1][0] == ny && s_dim[t - 1][1] == nz && s_n[t - 1] == n);
-    // block scans: heads before me, cells before me
-    int hc = head ? 1 : 0, cc_ = head ? n : 0;
-    int hi_ = hc, ci_ = cc_;
+    // block scan: cells before me
+    const int cc_ = head ? n : 0;
+    int ci_ = cc_;
     for (int o = 1; o < 32; o <<= 1) {
-        const int a1 = __shfl_up_sync(0xffffffffu, hi_, o), a2 = __shfl_up_sync(0xffffffffu, ci_, o);
-        if ((int)lane >= o) { hi_ += a1; ci_ += a2; }
+        const int a2 = __shfl_up_sync(0xffffffffu, ci_, o);
+        if ((int)lane >= o) ci_ += a2;
     }
-    if (lane == 31) { s_warp[0][warp] = hi_; s_warp[1][warp] = ci_; }
-    __syncthreads();   // also: everyone has read its left neighbour's box
-    int hbase = 0, cbase = 0, nheads = 0, ncells = 0;
-#pragma unroll
-    for (int w = 0; w < 8; w++) { if (w < warp) { hbase += s_warp[0][w]; cbase += s_warp[1][w]; } nheads += s_warp[0][w]; ncells += s_warp[1][w]; }
-    const int my_h = hbase + hi_ - hc, my_c = cbase + ci_ - cc_;
-    __syncthreads();   // s_lo / s_dim are about to be overwritten in head order
-    if (head) { s_lo[my_h][0] = lo[0]; s_lo[my_h][1] = lo[1]; s_lo[my_h][2] = lo[2]; s_dim[my_h][0] = ny; s_dim[my_h][1] = nz; s_start[my_h] = my_c; }
-    if (t == 0) s_start[nheads] = ncells;
+    if (lane == 31) s_warp[1][warp] = ci_;
     __syncthreads();
-    for (int c0 = 0; c0 < ncells; c0 += 256) {      // block-uniform trip count: every lane reaches the match.any
-        const int c = c0 + t;
-        uint64_t want = B2R_KEY_EMPTY;
-        uint32_t slot_i = 0;
-        if (c < ncells) {
-            int lo_h = 0, hi_h = nheads - 1;          // last head whose start <= c
-            while (lo_h < hi_h) { const int mid = (lo_h + hi_h + 1) >> 1; if (s_start[mid] <= c) lo_h = mid; else hi_h = mid - 1; }
-            const int r = c - s_start[lo_h], dy = s_dim[lo_h][0], dz = s_dim[lo_h][1];
-            const int a = s_lo[lo_h][0] + r / (dy * dz), b = s_lo[lo_h][1] + (r / dz) % dy, cz = s_lo[lo_h][2] + r % dz;
-            const uint64_t key = b2r_pack_key(a, b, cz);
-            const uint64_t hsh = b2r_mix64(key);
-            if (P.world <= 1 || (int)((hsh >> 33) % (uint64_t)P.world) == P.rank) { want = key; slot_i = (uint32_t)hsh & P.hash.mask; }
+    int cbase = 0, ncells = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) { if (w < warp) cbase += s_warp[1][w]; ncells += s_warp[1][w]; }
+    const int my_c = cbase + ci_ - cc_;
+    // The list holds ALLOC_CELLS cells; a block with more (large truncation against the unit length) goes round again.
+    for (int w0 = 0; w0 < ncells; w0 += ALLOC_CELLS) {
+        if (w0) __syncthreads();                       // the previous window has been consumed
+        if (head && my_c < w0 + ALLOC_CELLS && my_c + n > w0) {
+            const int nx = n / (ny * nz);
+            int c = my_c - w0;
+            for (int a = 0; a < nx; a++)
+                for (int b = 0; b < ny; b++)
+                    for (int cz = 0; cz < nz; cz++, c++)
+                        if (c >= 0 && c < ALLOC_CELLS) s_cell[c] = b2r_pack_key(lo[0] + a, lo[1] + b, lo[2] + cz);
         }
-        uint64_t got = 0;
-        uint32_t mk = 0;
-        if (want != B2R_KEY_EMPTY) {
-            const B2RSlot* slot = &P.hash.slots[slot_i];
-            got = __ldcg(reinterpret_cast<const unsigned long long*>(&slot->key));
-            mk = __ldcg(&slot->mask[P.q]);
-        }
-        const bool live = want != B2R_KEY_EMPTY && !(got == want && (mk & F.bit));
-        const unsigned peers = __match_any_sync(0xffffffffu, live ? want : (B2R_KEY_EMPTY - 1 - lane));
-        const bool leader = live && (lane == (unsigned)(__ffs(peers) - 1));
-        if (leader) {
-            if (got == want) {
-                const uint32_t old = atomicOr(&P.hash.slots[slot_i].mask[P.q], F.bit);
-                if (old == 0) {
-                    const int pos = atomicAdd(&P.counters[B2R_C_TOUCHED0 + P.q], 1);
-                    if (pos < P.cap_units) P.touched[pos] = (int)slot_i;
+        __syncthreads();
+        const int wn = min(ALLOC_CELLS, ncells - w0);
+        for (int c0 = 0; c0 < wn; c0 += 256 * ALLOC_IT) {   // block-uniform trip counts: every lane reaches the match.any
+            uint64_t want[ALLOC_IT], got[ALLOC_IT];
+            uint32_t slot_i[ALLOC_IT], mk[ALLOC_IT], old[ALLOC_IT];
+#pragma unroll
+            for (int it = 0; it < ALLOC_IT; it++) {
+                const int c = c0 + it * 256 + t;
+                want[it] = B2R_KEY_EMPTY; got[it] = 0; mk[it] = 0; slot_i[it] = 0;
+                if (c < wn) {
+                    const uint64_t key = s_cell[c];
+                    const uint64_t hsh = b2r_mix64(key);
+                    if (P.world <= 1 || (int)((hsh >> 33) % (uint64_t)P.world) == P.rank) {
+                        want[it] = key; slot_i[it] = (uint32_t)hsh & P.hash.mask;
+                        const B2RSlot* slot = &P.hash.slots[slot_i[it]];
+                        got[it] = __ldcg(reinterpret_cast<const unsigned long long*>(&slot->key));
+                        mk[it] = __ldcg(&slot->mask[P.q]);
+                    }
                 }
-            } else {
-                alloc_key(P, want, F.bit);
+            }
+            unsigned first = 0;                          // bit it: this lane saw the first touch of (unit, batch)
+#pragma unroll
+            for (int it = 0; it < ALLOC_IT; it++) {
+                old[it] = 1u;
+                if (c0 + it * 256 >= wn) break;          // block-uniform
+                const bool live = want[it] != B2R_KEY_EMPTY && !(got[it] == want[it] && (mk[it] & F.bit));
+                if (!__any_sync(0xffffffffu, live)) continue;
+                const unsigned peers = __match_any_sync(0xffffffffu, live ? want[it] : (B2R_KEY_EMPTY - 1 - lane));
+                const bool leader = live && (lane == (unsigned)(__ffs(peers) - 1));
+                if (leader) {
+                    if (got[it] == want[it]) { old[it] = atomicOr(&P.hash.slots[slot_i[it]].mask[P.q], F.bit); first |= 1u << it; }
+                    else alloc_key(P, want[it], F.bit);
+                }
+            }
+#pragma unroll
+            for (int it = 0; it < ALLOC_IT; it++) {
+                if (c0 + it * 256 >= wn) break;
+                const bool app = ((first >> it) & 1u) && old[it] == 0u;
+                const unsigned am = __ballot_sync(0xffffffffu, app);
+                if (am == 0u) continue;
+                int pos = 0;
+                if (lane == (unsigned)(__ffs(am) - 1)) pos = atomicAdd(&P.counters[B2R_C_TOUCHED0 + P.q], __popc(am));
+                pos = __shfl_sync(0xffffffffu, pos, __ffs(am) - 1) + __popc(am & ((1u << lane) - 1u));
+                if (app && pos < P.cap_units) P.touched[pos] = (int)slot_i[it];
             }
         }
     }
@@ -338,31 +459,6 @@ struct FuseParams {
     int cap_units;
     B2RFrame fr[B2R_MAX_BATCH];
 };
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE_%=;\n"
-        "bra WAIT_%=;\n"
-        "DONE_%=:\n"
-        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-// TMA bulk copy global -> shared, completion counted on an mbarrier (SASS: UBLKCP)
-__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
-                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
 
 template <int COLOR, int FUSE_STAGES>
 __global__ void __launch_bounds__(FUSE_THREADS, FUSE_MIN_CTAS) tsdf_fuse_kernel(const __grid_constant__ FuseParams P) {
@@ -592,6 +688,7 @@ static void tsdf_free(b2r_tsdf* h) {
     cudaFree(h->pool); cudaFree(h->counters); cudaFree(h->scratch);
     for (int i = 0; i < 3; i++) cudaFree(h->touched[i]);
     for (int i = 0; i < B2R_MAX_BATCH; i++) cudaFree(h->texel[i]);
+    cudaFree(h->mult);
     for (int i = 0; i < B2R_HOST_RING; i++) {
         if (h->ev_copied[i]) cudaEventDestroy(h->ev_copied[i]);
         if (h->ev_consumed[i]) cudaEventDestroy(h->ev_consumed[i]);
@@ -750,6 +847,15 @@ int b2r_tsdf_flush_pending(b2r_tsdf* h, cudaStream_t stream) {
 // ------------------------------------------------------------------------------------------------
 // integrate (device inputs): K1 now, K2 when the batch is full or the volume is read
 // ------------------------------------------------------------------------------------------------
+static bool host_fdiv_domain(float b) {    // b2r_div_domain on the host
+    uint32_t u; memcpy(&u, &b, 4);
+    return ((u >> 23) - 67u) < 120u && (u & 0x7FFFFFu) != 0x7FFFFFu;
+}
+static bool host_ddiv_domain(double b) {   // positive, 2^-60 <= b < 2^60, significand not all ones
+    uint64_t u; memcpy(&u, &b, 8);
+    const uint64_t e = u >> 52, m = u & 0xFFFFFFFFFFFFFull;
+    return e >= 1023 - 60 && e < 1023 + 60 && m != 0xFFFFFFFFFFFFFull;
+}
 static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth_is_u16, float depth_scale, float depth_trunc,
                                const uint8_t* color, int color_channels, int color_bgr, const float* gray, int W,
                                int H, double fx, double fy, double cx, double cy, const double* extrinsics,
@@ -769,6 +875,22 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
         for (int i = 0; i < h->max_batch; i++) B2R_CUDA(cudaMalloc((void**)&h->texel[i], npx * sizeof(float4)));
         h->texel_px = npx;
     }
+    const float fcx = (float)cx, fcy = (float)cy, ifx = 1.0f / (float)fx, ify = 1.0f / (float)fy;
+    const double mkey[6] = {(double)W, (double)H, fx, fy, cx, cy};
+    if (!h->mult || h->mult_px < npx || memcmp(mkey, h->mult_key, sizeof(mkey)) != 0) {
+        if (h->mult_px < npx) {
+            int rc = b2r_tsdf_flush_pending(h, stream);
+            if (rc != B2R_OK) return rc;
+            B2R_CUDA(cudaStreamSynchronize(stream));
+            if (h->mult) cudaFree(h->mult);
+            h->mult = nullptr; h->mult_px = 0;
+            B2R_CUDA(cudaMalloc((void**)&h->mult, npx * sizeof(float)));
+            h->mult_px = npx;
+        }
+        tsdf_mult_kernel<<<(unsigned)((npx + 255) / 256), 256, 0, stream>>>(h->mult, W, H, fcx, fcy, ifx, ify);
+        B2R_CHECK_LAUNCH();
+        memcpy(h->mult_key, mkey, sizeof(mkey));
+    }
     const size_t dstep = npx * (depth_is_u16 ? 2 : 4), cstep = npx * (size_t)color_channels;
     int done = 0;
     while (done < nf) {
@@ -782,7 +904,11 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
         P.W = W; P.H = H; P.depth_is_u16 = depth_is_u16;
         P.depth_scale = depth_scale; P.depth_trunc = depth_trunc;
         P.color_channels = color_channels; P.color_bgr = color_bgr;
-        P.fcx = (float)cx; P.fcy = (float)cy; P.ifx = 1.0f / (float)fx; P.ify = 1.0f / (float)fy;
+        P.fcx = fcx; P.fcy = fcy; P.ifx = ifx; P.ify = ify;
+        P.mult = h->mult;
+        P.rscale = 1.0f / depth_scale; P.scale_fast = host_fdiv_domain(depth_scale) ? 1 : 0;
+        P.rfx = 1.0 / fx; P.rfy = 1.0 / fy; P.runit = 1.0 / h->unit_length;
+        P.ddiv_fast = (host_ddiv_domain(fx) && host_ddiv_domain(fy) && host_ddiv_domain(h->unit_length)) ? 1 : 0;
         P.fx = fx; P.fy = fy; P.cx = cx; P.cy = cy;
         P.trunc = h->sdf_trunc; P.unit_length = h->unit_length; P.stride = h->stride;
         P.Ws = (W + h->stride - 1) / h->stride;
@@ -811,12 +937,17 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
             fr.safe_w = (float)W - 0.0001f; fr.safe_h = (float)H - 0.0001f;
             fr.W = W; fr.H = H; fr.texel = h->texel[slot];
         }
-        const size_t cbpp = (h->color_type == 1) ? (size_t)color_channels : (h->color_type == 2 ? 4 : 0);
-        P.vec_ok = (npx % 4 == 0) && ((uintptr_t)depth % 16 == 0) && (dstep % 16 == 0) &&
-                   (cbpp == 0 || ((uintptr_t)(h->color_type == 1 ? (const void*)color : (const void*)gray) % 16 == 0 && (npx * cbpp) % 16 == 0));
+        {
+            const void* cimg = (h->color_type == 1) ? (const void*)color : (h->color_type == 2 ? (const void*)gray : nullptr);
+            const size_t cb = (h->color_type == 1) ? (size_t)color_channels : (h->color_type == 2 ? 4 : 0);
+            P.tma_ok = (npx % 16 == 0) && ((uintptr_t)depth % 16 == 0) && (dstep % 16 == 0) &&
+                       (cb == 0 || ((uintptr_t)cimg % 16 == 0 && (npx * cb) % 16 == 0)) ? 1 : 0;
+            const char* e = getenv("B2R_K1_TMA");      // "0": force the LDG form of the pack role (parity test of the unaligned-image path)
+            if (e && atoi(e) == 0) P.tma_ok = 0;
+        }
         const dim3 grid((unsigned)(P.n_alloc_blocks + (npx + 256 * PACK_PX - 1) / (256 * PACK_PX)), (unsigned)take);
         const bool prof = prof_begin(h, 1, stream);
-        tsdf_pack_alloc_kernel<<<grid, 256, 0, stream>>>(P);
+        tsdf_pack_alloc_kernel<<<grid, 256, K1_DYN_SMEM, stream>>>(P);
         B2R_CHECK_LAUNCH();
         prof_end(h, prof, stream);
         h->pending += take;
@@ -1131,6 +1262,40 @@ B2R_API int b2r_selftest_div(int64_t n_per_mode, uint64_t seed, int64_t* mismatc
     if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
     cudaFree(d);
     if (e != cudaSuccess) { b2r_set_error("b2r_selftest_div: %s", cudaGetErrorString(e)); return B2R_ERR_CUDA; }
+    *mismatches_host = (int64_t)hcount;
+    return B2R_OK;
+}
+
+// Self-test of ddiv_const (the f64 shared-reciprocal division of the allocation samples): for the divisor b (fx, fy or
+// the unit length of a call) and its host-rounded reciprocal, counts numerators whose quotient differs bitwise from
+// div.rn.f64.  Numerators: random sign/significand, exponents 2^-40 .. 2^23, plus exact multiples of b and 0.
+__global__ void selftest_ddiv_kernel(double b, double y, uint64_t seed, int iters, unsigned long long* mismatches) {
+    uint64_t s = b2r_mix64(seed + ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 0x9E3779B97F4A7C15ull);
+    unsigned bad = 0;
+    for (int i = 0; i < iters; i++) {
+        const uint64_t r0 = ((uint64_t)selftest_rng(s) << 32) | selftest_rng(s);
+        const uint32_t r1 = selftest_rng(s);
+        double a = __longlong_as_double((long long)((r0 & 0x800FFFFFFFFFFFFFull) | ((uint64_t)(1023 - 40 + (r1 & 63u)) << 52)));
+        if ((r1 >> 8) % 61u == 0u) a = __dmul_rn(b, (double)((int)(r1 >> 16) - 32768));   // exact multiples, incl. 0
+        const double q = ddiv_const(a, b, y, 1), ref = __ddiv_rn(a, b);
+        bad += (__double_as_longlong(q) != __double_as_longlong(ref)) ? 1u : 0u;
+    }
+    if (bad) atomicAdd(mismatches, (unsigned long long)bad);
+}
+// Returns B2R_ERR_BAD_ARG when b is outside the domain the integrate call would accept for the fast path.
+B2R_API int b2r_selftest_ddiv(double b, int64_t n, uint64_t seed, int64_t* mismatches_host, cudaStream_t stream) {
+    if (!mismatches_host || n < 1 || !host_ddiv_domain(b)) return B2R_ERR_BAD_ARG;
+    unsigned long long* d = nullptr;
+    B2R_CUDA(cudaMalloc(&d, 8));
+    B2R_CUDA(cudaMemsetAsync(d, 0, 8, stream));
+    const int threads = 256, blocks = 1024;
+    const int iters = (int)((n + (int64_t)threads * blocks - 1) / ((int64_t)threads * blocks));
+    selftest_ddiv_kernel<<<blocks, threads, 0, stream>>>(b, 1.0 / b, seed, iters, d);
+    unsigned long long hcount = 0;
+    cudaError_t e = cudaMemcpyAsync(&hcount, d, 8, cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    cudaFree(d);
+    if (e != cudaSuccess) { b2r_set_error("b2r_selftest_ddiv: %s", cudaGetErrorString(e)); return B2R_ERR_CUDA; }
     *mismatches_host = (int64_t)hcount;
     return B2R_OK;
 }

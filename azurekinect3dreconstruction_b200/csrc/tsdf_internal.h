@@ -44,6 +44,9 @@ struct b2r_tsdf {
     B2RFrame frames[B2R_MAX_BATCH];
     float4* texel[B2R_MAX_BATCH];
     size_t texel_px;
+    float* mult;             // depth-to-camera-distance multiplier image of the cached intrinsics (shared by every frame)
+    size_t mult_px;
+    double mult_key[6];      // W, H, fx, fy, cx, cy the image was computed for
     int64_t batches;       // fused so far (alternates the sweep direction)
     int fuse_grid;         // persistent grid size of the fusion kernel
     int fuse_smem;         // dynamic shared memory of the fusion kernel

@@ -137,6 +137,9 @@ int b2r_selftest_u8_div255(void);
 /* GPU self-test of the shared-reciprocal IEEE division used by the fusion kernel: number of inputs whose
  * quotient differs bitwise from div.rn.f32 (must be 0) */
 int b2r_selftest_div(int64_t n_per_mode, uint64_t seed, int64_t* mismatches_host, cudaStream_t stream);
+/* Same for the f64 division by a per-call constant (fx, fy, unit length) in the allocation samples of a8: number of
+ * random numerators whose quotient by `b` differs bitwise from div.rn.f64 (must be 0) */
+int b2r_selftest_ddiv(double b, int64_t n, uint64_t seed, int64_t* mismatches_host, cudaStream_t stream);
 /* parity / checkpoint hooks: keys int32[n][3]; planes tsdf[n][4096], weight[n][4096], rgb[n][3][4096],
  * voxel index x*256 + y*16 + z (upstream IndexOf) */
 int b2r_tsdf_export_keys(b2r_tsdf* h, int32_t* keys3, int64_t n, cudaStream_t stream);

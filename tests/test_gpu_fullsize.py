@@ -93,6 +93,12 @@ def test_tsdf_full_size_invariances(nfov):
     assert same_state(ref, volume_state(run(1)))                          # fusion batch size does not change a bit
     assert same_state(ref, volume_state(run(5)))
     assert same_state(ref, volume_state(run(16, host=True)))              # nor does the ingest path
+    import os
+    os.environ["B2R_K1_TMA"] = "0"                                        # nor the LDG form of the pack role (unaligned images take it)
+    try:
+        assert same_state(ref, volume_state(run(16)))
+    finally:
+        del os.environ["B2R_K1_TMA"]
     # reset + replay is idempotent
     ref_vol.reset()
     assert ref_vol.num_units() == 0

@@ -282,6 +282,16 @@ def test_shared_reciprocal_division_is_ieee_exact():
     assert bad.value == 0
 
 
+def test_allocation_f64_division_by_call_constants_is_ieee_exact():
+    """a8's samples divide by fx, fy and the unit length through one host-rounded reciprocal each (K1); == div.rn.f64."""
+    import ctypes as C
+    from azurekinect3dreconstruction_b200 import _lib
+    for b in (504.2, 504.1, 605.6, 0.064, 0.032, 0.64, 4.0 / 512.0 * 16, 525.0, 1.0, 3.0, 1.0 / 3.0):
+        bad = C.c_int64(-1)
+        _lib.check(_lib.load().b2r_selftest_ddiv(b, 1 << 24, 777, C.byref(bad), _lib.stream_ptr()))
+        assert bad.value == 0, b
+
+
 def test_tsdf_batch_size_invariance(frames, small_kinect):
     """Deferred multi-frame fusion == frame-by-frame fusion, bit for bit, on every plane (incl. colour)."""
     intr = small_kinect.depth_intr
