@@ -315,3 +315,42 @@ def load_calibration(path: str):
     Ks = [PinholeCameraIntrinsic(d["width"], d["height"], d["fx"], d["fy"], d["cx"], d["cy"]) for d in data["intrinsics"]]
     Es = [np.asarray(e, dtype=np.float64) for e in data["extrinsics"]]
     return Ks, Es, data
+
+
+# ---- pose-graph JSON (o3d.io.write_pose_graph / read_pose_graph; capture_frames.py:62-64, bundlefusion_reconstruction.py:284-286)
+# Open3D's IJsonConvertible layout: matrices as flat arrays in Eigen's column-major coefficient order, every object
+# tagged with class_name / version_major / version_minor.
+def _pg_mat(a) -> list:
+    return [float(v) for v in np.asarray(a, dtype=np.float64).reshape(a.shape).T.reshape(-1)]
+
+
+def write_pose_graph(filename: str, pose_graph) -> bool:
+    doc = {
+        "class_name": "PoseGraph",
+        "edges": [{"class_name": "PoseGraphEdge", "confidence": float(e.confidence), "information": _pg_mat(e.information),
+                   "source_node_id": int(e.source_node_id), "target_node_id": int(e.target_node_id),
+                   "transformation": _pg_mat(e.transformation), "uncertain": bool(e.uncertain),
+                   "version_major": 1, "version_minor": 0} for e in pose_graph.edges],
+        "nodes": [{"class_name": "PoseGraphNode", "pose": _pg_mat(nd.pose), "version_major": 1, "version_minor": 0}
+                  for nd in pose_graph.nodes],
+        "version_major": 1, "version_minor": 0,
+    }
+    with open(filename, "w") as f:
+        json.dump(doc, f, indent="\t", sort_keys=True)
+        f.write("\n")
+    return True
+
+
+def read_pose_graph(filename: str):
+    from .pipelines.registration import PoseGraph, PoseGraphEdge, PoseGraphNode
+    with open(filename) as f:
+        doc = json.load(f)
+    if doc.get("class_name") != "PoseGraph":
+        raise RuntimeError("read_pose_graph: not a PoseGraph file: " + filename)
+    pg = PoseGraph()
+    for nd in doc.get("nodes", []):
+        pg.nodes.append(PoseGraphNode(np.asarray(nd["pose"], dtype=np.float64).reshape(4, 4).T))
+    for e in doc.get("edges", []):
+        pg.edges.append(PoseGraphEdge(e["source_node_id"], e["target_node_id"], np.asarray(e["transformation"], dtype=np.float64).reshape(4, 4).T,
+                                      np.asarray(e["information"], dtype=np.float64).reshape(6, 6).T, bool(e["uncertain"]), float(e["confidence"])))
+    return pg

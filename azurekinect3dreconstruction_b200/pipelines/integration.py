@@ -205,3 +205,21 @@ class ScalableTSDFVolume:
 
     def __repr__(self):
         return "ScalableTSDFVolume (B200) with %s." % ("no color" if self.color_type == 0 else "color")
+
+
+def reintegrate_frames(volume: ScalableTSDFVolume, depth_u16, color_u8, pose_graph, intrinsic: PinholeCameraIntrinsic,
+                       depth_scale: float = 1000.0, depth_trunc: float = 3.0, color_bgr: bool = False,
+                       pose_is_extrinsic: bool = False, chunk: int = 64) -> None:
+    """f3's GPU half: ``volume.reset()`` + every frame fused again under the optimised poses, through the batched path.
+
+    capture_frames.py:92-105 passes ``np.linalg.inv(node.pose)`` as the extrinsic (``pose_is_extrinsic=False``);
+    bundlefusion_reconstruction.py:306-315 passes ``node.pose`` itself (``pose_is_extrinsic=True``).
+    depth_u16 (n,H,W) / color_u8 (n,H,W,3|4): device or pinned-host tensors, frame i belongs to node i."""
+    n = len(pose_graph.nodes)
+    if depth_u16.shape[0] < n:
+        raise RuntimeError("reintegrate_frames: fewer frames than pose-graph nodes")
+    volume.reset()
+    for a in range(0, n, chunk):
+        b = min(n, a + chunk)
+        E = np.stack([nd.pose if pose_is_extrinsic else np.linalg.inv(nd.pose) for nd in pose_graph.nodes[a:b]])
+        volume.integrate_raw(depth_u16[a:b], color_u8[a:b] if color_u8 is not None else None, intrinsic, E, depth_scale, depth_trunc, color_bgr)

@@ -83,3 +83,112 @@ def registration_icp(source: PointCloud, target: PointCloud, max_correspondence_
         src_i = torch.nonzero(c >= 0).flatten().to(torch.int32)
         res.correspondence_set = Vector2iVector(torch.stack([src_i, c[src_i.long()]], dim=1))
     return res
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# f3: PoseGraph + global optimisation.  Reference call sites: capture_frames.py:31-32,74-89,164-166;
+# bundlefusion_reconstruction.py:179-199,232-273,292-304.  Field names and defaults follow Open3D 0.19
+# (pipelines/registration/PoseGraph.h, GlobalOptimizationConvergenceCriteria.h).
+# ---------------------------------------------------------------------------------------------------------------
+class PoseGraphNode:
+    def __init__(self, pose=None):
+        self.pose = np.identity(4) if pose is None else np.array(pose, dtype=np.float64).reshape(4, 4)
+
+    def __repr__(self):
+        return "PoseGraphNode, access pose to get its current pose."
+
+
+class PoseGraphEdge:
+    def __init__(self, source_node_id: int = -1, target_node_id: int = -1, transformation=None, information=None,
+                 uncertain: bool = False, confidence: float = 1.0):
+        self.source_node_id = int(source_node_id)
+        self.target_node_id = int(target_node_id)
+        self.transformation = np.identity(4) if transformation is None else np.array(transformation, dtype=np.float64).reshape(4, 4)
+        self.information = np.identity(6) if information is None else np.array(information, dtype=np.float64).reshape(6, 6)
+        self.uncertain = bool(uncertain)
+        self.confidence = float(confidence)
+
+    def __repr__(self):
+        return "PoseGraphEdge from nodes %d to %d, access transformation to get relative transformation" % (self.source_node_id, self.target_node_id)
+
+
+class PoseGraph:
+    def __init__(self):
+        self.nodes = []
+        self.edges = []
+
+    def __repr__(self):
+        return "PoseGraph with %d nodes and %d edges." % (len(self.nodes), len(self.edges))
+
+
+class GlobalOptimizationOption:
+    def __init__(self, max_correspondence_distance: float = 0.075, edge_prune_threshold: float = 0.25,
+                 preference_loop_closure: float = 1.0, reference_node: int = -1):
+        self.max_correspondence_distance = float(max_correspondence_distance)
+        self.edge_prune_threshold = float(edge_prune_threshold)
+        self.preference_loop_closure = float(preference_loop_closure)
+        self.reference_node = int(reference_node)
+
+
+class GlobalOptimizationConvergenceCriteria:
+    def __init__(self):
+        self.max_iteration = 100
+        self.min_relative_increment = 1e-6
+        self.min_relative_residual_increment = 1e-6
+        self.min_right_term = 1e-6
+        self.min_residual = 1e-6
+        self.max_iteration_lm = 20
+        self.upper_scale_factor = 2.0 / 3.0
+        self.lower_scale_factor = 1.0 / 3.0
+
+
+class GlobalOptimizationMethod:
+    pass
+
+
+class GlobalOptimizationLevenbergMarquardt(GlobalOptimizationMethod):
+    pass
+
+
+class GlobalOptimizationGaussNewton(GlobalOptimizationMethod):
+    """Present for name compatibility; the reference only ever passes Levenberg-Marquardt."""
+
+
+def global_optimization(pose_graph: PoseGraph, method: GlobalOptimizationMethod, criteria: GlobalOptimizationConvergenceCriteria,
+                        option: GlobalOptimizationOption) -> None:
+    """o3d.pipelines.registration.global_optimization: optimises ``pose_graph`` IN PLACE (poses updated, uncertain edges
+    under the prune threshold removed, confidences refreshed).  An invalid graph is left untouched with a warning, as
+    upstream does.  ``pose_graph.last_report`` (build extension) carries the iteration counts and residuals."""
+    if not isinstance(method, GlobalOptimizationLevenbergMarquardt):
+        raise NotImplementedError("global_optimization: only GlobalOptimizationLevenbergMarquardt is built (the reference uses no other)")
+    lib = _lib.load()
+    n, m = len(pose_graph.nodes), len(pose_graph.edges)
+    poses = np.ascontiguousarray(np.stack([nd.pose for nd in pose_graph.nodes]).astype(np.float64)) if n else np.zeros((0, 4, 4))
+    src = np.array([e.source_node_id for e in pose_graph.edges], dtype=np.int32)
+    dst = np.array([e.target_node_id for e in pose_graph.edges], dtype=np.int32)
+    trans = np.ascontiguousarray(np.stack([e.transformation for e in pose_graph.edges]).astype(np.float64)) if m else np.zeros((0, 4, 4))
+    info = np.ascontiguousarray(np.stack([e.information for e in pose_graph.edges]).astype(np.float64)) if m else np.zeros((0, 6, 6))
+    unc = np.array([1 if e.uncertain else 0 for e in pose_graph.edges], dtype=np.uint8)
+    conf = np.array([e.confidence for e in pose_graph.edges], dtype=np.float64)
+    keep = np.ones(m, dtype=np.uint8)
+    opt = np.array([option.max_correspondence_distance, option.edge_prune_threshold, option.preference_loop_closure, option.reference_node], dtype=np.float64)
+    cri = np.array([criteria.max_iteration, criteria.min_relative_increment, criteria.min_relative_residual_increment, criteria.min_right_term,
+                    criteria.min_residual, criteria.max_iteration_lm, criteria.upper_scale_factor, criteria.lower_scale_factor], dtype=np.float64)
+    rep = np.zeros(8, dtype=np.float64)
+    p = lambda a: a.ctypes.data_as(C.c_void_p) if a.size else None
+    rc = lib.b2r_posegraph_optimize(n, p(poses), m, p(src), p(dst), p(trans), p(info), p(unc), p(conf), p(keep), p(opt), p(cri), p(rep))
+    _lib.check(rc, "global_optimization")
+    pose_graph.last_report = dict(valid=bool(rep[0]), iterations=(int(rep[1]), int(rep[3])), lm_steps=(int(rep[2]), int(rep[4])),
+                                  residual_before=float(rep[5]), residual_after=float(rep[6]), edges_kept=int(rep[7]))
+    if not rep[0]:
+        import warnings
+        warnings.warn("[GlobalOptimization] " + _lib.last_error())
+        return
+    for i, nd in enumerate(pose_graph.nodes):
+        nd.pose = poses[i].copy()
+    kept = []
+    for k, e in enumerate(pose_graph.edges):
+        if keep[k]:
+            e.confidence = float(conf[k])
+            kept.append(e)
+    pose_graph.edges = kept

@@ -224,6 +224,23 @@ int b2r_pcd_voxel_down_sample(const double* xyz, const double* col, const double
 /* get_min_bound / get_max_bound: out6_host = {min xyz, max xyz}.  Synchronises. */
 int b2r_pcd_bounds(const double* xyz, int64_t n, double* out6_host, cudaStream_t stream);
 
+/* ---- f3: o3d.pipelines.registration.global_optimization(pose_graph, GlobalOptimizationLevenbergMarquardt(),
+ *      GlobalOptimizationConvergenceCriteria(), GlobalOptimizationOption(...))
+ *      (CodeThatKindaWorks/capture_frames.py:74-89; bundlefusion_reconstruction.py:260-273,292-304).
+ *      HOST arrays, row-major f64 (a small sparse LM); no CUDA device needed.
+ *      poses[n_nodes][16] in/out; transformation[n_edges][16]; information[n_edges][36]; confidence in/out;
+ *      keep[n_edges] out (upstream replaces the graph by the pruned one: drop the edges with keep == 0);
+ *      option4 = {max_correspondence_distance, edge_prune_threshold, preference_loop_closure, reference_node};
+ *      criteria8 = {max_iteration, min_relative_increment, min_relative_residual_increment, min_right_term,
+ *                   min_residual, max_iteration_lm, upper_scale_factor, lower_scale_factor};
+ *      report8 (may be NULL) = {valid, iterations / LM steps of pass 1, of pass 2, residual before, after, edges kept}.
+ *      An invalid graph (unconnected, bad node id, certain edge with confidence != 1) is left untouched as
+ *      upstream does (warning text in b2r_last_error, report8[0] = 0, returns B2R_OK). */
+int b2r_posegraph_optimize(int n_nodes, double* poses, int n_edges, const int32_t* src, const int32_t* dst,
+                           const double* transformation, const double* information, const uint8_t* uncertain,
+                           double* confidence, uint8_t* keep, const double* option4, const double* criteria8,
+                           double* report8);
+
 #ifdef __cplusplus
 }
 #endif

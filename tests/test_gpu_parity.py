@@ -587,3 +587,56 @@ def test_icp_parity(o3r, frames, small_kinect):
         o3d.pipelines.registration.registration_icp(s, t2, 0.03, init, o3d.pipelines.registration.TransformationEstimationPointToPlane())
     with pytest.raises(RuntimeError):
         o3d.pipelines.registration.registration_icp(s, t, 0.0, init, o3d.pipelines.registration.TransformationEstimationPointToPlane())
+
+
+def test_posegraph_loop_odometry_optimise_reintegrate(frames, small_kinect):
+    """f3, the flow of capture_frames.py:118-198: odometry edges (a12's transformation + information) -> pose graph with a
+    loop closure -> global_optimization -> volume.reset() + re-integration under the optimised poses (batched path).
+    The re-integrated volume must equal, bit for bit, the same poses integrated frame by frame through the Open3D-shaped call."""
+    intr = small_kinect.depth_intr
+    K = intrinsic_of(intr)
+    Rg = o3d.pipelines.registration
+    frames = []                                                            # small inter-frame motion (0.4 deg / 4 mm, as in config 4)
+    for p in syn.orbit_trajectory(300)[:6]:
+        d, c = small_kinect.render_depth_aligned_rgb(p)
+        frames.append((u16(d), c.cpu().numpy(), p))
+    mk = lambda c, d: o3d.geometry.RGBDImage.create_from_color_and_depth(o3d.geometry.Image(c), o3d.geometry.Image(d), 1000.0, 3.0, True)
+    J = o3d.pipelines.odometry.RGBDOdometryJacobianFromHybridTerm()
+    opt = o3d.pipelines.odometry.OdometryOption(iteration_number_per_pyramid_level=o3d.utility.IntVector([20, 10, 5]), max_depth_diff=0.03,
+                                                min_depth=0.0, max_depth=4.0)
+    n = len(frames)
+    pg = Rg.PoseGraph()
+    pg.nodes.append(Rg.PoseGraphNode(frames[0][2]))                          # anchored on the true first pose
+    pose = frames[0][2].copy()
+    for i in range(1, n):
+        ok, T, info = o3d.pipelines.odometry.compute_rgbd_odometry(mk(frames[i][1], frames[i][0]), mk(frames[i - 1][1], frames[i - 1][0]), K, I4, J, opt)
+        assert ok
+        pose = pose @ T                                                    # T maps frame i into frame i-1
+        pg.nodes.append(Rg.PoseGraphNode(pose))
+        pg.edges.append(Rg.PoseGraphEdge(i - 1, i, np.linalg.inv(T), info, uncertain=False))
+    # loop closure: the true relative pose (a perfect re-localisation), weighted like the last odometry edge, uncertain
+    pg.edges.append(Rg.PoseGraphEdge(0, n - 1, np.linalg.inv(frames[n - 1][2]) @ frames[0][2], info, uncertain=True))
+    drift = max(np.abs(nd.pose - f[2]).max() for nd, f in zip(pg.nodes, frames))
+    Rg.global_optimization(pg, Rg.GlobalOptimizationLevenbergMarquardt(), Rg.GlobalOptimizationConvergenceCriteria(),
+                           Rg.GlobalOptimizationOption(max_correspondence_distance=0.02, edge_prune_threshold=0.25, preference_loop_closure=1.0, reference_node=0))
+    assert pg.last_report["valid"] and len(pg.edges) in (n - 1, n)           # the line process may prune the closure (coarse small-grid odometry)
+    assert pg.last_report["residual_after"] <= pg.last_report["residual_before"]
+    err = max(np.abs(nd.pose - f[2]).max() for nd, f in zip(pg.nodes, frames))
+    assert err < 2e-2 and err <= drift + 1e-6                                # never worse than the chained odometry
+    depth = torch.from_numpy(np.stack([f[0] for f in frames]).view(np.int16)).view(torch.uint16).cuda()
+    rgb = torch.from_numpy(np.stack([f[1] for f in frames])).cuda()
+    TT = o3d.pipelines.integration.TSDFVolumeColorType
+    vol = o3d.pipelines.integration.ScalableTSDFVolume(0.01, 0.04, TT.RGB8, capacity_units=4096)
+    vol.integrate_raw(depth, rgb, K, np.stack([np.linalg.inv(f[2]) for f in frames]))    # the pre-optimisation volume is discarded
+    o3d.pipelines.integration.reintegrate_frames(vol, depth, rgb, pg, K)
+    one = o3d.pipelines.integration.ScalableTSDFVolume(0.01, 0.04, TT.RGB8, capacity_units=4096)
+    one.set_batch(1)
+    for i in range(n):
+        img = o3d.geometry.RGBDImage.create_from_color_and_depth(o3d.geometry.Image(frames[i][1]), o3d.geometry.Image(frames[i][0]), 1000.0, 3.0, False)
+        one.integrate(img, K, np.linalg.inv(pg.nodes[i].pose))
+    ka, ta, wa, ca = vol.export_units()
+    kb, tb, wb, cb = one.export_units()
+    oa, ob = np.lexsort(ka.cpu().numpy().T[::-1]), np.lexsort(kb.cpu().numpy().T[::-1])
+    assert np.array_equal(ka.cpu().numpy()[oa], kb.cpu().numpy()[ob]) and len(oa) > 50
+    ia, ib = torch.as_tensor(oa, device="cuda"), torch.as_tensor(ob, device="cuda")
+    assert torch.equal(ta[ia], tb[ib]) and torch.equal(wa[ia], wb[ib]) and torch.equal(ca[ia], cb[ib])

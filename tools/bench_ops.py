@@ -194,6 +194,46 @@ def main():
                                          "estimate_normals_hybrid_r0.1_nn30_ms": ms_nrm, "estimate_normals_hybrid_r0.02_nn30_ms": ms_nrm2,
                                          "orient_normals_ms": ms_ori, "timing": "wall clock around the public call incl. index build and result allocation"}
 
+    # ---- f3: pose graph from the odometry results above + a closure -> global_optimization (host LM) -> re-integration
+    Rg = o3d.pipelines.registration
+    pg = Rg.PoseGraph()
+    pg.nodes.append(Rg.PoseGraphNode(poses[0]))
+    cur = poses[0].copy()
+    for i, (ok, T_, info_) in enumerate(res):
+        cur = cur @ T_
+        pg.nodes.append(Rg.PoseGraphNode(cur))
+        pg.edges.append(Rg.PoseGraphEdge(i, i + 1, np.linalg.inv(T_), info_, uncertain=False))
+    nn = len(pg.nodes)
+    pg.edges.append(Rg.PoseGraphEdge(0, nn - 1, np.linalg.inv(poses[nn - 1]) @ poses[0], res[0][2], uncertain=True))
+    t0 = time.perf_counter()
+    Rg.global_optimization(pg, Rg.GlobalOptimizationLevenbergMarquardt(), Rg.GlobalOptimizationConvergenceCriteria(),
+                           Rg.GlobalOptimizationOption(max_correspondence_distance=0.02, edge_prune_threshold=0.25, preference_loop_closure=1.0, reference_node=0))
+    t_go = time.perf_counter() - t0
+    vol3 = o3d.pipelines.integration.ScalableTSDFVolume(0.004, 0.02, o3d.pipelines.integration.TSDFVolumeColorType.RGB8)
+    o3d.pipelines.integration.reintegrate_frames(vol3, dd[:nn], cc[:nn], pg, Kd); torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    o3d.pipelines.integration.reintegrate_frames(vol3, dd[:nn], cc[:nn], pg, Kd); vol3.flush(); torch.cuda.synchronize()
+    t_re = time.perf_counter() - t0
+    # a long synthetic chain for the solver alone: 2000 nodes, closures every 100
+    rngp = np.random.default_rng(0)
+    big = Rg.PoseGraph(); traj = syn.orbit_trajectory(2000); cur = traj[0].copy(); big.nodes.append(Rg.PoseGraphNode(cur))
+    I6 = np.identity(6) * 2000.0
+    for i in range(1, 2000):
+        v = np.concatenate([rngp.normal(0, 5e-4, 3), rngp.normal(0, 5e-4, 3)])
+        dT = np.identity(4); dT[:3, 3] = v[3:]; dT[0, 1], dT[1, 0], dT[0, 2], dT[2, 0], dT[1, 2], dT[2, 1] = -v[2], v[2], v[1], -v[1], -v[0], v[0]
+        T_ = np.linalg.inv(traj[i]) @ traj[i - 1] @ dT
+        cur = cur @ np.linalg.inv(T_); big.nodes.append(Rg.PoseGraphNode(cur)); big.edges.append(Rg.PoseGraphEdge(i - 1, i, T_, I6, False))
+    for i in range(0, 1800, 100):
+        big.edges.append(Rg.PoseGraphEdge(i, i + 150, np.linalg.inv(traj[i + 150]) @ traj[i], I6, True))
+    t0 = time.perf_counter()
+    Rg.global_optimization(big, Rg.GlobalOptimizationLevenbergMarquardt(), Rg.GlobalOptimizationConvergenceCriteria(),
+                           Rg.GlobalOptimizationOption(max_correspondence_distance=0.05, edge_prune_threshold=0.25, preference_loop_closure=2.0, reference_node=0))
+    t_big = time.perf_counter() - t0
+    out["posegraph_f3"] = {"nodes": nn, "edges": len(pg.edges), "global_optimization_ms": 1e3 * t_go, "report": pg.last_report,
+                           "reintegrate_frames": nn, "reintegrate_ms": 1e3 * t_re, "reintegrate_frames_per_s": nn / t_re,
+                           "chain_2000_nodes_18_closures_ms": 1e3 * t_big, "chain_2000_report": big.last_report,
+                           "note": "solver = host block-envelope LM inside libb2recon.so; re-integration = reset + batched K1/K2 on the GPU"}
+
     if a.cpu:   # bounded CPU-oracle samples (reported baseline only)
         from oracle import o3r
         Kt = (di["fx"], di["fy"], di["cx"], di["cy"])
