@@ -195,6 +195,12 @@ struct IcpArgs {
     IcpState* st;
     int max_iter;
     double rel_fitness, rel_rmse;
+    // TransformationEstimationForColoredICP (f4): two residual rows per correspondence
+    int colored;
+    const double* src_int;       // N: (r + g + b) / 3 of the source colours
+    const double* tgt_int;       // M
+    const double* tgt_grad;      // M*3: colour gradient on the target's tangent planes
+    double sqrt_lg, sqrt_lp;     // sqrt(lambda_geometric), sqrt(1 - lambda_geometric)
 };
 
 __global__ void __launch_bounds__(ICP_THREADS) icp_iter_kernel(const IcpArgs a) {
@@ -246,9 +252,36 @@ __global__ void __launch_bounds__(ICP_THREADS) icp_iter_kernel(const IcpArgs a) 
         if (best >= 0) {
             const double* t = a.tgt + 3 * best;
             const double* n = a.nrm + 3 * best;
-            const double r = xdadd(xdadd(xdmul(xdsub(s[0], t[0]), n[0]), xdmul(xdsub(s[1], t[1]), n[1])), xdmul(xdsub(s[2], t[2]), n[2]));
-            const double J[6] = {xdsub(xdmul(s[1], n[2]), xdmul(s[2], n[1])), xdsub(xdmul(s[2], n[0]), xdmul(s[0], n[2])),
-                                 xdsub(xdmul(s[0], n[1]), xdmul(s[1], n[0])), n[0], n[1], n[2]};
+            double r = xdadd(xdadd(xdmul(xdsub(s[0], t[0]), n[0]), xdmul(xdsub(s[1], t[1]), n[1])), xdmul(xdsub(s[2], t[2]), n[2]));
+            double J[6] = {xdsub(xdmul(s[1], n[2]), xdmul(s[2], n[1])), xdsub(xdmul(s[2], n[0]), xdmul(s[0], n[2])),
+                           xdsub(xdmul(s[0], n[1]), xdmul(s[1], n[0])), n[0], n[1], n[2]};
+            if (a.colored) {
+                // photometric row: the source point projected into the target's tangent plane, intensity predicted by the
+                // target's colour gradient there; d(is0_proj)/d(vs) = dit^T (I - n n^T)
+                const double dn = r;                                        // (vs - vt) . nt
+                const double* dit = a.tgt_grad + 3 * best;
+                double proj[3], ditM[3];
+#pragma unroll
+                for (int q = 0; q < 3; q++) proj[q] = xdsub(xdsub(s[q], xdmul(dn, n[q])), t[q]);   // vs_proj - vt
+                const double is0 = xdadd(xdadd(xdadd(xdmul(dit[0], proj[0]), xdmul(dit[1], proj[1])), xdmul(dit[2], proj[2])), a.tgt_int[best]);
+                const double dd = xdadd(xdadd(xdmul(dit[0], n[0]), xdmul(dit[1], n[1])), xdmul(dit[2], n[2]));
+#pragma unroll
+                for (int q = 0; q < 3; q++) ditM[q] = xdmul(a.sqrt_lp, xdsub(xdmul(dd, n[q]), dit[q]));   // sqrt(lp) * (-dit^T M)
+                const double r1 = xdmul(a.sqrt_lp, xdsub(a.src_int[i], is0));
+                const double J1[6] = {xdsub(xdmul(s[1], ditM[2]), xdmul(s[2], ditM[1])), xdsub(xdmul(s[2], ditM[0]), xdmul(s[0], ditM[2])),
+                                      xdsub(xdmul(s[0], ditM[1]), xdmul(s[1], ditM[0])), ditM[0], ditM[1], ditM[2]};
+                int k1 = 0;
+#pragma unroll
+                for (int p = 0; p < 6; p++)
+#pragma unroll
+                    for (int q = p; q < 6; q++) { acc[k1] = xdadd(acc[k1], xdmul(J1[p], J1[q])); k1++; }
+#pragma unroll
+                for (int p = 0; p < 6; p++) acc[21 + p] = xdadd(acc[21 + p], xdmul(J1[p], r1));
+                acc[27] = xdadd(acc[27], xdmul(r1, r1));
+                r = xdmul(a.sqrt_lg, r);
+#pragma unroll
+                for (int p = 0; p < 6; p++) J[p] = xdmul(a.sqrt_lg, J[p]);
+            }
             int k = 0;
 #pragma unroll
             for (int p = 0; p < 6; p++)
@@ -358,13 +391,14 @@ inline size_t al(size_t v) { return (v + 255) & ~(size_t)255; }
 
 }  // namespace
 
-// registration_icp with TransformationEstimationPointToPlane.  See include/b2recon.h.
-B2R_API int b2r_icp_point_to_plane(const double* src_xyz, int64_t N, const double* tgt_xyz, const double* tgt_nrm, int64_t M,
-                                   double max_dist, const double* init_host, int max_iter, double rel_fitness,
-                                   double rel_rmse, double* out_T_host, double* fitness_host, double* rmse_host,
-                                   int32_t* corr, cudaStream_t stream) {
+struct IcpColor { const double* src_int; const double* tgt_int; const double* tgt_grad; double lambda_geometric; };
+
+static int icp_run(const double* src_xyz, int64_t N, const double* tgt_xyz, const double* tgt_nrm, int64_t M,
+                   double max_dist, const double* init_host, int max_iter, double rel_fitness,
+                   double rel_rmse, double* out_T_host, double* fitness_host, double* rmse_host,
+                   int32_t* corr, const IcpColor* color, cudaStream_t stream) {
     if (!(max_dist > 0.0)) { b2r_set_error("[RegistrationICP] Invalid max_correspondence_distance."); return B2R_ERR_BAD_ARG; }
-    if (!tgt_nrm) { b2r_set_error("[RegistrationICP] TransformationEstimationPointToPlane requires target normals."); return B2R_ERR_FORMAT; }
+    if (!tgt_nrm) { b2r_set_error(color ? "ColoredICP requires target pointcloud to have normals." : "[RegistrationICP] TransformationEstimationPointToPlane requires target normals."); return B2R_ERR_FORMAT; }
     if (!src_xyz || !tgt_xyz || !init_host || !out_T_host || !fitness_host || !rmse_host || N < 0 || M < 0 || max_iter < 0 ||
         N > 0x7fffffff || M > 0x7fffffff) {
         b2r_set_error("b2r_icp_point_to_plane: bad argument");
@@ -429,6 +463,9 @@ B2R_API int b2r_icp_point_to_plane(const double* src_xyz, int64_t N, const doubl
     a.pcd = (double*)(b + o_pcd); a.N = N; a.tgt = tgt_xyz; a.nrm = tgt_nrm; a.sorted_idx = iout; a.cell_start = cs; a.cell_end = ce;
     a.g = g; a.max_dist = max_dist; a.corr = (int32_t*)(b + o_corr); a.partials = (double*)(b + o_part); a.st = st;
     a.max_iter = max_iter; a.rel_fitness = rel_fitness; a.rel_rmse = rel_rmse;
+    a.colored = color ? 1 : 0;
+    a.src_int = color ? color->src_int : nullptr; a.tgt_int = color ? color->tgt_int : nullptr; a.tgt_grad = color ? color->tgt_grad : nullptr;
+    a.sqrt_lg = color ? sqrt(color->lambda_geometric) : 1.0; a.sqrt_lp = color ? sqrt(1.0 - color->lambda_geometric) : 0.0;
     for (int k = 0; k <= max_iter; k++) {
         icp_iter_kernel<<<grid, ICP_THREADS, 0, stream>>>(a);
         if ((k & 15) == 15) {     // cheap early exit: look at the done flag every 16 launches
@@ -445,4 +482,130 @@ B2R_API int b2r_icp_point_to_plane(const double* src_xyz, int64_t N, const doubl
     *fitness_host = h1.fitness;
     *rmse_host = h1.rmse;
     return h1.iters;
+}
+
+
+// registration_icp with TransformationEstimationPointToPlane.  See include/b2recon.h.
+B2R_API int b2r_icp_point_to_plane(const double* src_xyz, int64_t N, const double* tgt_xyz, const double* tgt_nrm, int64_t M,
+                                   double max_dist, const double* init_host, int max_iter, double rel_fitness,
+                                   double rel_rmse, double* out_T_host, double* fitness_host, double* rmse_host,
+                                   int32_t* corr, cudaStream_t stream) {
+    return icp_run(src_xyz, N, tgt_xyz, tgt_nrm, M, max_dist, init_host, max_iter, rel_fitness, rel_rmse, out_T_host, fitness_host,
+                   rmse_host, corr, nullptr, stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// f4: registration_colored_icp (GoodColorReconstruction.py:246-254; Park et al. 2017 as in Open3D's ColoredICP.cpp)
+// ------------------------------------------------------------------------------------------------
+struct b2r_knn;
+extern "C" b2r_knn* b2r_knn_create(const double* xyz, int64_t n, double cell, int k_hint, cudaStream_t stream);
+extern "C" void b2r_knn_destroy(b2r_knn* h);
+extern "C" int b2r_knn_search(const b2r_knn* h, const double* query, int64_t nq, int k, double radius, int32_t* idx, double* d2,
+                              int32_t* counts, cudaStream_t stream);
+
+namespace {
+
+__global__ void intensity_kernel(const double* __restrict__ rgb, long long n, double* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = xddiv(xdadd(xdadd(rgb[3 * i], rgb[3 * i + 1]), rgb[3 * i + 2]), 3.0);
+}
+
+// InitializePointCloudForColoredICP: least-squares colour gradient on the tangent plane of every target point from its
+// hybrid-search neighbours (itself first), plus the row (nn-1) * n^T g = 0; normal equations accumulated in row order,
+// solved by an unpivoted LDL^T (zero gradient when fewer than 4 neighbours or a pivot is not positive).
+__global__ void color_gradient_kernel(const double* __restrict__ xyz, const double* __restrict__ nrm, const double* __restrict__ inten,
+                                      const int32_t* __restrict__ nbr, const int32_t* __restrict__ counts, int k, long long M,
+                                      double* __restrict__ grad) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= M) return;
+    double g[3] = {0.0, 0.0, 0.0};
+    const int nn = counts[i];
+    if (nn >= 4) {
+        const double vt[3] = {xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]}, nt[3] = {nrm[3 * i], nrm[3 * i + 1], nrm[3 * i + 2]};
+        const double it = inten[i];
+        double S[6] = {0, 0, 0, 0, 0, 0}, rhs[3] = {0, 0, 0};   // xx xy xz yy yz zz
+        for (int q = 1; q < nn; q++) {
+            const int j = nbr[i * (long long)k + q];
+            const double d[3] = {xdsub(xyz[3 * j], vt[0]), xdsub(xyz[3 * j + 1], vt[1]), xdsub(xyz[3 * j + 2], vt[2])};
+            const double dn = xdadd(xdadd(xdmul(d[0], nt[0]), xdmul(d[1], nt[1])), xdmul(d[2], nt[2]));
+            double a[3];
+#pragma unroll
+            for (int c = 0; c < 3; c++) a[c] = xdsub(xdsub(xyz[3 * j + c], xdmul(dn, nt[c])), vt[c]);   // vt_proj - vt
+            const double b = xdsub(inten[j], it);
+            S[0] = xdadd(S[0], xdmul(a[0], a[0])); S[1] = xdadd(S[1], xdmul(a[0], a[1])); S[2] = xdadd(S[2], xdmul(a[0], a[2]));
+            S[3] = xdadd(S[3], xdmul(a[1], a[1])); S[4] = xdadd(S[4], xdmul(a[1], a[2])); S[5] = xdadd(S[5], xdmul(a[2], a[2]));
+#pragma unroll
+            for (int c = 0; c < 3; c++) rhs[c] = xdadd(rhs[c], xdmul(a[c], b));
+        }
+        const double w = (double)(nn - 1);
+        const double a[3] = {xdmul(w, nt[0]), xdmul(w, nt[1]), xdmul(w, nt[2])};
+        S[0] = xdadd(S[0], xdmul(a[0], a[0])); S[1] = xdadd(S[1], xdmul(a[0], a[1])); S[2] = xdadd(S[2], xdmul(a[0], a[2]));
+        S[3] = xdadd(S[3], xdmul(a[1], a[1])); S[4] = xdadd(S[4], xdmul(a[1], a[2])); S[5] = xdadd(S[5], xdmul(a[2], a[2]));
+        // LDL^T of [[S0 S1 S2][S1 S3 S4][S2 S4 S5]]
+        const double d0 = S[0];
+        if (d0 > 0.0) {
+            const double l10 = xddiv(S[1], d0), l20 = xddiv(S[2], d0);
+            const double d1 = xdsub(S[3], xdmul(l10, S[1]));
+            if (d1 > 0.0) {
+                const double l21 = xddiv(xdsub(S[4], xdmul(l20, S[1])), d1);
+                const double d2 = xdsub(xdsub(S[5], xdmul(l20, S[2])), xdmul(xdmul(l21, l21), d1));
+                if (d2 > 0.0) {
+                    const double y0 = rhs[0], y1 = xdsub(rhs[1], xdmul(l10, y0)), y2 = xdsub(xdsub(rhs[2], xdmul(l20, y0)), xdmul(l21, y1));
+                    const double z2 = xddiv(y2, d2), z1 = xdsub(xddiv(y1, d1), xdmul(l21, z2));
+                    const double z0 = xdsub(xdsub(xddiv(y0, d0), xdmul(l10, z1)), xdmul(l20, z2));
+                    g[0] = z0; g[1] = z1; g[2] = z2;
+                }
+            }
+        }
+    }
+    grad[3 * i] = g[0]; grad[3 * i + 1] = g[1]; grad[3 * i + 2] = g[2];
+}
+
+}  // namespace
+
+// registration_colored_icp(source, target, max_dist, init, TransformationEstimationForColoredICP(lambda_geometric), criteria).
+// DEVICE f64 arrays; rgb in [0, 1] as PointCloud.colors holds them.  grad_out (optional, device [M][3]) receives the
+// target's colour gradients (parity hook).  Returns the iteration count.
+B2R_API int b2r_icp_colored(const double* src_xyz, const double* src_rgb, int64_t N, const double* tgt_xyz, const double* tgt_nrm,
+                            const double* tgt_rgb, int64_t M, double max_dist, double lambda_geometric, const double* init_host,
+                            int max_iter, double rel_fitness, double rel_rmse, double* out_T_host, double* fitness_host,
+                            double* rmse_host, int32_t* corr, double* grad_out, cudaStream_t stream) {
+    if (!tgt_nrm) { b2r_set_error("ColoredICP requires target pointcloud to have normals."); return B2R_ERR_FORMAT; }
+    if (!tgt_rgb) { b2r_set_error("ColoredICP requires target pointcloud to have colors."); return B2R_ERR_FORMAT; }
+    if (!src_rgb) { b2r_set_error("ColoredICP requires source pointcloud to have colors."); return B2R_ERR_FORMAT; }
+    if (!(lambda_geometric >= 0.0 && lambda_geometric <= 1.0)) { b2r_set_error("TransformationEstimationForColoredICP::lambda_geometric needs to be in range [0, 1]."); return B2R_ERR_BAD_ARG; }
+    if (!(max_dist > 0.0)) { b2r_set_error("[RegistrationICP] Invalid max_correspondence_distance."); return B2R_ERR_BAD_ARG; }
+    if (!src_xyz || !tgt_xyz || N < 0 || M < 0 || N > 0x7fffffff || M > 0x7fffffff) { b2r_set_error("b2r_icp_colored: bad argument"); return B2R_ERR_BAD_ARG; }
+    if (N == 0 || M == 0)
+        return icp_run(src_xyz, N, tgt_xyz, tgt_nrm, M, max_dist, init_host, max_iter, rel_fitness, rel_rmse, out_T_host, fitness_host, rmse_host, corr, nullptr, stream);
+    const int K = 30;                                       // KDTreeSearchParamHybrid(max_dist * 2, 30)
+    double *sint = nullptr, *tint = nullptr, *grad = nullptr;
+    int32_t *nbr = nullptr, *cnt = nullptr;
+    cudaError_t e = cudaMallocAsync((void**)&sint, (size_t)N * 8, stream);
+    if (e == cudaSuccess) e = cudaMallocAsync((void**)&tint, (size_t)M * 8, stream);
+    if (e == cudaSuccess) e = cudaMallocAsync((void**)&grad, (size_t)M * 24, stream);
+    if (e == cudaSuccess) e = cudaMallocAsync((void**)&nbr, (size_t)M * K * 4, stream);
+    if (e == cudaSuccess) e = cudaMallocAsync((void**)&cnt, (size_t)M * 4, stream);
+    int rc = B2R_OK;
+    if (e != cudaSuccess) { b2r_set_error("b2r_icp_colored: %s", cudaGetErrorString(e)); rc = B2R_ERR_CUDA; }
+    b2r_knn* tree = nullptr;
+    if (rc == B2R_OK) {
+        tree = b2r_knn_create(tgt_xyz, M, max_dist * 2.0, K, stream);
+        if (!tree) rc = B2R_ERR_CUDA;
+    }
+    if (rc == B2R_OK) rc = b2r_knn_search(tree, nullptr, M, K, max_dist * 2.0, nbr, nullptr, cnt, stream);
+    if (rc == B2R_OK) {
+        intensity_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>(src_rgb, (long long)N, sint);
+        intensity_kernel<<<(unsigned)((M + 255) / 256), 256, 0, stream>>>(tgt_rgb, (long long)M, tint);
+        color_gradient_kernel<<<(unsigned)((M + 127) / 128), 128, 0, stream>>>(tgt_xyz, tgt_nrm, tint, nbr, cnt, K, (long long)M, grad);
+        if (cudaGetLastError() != cudaSuccess) { b2r_set_error("b2r_icp_colored: launch failed"); rc = B2R_ERR_CUDA; }
+        if (rc == B2R_OK && grad_out && cudaMemcpyAsync(grad_out, grad, (size_t)M * 24, cudaMemcpyDeviceToDevice, stream) != cudaSuccess) rc = B2R_ERR_CUDA;
+    }
+    if (rc == B2R_OK) {
+        const IcpColor col = {sint, tint, grad, lambda_geometric};
+        rc = icp_run(src_xyz, N, tgt_xyz, tgt_nrm, M, max_dist, init_host, max_iter, rel_fitness, rel_rmse, out_T_host, fitness_host, rmse_host, corr, &col, stream);
+    }
+    if (tree) b2r_knn_destroy(tree);
+    cudaFreeAsync(sint, stream); cudaFreeAsync(tint, stream); cudaFreeAsync(grad, stream); cudaFreeAsync(nbr, stream); cudaFreeAsync(cnt, stream);
+    return rc;
 }

@@ -190,6 +190,16 @@ int b2r_icp_point_to_plane(const double* src_xyz, int64_t N, const double* tgt_x
                            double rel_rmse, double* out_T_host, double* fitness_host, double* rmse_host,
                            int32_t* corr, cudaStream_t stream);
 
+/* ---- f4 (part): o3d.pipelines.registration.registration_colored_icp(src, tgt, max_dist, init,
+ *      TransformationEstimationForColoredICP(), ICPConvergenceCriteria(...))  (GoodColorReconstruction.py:246-254).
+ *      DEVICE f64 arrays, colours in [0, 1]; the target's colour gradients (SearchHybrid(2 * max_dist, 30) neighbours) are
+ *      computed inside; grad_out optional device [M][3].  Missing normals / colours: B2R_ERR_FORMAT with upstream's text.
+ *      Returns the iteration count. */
+int b2r_icp_colored(const double* src_xyz, const double* src_rgb, int64_t N, const double* tgt_xyz, const double* tgt_nrm,
+                    const double* tgt_rgb, int64_t M, double max_dist, double lambda_geometric, const double* init_host,
+                    int max_iter, double rel_fitness, double rel_rmse, double* out_T_host, double* fitness_host,
+                    double* rmse_host, int32_t* corr, double* grad_out, cudaStream_t stream);
+
 /* ---- f1: point-cloud conditioning on either side of ICP.  All arrays DEVICE f64 [n][3] unless noted.
  *      Reference: pcd.remove_statistical_outlier(20, 2.0) / voxel_down_sample(v) / estimate_normals(Hybrid(r, max_nn)) /
  *      orient_normals_towards_camera_location -- GoodColorReconstruction.py:141-153,

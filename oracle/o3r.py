@@ -59,6 +59,8 @@ def lib():
     L.o3r_correspondence.restype = _i64
     L.o3r_correspondence.argtypes = [_vp, _vp, _i, _i, _d, _d, _d, _d, _vp, _d, _vp, _i64]
     L.o3r_icp_point_to_plane.argtypes = [_vp, _i64, _vp, _vp, _i64, _d, _vp, _i, _d, _d, _vp, C.POINTER(C.c_double), C.POINTER(C.c_double), _vp]
+    L.o3r_icp_colored.argtypes = [_vp, _vp, _i64, _vp, _vp, _vp, _i64, _d, _d, _vp, _i, _d, _d, _vp, C.POINTER(C.c_double), C.POINTER(C.c_double), _vp, _vp]
+    L.o3r_color_gradient.argtypes = [_vp, _vp, _vp, _i64, _d, _i, _vp]
     L.o3r_pcd_search.argtypes = [_vp, _i64, _vp, _i64, _i, _d, _vp, _vp, _vp]
     L.o3r_pcd_estimate_normals.argtypes = [_vp, _i64, _i, _d, _vp, _i, _vp]
     L.o3r_pcd_orient_normals.argtypes = [_vp, _i64, _vp, _vp]
@@ -260,6 +262,24 @@ def icp_point_to_plane(src, tgt, tgt_nrm, max_dist, init=None, max_iter=30, rel_
     if it < 0:
         raise RuntimeError("[RegistrationICP] invalid arguments (%d)" % it)
     return T, float(fit.value), float(rmse.value), corr, int(it)
+
+
+def icp_colored(src, src_rgb, tgt, tgt_nrm, tgt_rgb, max_dist, lambda_geometric=0.968, init=None, max_iter=30, rel_fitness=1e-6, rel_rmse=1e-6):
+    """registration_colored_icp. Returns (T, fitness, inlier_rmse, corr, iterations, target colour gradients)."""
+    s, t = _f64(src), _f64(tgt)
+    sc = _f64(src_rgb) if src_rgb is not None else None
+    tc = _f64(tgt_rgb) if tgt_rgb is not None else None
+    n = _f64(tgt_nrm) if tgt_nrm is not None else None
+    init = _f64(np.eye(4) if init is None else init)
+    T = np.empty((4, 4))
+    fit, rmse = C.c_double(0), C.c_double(0)
+    corr = np.empty((s.shape[0],), np.int32)
+    grad = np.empty((t.shape[0], 3))
+    it = lib().o3r_icp_colored(_p(s), _p(sc), s.shape[0], _p(t), _p(n), _p(tc), t.shape[0], max_dist, lambda_geometric, _p(init), max_iter,
+                               rel_fitness, rel_rmse, _p(T), C.byref(fit), C.byref(rmse), _p(corr), _p(grad))
+    if it < 0:
+        raise RuntimeError("[RegistrationColoredICP] invalid arguments (%d)" % it)
+    return T, float(fit.value), float(rmse.value), corr, int(it), grad
 
 
 def m4_inverse(m):

@@ -1198,6 +1198,124 @@ O3R_API int o3r_icp_point_to_plane(const double* src_xyz, int64_t N, const doubl
     return it;
 }
 
+// ---- f4: registration_colored_icp (GoodColorReconstruction.py:246-254) ------------------------------------------------
+// Open3D 0.19 pipelines/registration/ColoredICP.cpp: InitializePointCloudForColoredICP (colour gradient per target point from
+// its SearchHybrid(2 * max_dist, 30) neighbours, least squares on the tangent plane + orthogonality row) and
+// TransformationEstimationForColoredICP::ComputeTransformation (geometric row scaled sqrt(lambda), photometric row scaled
+// sqrt(1 - lambda)), inside the same RegistrationICP loop as point-to-plane.  The 3x3 normal equations are solved by an
+// unpivoted LDL^T (upstream: Eigen LDLT); a non-positive pivot or fewer than 4 neighbours leaves the gradient at zero.
+extern "C" void o3r_pcd_search(const double* pts, int64_t n, const double* q, int64_t nq, int k, double radius, int32_t* idx,
+                               double* d2, int32_t* counts);
+
+O3R_API void o3r_color_gradient(const double* xyz, const double* nrm, const double* rgb, int64_t M, double radius, int max_nn,
+                                double* grad) {
+    std::vector<int32_t> idx((size_t)M * max_nn), cnt((size_t)M);
+    o3r_pcd_search(xyz, M, xyz, M, max_nn, radius, idx.data(), nullptr, cnt.data());
+    for (int64_t k = 0; k < M; k++) {
+        double* g = grad + 3 * k;
+        g[0] = g[1] = g[2] = 0.0;
+        const int nn = cnt[k];
+        if (nn < 4) continue;
+        const double* vt = xyz + 3 * k;
+        const double* nt = nrm + 3 * k;
+        const double it = (rgb[3 * k] + rgb[3 * k + 1] + rgb[3 * k + 2]) / 3.0;
+        double AtA[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}}, Atb[3] = {0, 0, 0};
+        for (int i = 1; i <= nn; i++) {
+            double row[3], rhs;
+            if (i < nn) {
+                const int j = idx[(size_t)k * max_nn + i];
+                const double* va = xyz + 3 * j;
+                const double dn = (va[0] - vt[0]) * nt[0] + (va[1] - vt[1]) * nt[1] + (va[2] - vt[2]) * nt[2];
+                for (int c = 0; c < 3; c++) row[c] = (va[c] - dn * nt[c]) - vt[c];
+                rhs = (rgb[3 * j] + rgb[3 * j + 1] + rgb[3 * j + 2]) / 3.0 - it;
+            } else {
+                for (int c = 0; c < 3; c++) row[c] = (double)(nn - 1) * nt[c];
+                rhs = 0.0;
+            }
+            for (int a = 0; a < 3; a++) {
+                for (int b = 0; b < 3; b++) AtA[a][b] += row[a] * row[b];
+                Atb[a] += row[a] * rhs;
+            }
+        }
+        const double d0 = AtA[0][0];
+        if (!(d0 > 0.0)) continue;
+        const double l10 = AtA[1][0] / d0, l20 = AtA[2][0] / d0;
+        const double d1 = AtA[1][1] - l10 * AtA[1][0];
+        if (!(d1 > 0.0)) continue;
+        const double l21 = (AtA[2][1] - l20 * AtA[1][0]) / d1;
+        const double d2 = AtA[2][2] - l20 * AtA[2][0] - l21 * l21 * d1;
+        if (!(d2 > 0.0)) continue;
+        const double y0 = Atb[0], y1 = Atb[1] - l10 * y0, y2 = Atb[2] - l20 * y0 - l21 * y1;
+        const double z2 = y2 / d2, z1 = y1 / d1 - l21 * z2, z0 = y0 / d0 - l10 * z1 - l20 * z2;
+        g[0] = z0; g[1] = z1; g[2] = z2;
+    }
+}
+
+// Returns the iterations executed, or < 0 on the upstream LogError conditions (-1: max_dist <= 0, -2: no target normals,
+// -3: no target colours, -4: no source colours, -5: lambda outside [0, 1]).  grad_out optional [M][3].
+O3R_API int o3r_icp_colored(const double* src_xyz, const double* src_rgb, int64_t N, const double* tgt_xyz, const double* tgt_nrm,
+                            const double* tgt_rgb, int64_t M, double max_dist, double lambda_geometric, const double* init,
+                            int max_iter, double rel_fitness, double rel_rmse, double* out_T, double* out_fitness,
+                            double* out_rmse, int32_t* corr_out, double* grad_out) {
+    if (max_dist <= 0.0) return -1;
+    if (!tgt_nrm) return -2;
+    if (!tgt_rgb) return -3;
+    if (!src_rgb) return -4;
+    if (!(lambda_geometric >= 0.0 && lambda_geometric <= 1.0)) return -5;
+    std::vector<double> grad((size_t)3 * M);
+    o3r_color_gradient(tgt_xyz, tgt_nrm, tgt_rgb, M, max_dist * 2.0, 30, grad.data());
+    if (grad_out) std::memcpy(grad_out, grad.data(), sizeof(double) * 3 * M);
+    const double slg = std::sqrt(lambda_geometric), slp = std::sqrt(1.0 - lambda_geometric);
+    M4 T;
+    std::memcpy(T.m, init, sizeof(T.m));
+    std::vector<double> pcd(src_xyz, src_xyz + 3 * N);
+    o3r_transform_points(pcd.data(), N, T.m, nullptr);
+    Grid g;
+    g.build(tgt_xyz, M, max_dist);
+    std::vector<int32_t> corr;
+    IcpEval res = icp_evaluate(pcd, g, max_dist, corr);
+    int it = 0;
+    for (; it < max_iter; it++) {
+        M4 U = m4_identity();
+        if (res.n > 0) {
+            NormalEq ne;
+            ne.zero();
+            for (int64_t i = 0; i < N; i++) {
+                const int j = corr[i];
+                if (j < 0) continue;
+                const double* vs = &pcd[3 * i];
+                const double* vt = tgt_xyz + 3 * j;
+                const double* nt = tgt_nrm + 3 * j;
+                const double* dit = &grad[3 * (size_t)j];
+                const double dn = (vs[0] - vt[0]) * nt[0] + (vs[1] - vt[1]) * nt[1] + (vs[2] - vt[2]) * nt[2];
+                const double Jg[6] = {slg * (vs[1] * nt[2] - vs[2] * nt[1]), slg * (vs[2] * nt[0] - vs[0] * nt[2]), slg * (vs[0] * nt[1] - vs[1] * nt[0]),
+                                      slg * nt[0], slg * nt[1], slg * nt[2]};
+                ne.add_row(Jg, slg * dn);
+                double proj[3];
+                for (int c = 0; c < 3; c++) proj[c] = (vs[c] - dn * nt[c]) - vt[c];
+                const double is = (src_rgb[3 * i] + src_rgb[3 * i + 1] + src_rgb[3 * i + 2]) / 3.0;
+                const double itg = (tgt_rgb[3 * j] + tgt_rgb[3 * j + 1] + tgt_rgb[3 * j + 2]) / 3.0;
+                const double is0 = dit[0] * proj[0] + dit[1] * proj[1] + dit[2] * proj[2] + itg;
+                const double dd = dit[0] * nt[0] + dit[1] * nt[1] + dit[2] * nt[2];
+                const double m[3] = {slp * (dd * nt[0] - dit[0]), slp * (dd * nt[1] - dit[1]), slp * (dd * nt[2] - dit[2])};   // -dit^T (I - n n^T)
+                const double Jp[6] = {vs[1] * m[2] - vs[2] * m[1], vs[2] * m[0] - vs[0] * m[2], vs[0] * m[1] - vs[1] * m[0], m[0], m[1], m[2]};
+                ne.add_row(Jp, slp * (is - is0));
+            }
+            if (!solve_update(ne, &U)) U = m4_identity();
+        }
+        T = m4_mul(U, T);
+        o3r_transform_points(pcd.data(), N, U.m, nullptr);
+        IcpEval prev = res;
+        res = icp_evaluate(pcd, g, max_dist, corr);
+        if (std::fabs(prev.fitness - res.fitness) < rel_fitness && std::fabs(prev.rmse - res.rmse) < rel_rmse) { it++; break; }
+    }
+    std::memcpy(out_T, T.m, sizeof(T.m));
+    *out_fitness = res.fitness;
+    *out_rmse = res.rmse;
+    if (corr_out) std::memcpy(corr_out, corr.data(), sizeof(int32_t) * N);
+    return it;
+}
+
 // helpers exposed for tests
 O3R_API int o3r_m4_inverse(const double* in, double* out) {
     M4 a, b;

@@ -640,3 +640,47 @@ def test_posegraph_loop_odometry_optimise_reintegrate(frames, small_kinect):
     assert np.array_equal(ka.cpu().numpy()[oa], kb.cpu().numpy()[ob]) and len(oa) > 50
     ia, ib = torch.as_tensor(oa, device="cuda"), torch.as_tensor(ob, device="cuda")
     assert torch.equal(ta[ia], tb[ib]) and torch.equal(wa[ia], wb[ib]) and torch.equal(ca[ia], cb[ib])
+
+
+def test_colored_icp_parity(o3r, frames, small_kinect):
+    """f4 (part): registration_colored_icp through the C-ABI vs the CPU restatement -- colour gradients of the target,
+    correspondences (bit-exact nearest neighbours), pose <= 1e-6 rad / 1e-6 m; upstream's argument errors."""
+    intr = small_kinect.depth_intr
+    (ds, cs, ps), (dt, ct, pt) = frames[1], frames[0]
+    Kt = K_of(intr)
+    src, scol, _ = o3r.unproject(o3r.depth_to_float(ds), Kt, rgb=cs, stride=2)
+    tgt, tcol, _ = o3r.unproject(o3r.depth_to_float(dt), Kt, rgb=ct, stride=2)
+    nrm = image_normals(o3r.depth_to_float(dt), Kt, stride=2)
+    init = np.linalg.inv(pt) @ ps
+    init[:3, 3] += [0.003, -0.002, 0.002]
+    Rg = o3d.pipelines.registration
+    s, t = o3d.geometry.PointCloud(src), o3d.geometry.PointCloud(tgt)
+    s.colors, t.colors = o3d.utility.Vector3dVector(scol), o3d.utility.Vector3dVector(tcol)
+    t.normals = o3d.utility.Vector3dVector(nrm)
+    crit = Rg.ICPConvergenceCriteria(relative_fitness=1e-6, relative_rmse=1e-6, max_iteration=40)
+    for lam in (0.968, 0.5):
+        res = Rg.registration_colored_icp(s, t, 0.03, init, Rg.TransformationEstimationForColoredICP(lambda_geometric=lam), crit)
+        T_r, fit_r, rmse_r, corr_r, it_r, grad_r = o3r.icp_colored(src, scol, tgt, nrm, tcol, 0.03, lam, init, max_iter=40)
+        g = res.color_gradient.cpu().numpy()
+        assert np.abs(g - grad_r).max() <= 1e-9 * max(1.0, np.abs(grad_r).max())
+        assert np.abs(grad_r).max() > 1.0                                    # the synthetic checker texture has real gradients
+        assert res.num_iterations == it_r
+        assert np.abs(res.transformation[:3, 3] - T_r[:3, 3]).max() <= 1e-6
+        assert rot_angle(res.transformation[:3, :3] @ T_r[:3, :3].T) <= 1e-6
+        assert abs(res.fitness - fit_r) <= 1e-9 and abs(res.inlier_rmse - rmse_r) <= 1e-9
+        cs_ = np.asarray(res.correspondence_set)
+        assert np.array_equal(cs_, np.stack([np.flatnonzero(corr_r >= 0), corr_r[corr_r >= 0]], 1))
+    # the default estimation is lambda 0.968; the result differs from plain point-to-plane (the photometric rows matter)
+    plane = Rg.registration_icp(s, t, 0.03, init, Rg.TransformationEstimationPointToPlane(), crit)
+    col = Rg.registration_colored_icp(s, t, 0.03, init, criteria=crit)
+    assert np.abs(plane.transformation - col.transformation).max() > 1e-7
+    bare = o3d.geometry.PointCloud(tgt)
+    with pytest.raises(RuntimeError, match="normals"):
+        Rg.registration_colored_icp(s, bare, 0.03, init)
+    bare.normals = o3d.utility.Vector3dVector(nrm)
+    with pytest.raises(RuntimeError, match="target pointcloud to have colors"):
+        Rg.registration_colored_icp(s, bare, 0.03, init)
+    with pytest.raises(RuntimeError, match="source pointcloud to have colors"):
+        Rg.registration_colored_icp(o3d.geometry.PointCloud(src), t, 0.03, init)
+    with pytest.raises(RuntimeError, match="lambda_geometric"):
+        Rg.registration_colored_icp(s, t, 0.03, init, Rg.TransformationEstimationForColoredICP(lambda_geometric=1.2))

@@ -335,3 +335,40 @@ def test_icp_recovers_inverse_motion(o3r):
     # nothing within reach: identity update, fitness 0
     T0, fit0, rmse0, _, _ = o3r.icp_point_to_plane(src + 100.0, tgt, nrm, 0.05, max_iter=5)
     assert fit0 == 0.0 and rmse0 == 0.0 and np.array_equal(T0, np.eye(4))
+
+
+def test_colored_icp_gradient_is_analytic_and_colour_locks_the_in_plane_slide(o3r):
+    """f4 (registration_colored_icp): on a plane carrying a linear intensity the tangent-plane gradient is the analytic one;
+    a slide WITHIN the plane is invisible to point-to-plane ICP (zero residual) and recovered by the photometric term."""
+    g = np.arange(-30, 31) * 0.01
+    X, Y = np.meshgrid(g, g, indexing="ij")
+    rng = np.random.default_rng(0)
+    tgt = np.stack([X.ravel() + rng.normal(0, 1e-4, X.size), Y.ravel() + rng.normal(0, 1e-4, X.size), np.full(X.size, 2.0)], 1)
+    nrm = np.tile([0.0, 0.0, 1.0], (len(tgt), 1))
+    inside = (np.abs(tgt[:, 0]) < 0.25) & (np.abs(tgt[:, 1]) < 0.25)
+    # (1) linear intensity: exact gradient (max_iter = 0 only builds the gradients and evaluates)
+    a, b = 0.8, -0.5
+    lin = np.repeat((0.5 + a * tgt[:, 0] + b * tgt[:, 1])[:, None], 3, 1)
+    _, fit0, _, _, it0, grad = o3r.icp_colored(tgt[inside], lin[inside], tgt, nrm, lin, 0.02, max_iter=0)
+    assert it0 == 0 and fit0 == 1.0
+    np.testing.assert_allclose(grad[inside], np.tile([a, b, 0.0], (inside.sum(), 1)), atol=1e-9)
+    # (2) an intensity that varies in both directions makes both in-plane translations observable
+    inten = lambda p: 0.5 + 0.25 * np.sin(9.0 * p[:, 0]) + 0.25 * np.cos(7.0 * p[:, 1] + 0.3)
+    tcol = np.repeat(inten(tgt)[:, None], 3, 1)
+    shift = np.array([0.004, -0.003, 0.0])
+    inner = (np.abs(tgt[:, 0]) < 0.2) & (np.abs(tgt[:, 1]) < 0.2)
+    src = tgt[inner] + rng.normal(0, 2e-4, (inner.sum(), 3)) * [1, 1, 0]
+    scol = np.repeat(inten(src)[:, None], 3, 1)                              # the colour the surface has where the source point IS
+    src_shifted = src - shift                                               # expressed in a frame displaced by +shift
+    T, fit, rmse, corr, it, grad = o3r.icp_colored(src_shifted, scol, tgt, nrm, tcol, 0.02, max_iter=50)
+    assert fit == 1.0 and 1 <= it <= 50
+    np.testing.assert_allclose(T[:3, 3], shift, atol=3e-4)                   # finite-difference gradients over a 4 cm neighbourhood
+    np.testing.assert_allclose(T[:3, :3], np.eye(3), atol=2e-3)
+    Tp, *_ = o3r.icp_point_to_plane(src_shifted, tgt, nrm, 0.02, max_iter=50)
+    assert np.abs(Tp[:2, 3]).max() < 1e-9                                    # geometry alone cannot see the slide
+    for bad in (dict(tgt_nrm=None), dict(tgt_rgb=None), dict(src_rgb=None)):
+        kw = dict(src_rgb=scol, tgt_nrm=nrm, tgt_rgb=tcol); kw.update(bad)
+        with pytest.raises(RuntimeError):
+            o3r.icp_colored(src_shifted, kw["src_rgb"], tgt, kw["tgt_nrm"], kw["tgt_rgb"], 0.02)
+    with pytest.raises(RuntimeError):
+        o3r.icp_colored(src_shifted, scol, tgt, nrm, tcol, 0.02, lambda_geometric=1.5)

@@ -172,6 +172,22 @@ def main():
     out["icp_point_to_plane"] = {"source_points": len(p_src.points), "target_points": len(p_tgt.points), "iterations": int(r_icp.num_iterations), "ms": 1e3 * t_icp,
                                  "fitness": float(r_icp.fitness), "inlier_rmse": float(r_icp.inlier_rmse)}
 
+    # ---- f4 (part): registration_colored_icp between consecutive frames (GoodColorReconstruction.py:246-254)
+    def colored_cloud(i):
+        r_ = o3d.geometry.RGBDImage.create_from_color_and_depth(o3d.geometry.Image(cc[i]), o3d.geometry.Image(dd[i]), 1000.0, 3.0, False)
+        return o3d.geometry.PointCloud.create_from_rgbd_image(r_, Kd).voxel_down_sample(0.02)
+    c_src, c_tgt = colored_cloud(1), colored_cloud(0)
+    c_tgt.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(radius=0.04, max_nn=30))
+    c_tgt.orient_normals_towards_camera_location(np.array([0.0, 0.0, 0.0]))
+    cicp = lambda: o3d.pipelines.registration.registration_colored_icp(c_src, c_tgt, 0.03, np.eye(4), o3d.pipelines.registration.TransformationEstimationForColoredICP(),
+                                                                       o3d.pipelines.registration.ICPConvergenceCriteria(relative_fitness=1e-6, relative_rmse=1e-6, max_iteration=100))
+    r_c = cicp(); torch.cuda.synchronize()
+    t0 = time.perf_counter(); r_c = cicp(); torch.cuda.synchronize(); t_c = time.perf_counter() - t0
+    gt01 = np.linalg.inv(poses[0]) @ poses[1]
+    out["colored_icp_f4"] = {"source_points": len(c_src.points), "target_points": len(c_tgt.points), "iterations": int(r_c.num_iterations), "ms": 1e3 * t_c,
+                             "fitness": float(r_c.fitness), "inlier_rmse": float(r_c.inlier_rmse),
+                             "translation_error_m_vs_ground_truth": float(np.linalg.norm(r_c.transformation[:3, 3] - gt01[:3, 3]))}
+
     # ---- f1: per-frame conditioning chain of the reference (GoodColorReconstruction.py:141-153) on one full NFOV frame
     rgbd0 = o3d.geometry.RGBDImage.create_from_color_and_depth(o3d.geometry.Image(cc[0]), o3d.geometry.Image(dd[0]), 1000.0, 3.0, False)
     full = o3d.geometry.PointCloud.create_from_rgbd_image(rgbd0, Kd)
