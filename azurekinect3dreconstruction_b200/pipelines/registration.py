@@ -141,6 +141,46 @@ def registration_colored_icp(source: PointCloud, target: PointCloud, max_corresp
     return res
 
 
+class Feature:
+    """o3d.pipelines.registration.Feature: ``data`` is (dimension, num) like upstream; the device tensor behind it is
+    point-major (num, dimension) -- ``tensor`` (build extension)."""
+
+    def __init__(self, tensor: torch.Tensor = None):
+        self.tensor = tensor if tensor is not None else torch.zeros((0, 33), dtype=torch.float64)
+
+    @property
+    def data(self) -> np.ndarray:
+        return self.tensor.detach().cpu().numpy().T
+
+    def dimension(self) -> int:
+        return int(self.tensor.shape[1])
+
+    def num(self) -> int:
+        return int(self.tensor.shape[0])
+
+    def __repr__(self):
+        return "Feature class with dimension = %d and num = %d\nAccess its data via data member." % (self.dimension(), self.num())
+
+
+def compute_fpfh_feature(input: PointCloud, search_param) -> Feature:
+    """o3d.pipelines.registration.compute_fpfh_feature (BetterVisualizer2CamWorksCOLOR.py:211-214)."""
+    from ..geometry import KDTreeSearchParamHybrid, KDTreeSearchParamKNN
+    if not input.has_normals():
+        raise RuntimeError("[ComputeFPFHFeature] Failed because input point cloud has no normal.")
+    if isinstance(search_param, KDTreeSearchParamHybrid):
+        k, radius = int(search_param.max_nn), float(search_param.radius)
+    elif isinstance(search_param, KDTreeSearchParamKNN):
+        k, radius = int(search_param.knn), 0.0
+    else:
+        raise RuntimeError("compute_fpfh_feature: KDTreeSearchParamHybrid or KDTreeSearchParamKNN expected")
+    dev = _lib.require_cuda()
+    n = len(input.points)
+    out = torch.empty((n, 33), dtype=torch.float64, device=dev)
+    rc = _lib.load().b2r_compute_fpfh(_lib.ptr(input.points.tensor), _lib.ptr(input.normals.tensor), n, k, radius, _lib.ptr(out), _lib.stream_ptr())
+    _lib.check(rc, "compute_fpfh_feature")
+    return Feature(out)
+
+
 # ---------------------------------------------------------------------------------------------------------------
 # f3: PoseGraph + global optimisation (SURVEY 8(f)).  Reference call sites: capture_frames.py:31-32,74-89,164-166;
 # bundlefusion_reconstruction.py:179-199,232-273,292-304.  Field names and defaults follow Open3D 0.19

@@ -200,6 +200,12 @@ int b2r_icp_colored(const double* src_xyz, const double* src_rgb, int64_t N, con
                     int max_iter, double rel_fitness, double rel_rmse, double* out_T_host, double* fitness_host,
                     double* rmse_host, int32_t* corr, double* grad_out, cudaStream_t stream);
 
+/* ---- f4: o3d.pipelines.registration.compute_fpfh_feature(pcd, KDTreeSearchParamHybrid(radius, max_nn))
+ *      (BetterVisualizer2CamWorksCOLOR.py:211-214).  DEVICE f64; out [n][33] point-major (Feature.data transposed).
+ *      radius <= 0: KDTreeSearchParamKNN(max_nn).  No normals: B2R_ERR_FORMAT with upstream's text. */
+int b2r_compute_fpfh(const double* xyz, const double* normals, int64_t n, int max_nn, double radius, double* out,
+                     cudaStream_t stream);
+
 /* ---- f1: point-cloud conditioning on either side of ICP.  All arrays DEVICE f64 [n][3] unless noted.
  *      Reference: pcd.remove_statistical_outlier(20, 2.0) / voxel_down_sample(v) / estimate_normals(Hybrid(r, max_nn)) /
  *      orient_normals_towards_camera_location -- GoodColorReconstruction.py:141-153,

@@ -66,6 +66,7 @@ def lib():
     L.o3r_pcd_orient_normals.argtypes = [_vp, _i64, _vp, _vp]
     L.o3r_pcd_statistical_outlier.restype = _i64
     L.o3r_pcd_statistical_outlier.argtypes = [_vp, _i64, _i, _d, _vp, _vp]
+    L.o3r_compute_fpfh.argtypes = [_vp, _vp, _i64, _i, _d, _vp]
     L.o3r_pcd_voxel_down_sample.restype = _i64
     L.o3r_pcd_voxel_down_sample.argtypes = [_vp, _vp, _vp, _i64, _d, _vp, _vp, _vp, _vp]
     L.o3r_m4_inverse.argtypes = [_vp, _vp]
@@ -351,3 +352,14 @@ def pcd_voxel_down_sample(pts, voxel, colors=None, normals=None):
     ok = np.empty((n, 3), np.int32)
     m = lib().o3r_pcd_voxel_down_sample(_p(p), _p(c), _p(nr), n, float(voxel), _p(op), _p(oc), _p(on), _p(ok))
     return op[:m].copy(), (oc[:m].copy() if oc is not None else None), (on[:m].copy() if on is not None else None), ok[:m].copy()
+
+
+def compute_fpfh(pts, normals, max_nn=100, radius=0.0):
+    """compute_fpfh_feature: (n, 33) f64, point-major (upstream's Feature.data is the transpose)."""
+    p = _f64(pts)
+    if normals is None:
+        raise RuntimeError("[ComputeFPFHFeature] Failed because input point cloud has no normal.")
+    nr = _f64(normals)
+    out = np.empty((p.shape[0], 33))
+    lib().o3r_compute_fpfh(_p(p), _p(nr), p.shape[0], int(max_nn), float(radius), _p(out))
+    return out

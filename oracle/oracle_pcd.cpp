@@ -276,3 +276,82 @@ O3R_API int64_t o3r_pcd_voxel_down_sample(const double* pts, const double* col, 
     }
     return m;
 }
+
+// ---- f4: compute_fpfh_feature (BetterVisualizer2CamWorksCOLOR.py:211-214) ------------------------------------------------
+// Open3D 0.19 pipelines/registration/Feature.cpp: ComputePairFeatures / ComputeSPFHFeature / ComputeFPFHFeature, with PCL's
+// weighting (sum of neighbour SPFHs divided by squared distance, normalised to 100 per angle, plus the point's own SPFH).
+// One deviation, stated here and mirrored by the CUDA kernel: upstream picks the frame origin with
+// acos(|a1|) > acos(|a2|); acos is strictly decreasing, so this restates it as |a1| < |a2| (no libm call on the decision).
+namespace {
+void pair_features(const double* p1, const double* n1, const double* p2, const double* n2, double f[3]) {
+    f[0] = f[1] = f[2] = 0.0;
+    double dp[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
+    const double d = std::sqrt(dp[0] * dp[0] + dp[1] * dp[1] + dp[2] * dp[2]);
+    if (d == 0.0) return;
+    const double a1 = (n1[0] * dp[0] + n1[1] * dp[1] + n1[2] * dp[2]) / d;
+    const double a2 = (n2[0] * dp[0] + n2[1] * dp[1] + n2[2] * dp[2]) / d;
+    const double* na = n1;
+    const double* nb = n2;
+    double phi = a1;
+    if (std::fabs(a1) < std::fabs(a2)) {
+        na = n2; nb = n1;
+        for (int c = 0; c < 3; c++) dp[c] = -dp[c];
+        phi = -a2;
+    }
+    V3 v = cross(V3{dp[0], dp[1], dp[2]}, V3{na[0], na[1], na[2]});
+    const double vn = std::sqrt(v.x * v.x + v.y * v.y + v.z * v.z);
+    if (vn == 0.0) return;
+    v = {v.x / vn, v.y / vn, v.z / vn};
+    const V3 w = cross(V3{na[0], na[1], na[2]}, v);
+    f[2] = phi;
+    f[1] = v.x * nb[0] + v.y * nb[1] + v.z * nb[2];
+    f[0] = std::atan2(w.x * nb[0] + w.y * nb[1] + w.z * nb[2], na[0] * nb[0] + na[1] * nb[1] + na[2] * nb[2]);
+}
+inline int clamp_bin(double x) {
+    int h = (int)std::floor(x);
+    return h < 0 ? 0 : (h >= 11 ? 10 : h);
+}
+}  // namespace
+
+// out [n][33] point-major.  radius <= 0: KNN(max_nn); else Hybrid(radius, max_nn).  Returns -1 without normals.
+O3R_API int o3r_compute_fpfh(const double* pts, const double* nrm, int64_t n, int max_nn, double radius, double* out) {
+    if (!nrm) return -1;
+    const double PI = 3.14159265358979323846;
+    std::vector<double> spfh((size_t)n * 33, 0.0);
+    std::vector<std::vector<Nb>> nbs((size_t)n);
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t i = 0; i < n; i++) {
+        search(pts, n, pts + 3 * i, max_nn, radius, nbs[i]);
+        const std::vector<Nb>& nb = nbs[i];
+        if (nb.size() > 1) {
+            const double inc = 100.0 / (double)(nb.size() - 1);
+            for (size_t k = 1; k < nb.size(); k++) {
+                double f[3];
+                pair_features(pts + 3 * i, nrm + 3 * i, pts + 3 * (int64_t)nb[k].i, nrm + 3 * (int64_t)nb[k].i, f);
+                spfh[i * 33 + clamp_bin(11 * (f[0] + PI) / (2.0 * PI))] += inc;
+                spfh[i * 33 + 11 + clamp_bin(11 * (f[1] + 1.0) * 0.5)] += inc;
+                spfh[i * 33 + 22 + clamp_bin(11 * (f[2] + 1.0) * 0.5)] += inc;
+            }
+        }
+    }
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t i = 0; i < n; i++) {
+        double* o = out + i * 33;
+        for (int j = 0; j < 33; j++) o[j] = 0.0;
+        const std::vector<Nb>& nb = nbs[i];
+        if (nb.size() <= 1) continue;
+        double sum[3] = {0.0, 0.0, 0.0};
+        for (size_t k = 1; k < nb.size(); k++) {
+            const double dist = nb[k].d2;
+            if (dist == 0.0) continue;
+            for (int j = 0; j < 33; j++) {
+                const double val = spfh[(size_t)nb[k].i * 33 + j] / dist;
+                sum[j / 11] += val;
+                o[j] += val;
+            }
+        }
+        for (int j = 0; j < 3; j++) if (sum[j] != 0.0) sum[j] = 100.0 / sum[j];
+        for (int j = 0; j < 33; j++) { o[j] *= sum[j / 11]; o[j] += spfh[i * 33 + j]; }
+    }
+    return 0;
+}

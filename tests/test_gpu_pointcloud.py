@@ -193,3 +193,27 @@ def test_preprocess_then_icp_like_the_reference(o3r, small_kinect):
     assert res.fitness > 0.8
     assert np.linalg.norm(res.transformation[:3, 3] - gt[:3, 3]) < 5e-3
     assert np.abs(res.transformation[:3, :3] - gt[:3, :3]).max() < 5e-3
+
+
+def test_fpfh_parity(o3r, cloud):
+    """f4: compute_fpfh_feature on the down-sampled cloud of preprocess_point_cloud (BetterVisualizer2CamWorksCOLOR.py:197-216).
+    Same neighbour order and the same f64 summation order as the oracle: identical histograms except where glibc's and
+    CUDA's atan2 differ in the last bit exactly on a bin edge (none expected; a handful tolerated)."""
+    down = cloud.voxel_down_sample(0.03)
+    down.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(radius=0.06, max_nn=30))
+    xyz, nrm = np.asarray(down.points), np.asarray(down.normals)
+    assert len(xyz) > 2000
+    for param, kw in ((o3d.geometry.KDTreeSearchParamHybrid(radius=0.15, max_nn=100), dict(max_nn=100, radius=0.15)),
+                      (o3d.geometry.KDTreeSearchParamKNN(knn=25), dict(max_nn=25, radius=0.0))):
+        feat = o3d.pipelines.registration.compute_fpfh_feature(down, param)
+        assert feat.dimension() == 33 and feat.num() == len(xyz) and feat.data.shape == (33, len(xyz))
+        got = feat.tensor.cpu().numpy()
+        want = o3r.compute_fpfh(xyz, nrm, **kw)
+        rows_off = (np.abs(got - want).max(1) > 1e-9).sum()
+        assert rows_off <= max(2, len(xyz) // 2000), rows_off
+        ok = np.abs(got - want).max(1) <= 1e-9
+        assert np.array_equal(got[ok], want[ok])                             # where no bin flipped: bit-identical f64
+        np.testing.assert_allclose(got.reshape(-1, 3, 11).sum(2)[got.sum(1) > 0], 200.0, atol=1e-8)
+    bare = o3d.geometry.PointCloud(xyz)
+    with pytest.raises(RuntimeError, match="no normal"):
+        o3d.pipelines.registration.compute_fpfh_feature(bare, o3d.geometry.KDTreeSearchParamHybrid(radius=0.15, max_nn=100))

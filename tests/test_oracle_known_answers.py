@@ -372,3 +372,35 @@ def test_colored_icp_gradient_is_analytic_and_colour_locks_the_in_plane_slide(o3
             o3r.icp_colored(src_shifted, kw["src_rgb"], tgt, kw["tgt_nrm"], kw["tgt_rgb"], 0.02)
     with pytest.raises(RuntimeError):
         o3r.icp_colored(src_shifted, scol, tgt, nrm, tcol, 0.02, lambda_geometric=1.5)
+
+
+def test_fpfh_oracle_known_answers(o3r):
+    """f4 (compute_fpfh_feature): each of the three 11-bin blocks sums to 200 (100 from the weighted neighbour SPFHs + 100 from
+    the point's own SPFH) wherever a point has neighbours; on a PLANE with parallel normals every pair has alpha = phi = 0 and
+    theta = 0, so all mass sits in the middle bin of each block; the descriptor is invariant under rigid motion."""
+    rng = np.random.default_rng(1)
+    g = np.arange(-10, 11) * 0.01
+    X, Y = np.meshgrid(g, g, indexing="ij")
+    plane = np.stack([X.ravel(), Y.ravel(), np.zeros(X.size)], 1) + rng.normal(0, 1e-5, (X.size, 3)) * [1, 1, 0]
+    nrm = np.tile([0.0, 0.0, 1.0], (len(plane), 1))
+    f = o3r.compute_fpfh(plane, nrm, max_nn=30, radius=0.035)
+    assert f.shape == (len(plane), 33)
+    np.testing.assert_allclose(f.reshape(-1, 3, 11).sum(2), 200.0, atol=1e-9)
+    assert np.all(f[:, 5] > 199.999) and np.all(f[:, 16] > 199.999) and np.all(f[:, 27] > 199.999)
+    # a curved, bumpy surface: sums still 200, and rigid motion leaves the descriptor unchanged up to rounding
+    u, v = rng.random(1500) * 0.4 - 0.2, rng.random(1500) * 0.4 - 0.2
+    z = 0.05 * np.sin(12 * u) * np.cos(9 * v)
+    pts = np.stack([u, v, z], 1)
+    nz = np.stack([-0.6 * np.cos(12 * u) * np.cos(9 * v), 0.45 * np.sin(12 * u) * np.sin(9 * v), np.ones_like(u)], 1)
+    nn = nz / np.linalg.norm(nz, axis=1, keepdims=True)
+    f1 = o3r.compute_fpfh(pts, nn, max_nn=50, radius=0.05)
+    has = f1.sum(1) > 0
+    assert has.mean() > 0.99
+    np.testing.assert_allclose(f1[has].reshape(-1, 3, 11).sum(2), 200.0, atol=1e-8)
+    assert (f1[has] > 0).sum(1).mean() > 4.5                                 # spread over more bins than the plane (exactly 3)
+    from azurekinect3dreconstruction_b200 import synthetic as syn
+    M = syn.make_pose(syn.rot_z(0.7) @ syn.rot_x(-0.4), (0.3, -0.2, 1.1))
+    f2 = o3r.compute_fpfh(o3r.transform_points(pts, M), nn @ M[:3, :3].T, max_nn=50, radius=0.05)
+    assert np.abs(f1 - f2).max() < 25.0 and np.median(np.abs(f1 - f2)) < 1e-9  # only bin-edge flips / distance ties may move mass
+    with pytest.raises(RuntimeError):
+        o3r.compute_fpfh(pts, None)
