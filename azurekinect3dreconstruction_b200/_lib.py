@@ -76,6 +76,9 @@ SIGNATURES = {
     "b2r_pcd_bounds": (_i, [_vp, _i64, _pd, _vp]),
     "b2r_icp_colored": (_i, [_vp, _vp, _i64, _vp, _vp, _vp, _i64, _d, _d, _pd, _i, _d, _d, _pd, _pd, _pd, _vp, _vp, _vp]),
     "b2r_compute_fpfh": (_i, [_vp, _vp, _i64, _i, _d, _vp, _vp]),
+    "b2r_match_features": (_i, [_vp, _i64, _vp, _i64, _i, _vp, _vp]),
+    "b2r_ransac_correspondence": (_i, [_vp, _i64, _vp, _i64, _vp, _i64, _d, _i, _d, _d, _i64, _d, C.c_uint64, _pd, _pd, _pd, _pi64, _vp, _vp]),
+    "b2r_knn_evaluate_transforms": (_i, [_vp, _vp, _i64, _vp, _i64, _d, _vp, _vp, _vp]),
     "b2r_posegraph_optimize": (_i, [_i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b2r_icp_point_to_plane": (_i, [_vp, _i64, _vp, _vp, _i64, _d, _pd, _i, _d, _d, _pd, _pd, _pd, _vp, _vp]),
 }

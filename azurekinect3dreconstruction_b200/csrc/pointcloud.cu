@@ -801,3 +801,48 @@ B2R_API int b2r_pcd_bounds(const double* xyz, int64_t n, double* out6_host, cuda
     pcd_free(mm, stream);
     return rc;
 }
+
+// ---- f4: GetRegistrationResultAndCorrespondences for H candidate transforms at once -----------------------------------------
+// (the "expensive validation" of registration_ransac_based_on_*: every source point transformed, nearest target within
+// max_dist).  One CTA per transform; counts and squared-distance sums reduced in a fixed tree (deterministic).
+namespace {
+__global__ void __launch_bounds__(256) eval_transforms_kernel(const GridView G, const double* __restrict__ src, int64_t N,
+                                                              const double* __restrict__ T, double radius, int64_t* __restrict__ out_count,
+                                                              double* __restrict__ out_sum) {
+    __shared__ double sT[16];
+    if (threadIdx.x < 16) sT[threadIdx.x] = T[(int64_t)blockIdx.x * 16 + threadIdx.x];
+    __syncthreads();
+    long long cnt = 0;
+    double sum = 0.0;
+    for (int64_t i = threadIdx.x; i < N; i += blockDim.x) {
+        const double x = src[3 * i], y = src[3 * i + 1], z = src[3 * i + 2];
+        double h[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) h[r] = xdadd(xdadd(xdadd(xdmul(sT[4 * r], x), xdmul(sT[4 * r + 1], y)), xdmul(sT[4 * r + 2], z)), sT[4 * r + 3]);
+        double bd[1]; int32_t bi[1];
+        if (knn_query<1>(G, xddiv(h[0], h[3]), xddiv(h[1], h[3]), xddiv(h[2], h[3]), 1, radius, bd, bi) > 0) { cnt++; sum = xdadd(sum, bd[0]); }
+    }
+    __shared__ long long s_c[8];
+    __shared__ double s_s[8];
+    for (int o = 16; o > 0; o >>= 1) { cnt += __shfl_down_sync(0xffffffffu, cnt, o); sum = xdadd(sum, __shfl_down_sync(0xffffffffu, sum, o)); }
+    if ((threadIdx.x & 31) == 0) { s_c[threadIdx.x >> 5] = cnt; s_s[threadIdx.x >> 5] = sum; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        long long c = 0; double s = 0.0;
+        for (int w = 0; w < 8; w++) { c += s_c[w]; s = xdadd(s, s_s[w]); }
+        out_count[blockIdx.x] = c; out_sum[blockIdx.x] = s;
+    }
+}
+}  // namespace
+
+// tree indexes the TARGET; src DEVICE [N][3]; T DEVICE [H][16] row-major.  count[h] = source points with a target point at
+// squared distance < max_dist^2 after T[h] (KDTreeFlann::SearchHybrid(point, max_dist, 1) as upstream calls it), sumd2[h] = the
+// sum of those squared distances: fitness = count / N, inlier_rmse = sqrt(sumd2 / count).
+B2R_API int b2r_knn_evaluate_transforms(const b2r_knn* h, const double* src_xyz, int64_t N, const double* T, int64_t H, double max_dist,
+                                        int64_t* count, double* sumd2, cudaStream_t stream) {
+    if (!h || !src_xyz || !T || !count || !sumd2 || N < 0 || H < 0 || !(max_dist > 0.0)) { b2r_set_error("b2r_knn_evaluate_transforms: bad argument"); return B2R_ERR_BAD_ARG; }
+    if (H == 0) return B2R_OK;
+    eval_transforms_kernel<<<(unsigned)H, 256, 0, stream>>>(view_of(h), src_xyz, N, T, max_dist, count, sumd2);
+    B2R_CHECK_LAUNCH();
+    return B2R_OK;
+}

@@ -181,6 +181,116 @@ def compute_fpfh_feature(input: PointCloud, search_param) -> Feature:
     return Feature(out)
 
 
+class CorrespondenceChecker:
+    pass
+
+
+class CorrespondenceCheckerBasedOnEdgeLength(CorrespondenceChecker):
+    def __init__(self, similarity_threshold: float = 0.9):
+        self.similarity_threshold = float(similarity_threshold)
+
+
+class CorrespondenceCheckerBasedOnDistance(CorrespondenceChecker):
+    def __init__(self, distance_threshold: float):
+        self.distance_threshold = float(distance_threshold)
+
+
+class CorrespondenceCheckerBasedOnNormal(CorrespondenceChecker):
+    def __init__(self, normal_angle_threshold: float):
+        self.normal_angle_threshold = float(normal_angle_threshold)
+
+
+class RANSACConvergenceCriteria:
+    """RANSACConvergenceCriteria(max_iteration=100000, confidence=0.999); confidence is clamped to [0, 1] as upstream does, so
+    the reference's pre-0.12 call ``RANSACConvergenceCriteria(4000000, 500)`` means "always run every iteration"."""
+
+    def __init__(self, max_iteration: int = 100000, confidence: float = 0.999):
+        self.max_iteration = int(max_iteration)
+        self.confidence = max(min(float(confidence), 1.0), 0.0)
+
+
+def _checker_thresholds(checkers):
+    edge = dist = 0.0
+    for c in checkers or []:
+        if isinstance(c, CorrespondenceCheckerBasedOnEdgeLength):
+            edge = c.similarity_threshold
+        elif isinstance(c, CorrespondenceCheckerBasedOnDistance):
+            dist = c.distance_threshold
+        else:
+            raise RuntimeError("registration_ransac: only the edge-length and distance checkers are built (the reference passes no other)")
+    return edge, dist
+
+
+def registration_ransac_based_on_correspondence(source: PointCloud, target: PointCloud, corres, max_correspondence_distance: float,
+                                                estimation_method: TransformationEstimation = None, ransac_n: int = 3, checkers=None,
+                                                criteria: RANSACConvergenceCriteria = None, *, seed: int = 0) -> RegistrationResult:
+    """o3d.pipelines.registration.registration_ransac_based_on_correspondence.  ``seed`` (build extension) selects the draw
+    sequence; the result is deterministic for a given seed."""
+    estimation_method = estimation_method or TransformationEstimationPointToPoint(False)
+    criteria = criteria or RANSACConvergenceCriteria()
+    if not isinstance(estimation_method, TransformationEstimationPointToPoint) or getattr(estimation_method, "with_scaling", False):
+        raise RuntimeError("registration_ransac: TransformationEstimationPointToPoint(False) is the estimation the reference uses and the one built")
+    edge, dist = _checker_thresholds(checkers)
+    dev = _lib.require_cuda()
+    c = corres.tensor if hasattr(corres, "tensor") else (corres if torch.is_tensor(corres) else torch.as_tensor(np.asarray(corres)))
+    c = c.to(device=dev, dtype=torch.int32).contiguous().reshape(-1, 2)
+    N, M = len(source.points), len(target.points)
+    T = (C.c_double * 16)()
+    fit, rmse = C.c_double(0), C.c_double(0)
+    rep = (C.c_int64 * 4)()
+    corr = torch.full((max(N, 1),), -1, dtype=torch.int32, device=dev)
+    res = RegistrationResult()
+    if N and M and c.shape[0]:
+        rc = _lib.load().b2r_ransac_correspondence(_lib.ptr(source.points.tensor), N, _lib.ptr(target.points.tensor), M, _lib.ptr(c), c.shape[0],
+                                                   float(max_correspondence_distance), int(ransac_n), edge, dist, criteria.max_iteration,
+                                                   criteria.confidence, int(seed) & 0xFFFFFFFFFFFFFFFF, T, C.byref(fit), C.byref(rmse), rep,
+                                                   _lib.ptr(corr), _lib.stream_ptr())
+        _lib.check(rc, "registration_ransac")
+        res.transformation = np.array(T[:], dtype=np.float64).reshape(4, 4)
+        res.fitness, res.inlier_rmse = float(fit.value), float(rmse.value)
+        if res.fitness > 0.0:
+            cc = corr[:N]
+            src_i = torch.nonzero(cc >= 0).flatten().to(torch.int32)
+            res.correspondence_set = Vector2iVector(torch.stack([src_i, cc[src_i.long()]], dim=1))
+    res.ransac_report = dict(iterations=int(rep[0]), validated=int(rep[1]), winning_iteration=int(rep[2]), inlier_correspondences=int(rep[3]))
+    return res
+
+
+def registration_ransac_based_on_feature_matching(source: PointCloud, target: PointCloud, source_feature: Feature, target_feature: Feature,
+                                                  mutual_filter=False, max_correspondence_distance: float = None,
+                                                  estimation_method: TransformationEstimation = None, ransac_n: int = 3, checkers=None,
+                                                  criteria: RANSACConvergenceCriteria = None, *, seed: int = 0) -> RegistrationResult:
+    """o3d.pipelines.registration.registration_ransac_based_on_feature_matching (BetterVisualizer2CamWorksCOLOR.py:230-243).
+    Accepts both upstream signatures: 0.19's (``mutual_filter`` fifth) and the older one the reference was written against
+    (``max_correspondence_distance`` fifth / by keyword, no mutual filter)."""
+    if not isinstance(mutual_filter, (bool, np.bool_)):
+        if max_correspondence_distance is None:
+            max_correspondence_distance = float(mutual_filter)
+        mutual_filter = False
+    if max_correspondence_distance is None:
+        raise TypeError("registration_ransac_based_on_feature_matching: max_correspondence_distance is required")
+    if ransac_n < 3 or max_correspondence_distance <= 0.0:
+        return RegistrationResult()
+    dev = _lib.require_cuda()
+    lib = _lib.load()
+    fs, ft = source_feature.tensor.contiguous(), target_feature.tensor.contiguous()
+    ns, nt = fs.shape[0], ft.shape[0]
+    if ns == 0 or nt == 0:
+        return RegistrationResult()
+    ij = torch.empty((ns,), dtype=torch.int32, device=dev)
+    _lib.check(lib.b2r_match_features(_lib.ptr(fs), ns, _lib.ptr(ft), nt, int(fs.shape[1]), _lib.ptr(ij), _lib.stream_ptr()), "feature matching")
+    corres = torch.stack([torch.arange(ns, dtype=torch.int32, device=dev), ij], dim=1)
+    if mutual_filter:
+        ji = torch.empty((nt,), dtype=torch.int32, device=dev)
+        _lib.check(lib.b2r_match_features(_lib.ptr(ft), nt, _lib.ptr(fs), ns, int(fs.shape[1]), _lib.ptr(ji), _lib.stream_ptr()), "feature matching")
+        keep = ji[ij.long()] == torch.arange(ns, dtype=torch.int32, device=dev)
+        mutual = corres[keep]
+        if mutual.shape[0] >= ransac_n * 3:               # "Empirically mutual correspondence set should not be too small"
+            corres = mutual
+    return registration_ransac_based_on_correspondence(source, target, corres.contiguous(), max_correspondence_distance, estimation_method,
+                                                       ransac_n, checkers, criteria, seed=seed)
+
+
 # ---------------------------------------------------------------------------------------------------------------
 # f3: PoseGraph + global optimisation (SURVEY 8(f)).  Reference call sites: capture_frames.py:31-32,74-89,164-166;
 # bundlefusion_reconstruction.py:179-199,232-273,292-304.  Field names and defaults follow Open3D 0.19

@@ -206,6 +206,27 @@ int b2r_icp_colored(const double* src_xyz, const double* src_rgb, int64_t N, con
 int b2r_compute_fpfh(const double* xyz, const double* normals, int64_t n, int max_nn, double radius, double* out,
                      cudaStream_t stream);
 
+/* corres_ij of registration_ransac_based_on_feature_matching: nearest target feature (squared L2, ties -> lower index) of
+ * every query feature.  DEVICE f64 point-major [n][dim], dim <= 40. */
+int b2r_match_features(const double* query_feat, int64_t nq, const double* target_feat, int64_t nt, int dim, int32_t* out_idx,
+                       cudaStream_t stream);
+/* registration_ransac_based_on_correspondence(source, target, corres, max_dist, TransformationEstimationPointToPoint(False),
+ * ransac_n, [CorrespondenceCheckerBasedOnEdgeLength(edge_thr), CorrespondenceCheckerBasedOnDistance(dist_thr)],
+ * RANSACConvergenceCriteria(max_iteration, confidence))  (BetterVisualizer2CamWorksCOLOR.py:230-243).
+ * DEVICE: src [N][3], tgt [M][3], corres int32 [C][2], corr_out (optional) int32 [N] = nearest target of every source point
+ * under the winner, -1 beyond max_dist.  edge_thr / dist_thr <= 0: checker absent.  Deterministic for a given seed
+ * (csrc/features.cu).  HOST outputs; report4 (optional) = {iterations consumed, hypotheses validated, winning iteration,
+ * its inlier-correspondence count}.  Nothing acceptable: identity, fitness 0 (upstream's empty RegistrationResult). */
+int b2r_ransac_correspondence(const double* src_xyz, int64_t N, const double* tgt_xyz, int64_t M, const int32_t* corres, int64_t C,
+                              double max_dist, int ransac_n, double edge_thr, double dist_thr, int64_t max_iteration,
+                              double confidence, uint64_t seed, double* out_T_host, double* fitness_host, double* rmse_host,
+                              int64_t* report4_host, int32_t* corr_out, cudaStream_t stream);
+typedef struct b2r_knn b2r_knn;   /* the exact-neighbour index of row f1, declared below */
+/* The validation step on its own: count[h] = source points with a target point (indexed by `h`) closer than max_dist after
+ * T[h] (DEVICE [H][16]), sumd2[h] = sum of those squared distances.  DEVICE outputs. */
+int b2r_knn_evaluate_transforms(const b2r_knn* h, const double* src_xyz, int64_t N, const double* T, int64_t H, double max_dist,
+                                int64_t* count, double* sumd2, cudaStream_t stream);
+
 /* ---- f1: point-cloud conditioning on either side of ICP.  All arrays DEVICE f64 [n][3] unless noted.
  *      Reference: pcd.remove_statistical_outlier(20, 2.0) / voxel_down_sample(v) / estimate_normals(Hybrid(r, max_nn)) /
  *      orient_normals_towards_camera_location -- GoodColorReconstruction.py:141-153,

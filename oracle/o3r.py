@@ -67,6 +67,9 @@ def lib():
     L.o3r_pcd_statistical_outlier.restype = _i64
     L.o3r_pcd_statistical_outlier.argtypes = [_vp, _i64, _i, _d, _vp, _vp]
     L.o3r_compute_fpfh.argtypes = [_vp, _vp, _i64, _i, _d, _vp]
+    L.o3r_horn_rigid.argtypes = [_vp, _vp, _i, _vp]
+    L.o3r_match_features.argtypes = [_vp, _i64, _vp, _i64, _i, _vp]
+    L.o3r_ransac_correspondence.argtypes = [_vp, _i64, _vp, _i64, _vp, _i64, _d, _i, _d, _d, _i64, _d, C.c_uint64, _vp, C.POINTER(C.c_double), C.POINTER(C.c_double), _vp]
     L.o3r_pcd_voxel_down_sample.restype = _i64
     L.o3r_pcd_voxel_down_sample.argtypes = [_vp, _vp, _vp, _i64, _d, _vp, _vp, _vp, _vp]
     L.o3r_m4_inverse.argtypes = [_vp, _vp]
@@ -363,3 +366,32 @@ def compute_fpfh(pts, normals, max_nn=100, radius=0.0):
     out = np.empty((p.shape[0], 33))
     lib().o3r_compute_fpfh(_p(p), _p(nr), p.shape[0], int(max_nn), float(radius), _p(out))
     return out
+
+
+def horn_rigid(s, t):
+    """Rigid transform (no scale) minimising sum |R s_i + t - t_i|^2 (Horn's closed form)."""
+    a, b = _f64(s), _f64(t)
+    T = np.empty((4, 4))
+    lib().o3r_horn_rigid(_p(a), _p(b), a.shape[0], _p(T))
+    return T
+
+
+def match_features(query, target):
+    q, t = _f64(query), _f64(target)
+    out = np.empty((q.shape[0],), np.int32)
+    lib().o3r_match_features(_p(q), q.shape[0], _p(t), t.shape[0], q.shape[1], _p(out))
+    return out
+
+
+def ransac_correspondence(src, tgt, corres, max_dist, ransac_n=3, edge_thr=0.0, dist_thr=0.0, max_iteration=100000, confidence=0.999, seed=0):
+    """Returns (T, fitness, inlier_rmse, report = (consumed, validated, winning iteration, its inlier correspondences))."""
+    s, t = _f64(src), _f64(tgt)
+    c = np.ascontiguousarray(corres, dtype=np.int32)
+    T = np.empty((4, 4))
+    fit, rmse = C.c_double(0), C.c_double(0)
+    rep = np.zeros(4, np.int64)
+    rc = lib().o3r_ransac_correspondence(_p(s), s.shape[0], _p(t), t.shape[0], _p(c), c.shape[0], max_dist, ransac_n, edge_thr, dist_thr,
+                                         max_iteration, confidence, seed, _p(T), C.byref(fit), C.byref(rmse), _p(rep))
+    if rc != 0:
+        raise RuntimeError("ransac_correspondence: bad argument")
+    return T, float(fit.value), float(rmse.value), tuple(int(v) for v in rep)

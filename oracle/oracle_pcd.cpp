@@ -355,3 +355,166 @@ O3R_API int o3r_compute_fpfh(const double* pts, const double* nrm, int64_t n, in
     }
     return 0;
 }
+
+// ---- f4: registration_ransac_based_on_feature_matching (BetterVisualizer2CamWorksCOLOR.py:230-243) ------------------------
+// Open3D 0.19 Registration.cpp: nearest-feature correspondences, then RegistrationRANSACBasedOnCorrespondence.  Upstream's draw
+// order depends on the OpenMP schedule and a per-thread mt19937, so the project fixes ONE deterministic algorithm with the same
+// distribution (stated in csrc/features.cu and restated here, sequentially): splitmix-style counter generator per (iteration,
+// draw), Horn's closed-form rigid fit (upstream: Eigen::umeyama -- same optimum), upstream's checkers, full validation by
+// nearest neighbour, upstream's IsBetterRANSACThan and confidence rule, survivors taken in iteration order.
+namespace {
+inline uint64_t splitmix(uint64_t x) {
+    x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ull;
+    x ^= x >> 27; x *= 0x94d049bb133111ebull;
+    x ^= x >> 31;
+    return x;
+}
+inline uint32_t draw(uint64_t seed, uint64_t itr, int j, uint32_t C) {
+    const uint64_t h = splitmix(seed + itr * 0x9E3779B97F4A7C15ull + (uint64_t)(j + 1) * 0xD1B54A32D192ED03ull);
+    return (uint32_t)(((h >> 32) * (uint64_t)C) >> 32);
+}
+// Horn 1987 (closed-form absolute orientation with unit quaternions); cyclic Jacobi on the symmetric 4x4
+void horn(const double (*s)[3], const double (*t)[3], int n, double* T) {
+    double ms[3] = {0, 0, 0}, mt[3] = {0, 0, 0};
+    for (int i = 0; i < n; i++) for (int c = 0; c < 3; c++) { ms[c] += s[i][c]; mt[c] += t[i][c]; }
+    for (int c = 0; c < 3; c++) { ms[c] /= (double)n; mt[c] /= (double)n; }
+    double S[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
+    for (int i = 0; i < n; i++) for (int a = 0; a < 3; a++) for (int b = 0; b < 3; b++) S[a][b] += (s[i][a] - ms[a]) * (t[i][b] - mt[b]);
+    double A[4][4], V[4][4];
+    A[0][0] = S[0][0] + S[1][1] + S[2][2];
+    A[1][1] = S[0][0] - S[1][1] - S[2][2];
+    A[2][2] = S[1][1] - S[0][0] - S[2][2];
+    A[3][3] = S[2][2] - S[0][0] - S[1][1];
+    A[0][1] = A[1][0] = S[1][2] - S[2][1];
+    A[0][2] = A[2][0] = S[2][0] - S[0][2];
+    A[0][3] = A[3][0] = S[0][1] - S[1][0];
+    A[1][2] = A[2][1] = S[0][1] + S[1][0];
+    A[1][3] = A[3][1] = S[2][0] + S[0][2];
+    A[2][3] = A[3][2] = S[1][2] + S[2][1];
+    for (int a = 0; a < 4; a++) for (int b = 0; b < 4; b++) V[a][b] = a == b ? 1.0 : 0.0;
+    for (int sweep = 0; sweep < 16; sweep++) {
+        double off = 0.0;
+        for (int p = 0; p < 3; p++) for (int q = p + 1; q < 4; q++) off += A[p][q] * A[p][q];
+        if (off == 0.0) break;
+        for (int p = 0; p < 3; p++)
+            for (int q = p + 1; q < 4; q++) {
+                const double apq = A[p][q];
+                if (apq == 0.0) continue;
+                const double theta = (A[q][q] - A[p][p]) / (2.0 * apq);
+                const double tt = (theta >= 0.0 ? 1.0 : -1.0) / (std::fabs(theta) + std::sqrt(theta * theta + 1.0));
+                const double c = 1.0 / std::sqrt(tt * tt + 1.0), sn = tt * c;
+                for (int k = 0; k < 4; k++) { const double x = A[k][p], y = A[k][q]; A[k][p] = c * x - sn * y; A[k][q] = sn * x + c * y; }
+                for (int k = 0; k < 4; k++) { const double x = A[p][k], y = A[q][k]; A[p][k] = c * x - sn * y; A[q][k] = sn * x + c * y; }
+                for (int k = 0; k < 4; k++) { const double x = V[k][p], y = V[k][q]; V[k][p] = c * x - sn * y; V[k][q] = sn * x + c * y; }
+            }
+    }
+    int best = 0;
+    for (int k = 1; k < 4; k++) if (A[k][k] > A[best][best]) best = k;
+    double w = V[0][best], x = V[1][best], y = V[2][best], z = V[3][best];
+    const double qn = std::sqrt(w * w + x * x + y * y + z * z);
+    w /= qn; x /= qn; y /= qn; z /= qn;
+    const double R[3][3] = {{1.0 - 2.0 * (y * y + z * z), 2.0 * (x * y - w * z), 2.0 * (x * z + w * y)},
+                            {2.0 * (x * y + w * z), 1.0 - 2.0 * (x * x + z * z), 2.0 * (y * z - w * x)},
+                            {2.0 * (x * z - w * y), 2.0 * (y * z + w * x), 1.0 - 2.0 * (x * x + y * y)}};
+    for (int a = 0; a < 3; a++) {
+        for (int b = 0; b < 3; b++) T[4 * a + b] = R[a][b];
+        T[4 * a + 3] = mt[a] - (R[a][0] * ms[0] + R[a][1] * ms[1] + R[a][2] * ms[2]);
+    }
+    T[12] = T[13] = T[14] = 0.0; T[15] = 1.0;
+}
+inline void apply(const double* T, const double* p, double* o) {
+    for (int r = 0; r < 3; r++) o[r] = T[4 * r] * p[0] + T[4 * r + 1] * p[1] + T[4 * r + 2] * p[2] + T[4 * r + 3];
+}
+}  // namespace
+
+O3R_API void o3r_horn_rigid(const double* s, const double* t, int n, double* T) {
+    horn(reinterpret_cast<const double (*)[3]>(s), reinterpret_cast<const double (*)[3]>(t), n, T);
+}
+
+// nearest feature by squared L2 (index order summation, ties -> lower index)
+O3R_API void o3r_match_features(const double* qf, int64_t nq, const double* tf, int64_t nt, int dim, int32_t* out) {
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < nq; i++) {
+        double best = INFINITY; int32_t bi = -1;
+        for (int64_t j = 0; j < nt; j++) {
+            double d2 = 0.0;
+            for (int d = 0; d < dim; d++) { const double e = qf[i * dim + d] - tf[j * dim + d]; d2 += e * e; }
+            if (d2 < best) { best = d2; bi = (int32_t)j; }
+        }
+        out[i] = bi;
+    }
+}
+
+// report4 = {iterations consumed, hypotheses validated, winning iteration, its inlier-correspondence count}
+O3R_API int o3r_ransac_correspondence(const double* src, int64_t N, const double* tgt, int64_t M, const int32_t* corres, int64_t C,
+                                      double max_dist, int ransac_n, double edge_thr, double dist_thr, int64_t max_iteration,
+                                      double confidence, uint64_t seed, double* out_T, double* out_fitness, double* out_rmse, int64_t* report4) {
+    for (int i = 0; i < 16; i++) out_T[i] = (i % 5 == 0) ? 1.0 : 0.0;
+    *out_fitness = 0.0; *out_rmse = 0.0;
+    for (int i = 0; i < 4; i++) report4[i] = 0;
+    if (ransac_n < 3 || C < ransac_n || !(max_dist > 0.0)) return 0;
+    if (ransac_n > 8) return -1;
+    confidence = std::min(std::max(confidence, 0.0), 1.0);
+    const double r2 = max_dist * max_dist;
+    double best_fit = 0.0, best_rmse = 0.0;
+    int64_t est_k = max_iteration, validated = 0, consumed = 0, win = -1, win_inl = 0;
+    for (int64_t itr = 0; itr < max_iteration && itr < est_k; itr++) {
+        consumed = itr + 1;
+        double s[8][3], t[8][3];
+        for (int j = 0; j < ransac_n; j++) {
+            const uint32_t c = draw(seed, (uint64_t)itr, j, (uint32_t)C);
+            for (int k = 0; k < 3; k++) { s[j][k] = src[3 * (int64_t)corres[2 * c] + k]; t[j][k] = tgt[3 * (int64_t)corres[2 * c + 1] + k]; }
+        }
+        bool ok = true;
+        if (edge_thr > 0.0)
+            for (int i = 0; i < ransac_n && ok; i++)
+                for (int j = i + 1; j < ransac_n && ok; j++) {
+                    const double ds = std::sqrt((s[i][0] - s[j][0]) * (s[i][0] - s[j][0]) + (s[i][1] - s[j][1]) * (s[i][1] - s[j][1]) + (s[i][2] - s[j][2]) * (s[i][2] - s[j][2]));
+                    const double dt = std::sqrt((t[i][0] - t[j][0]) * (t[i][0] - t[j][0]) + (t[i][1] - t[j][1]) * (t[i][1] - t[j][1]) + (t[i][2] - t[j][2]) * (t[i][2] - t[j][2]));
+                    if (ds < dt * edge_thr || dt < ds * edge_thr) ok = false;
+                }
+        if (!ok) continue;
+        double T[16];
+        horn(s, t, ransac_n, T);
+        if (dist_thr > 0.0)
+            for (int i = 0; i < ransac_n && ok; i++) {
+                double p[3]; apply(T, s[i], p);
+                const double d2 = (t[i][0] - p[0]) * (t[i][0] - p[0]) + (t[i][1] - p[1]) * (t[i][1] - p[1]) + (t[i][2] - p[2]) * (t[i][2] - p[2]);
+                if (std::sqrt(d2) > dist_thr) ok = false;
+            }
+        for (int k = 0; k < 16; k++) if (!std::isfinite(T[k])) ok = false;
+        if (!ok) continue;
+        validated++;
+        int64_t cnt = 0; double sum = 0.0;
+#pragma omp parallel for schedule(static) reduction(+ : cnt, sum)
+        for (int64_t i = 0; i < N; i++) {
+            double p[3]; apply(T, src + 3 * i, p);
+            double bd = INFINITY;
+            for (int64_t j = 0; j < M; j++) {
+                const double dx = tgt[3 * j] - p[0], dy = tgt[3 * j + 1] - p[1], dz = tgt[3 * j + 2] - p[2];
+                const double d2 = dx * dx + dy * dy + dz * dz;
+                if (d2 < bd) bd = d2;
+            }
+            if (bd < r2) { cnt++; sum += bd; }
+        }
+        const double fit = (double)cnt / (double)N, rm = cnt > 0 ? std::sqrt(sum / (double)cnt) : 0.0;
+        if (fit > best_fit || (fit == best_fit && rm < best_rmse)) {
+            best_fit = fit; best_rmse = rm; win = itr; std::memcpy(out_T, T, sizeof(T));
+            int64_t inl = 0;
+            for (int64_t c = 0; c < C; c++) {
+                double p[3]; apply(T, src + 3 * (int64_t)corres[2 * c], p);
+                const double* q = tgt + 3 * (int64_t)corres[2 * c + 1];
+                const double d2 = (q[0] - p[0]) * (q[0] - p[0]) + (q[1] - p[1]) * (q[1] - p[1]) + (q[2] - p[2]) * (q[2] - p[2]);
+                if (std::sqrt(d2) < max_dist) inl++;
+            }
+            win_inl = inl;
+            const double ratio = (double)inl / (double)C;
+            const double k_d = std::log(1.0 - confidence) / std::log(1.0 - std::pow(ratio, (double)ransac_n));
+            if (std::isfinite(k_d) && k_d >= 0.0 && k_d < (double)est_k) est_k = (int64_t)std::ceil(k_d);
+        }
+    }
+    if (consumed > est_k) consumed = est_k;
+    *out_fitness = best_fit; *out_rmse = best_rmse;
+    report4[0] = consumed; report4[1] = validated; report4[2] = win; report4[3] = win_inl;
+    return 0;
+}

@@ -217,3 +217,77 @@ def test_fpfh_parity(o3r, cloud):
     bare = o3d.geometry.PointCloud(xyz)
     with pytest.raises(RuntimeError, match="no normal"):
         o3d.pipelines.registration.compute_fpfh_feature(bare, o3d.geometry.KDTreeSearchParamHybrid(radius=0.15, max_nn=100))
+
+
+def test_ransac_feature_matching_parity_and_reference_call(o3r, small_kinect):
+    """f4: detect_and_estimate_transformation of BetterVisualizer2CamWorksCOLOR.py:219-243 -- two views of the scene,
+    preprocess (down-sample, normals, FPFH), nearest-feature correspondences, RANSAC.  The correspondence list is bit-exact
+    vs the oracle; the RANSAC winner (same seed, same draws, same rigid fits) is the same iteration with the same
+    transformation; the transformation aligns the views."""
+    K = intrinsic_of(small_kinect.depth_intr)
+    poses = syn.orbit_trajectory(8, yaw_sweep_deg=16.0)
+    Rg = o3d.pipelines.registration
+    voxel = 0.06
+
+    def view(p):
+        d, c = small_kinect.render_depth_aligned_rgb(p)
+        rgbd = o3d.geometry.RGBDImage.create_from_color_and_depth(o3d.geometry.Image(c), o3d.geometry.Image(d), 1000.0, 3.0, False)
+        pc = o3d.geometry.PointCloud.create_from_rgbd_image(rgbd, K)
+        down = pc.voxel_down_sample(voxel)
+        down.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(radius=voxel * 2, max_nn=30))
+        return down, Rg.compute_fpfh_feature(down, o3d.geometry.KDTreeSearchParamHybrid(radius=voxel * 5, max_nn=100))
+
+    (src, fs), (tgt, ft) = view(poses[5]), view(poses[0])
+    truth = np.linalg.inv(poses[0]) @ poses[5]                               # source camera -> target camera
+    sx, tx = np.asarray(src.points), np.asarray(tgt.points)
+    assert len(sx) > 500 and len(tx) > 500
+    # nearest features: exact
+    want_ij = o3r.match_features(fs.tensor.cpu().numpy(), ft.tensor.cpu().numpy())
+    ij = torch.empty((len(sx),), dtype=torch.int32, device="cuda")
+    _lib.check(_lib.load().b2r_match_features(_lib.ptr(fs.tensor), len(sx), _lib.ptr(ft.tensor), len(tx), 33, _lib.ptr(ij), _lib.stream_ptr()))
+    assert np.array_equal(ij.cpu().numpy(), want_ij)
+    corres = np.stack([np.arange(len(sx), dtype=np.int32), want_ij], 1)
+    dist = voxel * 1.5
+    crit = Rg.RANSACConvergenceCriteria(30000, 0.999)
+    checkers = [Rg.CorrespondenceCheckerBasedOnEdgeLength(0.9), Rg.CorrespondenceCheckerBasedOnDistance(dist)]
+    res = Rg.registration_ransac_based_on_correspondence(src, tgt, o3d.utility.Vector2iVector(corres), dist * 2, Rg.TransformationEstimationPointToPoint(False),
+                                                         3, checkers, crit, seed=3)
+    T_r, fit_r, rmse_r, rep_r = o3r.ransac_correspondence(sx, tx, corres, dist * 2, ransac_n=3, edge_thr=0.9, dist_thr=dist, max_iteration=30000,
+                                                          confidence=0.999, seed=3)
+    rep = res.ransac_report
+    assert (rep["iterations"], rep["validated"], rep["winning_iteration"], rep["inlier_correspondences"]) == rep_r
+    assert np.abs(res.transformation - T_r).max() <= 1e-12                   # same draws, same closed-form fit
+    assert res.fitness == fit_r and abs(res.inlier_rmse - rmse_r) <= 1e-12
+    assert res.fitness > 0.5
+    # a coarse alignment (FPFH on a box room is ambiguous; max_correspondence_distance is 3 voxels) ...
+    assert np.abs(res.transformation[:3, 3] - truth[:3, 3]).max() < 0.3 and np.abs(res.transformation[:3, :3] - truth[:3, :3]).max() < 0.3
+    # ... which the reference then hands to point-to-plane ICP (BetterVisualizer2CamWorksCOLOR.py:252-259)
+    fine = Rg.registration_icp(src, tgt, dist, res.transformation, Rg.TransformationEstimationPointToPlane(), Rg.ICPConvergenceCriteria(max_iteration=50))
+    assert fine.fitness > 0.5
+    assert np.abs(fine.transformation[:3, 3] - truth[:3, 3]).max() <= np.abs(res.transformation[:3, 3] - truth[:3, 3]).max() + 1e-3
+    cs = np.asarray(res.correspondence_set)
+    assert len(cs) == round(res.fitness * len(sx)) and (cs[:, 0] < len(sx)).all() and (cs[:, 1] < len(tx)).all()
+    # the reference's call, verbatim argument style (older signature: no mutual_filter, "500" as the second criterion)
+    ref_style = Rg.registration_ransac_based_on_feature_matching(
+        src, tgt, fs, ft, max_correspondence_distance=dist * 2, estimation_method=Rg.TransformationEstimationPointToPoint(False), ransac_n=4,
+        checkers=[Rg.CorrespondenceCheckerBasedOnEdgeLength(0.9), Rg.CorrespondenceCheckerBasedOnDistance(dist)],
+        criteria=Rg.RANSACConvergenceCriteria(200000, 500))
+    assert ref_style.ransac_report["iterations"] == 200000                   # confidence clamps to 1: the whole budget runs
+    assert ref_style.fitness > 0.5 and ref_style.transformation.trace() != 4.0
+    new_style = Rg.registration_ransac_based_on_feature_matching(src, tgt, fs, ft, True, dist * 2, Rg.TransformationEstimationPointToPoint(False), 3,
+                                                                 checkers, Rg.RANSACConvergenceCriteria(20000, 0.999))
+    assert new_style.fitness > 0.3
+    # the validation primitive on its own == brute force
+    from azurekinect3dreconstruction_b200.geometry import _Knn
+    Ts = np.stack([truth, np.eye(4), res.transformation])
+    knn = _Knn(dev(tx), dist * 2, 1)
+    cnt = torch.empty((3,), dtype=torch.int64, device="cuda"); sm = torch.empty((3,), dtype=torch.float64, device="cuda")
+    _lib.check(_lib.load().b2r_knn_evaluate_transforms(knn._h, _lib.ptr(dev(sx)), len(sx), _lib.ptr(dev(Ts)), 3, dist * 2, _lib.ptr(cnt), _lib.ptr(sm), _lib.stream_ptr()))
+    torch.cuda.synchronize(); knn.close()
+    for h in range(3):
+        moved = o3r.transform_points(sx, Ts[h])
+        d2 = ((moved[:, None, :] - tx[None]) ** 2).sum(-1).min(1)
+        assert int(cnt[h]) == int((d2 < (dist * 2) ** 2).sum())
+        assert abs(float(sm[h]) - d2[d2 < (dist * 2) ** 2].sum()) <= 1e-9
+    with pytest.raises(RuntimeError):
+        Rg.registration_ransac_based_on_correspondence(src, tgt, corres, dist, Rg.TransformationEstimationPointToPlane(), 3, [], crit)

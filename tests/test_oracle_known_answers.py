@@ -404,3 +404,50 @@ def test_fpfh_oracle_known_answers(o3r):
     assert np.abs(f1 - f2).max() < 25.0 and np.median(np.abs(f1 - f2)) < 1e-9  # only bin-edge flips / distance ties may move mass
     with pytest.raises(RuntimeError):
         o3r.compute_fpfh(pts, None)
+
+
+def test_ransac_oracle_known_answers(o3r):
+    """f4 (registration_ransac_based_on_*): Horn's closed form equals the SVD (Kabsch / umeyama without scale) optimum; with
+    60 % wrong correspondences RANSAC still recovers the motion; checkers reject inconsistent samples; degenerate arguments
+    return upstream's empty result; same seed -> same answer."""
+    from azurekinect3dreconstruction_b200 import synthetic as syn
+    rng = np.random.default_rng(7)
+    for n in (3, 4, 8):
+        s = rng.normal(0, 1, (n, 3))
+        M = syn.make_pose(syn.rot_z(0.9) @ syn.rot_y(-0.5) @ syn.rot_x(0.3), (0.4, -1.2, 0.7))
+        t = o3r.transform_points(s, M) + rng.normal(0, 1e-3, (n, 3))
+        T = o3r.horn_rigid(s, t)
+        ms, mt = s.mean(0), t.mean(0)
+        U, _, Vt = np.linalg.svd((t - mt).T @ (s - ms))
+        D = np.diag([1.0, 1.0, np.sign(np.linalg.det(U @ Vt))])
+        Rk = U @ D @ Vt
+        np.testing.assert_allclose(T[:3, :3], Rk, atol=1e-9)
+        np.testing.assert_allclose(T[:3, 3], mt - Rk @ ms, atol=1e-9)
+        np.testing.assert_allclose(T[:3, :3] @ T[:3, :3].T, np.eye(3), atol=1e-12)
+    # a bumpy surface, its moved copy, and a correspondence list that is 60 % garbage
+    u, v = rng.random(600) * 2 - 1, rng.random(600) * 2 - 1
+    tgt = np.stack([u, v, 0.3 * np.sin(3 * u) * np.cos(2 * v) + 0.2 * u * v], 1)
+    M = syn.make_pose(syn.rot_z(0.6) @ syn.rot_x(-0.35), (0.5, -0.3, 0.8))
+    src = o3r.transform_points(tgt, np.linalg.inv(M)) + rng.normal(0, 2e-4, tgt.shape)
+    corres = np.stack([np.arange(600), np.arange(600)], 1).astype(np.int32)
+    bad = rng.random(600) < 0.6
+    corres[bad, 1] = rng.integers(0, 600, bad.sum())
+    T, fit, rmse, rep = o3r.ransac_correspondence(src, tgt, corres, 0.02, ransac_n=4, edge_thr=0.9, dist_thr=0.02, max_iteration=20000, confidence=0.999, seed=1)
+    np.testing.assert_allclose(T, M, atol=5e-3)
+    assert fit > 0.95 and rmse < 5e-3 and 0 <= rep[2] < rep[0] <= 20000 and rep[1] >= 1
+    assert rep[0] < 20000                                                    # the confidence rule cut the budget short
+    assert rep[3] >= 0.3 * 600                                               # the winner explains the clean 40 %
+    T2, fit2, rmse2, rep2 = o3r.ransac_correspondence(src, tgt, corres, 0.02, ransac_n=4, edge_thr=0.9, dist_thr=0.02, max_iteration=20000, confidence=0.999, seed=1)
+    assert np.array_equal(T, T2) and rep == rep2                             # deterministic for a seed
+    _, _, _, rep3 = o3r.ransac_correspondence(src, tgt, corres, 0.02, ransac_n=4, max_iteration=300, confidence=1.0, seed=1)
+    assert rep3[0] == 300 and rep3[1] == 300                                 # no checkers: every draw is validated; confidence 1 never stops early
+    Te, fe, re_, repe = o3r.ransac_correspondence(src, tgt, corres[:2], 0.02, ransac_n=3)
+    assert np.array_equal(Te, np.eye(4)) and fe == 0.0 and repe[0] == 0      # fewer correspondences than ransac_n: empty result
+    Te, fe, _, _ = o3r.ransac_correspondence(src, tgt, corres, 0.0, ransac_n=3)
+    assert np.array_equal(Te, np.eye(4)) and fe == 0.0
+    # nearest-feature matching: exact argmin, ties to the lower index
+    fq, ft = rng.random((50, 33)), rng.random((70, 33))
+    ft[10] = ft[3]
+    fq[0] = ft[3]
+    m = o3r.match_features(fq, ft)
+    assert m[0] == 3 and np.array_equal(m, ((fq[:, None, :] - ft[None]) ** 2).sum(-1).argmin(1).astype(np.int32))

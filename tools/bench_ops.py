@@ -188,6 +188,36 @@ def main():
                              "fitness": float(r_c.fitness), "inlier_rmse": float(r_c.inlier_rmse),
                              "translation_error_m_vs_ground_truth": float(np.linalg.norm(r_c.transformation[:3, 3] - gt01[:3, 3]))}
 
+    # ---- f4: preprocess_point_cloud + global registration of two views (BetterVisualizer2CamWorksCOLOR.py:197-243), full NFOV frames
+    Rg4 = o3d.pipelines.registration
+    vox = 0.05
+    def prep(i):
+        r_ = o3d.geometry.RGBDImage.create_from_color_and_depth(o3d.geometry.Image(cc[i]), o3d.geometry.Image(dd[i]), 1000.0, 3.0, False)
+        pc_, _ = o3d.geometry.PointCloud.create_from_rgbd_image(r_, Kd).remove_statistical_outlier(nb_neighbors=20, std_ratio=2.0)
+        dn_ = pc_.voxel_down_sample(vox)
+        dn_.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(radius=vox * 2, max_nn=30))
+        torch.cuda.synchronize(); t0_ = time.perf_counter()
+        f_ = Rg4.compute_fpfh_feature(dn_, o3d.geometry.KDTreeSearchParamHybrid(radius=vox * 5, max_nn=100)); torch.cuda.synchronize()
+        return dn_, f_, time.perf_counter() - t0_
+    far = min(len(poses) - 1, F - 1)
+    prep(0)
+    (g_src, g_fs, t_f1), (g_tgt, g_ft, t_f2) = prep(far), prep(0)
+    dthr = vox * 1.5
+    def ransac(iters, conf):
+        return Rg4.registration_ransac_based_on_feature_matching(
+            g_src, g_tgt, g_fs, g_ft, max_correspondence_distance=dthr * 2, estimation_method=Rg4.TransformationEstimationPointToPoint(False), ransac_n=4,
+            checkers=[Rg4.CorrespondenceCheckerBasedOnEdgeLength(0.9), Rg4.CorrespondenceCheckerBasedOnDistance(dthr)],
+            criteria=Rg4.RANSACConvergenceCriteria(iters, conf))
+    ransac(100000, 0.999); torch.cuda.synchronize()
+    t0 = time.perf_counter(); r_g = ransac(4000000, 500); torch.cuda.synchronize(); t_g = time.perf_counter() - t0      # the reference's criteria
+    t0 = time.perf_counter(); r_q = ransac(4000000, 0.999); torch.cuda.synchronize(); t_q = time.perf_counter() - t0
+    gtf = np.linalg.inv(poses[0]) @ poses[far]
+    out["global_registration_f4"] = {"voxel": vox, "source_points": len(g_src.points), "target_points": len(g_tgt.points), "fpfh_ms": 1e3 * 0.5 * (t_f1 + t_f2),
+                                     "ransac_4M_iterations_ms": 1e3 * t_g, "ransac_4M_report": r_g.ransac_report, "fitness": float(r_g.fitness),
+                                     "translation_error_m_vs_ground_truth": float(np.linalg.norm(r_g.transformation[:3, 3] - gtf[:3, 3])),
+                                     "ransac_confidence_0.999_ms": 1e3 * t_q, "ransac_confidence_0.999_report": r_q.ransac_report,
+                                     "views": [0, far]}
+
     # ---- f1: per-frame conditioning chain of the reference (GoodColorReconstruction.py:141-153) on one full NFOV frame
     rgbd0 = o3d.geometry.RGBDImage.create_from_color_and_depth(o3d.geometry.Image(cc[0]), o3d.geometry.Image(dd[0]), 1000.0, 3.0, False)
     full = o3d.geometry.PointCloud.create_from_rgbd_image(rgbd0, Kd)
