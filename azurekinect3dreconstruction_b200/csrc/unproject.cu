@@ -504,7 +504,7 @@ __device__ __forceinline__ int unproject_chunk_fast(const UnprojParams& P, int b
 template <int CMODE, bool GATHER, bool WANT_IDX, bool FAST>
 __device__ __forceinline__ int unproject_chunk(const UnprojParams& P, int b, int chunk, int row, int col, int64_t off, const float* T,
                                                float* s_xyz, float* s_rgb, int32_t* s_idx, int32_t* s_gidx, int* ws) {
-    constexpr int PPT = 8, CHUNK = UNP_THREADS * PPT;
+    constexpr int PPT = 8;
     const int s0 = (chunk * UNP_THREADS + threadIdx.x) * PPT;
     const size_t fbase = (size_t)b * P.W * P.H;
     float d[PPT]; int pix[PPT];

@@ -164,3 +164,73 @@ def test_cuda_reproduces_golden_v2():
     pcd.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(0.08, 16))
     dots = np.einsum("ij,ij->i", np.asarray(pcd.normals), G2["f1_normals"])
     assert np.abs(np.abs(dots) - 1.0).max() <= 1e-9
+
+
+G3 = np.load(os.path.join(os.path.dirname(__file__), "golden", "hotpath_v3.npz"))
+
+
+def _g3_pose_graph():
+    import azurekinect3dreconstruction_b200 as o3d
+    R = o3d.pipelines.registration
+    pg = R.PoseGraph()
+    for p in G3["f3_nodes"]:
+        pg.nodes.append(R.PoseGraphNode(p))
+    for k in range(len(G3["f3_src"])):
+        pg.edges.append(R.PoseGraphEdge(int(G3["f3_src"][k]), int(G3["f3_dst"][k]), G3["f3_T"][k], G3["f3_info"][k], bool(G3["f3_uncertain"][k])))
+    o = G3["f3_option"]
+    return pg, R, R.GlobalOptimizationOption(float(o[0]), float(o[1]), float(o[2]), int(o[3]))
+
+
+def test_golden_v3_pose_graph_and_cpu_oracles(o3r):
+    """Rows f3 / f4: the CPU restatements reproduce the committed fixture (pins them against drift), and the host LM of
+    libb2recon.so (envelope Cholesky) lands on the fixture's dense-solver result."""
+    pg, R, opt = _g3_pose_graph()
+    R.global_optimization(pg, R.GlobalOptimizationLevenbergMarquardt(), R.GlobalOptimizationConvergenceCriteria(), opt)
+    rep = pg.last_report
+    assert [rep["iterations"][0], rep["lm_steps"][0], rep["iterations"][1], rep["lm_steps"][1]] == G3["f3_iters"].tolist()
+    assert np.array_equal(np.array([[e.source_node_id, e.target_node_id] for e in pg.edges], np.int32), G3["f3_out_edges"])
+    assert np.abs(np.stack([nd.pose for nd in pg.nodes]) - G3["f3_out_nodes"]).max() <= 1e-9
+    assert np.abs(np.array([e.confidence for e in pg.edges]) - G3["f3_out_conf"]).max() <= 1e-9
+    T, fit, rmse, corr, it, grad = o3r.icp_colored(G3["c_src"], G3["c_src_rgb"], G3["c_tgt"], G3["c_tgt_nrm"], G3["c_tgt_rgb"], 0.03, 0.968, np.eye(4), max_iter=30)
+    assert it == int(G3["c_iters"][0]) and np.array_equal(corr, G3["c_corr"])
+    assert np.abs(T - G3["c_T"]).max() <= 1e-12 and np.abs(grad - G3["c_grad"]).max() <= 1e-9
+    assert np.abs(T[:3, 3] - G3["c_truth"][:3, 3]).max() < 1e-3                 # the fixture itself is near the true motion
+    fa = o3r.compute_fpfh(G3["g_src"], G3["g_src_nrm"], 60, 0.12)
+    assert np.array_equal(fa, G3["g_fpfh_src"])
+    ij = o3r.match_features(G3["g_fpfh_src"], G3["g_fpfh_tgt"])
+    assert np.array_equal(ij, G3["g_match"])
+    corres = np.stack([np.arange(len(ij), dtype=np.int32), ij], 1)
+    RT, rfit, rrmse, rrep = o3r.ransac_correspondence(G3["g_src"], G3["g_tgt"], corres, 0.05, ransac_n=3, edge_thr=0.9, dist_thr=0.03, max_iteration=50000,
+                                                      confidence=0.999, seed=5)
+    assert list(rrep) == G3["g_report"].tolist() and np.array_equal(RT, G3["g_T"]) and rfit == G3["g_fit"][0]
+    assert np.abs(RT - G3["g_truth"]).max() < 0.05
+
+
+@pytest.mark.gpu
+def test_cuda_reproduces_golden_v3():
+    import azurekinect3dreconstruction_b200 as o3d
+    R = o3d.pipelines.registration
+    s, t = o3d.geometry.PointCloud(G3["c_src"]), o3d.geometry.PointCloud(G3["c_tgt"])
+    s.colors, t.colors = o3d.utility.Vector3dVector(G3["c_src_rgb"]), o3d.utility.Vector3dVector(G3["c_tgt_rgb"])
+    t.normals = o3d.utility.Vector3dVector(G3["c_tgt_nrm"])
+    res = R.registration_colored_icp(s, t, 0.03, np.eye(4), R.TransformationEstimationForColoredICP(0.968), R.ICPConvergenceCriteria(1e-6, 1e-6, 30))
+    assert res.num_iterations == int(G3["c_iters"][0])
+    assert np.abs(res.transformation - G3["c_T"]).max() <= 1e-6 and np.abs(res.color_gradient.cpu().numpy() - G3["c_grad"]).max() <= 1e-9
+    corr = np.full(len(G3["c_src"]), -1, np.int32)
+    cs = np.asarray(res.correspondence_set)
+    corr[cs[:, 0]] = cs[:, 1]
+    assert np.array_equal(corr, G3["c_corr"])
+    a, b = o3d.geometry.PointCloud(G3["g_src"]), o3d.geometry.PointCloud(G3["g_tgt"])
+    a.normals, b.normals = o3d.utility.Vector3dVector(G3["g_src_nrm"]), o3d.utility.Vector3dVector(G3["g_tgt_nrm"])
+    par = o3d.geometry.KDTreeSearchParamHybrid(radius=0.12, max_nn=60)
+    fa, fb = R.compute_fpfh_feature(a, par), R.compute_fpfh_feature(b, par)
+    ga, gb = fa.tensor.cpu().numpy(), fb.tensor.cpu().numpy()
+    assert (np.abs(ga - G3["g_fpfh_src"]).max(1) > 1e-9).sum() <= 1 and (np.abs(gb - G3["g_fpfh_tgt"]).max(1) > 1e-9).sum() <= 1
+    fa.tensor = torch.as_tensor(G3["g_fpfh_src"]).cuda()                       # the fixture's features: the rest must then be exact
+    fb.tensor = torch.as_tensor(G3["g_fpfh_tgt"]).cuda()
+    out = R.registration_ransac_based_on_feature_matching(a, b, fa, fb, False, 0.05, R.TransformationEstimationPointToPoint(False), 3,
+                                                          [R.CorrespondenceCheckerBasedOnEdgeLength(0.9), R.CorrespondenceCheckerBasedOnDistance(0.03)],
+                                                          R.RANSACConvergenceCriteria(50000, 0.999), seed=5)
+    rep = out.ransac_report
+    assert [rep["iterations"], rep["validated"], rep["winning_iteration"], rep["inlier_correspondences"]] == G3["g_report"].tolist()
+    assert np.abs(out.transformation - G3["g_T"]).max() <= 1e-12 and out.fitness == G3["g_fit"][0]

@@ -25,6 +25,9 @@ VOXEL, TRUNC = 0.02, 0.08
 
 
 def main():
+    if "--only-v3" in sys.argv:
+        make_v3()
+        return
     kin = syn.SyntheticKinect(depth_intrinsics=INTR, seed=7, dropout=0.02)
     poses = syn.orbit_trajectory(3, yaw_sweep_deg=4.0)
     K = (INTR["fx"], INTR["fy"], INTR["cx"], INTR["cy"])
@@ -113,6 +116,73 @@ def make_v2(kin, poses, depth, rgb, K):
     path = os.path.join(ROOT, "tests", "golden", "hotpath_v2.npz")
     np.savez_compressed(path, **out)
     print(path, os.path.getsize(path), "bytes;", len(xyz), "points,", int((gi >= 0).sum()), "gathered texels,", len(vp), "voxels")
+
+
+def make_v3():
+    """tests/golden/hotpath_v3.npz: rows f3 / f4 -- pose-graph optimisation, coloured ICP (gradients + pose), FPFH, nearest
+    features and RANSAC, on inputs small enough for the dense / brute-force CPU restatements."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import posegraph as pgref
+    rng = np.random.default_rng(11)
+    # f3: 14-node orbit, noisy odometry chain, two true closures, one false closure
+    n = 14
+    gt = syn.orbit_trajectory(n)
+    info = np.identity(6) * 2000.0
+    mot = lambda r, t: pgref.transform_vector6d_to_matrix4d(np.concatenate([rng.normal(0, r, 3), rng.normal(0, t, 3)]))
+    nodes, edges = [gt[0].copy()], []
+    for i in range(1, n):
+        T = np.linalg.inv(gt[i]) @ gt[i - 1] @ mot(0.002, 0.003)
+        nodes.append(nodes[i - 1] @ np.linalg.inv(T))
+        edges.append(dict(s=i - 1, t=i, T=T, info=info, uncertain=False, conf=1.0))
+    for a, b in ((0, 13), (2, 10)):
+        edges.append(dict(s=a, t=b, T=np.linalg.inv(gt[b]) @ gt[a], info=info, uncertain=True, conf=1.0))
+    edges.append(dict(s=1, t=8, T=np.linalg.inv(gt[8]) @ gt[1] @ pgref.transform_vector6d_to_matrix4d(np.array([0.3, -0.2, 0.4, 0.5, -0.4, 0.3])),
+                      info=info, uncertain=True, conf=1.0))
+    opt = dict(max_correspondence_distance=0.05, edge_prune_threshold=0.25, preference_loop_closure=2.0, reference_node=0)
+    on, oe, (r1, r2) = pgref.global_optimization(nodes, edges, opt)
+    out = dict(f3_nodes=np.stack(nodes), f3_src=np.array([e["s"] for e in edges], np.int32), f3_dst=np.array([e["t"] for e in edges], np.int32),
+               f3_T=np.stack([e["T"] for e in edges]), f3_info=np.stack([e["info"] for e in edges]),
+               f3_uncertain=np.array([e["uncertain"] for e in edges], np.uint8), f3_option=np.array([0.05, 0.25, 2.0, 0.0]),
+               f3_out_nodes=np.stack(on), f3_out_edges=np.array([[e["s"], e["t"]] for e in oe], np.int32),
+               f3_out_conf=np.array([e["conf"] for e in oe]), f3_iters=np.array([r1[0], r1[1], r2[0], r2[1]], np.int64))
+    # f4 coloured ICP: a gently curved textured sheet and a slightly moved, re-sampled copy
+    def sheet(m, seed):
+        r = np.random.default_rng(seed)
+        u, v = r.random(m) * 0.5 - 0.25, r.random(m) * 0.5 - 0.25
+        z = 2.0 + 0.03 * np.sin(5 * u) + 0.02 * v * v
+        p = np.stack([u, v, z], 1)
+        nz = np.stack([-0.15 * np.cos(5 * u), -0.04 * v, np.ones_like(u)], 1)
+        inten = 0.5 + 0.25 * np.sin(18 * u) * np.cos(14 * v) + 0.1 * u
+        return p, nz / np.linalg.norm(nz, axis=1, keepdims=True), np.stack([inten, inten * 0.9 + 0.05, inten * 0.8 + 0.1], 1)
+    tp, tn, tc = sheet(1400, 1)
+    sp, _, sc = sheet(900, 2)
+    M = syn.make_pose(syn.rot_z(0.01) @ syn.rot_x(-0.008), (0.004, -0.003, 0.002))
+    sp = o3r.transform_points(sp, np.linalg.inv(M))
+    T, fit, rmse, corr, it, grad = o3r.icp_colored(sp, sc, tp, tn, tc, 0.03, 0.968, np.eye(4), max_iter=30)
+    out.update(c_src=sp, c_src_rgb=sc, c_tgt=tp, c_tgt_nrm=tn, c_tgt_rgb=tc, c_T=T, c_fit=np.array([fit, rmse]), c_iters=np.array([it]),
+               c_corr=corr, c_grad=grad, c_truth=M)
+    # f4 FPFH + nearest features + RANSAC: a bumpy surface and its moved copy (different sampling), 3-sample RANSAC
+    def bumpy(m, seed):
+        r = np.random.default_rng(seed)
+        u, v = r.random(m) * 0.8 - 0.4, r.random(m) * 0.8 - 0.4
+        z = 0.08 * np.sin(9 * u) * np.cos(7 * v) + 0.05 * np.cos(11 * u * v) + 0.3 * u * u
+        p = np.stack([u, v, z], 1)
+        nrm, _ = o3r.pcd_estimate_normals(p, 20, 0.08)
+        return p, o3r.pcd_orient_normals(p, nrm, (0.0, 0.0, 5.0))
+    bp, bn = bumpy(700, 3)
+    ap, an = bumpy(650, 4)
+    G = syn.make_pose(syn.rot_z(0.5) @ syn.rot_y(0.2), (0.3, -0.1, 0.6))
+    ap, an = o3r.transform_points(ap, np.linalg.inv(G)), an @ G[:3, :3]      # source = target surface seen from another frame
+    fa, fb = o3r.compute_fpfh(ap, an, 60, 0.12), o3r.compute_fpfh(bp, bn, 60, 0.12)
+    ij = o3r.match_features(fa, fb)
+    corres = np.stack([np.arange(len(ap), dtype=np.int32), ij], 1)
+    RT, rfit, rrmse, rrep = o3r.ransac_correspondence(ap, bp, corres, 0.05, ransac_n=3, edge_thr=0.9, dist_thr=0.03, max_iteration=50000, confidence=0.999, seed=5)
+    out.update(g_src=ap, g_src_nrm=an, g_tgt=bp, g_tgt_nrm=bn, g_fpfh_src=fa, g_fpfh_tgt=fb, g_match=ij, g_T=RT, g_fit=np.array([rfit, rrmse]),
+               g_report=np.array(rrep, np.int64), g_truth=G)
+    path = os.path.join(ROOT, "tests", "golden", "hotpath_v3.npz")
+    np.savez_compressed(path, **out)
+    print(path, os.path.getsize(path), "bytes; pose graph kept", len(oe), "of", len(edges), "edges, iterations", r1, r2,
+          "| coloured ICP", it, "iterations fit", fit, "| RANSAC", rrep, "fit", rfit, "err", np.abs(RT - G).max())
 
 
 if __name__ == "__main__":
