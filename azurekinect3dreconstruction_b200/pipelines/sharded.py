@@ -197,7 +197,8 @@ class HostFrameExchange:
     When the frames start in HOST memory, pushing every frame through every GPU's PCIe link would cap the job at one
     link's bandwidth whatever the GPU count.  Instead rank r copies only its 1/world share host->device (pinned,
     asynchronous, on a copy stream), and one NCCL all-gather per super-chunk hands every rank all frames over
-    NVLink/NVSwitch; the next super-chunk's upload overlaps the current gather + integration (double buffering).
+    NVLink/NVSwitch.  Three streams, double-buffered: the copy stream uploads super-chunk i + 2 and the communication
+    stream gathers super-chunk i + 1 while the caller's stream integrates super-chunk i.
     `consume(depth, color, first_frame, n_valid)` receives device tensors in global frame order."""
 
     def __init__(self, frame_shape, color_channels: int, per: int = 8, group=None, device=None):
@@ -212,8 +213,10 @@ class HostFrameExchange:
         self.ld, self.lc = mk(self.per, (self.H, self.W), torch.int16), mk(self.per, (self.H, self.W, self.ch), torch.uint8)
         self.gd, self.gc = mk(S, (self.H, self.W), torch.int16), mk(S, (self.H, self.W, self.ch), torch.uint8)
         self.copy_stream = torch.cuda.Stream(device=device) if cuda else None
-        self.uploaded = [torch.cuda.Event() for _ in range(2)] if cuda else None
-        self.consumed = [torch.cuda.Event() for _ in range(2)] if cuda else None
+        self.comm_stream = torch.cuda.Stream(device=device) if cuda else None
+        ev = lambda: [torch.cuda.Event() for _ in range(2)] if cuda else None
+        self.uploaded, self.consumed = ev(), ev()       # local slot: filled by the copy stream / read by the gather
+        self.gathered, self.released = ev(), ev()       # gathered slot: filled by the gather / read by the consumer
         self.bytes_uploaded = 0
 
     def _upload(self, slot, depth_h, color_h, f0, f1):
@@ -230,23 +233,45 @@ class HostFrameExchange:
                 self.uploaded[slot].record(self.copy_stream)
         self.bytes_uploaded += n * self.H * self.W * (2 + self.ch)
 
+    def _gather(self, slot):
+        def both():
+            self.dist.all_gather_into_tensor(self.gd[slot].view(torch.uint8).reshape(-1), self.ld[slot].view(torch.uint8).reshape(-1), group=self.group)
+            self.dist.all_gather_into_tensor(self.gc[slot].reshape(-1), self.lc[slot].reshape(-1), group=self.group)
+        if self.comm_stream is None:
+            both()
+            return
+        with torch.cuda.stream(self.comm_stream):
+            self.comm_stream.wait_event(self.uploaded[slot])
+            self.comm_stream.wait_event(self.released[slot])          # the consumer of this slot two rounds ago has read it
+            both()
+            self.consumed[slot].record(self.comm_stream)
+            self.gathered[slot].record(self.comm_stream)
+
     def run(self, depth_h: torch.Tensor, color_h: torch.Tensor, consume) -> None:
         """depth_h (F,H,W) uint16, color_h (F,H,W,ch) uint8 -- pinned host tensors (identical on every rank)."""
         plan = superchunk_plan(int(depth_h.shape[0]), self.world, self.per)
         if not plan:
             return
+        n = len(plan)
+        if self.comm_stream is not None:
+            # the buffers may still be read by work the caller enqueued earlier (a previous run's last consumers)
+            self.copy_stream.wait_stream(torch.cuda.current_stream())
+            self.comm_stream.wait_stream(torch.cuda.current_stream())
         self._upload(0, depth_h, color_h, *plan[0][2][self.rank])
+        if n > 1:
+            self._upload(1, depth_h, color_h, *plan[1][2][self.rank])
+        self._gather(0)
         for i, (f_start, n_valid, _) in enumerate(plan):
             slot = i & 1
-            if i + 1 < len(plan):
-                self._upload(slot ^ 1, depth_h, color_h, *plan[i + 1][2][self.rank])
-            if self.copy_stream is not None:
-                torch.cuda.current_stream().wait_event(self.uploaded[slot])
-            self.dist.all_gather_into_tensor(self.gd[slot].view(torch.uint8).reshape(-1), self.ld[slot].view(torch.uint8).reshape(-1), group=self.group)
-            self.dist.all_gather_into_tensor(self.gc[slot].reshape(-1), self.lc[slot].reshape(-1), group=self.group)
-            if self.copy_stream is not None:
-                self.consumed[slot].record(torch.cuda.current_stream())
+            if i + 1 < n:
+                self._gather(slot ^ 1)                                 # overlaps the integration of super-chunk i
+            if i + 2 < n:
+                self._upload(slot, depth_h, color_h, *plan[i + 2][2][self.rank])   # waits for gather i to have read the slot
+            if self.comm_stream is not None:
+                torch.cuda.current_stream().wait_event(self.gathered[slot])
             consume(self.gd[slot][:n_valid].view(torch.uint16), self.gc[slot][:n_valid], f_start, n_valid)
+            if self.comm_stream is not None:
+                self.released[slot].record(torch.cuda.current_stream())
 
 
 def integrate_host_frames(vol: ScalableTSDFVolume, depth_h: torch.Tensor, color_h: torch.Tensor, intrinsic, extrinsics,

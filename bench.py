@@ -311,6 +311,10 @@ def main():
         step_e2e()
     ms_e2e = timed(step_e2e, args.steps)
     fps_e2e = args.frames * args.steps / (ms_e2e * 1e-3)
+    st_e2e = vol.stats()
+    # the end-to-end arm must leave this rank's shard exactly as the device-resident arm did (same units, same voxel updates)
+    if (st_e2e["num_units"], st_e2e["updated_voxels"], st_e2e["errors"]) != (st["num_units"], st["updated_voxels"], st["errors"]):
+        raise RuntimeError("e2e arm diverged from the device arm: %r vs %r" % (st_e2e, st))
     h2d_bytes = int(depth_h.numel() * 2 + rgb_h.numel())
 
     # ---- CPU baseline (rank 0, bounded sample) ---------------------------------------------------------
