@@ -15,7 +15,7 @@ ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libb2recon.so")
 SOURCES = ["tsdf.cu", "unproject.cu", "extract.cu", "odometry.cu", "icp.cu", "pointcloud.cu", "posegraph.cu", "features.cu"]
-HEADERS = ["common.cuh", "host_math.h", "tsdf_internal.h", "mc_tables.h"]
+HEADERS = ["common.cuh", "host_math.h", "tsdf_internal.h", "mc_tables.h", "rigid_fit.cuh"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

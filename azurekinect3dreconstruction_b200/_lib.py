@@ -74,6 +74,7 @@ SIGNATURES = {
     "b2r_pcd_gather_rows": (_i, [_vp, _vp, _i64, _i, _i, _vp, _vp]),
     "b2r_pcd_voxel_down_sample": (_i, [_vp, _vp, _vp, _i64, _d, _vp, _vp, _vp, _vp, _i64, _pi64, _vp]),
     "b2r_pcd_bounds": (_i, [_vp, _i64, _pd, _vp]),
+    "b2r_icp_point_to_point": (_i, [_vp, _i64, _vp, _i64, _d, _pd, _i, _d, _d, _pd, _pd, _pd, _vp, _vp]),
     "b2r_icp_colored": (_i, [_vp, _vp, _i64, _vp, _vp, _vp, _i64, _d, _d, _pd, _i, _d, _d, _pd, _pd, _pd, _vp, _vp, _vp]),
     "b2r_compute_fpfh": (_i, [_vp, _vp, _i64, _i, _d, _vp, _vp]),
     "b2r_match_features": (_i, [_vp, _i64, _vp, _i64, _i, _vp, _vp]),

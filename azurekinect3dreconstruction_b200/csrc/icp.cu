@@ -15,6 +15,7 @@
 // The host only reads the final state.
 #include "common.cuh"
 #include "host_math.h"
+#include "rigid_fit.cuh"
 #include <cub/cub.cuh>
 #include <math.h>
 
@@ -201,6 +202,7 @@ struct IcpArgs {
     const double* tgt_int;       // M
     const double* tgt_grad;      // M*3: colour gradient on the target's tangent planes
     double sqrt_lg, sqrt_lp;     // sqrt(lambda_geometric), sqrt(1 - lambda_geometric)
+    int p2p;                     // TransformationEstimationPointToPoint: accumulate the cross-covariance sums instead of JtJ / Jtr
 };
 
 __global__ void __launch_bounds__(ICP_THREADS) icp_iter_kernel(const IcpArgs a) {
@@ -249,7 +251,22 @@ __global__ void __launch_bounds__(ICP_THREADS) icp_iter_kernel(const IcpArgs a) 
                     }
         }
         a.corr[i] = best;
-        if (best >= 0) {
+        if (best >= 0 && a.p2p) {
+            // sums for the closed-form rigid fit, taken about the grid origin (keeps sum s t^T - n ms mt^T well conditioned)
+            const double* t = a.tgt + 3 * best;
+            const double sc[3] = {xdsub(s[0], a.g.lo[0]), xdsub(s[1], a.g.lo[1]), xdsub(s[2], a.g.lo[2])};
+            const double tc[3] = {xdsub(t[0], a.g.lo[0]), xdsub(t[1], a.g.lo[1]), xdsub(t[2], a.g.lo[2])};
+#pragma unroll
+            for (int p = 0; p < 3; p++) {
+#pragma unroll
+                for (int q = 0; q < 3; q++) acc[3 * p + q] = xdadd(acc[3 * p + q], xdmul(sc[p], tc[q]));
+                acc[9 + p] = xdadd(acc[9 + p], sc[p]);
+                acc[12 + p] = xdadd(acc[12 + p], tc[p]);
+            }
+            acc[27] = xdadd(acc[27], bd);
+            acc[28] = xdadd(acc[28], bd);
+            acc[29] += 1.0;
+        } else if (best >= 0) {
             const double* t = a.tgt + 3 * best;
             const double* n = a.nrm + 3 * best;
             double r = xdadd(xdadd(xdmul(xdsub(s[0], t[0]), n[0]), xdmul(xdsub(s[1], t[1]), n[1])), xdmul(xdsub(s[2], t[2]), n[2]));
@@ -360,7 +377,19 @@ __global__ void __launch_bounds__(ICP_THREADS) icp_iter_kernel(const IcpArgs a) 
     if (done) { st->done = 1; return; }
     // TransformationEstimationPointToPlane::ComputeTransformation for the next iteration
     double U[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
-    if (n > 0.0) {
+    if (n > 0.0 && a.p2p) {
+        // TransformationEstimationPointToPoint::ComputeTransformation (no scaling): closed-form rigid fit of the pairs
+        double msr[3], mtr[3], ms[3], mt[3], S[3][3];
+        for (int p = 0; p < 3; p++) { msr[p] = xddiv(tot[9 + p], n); mtr[p] = xddiv(tot[12 + p], n); }
+        for (int p = 0; p < 3; p++)
+            for (int q = 0; q < 3; q++) S[p][q] = xdsub(tot[3 * p + q], xdmul(xdmul(n, msr[p]), mtr[q]));
+        for (int p = 0; p < 3; p++) { ms[p] = xdadd(msr[p], a.g.lo[p]); mt[p] = xdadd(mtr[p], a.g.lo[p]); }
+        double Tn[16];
+        horn_from_covariance(S, ms, mt, Tn);
+        bool fin = true;
+        for (int i = 0; i < 16; i++) fin = fin && isfinite(Tn[i]);
+        if (fin) for (int i = 0; i < 16; i++) U[i] = Tn[i];
+    } else if (n > 0.0) {
         double A[36], nb[6], x[6];
         int q = 0;
         for (int p = 0; p < 6; p++) for (int r = p; r < 6; r++) { A[p * 6 + r] = tot[q]; A[r * 6 + p] = tot[q]; q++; }
@@ -392,13 +421,16 @@ inline size_t al(size_t v) { return (v + 255) & ~(size_t)255; }
 }  // namespace
 
 struct IcpColor { const double* src_int; const double* tgt_int; const double* tgt_grad; double lambda_geometric; };
+static const IcpColor kPointToPoint = {nullptr, nullptr, nullptr, -1.0};     // marker: point-to-point estimation
 
 static int icp_run(const double* src_xyz, int64_t N, const double* tgt_xyz, const double* tgt_nrm, int64_t M,
                    double max_dist, const double* init_host, int max_iter, double rel_fitness,
                    double rel_rmse, double* out_T_host, double* fitness_host, double* rmse_host,
                    int32_t* corr, const IcpColor* color, cudaStream_t stream) {
     if (!(max_dist > 0.0)) { b2r_set_error("[RegistrationICP] Invalid max_correspondence_distance."); return B2R_ERR_BAD_ARG; }
-    if (!tgt_nrm) { b2r_set_error(color ? "ColoredICP requires target pointcloud to have normals." : "[RegistrationICP] TransformationEstimationPointToPlane requires target normals."); return B2R_ERR_FORMAT; }
+    const bool p2p = color == &kPointToPoint;
+    if (p2p) color = nullptr;
+    if (!tgt_nrm && !p2p) { b2r_set_error(color ? "ColoredICP requires target pointcloud to have normals." : "[RegistrationICP] TransformationEstimationPointToPlane requires target normals."); return B2R_ERR_FORMAT; }
     if (!src_xyz || !tgt_xyz || !init_host || !out_T_host || !fitness_host || !rmse_host || N < 0 || M < 0 || max_iter < 0 ||
         N > 0x7fffffff || M > 0x7fffffff) {
         b2r_set_error("b2r_icp_point_to_plane: bad argument");
@@ -464,6 +496,7 @@ static int icp_run(const double* src_xyz, int64_t N, const double* tgt_xyz, cons
     a.g = g; a.max_dist = max_dist; a.corr = (int32_t*)(b + o_corr); a.partials = (double*)(b + o_part); a.st = st;
     a.max_iter = max_iter; a.rel_fitness = rel_fitness; a.rel_rmse = rel_rmse;
     a.colored = color ? 1 : 0;
+    a.p2p = p2p ? 1 : 0;
     a.src_int = color ? color->src_int : nullptr; a.tgt_int = color ? color->tgt_int : nullptr; a.tgt_grad = color ? color->tgt_grad : nullptr;
     a.sqrt_lg = color ? sqrt(color->lambda_geometric) : 1.0; a.sqrt_lp = color ? sqrt(1.0 - color->lambda_geometric) : 0.0;
     for (int k = 0; k <= max_iter; k++) {
@@ -492,6 +525,15 @@ B2R_API int b2r_icp_point_to_plane(const double* src_xyz, int64_t N, const doubl
                                    int32_t* corr, cudaStream_t stream) {
     return icp_run(src_xyz, N, tgt_xyz, tgt_nrm, M, max_dist, init_host, max_iter, rel_fitness, rel_rmse, out_T_host, fitness_host,
                    rmse_host, corr, nullptr, stream);
+}
+
+// registration_icp with TransformationEstimationPointToPoint(with_scaling=False)
+// (CodeThatWorks/Works2CamerasCOLORVisualizer.py:252-257, CodeThatKindaWorks/BetterVisualizerD2cameras.py:248-253).
+B2R_API int b2r_icp_point_to_point(const double* src_xyz, int64_t N, const double* tgt_xyz, int64_t M, double max_dist,
+                                   const double* init_host, int max_iter, double rel_fitness, double rel_rmse, double* out_T_host,
+                                   double* fitness_host, double* rmse_host, int32_t* corr, cudaStream_t stream) {
+    return icp_run(src_xyz, N, tgt_xyz, nullptr, M, max_dist, init_host, max_iter, rel_fitness, rel_rmse, out_T_host, fitness_host,
+                   rmse_host, corr, &kPointToPoint, stream);
 }
 
 // ------------------------------------------------------------------------------------------------

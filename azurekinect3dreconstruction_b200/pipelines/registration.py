@@ -60,9 +60,12 @@ def registration_icp(source: PointCloud, target: PointCloud, max_correspondence_
     criteria = criteria or ICPConvergenceCriteria()
     if max_correspondence_distance <= 0.0:
         raise RuntimeError("[RegistrationICP] Invalid max_correspondence_distance.")
-    if not isinstance(estimation_method, TransformationEstimationPointToPlane):
-        raise RuntimeError("registration_icp: only TransformationEstimationPointToPlane is on the B200 hot path")
-    if not target.has_normals():
+    p2p = isinstance(estimation_method, TransformationEstimationPointToPoint)
+    if p2p and estimation_method.with_scaling:
+        raise RuntimeError("registration_icp: TransformationEstimationPointToPoint(with_scaling=True) is not built (the reference never scales)")
+    if not p2p and not isinstance(estimation_method, TransformationEstimationPointToPlane):
+        raise RuntimeError("registration_icp: TransformationEstimationPointToPoint / PointToPlane expected (coloured ICP: registration_colored_icp)")
+    if not p2p and not target.has_normals():
         raise RuntimeError("[RegistrationICP] TransformationEstimationPointToPlane and TransformationEstimationColoredICP require pre-computed normal vectors for target PointCloud.")
     _lib.require_cuda()
     init = np.eye(4) if init is None else np.asarray(init, dtype=np.float64)
@@ -70,10 +73,16 @@ def registration_icp(source: PointCloud, target: PointCloud, max_correspondence_
     corr = torch.empty((max(N, 1),), dtype=torch.int32, device=source.points.tensor.device)
     T = (C.c_double * 16)()
     fit, rmse = C.c_double(0), C.c_double(0)
-    rc = _lib.load().b2r_icp_point_to_plane(_lib.ptr(source.points.tensor), N, _lib.ptr(target.points.tensor), _lib.ptr(target.normals.tensor), M,
-                                            float(max_correspondence_distance), _lib.dbl16(init), criteria.max_iteration,
-                                            criteria.relative_fitness, criteria.relative_rmse, T, C.byref(fit), C.byref(rmse),
-                                            _lib.ptr(corr), _lib.stream_ptr())
+    if p2p:
+        rc = _lib.load().b2r_icp_point_to_point(_lib.ptr(source.points.tensor), N, _lib.ptr(target.points.tensor), M,
+                                                float(max_correspondence_distance), _lib.dbl16(init), criteria.max_iteration,
+                                                criteria.relative_fitness, criteria.relative_rmse, T, C.byref(fit), C.byref(rmse),
+                                                _lib.ptr(corr), _lib.stream_ptr())
+    else:
+        rc = _lib.load().b2r_icp_point_to_plane(_lib.ptr(source.points.tensor), N, _lib.ptr(target.points.tensor), _lib.ptr(target.normals.tensor), M,
+                                                float(max_correspondence_distance), _lib.dbl16(init), criteria.max_iteration,
+                                                criteria.relative_fitness, criteria.relative_rmse, T, C.byref(fit), C.byref(rmse),
+                                                _lib.ptr(corr), _lib.stream_ptr())
     _lib.check(rc, "registration_icp")
     res = RegistrationResult()
     res.transformation = np.array(T[:], dtype=np.float64).reshape(4, 4)

@@ -190,6 +190,12 @@ int b2r_icp_point_to_plane(const double* src_xyz, int64_t N, const double* tgt_x
                            double rel_rmse, double* out_T_host, double* fitness_host, double* rmse_host,
                            int32_t* corr, cudaStream_t stream);
 
+/* registration_icp with TransformationEstimationPointToPoint(False) (Works2CamerasCOLORVisualizer.py:252-257): the same
+ * on-device loop, update = closed-form rigid fit (Horn) of the correspondences.  No normals needed. */
+int b2r_icp_point_to_point(const double* src_xyz, int64_t N, const double* tgt_xyz, int64_t M, double max_dist,
+                           const double* init_host, int max_iter, double rel_fitness, double rel_rmse, double* out_T_host,
+                           double* fitness_host, double* rmse_host, int32_t* corr, cudaStream_t stream);
+
 /* ---- f4 (part): o3d.pipelines.registration.registration_colored_icp(src, tgt, max_dist, init,
  *      TransformationEstimationForColoredICP(), ICPConvergenceCriteria(...))  (GoodColorReconstruction.py:246-254).
  *      DEVICE f64 arrays, colours in [0, 1]; the target's colour gradients (SearchHybrid(2 * max_dist, 30) neighbours) are

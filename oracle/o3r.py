@@ -59,6 +59,7 @@ def lib():
     L.o3r_correspondence.restype = _i64
     L.o3r_correspondence.argtypes = [_vp, _vp, _i, _i, _d, _d, _d, _d, _vp, _d, _vp, _i64]
     L.o3r_icp_point_to_plane.argtypes = [_vp, _i64, _vp, _vp, _i64, _d, _vp, _i, _d, _d, _vp, C.POINTER(C.c_double), C.POINTER(C.c_double), _vp]
+    L.o3r_icp_point_to_point.argtypes = [_vp, _i64, _vp, _i64, _d, _vp, _i, _d, _d, _vp, C.POINTER(C.c_double), C.POINTER(C.c_double), _vp]
     L.o3r_icp_colored.argtypes = [_vp, _vp, _i64, _vp, _vp, _vp, _i64, _d, _d, _vp, _i, _d, _d, _vp, C.POINTER(C.c_double), C.POINTER(C.c_double), _vp, _vp]
     L.o3r_color_gradient.argtypes = [_vp, _vp, _vp, _i64, _d, _i, _vp]
     L.o3r_pcd_search.argtypes = [_vp, _i64, _vp, _i64, _i, _d, _vp, _vp, _vp]
@@ -262,6 +263,19 @@ def icp_point_to_plane(src, tgt, tgt_nrm, max_dist, init=None, max_iter=30, rel_
     fit, rmse = C.c_double(0), C.c_double(0)
     corr = np.empty((s.shape[0],), np.int32)
     it = lib().o3r_icp_point_to_plane(_p(s), s.shape[0], _p(t), _p(n), t.shape[0], max_dist, _p(init), max_iter, rel_fitness, rel_rmse,
+                                      _p(T), C.byref(fit), C.byref(rmse), _p(corr))
+    if it < 0:
+        raise RuntimeError("[RegistrationICP] invalid arguments (%d)" % it)
+    return T, float(fit.value), float(rmse.value), corr, int(it)
+
+
+def icp_point_to_point(src, tgt, max_dist, init=None, max_iter=30, rel_fitness=1e-6, rel_rmse=1e-6):
+    s, t = _f64(src), _f64(tgt)
+    init = _f64(np.eye(4) if init is None else init)
+    T = np.empty((4, 4))
+    fit, rmse = C.c_double(0), C.c_double(0)
+    corr = np.empty((s.shape[0],), np.int32)
+    it = lib().o3r_icp_point_to_point(_p(s), s.shape[0], _p(t), t.shape[0], max_dist, _p(init), max_iter, rel_fitness, rel_rmse,
                                       _p(T), C.byref(fit), C.byref(rmse), _p(corr))
     if it < 0:
         raise RuntimeError("[RegistrationICP] invalid arguments (%d)" % it)

@@ -1198,6 +1198,48 @@ O3R_API int o3r_icp_point_to_plane(const double* src_xyz, int64_t N, const doubl
     return it;
 }
 
+// registration_icp with TransformationEstimationPointToPoint(false) (Works2CamerasCOLORVisualizer.py:252-257): same loop, the
+// update is the rigid least-squares fit of the correspondences (upstream: Eigen::umeyama; here Horn's closed form, two-pass).
+extern "C" void o3r_horn_rigid(const double* s, const double* t, int n, double* T);
+
+O3R_API int o3r_icp_point_to_point(const double* src_xyz, int64_t N, const double* tgt_xyz, int64_t M, double max_dist, const double* init,
+                                   int max_iter, double rel_fitness, double rel_rmse, double* out_T, double* out_fitness, double* out_rmse,
+                                   int32_t* corr_out) {
+    if (max_dist <= 0.0) return -1;
+    M4 T;
+    std::memcpy(T.m, init, sizeof(T.m));
+    std::vector<double> pcd(src_xyz, src_xyz + 3 * N);
+    o3r_transform_points(pcd.data(), N, T.m, nullptr);
+    Grid g;
+    g.build(tgt_xyz, M, max_dist);
+    std::vector<int32_t> corr;
+    IcpEval res = icp_evaluate(pcd, g, max_dist, corr);
+    int it = 0;
+    std::vector<double> ps, pt;
+    for (; it < max_iter; it++) {
+        M4 U = m4_identity();
+        if (res.n > 0) {
+            ps.clear(); pt.clear();
+            for (int64_t i = 0; i < N; i++) {
+                if (corr[i] < 0) continue;
+                for (int c = 0; c < 3; c++) { ps.push_back(pcd[3 * i + c]); pt.push_back(tgt_xyz[3 * (int64_t)corr[i] + c]); }
+            }
+            o3r_horn_rigid(ps.data(), pt.data(), (int)(ps.size() / 3), U.m);
+            for (int k = 0; k < 16; k++) if (!std::isfinite(U.m[k])) { U = m4_identity(); break; }
+        }
+        T = m4_mul(U, T);
+        o3r_transform_points(pcd.data(), N, U.m, nullptr);
+        IcpEval prev = res;
+        res = icp_evaluate(pcd, g, max_dist, corr);
+        if (std::fabs(prev.fitness - res.fitness) < rel_fitness && std::fabs(prev.rmse - res.rmse) < rel_rmse) { it++; break; }
+    }
+    std::memcpy(out_T, T.m, sizeof(T.m));
+    *out_fitness = res.fitness;
+    *out_rmse = res.rmse;
+    if (corr_out) std::memcpy(corr_out, corr.data(), sizeof(int32_t) * N);
+    return it;
+}
+
 // ---- f4: registration_colored_icp (GoodColorReconstruction.py:246-254) ------------------------------------------------
 // Open3D 0.19 pipelines/registration/ColoredICP.cpp: InitializePointCloudForColoredICP (colour gradient per target point from
 // its SearchHybrid(2 * max_dist, 30) neighbours, least squares on the tangent plane + orthogonality row) and

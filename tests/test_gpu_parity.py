@@ -582,6 +582,16 @@ def test_icp_parity(o3r, frames, small_kinect):
     cs = np.asarray(res.correspondence_set)
     ref_pairs = np.stack([np.flatnonzero(corr_r >= 0), corr_r[corr_r >= 0]], 1)
     assert np.array_equal(cs, ref_pairs)                                     # nearest-neighbour result: bit-exact
+    # TransformationEstimationPointToPoint (Works2CamerasCOLORVisualizer.py:252-257): no normals needed
+    bare_t = o3d.geometry.PointCloud(tgt)
+    rq = o3d.pipelines.registration.registration_icp(s, bare_t, 0.03, init, o3d.pipelines.registration.TransformationEstimationPointToPoint(), crit)
+    Tq, fitq, rmseq, corrq, itq = o3r.icp_point_to_point(src, tgt, 0.03, init, max_iter=40)
+    assert rq.num_iterations == itq
+    assert np.abs(rq.transformation[:3, 3] - Tq[:3, 3]).max() <= 1e-6 and rot_angle(rq.transformation[:3, :3] @ Tq[:3, :3].T) <= 1e-6
+    assert abs(rq.fitness - fitq) <= 1e-9 and abs(rq.inlier_rmse - rmseq) <= 1e-9
+    assert np.array_equal(np.asarray(rq.correspondence_set), np.stack([np.flatnonzero(corrq >= 0), corrq[corrq >= 0]], 1))
+    with pytest.raises(RuntimeError, match="with_scaling"):
+        o3d.pipelines.registration.registration_icp(s, bare_t, 0.03, init, o3d.pipelines.registration.TransformationEstimationPointToPoint(True), crit)
     t2 = o3d.geometry.PointCloud(tgt)
     with pytest.raises(RuntimeError, match="normal"):
         o3d.pipelines.registration.registration_icp(s, t2, 0.03, init, o3d.pipelines.registration.TransformationEstimationPointToPlane())

@@ -332,6 +332,13 @@ def test_icp_recovers_inverse_motion(o3r):
         o3r.icp_point_to_plane(src, tgt, nrm, 0.0)
     with pytest.raises(RuntimeError):
         o3r.icp_point_to_plane(src, tgt, None, 0.05)
+    # TransformationEstimationPointToPoint: same loop, closed-form rigid fit per iteration (slower convergence, same fixed point)
+    Tq, fitq, rmseq, corrq, itq = o3r.icp_point_to_point(src, tgt, 0.05, max_iter=200)
+    assert fitq > 0.99 and 1 <= itq <= 200
+    np.testing.assert_allclose(Tq @ M, np.eye(4), atol=5e-3)
+    np.testing.assert_allclose(Tq[:3, :3] @ Tq[:3, :3].T, np.eye(3), atol=1e-12)
+    with pytest.raises(RuntimeError):
+        o3r.icp_point_to_point(src, tgt, -1.0)
     # nothing within reach: identity update, fitness 0
     T0, fit0, rmse0, _, _ = o3r.icp_point_to_plane(src + 100.0, tgt, nrm, 0.05, max_iter=5)
     assert fit0 == 0.0 and rmse0 == 0.0 and np.array_equal(T0, np.eye(4))
