@@ -258,6 +258,12 @@ class PointCloud:
         self.__init__()
         return self
 
+    def paint_uniform_color(self, color):
+        """PointCloud::PaintUniformColor (the reference tints each camera's cloud, BetterVisualizer2CamWorksCOLOR.py)."""
+        c = torch.as_tensor(np.asarray(color, dtype=np.float64).reshape(3), dtype=torch.float64, device=self._points.tensor.device)
+        self._colors = Vector3dVector(c.expand(len(self._points), 3).contiguous())
+        return self
+
     # ---- factories ---------------------------------------------------------------------------------
     @staticmethod
     def create_from_rgbd_image(image: RGBDImage, intrinsic: PinholeCameraIntrinsic, extrinsic=_IDENTITY,
@@ -517,6 +523,12 @@ class TriangleMesh:
 
     def is_empty(self):
         return not self.has_vertices()
+
+    def paint_uniform_color(self, color):
+        """TriangleMesh::PaintUniformColor"""
+        c = torch.as_tensor(np.asarray(color, dtype=np.float64).reshape(3), dtype=torch.float64, device=self._vertices.tensor.device)
+        self._vertex_colors = Vector3dVector(c.expand(len(self._vertices), 3).contiguous())
+        return self
 
     def compute_vertex_normals(self, normalized: bool = True) -> "TriangleMesh":
         """TriangleMesh::ComputeVertexNormals (GoodColorReconstruction.py:286; SURVEY A.5)."""

@@ -129,6 +129,13 @@ def test_pointcloud_merge_semantics_and_vectors():
     assert m.is_empty() and not m.has_triangles()
     crit = o3d.pipelines.registration.ICPConvergenceCriteria(max_iteration=100)
     assert (crit.relative_fitness, crit.relative_rmse, crit.max_iteration) == (1e-6, 1e-6, 100)
+    # paint_uniform_color (every two-camera script tints its clouds), RANSAC criteria clamping, checker classes
+    assert a.paint_uniform_color([1, 0.706, 0]) is a and np.array_equal(np.asarray(a.colors), np.tile([1, 0.706, 0], (3, 1)))
+    R = o3d.pipelines.registration
+    assert R.RANSACConvergenceCriteria(4000000, 500).confidence == 1.0 and R.RANSACConvergenceCriteria().max_iteration == 100000
+    assert R.CorrespondenceCheckerBasedOnEdgeLength(0.9).similarity_threshold == 0.9
+    assert R.TransformationEstimationForColoredICP().lambda_geometric == 0.968
+    assert R.GlobalOptimizationOption().reference_node == -1 and R.PoseGraphEdge().confidence == 1.0
 
 
 def test_marching_cubes_tables_are_valid():
