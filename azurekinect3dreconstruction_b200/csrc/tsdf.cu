@@ -80,7 +80,7 @@ struct PackFrame {
     const void* depth;        // u16 or f32, W*H
     const uint8_t* color;     // u8, channels 3|4 (may be null)
     const float* gray;        // f32 intensity (Gray32), may be null
-    float4* texel;
+    float2* texel;
     double pose[12];          // extrinsic^-1, rows 0..2
     uint32_t bit;             // 1 << (index of the frame in the pending batch)
     uint32_t pad;
@@ -247,7 +247,6 @@ __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(con
         const int base = (bidx * (int)(blockDim.x >> 5) + (int)(threadIdx.x >> 5)) * (32 * PACK_PX) + lane;
         if (base - lane >= npx) return;
         uint32_t dv[PACK_PX], cv[PACK_PX];
-        float m[PACK_PX];
         const bool full = base - lane + 32 * PACK_PX <= npx;
         if (P.tma_ok) {
             // The tile's depth, colour and multiplier bytes arrive by three TMA bulk copies (one elected thread, one
@@ -261,14 +260,12 @@ __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(con
             const uint32_t cbytes = F.color ? (uint32_t)P.color_channels : (F.gray ? 4u : 0u);
             unsigned char* s_d = k1_smem;
             unsigned char* s_c = k1_smem + PACK_TILE * 4;
-            float* s_m = reinterpret_cast<float*>(k1_smem + PACK_TILE * 8);
             if (threadIdx.x == 0) {
                 mbar_init(&tile_bar, 1);
                 asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-                mbar_expect_tx(&tile_bar, (uint32_t)tpx * (dbytes + cbytes + 4u));
+                mbar_expect_tx(&tile_bar, (uint32_t)tpx * (dbytes + cbytes));
                 tma_load_1d(s_d, (const unsigned char*)F.depth + (size_t)tile0 * dbytes, (uint32_t)tpx * dbytes, &tile_bar);
                 if (cbytes) tma_load_1d(s_c, (F.color ? (const unsigned char*)F.color : (const unsigned char*)F.gray) + (size_t)tile0 * cbytes, (uint32_t)tpx * cbytes, &tile_bar);
-                tma_load_1d(s_m, P.mult + tile0, (uint32_t)tpx * 4u, &tile_bar);
             }
             __syncthreads();                 // the barrier's initialisation is visible to the waiters
             mbar_wait(&tile_bar, 0);
@@ -277,7 +274,6 @@ __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(con
             for (int k = 0; k < PACK_PX; k++) {
                 const int li = min(l0 + 32 * k, tpx - 1);
                 dv[k] = P.depth_is_u16 ? (uint32_t)reinterpret_cast<const uint16_t*>(s_d)[li] : reinterpret_cast<const uint32_t*>(s_d)[li];
-                m[k] = s_m[li];
                 if (cbytes == 4u) cv[k] = reinterpret_cast<const uint32_t*>(s_c)[li];
                 else if (cbytes == 3u) cv[k] = (uint32_t)s_c[3 * li] | ((uint32_t)s_c[3 * li + 1] << 8) | ((uint32_t)s_c[3 * li + 2] << 16);
                 else cv[k] = 0u;
@@ -287,7 +283,6 @@ __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(con
         for (int k = 0; k < PACK_PX; k++) {
             const int idx = full ? base + 32 * k : min(base + 32 * k, npx - 1);
             dv[k] = P.depth_is_u16 ? (uint32_t)__ldg((const uint16_t*)F.depth + idx) : __float_as_uint(__ldg((const float*)F.depth + idx));
-            m[k] = __ldg(P.mult + idx);
             if (F.color) {
                 if (P.color_channels == 4) {
                     cv[k] = __ldg(reinterpret_cast<const uint32_t*>(F.color) + idx);      // 0x..BBGGRR in memory order: byte 0 = channel 0
@@ -308,7 +303,7 @@ __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(con
             const int idx = base + 32 * k;
             const float d = P.depth_is_u16 ? depth_from_u16(P, dv[k]) : __uint_as_float(dv[k]);
             const uint32_t c = F.color ? __byte_perm(cv[k], 0, sel) : cv[k];
-            if (full || idx < npx) F.texel[idx] = make_float4(d, m[k], __uint_as_float(c), 0.0f);
+            if (full || idx < npx) F.texel[idx] = make_float2(d, __uint_as_float(c));
         }
         return;
     }
@@ -436,17 +431,15 @@ __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(con
 // ------------------------------------------------------------------------------------------------
 // K2: fuse
 // ------------------------------------------------------------------------------------------------
-#define FUSE_THREADS 256
 #ifndef FUSE_MIN_CTAS
 #define FUSE_MIN_CTAS 4   // 64 registers/thread: 32 resident warps per SM (measured best; 3 and 5 are slower)
 #endif
-#define FUSE_MAX_ITEMS 64          // work items resolved per CTA per chunk
-#define FUSE_SLAB 1024             // floats per plane per slab (4 x-layers x 16 x 16)
 
 struct FuseParams {
     int nframes;
     int q;                   // batch buffer being fused; (q+2)%3 = previous batch (its masks get cleared),
                              // (q+1)%3 = next batch (its counter gets zeroed)
+    int ring_rounds;         // passes with at least this many items per CTA run the prefetching ring
     int reverse;             // sweep direction (alternates per batch: the tail of the last sweep is still in L2)
     float vl, hv, trunc, inv_trunc;
     double unit_length;
@@ -460,19 +453,19 @@ struct FuseParams {
     B2RFrame fr[B2R_MAX_BATCH];
 };
 
-template <int COLOR, int FUSE_STAGES>
-__global__ void __launch_bounds__(FUSE_THREADS, FUSE_MIN_CTAS) tsdf_fuse_kernel(const __grid_constant__ FuseParams P) {
+template <int COLOR, int FUSE_STAGES, int XL>
+__global__ void __launch_bounds__(64 * XL, FUSE_MIN_CTAS * 4 / XL) tsdf_fuse_kernel(const __grid_constant__ FuseParams P) {
     constexpr int PLANES = COLOR ? 5 : 2;
+    // XL = x-layers per work item (4: 256 threads, 4 items per unit; 2: 128 threads, 8 items per unit -- the finer
+    // quantum keeps a sharded rank's short passes balanced over the persistent grid)
+    constexpr int FUSE_THREADS = 64 * XL, FUSE_SLAB = 256 * XL, IS = XL == 4 ? 2 : 3, IM = (1 << IS) - 1;
     extern __shared__ __align__(128) unsigned char fuse_smem[];
     float* stage = reinterpret_cast<float*>(fuse_smem);                        // [FUSE_STAGES][PLANES][FUSE_SLAB]
     __shared__ __align__(8) uint64_t full_bar[FUSE_STAGES];
-    __shared__ int s_unit[FUSE_MAX_ITEMS];
-    __shared__ uint32_t s_mask[FUSE_MAX_ITEMS];
-    __shared__ int s_key[FUSE_MAX_ITEMS][3];
 
     const int tid = threadIdx.x;
     const int T = min(P.counters[B2R_C_TOUCHED0 + P.q], P.cap_units);
-    const int nwork = T * 4;
+    const int nwork = T << IS;
 
     // ---- housekeeping for the rotating batch buffers
     {
@@ -481,6 +474,7 @@ __global__ void __launch_bounds__(FUSE_THREADS, FUSE_MIN_CTAS) tsdf_fuse_kernel(
         for (int i = blockIdx.x * FUSE_THREADS + tid; i < Tp; i += gridDim.x * FUSE_THREADS) P.slots[P.touched_prev[i]].mask[qp] = 0u;
         if (blockIdx.x == 0 && tid == 0) {
             P.counters[B2R_C_TOUCHED0 + (P.q + 1) % 3] = 0;
+            P.counters[B2R_C_WORK0 + (P.q + 1) % 3] = 0;   // the next pass draws its items from a fresh counter
             P.counters[B2R_C_LAST_TOUCHED] = T;
         }
     }
@@ -493,49 +487,63 @@ __global__ void __launch_bounds__(FUSE_THREADS, FUSE_MIN_CTAS) tsdf_fuse_kernel(
     unsigned int upd = 0, pairs = 0;
     uint32_t it_seq = 0;   // items issued through the ring so far by this CTA (stage = seq % STAGES)
 
-    const int my_items = (nwork > (int)blockIdx.x) ? (nwork - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
-    for (int chunk0 = 0; chunk0 < my_items; chunk0 += FUSE_MAX_ITEMS) {
-        const int n_it = min(FUSE_MAX_ITEMS, my_items - chunk0);
-        __syncthreads();   // previous chunk fully consumed (info arrays + ring are free); barriers initialised
-        // ---- resolve this chunk's work items in parallel: touched -> slot {key, unit, mask}
-        if (tid < n_it) {
-            int w = (int)blockIdx.x + (chunk0 + tid) * (int)gridDim.x;
-            if (P.reverse) w = nwork - 1 - w;
-            const B2RSlot* slot = &P.slots[P.touched[w >> 2]];
+    // ---- dynamic work distribution: items differ in cost (1..16 frames each), so CTAs draw items from a counter as they
+    // finish instead of owning a fixed stride of the list.  Long passes (>= ring_rounds items per CTA) run the TMA ring:
+    // the next item is claimed and in flight while the current one is fused, and thread 0 also pre-claims the index and
+    // touched-list entry of the item after that (consumed one fetch later, so a fetch waits for ONE L2 round trip) -- but
+    // only while the list is far from its end, so the tail is not hoarded.  Short passes (a sharded rank sees ~2 items
+    // per CTA) claim strictly one item at a time: balance matters more there than the exposed load, which the other
+    // resident CTAs of the SM cover.
+    __shared__ int s_us[FUSE_STAGES];            // per ring stage: (unit << IS) | slab, or -1 = the list is exhausted
+    __shared__ uint32_t s_fm[FUSE_STAGES];
+    __shared__ int s_k[FUSE_STAGES][3];
+    int* const work_ctr = &P.counters[B2R_C_WORK0 + P.q];
+    const bool ring = nwork >= P.ring_rounds * (int)gridDim.x;
+    const int look_end = ring ? nwork - 3 * (int)gridDim.x : 0;   // pre-claim only items before this index
+    int w1 = -1, sl1 = 0;                        // thread 0: pre-claimed item (-1 = none) and its slot index
+    auto fetch = [&](uint32_t st) {              // thread 0: next live item -> stage st (info + TMA), or -1
+        for (;;) {
+            int cw = w1, csl = sl1;
+            w1 = -1;
+            if (cw < 0) {
+                cw = atomicAdd(work_ctr, 1);
+                if (cw < nwork) csl = __ldcg(&P.touched[(P.reverse ? nwork - 1 - cw : cw) >> IS]);
+            }
+            if (cw >= nwork) { s_us[st] = -1; return; }
+            const B2RSlot* slot = &P.slots[csl];
             const uint4 lo = __ldcg(reinterpret_cast<const uint4*>(slot));
             const uint4 hi = __ldcg(reinterpret_cast<const uint4*>(slot) + 1);
-            const uint64_t key = ((uint64_t)lo.y << 32) | lo.x;
-            int kx, ky, kz;
-            b2r_unpack_key(key, kx, ky, kz);
-            s_unit[tid] = (int)lo.z;
-            s_mask[tid] = ((int)lo.z < 0) ? 0u : (P.q == 0 ? lo.w : (P.q == 1 ? hi.x : hi.y));
-            s_key[tid][0] = kx; s_key[tid][1] = ky; s_key[tid][2] = kz;
-            // slab index rides in the top bits of the unit word
-            s_unit[tid] = ((int)lo.z < 0) ? -1 : (((int)lo.z << 2) | (w & 3));
-        }
-        __syncthreads();
-        // ---- prologue: fill the ring
-        if (tid == 0) {
-            for (int i = 0; i < min(FUSE_STAGES, n_it); i++) {
-                const uint32_t st = (it_seq + i) % FUSE_STAGES;
-                const int us = s_unit[i];
-                if (us >= 0 && s_mask[i]) {
-                    const float* src = P.pool + (int64_t)(us >> 2) * P.unit_stride + (us & 3) * FUSE_SLAB;
-                    mbar_expect_tx(&full_bar[st], PLANES * FUSE_SLAB * 4);
-#pragma unroll
-                    for (int pl = 0; pl < PLANES; pl++) tma_load_1d(stage + (st * PLANES + pl) * FUSE_SLAB, src + pl * B2R_UNIT_VOX, FUSE_SLAB * 4, &full_bar[st]);
-                } else {
-                    mbar_expect_tx(&full_bar[st], 0);   // skipped item: keep the stage's phase in step
-                }
+            if (cw < look_end) {
+                w1 = atomicAdd(work_ctr, 1);
+                if (w1 < nwork) sl1 = __ldcg(&P.touched[(P.reverse ? nwork - 1 - w1 : w1) >> IS]);
             }
+            const uint32_t m = P.q == 0 ? lo.w : (P.q == 1 ? hi.x : hi.y);
+            if ((int)lo.z < 0 || m == 0u) continue;    // unit without storage (pool overflow) or nothing pending
+            const int w = P.reverse ? nwork - 1 - cw : cw;
+            int kx, ky, kz;
+            b2r_unpack_key(((uint64_t)lo.y << 32) | lo.x, kx, ky, kz);
+            s_us[st] = ((int)lo.z << IS) | (w & IM); s_fm[st] = m;
+            s_k[st][0] = kx; s_k[st][1] = ky; s_k[st][2] = kz;
+            const float* src = P.pool + (int64_t)(int)lo.z * P.unit_stride + (w & IM) * FUSE_SLAB;
+            mbar_expect_tx(&full_bar[st], PLANES * FUSE_SLAB * 4);
+#pragma unroll
+            for (int pl = 0; pl < PLANES; pl++) tma_load_1d(stage + (st * PLANES + pl) * FUSE_SLAB, src + pl * B2R_UNIT_VOX, FUSE_SLAB * 4, &full_bar[st]);
+            return;
         }
-        for (int it = 0; it < n_it; it++, it_seq++) {
+    };
+    if (tid == 0) {
+        for (int s = 0; s < (ring ? FUSE_STAGES : 1); s++) fetch(s);
+    }
+    __syncthreads();   // barriers initialised, first items published
+    {
+        for (;; it_seq++) {
             const uint32_t st = it_seq % FUSE_STAGES;
-            const int us = s_unit[it];
-            const uint32_t fmask = s_mask[it];
-            if (us >= 0 && fmask) {
-                const int unit = us >> 2, x = ((us & 3) << 2) + xl;
-                const int kx = s_key[it][0], ky = s_key[it][1], kz = s_key[it][2];
+            const int us = s_us[st];
+            if (us < 0) break;
+            const uint32_t fmask = s_fm[st];
+            {
+                const int unit = us >> IS, x = (us & IM) * XL + xl;
+                const int kx = s_k[st][0], ky = s_k[st][1], kz = s_k[st][2];
                 // voxel-centre column base: float(hv + vl*x + origin.x) with the f32->f64 promotion of upstream
                 const float px = (float)xdadd((double)xfadd(P.hv, xfmul(P.vl, (float)x)), xdmul((double)kx, P.unit_length));
                 const float py = (float)xdadd((double)xfadd(P.hv, xfmul(P.vl, (float)y)), xdmul((double)ky, P.unit_length));
@@ -556,7 +564,7 @@ __global__ void __launch_bounds__(FUSE_THREADS, FUSE_MIN_CTAS) tsdf_fuse_kernel(
                 float* gp = reinterpret_cast<float*>(&gs);
                 float* bp = reinterpret_cast<float*>(&bs);
                 const unsigned upd0 = upd;
-                pairs += (tid == 0 && (us & 3) == 0) ? __popc(fmask) : 0;
+                pairs += (tid == 0 && (us & IM) == 0) ? __popc(fmask) : 0;
                 for (uint32_t fm = fmask; fm; fm &= fm - 1) {
                     const B2RFrame& F = P.fr[__ffs(fm) - 1];
                     float pcx = xfadd(xfadd(xfadd(xfmul(F.E[0], px), xfmul(F.E[1], py)), xfmul(F.E[2], pz)), F.E[3]);
@@ -573,11 +581,13 @@ __global__ void __launch_bounds__(FUSE_THREADS, FUSE_MIN_CTAS) tsdf_fuse_kernel(
                     }
                     // pass 1: project the 4 voxels, issue the 4 texel gathers together
                     float zc[4];
-                    float4 tx[4];
+                    float2 tx[4];
+                    float mk[4];
 #pragma unroll
                     for (int k = 0; k < 4; k++) {
                         zc[k] = pcz;
-                        tx[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        tx[k] = make_float2(0.f, 0.f);
+                        mk[k] = 0.f;
                         if (pcz > 0.0f) {
                             // u_f = pc.x*fx/pc.z + cx + 0.5f, v_f likewise: both quotients share RN(1/pc.z).
                             // Outside b2r_div_domain (pc.z < 2^-60, ...) take div.rn.  Inside it the Markstein
@@ -594,7 +604,11 @@ __global__ void __launch_bounds__(FUSE_THREADS, FUSE_MIN_CTAS) tsdf_fuse_kernel(
                             const float u_f = xfadd(xfadd(qx, F.cx), 0.5f);
                             const float v_f = xfadd(xfadd(qy, F.cy), 0.5f);
                             const bool in = (u_f >= 0.0001f) & (u_f < F.safe_w) & (v_f >= 0.0001f) & (v_f < F.safe_h);
-                            if (in) tx[k] = __ldg(&F.texel[(int)v_f * F.W + (int)u_f]);
+                            if (in) {
+                                const int pix = (int)v_f * F.W + (int)u_f;
+                                tx[k] = __ldg(&F.texel[pix]);
+                                mk[k] = __ldg(&F.mult[pix]);       // frame-independent, L1/L2 resident
+                            }
                         }
                         pcx = xfadd(pcx, F.Es02); pcy = xfadd(pcy, F.Es12); pcz = xfadd(pcz, F.Es22);
                     }
@@ -603,17 +617,17 @@ __global__ void __launch_bounds__(FUSE_THREADS, FUSE_MIN_CTAS) tsdf_fuse_kernel(
 #pragma unroll
                     for (int k = 0; k < 4; k++) {
                         if (tx[k].x > 0.0f) {
-                            const float sdf = xfmul(xfsub(tx[k].x, zc[k]), tx[k].y);
+                            const float sdf = xfmul(xfsub(tx[k].x, zc[k]), mk[k]);
                             if (sdf > -P.trunc) {
                                 const float tv = fminf(1.0f, xfmul(sdf, P.inv_trunc));
                                 const float wgt = wp[k];
                                 const float w1 = xfadd(wgt, 1.0f);
                                 float c0 = 0.f, c1 = 0.f, c2 = 0.f;
                                 if (COLOR == 1) {
-                                    const uint32_t c = __float_as_uint(tx[k].z);
+                                    const uint32_t c = __float_as_uint(tx[k].y);
                                     c0 = byte_to_float<0>(c); c1 = byte_to_float<1>(c); c2 = byte_to_float<2>(c);
                                 } else if (COLOR == 2) {
-                                    c0 = c1 = c2 = tx[k].z;
+                                    c0 = c1 = c2 = tx[k].y;
                                 }
                                 const float at = xfadd(xfmul(tp[k], wgt), tv);
                                 float ar = 0.f, ag = 0.f, ab = 0.f;
@@ -633,7 +647,7 @@ __global__ void __launch_bounds__(FUSE_THREADS, FUSE_MIN_CTAS) tsdf_fuse_kernel(
                     }
                 }
                 if (upd != upd0) {
-                    float* base = P.pool + (int64_t)unit * P.unit_stride + (us & 3) * FUSE_SLAB + f4 * 4;
+                    float* base = P.pool + (int64_t)unit * P.unit_stride + (us & IM) * FUSE_SLAB + f4 * 4;
                     *reinterpret_cast<float4*>(base) = ts;
                     *reinterpret_cast<float4*>(base + B2R_UNIT_VOX) = ws;
                     if (COLOR) {
@@ -643,19 +657,9 @@ __global__ void __launch_bounds__(FUSE_THREADS, FUSE_MIN_CTAS) tsdf_fuse_kernel(
                     }
                 }
             }
-            __syncthreads();   // every thread has read its float4s of this stage -> the stage is free
-            if (tid == 0 && it + FUSE_STAGES < n_it) {
-                const int nx = it + FUSE_STAGES;
-                const int us2 = s_unit[nx];
-                if (us2 >= 0 && s_mask[nx]) {
-                    const float* src = P.pool + (int64_t)(us2 >> 2) * P.unit_stride + (us2 & 3) * FUSE_SLAB;
-                    mbar_expect_tx(&full_bar[st], PLANES * FUSE_SLAB * 4);
-#pragma unroll
-                    for (int pl = 0; pl < PLANES; pl++) tma_load_1d(stage + (st * PLANES + pl) * FUSE_SLAB, src + pl * B2R_UNIT_VOX, FUSE_SLAB * 4, &full_bar[st]);
-                } else {
-                    mbar_expect_tx(&full_bar[st], 0);
-                }
-            }
+            __syncthreads();   // every thread has read its float4s and the info of this stage -> the stage is free
+            if (tid == 0) fetch(ring ? st : (it_seq + 1) % FUSE_STAGES);
+            if (!ring) __syncthreads();   // one item at a time: the claim just made is the next iteration's
         }
     }
     // N_upd accounting: warp shuffle -> one atomic per warp
@@ -702,9 +706,13 @@ static void tsdf_free(b2r_tsdf* h) {
 }
 
 typedef void (*fuse_fn_t)(const FuseParams);
-static fuse_fn_t fuse_fn(int color_type, int stages) {
-    if (stages >= 3) return color_type == 0 ? tsdf_fuse_kernel<0, 3> : (color_type == 1 ? tsdf_fuse_kernel<1, 3> : tsdf_fuse_kernel<2, 3>);
-    return color_type == 0 ? tsdf_fuse_kernel<0, 2> : (color_type == 1 ? tsdf_fuse_kernel<1, 2> : tsdf_fuse_kernel<2, 2>);
+template <int XL>
+static fuse_fn_t fuse_fn_xl(int color_type, int stages) {
+    if (stages >= 3) return color_type == 0 ? tsdf_fuse_kernel<0, 3, XL> : (color_type == 1 ? tsdf_fuse_kernel<1, 3, XL> : tsdf_fuse_kernel<2, 3, XL>);
+    return color_type == 0 ? tsdf_fuse_kernel<0, 2, XL> : (color_type == 1 ? tsdf_fuse_kernel<1, 2, XL> : tsdf_fuse_kernel<2, 2, XL>);
+}
+static fuse_fn_t fuse_fn(int color_type, int stages, int xl) {
+    return xl == 2 ? fuse_fn_xl<2>(color_type, stages) : fuse_fn_xl<4>(color_type, stages);
 }
 
 B2R_API b2r_tsdf* b2r_tsdf_create(double voxel_length, double sdf_trunc, int color_type, int unit_resolution,
@@ -744,12 +752,15 @@ B2R_API b2r_tsdf* b2r_tsdf_create(double voxel_length, double sdf_trunc, int col
     }
     if (e == cudaSuccess) {
         const int stages = env_int("B2R_FUSE_STAGES", 2, 2, 3);
-        h->fuse_smem = stages * h->planes * FUSE_SLAB * 4;
-        fuse_fn_t fn = fuse_fn(color_type, stages);
+        // work quantum of K2: 4 x-layers per item; 2 (128-thread CTAs, 8 per SM) measured equal at every world size
+        h->fuse_xl = env_int("B2R_FUSE_XL", 4, 2, 4) == 2 ? 2 : 4;
+        h->fuse_ring_rounds = env_int("B2R_FUSE_RING_ROUNDS", 6, 0, 1 << 20);
+        h->fuse_smem = stages * h->planes * 256 * h->fuse_xl * 4;
+        fuse_fn_t fn = fuse_fn(color_type, stages, h->fuse_xl);
         e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fuse_smem);
         int nsm = 148, per_sm = 1;
         cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, h->device);
-        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, FUSE_THREADS, h->fuse_smem);
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 64 * h->fuse_xl, h->fuse_smem);
         if (per_sm < 1) per_sm = 1;
         h->fuse_grid = nsm * per_sm;
     }
@@ -826,6 +837,7 @@ int b2r_tsdf_flush_pending(b2r_tsdf* h, cudaStream_t stream) {
     FuseParams F;
     memset(&F, 0, sizeof(F));
     F.nframes = h->pending; F.q = h->q; F.reverse = (int)(h->batches & 1);
+    F.ring_rounds = h->fuse_ring_rounds;
     F.vl = (float)h->voxel_length; F.hv = F.vl * 0.5f;
     F.trunc = (float)h->sdf_trunc; F.inv_trunc = 1.0f / F.trunc;
     F.unit_length = h->unit_length;
@@ -833,9 +845,9 @@ int b2r_tsdf_flush_pending(b2r_tsdf* h, cudaStream_t stream) {
     F.slots = h->hash.slots; F.pool = h->pool; F.unit_stride = (int64_t)h->planes * B2R_UNIT_VOX;
     F.counters = h->counters; F.cap_units = (int)h->cap_units;
     for (int i = 0; i < h->pending; i++) F.fr[i] = h->frames[i];
-    const int stages = h->fuse_smem / (h->planes * FUSE_SLAB * 4);
+    const int stages = h->fuse_smem / (h->planes * 256 * h->fuse_xl * 4);
     const bool prof = prof_begin(h, 2, stream);
-    fuse_fn(h->color_type, stages)<<<h->fuse_grid, FUSE_THREADS, h->fuse_smem, stream>>>(F);
+    fuse_fn(h->color_type, stages, h->fuse_xl)<<<h->fuse_grid, 64 * h->fuse_xl, h->fuse_smem, stream>>>(F);
     B2R_CHECK_LAUNCH();
     prof_end(h, prof, stream);
     h->q = (h->q + 1) % 3;
@@ -872,15 +884,16 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
         B2R_CUDA(cudaStreamSynchronize(stream));
         for (int i = 0; i < B2R_MAX_BATCH; i++) { if (h->texel[i]) cudaFree(h->texel[i]); h->texel[i] = nullptr; }
         h->texel_px = 0;
-        for (int i = 0; i < h->max_batch; i++) B2R_CUDA(cudaMalloc((void**)&h->texel[i], npx * sizeof(float4)));
+        for (int i = 0; i < h->max_batch; i++) B2R_CUDA(cudaMalloc((void**)&h->texel[i], npx * sizeof(float2)));
         h->texel_px = npx;
     }
     const float fcx = (float)cx, fcy = (float)cy, ifx = 1.0f / (float)fx, ify = 1.0f / (float)fy;
     const double mkey[6] = {(double)W, (double)H, fx, fy, cx, cy};
     if (!h->mult || h->mult_px < npx || memcmp(mkey, h->mult_key, sizeof(mkey)) != 0) {
+        // K2 reads the multiplier image at fusion time: frames still pending were packed for the old intrinsics
+        int rc = b2r_tsdf_flush_pending(h, stream);
+        if (rc != B2R_OK) return rc;
         if (h->mult_px < npx) {
-            int rc = b2r_tsdf_flush_pending(h, stream);
-            if (rc != B2R_OK) return rc;
             B2R_CUDA(cudaStreamSynchronize(stream));
             if (h->mult) cudaFree(h->mult);
             h->mult = nullptr; h->mult_px = 0;
@@ -935,7 +948,7 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
             fr.Es02 = fr.E[2] * vl; fr.Es12 = fr.E[6] * vl; fr.Es22 = fr.E[10] * vl;
             fr.fx = (float)fx; fr.fy = (float)fy; fr.cx = (float)cx; fr.cy = (float)cy;
             fr.safe_w = (float)W - 0.0001f; fr.safe_h = (float)H - 0.0001f;
-            fr.W = W; fr.H = H; fr.texel = h->texel[slot];
+            fr.W = W; fr.H = H; fr.texel = h->texel[slot]; fr.mult = h->mult;
         }
         {
             const void* cimg = (h->color_type == 1) ? (const void*)color : (h->color_type == 2 ? (const void*)gray : nullptr);
@@ -1085,7 +1098,7 @@ B2R_API int b2r_tsdf_set_batch(b2r_tsdf* h, int max_batch, cudaStream_t stream) 
     if (max_batch > h->max_batch && h->texel_px) {
         B2R_CUDA(cudaStreamSynchronize(stream));
         for (int i = h->max_batch; i < max_batch; i++)
-            if (!h->texel[i]) B2R_CUDA(cudaMalloc((void**)&h->texel[i], h->texel_px * sizeof(float4)));
+            if (!h->texel[i]) B2R_CUDA(cudaMalloc((void**)&h->texel[i], h->texel_px * sizeof(float2)));
     }
     h->max_batch = max_batch;
     return B2R_OK;

@@ -10,6 +10,7 @@ enum {
     B2R_C_UPDATED = 6,     // u64 (words 6,7): voxels whose record changed, cumulative (N_upd)
     B2R_C_TOUCHED_TOTAL = 8,  // u64 (words 8,9): cumulative (unit, frame) pairs fused
     B2R_C_LAST_TOUCHED = 10,  // units touched by the most recent fused batch
+    B2R_C_WORK0 = 11,         // K2 work-item counters of the three rotating batch buffers (words 11,12,13)
     B2R_C_WORDS = 16
 };
 
@@ -22,7 +23,8 @@ struct B2RFrame {
     float Es02, Es12, Es22;  // E(:,2) * voxel_length (f32)
     float fx, fy, cx, cy, safe_w, safe_h;
     int W, H;
-    const float4* texel;     // packed frame: {depth m, ray multiplier, rgb8 | gray f32 bits, 0}
+    const float2* texel;     // packed frame: {depth m, rgb8 | gray f32 bits}
+    const float* mult;       // ray multiplier image of the frame's intrinsics (handle cache)
 };
 
 struct b2r_tsdf {
@@ -42,7 +44,7 @@ struct b2r_tsdf {
     int pending;           // frames in it
     int max_batch;         // <= B2R_MAX_BATCH
     B2RFrame frames[B2R_MAX_BATCH];
-    float4* texel[B2R_MAX_BATCH];
+    float2* texel[B2R_MAX_BATCH];
     size_t texel_px;
     float* mult;             // depth-to-camera-distance multiplier image of the cached intrinsics (shared by every frame)
     size_t mult_px;
@@ -50,6 +52,8 @@ struct b2r_tsdf {
     int64_t batches;       // fused so far (alternates the sweep direction)
     int fuse_grid;         // persistent grid size of the fusion kernel
     int fuse_smem;         // dynamic shared memory of the fusion kernel
+    int fuse_xl;           // x-layers per K2 work item (4 or 2)
+    int fuse_ring_rounds;  // K2 passes shorter than this many items per CTA claim one item at a time
     // host-input pipeline (b2r_tsdf_integrate_host)
     cudaStream_t copy_stream;
     cudaEvent_t ev_copied[B2R_HOST_RING], ev_consumed[B2R_HOST_RING];

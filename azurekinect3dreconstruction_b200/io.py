@@ -354,3 +354,31 @@ def read_pose_graph(filename: str):
         pg.edges.append(PoseGraphEdge(e["source_node_id"], e["target_node_id"], np.asarray(e["transformation"], dtype=np.float64).reshape(4, 4).T,
                                       np.asarray(e["information"], dtype=np.float64).reshape(6, 6).T, bool(e["uncertain"]), float(e["confidence"])))
     return pg
+
+
+# ---------------------------------------------------------------- images (o3d.io.read_image / write_image)
+def read_image(filename: str):
+    """`o3d.io.read_image(path)` (CodeThatWorks/RGBD_Odometry.py:10-13): PNG/JPG -> geometry.Image.  8-bit colour
+    comes back as RGB (Open3D's channel order), 16-bit single-channel depth PNGs stay u16.  A missing or
+    undecodable file gives an empty Image plus a warning upstream; here it raises, since every caller goes
+    straight on to create_from_color_and_depth, which would raise anyway."""
+    import cv2
+    from .geometry import Image
+    a = cv2.imread(filename, cv2.IMREAD_UNCHANGED)
+    if a is None:
+        raise RuntimeError(f"read_image: cannot read {filename}")
+    if a.ndim == 3:
+        a = a[:, :, 2::-1] if a.shape[2] >= 3 else a[:, :, 0]  # BGR(A) -> RGB, alpha dropped like upstream's PNG reader
+    return Image(np.ascontiguousarray(a))
+
+
+def write_image(filename: str, image, quality: int = -1) -> bool:
+    """`o3d.io.write_image(path, image)`: u8 (1 or 3 channels, RGB order) or u16 single-channel -> PNG/JPG."""
+    import cv2
+    a = image.numpy() if hasattr(image, "numpy") else np.asarray(image)
+    if a.dtype not in (np.uint8, np.uint16):
+        raise RuntimeError("write_image: only 8-bit and 16-bit integer images can be written")
+    if a.ndim == 3 and a.shape[2] == 3:
+        a = a[:, :, ::-1]
+    params = [cv2.IMWRITE_JPEG_QUALITY, quality] if quality >= 0 and _ext(filename) in ("jpg", "jpeg") else []
+    return bool(cv2.imwrite(filename, np.ascontiguousarray(a), params))
