@@ -11,8 +11,8 @@ A drop-in for the Open3D-shaped API the reference scripts call (``import open3d 
 All arithmetic runs in hand-written sm_100a CUDA behind the C-ABI of include/b2recon.h
 (libb2recon.so); there is no CPU fallback.  See DESIGN.md / INTEGRATION.md.
 """
-from . import camera, geometry, io, pipelines, synthetic, utility  # noqa: F401
+from . import camera, core, geometry, io, pipelines, synthetic, utility  # noqa: F401
 from ._lib import LIB_PATH, load as load_library  # noqa: F401
 
 __version__ = "0.1.0"
-__all__ = ["camera", "geometry", "io", "pipelines", "synthetic", "utility", "load_library", "LIB_PATH"]
+__all__ = ["camera", "core", "geometry", "io", "pipelines", "synthetic", "utility", "load_library", "LIB_PATH"]

@@ -565,7 +565,9 @@ __global__ void __launch_bounds__(64 * XL, FUSE_MIN_CTAS * 4 / XL) tsdf_fuse_ker
                 float* bp = reinterpret_cast<float*>(&bs);
                 const unsigned upd0 = upd;
                 pairs += (tid == 0 && (us & IM) == 0) ? __popc(fmask) : 0;
-                for (uint32_t fm = fmask; fm; fm &= fm - 1) {
+                // fmask is the same in every lane; the warp reduction says so to the compiler, which then keeps the frame loop
+                // and the frame's constants in the uniform datapath (LDCU into uniform registers, not one LDC per value per thread)
+                for (uint32_t fm = __reduce_or_sync(0xffffffffu, fmask); fm; fm &= fm - 1) {
                     const B2RFrame& F = P.fr[__ffs(fm) - 1];
                     float pcx = xfadd(xfadd(xfadd(xfmul(F.E[0], px), xfmul(F.E[1], py)), xfmul(F.E[2], pz)), F.E[3]);
                     float pcy = xfadd(xfadd(xfadd(xfmul(F.E[4], px), xfmul(F.E[5], py)), xfmul(F.E[6], pz)), F.E[7]);
@@ -732,7 +734,7 @@ B2R_API b2r_tsdf* b2r_tsdf_create(double voxel_length, double sdf_trunc, int col
     h->color_type = color_type; h->res = unit_resolution; h->stride = depth_sampling_stride;
     h->planes = color_type == 0 ? 2 : 5;
     h->cap_units = capacity_units; h->rank = rank; h->world = world;
-    h->max_batch = env_int("B2R_TSDF_BATCH", 16, 1, B2R_MAX_BATCH);
+    h->max_batch = env_int("B2R_TSDF_BATCH", B2R_MAX_BATCH, 1, B2R_MAX_BATCH);
     cudaError_t e = cudaGetDevice(&h->device);
     h->nslots = next_pow2((uint64_t)capacity_units * 2);
     h->hash.mask = h->nslots - 1;

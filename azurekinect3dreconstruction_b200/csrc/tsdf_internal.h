@@ -15,7 +15,7 @@ enum {
 };
 
 #define B2R_HOST_RING 3
-#define B2R_MAX_BATCH 16   // frames fused per pass over the touched units (bits of B2RSlot::mask)
+#define B2R_MAX_BATCH 32   // frames fused per pass over the touched units (bits of B2RSlot::mask)
 
 // what the fusion kernel needs to know about one pending frame (kernel parameter, by value)
 struct B2RFrame {

@@ -380,5 +380,5 @@ def write_image(filename: str, image, quality: int = -1) -> bool:
         raise RuntimeError("write_image: only 8-bit and 16-bit integer images can be written")
     if a.ndim == 3 and a.shape[2] == 3:
         a = a[:, :, ::-1]
-    params = [cv2.IMWRITE_JPEG_QUALITY, quality] if quality >= 0 and _ext(filename) in ("jpg", "jpeg") else []
+    params = [cv2.IMWRITE_JPEG_QUALITY, quality] if quality >= 0 and _ext(filename) in (".jpg", ".jpeg") else []
     return bool(cv2.imwrite(filename, np.ascontiguousarray(a), params))

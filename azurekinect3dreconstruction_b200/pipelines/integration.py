@@ -110,7 +110,7 @@ class ScalableTSDFVolume:
         _lib.check(self._lib.b2r_tsdf_flush(self._h, _lib.stream_ptr()), "flush")
 
     def set_batch(self, max_batch: int) -> None:
-        """Frames fused per pass over the touched units (1..16; 1 = strictly per-call fusion)."""
+        """Frames fused per pass over the touched units (1..32; 1 = strictly per-call fusion)."""
         _lib.check(self._lib.b2r_tsdf_set_batch(self._h, int(max_batch), _lib.stream_ptr()), "set_batch")
 
     # ---- stats / parity hooks -----------------------------------------------------------------------

@@ -262,7 +262,7 @@ def main():
                 "updated_voxels_per_frame": n_upd / args.frames, "touched_units_per_frame": s1["touched_units"] / args.frames,
                 "fuse_ms_total": prof[2], "pack_ms_total": prof[1]}
 
-    batch = int(os.environ.get("B2R_TSDF_BATCH", "16"))
+    batch = int(os.environ.get("B2R_TSDF_BATCH", "32"))
     kp = kernel_pass(batch)
     k1 = kernel_pass(1)                                 # strictly per-frame fusion: the streaming (HBM-bound) form
     vol.set_batch(batch)

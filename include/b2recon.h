@@ -116,7 +116,7 @@ int b2r_tsdf_integrate_host(b2r_tsdf* h, int n, const void* depth_host, int dept
                             cudaStream_t stream);
 
 /* Frames are packed and their blocks allocated when integrate is called; the per-voxel update of up to
- * max_batch (default 16, env B2R_TSDF_BATCH, <= 16) pending frames runs as ONE pass over the touched
+ * max_batch (default 32, env B2R_TSDF_BATCH, <= 32) pending frames runs as ONE pass over the touched
  * units when the batch is full or when anything reads the volume (stats, export, extract, ...).  Results
  * are bit-identical to frame-by-frame integration.  b2r_tsdf_flush forces the pass; b2r_tsdf_set_batch(1)
  * gives strictly per-call fusion. */

@@ -20,7 +20,7 @@ TT = o3d.pipelines.integration.TSDFVolumeColorType
 @pytest.fixture(scope="module")
 def nfov():
     kin = syn.SyntheticKinect(seed=0, dropout=0.02, noise_sigma_mm=1.0, device="cuda")
-    poses = syn.orbit_trajectory(300)[:12]
+    poses = syn.orbit_trajectory(300)[:40]
     fr = [kin.render_depth_aligned_rgb(p) for p in poses]
     depth = torch.stack([f[0].view(torch.int16) for f in fr]).contiguous().view(torch.uint16)
     rgb = torch.stack([f[1] for f in fr]).contiguous()
@@ -92,6 +92,8 @@ def test_tsdf_full_size_invariances(nfov):
     assert len(ref[0]) > 2000 and int(ref_vol.stats()["errors"]) == 0
     assert same_state(ref, volume_state(run(1)))                          # fusion batch size does not change a bit
     assert same_state(ref, volume_state(run(5)))
+    assert same_state(ref, volume_state(run(32)))                         # one pass over 32 frames (all mask bits), then 8
+    assert same_state(ref, volume_state(run(24)))
     assert same_state(ref, volume_state(run(16, host=True)))              # nor does the ingest path
     import os
     os.environ["B2R_K1_TMA"] = "0"                                        # nor the LDG form of the pack role (unaligned images take it)

@@ -301,7 +301,7 @@ def test_tsdf_batch_size_invariance(frames, small_kinect):
     color = torch.stack([torch.from_numpy(frames[i][1]) for i in range(n)]).cuda()
     E = np.stack([np.linalg.inv(frames[i][2]) for i in range(n)])
     out = []
-    for batch in (1, 4, 16):
+    for batch in (1, 4, 16, 32):
         v = o3d.pipelines.integration.ScalableTSDFVolume(0.004, 0.02, o3d.pipelines.integration.TSDFVolumeColorType.RGB8, capacity_units=30000)
         v.set_batch(batch)
         v.integrate_raw(depth[:2], color[:2], K, E[:2])

@@ -108,3 +108,35 @@ def test_reference_frame_trajectory_and_calibration_files(tmp_path):
     K2, E2, _ = io.load_calibration(cp)
     assert np.array_equal(K2[1].intrinsic_matrix, Ks[1].intrinsic_matrix) and K2[0].width == 640
     assert np.array_equal(E2[1], Es[1])
+
+
+def test_image_files_round_trip_like_the_odometry_script(tmp_path):
+    """o3d.io.read_image on a colour PNG and a 16-bit depth PNG (RGBD_Odometry.py:10-13), then the RGBD pair."""
+    rng = np.random.default_rng(3)
+    color = rng.integers(0, 256, (48, 64, 3), dtype=np.uint8)
+    depth = rng.integers(0, 4000, (48, 64), dtype=np.uint16)
+    cp, dp = str(tmp_path / "c.png"), str(tmp_path / "d.png")
+    assert io.write_image(cp, o3d.geometry.Image(color)) and io.write_image(dp, o3d.geometry.Image(depth))
+    c2, d2 = io.read_image(cp), io.read_image(dp)
+    assert np.array_equal(np.asarray(c2), color) and np.asarray(c2).dtype == np.uint8       # RGB order preserved
+    assert np.array_equal(np.asarray(d2), depth) and np.asarray(d2).dtype == np.uint16
+    assert (c2.width, c2.height, c2.channels, d2.bytes_per_channel) == (64, 48, 3, 2)
+    try:
+        io.read_image(str(tmp_path / "missing.png"))
+        assert False, "expected an error"
+    except RuntimeError:
+        pass
+
+
+def test_core_device_probe_of_the_reference():
+    """GoodColorReconstruction.py:88-97: hasattr(o3d.core, 'cuda') / is_available() / Device("CUDA:0")."""
+    assert hasattr(o3d, "core") and hasattr(o3d.core, "cuda")
+    assert isinstance(o3d.core.cuda.is_available(), bool)
+    d = o3d.core.Device("CUDA:0")
+    assert d.is_cuda() and d.get_id() == 0 and repr(d) == "CUDA:0"
+    assert o3d.core.Device("CPU:0") == o3d.core.Device() and o3d.core.Device("cpu:0").is_cpu()
+    try:
+        o3d.core.Device("TPU:0")
+        assert False, "expected an error"
+    except RuntimeError:
+        pass

@@ -1,10 +1,8 @@
-# Round-end verification: GPU tests, smoke, both bench arms, ops bench, then the ncu launch list of the bench command
+# Round-end verification: GPU tests, smoke, both bench arms, ops bench, then the ncu evidence of the bench command
 set -x
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_gpu.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/smoke.log 2>&1; echo "rc=$?" >> gpurun_out/smoke.log
 timeout 600 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "rc=$?" >> gpurun_out/bench.err
 timeout 600 python bench.py --impl reference > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "rc=$?" >> gpurun_out/bench_ref.err
-timeout 600 python tools/bench_ops.py > gpurun_out/bench_ops.json 2> gpurun_out/bench_ops.err; echo "rc=$?" >> gpurun_out/bench_ops.err
-CMD="python bench.py --steps 1 --warmup 1 --frames 48 --no-cpu-baseline"
-timeout 300 $CMD > gpurun_out/plain.log 2>&1 && \
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:tsdf -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu1.log 2>&1
+timeout 600 python tools/shard_probe.py --xls 4 --batches 32 > gpurun_out/shard_probe.json 2> gpurun_out/shard_probe.err; echo "rc=$?" >> gpurun_out/shard_probe.err
+bash tools/gpu_prof.sh
