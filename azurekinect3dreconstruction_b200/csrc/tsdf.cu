@@ -590,22 +590,22 @@ __global__ void __launch_bounds__(64 * XL, FUSE_MIN_CTAS * 4 / XL) tsdf_fuse_ker
                         zc[k] = pcz;
                         tx[k] = make_float2(0.f, 0.f);
                         mk[k] = 0.f;
-                        if (pcz > 0.0f) {
+                        {
                             // u_f = pc.x*fx/pc.z + cx + 0.5f, v_f likewise: both quotients share RN(1/pc.z).
-                            // Outside b2r_div_domain (pc.z < 2^-60, ...) take div.rn.  Inside it the Markstein
-                            // quotient is RN(a/b) unless |a| is so small that r underflows, and then |q| < 2^-40
-                            // cannot change RN(q + cx) -- the pixel picked is the same either way.
+                            // Inside b2r_div_domain (2^-60 <= pc.z < 2^60, which implies pc.z > 0) the Markstein quotient is
+                            // RN(a/b) unless |a| is so small that r underflows, and then |q| < 2^-40 cannot change
+                            // RN(q + cx) -- the pixel picked is the same either way.  The fast form is computed without a
+                            // branch (its value is unused outside the domain); a positive pc.z outside the domain takes
+                            // div.rn on a cold path; pc.z <= 0 or NaN never projects.
+                            const bool dom = b2r_div_domain(pcz);
                             const float ax = xfmul(pcx, F.fx), ay = xfmul(pcy, F.fy);
-                            float qx, qy;
-                            if (__builtin_expect(b2r_div_domain(pcz), 1)) {
-                                const float inv = b2r_rcp_markstein(pcz);
-                                qx = b2r_div_fast(ax, pcz, inv); qy = b2r_div_fast(ay, pcz, inv);
-                            } else {
-                                qx = __fdiv_rn(ax, pcz); qy = __fdiv_rn(ay, pcz);
-                            }
+                            const float inv = b2r_rcp_markstein(pcz);
+                            float qx = b2r_div_fast(ax, pcz, inv), qy = b2r_div_fast(ay, pcz, inv);
+                            bool ok = dom;
+                            if (__builtin_expect(!dom && pcz > 0.0f, 0)) { qx = __fdiv_rn(ax, pcz); qy = __fdiv_rn(ay, pcz); ok = true; }
                             const float u_f = xfadd(xfadd(qx, F.cx), 0.5f);
                             const float v_f = xfadd(xfadd(qy, F.cy), 0.5f);
-                            const bool in = (u_f >= 0.0001f) & (u_f < F.safe_w) & (v_f >= 0.0001f) & (v_f < F.safe_h);
+                            const bool in = ok & (u_f >= 0.0001f) & (u_f < F.safe_w) & (v_f >= 0.0001f) & (v_f < F.safe_h);
                             if (in) {
                                 const int pix = (int)v_f * F.W + (int)u_f;
                                 tx[k] = __ldg(&F.texel[pix]);
@@ -618,9 +618,9 @@ __global__ void __launch_bounds__(64 * XL, FUSE_MIN_CTAS * 4 / XL) tsdf_fuse_ker
                     // the division domain except 2^24 - 1 (all-ones significand); numerators are 0 or >= 2^-60.
 #pragma unroll
                     for (int k = 0; k < 4; k++) {
-                        if (tx[k].x > 0.0f) {
+                        {
                             const float sdf = xfmul(xfsub(tx[k].x, zc[k]), mk[k]);
-                            if (sdf > -P.trunc) {
+                            if ((tx[k].x > 0.0f) & (sdf > -P.trunc)) {
                                 const float tv = fminf(1.0f, xfmul(sdf, P.inv_trunc));
                                 const float wgt = wp[k];
                                 const float w1 = xfadd(wgt, 1.0f);
