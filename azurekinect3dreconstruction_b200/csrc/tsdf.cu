@@ -634,11 +634,12 @@ __global__ void __launch_bounds__(64 * XL, FUSE_MIN_CTAS * 4 / XL) tsdf_fuse_ker
                                 const float at = xfadd(xfmul(tp[k], wgt), tv);
                                 float ar = 0.f, ag = 0.f, ab = 0.f;
                                 if (COLOR) { ar = xfadd(xfmul(rp[k], wgt), c0); ag = xfadd(xfmul(gp[k], wgt), c1); ab = xfadd(xfmul(bp[k], wgt), c2); }
-                                if (__builtin_expect(b2r_div_domain(w1), 1)) {
+                                {
                                     const float inv = b2r_rcp_markstein(w1);
                                     tp[k] = b2r_div_fast(at, w1, inv);
                                     if (COLOR) { rp[k] = b2r_div_fast(ar, w1, inv); gp[k] = b2r_div_fast(ag, w1, inv); bp[k] = b2r_div_fast(ab, w1, inv); }
-                                } else {
+                                }
+                                if (__builtin_expect(!b2r_div_domain(w1), 0)) {     // cold: w1 = 2^24 - 1, or a non-integer weight imported into the pool
                                     tp[k] = __fdiv_rn(at, w1);
                                     if (COLOR) { rp[k] = __fdiv_rn(ar, w1); gp[k] = __fdiv_rn(ag, w1); bp[k] = __fdiv_rn(ab, w1); }
                                 }
