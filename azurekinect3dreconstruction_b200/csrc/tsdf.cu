@@ -12,9 +12,10 @@
 // Two kernels, both on the caller's stream:
 //   K1 tsdf_pack_alloc_kernel (at every integrate call; one launch can take a batch of frames; the two roles are
 //      dealt out evenly over the launch order so the latency-bound one runs beside the bandwidth-bound one):
-//        pack role  - a CTA stages 2048 pixels of depth, colour and the cached depth-to-camera-distance multiplier
-//                     image by three TMA bulk copies, fuses the RGBDImage conversion (u16 -> f32 metres, trunc) and
-//                     writes ONE 16-byte texel {d, mult, rgb8, 0} per pixel, 512 contiguous bytes per warp store;
+//        pack role  - a CTA stages 2048 pixels of depth and colour by two TMA bulk copies, fuses the RGBDImage
+//                     conversion (u16 -> f32 metres, trunc) and writes ONE 8-byte texel {d, rgb8 | gray} per pixel,
+//                     256 contiguous bytes per warp store (the depth-to-camera-distance multiplier image depends on
+//                     the intrinsics only: it is cached in the handle and gathered by K2 beside the texel);
 //        alloc role - one thread per depth_sampling_stride-th pixel unprojects in f64 (divisions by fx, fy and the
 //                     unit length through host-rounded reciprocals, exact); runs of equal key boxes are merged, the
 //                     run heads write their cells' keys into a shared list and the block probes them in parallel
@@ -22,9 +23,9 @@
 //                     of a (unit, batch) are appended to the batch's touched list (one counter atomic per warp) and
 //                     the frame's bit is OR-ed into the slot's batch mask.
 //   K2 tsdf_fuse_kernel (when max_batch frames are pending, or when anything reads the volume):
-//        persistent CTAs over (touched unit x 4 x-slabs).  A slab (planes x 4 KiB) is staged into shared
-//        memory by TMA bulk copies (cp.async.bulk + mbarrier) through a 3-deep ring, so the next two
-//        slabs are in flight while the current one is fused.  A thread owns 4 consecutive z voxels, keeps
+//        persistent CTAs draw work items (touched unit x 4 x-slabs) from a counter.  A slab (planes x 4 KiB) is
+//        staged into shared memory by TMA bulk copies (cp.async.bulk + mbarrier) through a 2-deep ring, so the
+//        next slab is in flight while the current one is fused.  A thread owns 4 consecutive z voxels, keeps
 //        them in registers while it applies EVERY pending frame that touches the unit (in frame order,
 //        so the result equals frame-by-frame integration bit for bit), and writes the record back once,
 //        only if it changed.  HBM traffic per frame therefore falls with the batch size; the voxel
@@ -1014,8 +1015,12 @@ B2R_API int b2r_tsdf_integrate_host(b2r_tsdf* h, int n, const void* depth_host, 
     B2RDeviceGuard g(h->device);
     const size_t npx = (size_t)W * H;
     const size_t dbytes = npx * (depth_is_u16 ? 2 : 4), cbytes = color_host ? npx * (size_t)color_channels : 0;
-    // a ring slot stages one chunk of up to max_batch frames: two large copies and ONE K1 launch per chunk
-    const size_t need_d = dbytes * h->max_batch, need_c = cbytes ? cbytes * h->max_batch : 16;
+    // a ring slot stages one chunk of up to `chunk` frames: two copies and ONE K1 launch per chunk.  Chunks are shorter than a
+    // fusion batch so that the first K1 starts after 8 frames' worth of PCIe time, not 32, and the ring is deep enough to
+    // keep the copy engine busy through a whole K2 pass (B2R_HOST_RING x chunk frames buffered >= one batch).
+    int chunk = env_int("B2R_HOST_CHUNK", 8, 1, B2R_MAX_BATCH);
+    if (chunk > h->max_batch) chunk = h->max_batch;
+    const size_t need_d = dbytes * chunk, need_c = cbytes ? cbytes * chunk : 16;
     if (h->stage_depth_bytes < need_d || h->stage_color_bytes < need_c) {
         B2R_CUDA(cudaStreamSynchronize(stream));
         B2R_CUDA(cudaStreamSynchronize(h->copy_stream));
@@ -1035,6 +1040,7 @@ B2R_API int b2r_tsdf_integrate_host(b2r_tsdf* h, int n, const void* depth_host, 
     while (f < n) {
         int room = h->max_batch - h->pending;
         if (room <= 0) room = h->max_batch;
+        if (room > chunk) room = chunk;
         const int take = n - f < room ? n - f : room;
         const int r = (int)(h->host_seq % B2R_HOST_RING);
         if (h->host_seq >= B2R_HOST_RING) B2R_CUDA(cudaStreamWaitEvent(h->copy_stream, h->ev_consumed[r], 0));

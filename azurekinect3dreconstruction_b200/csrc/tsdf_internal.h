@@ -14,7 +14,7 @@ enum {
     B2R_C_WORDS = 16
 };
 
-#define B2R_HOST_RING 3
+#define B2R_HOST_RING 6
 #define B2R_MAX_BATCH 32   // frames fused per pass over the touched units (bits of B2RSlot::mask)
 
 // what the fusion kernel needs to know about one pending frame (kernel parameter, by value)
