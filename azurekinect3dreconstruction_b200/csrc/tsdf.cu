@@ -101,6 +101,7 @@ struct PackParams {
     float rscale; int scale_fast;  // RN(1/depth_scale); depth_scale inside b2r_div_domain
     double rfx, rfy, runit;        // RN(1/fx), RN(1/fy), RN(1/unit_length)
     int ddiv_fast;                 // all three f64 divisors qualify for the shared-reciprocal division
+    int role32;                    // grid size x allocation blocks < 2^32: the role split runs in 32-bit arithmetic
     int tma_ok;                    // every tile of every image is a 16-byte aligned multiple of 16 bytes: TMA staging in the pack role
     int rank, world;
     int q;                         // batch buffer (mask word) in use
@@ -227,8 +228,10 @@ __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(con
     // floor(L * n_alloc_total / n_total) when A(L + 1) > A(L), else pack block L - A(L).
     const unsigned L = blockIdx.y * gridDim.x + blockIdx.x;
     const unsigned n_total = gridDim.x * gridDim.y, n_alloc_total = (unsigned)P.n_alloc_blocks * gridDim.y;
-    const unsigned A0 = (unsigned)(((unsigned long long)L * n_alloc_total) / n_total);
-    const unsigned A1 = (unsigned)(((unsigned long long)(L + 1) * n_alloc_total) / n_total);
+    // (the products fit 32 bits for every image the host lets through with role32 set; the emulated 64-bit division
+    // was 9 % of this kernel's instructions)
+    const unsigned A0 = P.role32 ? (L * n_alloc_total) / n_total : (unsigned)(((unsigned long long)L * n_alloc_total) / n_total);
+    const unsigned A1 = P.role32 ? ((L + 1) * n_alloc_total) / n_total : (unsigned)(((unsigned long long)(L + 1) * n_alloc_total) / n_total);
     const bool role_pack = A1 == A0;
     const unsigned n_role = role_pack ? gridDim.x - (unsigned)P.n_alloc_blocks : (unsigned)P.n_alloc_blocks;
     const unsigned ridx = role_pack ? L - A0 : A0;
@@ -963,6 +966,7 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
             if (e && atoi(e) == 0) P.tma_ok = 0;
         }
         const dim3 grid((unsigned)(P.n_alloc_blocks + (npx + 256 * PACK_PX - 1) / (256 * PACK_PX)), (unsigned)take);
+        P.role32 = ((unsigned long long)grid.x * grid.y) * ((unsigned long long)P.n_alloc_blocks * grid.y) < (1ull << 32) ? 1 : 0;
         const bool prof = prof_begin(h, 1, stream);
         tsdf_pack_alloc_kernel<<<grid, 256, K1_DYN_SMEM, stream>>>(P);
         B2R_CHECK_LAUNCH();
