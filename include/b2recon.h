@@ -109,7 +109,8 @@ int b2r_tsdf_integrate_batch(b2r_tsdf* h, int n, const void* depth, int depth_is
                              float depth_trunc, const uint8_t* color, int color_channels, int color_bgr, int W,
                              int H, double fx, double fy, double cx, double cy, const double* extrinsics_host,
                              cudaStream_t stream);
-/* same with HOST images: H2D copies overlap fusion through an internal 3-deep device ring */
+/* same with HOST images: H2D copies overlap fusion through an internal 6-deep device ring of 8-frame chunks
+ * (env B2R_HOST_CHUNK) */
 int b2r_tsdf_integrate_host(b2r_tsdf* h, int n, const void* depth_host, int depth_is_u16, float depth_scale,
                             float depth_trunc, const uint8_t* color_host, int color_channels, int color_bgr, int W,
                             int H, double fx, double fy, double cx, double cy, const double* extrinsics_host,
