@@ -118,6 +118,36 @@ def test_tsdf_full_size_invariances(nfov):
     assert same_state(ref, merged)
 
 
+def test_tsdf_item_scheduling_modes_are_repeatable(nfov):
+    """K2 draws its work items from a counter, so the order in which units are fused changes from run to run and with the
+    scheduling mode (prefetching ring with look-ahead claims / one item at a time / 2-layer items).  Every voxel record must
+    come out the same regardless: a race in the item hand-off protocol would show up here as a differing bit."""
+    import os
+    kin, depth, rgb, K, E = nfov
+
+    def run(env):
+        old = {k: os.environ.get(k) for k in env}
+        os.environ.update(env)
+        try:
+            vol = o3d.pipelines.integration.ScalableTSDFVolume(0.004, 0.02, TT.RGB8, capacity_units=12000)
+            vol.integrate_raw(depth, rgb, K, E, 1000.0, 3.0)
+            return volume_state(vol), vol.stats()
+        finally:
+            for k, v in old.items():
+                if v is None:
+                    del os.environ[k]
+                else:
+                    os.environ[k] = v
+
+    ref, st = run({})
+    for env in ({"B2R_FUSE_RING_ROUNDS": "0"}, {"B2R_FUSE_RING_ROUNDS": "1000000"}, {"B2R_FUSE_XL": "2"},
+                {"B2R_FUSE_XL": "2", "B2R_FUSE_RING_ROUNDS": "1000000"}, {"B2R_FUSE_STAGES": "3"}):
+        for _ in range(3):
+            got, st2 = run(env)
+            assert same_state(ref, got), env
+            assert st2["updated_voxels"] == st["updated_voxels"] and st2["touched_units"] == st["touched_units"], env
+
+
 def test_mesh_full_size_properties(nfov):
     kin, depth, rgb, K, E = nfov
     vl = 0.004
