@@ -66,7 +66,7 @@ def build_cuda(force: bool = False, verbose: bool = False) -> str:
 def build_oracle(force: bool = False) -> str:
     odir = os.path.join(ROOT, "oracle")
     lib = os.path.join(odir, "liboracle.so")
-    deps = [os.path.join(odir, "oracle.cpp"), os.path.join(odir, "oracle_pcd.cpp"), os.path.join(odir, "mc_tables.h"), os.path.join(odir, "Makefile")]
+    deps = [os.path.join(odir, "oracle.cpp"), os.path.join(odir, "oracle_pcd.cpp"), os.path.join(CSRC, "mc_tables.h"), os.path.join(odir, "Makefile")]
     if force or _stale(lib, deps):
         res = subprocess.run(["make", "-C", odir] + (["-B"] if force else []), capture_output=True, text=True)
         if res.returncode != 0:

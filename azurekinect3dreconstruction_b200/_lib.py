@@ -30,6 +30,7 @@ SIGNATURES = {
     "b2r_m4_mul": (None, [_pd, _pd, _pd]),
     "b2r_unit_owner": (_i, [_i, _i, _i, _i]),
     "b2r_depth_to_float": (_i, [_vp, _i64, _f, _f, _vp, _vp]),
+    "b2r_depth_to_float_typed": (_i, [_vp, _i, _i64, _f, _f, _vp, _vp]),
     "b2r_rgb_to_intensity": (_i, [_vp, _i64, _i, _i, _vp, _vp]),
     "b2r_unproject_scratch_words": (_i64, [_i, _i, _i, _i, _i]),
     "b2r_unproject": (_i, [_vp, _i, _f, _f, _i, _i, _i, _vp, _i, _i, _i, _i, _vp, _pd, _pd, _pd, _vp, _i, _i, _i,

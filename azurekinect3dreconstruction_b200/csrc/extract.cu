@@ -696,39 +696,67 @@ B2R_API int b2r_tsdf_extract_mesh(b2r_tsdf* h, double* vtx, double* vcol, int32_
 }
 
 // ---- TriangleMesh.compute_vertex_normals() (GoodColorReconstruction.py:286) --------
+// Upstream: ComputeTriangleNormals(false) -- the UN-normalised cross products (so a triangle weighs in by its area) are
+// added to their three vertices in triangle order, then every sum is normalised (zero stays zero, NaN -> (0, 0, 1)).
+// Here: the 3 F (vertex, triangle) incidences are sorted by vertex with a STABLE radix sort, so each vertex sees its
+// triangles in ascending triangle order, and one thread per vertex adds them up in that order: the f64 sums are the
+// sequential loop's, bit for bit, and the same on every run (no floating-point atomics).
 namespace {
-__global__ void tri_normals_accumulate_kernel(const double* vtx, const int32_t* tri, int64_t nF, double* out) {
-    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= nF) return;
-    const int i0 = tri[3 * t], i1 = tri[3 * t + 1], i2 = tri[3 * t + 2];
-    const double ax = vtx[3 * i0], ay = vtx[3 * i0 + 1], az = vtx[3 * i0 + 2];
-    const double e1x = xdsub(vtx[3 * i1], ax), e1y = xdsub(vtx[3 * i1 + 1], ay), e1z = xdsub(vtx[3 * i1 + 2], az);
-    const double e2x = xdsub(vtx[3 * i2], ax), e2y = xdsub(vtx[3 * i2 + 1], ay), e2z = xdsub(vtx[3 * i2 + 2], az);
-    double nx = xdsub(xdmul(e1y, e2z), xdmul(e1z, e2y)), ny = xdsub(xdmul(e1z, e2x), xdmul(e1x, e2z)), nz = xdsub(xdmul(e1x, e2y), xdmul(e1y, e2x));
-    const double len = sqrt(xdadd(xdadd(xdmul(nx, nx), xdmul(ny, ny)), xdmul(nz, nz)));
-    if (len > 0.0) { nx = xddiv(nx, len); ny = xddiv(ny, len); nz = xddiv(nz, len); }
-    const int idx[3] = {i0, i1, i2};
-#pragma unroll
-    for (int k = 0; k < 3; k++) {
-        atomicAdd(&out[3 * idx[k]], nx); atomicAdd(&out[3 * idx[k] + 1], ny); atomicAdd(&out[3 * idx[k] + 2], nz);
-    }
+__global__ void incidence_fill_kernel(int32_t* tri_of_corner, int64_t n3) {
+    const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < n3) tri_of_corner[c] = (int32_t)(c / 3);
 }
-__global__ void normalize_kernel(double* n, int64_t nV) {
+__global__ void vertex_normals_gather_kernel(const double* __restrict__ vtx, const int32_t* __restrict__ tri, const int32_t* __restrict__ vsorted,
+                                             const int32_t* __restrict__ tsorted, int64_t n3, double* __restrict__ out) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nV) return;
-    const double x = n[3 * i], y = n[3 * i + 1], z = n[3 * i + 2];
-    const double len = sqrt(xdadd(xdadd(xdmul(x, x), xdmul(y, y)), xdmul(z, z)));
-    if (len > 0.0) { n[3 * i] = xddiv(x, len); n[3 * i + 1] = xddiv(y, len); n[3 * i + 2] = xddiv(z, len); }
+    if (i >= n3) return;
+    const int v = vsorted[i];
+    if (i > 0 && vsorted[i - 1] == v) return;          // not the head of this vertex's run
+    double sx = 0.0, sy = 0.0, sz = 0.0;
+    for (int64_t j = i; j < n3 && vsorted[j] == v; j++) {
+        const int t = tsorted[j];
+        const int i0 = tri[3 * t], i1 = tri[3 * t + 1], i2 = tri[3 * t + 2];
+        const double ax = vtx[3 * i0], ay = vtx[3 * i0 + 1], az = vtx[3 * i0 + 2];
+        const double e1x = xdsub(vtx[3 * i1], ax), e1y = xdsub(vtx[3 * i1 + 1], ay), e1z = xdsub(vtx[3 * i1 + 2], az);
+        const double e2x = xdsub(vtx[3 * i2], ax), e2y = xdsub(vtx[3 * i2 + 1], ay), e2z = xdsub(vtx[3 * i2 + 2], az);
+        sx = xdadd(sx, xdsub(xdmul(e1y, e2z), xdmul(e1z, e2y)));
+        sy = xdadd(sy, xdsub(xdmul(e1z, e2x), xdmul(e1x, e2z)));
+        sz = xdadd(sz, xdsub(xdmul(e1x, e2y), xdmul(e1y, e2x)));
+    }
+    const double z = xdadd(xdadd(xdmul(sx, sx), xdmul(sy, sy)), xdmul(sz, sz));
+    if (z > 0.0) { const double len = sqrt(z); sx = xddiv(sx, len); sy = xddiv(sy, len); sz = xddiv(sz, len); }
+    if (sx != sx) { sx = 0.0; sy = 0.0; sz = 1.0; }
+    out[3 * (int64_t)v] = sx; out[3 * (int64_t)v + 1] = sy; out[3 * (int64_t)v + 2] = sz;
 }
 }  // namespace
 
 B2R_API int b2r_mesh_vertex_normals(const double* vtx, int64_t nV, const int32_t* tri, int64_t nF, double* out, cudaStream_t stream) {
-    if (!vtx || !tri || !out || nV < 0 || nF < 0) return B2R_ERR_BAD_ARG;
+    if (!vtx || !tri || !out || nV < 0 || nF < 0 || nF > (int64_t)0x7fffffff / 3) return B2R_ERR_BAD_ARG;
     if (nV == 0) return B2R_OK;
-    B2R_CUDA(cudaMemsetAsync(out, 0, (size_t)nV * 24, stream));
-    if (nF) tri_normals_accumulate_kernel<<<(unsigned)((nF + 255) / 256), 256, 0, stream>>>(vtx, tri, nF, out);
-    B2R_CHECK_LAUNCH();
-    normalize_kernel<<<(unsigned)((nV + 255) / 256), 256, 0, stream>>>(out, nV);
-    B2R_CHECK_LAUNCH();
+    B2R_CUDA(cudaMemsetAsync(out, 0, (size_t)nV * 24, stream));     // vertices without a triangle keep the zero normal
+    if (nF == 0) return B2R_OK;
+    const int64_t n3 = 3 * nF;
+    int end_bit = 1;
+    while (end_bit < 31 && ((int64_t)1 << end_bit) < nV) end_bit++;
+    size_t tmp_bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, (const int32_t*)nullptr, (int32_t*)nullptr, (const int32_t*)nullptr, (int32_t*)nullptr, (int)n3, 0, end_bit, stream);
+    const size_t a = align_up((size_t)n3 * 4);
+    char* buf = nullptr;
+    B2R_CUDA(cudaMallocAsync((void**)&buf, 3 * a + align_up(tmp_bytes), stream));
+    int32_t* t_in = (int32_t*)buf;
+    int32_t* v_out = (int32_t*)(buf + a);
+    int32_t* t_out = (int32_t*)(buf + 2 * a);
+    void* tmp = buf + 3 * a;
+    const unsigned blocks = (unsigned)((n3 + 255) / 256);
+    incidence_fill_kernel<<<blocks, 256, 0, stream>>>(t_in, n3);
+    cudaError_t e = cudaGetLastError();
+    // the triangle array itself is the key array: corner c = 3 t + k holds the vertex id of incidence (t, k)
+    if (e == cudaSuccess) e = cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, tri, v_out, (const int32_t*)t_in, t_out, (int)n3, 0, end_bit, stream);
+    if (e == cudaSuccess) {
+        vertex_normals_gather_kernel<<<blocks, 256, 0, stream>>>(vtx, tri, v_out, t_out, n3, out);
+        e = cudaGetLastError();
+    }
+    cudaFreeAsync(buf, stream);
+    if (e != cudaSuccess) { b2r_set_error("b2r_mesh_vertex_normals: %s", cudaGetErrorString(e)); return B2R_ERR_CUDA; }
     return B2R_OK;
 }

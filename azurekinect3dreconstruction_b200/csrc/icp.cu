@@ -18,6 +18,7 @@
 #include "rigid_fit.cuh"
 #include <cub/cub.cuh>
 #include <math.h>
+#include <mutex>
 
 namespace {
 
@@ -441,8 +442,14 @@ static int icp_run(const double* src_xyz, int64_t N, const double* tgt_xyz, cons
         *fitness_host = 0.0; *rmse_host = 0.0;
         return 0;
     }
+    // The per-device workspace is process-global and a ctypes call releases the GIL (the reference runs one thread per
+    // camera): one ICP at a time per device; the lock is held until the results have been read back.
+    int cur_dev = 0;
+    B2R_CUDA(cudaGetDevice(&cur_dev));
+    static std::mutex icp_mu[16];
+    std::lock_guard<std::mutex> icp_lock(icp_mu[cur_dev & 15]);
     int nsm = 148;
-    cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, 0);
+    cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, cur_dev);
     unsigned grid = (unsigned)((N + ICP_THREADS - 1) / ICP_THREADS);
     if (grid > (unsigned)nsm * 4) grid = (unsigned)nsm * 4;
     const size_t max_cells = (size_t)8 << 20;

@@ -15,6 +15,7 @@
 //                      adds the partials in block order (deterministic), solves the 6x6 system by pivoted
 //                      LDLT and left-multiplies the pose, all in one launch.
 // Image filters keep upstream's rounding points (f64 accumulate, f32 store after each separable pass).
+#include <mutex>
 #include "common.cuh"
 #include "host_math.h"
 #include <math.h>
@@ -462,8 +463,14 @@ B2R_API int b2r_odometry(const float* src_gray, const float* src_depth, const fl
         off[l] = total_px; total_px += ((size_t)Wl[l] * Hl[l] + 63) & ~(size_t)63;
     }
     const size_t N0 = (size_t)W * H;
+    // Workspace and graph cache are process-global per device and a ctypes call releases the GIL (the reference runs one
+    // thread per camera): one odometry at a time per device; the lock is held until the result has been read back.
+    int cur_dev = 0;
+    B2R_CUDA(cudaGetDevice(&cur_dev));
+    static std::mutex odo_mu[16];
+    std::lock_guard<std::mutex> odo_lock(odo_mu[cur_dev & 15]);
     int nsm = 148;
-    cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, 0);
+    cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, cur_dev);
     const unsigned red_grid_max = (unsigned)nsm * 2;
     // workspace: 8 pyramids + 1 temp image + 4 staged inputs + zbuf + partials + state
     const size_t N0p = (N0 + 63) & ~(size_t)63;

@@ -796,16 +796,23 @@ __global__ void tsdf_clear_slots_kernel(B2RSlot* slots, uint32_t n) {
     slots[i] = s;
 }
 
+// zeroes the units allocated so far; the count is read ON THE DEVICE, so reset() needs no host round trip
+__global__ void tsdf_clear_pool_kernel(float4* pool, int64_t unit_f4, const int32_t* counters, int cap) {
+    const int n = min(counters[B2R_C_NUM_UNITS], cap);
+    const int64_t total = (int64_t)n * unit_f4;
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) pool[i] = z;
+}
+
 // volume.reset()  (bundlefusion_reconstruction.py:309, capture_frames.py:94).  Pending frames are dropped:
-// integrate-then-reset leaves an empty volume either way.
+// integrate-then-reset leaves an empty volume either way.  Fully asynchronous on `stream` (three launches, no copy back).
 B2R_API int b2r_tsdf_reset(b2r_tsdf* h, cudaStream_t stream) {
     if (!h) return B2R_ERR_BAD_ARG;
     B2RDeviceGuard g(h->device);
-    int32_t n = 0;
-    B2R_CUDA(cudaMemcpyAsync(&n, h->counters + B2R_C_NUM_UNITS, 4, cudaMemcpyDeviceToHost, stream));
-    B2R_CUDA(cudaStreamSynchronize(stream));
-    if (n > h->cap_units || n < 0) n = (int32_t)h->cap_units;
-    if (n) B2R_CUDA(cudaMemsetAsync(h->pool, 0, (size_t)n * h->planes * B2R_UNIT_VOX * sizeof(float), stream));
+    int nsm = 148;
+    cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, h->device);
+    tsdf_clear_pool_kernel<<<nsm * 8, 256, 0, stream>>>(reinterpret_cast<float4*>(h->pool), (int64_t)h->planes * (B2R_UNIT_VOX / 4), h->counters, (int)h->cap_units);
+    B2R_CHECK_LAUNCH();
     tsdf_clear_slots_kernel<<<(h->nslots + 255) / 256, 256, 0, stream>>>(h->hash.slots, h->nslots);
     B2R_CHECK_LAUNCH();
     B2R_CUDA(cudaMemsetAsync(h->counters, 0, B2R_C_WORDS * 4, stream));
@@ -1008,8 +1015,10 @@ B2R_API int b2r_tsdf_integrate_batch(b2r_tsdf* h, int n, const void* depth, int 
                                W, H, fx, fy, cx, cy, extrinsics, stream);
 }
 
-// Same, with HOST images (pinned for true overlap): each frame's H2D copy runs on an internal copy
-// stream into a 3-deep device ring while earlier frames are packed / fused on `stream`.
+// Same, with HOST images (pinned for true overlap): each chunk's H2D copy runs on an internal copy
+// stream into a B2R_HOST_RING-deep device ring while earlier frames are packed / fused on `stream`.
+// Lifetime contract: the host buffers must be fully written when the call is made (the copies do not wait for work
+// queued on `stream`); they may be reused or freed as soon as the call returns (it waits for its last copy).
 B2R_API int b2r_tsdf_integrate_host(b2r_tsdf* h, int n, const void* depth_host, int depth_is_u16, float depth_scale,
                                     float depth_trunc, const uint8_t* color_host, int color_channels, int color_bgr,
                                     int W, int H, double fx, double fy, double cx, double cy,
@@ -1040,7 +1049,7 @@ B2R_API int b2r_tsdf_integrate_host(b2r_tsdf* h, int n, const void* depth_host, 
         h->stage_depth_bytes = need_d; h->stage_color_bytes = need_c;
         h->host_seq = 0;
     }
-    int f = 0;
+    int f = 0, last_r = -1;
     while (f < n) {
         int room = h->max_batch - h->pending;
         if (room <= 0) room = h->max_batch;
@@ -1059,7 +1068,11 @@ B2R_API int b2r_tsdf_integrate_host(b2r_tsdf* h, int n, const void* depth_host, 
         B2R_CUDA(cudaEventRecord(h->ev_consumed[r], stream));   // K1 has packed the chunk: the ring slot is free
         h->host_seq++;
         f += take;
+        last_r = r;
     }
+    // The caller may free or rewrite its host buffer as soon as this returns (a pinned per-chunk temporary, say): wait -- on
+    // the HOST, for the copy engine only -- until the call's last H2D copy has left it.  K1 / K2 stay asynchronous.
+    if (last_r >= 0) B2R_CUDA(cudaEventSynchronize(h->ev_copied[last_r]));
     return B2R_OK;
 }
 
@@ -1167,13 +1180,14 @@ __global__ void tsdf_import_keys_kernel(B2RHash hash, int32_t* unit_keys, int32_
     atomicOr(&counters[B2R_C_ERR], 4);
 }
 
+// one CTA per (unit, quarter): the unit index rides on grid.x (up to 2^31 - 1 blocks), not on grid.y (65 535)
 __global__ void tsdf_import_planes_kernel(float* pool, int64_t unit_stride, int planes, const int32_t* ids, int n,
                                           const float* tsdf, const float* weight, const float* rgb) {
-    const int u = blockIdx.y;
+    const int u = blockIdx.x >> 2, part = blockIdx.x & 3;
     const int id = ids[u];
     if (id < 0) return;
-    for (int v = blockIdx.x * blockDim.x + threadIdx.x; v < B2R_UNIT_VOX; v += gridDim.x * blockDim.x) {
-        float* base = pool + (int64_t)id * unit_stride;
+    float* base = pool + (int64_t)id * unit_stride;
+    for (int v = part * 1024 + threadIdx.x; v < (part + 1) * 1024; v += blockDim.x) {
         base[v] = tsdf[(int64_t)u * B2R_UNIT_VOX + v];
         base[B2R_UNIT_VOX + v] = weight[(int64_t)u * B2R_UNIT_VOX + v];
         if (planes == 5 && rgb)
@@ -1185,7 +1199,7 @@ __global__ void tsdf_import_planes_kernel(float* pool, int64_t unit_stride, int 
 // Used to load analytic volumes in tests and to restore a saved volume.
 B2R_API int b2r_tsdf_import_units(b2r_tsdf* h, const int32_t* keys3, int64_t n, const float* tsdf, const float* weight,
                                   const float* rgb, cudaStream_t stream) {
-    if (!h || !keys3 || !tsdf || !weight || n < 0) return B2R_ERR_BAD_ARG;
+    if (!h || !keys3 || !tsdf || !weight || n < 0 || n > (1 << 28)) return B2R_ERR_BAD_ARG;
     if (n == 0) return B2R_OK;
     B2RDeviceGuard g(h->device);
     int rc = b2r_tsdf_flush_pending(h, stream);
@@ -1196,8 +1210,7 @@ B2R_API int b2r_tsdf_import_units(b2r_tsdf* h, const int32_t* keys3, int64_t n, 
     int32_t* ids = (int32_t*)h->scratch;
     tsdf_import_keys_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(h->hash, h->unit_keys, h->counters, keys3, (int)n, (int)h->cap_units, ids);
     B2R_CHECK_LAUNCH();
-    dim3 grid(4, (unsigned)n);
-    tsdf_import_planes_kernel<<<grid, 256, 0, stream>>>(h->pool, (int64_t)h->planes * B2R_UNIT_VOX, h->planes, ids, (int)n, tsdf, weight, rgb);
+    tsdf_import_planes_kernel<<<(unsigned)(4 * n), 256, 0, stream>>>(h->pool, (int64_t)h->planes * B2R_UNIT_VOX, h->planes, ids, (int)n, tsdf, weight, rgb);
     B2R_CHECK_LAUNCH();
     return B2R_OK;
 }

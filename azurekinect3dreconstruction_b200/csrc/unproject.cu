@@ -890,6 +890,27 @@ B2R_API int b2r_depth_to_float(const uint16_t* depth, int64_t n, float depth_sca
     B2R_CHECK_LAUNCH();
     return B2R_OK;
 }
+// ConvertDepthToFloatImage on the other 1-channel depth types upstream's CreateFloatImage accepts:
+// dtype 1 = f32 (copied, then / scale), dtype 2 = u8 (/ 255.0f first), dtype 0 = u16 (same as b2r_depth_to_float).
+template <typename T, bool DIV255>
+__global__ void depth_any_to_float_kernel(const T* in, int64_t n, float scale, float trunc, float* out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float d = (float)in[i];
+    if (DIV255) d = xfdiv(d, 255.0f);
+    d = xfdiv(d, scale);
+    if (d >= trunc) d = 0.0f;
+    out[i] = d;
+}
+B2R_API int b2r_depth_to_float_typed(const void* depth, int dtype, int64_t n, float depth_scale, float depth_trunc, float* out, cudaStream_t stream) {
+    if (!depth || !out || n < 0 || dtype < 0 || dtype > 2) return B2R_ERR_BAD_ARG;
+    const unsigned g = (unsigned)((n + 255) / 256);
+    if (n && dtype == 0) depth_to_float_kernel<<<g, 256, 0, stream>>>((const uint16_t*)depth, n, depth_scale, depth_trunc, out);
+    if (n && dtype == 1) depth_any_to_float_kernel<float, false><<<g, 256, 0, stream>>>((const float*)depth, n, depth_scale, depth_trunc, out);
+    if (n && dtype == 2) depth_any_to_float_kernel<uint8_t, true><<<g, 256, 0, stream>>>((const uint8_t*)depth, n, depth_scale, depth_trunc, out);
+    B2R_CHECK_LAUNCH();
+    return B2R_OK;
+}
 B2R_API int b2r_rgb_to_intensity(const uint8_t* rgb, int64_t n, int channels, int bgr, float* out, cudaStream_t stream) {
     if (!rgb || !out || n < 0 || (channels != 3 && channels != 4)) return B2R_ERR_BAD_ARG;
     if (n) rgb_to_intensity_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(rgb, n, channels, bgr, out);

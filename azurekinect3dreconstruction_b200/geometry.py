@@ -89,18 +89,12 @@ class RGBDImage:
         n = dt.numel()
         if dt.dim() != 2:
             raise RuntimeError("[CreateFromColorAndDepth] Unsupported image format.")
-        if dt.dtype == torch.uint16:
-            _lib.require_cuda()
-            f = torch.empty(dt.shape, dtype=torch.float32, device=dt.device)
-            _lib.check(lib.b2r_depth_to_float(_lib.ptr(dt), n, float(depth_scale), float(depth_trunc), _lib.ptr(f), _lib.stream_ptr()))
-        elif dt.dtype == torch.float32:
-            f = dt / np.float32(depth_scale)          # ConvertDepthToFloatImage on an f32 image
-            f = torch.where(f >= np.float32(depth_trunc), torch.zeros_like(f), f)
-        elif dt.dtype == torch.uint8:
-            f = dt.to(torch.float32) / np.float32(255.0) / np.float32(depth_scale)
-            f = torch.where(f >= np.float32(depth_trunc), torch.zeros_like(f), f)
-        else:
+        kind = {torch.uint16: 0, torch.float32: 1, torch.uint8: 2}.get(dt.dtype)     # ConvertDepthToFloatImage's 1-channel types
+        if kind is None:
             raise RuntimeError("[CreateFromColorAndDepth] Unsupported image format.")
+        _lib.require_cuda()
+        f = torch.empty(dt.shape, dtype=torch.float32, device=dt.device)
+        _lib.check(lib.b2r_depth_to_float_typed(_lib.ptr(dt), kind, n, float(depth_scale), float(depth_trunc), _lib.ptr(f), _lib.stream_ptr()))
         out.depth = Image(f)
         ct = color.tensor
         if convert_rgb_to_intensity:

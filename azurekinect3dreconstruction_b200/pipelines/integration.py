@@ -90,6 +90,22 @@ class ScalableTSDFVolume:
         (the reset + re-integrate loop of bundlefusion_reconstruction.py:309-315). Device or pinned-host tensors."""
         if depth_u16.dim() == 2:
             depth_u16, color_u8 = depth_u16[None], (color_u8[None] if color_u8 is not None else None)
+        # upstream's format check (SURVEY A.4), applied to the raw batch: anything else would make K1 read out of bounds
+        bad = depth_u16.dim() != 3 or depth_u16.dtype not in (torch.uint16, torch.float32) or not depth_u16.is_contiguous() \
+            or tuple(depth_u16.shape[1:]) != (intrinsic.height, intrinsic.width)
+        if self.color_type == TSDFVolumeColorType.RGB8:
+            bad = bad or color_u8 is None or color_u8.dtype != torch.uint8 or color_u8.dim() != 4 or color_u8.shape[3] not in (3, 4) \
+                or tuple(color_u8.shape[:3]) != tuple(depth_u16.shape) or color_u8.device != depth_u16.device or not color_u8.is_contiguous()
+        elif self.color_type == TSDFVolumeColorType.Gray32:
+            bad = True                                   # Gray32 volumes take RGBDImages through integrate()
+        else:
+            color_u8 = None
+        if bad:
+            raise RuntimeError("[ScalableTSDFVolume::Integrate] Unsupported image format.")
+        if not depth_u16.is_cuda and not depth_u16.is_pinned():
+            # pageable host frames: stage through pinned memory so the copy ring stays asynchronous
+            depth_u16 = depth_u16.view(torch.int16).pin_memory().view(torch.uint16) if depth_u16.dtype == torch.uint16 else depth_u16.pin_memory()
+            color_u8 = color_u8.pin_memory() if color_u8 is not None else None
         B, H, W = depth_u16.shape
         E = np.ascontiguousarray(np.asarray(extrinsics, dtype=np.float64).reshape(-1))
         if E.size != 16 * B:

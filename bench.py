@@ -14,7 +14,11 @@ units, depth_sampling_stride 4.  One STEP = volume.reset() + integrate all frame
             x frames per launch over its CUDA-event duration, against MEASURED_PEAKS.json hbm_gbs; the same
             for strictly per-frame launches (batch 1) under "single_frame_pass".
 * cpu_baseline: the CPU oracle (port of Open3D 0.19 legacy semantics; Open3D itself cannot be installed
-            here) on a bounded sample of the same frames, all host threads.
+            here) on the SAME 300-frame step, all host threads, one timed pass; `upstream_structure` = the same code
+            parallelised as upstream is (OpenMP over x inside one unit) on the first frames of the trajectory.
+* parity_checked: after that pass the GPU volume of the same frames is compared with the oracle's (unit-key set,
+            TSDF + weight bit-exact, colour <= 1e-3, updated-voxel / (unit, frame) counters, mesh topology).
+* --impl reference: the CPU arm on the same config: every step = reset + all 300 frames.
 * N > 1   : the volume is sharded by unit-key hash; every rank sees every frame (resident in its
             HBM) and integrates only its own units; no data-path collective; strong scaling.
 """
@@ -47,19 +51,19 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--frames", type=int, default=300)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--ref-frames", type=int, default=6, help="frames per step of the CPU reference arm")
+    ap.add_argument("--upstream-frames", type=int, default=40, help="frames of the upstream-structure (OpenMP inside a unit) CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the secondary records (configs 1, 2, 4, 5, per-frame API)")
     return ap.parse_args()
 
 
-def workload_config(args, extra=None):
-    cfg = {"workload": "configs[2]: ScalableTSDFVolume.integrate over a %d-frame synthetic orbit, NFOV 640x576 u16 depth + "
-                       "aligned u8 RGB, voxel 4 mm, sdf_trunc 2 cm, unit 16^3, stride 4; step = reset + all frames" % args.frames,
-           "frames_per_step": args.frames, "voxel_length": VOXEL, "sdf_trunc": TRUNC, "color_type": "RGB8",
-           "l2_policy": "inputs (%.0f MB of frames) and the touched voxel pool are larger than the 126 MB L2" % (args.frames * 1.84)}
-    if extra:
-        cfg.update(extra)
-    return cfg
+def workload_config(args):
+    """Identical in both arms (b200 / reference) for the same command line: it names the workload, nothing else."""
+    return {"workload": "configs[2]: ScalableTSDFVolume.integrate over a %d-frame synthetic orbit, NFOV 640x576 u16 depth + "
+                        "aligned u8 RGB, voxel 4 mm, sdf_trunc 2 cm, unit 16^3, stride 4; step = reset + all frames" % args.frames,
+            "frames_per_step": args.frames, "voxel_length": VOXEL, "sdf_trunc": TRUNC, "color_type": "RGB8",
+            "depth_scale": DEPTH_SCALE, "depth_trunc": DEPTH_TRUNC,
+            "l2_policy": "inputs (%.0f MB of frames) and the touched voxel pool are larger than the 126 MB L2" % (args.frames * 1.84)}
 
 
 def make_frames(n_frames, device, trajectory_len=None):
@@ -128,12 +132,14 @@ def hbm_peak():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def cpu_reference(depth_np, rgb_np, E, intr, n_frames, steps, warmup):
-    """Times the CPU oracle (Open3D-legacy port, OpenMP over units, all host threads). Returns (frames/s, ms/step, cores)."""
+def cpu_reference(depth_np, rgb_np, E, intr, n_frames, steps, warmup, parallel_units=True, keep=False):
+    """Times the CPU oracle (Open3D-legacy port, all host threads) on reset + n_frames frames per step.
+    parallel_units=True: OpenMP over volume units; False: upstream's structure (OpenMP over x inside one unit).
+    Returns (frames/s, ms/step, cores[, the volume of the last step])."""
     from oracle import o3r
     o3r.set_num_threads(os.cpu_count() or 1)       # all host cores, also under torchrun (which exports OMP_NUM_THREADS=1)
     Kt = (intr["fx"], intr["fy"], intr["cx"], intr["cy"])
-    vol = o3r.TSDF(VOXEL, TRUNC, 1, 16, 4, parallel_units=True)
+    vol = o3r.TSDF(VOXEL, TRUNC, 1, 16, 4, parallel_units=parallel_units)
     times = []
     for s in range(warmup + steps):
         vol.reset()
@@ -146,28 +152,38 @@ def cpu_reference(depth_np, rgb_np, E, intr, n_frames, steps, warmup):
         if s >= warmup:
             times.append(dt)
     total = sum(times)
-    return n_frames * len(times) / total, 1e3 * total / len(times), o3r.num_threads()
+    out = (n_frames * len(times) / total, 1e3 * total / len(times), o3r.num_threads())
+    return out + (vol,) if keep else out
+
+
+def upstream_structure_sample(depth_np, rgb_np, E, intr, nf):
+    fps, ms, cores = cpu_reference(depth_np[:nf], rgb_np[:nf], E[:nf], intr, nf, 1, 0, parallel_units=False)
+    return {"value": fps, "unit": "frames/s", "cores": cores,
+            "sample": "reset + first %d frames of the trajectory, OpenMP over x inside one unit (upstream's loop structure), 1 pass" % nf}
 
 
 def run_reference(args):
     """--impl reference: the reference's own CPU implementation of the path.  Open3D 0.19 cannot be installed or
     compiled here (no sources under /root/reference, no network), so this is the oracle port, all host threads,
-    on a bounded sample (the first --ref-frames frames of the same trajectory per step)."""
+    on the SAME config as the b200 arm: every step = reset + all frames of the trajectory."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     import torch
-    nf = max(1, min(args.ref_frames, args.frames))
-    depth, rgb, E, intr = make_frames(nf, torch.device("cpu"), args.frames)
-    depth_np = depth.view(torch.int16).numpy().view(np.uint16)
-    rgb_np = rgb.numpy()
-    fps, ms, cores = cpu_reference(depth_np, rgb_np, E, intr, nf, args.steps, args.warmup)
+    # the synthetic frames are rendered wherever it is fastest (input generation is not part of the timed path)
+    rdev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0"))) if torch.cuda.is_available() else torch.device("cpu")
+    depth, rgb, E, intr = make_frames(args.frames, rdev)
+    depth_np = depth.cpu().view(torch.int16).numpy().view(np.uint16)
+    rgb_np = rgb.cpu().numpy()
+    fps, ms, cores = cpu_reference(depth_np, rgb_np, E, intr, args.frames, args.steps, args.warmup)
+    up = upstream_structure_sample(depth_np, rgb_np, E, intr, max(1, min(args.upstream_frames, args.frames)))
     line = {"metric": "tsdf_integrated_depth_frames_per_sec_640x576", "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
-            "config": workload_config(args, {"sample": "first %d frames of the trajectory per step" % nf}),
+            "config": workload_config(args),
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
-                             "sample": "reset + first %d frames of the %d-frame trajectory per step, OpenMP over volume units" % (nf, args.frames)},
+                             "sample": "the whole step: reset + all %d frames, OpenMP over volume units" % args.frames,
+                             "upstream_structure": up},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
@@ -266,12 +282,16 @@ def main():
     kp = kernel_pass(batch)
     k1 = kernel_pass(1)                                 # strictly per-frame fusion: the streaming (HBM-bound) form
     vol.set_batch(batch)
+    # DRAM bytes per launch come from one `ncu --set full` capture of this same command; they are quoted only when the capture
+    # matches this run (GPU count, frames per launch), else null
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "fuse_kernel_traffic.json")
     if os.path.exists(tpath):
         try:
             with open(tpath) as f:
-                traffic = json.load(f).get("dram_bytes_per_launch")
+                tj = json.load(f)
+            if int(tj.get("n_gpus", 1)) == world and int(tj.get("frames", 0)) == args.frames and int(tj.get("batch", 0)) == batch:
+                traffic = tj.get("dram_bytes_per_launch")
         except Exception:
             traffic = None
     roofline = {"kernel": "tsdf_fuse_kernel<RGB8> (batch of %d frames per pass)" % batch, "bound": "hbm", "achieved": kp["achieved"],
@@ -317,25 +337,33 @@ def main():
         raise RuntimeError("e2e arm diverged from the device arm: %r vs %r" % (st_e2e, st))
     h2d_bytes = int(depth_h.numel() * 2 + rgb_h.numel())
 
-    # ---- CPU baseline (rank 0, bounded sample) ---------------------------------------------------------
-    cpu = None
+    # ---- CPU baseline (rank 0, N = 1): the same 300-frame step on the host cores, then the parity check -----------------
+    cpu = parity = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        nf = max(1, min(args.ref_frames, args.frames))
-        dn = depth_h[:nf].view(torch.int16).numpy().view(np.uint16)
-        cn = rgb_h[:nf].numpy()
-        cfps, cms, cores = cpu_reference(dn, cn, E[:nf], intr, nf, 2, 1)
+        from oracle import compare
+        dn = depth_h.view(torch.int16).numpy().view(np.uint16)
+        cn = rgb_h.numpy()
+        cfps, cms, cores, ref_vol = cpu_reference(dn, cn, E, intr, args.frames, 1, 0, keep=True)
         cpu = {"value": cfps, "unit": "frames/s", "cores": cores, "kind": "port",
-               "sample": "reset + first %d frames of the trajectory, 2 timed passes, OpenMP over volume units" % nf}
+               "sample": "the whole step: reset + all %d frames, 1 timed pass, OpenMP over volume units" % args.frames,
+               "upstream_structure": upstream_structure_sample(dn, cn, E, intr, max(1, min(args.upstream_frames, args.frames)))}
+        # the volume the e2e arm just left behind (same frames, host ingest, batch 32) against the oracle's
+        parity = {"frames": args.frames}
+        parity.update(compare.volume_vs_oracle(vol, ref_vol))
+        parity["bit_exact"] = bool(parity["tsdf_weight_bit_exact"] and parity["counters_equal"])
+        parity["mesh"] = compare.mesh_vs_oracle(vol, ref_vol, VOXEL)
+        del ref_vol
 
     if rank == 0:
         line = {"metric": "tsdf_integrated_depth_frames_per_sec_640x576", "value": fps, "unit": "frames/s", "n_gpus": n_gpus,
                 "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": workload_config(args, {"sharding": "unit-key hash over %d rank(s)" % world, "units_allocated_rank0": st["num_units"]}),
-                "roofline": roofline, "cpu_baseline": cpu,
+                "config": workload_config(args), "impl": "b200",
+                "sharding": {"rule": "unit-key hash over %d rank(s)" % world, "units_allocated_rank0": st["num_units"]},
+                "roofline": roofline, "cpu_baseline": cpu, "parity_checked": parity,
                 "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes * world,
                         "ms_per_step": ms_e2e / args.steps,
-                        "ingest": ("host frames -> one GPU over PCIe (3-deep staged ring)" if world == 1 else
+                        "ingest": ("host frames -> one GPU over PCIe (6-deep ring of 8-frame chunks)" if world == 1 else
                                    "each rank uploads 1/%d of the frames over its PCIe link; NCCL all-gather over NVLink hands every rank all frames "
                                    "(h2d_bytes_per_step is the whole job's)" % world)},
                 "gpu_launches": args.steps * n_launches_step, "clocks": clocks}

@@ -55,6 +55,9 @@ int b2r_unit_owner(int kx, int ky, int kz, int world);
  *      GoodColorReconstruction.py:131-137, RGBD_Odometry.py:15-18).  Normally fused into consumers. */
 int b2r_depth_to_float(const uint16_t* depth, int64_t n, float depth_scale, float depth_trunc, float* out,
                        cudaStream_t stream);
+/* the other 1-channel depth types upstream's ConvertDepthToFloatImage accepts: dtype 0 = u16, 1 = f32, 2 = u8 (/255 first) */
+int b2r_depth_to_float_typed(const void* depth, int dtype, int64_t n, float depth_scale, float depth_trunc, float* out,
+                             cudaStream_t stream);
 int b2r_rgb_to_intensity(const uint8_t* rgb, int64_t n, int channels, int bgr, float* out, cudaStream_t stream);
 
 /* ---- a3/a4/a5/a6: PointCloud.create_from_rgbd_image / create_from_depth_image (+ fused a1 conversion,

@@ -26,7 +26,8 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    srcs = [os.path.join(_DIR, f) for f in ("oracle.cpp", "oracle_pcd.cpp")]
+    srcs = [os.path.join(_DIR, f) for f in ("oracle.cpp", "oracle_pcd.cpp")] + \
+           [os.path.join(os.path.dirname(_DIR), "azurekinect3dreconstruction_b200", "csrc", "mc_tables.h")]
     if not os.path.exists(_LIB) or any(os.path.exists(f) and os.path.getmtime(f) > os.path.getmtime(_LIB) for f in srcs):
         subprocess.run(["make", "-C", _DIR], check=True, capture_output=True)
     L = C.CDLL(_LIB)
@@ -41,12 +42,14 @@ def lib():
     L.o3r_tsdf_destroy.argtypes = [_vp]
     L.o3r_tsdf_reset.argtypes = [_vp]
     L.o3r_tsdf_set_parallel_units.argtypes = [_vp, _i]
-    for n in ("o3r_tsdf_num_units", "o3r_tsdf_last_updated", "o3r_tsdf_last_touched", "o3r_tsdf_extract_points"):
+    for n in ("o3r_tsdf_num_units", "o3r_tsdf_last_updated", "o3r_tsdf_last_touched", "o3r_tsdf_total_updated", "o3r_tsdf_total_touched",
+              "o3r_tsdf_extract_points"):
         getattr(L, n).restype = _i64
         getattr(L, n).argtypes = [_vp]
     L.o3r_tsdf_integrate.argtypes = [_vp, _vp, _vp, _vp, _i, _i, _d, _d, _d, _d, _vp]
     L.o3r_tsdf_export_keys.argtypes = [_vp, _vp]
     L.o3r_tsdf_export_unit.argtypes = [_vp, _vp, _vp, _vp, _vp]
+    L.o3r_tsdf_export_range.argtypes = [_vp, _i64, _i64, _vp, _vp, _vp, _vp]
     L.o3r_tsdf_import_unit.argtypes = [_vp, _vp, _vp, _vp, _vp]
     L.o3r_tsdf_extract_points_copy.argtypes = [_vp, _vp, _vp, _vp]
     L.o3r_tsdf_extract_mesh.restype = _i64
@@ -176,6 +179,27 @@ class TSDF:
 
     def last_touched(self):
         return int(lib().o3r_tsdf_last_touched(self.h))
+
+    def total_updated(self):
+        """Voxel records changed since the last reset (the roofline numerator N_upd)."""
+        return int(lib().o3r_tsdf_total_updated(self.h))
+
+    def total_touched(self):
+        """(unit, frame) pairs fused since the last reset."""
+        return int(lib().o3r_tsdf_total_touched(self.h))
+
+    def export_range(self, first=0, count=None):
+        """Units [first, first+count) in first-touch order: keys (n,3) i32, tsdf (n,res^3) f32, weight (n,res^3) f32,
+        rgb (n,3,res^3) f64 or None."""
+        n = self.num_units()
+        count = n - first if count is None else min(count, n - first)
+        nv = self.res ** 3
+        keys = np.empty((count, 3), np.int32)
+        t, w = np.empty((count, nv), np.float32), np.empty((count, nv), np.float32)
+        c = np.empty((count, 3, nv), np.float64) if self.color_type else None
+        if count:
+            lib().o3r_tsdf_export_range(self.h, first, count, _p(keys), _p(t), _p(w), _p(c))
+        return keys, t, w, c
 
     def keys(self):
         k = np.empty((self.num_units(), 3), np.int32)

@@ -32,7 +32,7 @@
 #endif
 
 #define MC_TABLE_QUAL static const
-#include "mc_tables.h"
+#include "../azurekinect3dreconstruction_b200/csrc/mc_tables.h"   // the one generated copy of the constant tables (tools/gen_mc_tables.py)
 
 #define O3R_API extern "C" __attribute__((visibility("default")))
 
@@ -378,6 +378,8 @@ struct Volume {
     std::vector<std::unique_ptr<Unit>> units;
     int64_t last_updated = 0;  // voxels whose record changed in the last integrate (N_upd)
     int64_t last_touched = 0;
+    int64_t total_updated = 0;  // the same, summed over every integrate since the last reset
+    int64_t total_touched = 0;  // (unit, frame) pairs since the last reset
 
     int find(const Key& k) const {
         auto it = map.find(k);
@@ -483,11 +485,14 @@ O3R_API void o3r_tsdf_reset(void* h) {
     auto* v = (Volume*)h;
     v->map.clear();
     v->units.clear();
+    v->last_updated = v->last_touched = v->total_updated = v->total_touched = 0;
 }
 O3R_API void o3r_tsdf_set_parallel_units(void* h, int on) { ((Volume*)h)->parallel_units = on; }
 O3R_API int64_t o3r_tsdf_num_units(void* h) { return (int64_t)((Volume*)h)->units.size(); }
 O3R_API int64_t o3r_tsdf_last_updated(void* h) { return ((Volume*)h)->last_updated; }
 O3R_API int64_t o3r_tsdf_last_touched(void* h) { return ((Volume*)h)->last_touched; }
+O3R_API int64_t o3r_tsdf_total_updated(void* h) { return ((Volume*)h)->total_updated; }
+O3R_API int64_t o3r_tsdf_total_touched(void* h) { return ((Volume*)h)->total_touched; }
 
 // ScalableTSDFVolume::Integrate.  depth: f32 metres W x H; colour: u8x3 (RGB8) or f32 (Gray32).
 // Returns 0, or -1 on the upstream "Unsupported image format" condition (checked by the caller's
@@ -540,6 +545,8 @@ O3R_API int o3r_tsdf_integrate(void* h, const float* depth, const uint8_t* rgb, 
     }
     V.last_updated = updated;
     V.last_touched = (int64_t)order.size();
+    V.total_updated += updated;
+    V.total_touched += (int64_t)order.size();
     return 0;
 }
 
@@ -561,6 +568,25 @@ O3R_API int o3r_tsdf_export_unit(void* h, const int32_t* key, float* tsdf, float
         if (rgb) { rgb[3 * i] = vox[i].color[0]; rgb[3 * i + 1] = vox[i].color[1]; rgb[3 * i + 2] = vox[i].color[2]; }
     }
     return 0;
+}
+
+// Bulk export of units [first, first + count) in the oracle's own unit order (first-touch order), as planes:
+// keys3 [count][3], tsdf / weight [count][res^3], rgb [count][3][res^3] f64 (may be null) -- the layout the full-size
+// parity tests upload and compare on the GPU in one go.
+O3R_API void o3r_tsdf_export_range(void* h, int64_t first, int64_t count, int32_t* keys3, float* tsdf, float* weight, double* rgb) {
+    auto& V = *(Volume*)h;
+    const size_t nv = (size_t)V.res * V.res * V.res;
+#pragma omp parallel for schedule(static)
+    for (int64_t u = 0; u < count; u++) {
+        const Unit& U = *V.units[(size_t)(first + u)];
+        keys3[3 * u] = U.index.x; keys3[3 * u + 1] = U.index.y; keys3[3 * u + 2] = U.index.z;
+        for (size_t i = 0; i < nv; i++) {
+            tsdf[(size_t)u * nv + i] = U.voxels[i].tsdf;
+            weight[(size_t)u * nv + i] = U.voxels[i].weight;
+            if (rgb)
+                for (int c = 0; c < 3; c++) rgb[((size_t)u * 3 + c) * nv + i] = U.voxels[i].color[c];
+        }
+    }
 }
 
 // Test hook: write one unit's voxels directly (used to build analytic SDF volumes for MC tests).
@@ -764,6 +790,9 @@ O3R_API void o3r_tsdf_extract_mesh_copy(double* vtx, double* vcol, int32_t* tri,
 // TriangleMesh::ComputeVertexNormals (called right after extract_triangle_mesh, e.g.
 // GoodColorReconstruction.py:286; SURVEY A.5 last paragraph).
 O3R_API void o3r_mesh_vertex_normals(const double* vtx, int64_t nV, const int32_t* tri, int64_t nF, double* out) {
+    // upstream: ComputeTriangleNormals(false) -- the UN-normalised cross products (area weighted) are summed per vertex in
+    // triangle order, then NormalizeNormals(): Eigen's normalize() leaves a zero vector alone (z > 0 test), and a NaN
+    // result becomes (0, 0, 1).
     std::fill(out, out + 3 * nV, 0.0);
     for (int64_t t = 0; t < nF; t++) {
         const double* a = vtx + 3 * tri[3 * t];
@@ -771,15 +800,14 @@ O3R_API void o3r_mesh_vertex_normals(const double* vtx, int64_t nV, const int32_
         const double* c = vtx + 3 * tri[3 * t + 2];
         double e1[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]}, e2[3] = {c[0] - a[0], c[1] - a[1], c[2] - a[2]};
         double n[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
-        double len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
-        if (len > 0) { n[0] /= len; n[1] /= len; n[2] /= len; }
         for (int k = 0; k < 3; k++)
             for (int q = 0; q < 3; q++) out[3 * tri[3 * t + k] + q] += n[q];
     }
     for (int64_t v = 0; v < nV; v++) {
         double* n = out + 3 * v;
-        double len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
-        if (len > 0) { n[0] /= len; n[1] /= len; n[2] /= len; }
+        double z = n[0] * n[0] + n[1] * n[1] + n[2] * n[2];
+        if (z > 0) { double len = std::sqrt(z); n[0] /= len; n[1] /= len; n[2] /= len; }
+        if (std::isnan(n[0])) { n[0] = 0.0; n[1] = 0.0; n[2] = 1.0; }
     }
 }
 

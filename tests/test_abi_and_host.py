@@ -96,13 +96,22 @@ def test_image_and_rgbd_host_checks():
     assert d16.bytes_per_channel == 2 and np.array_equal(np.asarray(d16), np.arange(48, dtype=np.uint16).reshape(6, 8))
     with pytest.raises(RuntimeError, match="Unsupported image format"):
         o3d.geometry.RGBDImage.create_from_color_and_depth(img, o3d.geometry.Image(np.zeros((6, 9), np.uint16)))
-    # f32 depth + f32 colour needs no kernel: ConvertDepthToFloatImage still divides by depth_scale
+    # f32 depth: ConvertDepthToFloatImage still divides by depth_scale -- on the library (b2r_depth_to_float_typed);
+    # without a CUDA device the shim refuses instead of computing on the host (no CPU fallback)
     f = o3d.geometry.Image(np.full((6, 8), 1500.0, np.float32))
     g = o3d.geometry.Image(np.full((6, 8), 0.5, np.float32))
+    import torch
+    if not torch.cuda.is_available():
+        with pytest.raises(RuntimeError, match="no CPU fallback"):
+            o3d.geometry.RGBDImage.create_from_color_and_depth(g, f, 1000.0, 3.0, True)
+        return
     rgbd = o3d.geometry.RGBDImage.create_from_color_and_depth(g, f, 1000.0, 3.0, True)
     assert np.all(np.asarray(rgbd.depth) == 1.5) and np.all(np.asarray(rgbd.color) == 0.5)
     rgbd = o3d.geometry.RGBDImage.create_from_color_and_depth(g, f, 1000.0, 1.5, True)
     assert np.all(np.asarray(rgbd.depth) == 0.0)                          # >= trunc -> 0
+    d8 = o3d.geometry.Image(np.full((6, 8), 51, np.uint8))                # 1-channel u8 depth: / 255.0f first
+    rgbd = o3d.geometry.RGBDImage.create_from_color_and_depth(g, d8, 0.1, 3.0, True)
+    assert np.all(np.asarray(rgbd.depth) == np.float32(np.float32(51) / np.float32(255.0)) / np.float32(0.1))
 
 
 def test_pointcloud_merge_semantics_and_vectors():
@@ -142,14 +151,14 @@ def test_marching_cubes_tables_are_valid():
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     import gen_mc_tables as g
     assert g.validate()
-    # both generated headers are current
+    # the generated header (one copy, shared by the CUDA and the oracle builds) is current
     import tempfile
     with tempfile.TemporaryDirectory() as td:
         p = os.path.join(td, "mc_tables.h")
         g.emit(p)
         ref = open(p).read()
-    for rel in ("azurekinect3dreconstruction_b200/csrc/mc_tables.h", "oracle/mc_tables.h"):
-        assert open(os.path.join(ROOT, rel)).read() == ref
+    assert open(os.path.join(ROOT, "azurekinect3dreconstruction_b200/csrc/mc_tables.h")).read() == ref
+    assert not os.path.exists(os.path.join(ROOT, "oracle/mc_tables.h"))
 
 
 def test_synthetic_source_contract(small_kinect, tmp_path):
