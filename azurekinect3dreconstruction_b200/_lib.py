@@ -45,6 +45,7 @@ SIGNATURES = {
     "b2r_tsdf_capacity": (_i64, [_vp]),
     "b2r_tsdf_integrate": (_i, [_vp, _vp, _i, _f, _f, _vp, _i, _i, _vp, _i, _i, _d, _d, _d, _d, _pd, _vp]),
     "b2r_tsdf_integrate_batch": (_i, [_vp, _i, _vp, _i, _f, _f, _vp, _i, _i, _i, _i, _d, _d, _d, _d, _pd, _vp]),
+    "b2r_tsdf_integrate_frames": (_i, [_vp, _i, _vp, _i, _f, _f, _vp, _i, _i, _i, _i, _d, _d, _d, _d, _pd, _vp]),
     "b2r_tsdf_integrate_host": (_i, [_vp, _i, _vp, _i, _f, _f, _vp, _i, _i, _i, _i, _d, _d, _d, _d, _pd, _vp]),
     "b2r_tsdf_stats": (_i, [_vp, _pi64, _vp]),
     "b2r_tsdf_profile": (_i, [_vp, _i]),

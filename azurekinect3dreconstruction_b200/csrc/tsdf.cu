@@ -882,10 +882,13 @@ static bool host_ddiv_domain(double b) {   // positive, 2^-60 <= b < 2^60, signi
     const uint64_t e = u >> 52, m = u & 0xFFFFFFFFFFFFFull;
     return e >= 1023 - 60 && e < 1023 + 60 && m != 0xFFFFFFFFFFFFFull;
 }
+// Frames are either stored back to back (depth / color / gray = base pointers) or scattered (depth_ptrs / color_ptrs = HOST
+// arrays of nf device pointers, e.g. the slots of an all-gather buffer in the order they are to be fused).
 static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth_is_u16, float depth_scale, float depth_trunc,
                                const uint8_t* color, int color_channels, int color_bgr, const float* gray, int W,
                                int H, double fx, double fy, double cx, double cy, const double* extrinsics,
-                               cudaStream_t stream) {
+                               cudaStream_t stream, const void* const* depth_ptrs = nullptr, const uint8_t* const* color_ptrs = nullptr) {
+    if (depth_ptrs) { depth = depth_ptrs[0]; if (color_ptrs) color = color_ptrs[0]; }
     if (!h || !depth || !extrinsics || W < 1 || H < 1 || nf < 1) { b2r_set_error("b2r_tsdf_integrate: bad argument"); return B2R_ERR_BAD_ARG; }
     // upstream: "[ScalableTSDFVolume::Integrate] Unsupported image format."
     if (h->color_type == 1 && (!color || (color_channels != 3 && color_channels != 4))) { b2r_set_error("[ScalableTSDFVolume::Integrate] Unsupported image format."); return B2R_ERR_FORMAT; }
@@ -950,8 +953,9 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
             if (!b2r::m4_inverse(E, pose)) { b2r_set_error("b2r_tsdf_integrate: singular extrinsic"); return B2R_ERR_SINGULAR; }
             const int slot = h->pending + f;
             PackFrame& pf = P.fr[f];
-            pf.depth = (const char*)depth + (size_t)(done + f) * dstep;
-            pf.color = (h->color_type == 1) ? color + (size_t)(done + f) * cstep : nullptr;
+            pf.depth = depth_ptrs ? depth_ptrs[done + f] : (const void*)((const char*)depth + (size_t)(done + f) * dstep);
+            pf.color = (h->color_type == 1) ? (color_ptrs ? color_ptrs[done + f] : color + (size_t)(done + f) * cstep) : nullptr;
+            if (!pf.depth || (h->color_type == 1 && !pf.color)) { b2r_set_error("b2r_tsdf_integrate_frames: null frame pointer"); return B2R_ERR_BAD_ARG; }
             pf.gray = (h->color_type == 2) ? gray + (size_t)(done + f) * npx : nullptr;
             pf.texel = h->texel[slot];
             for (int i = 0; i < 12; i++) pf.pose[i] = pose[i];
@@ -969,6 +973,8 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
             const size_t cb = (h->color_type == 1) ? (size_t)color_channels : (h->color_type == 2 ? 4 : 0);
             P.tma_ok = (npx % 16 == 0) && ((uintptr_t)depth % 16 == 0) && (dstep % 16 == 0) &&
                        (cb == 0 || ((uintptr_t)cimg % 16 == 0 && (npx * cb) % 16 == 0)) ? 1 : 0;
+            for (int f = 0; f < take && depth_ptrs; f++)
+                if ((uintptr_t)P.fr[f].depth % 16 != 0 || (P.fr[f].color && (uintptr_t)P.fr[f].color % 16 != 0)) P.tma_ok = 0;
             const char* e = getenv("B2R_K1_TMA");      // "0": force the LDG form of the pack role (parity test of the unaligned-image path)
             if (e && atoi(e) == 0) P.tma_ok = 0;
         }
@@ -1013,6 +1019,22 @@ B2R_API int b2r_tsdf_integrate_batch(b2r_tsdf* h, int n, const void* depth, int 
     B2RDeviceGuard g(h->device);
     return tsdf_integrate_impl(h, n, depth, depth_is_u16, depth_scale, depth_trunc, color, color_channels, color_bgr, nullptr,
                                W, H, fx, fy, cx, cy, extrinsics, stream);
+}
+
+// n same-shaped frames that are NOT stored back to back: depth_ptrs / color_ptrs are HOST arrays of n DEVICE pointers, fused
+// in array order (config 5: the slots of a per-tick all-gather buffer, taken tick-major so that the fusion order -- which
+// decides the running averages bit for bit -- does not depend on the number of ranks).  extrinsics: HOST n*16 f64.
+B2R_API int b2r_tsdf_integrate_frames(b2r_tsdf* h, int n, const void* const* depth_ptrs, int depth_is_u16, float depth_scale,
+                                      float depth_trunc, const uint8_t* const* color_ptrs, int color_channels, int color_bgr,
+                                      int W, int H, double fx, double fy, double cx, double cy,
+                                      const double* extrinsics, cudaStream_t stream) {
+    if (!h || !depth_ptrs || n < 0) return B2R_ERR_BAD_ARG;
+    if (n == 0) return B2R_OK;
+    if (h->color_type == 2) { b2r_set_error("b2r_tsdf_integrate_frames: Gray32 volumes take frames through b2r_tsdf_integrate"); return B2R_ERR_FORMAT; }
+    if (h->color_type == 1 && !color_ptrs) { b2r_set_error("[ScalableTSDFVolume::Integrate] Unsupported image format."); return B2R_ERR_FORMAT; }
+    B2RDeviceGuard g(h->device);
+    return tsdf_integrate_impl(h, n, nullptr, depth_is_u16, depth_scale, depth_trunc, nullptr, color_channels, color_bgr, nullptr,
+                               W, H, fx, fy, cx, cy, extrinsics, stream, depth_ptrs, color_ptrs);
 }
 
 // Same, with HOST images (pinned for true overlap): each chunk's H2D copy runs on an internal copy

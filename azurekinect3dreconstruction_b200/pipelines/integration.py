@@ -118,6 +118,25 @@ class ScalableTSDFVolume:
                 1 if color_bgr else 0, W, H, fx, fy, cx, cy, _lib.dbl16(E), _lib.stream_ptr())
         _lib.check(rc, "integrate_raw")
 
+    def integrate_frames(self, depth_ptrs, color_ptrs, color_channels: int, intrinsic: PinholeCameraIntrinsic, extrinsics,
+                         depth_scale: float = 1000.0, depth_trunc: float = 3.0, color_bgr: bool = False) -> None:
+        """Frames that are not stored back to back (b2r_tsdf_integrate_frames): ``depth_ptrs`` / ``color_ptrs`` are sequences of
+        DEVICE addresses of u16 depth / u8 colour images of the intrinsic's size, fused in sequence order (config 5: the slots
+        of a per-tick all-gather buffer, tick-major).  The caller keeps the buffers alive until the stream has consumed them."""
+        n = len(depth_ptrs)
+        E = np.ascontiguousarray(np.asarray(extrinsics, dtype=np.float64).reshape(-1))
+        if E.size != 16 * n or (color_ptrs is not None and len(color_ptrs) != n):
+            raise RuntimeError("integrate_frames: need one 4x4 extrinsic (and one colour image) per frame")
+        if self.color_type == TSDFVolumeColorType.RGB8 and (color_ptrs is None or color_channels not in (3, 4)):
+            raise RuntimeError("[ScalableTSDFVolume::Integrate] Unsupported image format.")
+        fx, fy, cx, cy = intrinsic.fxfycxcy()
+        dp = (C.c_void_p * n)(*[int(p) for p in depth_ptrs])
+        cp = (C.c_void_p * n)(*[int(p) for p in color_ptrs]) if color_ptrs is not None else None
+        rc = self._lib.b2r_tsdf_integrate_frames(self._h, n, dp, 1, float(depth_scale), float(depth_trunc), cp, int(color_channels),
+                                                 1 if color_bgr else 0, intrinsic.width, intrinsic.height, fx, fy, cx, cy,
+                                                 _lib.dbl16(E), _lib.stream_ptr())
+        _lib.check(rc, "integrate_frames")
+
     def reset(self) -> None:
         _lib.check(self._lib.b2r_tsdf_reset(self._h, _lib.stream_ptr()), "reset")
 

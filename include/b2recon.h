@@ -112,8 +112,16 @@ int b2r_tsdf_integrate_batch(b2r_tsdf* h, int n, const void* depth, int depth_is
                              float depth_trunc, const uint8_t* color, int color_channels, int color_bgr, int W,
                              int H, double fx, double fy, double cx, double cy, const double* extrinsics_host,
                              cudaStream_t stream);
+/* n same-shaped frames NOT stored back to back: HOST arrays of n DEVICE pointers, fused in array order -- the slots of
+ * a per-tick all-gather buffer taken tick-major (config 5: several cameras into one volume,
+ * BetterVisualizerD2camerasWORKSkinda.py:546-551 integrates camera 0 then camera 1 of every tick) */
+int b2r_tsdf_integrate_frames(b2r_tsdf* h, int n, const void* const* depth_ptrs, int depth_is_u16, float depth_scale,
+                              float depth_trunc, const uint8_t* const* color_ptrs, int color_channels, int color_bgr,
+                              int W, int H, double fx, double fy, double cx, double cy,
+                              const double* extrinsics_host, cudaStream_t stream);
 /* same with HOST images: H2D copies overlap fusion through an internal 6-deep device ring of 8-frame chunks
- * (env B2R_HOST_CHUNK) */
+ * (env B2R_HOST_CHUNK).  The host buffers must be fully written when the call is made; they may be reused or freed
+ * as soon as it returns (the call waits for its last copy, not for the kernels). */
 int b2r_tsdf_integrate_host(b2r_tsdf* h, int n, const void* depth_host, int depth_is_u16, float depth_scale,
                             float depth_trunc, const uint8_t* color_host, int color_channels, int color_bgr, int W,
                             int H, double fx, double fy, double cx, double cy, const double* extrinsics_host,

@@ -120,7 +120,7 @@ def test_config5_one_tick_shards_single_and_oracle_agree(o3r):
     single = o3d.pipelines.integration.ScalableTSDFVolume(VL5, TR5, TT.RGB8, capacity_units=cap)
     single.integrate_raw(depth, rgb, K, E, 1000.0, trunc_m)
     st = single.stats()
-    assert st["errors"] == 0 and st["num_units"] > 60000
+    assert st["errors"] == 0 and st["num_units"] > 30000
     shards = [o3d.pipelines.integration.ScalableTSDFVolume(VL5, TR5, TT.RGB8, capacity_units=cap // 2 + 20000, rank=r, world=2) for r in range(2)]
     n_shard_units, upd = 0, 0
     for v in shards:
@@ -152,7 +152,7 @@ def test_config5_one_tick_shards_single_and_oracle_agree(o3r):
         ref.integrate(o3r.depth_to_float(dn[i], 1000.0, trunc_m), Kt, E[i], rgb=cn[i])
     vol.integrate_raw(depth[:n_or], rgb[:n_or], K, E[:n_or], 1000.0, trunc_m)
     rep = compare.volume_vs_oracle(vol, ref)
-    assert rep["units"] > 15000 * min(n_or, 2)
+    assert rep["units"] > 15000
     print("config5 oracle leg: %d stream(s), %d units, %d updated voxel records" % (n_or, rep["units"], rep["updated_voxels"]))
 
 
