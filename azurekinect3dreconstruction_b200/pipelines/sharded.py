@@ -282,3 +282,110 @@ def integrate_host_frames(vol: ScalableTSDFVolume, depth_h: torch.Tensor, color_
         return
     E = np.asarray(extrinsics, dtype=np.float64).reshape(-1, 4, 4)
     exchange.run(depth_h, color_h, lambda d, c, f0, n: vol.integrate_raw(d, c, intrinsic, E[f0:f0 + n], depth_scale, depth_trunc))
+
+
+# ---- config 5: one camera stream per rank, every tick's frames exchanged over NVLink ---------------------------------
+class StreamTickExchange:
+    """BASELINE configs[4] / north_star: "independent camera/frame streams map one per GPU ... each frame's depth/color/pose is
+    broadcast and each rank integrates only its own blocks" (the reference's precedent integrates camera 0 then camera 1 of
+    every tick into one volume: CodeThatKindaWorks/BetterVisualizerD2camerasWORKSkinda.py:546-551).
+
+    Stream s lives on rank ``s // streams_per_rank`` only.  A frame travels as one RECORD ``[depth u16 | colour u8 | extrinsic
+    16 x f64]`` (each part 256-byte aligned, so K1's TMA staging applies to the gathered slots as they lie); ``pack`` writes
+    records (what a capture thread does once per frame).  ``run`` walks the ticks in batches of ``ticks_per_batch``: ONE
+    ``all_gather_into_tensor`` per batch on a communication stream hands every rank every stream's records -- double-buffered,
+    so the gather of batch i + 1 overlaps the integration of batch i -- and ``consume`` gets the slot addresses TICK-MAJOR,
+    stream-minor: the fusion order (which decides the running averages bit for bit) is the same for every world size."""
+
+    def __init__(self, frame_shape, color_channels: int, n_streams: int, ticks_per_batch: int = 4, group=None, device=None):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        if dist.is_available() and dist.is_initialized():
+            self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        else:
+            self.rank, self.world = 0, 1
+        if n_streams % self.world:
+            raise ValueError("StreamTickExchange: %d streams do not divide over %d ranks" % (n_streams, self.world))
+        (self.H, self.W), self.ch = frame_shape, int(color_channels)
+        self.n_streams, self.s_local, self.T = int(n_streams), n_streams // self.world, int(ticks_per_batch)
+        al = lambda n: (n + 255) & ~255
+        self.off_color = al(self.H * self.W * 2)
+        self.off_pose = self.off_color + al(self.H * self.W * self.ch)
+        self.rec = self.off_pose + 256
+        self.device = device
+        cuda = device is not None and torch.device(device).type == "cuda"
+        self.gathered = [torch.zeros((self.world * self.T * self.s_local, self.rec), dtype=torch.uint8, device=device) for _ in range(2)] \
+            if self.world > 1 else None
+        self.comm_stream = torch.cuda.Stream(device=device) if (cuda and self.world > 1) else None
+        self.ev_gathered = [torch.cuda.Event() for _ in range(2)] if self.comm_stream else None
+        self.ev_released = [torch.cuda.Event() for _ in range(2)] if self.comm_stream else None
+        self.bytes_gathered = 0
+
+    def scratch_bytes(self) -> int:
+        return 0 if self.gathered is None else 2 * self.gathered[0].numel()
+
+    def pack(self, depth_u16: torch.Tensor, color_u8: torch.Tensor, extrinsics, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """(n,H,W) u16 + (n,H,W,ch) u8 + n 4x4 f64 -> (n, rec) u8 records on the frames' device."""
+        n = int(depth_u16.shape[0])
+        rec = out if out is not None else torch.zeros((n, self.rec), dtype=torch.uint8, device=depth_u16.device)
+        rec[:, :self.H * self.W * 2] = depth_u16.reshape(n, -1).view(torch.uint8)
+        rec[:, self.off_color:self.off_color + self.H * self.W * self.ch] = color_u8.reshape(n, -1)
+        E = torch.as_tensor(np.ascontiguousarray(np.asarray(extrinsics, dtype=np.float64).reshape(n, 16)))
+        rec[:, self.off_pose:self.off_pose + 128] = E.view(torch.uint8).reshape(n, 128).to(rec.device)
+        return rec
+
+    def _gather(self, slot: int, local: torch.Tensor, t: int):
+        """local: (t, s_local, rec) records of this rank for t ticks -> gathered[slot][: world * t * s_local]."""
+        dst = self.gathered[slot][: self.world * t * self.s_local].reshape(-1)
+        if self.comm_stream is None:
+            self.dist.all_gather_into_tensor(dst, local.reshape(-1), group=self.group)
+        else:
+            with torch.cuda.stream(self.comm_stream):
+                self.comm_stream.wait_event(self.ev_released[slot])       # the integration that read this slot two batches ago
+                self.dist.all_gather_into_tensor(dst, local.reshape(-1), group=self.group)
+                self.ev_gathered[slot].record(self.comm_stream)
+        self.bytes_gathered += dst.numel()
+
+    def run(self, packed_local: torch.Tensor, consume) -> None:
+        """packed_local: (ticks, s_local, rec) u8 -- this rank's streams, resident on its device.
+        consume(depth_ptrs, color_ptrs, extrinsics (n,4,4) f64 host, first_tick, n_ticks): n = n_ticks * n_streams frames,
+        tick-major.  The slots stay valid until consume's work on the current stream has run (K1 reads them at once)."""
+        ticks = int(packed_local.shape[0])
+        assert tuple(packed_local.shape[1:]) == (self.s_local, self.rec) and packed_local.is_contiguous()
+        batches = [(t0, min(self.T, ticks - t0)) for t0 in range(0, ticks, self.T)]
+        if self.world == 1:
+            for t0, t in batches:                                     # nothing to exchange: the records are consumed where they lie
+                self._consume(packed_local[t0:t0 + t].reshape(t * self.s_local, self.rec), t0, t, consume, single=True)
+            return
+        if self.comm_stream is not None:
+            self.comm_stream.wait_stream(torch.cuda.current_stream())     # the records were written on the caller's stream
+        self._gather(0, packed_local[batches[0][0]:batches[0][0] + batches[0][1]], batches[0][1])
+        for i, (t0, t) in enumerate(batches):
+            slot = i & 1
+            if i + 1 < len(batches):
+                n0, nt = batches[i + 1]
+                self._gather(slot ^ 1, packed_local[n0:n0 + nt], nt)      # overlaps the integration of batch i
+            if self.comm_stream is not None:
+                self.ev_gathered[slot].synchronize()                       # the poses are read on the host
+                torch.cuda.current_stream().wait_event(self.ev_gathered[slot])
+            self._consume(self.gathered[slot][: self.world * t * self.s_local], t0, t, consume, single=False)
+            if self.comm_stream is not None:
+                self.ev_released[slot].record(torch.cuda.current_stream())
+
+    def _consume(self, recs: torch.Tensor, t0: int, t: int, consume, single: bool):
+        # recs rows: single -> [tick][stream]; gathered -> [rank][tick][local stream]
+        poses = recs[:, self.off_pose:self.off_pose + 128].cpu().contiguous().view(torch.float64).reshape(-1, 4, 4).numpy()
+        base = recs.data_ptr()
+        rows = []
+        for tt in range(t):
+            for s in range(self.n_streams):
+                rows.append(tt * self.s_local + s if single else ((s // self.s_local) * t + tt) * self.s_local + s % self.s_local)
+        dptr = [base + r * self.rec for r in rows]
+        cptr = [p + self.off_color for p in dptr]
+        consume(dptr, cptr, poses[rows], t0, t)
+
+
+def integrate_stream_ticks(vol: ScalableTSDFVolume, exchange: StreamTickExchange, packed_local: torch.Tensor, intrinsic,
+                           depth_scale: float = 1000.0, depth_trunc: float = 3.0) -> None:
+    """All ticks of all streams into this rank's shard: exchange (NVLink all-gather per tick batch) + integrate_frames."""
+    exchange.run(packed_local, lambda dp, cp, E, t0, t: vol.integrate_frames(dp, cp, exchange.ch, intrinsic, E, depth_scale, depth_trunc))

@@ -53,6 +53,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--upstream-frames", type=int, default=40, help="frames of the upstream-structure (OpenMP inside a unit) CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--c5-ticks", type=int, default=64, help="ticks of the config-5 secondary record (8 WFOV streams per tick)")
     ap.add_argument("--no-secondary", action="store_true", help="skip the secondary records (configs 1, 2, 4, 5, per-frame API)")
     return ap.parse_args()
 
@@ -337,6 +338,35 @@ def main():
         raise RuntimeError("e2e arm diverged from the device arm: %r vs %r" % (st_e2e, st))
     h2d_bytes = int(depth_h.numel() * 2 + rgb_h.numel())
 
+    # ---- secondary records: the other north_star targets, in the same driver-run line -------------------------------------
+    secondary = None
+    if not args.no_secondary:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_secondary as bs
+        secondary = {}
+
+        def record(name, fn, *a, **k):
+            try:
+                secondary[name] = fn(*a, **k)
+            except Exception as e:                     # a secondary record never takes the headline line down with it
+                secondary[name] = {"error": repr(e)[:300]}
+        if rank == 0:
+            poses = None
+            from azurekinect3dreconstruction_b200 import synthetic as syn
+            poses = syn.orbit_trajectory(args.frames)
+            record("unproject", bs.unproject_record, dev, peak)
+            if world == 1:
+                record("extract", bs.extract_record, vol, depth, rgb, K, E, peak)
+                step_device()                          # extract_record integrated extra frames: restore the step's volume
+            record("odometry", bs.odometry_record, depth, rgb, K, poses)
+            record("per_frame_api", bs.per_frame_api_record, depth_h, rgb_h, K, E)
+        # config 5 is collective: every rank takes part
+        try:
+            c5 = bs.config5_record(dev, rank, world, ticks=args.c5_ticks)
+        except Exception as e:
+            c5 = {"error": repr(e)[:300]}
+        secondary["config5"] = c5
+
     # ---- CPU baseline (rank 0, N = 1): the same 300-frame step on the host cores, then the parity check -----------------
     cpu = parity = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -347,7 +377,7 @@ def main():
         cpu = {"value": cfps, "unit": "frames/s", "cores": cores, "kind": "port",
                "sample": "the whole step: reset + all %d frames, 1 timed pass, OpenMP over volume units" % args.frames,
                "upstream_structure": upstream_structure_sample(dn, cn, E, intr, max(1, min(args.upstream_frames, args.frames)))}
-        # the volume the e2e arm just left behind (same frames, host ingest, batch 32) against the oracle's
+        # the volume of the bench step (same 300 frames, batch 32) against the oracle's
         parity = {"frames": args.frames}
         parity.update(compare.volume_vs_oracle(vol, ref_vol))
         parity["bit_exact"] = bool(parity["tsdf_weight_bit_exact"] and parity["counters_equal"])
@@ -360,7 +390,7 @@ def main():
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": workload_config(args), "impl": "b200",
                 "sharding": {"rule": "unit-key hash over %d rank(s)" % world, "units_allocated_rank0": st["num_units"]},
-                "roofline": roofline, "cpu_baseline": cpu, "parity_checked": parity,
+                "roofline": roofline, "cpu_baseline": cpu, "parity_checked": parity, "secondary": secondary,
                 "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes * world,
                         "ms_per_step": ms_e2e / args.steps,
                         "ingest": ("host frames -> one GPU over PCIe (6-deep ring of 8-frame chunks)" if world == 1 else

@@ -123,8 +123,13 @@ def test_config5_one_tick_shards_single_and_oracle_agree(o3r):
     assert st["errors"] == 0 and st["num_units"] > 30000
     shards = [o3d.pipelines.integration.ScalableTSDFVolume(VL5, TR5, TT.RGB8, capacity_units=cap // 2 + 20000, rank=r, world=2) for r in range(2)]
     n_shard_units, upd = 0, 0
+    # the shards take the frames the way config 5 delivers them: frame records {depth | colour | pose} consumed where they lie
+    # through b2r_tsdf_integrate_frames (pointer lists, tick-major); the single volume took the plain back-to-back batch
+    from azurekinect3dreconstruction_b200.pipelines import sharded
+    ex = sharded.StreamTickExchange((1024, 1024), 3, 8, ticks_per_batch=4, device="cuda")
+    packed = ex.pack(depth, rgb, E).reshape(1, 8, ex.rec)
     for v in shards:
-        v.integrate_raw(depth, rgb, K, E, 1000.0, trunc_m)
+        sharded.integrate_stream_ticks(v, ex, packed, K, 1000.0, trunc_m)
         s2 = v.stats()
         assert s2["errors"] == 0
         n_shard_units += s2["num_units"]; upd += s2["updated_voxels"]

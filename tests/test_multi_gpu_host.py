@@ -62,6 +62,31 @@ def _worker(rank, world, port, q):
         got_c = torch.cat([c for _, _, _, c in seen])
         assert torch.equal(got_d, depth.view(torch.int16)) and torch.equal(got_c, color)
         assert ex.bytes_uploaded == (6 if rank == 0 else 5) * H * W * 5          # rank 0: frames 0-2, 6-8; rank 1: 3-5, 9-10
+        # config 5's stream exchange: 4 streams (2 per rank), 5 ticks in batches of 2 -> every rank sees every frame, tick-major
+        import ctypes as C
+        S, ticks, H5, W5 = 4, 5, 3, 8
+        tex = sharded.StreamTickExchange((H5, W5), 3, S, ticks_per_batch=2, device=None)
+        assert (tex.rank, tex.world, tex.s_local) == (rank, world, 2)
+        fd = lambda t, s: torch.full((H5, W5), 1000 * t + s, dtype=torch.int16).view(torch.uint16)
+        fc = lambda t, s: torch.full((H5, W5, 3), (7 * t + s) % 256, dtype=torch.uint8)
+        fe = lambda t, s: np.eye(4) * (1 + t) + s
+        mine = [s for s in range(S) if s // tex.s_local == rank]
+        packed = torch.stack([tex.pack(torch.stack([fd(t, s) for s in mine]), torch.stack([fc(t, s) for s in mine]), np.stack([fe(t, s) for s in mine]))
+                              for t in range(ticks)])
+        assert packed.shape == (ticks, 2, tex.rec) and tex.off_color % 256 == 0 and tex.off_pose % 256 == 0
+        got = []
+
+        def consume(dp, cp, E, t0, t):
+            assert len(dp) == len(cp) == t * S and E.shape == (t * S, 4, 4)
+            for i in range(t * S):
+                d = np.frombuffer((C.c_uint8 * (H5 * W5 * 2)).from_address(dp[i]), dtype=np.uint16).copy()
+                c = np.frombuffer((C.c_uint8 * (H5 * W5 * 3)).from_address(cp[i]), dtype=np.uint8).copy()
+                got.append((t0 + i // S, i % S, int(d[0]), int(d[-1]), int(c[0]), E[i].copy()))
+        tex.run(packed, consume)
+        assert [(t, s) for t, s, *_ in got] == [(t, s) for t in range(ticks) for s in range(S)]
+        for t, s, d0, d1, c0, E in got:
+            assert d0 == d1 == 1000 * t + s and c0 == (7 * t + s) % 256 and np.array_equal(E, fe(t, s))
+        assert tex.bytes_gathered == ticks * S * tex.rec
         q.put((rank, "ok"))
     except Exception as e:  # pragma: no cover
         q.put((rank, repr(e)))
