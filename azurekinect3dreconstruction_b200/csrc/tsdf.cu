@@ -95,7 +95,7 @@ struct PackParams {
     float fcx, fcy, ifx, ify;      // (float)cx, (float)cy, 1.0f/(float)fx, 1.0f/(float)fy
     double fx, fy, cx, cy;         // f64 intrinsics for the allocation samples
     double trunc, unit_length;
-    int stride, Ws, n_samples;
+    int stride, Ws, Hs, tiles_x;   // sample grid and its 16 x 16 tiles
     int n_alloc_blocks;
     const float* mult;             // cached multiplier image (pack_mult of every pixel)
     float rscale; int scale_fast;  // RN(1/depth_scale); depth_scale inside b2r_div_domain
@@ -175,10 +175,13 @@ __device__ __noinline__ void alloc_key(const PackParams& P, uint64_t key, uint32
 
 #define PACK_PX 8       // pixels per thread in the pack role
 #define PACK_TILE (256 * PACK_PX)   // pixels per CTA of the pack role
-#define K1_DYN_SMEM (PACK_TILE * 12) // dynamic shared memory: the pack role's staged tile; the alloc role's cell list aliases it
-#define ALLOC_CELLS 2048 // cell keys staged per window of the alloc role
+#define K1_DYN_SMEM (PACK_TILE * 12) // dynamic shared memory: the pack role's staged tile; the alloc role's key set aliases it
+#ifndef ALLOC_SET_LOG2
+#define ALLOC_SET_LOG2 10 // shared-memory key set of the alloc role: 1024 slots (a 64 x 64-pixel tile touches a few dozen units)
+#endif
+#define ALLOC_SET (1 << ALLOC_SET_LOG2)
 #ifndef ALLOC_IT
-#define ALLOC_IT 2       // cells per thread whose slot probes are in flight together (2 measured best; 4 spills)
+#define ALLOC_IT 2       // set slots per thread whose hash probes are in flight together
 #endif
 #ifndef PACK_MIN_CTAS
 #define PACK_MIN_CTAS 5
@@ -311,13 +314,22 @@ __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(con
         }
         return;
     }
-    // ---- alloc role (a8): block allocation from the stride-sampled pixels (f64 chain)
-    const int s = bidx * (int)blockDim.x + (int)threadIdx.x;
+    // ---- alloc role (a8): block allocation from the stride-sampled pixels (f64 chain).
+    // A CTA owns a 16 x 16 TILE of samples (64 x 64 pixels at stride 4): a compact patch of the surface touches a few dozen
+    // units, against the hundreds a 256-sample raster strip crosses.  Three stages:
+    //   (1) one thread per sample: the upstream f64 chain -> integer key box;
+    //   (2) lanes holding the same box elect one leader (match.any), and the leaders insert their boxes' keys into a
+    //       shared-memory open-addressing SET: after it the CTA holds every unit key its tile touches exactly once;
+    //   (3) the threads take the set's slots ALLOC_IT at a time: hash-slot probes of all of a thread's keys in flight together
+    //       (unit exists and this frame's bit is set: done), then one atomicOr per key that needs it, results consumed after
+    //       all are in flight, first touches appended to the touched list with one counter atomic per warp; absent keys take
+    //       the CAS probing slow path.  Only the owner rank's keys are probed (sharded handles).
+    const int tile_x = bidx % P.tiles_x, tile_y = bidx / P.tiles_x;
+    const int sj = tile_x * 16 + (int)(threadIdx.x & 15u), si = tile_y * 16 + (int)(threadIdx.x >> 4);
     const unsigned lane = threadIdx.x & 31u;
     int lo[3] = {0, 0, 0};
-    int ny = 1, nz = 1, n = 0;   // n = cells in this sample's box (0: no valid depth)
-    if (s < P.n_samples) {
-        const int si = s / P.Ws, sj = s - si * P.Ws;
+    int ex[3] = {0, 0, 0};       // box extents; ex[0] == 0: this sample contributes nothing
+    if (sj < P.Ws && si < P.Hs) {
         const int i = si * P.stride, j = sj * P.stride;
         const float d = load_depth_m(P, F.depth, i * P.W + j);
         if (d > 0.0f) {
@@ -337,97 +349,75 @@ __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(con
             if (ext[0] < 0 || ext[1] < 0 || ext[2] < 0 || ext[0] * ext[1] * ext[2] > 4096) {
                 atomicOr(&P.counters[B2R_C_ERR], 2);   // key out of range / degenerate box: report, don't loop
             } else {
-                ny = (int)ext[1]; nz = (int)ext[2]; n = (int)(ext[0] * ext[1] * ext[2]);
+                ex[0] = (int)ext[0]; ex[1] = (int)ext[1]; ex[2] = (int)ext[2];
             }
         }
     }
-    // Neighbouring samples mostly share a box.  Keep one box per RUN of equal boxes (run heads) and let every head
-    // write its cells' keys, end to end, into a shared list; then the 256 threads take the cells ALLOC_IT at a time:
-    // (A) the slot probes of all of a thread's cells are issued together -- the common case (unit exists, this frame's
-    // bit already set) ends there; (B) lanes holding the same key elect a leader (match.any) whose atomicOr marks the
-    // unit; (C) the atomics' results are consumed only after all of them are in flight, and first touches are appended
-    // to the touched list with one counter atomic per warp.  Absent keys / collisions take the probing slow path.
-    __shared__ int s_lo[256][3];
-    __shared__ int s_n[256];
-    __shared__ int s_dim[256][2];     // ny, nz of the box
-    __shared__ int s_warp[2][8];
     extern __shared__ __align__(128) unsigned char k1_smem[];
-    uint64_t* s_cell = reinterpret_cast<uint64_t*>(k1_smem);    // ALLOC_CELLS * 8 <= K1_DYN_SMEM
-    const int t = threadIdx.x, warp = t >> 5;
-    s_lo[t][0] = lo[0]; s_lo[t][1] = lo[1]; s_lo[t][2] = lo[2]; s_dim[t][0] = ny; s_dim[t][1] = nz; s_n[t] = n;
+    unsigned long long* s_set = reinterpret_cast<unsigned long long*>(k1_smem);    // ALLOC_SET * 8 <= K1_DYN_SMEM
+    for (int q = threadIdx.x; q < ALLOC_SET; q += blockDim.x) s_set[q] = B2R_KEY_EMPTY;
     __syncthreads();
-    bool head = n > 0;
-    if (head && t > 0)
-        head = !(s_lo[t - 1][0] == lo[0] && s_lo[t - 1][1] == lo[1] && s_lo[t - 1][2] == lo[2] && s_dim[t - 1][0] == ny && s_dim[t - 1][1] == nz && s_n[t - 1] == n);
-    // block scan: cells before me
-    const int cc_ = head ? n : 0;
-    int ci_ = cc_;
-    for (int o = 1; o < 32; o <<= 1) {
-        const int a2 = __shfl_up_sync(0xffffffffu, ci_, o);
-        if ((int)lane >= o) ci_ += a2;
-    }
-    if (lane == 31) s_warp[1][warp] = ci_;
-    __syncthreads();
-    int cbase = 0, ncells = 0;
-#pragma unroll
-    for (int w = 0; w < 8; w++) { if (w < warp) cbase += s_warp[1][w]; ncells += s_warp[1][w]; }
-    const int my_c = cbase + ci_ - cc_;
-    // The list holds ALLOC_CELLS cells; a block with more (large truncation against the unit length) goes round again.
-    for (int w0 = 0; w0 < ncells; w0 += ALLOC_CELLS) {
-        if (w0) __syncthreads();                       // the previous window has been consumed
-        if (head && my_c < w0 + ALLOC_CELLS && my_c + n > w0) {
-            const int nx = n / (ny * nz);
-            int c = my_c - w0;
-            for (int a = 0; a < nx; a++)
-                for (int b = 0; b < ny; b++)
-                    for (int cz = 0; cz < nz; cz++, c++)
-                        if (c >= 0 && c < ALLOC_CELLS) s_cell[c] = b2r_pack_key(lo[0] + a, lo[1] + b, lo[2] + cz);
-        }
-        __syncthreads();
-        const int wn = min(ALLOC_CELLS, ncells - w0);
-        for (int c0 = 0; c0 < wn; c0 += 256 * ALLOC_IT) {   // block-uniform trip counts: every lane reaches the match.any
-            uint64_t want[ALLOC_IT], got[ALLOC_IT];
-            uint32_t slot_i[ALLOC_IT], mk[ALLOC_IT], old[ALLOC_IT];
-#pragma unroll
-            for (int it = 0; it < ALLOC_IT; it++) {
-                const int c = c0 + it * 256 + t;
-                want[it] = B2R_KEY_EMPTY; got[it] = 0; mk[it] = 0; slot_i[it] = 0;
-                if (c < wn) {
-                    const uint64_t key = s_cell[c];
-                    const uint64_t hsh = b2r_mix64(key);
-                    if (P.world <= 1 || (int)((hsh >> 33) % (uint64_t)P.world) == P.rank) {
-                        want[it] = key; slot_i[it] = (uint32_t)hsh & P.hash.mask;
-                        const B2RSlot* slot = &P.hash.slots[slot_i[it]];
-                        got[it] = __ldcg(reinterpret_cast<const unsigned long long*>(&slot->key));
-                        mk[it] = __ldcg(&slot->mask[P.q]);
+    // (2) one leader per distinct box in the warp; its keys go into the set (a key the set cannot take after 32 probes goes
+    //     straight to the global table: correct, just slower -- only a box of hundreds of units per sample gets there)
+    {
+        const uint64_t bkey = ex[0] ? b2r_pack_key(lo[0], lo[1], lo[2]) : (B2R_KEY_EMPTY - 1 - lane);
+        const unsigned ecode = (unsigned)(ex[0] | (ex[1] << 10) | (ex[2] << 20));
+        const unsigned peers = __match_any_sync(0xffffffffu, bkey) & __match_any_sync(0xffffffffu, ecode);
+        if (ex[0] && lane == (unsigned)(__ffs(peers) - 1)) {
+            for (int a = 0; a < ex[0]; a++)
+                for (int b = 0; b < ex[1]; b++)
+                    for (int c = 0; c < ex[2]; c++) {
+                        const unsigned long long key = b2r_pack_key(lo[0] + a, lo[1] + b, lo[2] + c);
+                        unsigned hs = (((unsigned)key * 0x9E3779B1u) ^ ((unsigned)(key >> 21) * 0x85EBCA77u) ^ ((unsigned)(key >> 42) * 0xC2B2AE3Du)) >> (32 - ALLOC_SET_LOG2);
+                        bool placed = false;
+                        for (int probe = 0; probe < 32 && !placed; probe++, hs = (hs + 1) & (ALLOC_SET - 1)) {
+                            const unsigned long long old = atomicCAS(&s_set[hs], (unsigned long long)B2R_KEY_EMPTY, key);
+                            placed = old == B2R_KEY_EMPTY || old == key;
+                        }
+                        if (!placed && (P.world <= 1 || b2r_owner(key, P.world) == P.rank)) alloc_key(P, key, F.bit);
                     }
+        }
+    }
+    __syncthreads();
+    // (3) global probes: every key of the set once
+    for (int c0 = 0; c0 < ALLOC_SET; c0 += 256 * ALLOC_IT) {
+        uint64_t want[ALLOC_IT], got[ALLOC_IT];
+        uint32_t slot_i[ALLOC_IT], mk[ALLOC_IT], old[ALLOC_IT];
+#pragma unroll
+        for (int it = 0; it < ALLOC_IT; it++) {
+            want[it] = s_set[c0 + it * 256 + (int)threadIdx.x];
+            got[it] = 0; mk[it] = 0; slot_i[it] = 0;
+            if (want[it] != B2R_KEY_EMPTY) {
+                const uint64_t hsh = b2r_mix64(want[it]);
+                if (P.world <= 1 || (int)((uint32_t)(hsh >> 33) % (uint32_t)P.world) == P.rank) {
+                    slot_i[it] = (uint32_t)hsh & P.hash.mask;
+                    const B2RSlot* slot = &P.hash.slots[slot_i[it]];
+                    got[it] = __ldcg(reinterpret_cast<const unsigned long long*>(&slot->key));
+                    mk[it] = __ldcg(&slot->mask[P.q]);
+                } else {
+                    want[it] = B2R_KEY_EMPTY;      // another rank's unit
                 }
             }
-            unsigned first = 0;                          // bit it: this lane saw the first touch of (unit, batch)
+        }
+        unsigned first = 0;                          // bit it: this lane saw the first touch of (unit, batch)
 #pragma unroll
-            for (int it = 0; it < ALLOC_IT; it++) {
-                old[it] = 1u;
-                if (c0 + it * 256 >= wn) break;          // block-uniform
-                const bool live = want[it] != B2R_KEY_EMPTY && !(got[it] == want[it] && (mk[it] & F.bit));
-                if (!__any_sync(0xffffffffu, live)) continue;
-                const unsigned peers = __match_any_sync(0xffffffffu, live ? want[it] : (B2R_KEY_EMPTY - 1 - lane));
-                const bool leader = live && (lane == (unsigned)(__ffs(peers) - 1));
-                if (leader) {
-                    if (got[it] == want[it]) { old[it] = atomicOr(&P.hash.slots[slot_i[it]].mask[P.q], F.bit); first |= 1u << it; }
-                    else alloc_key(P, want[it], F.bit);
-                }
+        for (int it = 0; it < ALLOC_IT; it++) {
+            old[it] = 1u;
+            const bool live = want[it] != B2R_KEY_EMPTY && !(got[it] == want[it] && (mk[it] & F.bit));
+            if (live) {
+                if (got[it] == want[it]) { old[it] = atomicOr(&P.hash.slots[slot_i[it]].mask[P.q], F.bit); first |= 1u << it; }
+                else alloc_key(P, want[it], F.bit);
             }
+        }
 #pragma unroll
-            for (int it = 0; it < ALLOC_IT; it++) {
-                if (c0 + it * 256 >= wn) break;
-                const bool app = ((first >> it) & 1u) && old[it] == 0u;
-                const unsigned am = __ballot_sync(0xffffffffu, app);
-                if (am == 0u) continue;
-                int pos = 0;
-                if (lane == (unsigned)(__ffs(am) - 1)) pos = atomicAdd(&P.counters[B2R_C_TOUCHED0 + P.q], __popc(am));
-                pos = __shfl_sync(0xffffffffu, pos, __ffs(am) - 1) + __popc(am & ((1u << lane) - 1u));
-                if (app && pos < P.cap_units) P.touched[pos] = (int)slot_i[it];
-            }
+        for (int it = 0; it < ALLOC_IT; it++) {
+            const bool app = ((first >> it) & 1u) && old[it] == 0u;
+            const unsigned am = __ballot_sync(0xffffffffu, app);
+            if (am == 0u) continue;
+            int pos = 0;
+            if (lane == (unsigned)(__ffs(am) - 1)) pos = atomicAdd(&P.counters[B2R_C_TOUCHED0 + P.q], __popc(am));
+            pos = __shfl_sync(0xffffffffu, pos, __ffs(am) - 1) + __popc(am & ((1u << lane) - 1u));
+            if (app && pos < P.cap_units) P.touched[pos] = (int)slot_i[it];
         }
     }
 }
@@ -942,8 +932,9 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
         P.fx = fx; P.fy = fy; P.cx = cx; P.cy = cy;
         P.trunc = h->sdf_trunc; P.unit_length = h->unit_length; P.stride = h->stride;
         P.Ws = (W + h->stride - 1) / h->stride;
-        P.n_samples = P.Ws * ((H + h->stride - 1) / h->stride);
-        P.n_alloc_blocks = (P.n_samples + 255) / 256;
+        P.Hs = (H + h->stride - 1) / h->stride;
+        P.tiles_x = (P.Ws + 15) / 16;
+        P.n_alloc_blocks = P.tiles_x * ((P.Hs + 15) / 16);
         P.rank = h->rank; P.world = h->world; P.q = h->q;
         P.hash = h->hash; P.unit_keys = h->unit_keys; P.touched = h->touched[h->q];
         P.counters = h->counters; P.cap_units = (int)h->cap_units;
