@@ -96,12 +96,13 @@ struct PackParams {
     double fx, fy, cx, cy;         // f64 intrinsics for the allocation samples
     double trunc, unit_length;
     int stride, Ws, Hs, tiles_x;   // sample grid and its 16 x 16 tiles
-    int n_alloc_blocks;
+    int n_alloc_blocks;            // allocation tiles per frame
+    int n_frames, tiles_per_frame, n_pack;   // frames in this launch, pixel tiles per frame, persistent pack CTAs
+    uint32_t pack_stage_bytes, pack_coff;    // ring stage size and the colour part's offset inside a stage
     const float* mult;             // cached multiplier image (pack_mult of every pixel)
     float rscale; int scale_fast;  // RN(1/depth_scale); depth_scale inside b2r_div_domain
     double rfx, rfy, runit;        // RN(1/fx), RN(1/fy), RN(1/unit_length)
     int ddiv_fast;                 // all three f64 divisors qualify for the shared-reciprocal division
-    int role32;                    // grid size x allocation blocks < 2^32: the role split runs in 32-bit arithmetic
     int tma_ok;                    // every tile of every image is a 16-byte aligned multiple of 16 bytes: TMA staging in the pack role
     int rank, world;
     int q;                         // batch buffer (mask word) in use
@@ -175,7 +176,12 @@ __device__ __noinline__ void alloc_key(const PackParams& P, uint64_t key, uint32
 
 #define PACK_PX 8       // pixels per thread in the pack role
 #define PACK_TILE (256 * PACK_PX)   // pixels per CTA of the pack role
-#define K1_DYN_SMEM (PACK_TILE * 12) // dynamic shared memory: the pack role's staged tile; the alloc role's key set aliases it
+#ifndef PACK_STAGES
+#define PACK_STAGES 3   // ring of staged tiles per persistent pack CTA (dynamic shared memory; the alloc role's key set aliases it)
+#endif
+#ifndef PACK_CTAS_PER_SM
+#define PACK_CTAS_PER_SM 2
+#endif
 #ifndef ALLOC_SET_LOG2
 #define ALLOC_SET_LOG2 10 // shared-memory key set of the alloc role: 1024 slots (a 64 x 64-pixel tile touches a few dozen units)
 #endif
@@ -214,7 +220,7 @@ struct K1Trace {
     __device__ ~K1Trace() {
         __syncthreads();
         if (threadIdx.x == 0) {
-            const unsigned L = blockIdx.y * gridDim.x + blockIdx.x;
+            const unsigned L = blockIdx.x;
             unsigned sm; asm("mov.u32 %0, %smid;" : "=r"(sm));
             if (L < 8192) { g_k1_trace[4 * L] = t0; g_k1_trace[4 * L + 1] = k1_now(); g_k1_trace[4 * L + 2] = sm; g_k1_trace[4 * L + 3] = role; }
         }
@@ -225,95 +231,102 @@ B2R_API int b2r_debug_k1_trace(unsigned long long* out, int n) {
 }
 #endif
 __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(const __grid_constant__ PackParams P) {
-    // The two roles are dealt out evenly over the launch order (CTAs start in linear block order): the latency-bound
-    // allocation CTAs then run beside the bandwidth-bound pack CTAs from the first wave to the last, instead of each
-    // frame's allocation starting only when its row of the grid comes up.  Position L takes allocation block A(L) =
-    // floor(L * n_alloc_total / n_total) when A(L + 1) > A(L), else pack block L - A(L).
-    const unsigned L = blockIdx.y * gridDim.x + blockIdx.x;
-    const unsigned n_total = gridDim.x * gridDim.y, n_alloc_total = (unsigned)P.n_alloc_blocks * gridDim.y;
-    // (the products fit 32 bits for every image the host lets through with role32 set; the emulated 64-bit division
-    // was 9 % of this kernel's instructions)
-    const unsigned A0 = P.role32 ? (L * n_alloc_total) / n_total : (unsigned)(((unsigned long long)L * n_alloc_total) / n_total);
-    const unsigned A1 = P.role32 ? ((L + 1) * n_alloc_total) / n_total : (unsigned)(((unsigned long long)(L + 1) * n_alloc_total) / n_total);
-    const bool role_pack = A1 == A0;
-    const unsigned n_role = role_pack ? gridDim.x - (unsigned)P.n_alloc_blocks : (unsigned)P.n_alloc_blocks;
-    const unsigned ridx = role_pack ? L - A0 : A0;
-    const int fidx = (int)(ridx / n_role), bidx = (int)(ridx - (unsigned)fidx * n_role);
-    const PackFrame& F = P.fr[fidx];
+    // One launch, two roles.  The first n_pack CTAs are PERSISTENT pack CTAs: each walks the launch's pixel tiles with stride
+    // n_pack through a PACK_STAGES-deep ring of TMA bulk copies, so a tile's HBM latency is paid while the tiles before it
+    // are converted (one tile per short-lived CTA spent two thirds of its life waiting for its own copy).  Every CTA after
+    // them takes one allocation tile; those are latency-bound and run beside the bandwidth-bound pack CTAs for the whole
+    // launch (CTAs start in linear block order, so the pack CTAs are resident first).
+    const unsigned L = blockIdx.x;
+    const bool role_pack = L < (unsigned)P.n_pack;
 #ifdef B2R_K1_TRACE
     K1Trace trace_(role_pack ? 1 : 0);
 #endif
     if (role_pack) {
-        // ---- pack role: a1 depth conversion + the cached CreateDepthToCameraDistanceMultiplierFloatImage + colour.
-        //      A warp owns 32 * PACK_PX consecutive pixels; in step k lane l takes pixel 32 k + l, so every 16-byte
-        //      texel store of the warp lands in 512 contiguous bytes (4 full lines per request instead of 32 partial
-        //      ones -- the store REQUEST rate, not the bytes, bounded the thread-contiguous layout).  All loads of the
-        //      PACK_PX steps are issued before the first use.
+        // ---- pack role: a1 depth conversion + colour.  A warp owns 32 * PACK_PX consecutive pixels of a tile; in step k lane l
+        //      takes pixel 32 k + l, so every 8-byte texel store of the warp lands in 256 contiguous bytes (the store REQUEST
+        //      rate, not the bytes, bounded the thread-contiguous layout).
+        extern __shared__ __align__(128) unsigned char k1_smem[];
+        __shared__ __align__(8) uint64_t tile_bar[PACK_STAGES];
         const int npx = P.W * P.H;
         const int lane = threadIdx.x & 31;
-        const int base = (bidx * (int)(blockDim.x >> 5) + (int)(threadIdx.x >> 5)) * (32 * PACK_PX) + lane;
-        if (base - lane >= npx) return;
-        uint32_t dv[PACK_PX], cv[PACK_PX];
-        const bool full = base - lane + 32 * PACK_PX <= npx;
-        if (P.tma_ok) {
-            // The tile's depth, colour and multiplier bytes arrive by three TMA bulk copies (one elected thread, one
-            // mbarrier): the LDG form of the same reads was bounded by the requests an SM may have in flight, not by
-            // HBM.  Dynamic shared memory: [depth | colour or gray | multiplier], PACK_TILE pixels each.
-            extern __shared__ __align__(128) unsigned char k1_smem[];
-            __shared__ __align__(8) uint64_t tile_bar;
-            const int tile0 = bidx * PACK_TILE;
-            const int tpx = min(PACK_TILE, npx - tile0);
-            const uint32_t dbytes = P.depth_is_u16 ? 2u : 4u;
-            const uint32_t cbytes = F.color ? (uint32_t)P.color_channels : (F.gray ? 4u : 0u);
-            unsigned char* s_d = k1_smem;
-            unsigned char* s_c = k1_smem + PACK_TILE * 4;
-            if (threadIdx.x == 0) {
-                mbar_init(&tile_bar, 1);
-                asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-                mbar_expect_tx(&tile_bar, (uint32_t)tpx * (dbytes + cbytes));
-                tma_load_1d(s_d, (const unsigned char*)F.depth + (size_t)tile0 * dbytes, (uint32_t)tpx * dbytes, &tile_bar);
-                if (cbytes) tma_load_1d(s_c, (F.color ? (const unsigned char*)F.color : (const unsigned char*)F.gray) + (size_t)tile0 * cbytes, (uint32_t)tpx * cbytes, &tile_bar);
-            }
-            __syncthreads();                 // the barrier's initialisation is visible to the waiters
-            mbar_wait(&tile_bar, 0);
-            const int l0 = (threadIdx.x >> 5) * (32 * PACK_PX) + lane;
-#pragma unroll
-            for (int k = 0; k < PACK_PX; k++) {
-                const int li = min(l0 + 32 * k, tpx - 1);
-                dv[k] = P.depth_is_u16 ? (uint32_t)reinterpret_cast<const uint16_t*>(s_d)[li] : reinterpret_cast<const uint32_t*>(s_d)[li];
-                if (cbytes == 4u) cv[k] = reinterpret_cast<const uint32_t*>(s_c)[li];
-                else if (cbytes == 3u) cv[k] = (uint32_t)s_c[3 * li] | ((uint32_t)s_c[3 * li + 1] << 8) | ((uint32_t)s_c[3 * li + 2] << 16);
-                else cv[k] = 0u;
-            }
-        } else {
-#pragma unroll
-        for (int k = 0; k < PACK_PX; k++) {
-            const int idx = full ? base + 32 * k : min(base + 32 * k, npx - 1);
-            dv[k] = P.depth_is_u16 ? (uint32_t)__ldg((const uint16_t*)F.depth + idx) : __float_as_uint(__ldg((const float*)F.depth + idx));
-            if (F.color) {
-                if (P.color_channels == 4) {
-                    cv[k] = __ldg(reinterpret_cast<const uint32_t*>(F.color) + idx);      // 0x..BBGGRR in memory order: byte 0 = channel 0
-                } else {
-                    const uint8_t* q = F.color + (size_t)idx * 3;
-                    cv[k] = (uint32_t)__ldg(q) | ((uint32_t)__ldg(q + 1) << 8) | ((uint32_t)__ldg(q + 2) << 16);
-                }
-            } else if (F.gray) {
-                cv[k] = __float_as_uint(__ldg(F.gray + idx));
-            } else {
-                cv[k] = 0u;
-            }
-        }
-        }
+        const int total = P.n_frames * P.tiles_per_frame;
+        const uint32_t dbytes = P.depth_is_u16 ? 2u : 4u;
+        const uint32_t cbytes = P.fr[0].color ? (uint32_t)P.color_channels : (P.fr[0].gray ? 4u : 0u);
         const uint32_t sel = P.color_bgr ? 0x4012u : 0x4210u;   // swap byte 0 and byte 2 for BGR; byte 3 cleared
+        auto issue = [&](int t, int st) {                        // thread 0: tile t -> ring stage st
+            const int f = t / P.tiles_per_frame, tile0 = (t - f * P.tiles_per_frame) * PACK_TILE;
+            const int tpx = min(PACK_TILE, npx - tile0);
+            const PackFrame& F = P.fr[f];
+            unsigned char* sb = k1_smem + (size_t)st * P.pack_stage_bytes;
+            mbar_expect_tx(&tile_bar[st], (uint32_t)tpx * (dbytes + cbytes));
+            tma_load_1d(sb, (const unsigned char*)F.depth + (size_t)tile0 * dbytes, (uint32_t)tpx * dbytes, &tile_bar[st]);
+            if (cbytes) tma_load_1d(sb + P.pack_coff, (F.color ? (const unsigned char*)F.color : (const unsigned char*)F.gray) + (size_t)tile0 * cbytes, (uint32_t)tpx * cbytes, &tile_bar[st]);
+        };
+        if (P.tma_ok) {
+            if (threadIdx.x == 0) {
+                for (int st = 0; st < PACK_STAGES; st++) mbar_init(&tile_bar[st], 1);
+                asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+                for (int k = 0; k < PACK_STAGES - 1; k++)
+                    if ((int)L + k * P.n_pack < total) issue((int)L + k * P.n_pack, k);
+            }
+            __syncthreads();                 // the barriers' initialisation is visible to the waiters
+        }
+        int k = 0;
+        for (int t = (int)L; t < total; t += P.n_pack, k++) {
+            const int f = t / P.tiles_per_frame, tile0 = (t - f * P.tiles_per_frame) * PACK_TILE;
+            const int tpx = min(PACK_TILE, npx - tile0);
+            const PackFrame& F = P.fr[f];
+            const int l0 = (threadIdx.x >> 5) * (32 * PACK_PX) + lane;
+            uint32_t dv[PACK_PX], cv[PACK_PX];
+            if (P.tma_ok) {
+                const int st = k % PACK_STAGES;
+                // the stage freed by the previous iteration's closing barrier takes the tile PACK_STAGES - 1 ahead
+                if (threadIdx.x == 0 && t + (PACK_STAGES - 1) * P.n_pack < total) issue(t + (PACK_STAGES - 1) * P.n_pack, (k + PACK_STAGES - 1) % PACK_STAGES);
+                mbar_wait(&tile_bar[st], (uint32_t)(k / PACK_STAGES) & 1u);
+                const unsigned char* s_d = k1_smem + (size_t)st * P.pack_stage_bytes;
+                const unsigned char* s_c = s_d + P.pack_coff;
 #pragma unroll
-        for (int k = 0; k < PACK_PX; k++) {
-            const int idx = base + 32 * k;
-            const float d = P.depth_is_u16 ? depth_from_u16(P, dv[k]) : __uint_as_float(dv[k]);
-            const uint32_t c = F.color ? __byte_perm(cv[k], 0, sel) : cv[k];
-            if (full || idx < npx) F.texel[idx] = make_float2(d, __uint_as_float(c));
+                for (int q = 0; q < PACK_PX; q++) {
+                    const int li = min(l0 + 32 * q, tpx - 1);
+                    dv[q] = P.depth_is_u16 ? (uint32_t)reinterpret_cast<const uint16_t*>(s_d)[li] : reinterpret_cast<const uint32_t*>(s_d)[li];
+                    if (cbytes == 4u) cv[q] = reinterpret_cast<const uint32_t*>(s_c)[li];
+                    else if (cbytes == 3u) cv[q] = (uint32_t)s_c[3 * li] | ((uint32_t)s_c[3 * li + 1] << 8) | ((uint32_t)s_c[3 * li + 2] << 16);
+                    else cv[q] = 0u;
+                }
+            } else {
+                // images that are not 16-byte aligned tile by tile: the same tile through plain loads
+#pragma unroll
+                for (int q = 0; q < PACK_PX; q++) {
+                    const int idx = tile0 + min(l0 + 32 * q, tpx - 1);
+                    dv[q] = P.depth_is_u16 ? (uint32_t)__ldg((const uint16_t*)F.depth + idx) : __float_as_uint(__ldg((const float*)F.depth + idx));
+                    if (F.color) {
+                        if (P.color_channels == 4) {
+                            cv[q] = __ldg(reinterpret_cast<const uint32_t*>(F.color) + idx);      // 0x..BBGGRR in memory order: byte 0 = channel 0
+                        } else {
+                            const uint8_t* c3 = F.color + (size_t)idx * 3;
+                            cv[q] = (uint32_t)__ldg(c3) | ((uint32_t)__ldg(c3 + 1) << 8) | ((uint32_t)__ldg(c3 + 2) << 16);
+                        }
+                    } else if (F.gray) {
+                        cv[q] = __float_as_uint(__ldg(F.gray + idx));
+                    } else {
+                        cv[q] = 0u;
+                    }
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < PACK_PX; q++) {
+                const int li = l0 + 32 * q;
+                const float d = P.depth_is_u16 ? depth_from_u16(P, dv[q]) : __uint_as_float(dv[q]);
+                const uint32_t c = F.color ? __byte_perm(cv[q], 0, sel) : cv[q];
+                if (li < tpx) F.texel[tile0 + li] = make_float2(d, __uint_as_float(c));
+            }
+            if (P.tma_ok) __syncthreads();   // every thread has read this stage: it may be refilled
         }
         return;
     }
+    const unsigned ridx = L - (unsigned)P.n_pack;
+    const int fidx = (int)(ridx / (unsigned)P.n_alloc_blocks), bidx = (int)(ridx - (unsigned)fidx * (unsigned)P.n_alloc_blocks);
+    const PackFrame& F = P.fr[fidx];
     // ---- alloc role (a8): block allocation from the stride-sampled pixels (f64 chain).
     // A CTA owns a 16 x 16 TILE of samples (64 x 64 pixels at stride 4): a compact patch of the surface touches a few dozen
     // units, against the hundreds a 256-sample raster strip crosses.  Three stages:
@@ -354,7 +367,7 @@ __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(con
         }
     }
     extern __shared__ __align__(128) unsigned char k1_smem[];
-    unsigned long long* s_set = reinterpret_cast<unsigned long long*>(k1_smem);    // ALLOC_SET * 8 <= K1_DYN_SMEM
+    unsigned long long* s_set = reinterpret_cast<unsigned long long*>(k1_smem);    // the launch reserves >= ALLOC_SET * 8 bytes
     for (int q = threadIdx.x; q < ALLOC_SET; q += blockDim.x) s_set[q] = B2R_KEY_EMPTY;
     __syncthreads();
     // (2) one leader per distinct box in the warp; its keys go into the set (a key the set cannot take after 32 probes goes
@@ -757,6 +770,8 @@ B2R_API b2r_tsdf* b2r_tsdf_create(double voxel_length, double sdf_trunc, int col
         e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fuse_smem);
         int nsm = 148, per_sm = 1;
         cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, h->device);
+        h->n_sm = nsm;
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(tsdf_pack_alloc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PACK_STAGES * PACK_TILE * 8 + 256);
         if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 64 * h->fuse_xl, h->fuse_smem);
         if (per_sm < 1) per_sm = 1;
         h->fuse_grid = nsm * per_sm;
@@ -969,10 +984,20 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
             const char* e = getenv("B2R_K1_TMA");      // "0": force the LDG form of the pack role (parity test of the unaligned-image path)
             if (e && atoi(e) == 0) P.tma_ok = 0;
         }
-        const dim3 grid((unsigned)(P.n_alloc_blocks + (npx + 256 * PACK_PX - 1) / (256 * PACK_PX)), (unsigned)take);
-        P.role32 = ((unsigned long long)grid.x * grid.y) * ((unsigned long long)P.n_alloc_blocks * grid.y) < (1ull << 32) ? 1 : 0;
+        P.n_frames = take;
+        P.tiles_per_frame = (int)((npx + PACK_TILE - 1) / PACK_TILE);
+        {
+            const size_t cb = (h->color_type == 1) ? (size_t)color_channels : (h->color_type == 2 ? 4 : 0);
+            P.pack_coff = (uint32_t)(((size_t)PACK_TILE * (depth_is_u16 ? 2 : 4) + 127) & ~(size_t)127);
+            P.pack_stage_bytes = P.pack_coff + (uint32_t)(((size_t)PACK_TILE * cb + 127) & ~(size_t)127);
+        }
+        const long long tiles = (long long)take * P.tiles_per_frame;
+        P.n_pack = (int)(tiles < (long long)h->n_sm * PACK_CTAS_PER_SM ? tiles : (long long)h->n_sm * PACK_CTAS_PER_SM);
+        size_t k1_smem = (size_t)PACK_STAGES * P.pack_stage_bytes;
+        if (k1_smem < (size_t)ALLOC_SET * 8) k1_smem = (size_t)ALLOC_SET * 8;
+        const unsigned grid = (unsigned)(P.n_pack + take * P.n_alloc_blocks);
         const bool prof = prof_begin(h, 1, stream);
-        tsdf_pack_alloc_kernel<<<grid, 256, K1_DYN_SMEM, stream>>>(P);
+        tsdf_pack_alloc_kernel<<<grid, 256, k1_smem, stream>>>(P);
         B2R_CHECK_LAUNCH();
         prof_end(h, prof, stream);
         h->pending += take;

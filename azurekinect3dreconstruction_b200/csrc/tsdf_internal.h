@@ -50,6 +50,7 @@ struct b2r_tsdf {
     size_t mult_px;
     double mult_key[6];      // W, H, fx, fy, cx, cy the image was computed for
     int64_t batches;       // fused so far (alternates the sweep direction)
+    int n_sm;              // SMs of the handle's device
     int fuse_grid;         // persistent grid size of the fusion kernel
     int fuse_smem;         // dynamic shared memory of the fusion kernel
     int fuse_xl;           // x-layers per K2 work item (4 or 2)
