@@ -95,7 +95,7 @@ struct PackParams {
     float fcx, fcy, ifx, ify;      // (float)cx, (float)cy, 1.0f/(float)fx, 1.0f/(float)fy
     double fx, fy, cx, cy;         // f64 intrinsics for the allocation samples
     double trunc, unit_length;
-    int stride, Ws, Hs, tiles_x;   // sample grid and its 16 x 16 tiles
+    int stride, Ws, Hs, tiles_x;   // sample grid and its tiles of 32 x (8 * ALLOC_SPT) samples
     int n_alloc_blocks;            // allocation tiles per frame
     int n_frames, tiles_per_frame, n_pack;   // frames in this launch, pixel tiles per frame, persistent pack CTAs
     uint32_t pack_stage_bytes, pack_coff;    // ring stage size and the colour part's offset inside a stage
@@ -182,12 +182,13 @@ __device__ __noinline__ void alloc_key(const PackParams& P, uint64_t key, uint32
 #ifndef PACK_CTAS_PER_SM
 #define PACK_CTAS_PER_SM 2
 #endif
-#ifndef ALLOC_SET_LOG2
-#define ALLOC_SET_LOG2 10 // shared-memory key set of the alloc role: 1024 slots (a 64 x 64-pixel tile touches a few dozen units)
+#ifndef ALLOC_SPT
+#define ALLOC_SPT 4        // samples per thread of an allocation tile: 32 x (8 * ALLOC_SPT) samples per CTA
 #endif
-#define ALLOC_SET (1 << ALLOC_SET_LOG2)
+#define ALLOC_LIST 2048  // compacted key list of an allocation tile (entries beyond it take the direct path)
+#define ALLOC_SMEM (4096 + ALLOC_LIST * 2)
 #ifndef ALLOC_IT
-#define ALLOC_IT 2       // set slots per thread whose hash probes are in flight together
+#define ALLOC_IT 2       // keys per thread whose hash probes are in flight together
 #endif
 #ifndef PACK_MIN_CTAS
 #define PACK_MIN_CTAS 5
@@ -213,6 +214,8 @@ __global__ void tsdf_mult_kernel(float* __restrict__ mult, int W, int H, float f
 
 #ifdef B2R_K1_TRACE
 __device__ unsigned long long g_k1_trace[4 * 8192];
+__device__ unsigned long long g_k1_marks[8 * 8192];   // per CTA: stage timestamps of the alloc role (thread 0)
+#define K1_MARK(i) do { if (threadIdx.x == 0 && blockIdx.x < 8192) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_k1_marks[8 * blockIdx.x + (i)] = t_; } } while (0)
 __device__ __forceinline__ unsigned long long k1_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 struct K1Trace {
     unsigned long long t0; int role;
@@ -226,9 +229,14 @@ struct K1Trace {
         }
     }
 };
+B2R_API int b2r_debug_k1_marks(unsigned long long* out, int n) {
+    return cudaMemcpyFromSymbol(out, g_k1_marks, sizeof(unsigned long long) * 8 * (size_t)n) == cudaSuccess ? 0 : -1;
+}
 B2R_API int b2r_debug_k1_trace(unsigned long long* out, int n) {
     return cudaMemcpyFromSymbol(out, g_k1_trace, sizeof(unsigned long long) * 4 * (size_t)n) == cudaSuccess ? 0 : -1;
 }
+#else
+#define K1_MARK(i) do { } while (0)
 #endif
 __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(const __grid_constant__ PackParams P) {
     // One launch, two roles.  The first n_pack CTAs are PERSISTENT pack CTAs: each walks the launch's pixel tiles with stride
@@ -328,87 +336,159 @@ __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(con
     const int fidx = (int)(ridx / (unsigned)P.n_alloc_blocks), bidx = (int)(ridx - (unsigned)fidx * (unsigned)P.n_alloc_blocks);
     const PackFrame& F = P.fr[fidx];
     // ---- alloc role (a8): block allocation from the stride-sampled pixels (f64 chain).
-    // A CTA owns a 16 x 16 TILE of samples (64 x 64 pixels at stride 4): a compact patch of the surface touches a few dozen
-    // units, against the hundreds a 256-sample raster strip crosses.  Three stages:
-    //   (1) one thread per sample: the upstream f64 chain -> integer key box;
-    //   (2) lanes holding the same box elect one leader (match.any), and the leaders insert their boxes' keys into a
-    //       shared-memory open-addressing SET: after it the CTA holds every unit key its tile touches exactly once;
-    //   (3) the threads take the set's slots ALLOC_IT at a time: hash-slot probes of all of a thread's keys in flight together
+    // A CTA owns a 32 x 32 TILE of samples (128 x 128 pixels at stride 4; ALLOC_SPT samples per thread): a compact patch of the
+    // surface touches a few dozen units, against the hundreds a raster strip of as many samples crosses, and the latency of
+    // the tile's depth loads and of its hash round trips is paid once per 1024 samples.  Three stages:
+    //   (1) per sample the upstream f64 chain -> integer key box;
+    //   (2) the boxes are OR-ed into a shared-memory bitmap of unit coordinates relative to the tile's minimum corner, which is
+    //       then compacted into a list: every unit key the tile touches, exactly once;
+    //   (3) the threads take the list ALLOC_IT keys at a time: hash-slot probes of all of a thread's keys in flight together
     //       (unit exists and this frame's bit is set: done), then one atomicOr per key that needs it, results consumed after
     //       all are in flight, first touches appended to the touched list with one counter atomic per warp; absent keys take
     //       the CAS probing slow path.  Only the owner rank's keys are probed (sharded handles).
+    K1_MARK(0);
     const int tile_x = bidx % P.tiles_x, tile_y = bidx / P.tiles_x;
-    const int sj = tile_x * 16 + (int)(threadIdx.x & 15u), si = tile_y * 16 + (int)(threadIdx.x >> 4);
     const unsigned lane = threadIdx.x & 31u;
-    int lo[3] = {0, 0, 0};
-    int ex[3] = {0, 0, 0};       // box extents; ex[0] == 0: this sample contributes nothing
-    if (sj < P.Ws && si < P.Hs) {
-        const int i = si * P.stride, j = sj * P.stride;
-        const float d = load_depth_m(P, F.depth, i * P.W + j);
+    const int warp = threadIdx.x >> 5;
+    // thread t takes samples (row 8 k + warp, column lane) of the tile, k = 0 .. ALLOC_SPT - 1: a warp holds 32 neighbours of
+    // one sample row.  All depth loads are issued before the first f64 chain starts.
+    const int sj = tile_x * 32 + (int)lane;
+    float dpt[ALLOC_SPT];
+#pragma unroll
+    for (int k = 0; k < ALLOC_SPT; k++) {
+        const int si = tile_y * (8 * ALLOC_SPT) + 8 * k + warp;
+        dpt[k] = (sj < P.Ws && si < P.Hs) ? load_depth_m(P, F.depth, si * P.stride * P.W + sj * P.stride) : 0.0f;
+    }
+    uint64_t bkey[ALLOC_SPT];      // packed lo corner of the sample's key box
+    uint32_t ecode[ALLOC_SPT];     // its extents, 10 bits each; 0 = the sample contributes nothing
+    int mn[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff};
+#pragma unroll
+    for (int k = 0; k < ALLOC_SPT; k++) {
+        bkey[k] = 0; ecode[k] = 0u;
+        const float d = dpt[k];
         if (d > 0.0f) {
+            const int i = (tile_y * (8 * ALLOC_SPT) + 8 * k + warp) * P.stride, j = sj * P.stride;
             const double z = (double)d;
             const double x = ddiv_const(xdmul(xdsub((double)j, P.cx), z), P.fx, P.rfx, P.ddiv_fast);
             const double y = ddiv_const(xdmul(xdsub((double)i, P.cy), z), P.fy, P.rfy, P.ddiv_fast);
             long long ext[3];
+            int lo[3];
 #pragma unroll
-            for (int k = 0; k < 3; k++) {
-                const double p = xdadd(xdadd(xdadd(xdmul(F.pose[4 * k], x), xdmul(F.pose[4 * k + 1], y)), xdmul(F.pose[4 * k + 2], z)), F.pose[4 * k + 3]);
+            for (int a = 0; a < 3; a++) {
+                const double p = xdadd(xdadd(xdadd(xdmul(F.pose[4 * a], x), xdmul(F.pose[4 * a + 1], y)), xdmul(F.pose[4 * a + 2], z)), F.pose[4 * a + 3]);
                 const double fl = floor(ddiv_const(xdsub(p, P.trunc), P.unit_length, P.runit, P.ddiv_fast));
                 const double fh = floor(ddiv_const(xdadd(p, P.trunc), P.unit_length, P.runit, P.ddiv_fast));
                 const bool ok = fl >= -(double)B2R_KEY_BIAS && fh < (double)B2R_KEY_BIAS;   // also false for NaN
-                lo[k] = ok ? (int)fl : 0;
-                ext[k] = ok ? (long long)((int)fh - (int)fl + 1) : -1;
+                lo[a] = ok ? (int)fl : 0;
+                ext[a] = ok ? (long long)((int)fh - (int)fl + 1) : -1;
             }
             if (ext[0] < 0 || ext[1] < 0 || ext[2] < 0 || ext[0] * ext[1] * ext[2] > 4096) {
                 atomicOr(&P.counters[B2R_C_ERR], 2);   // key out of range / degenerate box: report, don't loop
             } else {
-                ex[0] = (int)ext[0]; ex[1] = (int)ext[1]; ex[2] = (int)ext[2];
+                bkey[k] = b2r_pack_key(lo[0], lo[1], lo[2]);
+                ecode[k] = (uint32_t)ext[0] | ((uint32_t)ext[1] << 10) | ((uint32_t)ext[2] << 20);
+                mn[0] = min(mn[0], lo[0]); mn[1] = min(mn[1], lo[1]); mn[2] = min(mn[2], lo[2]);
             }
         }
     }
+    K1_MARK(1);
+    // (2) The tile's keys as a BITMAP: bit (x, y, z) of a 32 x 32 x 32 window of unit coordinates anchored at the tile's minimum
+    //     corner (a 128 x 128-pixel patch spans a few units per axis; 32 units are 2 m at 4 mm voxels).  A sample whose box
+    //     differs from its left neighbour's ORs one word per (x, y) of its box -- the z extent is a run of bits -- so building
+    //     the tile's duplicate-free key set costs a handful of native 32-bit shared-memory atomics per box and no probing
+    //     loop.  Cells outside the window (a depth discontinuity of more than 31 units inside one tile) go straight to the
+    //     global table.
     extern __shared__ __align__(128) unsigned char k1_smem[];
-    unsigned long long* s_set = reinterpret_cast<unsigned long long*>(k1_smem);    // the launch reserves >= ALLOC_SET * 8 bytes
-    for (int q = threadIdx.x; q < ALLOC_SET; q += blockDim.x) s_set[q] = B2R_KEY_EMPTY;
-    __syncthreads();
-    // (2) one leader per distinct box in the warp; its keys go into the set (a key the set cannot take after 32 probes goes
-    //     straight to the global table: correct, just slower -- only a box of hundreds of units per sample gets there)
+    uint32_t* s_bm = reinterpret_cast<uint32_t*>(k1_smem);                         // 1024 words
+    uint16_t* s_list = reinterpret_cast<uint16_t*>(k1_smem + 4096);                 // ALLOC_LIST compacted cell ids
+    __shared__ int s_wmin[8][3];
+    __shared__ int s_wcnt[8];
     {
-        const uint64_t bkey = ex[0] ? b2r_pack_key(lo[0], lo[1], lo[2]) : (B2R_KEY_EMPTY - 1 - lane);
-        const unsigned ecode = (unsigned)(ex[0] | (ex[1] << 10) | (ex[2] << 20));
-        const unsigned peers = __match_any_sync(0xffffffffu, bkey) & __match_any_sync(0xffffffffu, ecode);
-        if (ex[0] && lane == (unsigned)(__ffs(peers) - 1)) {
-            for (int a = 0; a < ex[0]; a++)
-                for (int b = 0; b < ex[1]; b++)
-                    for (int c = 0; c < ex[2]; c++) {
-                        const unsigned long long key = b2r_pack_key(lo[0] + a, lo[1] + b, lo[2] + c);
-                        unsigned hs = (((unsigned)key * 0x9E3779B1u) ^ ((unsigned)(key >> 21) * 0x85EBCA77u) ^ ((unsigned)(key >> 42) * 0xC2B2AE3Du)) >> (32 - ALLOC_SET_LOG2);
-                        bool placed = false;
-                        for (int probe = 0; probe < 32 && !placed; probe++, hs = (hs + 1) & (ALLOC_SET - 1)) {
-                            const unsigned long long old = atomicCAS(&s_set[hs], (unsigned long long)B2R_KEY_EMPTY, key);
-                            placed = old == B2R_KEY_EMPTY || old == key;
-                        }
-                        if (!placed && (P.world <= 1 || b2r_owner(key, P.world) == P.rank)) alloc_key(P, key, F.bit);
+        const int m0 = __reduce_min_sync(0xffffffffu, mn[0]);
+        const int m1 = __reduce_min_sync(0xffffffffu, mn[1]);
+        const int m2 = __reduce_min_sync(0xffffffffu, mn[2]);
+        if (lane == 0) { s_wmin[warp][0] = m0; s_wmin[warp][1] = m1; s_wmin[warp][2] = m2; }
+    }
+    for (int q = threadIdx.x; q < 1024; q += blockDim.x) s_bm[q] = 0u;
+    __syncthreads();
+    int org[3];
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        int m = s_wmin[0][a];
+#pragma unroll
+        for (int w = 1; w < 8; w++) m = min(m, s_wmin[w][a]);
+        org[a] = m;
+    }
+#pragma unroll
+    for (int k = 0; k < ALLOC_SPT; k++) {
+        const uint64_t pk = __shfl_up_sync(0xffffffffu, bkey[k], 1);
+        const uint32_t pe = __shfl_up_sync(0xffffffffu, ecode[k], 1);
+        if (ecode[k] && (lane == 0 || pk != bkey[k] || pe != ecode[k])) {
+            int lo0, lo1, lo2;
+            b2r_unpack_key(bkey[k], lo0, lo1, lo2);
+            const int e0 = (int)(ecode[k] & 1023u), e1 = (int)((ecode[k] >> 10) & 1023u), e2 = (int)(ecode[k] >> 20);
+            const int rz = lo2 - org[2];                      // >= 0
+            const int nz_in = max(0, min(e2, 32 - rz));      // cells of the z run inside the window
+            const uint32_t zmask = nz_in >= 32 ? 0xffffffffu : (((1u << nz_in) - 1u) << (rz & 31));
+            for (int a = 0; a < e0; a++)
+                for (int b = 0; b < e1; b++) {
+                    const int rx = lo0 + a - org[0], ry = lo1 + b - org[1];
+                    const bool in_xy = rx < 32 && ry < 32;
+                    if (in_xy && nz_in > 0) atomicOr(&s_bm[rx * 32 + ry], zmask);
+                    for (int c = in_xy ? nz_in : 0; c < e2; c++) {          // outside the window: direct (rare)
+                        const uint64_t key = b2r_pack_key(lo0 + a, lo1 + b, lo2 + c);
+                        if (P.world <= 1 || b2r_owner(key, P.world) == P.rank) alloc_key(P, key, F.bit);
                     }
+                }
         }
     }
     __syncthreads();
-    // (3) global probes: every key of the set once
-    for (int c0 = 0; c0 < ALLOC_SET; c0 += 256 * ALLOC_IT) {
+    // compaction: thread t owns words 4 t .. 4 t + 3; set bits -> consecutive entries of s_list (cell id = word * 32 + bit)
+    uint32_t wv[4];
+    int cnt = 0;
+#pragma unroll
+    for (int q = 0; q < 4; q++) { wv[q] = s_bm[4 * threadIdx.x + q]; cnt += __popc(wv[q]); }
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, o); if ((int)lane >= o) incl += v; }
+    if (lane == 31) s_wcnt[warp] = incl;
+    __syncthreads();
+    int pos0 = incl - cnt, nkeys = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) { if (w < warp) pos0 += s_wcnt[w]; nkeys += s_wcnt[w]; }
+#pragma unroll
+    for (int q = 0; q < 4; q++)
+        for (uint32_t m = wv[q]; m; m &= m - 1) {
+            const int cell = (4 * (int)threadIdx.x + q) * 32 + (__ffs(m) - 1);
+            if (pos0 < ALLOC_LIST) {
+                s_list[pos0] = (uint16_t)cell;
+            } else {                                                           // more keys than the list holds: direct (rare)
+                const uint64_t key = b2r_pack_key(org[0] + (cell >> 10), org[1] + ((cell >> 5) & 31), org[2] + (cell & 31));
+                if (P.world <= 1 || b2r_owner(key, P.world) == P.rank) alloc_key(P, key, F.bit);
+            }
+            pos0++;
+        }
+    __syncthreads();
+    nkeys = min(nkeys, ALLOC_LIST);
+    K1_MARK(2);
+    // (3) global probes: every key of the tile once, ALLOC_IT per thread in flight together
+    for (int c0 = 0; c0 < nkeys; c0 += 256 * ALLOC_IT) {
         uint64_t want[ALLOC_IT], got[ALLOC_IT];
         uint32_t slot_i[ALLOC_IT], mk[ALLOC_IT], old[ALLOC_IT];
 #pragma unroll
         for (int it = 0; it < ALLOC_IT; it++) {
-            want[it] = s_set[c0 + it * 256 + (int)threadIdx.x];
-            got[it] = 0; mk[it] = 0; slot_i[it] = 0;
-            if (want[it] != B2R_KEY_EMPTY) {
-                const uint64_t hsh = b2r_mix64(want[it]);
+            const int c = c0 + it * 256 + (int)threadIdx.x;
+            want[it] = B2R_KEY_EMPTY; got[it] = 0; mk[it] = 0; slot_i[it] = 0;
+            if (c < nkeys) {
+                const int cell = s_list[c];
+                const uint64_t key = b2r_pack_key(org[0] + (cell >> 10), org[1] + ((cell >> 5) & 31), org[2] + (cell & 31));
+                const uint64_t hsh = b2r_mix64(key);
                 if (P.world <= 1 || (int)((uint32_t)(hsh >> 33) % (uint32_t)P.world) == P.rank) {
+                    want[it] = key;
                     slot_i[it] = (uint32_t)hsh & P.hash.mask;
                     const B2RSlot* slot = &P.hash.slots[slot_i[it]];
                     got[it] = __ldcg(reinterpret_cast<const unsigned long long*>(&slot->key));
                     mk[it] = __ldcg(&slot->mask[P.q]);
-                } else {
-                    want[it] = B2R_KEY_EMPTY;      // another rank's unit
                 }
             }
         }
@@ -433,6 +513,7 @@ __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(con
             if (app && pos < P.cap_units) P.touched[pos] = (int)slot_i[it];
         }
     }
+    K1_MARK(4);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -948,8 +1029,8 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
         P.trunc = h->sdf_trunc; P.unit_length = h->unit_length; P.stride = h->stride;
         P.Ws = (W + h->stride - 1) / h->stride;
         P.Hs = (H + h->stride - 1) / h->stride;
-        P.tiles_x = (P.Ws + 15) / 16;
-        P.n_alloc_blocks = P.tiles_x * ((P.Hs + 15) / 16);
+        P.tiles_x = (P.Ws + 31) / 32;
+        P.n_alloc_blocks = P.tiles_x * ((P.Hs + 8 * ALLOC_SPT - 1) / (8 * ALLOC_SPT));
         P.rank = h->rank; P.world = h->world; P.q = h->q;
         P.hash = h->hash; P.unit_keys = h->unit_keys; P.touched = h->touched[h->q];
         P.counters = h->counters; P.cap_units = (int)h->cap_units;
@@ -994,7 +1075,7 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
         const long long tiles = (long long)take * P.tiles_per_frame;
         P.n_pack = (int)(tiles < (long long)h->n_sm * PACK_CTAS_PER_SM ? tiles : (long long)h->n_sm * PACK_CTAS_PER_SM);
         size_t k1_smem = (size_t)PACK_STAGES * P.pack_stage_bytes;
-        if (k1_smem < (size_t)ALLOC_SET * 8) k1_smem = (size_t)ALLOC_SET * 8;
+        if (k1_smem < (size_t)ALLOC_SMEM) k1_smem = (size_t)ALLOC_SMEM;
         const unsigned grid = (unsigned)(P.n_pack + take * P.n_alloc_blocks);
         const bool prof = prof_begin(h, 1, stream);
         tsdf_pack_alloc_kernel<<<grid, 256, k1_smem, stream>>>(P);
