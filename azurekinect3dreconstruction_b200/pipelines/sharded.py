@@ -176,19 +176,23 @@ class ShardedTSDFVolume:
 
 
 # ---- host-frame ingest at world > 1: upload 1/world per rank over PCIe, exchange over NVLink -----------------------
-def superchunk_plan(n_frames: int, world: int, per: int):
-    """Frames are consumed in super-chunks of world * per; inside super-chunk i rank r uploads the `per` consecutive
-    frames starting at i * world * per + r * per, so the rank-major all-gather buffer is in GLOBAL FRAME ORDER (fusion
-    order decides the running averages bit for bit).  Returns [(first_frame, n_valid, [(f0, f1) per rank])]."""
-    S = world * per
-    plan = []
-    for f_start in range(0, n_frames, S):
+def superchunk_plan(n_frames: int, world: int, per, ramp: bool = False):
+    """Frames are consumed in super-chunks of world * per; inside a super-chunk rank r uploads the `per` consecutive
+    frames starting at first + r * per, so the rank-major all-gather buffer is in GLOBAL FRAME ORDER (fusion
+    order decides the running averages bit for bit).  ramp=True starts with small super-chunks (per = 1, 2, 4, ... up to
+    `per`): the first integration then starts after one frame's upload + gather instead of `per` frames', and the pipeline's
+    fill time shrinks accordingly.  Returns [(first_frame, n_valid, [(f0, f1) per rank])]."""
+    plan, f_start, cur = [], 0, (1 if ramp else int(per))
+    while f_start < n_frames:
+        S = world * cur
         n_valid = min(S, n_frames - f_start)
         ranges = []
         for r in range(world):
-            f0 = min(f_start + r * per, f_start + n_valid)
-            ranges.append((f0, min(f0 + per, f_start + n_valid)))
+            f0 = min(f_start + r * cur, f_start + n_valid)
+            ranges.append((f0, min(f0 + cur, f_start + n_valid)))
         plan.append((f_start, n_valid, ranges))
+        f_start += n_valid
+        cur = min(int(per), cur * 2)
     return plan
 
 
@@ -196,80 +200,106 @@ class HostFrameExchange:
     """north_star: "each frame's depth/color/pose is broadcast and each rank integrates only its own blocks".
     When the frames start in HOST memory, pushing every frame through every GPU's PCIe link would cap the job at one
     link's bandwidth whatever the GPU count.  Instead rank r copies only its 1/world share host->device (pinned,
-    asynchronous, on a copy stream), and one NCCL all-gather per super-chunk hands every rank all frames over
-    NVLink/NVSwitch.  Three streams, double-buffered: the copy stream uploads super-chunk i + 2 and the communication
-    stream gathers super-chunk i + 1 while the caller's stream integrates super-chunk i.
-    `consume(depth, color, first_frame, n_valid)` receives device tensors in global frame order."""
+    asynchronous, on a copy stream) into frame RECORDS [depth | colour] (256-byte aligned parts), and ONE NCCL all-gather
+    per super-chunk hands every rank all records over NVLink/NVSwitch.  Three streams, double-buffered: the copy stream
+    uploads super-chunk i + 2 and the communication stream gathers super-chunk i + 1 while the caller's stream integrates
+    super-chunk i; the super-chunks ramp up (1, 2, 4, ... frames per rank) so the pipeline fills quickly.
+    `consume(depth_ptrs, color_ptrs, first_frame, n_valid)` receives device addresses in global frame order."""
 
-    def __init__(self, frame_shape, color_channels: int, per: int = 8, group=None, device=None):
+    def __init__(self, frame_shape, color_channels: int, per: int = 8, group=None, device=None, ramp: bool = True):
         import torch.distributed as dist
         self.dist, self.group = dist, group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
-        self.per, (self.H, self.W), self.ch = int(per), frame_shape, int(color_channels)
+        self.per, (self.H, self.W), self.ch, self.ramp = int(per), frame_shape, int(color_channels), bool(ramp)
         self.device = device
         cuda = device is not None and torch.device(device).type == "cuda"
-        S = self.per * self.world
-        mk = lambda n, shape, dt: [torch.zeros((n,) + shape, dtype=dt, device=device) for _ in range(2)]
-        self.ld, self.lc = mk(self.per, (self.H, self.W), torch.int16), mk(self.per, (self.H, self.W, self.ch), torch.uint8)
-        self.gd, self.gc = mk(S, (self.H, self.W), torch.int16), mk(S, (self.H, self.W, self.ch), torch.uint8)
+        al = lambda n: (n + 255) & ~255
+        self.dbytes, self.cbytes = self.H * self.W * 2, self.H * self.W * self.ch
+        self.off_color = al(self.dbytes)
+        self.rec = self.off_color + al(self.cbytes)
+        self.local = [torch.zeros((self.per, self.rec), dtype=torch.uint8, device=device) for _ in range(2)]
+        self.gathered = [torch.zeros((self.world * self.per, self.rec), dtype=torch.uint8, device=device) for _ in range(2)]
         self.copy_stream = torch.cuda.Stream(device=device) if cuda else None
         self.comm_stream = torch.cuda.Stream(device=device) if cuda else None
         ev = lambda: [torch.cuda.Event() for _ in range(2)] if cuda else None
         self.uploaded, self.consumed = ev(), ev()       # local slot: filled by the copy stream / read by the gather
-        self.gathered, self.released = ev(), ev()       # gathered slot: filled by the gather / read by the consumer
+        self.gathered_ev, self.released = ev(), ev()    # gathered slot: filled by the gather / read by the consumer
         self.bytes_uploaded = 0
+        self.timeline = None                            # set to [] to collect (stage, super-chunk, start event, end event)
 
-    def _upload(self, slot, depth_h, color_h, f0, f1):
+    def _mark(self, stage, i, stream):
+        if self.timeline is None or stream is None:
+            return None
+        e = torch.cuda.Event(enable_timing=True)
+        e.record(stream)
+        self.timeline.append((stage, i, e))
+        return e
+
+    def _upload(self, i, slot, depth_h, color_h, f0, f1, cur):
         n = f1 - f0
+        loc = self.local[slot]
+        dview = lambda k: loc[k, :self.dbytes]
         if self.copy_stream is None:
-            if n > 0:
-                self.ld[slot][:n].copy_(depth_h[f0:f1].view(torch.int16)); self.lc[slot][:n].copy_(color_h[f0:f1])
+            for k in range(n):
+                loc[k, :self.dbytes] = depth_h[f0 + k].reshape(-1).view(torch.uint8)
+                loc[k, self.off_color:self.off_color + self.cbytes] = color_h[f0 + k].reshape(-1)
         else:
             with torch.cuda.stream(self.copy_stream):
                 self.copy_stream.wait_event(self.consumed[slot])       # the gather that read this slot two rounds ago
+                self._mark("upload_begin", i, self.copy_stream)
                 if n > 0:
-                    self.ld[slot][:n].copy_(depth_h[f0:f1].view(torch.int16), non_blocking=True)
-                    self.lc[slot][:n].copy_(color_h[f0:f1], non_blocking=True)
+                    # two strided 2-D copies (rows = frames) straight from the pinned host frames into the records
+                    loc[:n, :self.dbytes].copy_(depth_h[f0:f1].reshape(n, -1).view(torch.uint8), non_blocking=True)
+                    loc[:n, self.off_color:self.off_color + self.cbytes].copy_(color_h[f0:f1].reshape(n, -1), non_blocking=True)
+                self._mark("upload_end", i, self.copy_stream)
                 self.uploaded[slot].record(self.copy_stream)
         self.bytes_uploaded += n * self.H * self.W * (2 + self.ch)
 
-    def _gather(self, slot):
-        def both():
-            self.dist.all_gather_into_tensor(self.gd[slot].view(torch.uint8).reshape(-1), self.ld[slot].view(torch.uint8).reshape(-1), group=self.group)
-            self.dist.all_gather_into_tensor(self.gc[slot].reshape(-1), self.lc[slot].reshape(-1), group=self.group)
+    def _gather(self, i, slot, cur):
+        src = self.local[slot][:cur].reshape(-1)
+        dst = self.gathered[slot][: self.world * cur].reshape(-1)
         if self.comm_stream is None:
-            both()
+            self.dist.all_gather_into_tensor(dst, src, group=self.group)
             return
         with torch.cuda.stream(self.comm_stream):
             self.comm_stream.wait_event(self.uploaded[slot])
             self.comm_stream.wait_event(self.released[slot])          # the consumer of this slot two rounds ago has read it
-            both()
+            self._mark("gather_begin", i, self.comm_stream)
+            self.dist.all_gather_into_tensor(dst, src, group=self.group)
+            self._mark("gather_end", i, self.comm_stream)
             self.consumed[slot].record(self.comm_stream)
-            self.gathered[slot].record(self.comm_stream)
+            self.gathered_ev[slot].record(self.comm_stream)
 
     def run(self, depth_h: torch.Tensor, color_h: torch.Tensor, consume) -> None:
         """depth_h (F,H,W) uint16, color_h (F,H,W,ch) uint8 -- pinned host tensors (identical on every rank)."""
-        plan = superchunk_plan(int(depth_h.shape[0]), self.world, self.per)
+        plan = superchunk_plan(int(depth_h.shape[0]), self.world, self.per, self.ramp)
         if not plan:
             return
         n = len(plan)
+        cur_of = lambda i: max(f1 - f0 for f0, f1 in plan[i][2])     # frames per rank of super-chunk i (its rank-0 share)
         if self.comm_stream is not None:
             # the buffers may still be read by work the caller enqueued earlier (a previous run's last consumers)
             self.copy_stream.wait_stream(torch.cuda.current_stream())
             self.comm_stream.wait_stream(torch.cuda.current_stream())
-        self._upload(0, depth_h, color_h, *plan[0][2][self.rank])
+        self._upload(0, 0, depth_h, color_h, *plan[0][2][self.rank], cur_of(0))
         if n > 1:
-            self._upload(1, depth_h, color_h, *plan[1][2][self.rank])
-        self._gather(0)
+            self._upload(1, 1, depth_h, color_h, *plan[1][2][self.rank], cur_of(1))
+        self._gather(0, 0, cur_of(0))
         for i, (f_start, n_valid, _) in enumerate(plan):
             slot = i & 1
             if i + 1 < n:
-                self._gather(slot ^ 1)                                 # overlaps the integration of super-chunk i
+                self._gather(i + 1, slot ^ 1, cur_of(i + 1))           # overlaps the integration of super-chunk i
             if i + 2 < n:
-                self._upload(slot, depth_h, color_h, *plan[i + 2][2][self.rank])   # waits for gather i to have read the slot
+                self._upload(i + 2, slot, depth_h, color_h, *plan[i + 2][2][self.rank], cur_of(i + 2))   # waits for gather i to have read the slot
+            cur = cur_of(i)
             if self.comm_stream is not None:
-                torch.cuda.current_stream().wait_event(self.gathered[slot])
-            consume(self.gd[slot][:n_valid].view(torch.uint16), self.gc[slot][:n_valid], f_start, n_valid)
+                torch.cuda.current_stream().wait_event(self.gathered_ev[slot])
+            base = self.gathered[slot].data_ptr()
+            # frame f_start + k sits in row k of the gathered buffer (rank-major rows of `cur` records = global frame order)
+            dptr = [base + k * self.rec for k in range(n_valid)]
+            self._mark("integrate_begin", i, torch.cuda.current_stream() if self.comm_stream is not None else None)
+            consume(dptr, [p + self.off_color for p in dptr], f_start, n_valid)
+            self._mark("integrate_end", i, torch.cuda.current_stream() if self.comm_stream is not None else None)
             if self.comm_stream is not None:
                 self.released[slot].record(torch.cuda.current_stream())
 
@@ -281,7 +311,7 @@ def integrate_host_frames(vol: ScalableTSDFVolume, depth_h: torch.Tensor, color_
         vol.integrate_raw(depth_h, color_h, intrinsic, extrinsics, depth_scale, depth_trunc)
         return
     E = np.asarray(extrinsics, dtype=np.float64).reshape(-1, 4, 4)
-    exchange.run(depth_h, color_h, lambda d, c, f0, n: vol.integrate_raw(d, c, intrinsic, E[f0:f0 + n], depth_scale, depth_trunc))
+    exchange.run(depth_h, color_h, lambda dp, cp, f0, n: vol.integrate_frames(dp, cp, exchange.ch, intrinsic, E[f0:f0 + n], depth_scale, depth_trunc))
 
 
 # ---- config 5: one camera stream per rank, every tick's frames exchanged over NVLink ---------------------------------

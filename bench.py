@@ -318,7 +318,8 @@ def main():
     exchange = None
     if world > 1:
         from azurekinect3dreconstruction_b200.pipelines import sharded
-        exchange = sharded.HostFrameExchange((H, W), 3, per=int(os.environ.get("B2R_EXCHANGE_PER", "8")), device=dev)
+        exchange = sharded.HostFrameExchange((H, W), 3, per=int(os.environ.get("B2R_EXCHANGE_PER", "8")), device=dev,
+                                             ramp=os.environ.get("B2R_EXCHANGE_RAMP", "1") != "0")
 
     def step_e2e():
         vol.reset()
@@ -333,6 +334,20 @@ def main():
     ms_e2e = timed(step_e2e, args.steps)
     fps_e2e = args.frames * args.steps / (ms_e2e * 1e-3)
     st_e2e = vol.stats()
+    if exchange is not None and os.environ.get("B2R_E2E_TIMELINE"):
+        # one more step with an event at the start and end of every upload / gather / integrate stage (rank 0's view): what
+        # bounds the end-to-end arm at N > 1 is read off this timeline (profiles/r2_e2e_timeline_nN.json)
+        exchange.timeline = []
+        barrier()
+        t_origin = torch.cuda.Event(enable_timing=True)
+        t_origin.record()
+        step_e2e()
+        barrier()
+        if rank == 0:
+            rows = [{"stage": st_, "superchunk": i, "t_ms": t_origin.elapsed_time(e)} for st_, i, e in exchange.timeline]
+            with open(os.environ["B2R_E2E_TIMELINE"], "w") as f:
+                json.dump({"n_gpus": world, "frames": args.frames, "per": exchange.per, "ramp": exchange.ramp, "events": rows}, f)
+        exchange.timeline = None
     # the end-to-end arm must leave this rank's shard exactly as the device-resident arm did (same units, same voxel updates)
     if (st_e2e["num_units"], st_e2e["updated_voxels"], st_e2e["errors"]) != (st["num_units"], st["updated_voxels"], st["errors"]):
         raise RuntimeError("e2e arm diverged from the device arm: %r vs %r" % (st_e2e, st))

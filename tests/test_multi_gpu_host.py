@@ -54,16 +54,24 @@ def _worker(rank, world, port, q):
         F, H, W = 11, 4, 6                                                       # ragged: 11 frames, super-chunks of 2 x 3
         depth = (torch.arange(F * H * W, dtype=torch.int32) % 60000).to(torch.int16).reshape(F, H, W).view(torch.uint16)
         color = (torch.arange(F * H * W * 3, dtype=torch.int64) % 251).to(torch.uint8).reshape(F, H, W, 3)
-        ex = sharded.HostFrameExchange((H, W), 3, per=3, device=None)
-        seen = []
-        ex.run(depth, color, lambda d, c, f0, n: seen.append((f0, n, d.clone(), c.clone())))
-        assert [(f0, n) for f0, n, _, _ in seen] == [(0, 6), (6, 5)]
-        got_d = torch.cat([d.view(torch.int16) for _, _, d, _ in seen])
-        got_c = torch.cat([c for _, _, _, c in seen])
-        assert torch.equal(got_d, depth.view(torch.int16)) and torch.equal(got_c, color)
-        assert ex.bytes_uploaded == (6 if rank == 0 else 5) * H * W * 5          # rank 0: frames 0-2, 6-8; rank 1: 3-5, 9-10
-        # config 5's stream exchange: 4 streams (2 per rank), 5 ticks in batches of 2 -> every rank sees every frame, tick-major
         import ctypes as C
+        for ramp, expect in ((False, [(0, 6), (6, 5)]), (True, [(0, 2), (2, 4), (6, 5)])):
+            ex = sharded.HostFrameExchange((H, W), 3, per=3, device=None, ramp=ramp)
+            seen = []
+
+            def consume(dp, cp, f0, n):
+                assert len(dp) == len(cp) == n
+                d = [np.frombuffer((C.c_uint8 * (H * W * 2)).from_address(p), dtype=np.int16).copy().reshape(H, W) for p in dp]
+                c = [np.frombuffer((C.c_uint8 * (H * W * 3)).from_address(p), dtype=np.uint8).copy().reshape(H, W, 3) for p in cp]
+                seen.append((f0, n, np.stack(d), np.stack(c)))
+            ex.run(depth, color, consume)
+            assert [(f0, n) for f0, n, _, _ in seen] == expect
+            got_d = np.concatenate([d for _, _, d, _ in seen])
+            got_c = np.concatenate([c for _, _, _, c in seen])
+            assert np.array_equal(got_d, depth.view(torch.int16).numpy()) and np.array_equal(got_c, color.numpy())
+            plan = sharded.superchunk_plan(F, world, 3, ramp)
+            assert ex.bytes_uploaded == sum(f1 - f0 for _, _, rg in plan for f0, f1 in [rg[rank]]) * H * W * 5
+        # config 5's stream exchange: 4 streams (2 per rank), 5 ticks in batches of 2 -> every rank sees every frame, tick-major
         S, ticks, H5, W5 = 4, 5, 3, 8
         tex = sharded.StreamTickExchange((H5, W5), 3, S, ticks_per_batch=2, device=None)
         assert (tex.rank, tex.world, tex.s_local) == (rank, world, 2)
@@ -117,8 +125,9 @@ def test_unit_owner_python_mirror_matches_library():
 
 
 def test_superchunk_plan_keeps_global_frame_order():
-    for F, world, per in ((300, 8, 8), (11, 2, 3), (5, 4, 2), (64, 8, 8), (1, 2, 4)):
-        plan = sharded.superchunk_plan(F, world, per)
+    for F, world, per, ramp in ((300, 8, 8, False), (11, 2, 3, False), (5, 4, 2, False), (64, 8, 8, False), (1, 2, 4, False),
+                                (300, 8, 8, True), (11, 2, 3, True), (7, 4, 4, True), (300, 2, 16, True)):
+        plan = sharded.superchunk_plan(F, world, per, ramp)
         covered = []
         for f_start, n_valid, ranges in plan:
             assert len(ranges) == world and 0 < n_valid <= world * per
@@ -126,7 +135,8 @@ def test_superchunk_plan_keeps_global_frame_order():
             for r, (f0, f1) in enumerate(ranges):
                 assert 0 <= f1 - f0 <= per
                 if f1 > f0:
-                    assert f0 - f_start == r * per                              # slot index in the gathered buffer == frame index
+                    cur = ranges[0][1] - ranges[0][0]
+                    assert f0 - f_start == r * cur                              # row in the gathered buffer == frame index
                 covered += list(range(f0, f1))
             assert covered[-n_valid:] == list(range(f_start, f_start + n_valid))
         assert covered == list(range(F))
