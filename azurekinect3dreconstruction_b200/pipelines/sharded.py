@@ -215,10 +215,12 @@ class HostFrameExchange:
         cuda = device is not None and torch.device(device).type == "cuda"
         al = lambda n: (n + 255) & ~255
         self.dbytes, self.cbytes = self.H * self.W * 2, self.H * self.W * self.ch
-        self.off_color = al(self.dbytes)
-        self.rec = self.off_color + al(self.cbytes)
-        self.local = [torch.zeros((self.per, self.rec), dtype=torch.uint8, device=device) for _ in range(2)]
-        self.gathered = [torch.zeros((self.world * self.per, self.rec), dtype=torch.uint8, device=device) for _ in range(2)]
+        # a rank's share of a super-chunk of `cur` frames per rank travels as ONE block [cur depth images | cur colour images]
+        # (each image padded to 256 bytes): two contiguous DMA copies fill it, one all-gather moves it
+        self.dpad, self.cpad = al(self.dbytes), al(self.cbytes)
+        self.rec = self.dpad + self.cpad
+        self.local = [torch.zeros((self.per * self.rec,), dtype=torch.uint8, device=device) for _ in range(2)]
+        self.gathered = [torch.zeros((self.world * self.per * self.rec,), dtype=torch.uint8, device=device) for _ in range(2)]
         self.copy_stream = torch.cuda.Stream(device=device) if cuda else None
         self.comm_stream = torch.cuda.Stream(device=device) if cuda else None
         ev = lambda: [torch.cuda.Event() for _ in range(2)] if cuda else None
@@ -238,26 +240,38 @@ class HostFrameExchange:
     def _upload(self, i, slot, depth_h, color_h, f0, f1, cur):
         n = f1 - f0
         loc = self.local[slot]
-        dview = lambda k: loc[k, :self.dbytes]
+        dblk = loc[: cur * self.dpad].view(cur, self.dpad)
+        cblk = loc[cur * self.dpad: cur * self.rec].view(cur, self.cpad)
+
+        def fill(nb):
+            # contiguous destinations only: a strided host -> device copy_ would be staged and scattered by a KERNEL, which waits
+            # for SM room behind the persistent fusion grid; cudaMemcpyAsync on the copy engine does not
+            if n <= 0:
+                return
+            if self.dpad == self.dbytes:
+                dblk[:n].copy_(depth_h[f0:f1].reshape(n, -1).view(torch.uint8), non_blocking=nb)
+            else:
+                for k in range(n):
+                    dblk[k, :self.dbytes].copy_(depth_h[f0 + k].reshape(-1).view(torch.uint8), non_blocking=nb)
+            if self.cpad == self.cbytes:
+                cblk[:n].copy_(color_h[f0:f1].reshape(n, -1), non_blocking=nb)
+            else:
+                for k in range(n):
+                    cblk[k, :self.cbytes].copy_(color_h[f0 + k].reshape(-1), non_blocking=nb)
         if self.copy_stream is None:
-            for k in range(n):
-                loc[k, :self.dbytes] = depth_h[f0 + k].reshape(-1).view(torch.uint8)
-                loc[k, self.off_color:self.off_color + self.cbytes] = color_h[f0 + k].reshape(-1)
+            fill(False)
         else:
             with torch.cuda.stream(self.copy_stream):
                 self.copy_stream.wait_event(self.consumed[slot])       # the gather that read this slot two rounds ago
                 self._mark("upload_begin", i, self.copy_stream)
-                if n > 0:
-                    # two strided 2-D copies (rows = frames) straight from the pinned host frames into the records
-                    loc[:n, :self.dbytes].copy_(depth_h[f0:f1].reshape(n, -1).view(torch.uint8), non_blocking=True)
-                    loc[:n, self.off_color:self.off_color + self.cbytes].copy_(color_h[f0:f1].reshape(n, -1), non_blocking=True)
+                fill(True)
                 self._mark("upload_end", i, self.copy_stream)
                 self.uploaded[slot].record(self.copy_stream)
         self.bytes_uploaded += n * self.H * self.W * (2 + self.ch)
 
     def _gather(self, i, slot, cur):
-        src = self.local[slot][:cur].reshape(-1)
-        dst = self.gathered[slot][: self.world * cur].reshape(-1)
+        src = self.local[slot][: cur * self.rec]
+        dst = self.gathered[slot][: self.world * cur * self.rec]
         if self.comm_stream is None:
             self.dist.all_gather_into_tensor(dst, src, group=self.group)
             return
@@ -295,10 +309,11 @@ class HostFrameExchange:
             if self.comm_stream is not None:
                 torch.cuda.current_stream().wait_event(self.gathered_ev[slot])
             base = self.gathered[slot].data_ptr()
-            # frame f_start + k sits in row k of the gathered buffer (rank-major rows of `cur` records = global frame order)
-            dptr = [base + k * self.rec for k in range(n_valid)]
+            # frame f_start + k is image k % cur of rank k // cur's block (rank-major blocks = global frame order)
+            dptr = [base + (k // cur) * cur * self.rec + (k % cur) * self.dpad for k in range(n_valid)]
+            cptr = [base + (k // cur) * cur * self.rec + cur * self.dpad + (k % cur) * self.cpad for k in range(n_valid)]
             self._mark("integrate_begin", i, torch.cuda.current_stream() if self.comm_stream is not None else None)
-            consume(dptr, [p + self.off_color for p in dptr], f_start, n_valid)
+            consume(dptr, cptr, f_start, n_valid)
             self._mark("integrate_end", i, torch.cuda.current_stream() if self.comm_stream is not None else None)
             if self.comm_stream is not None:
                 self.released[slot].record(torch.cuda.current_stream())
