@@ -202,11 +202,11 @@ class HostFrameExchange:
     link's bandwidth whatever the GPU count.  Instead rank r copies only its 1/world share host->device (pinned,
     asynchronous, on a copy stream) into frame RECORDS [depth | colour] (256-byte aligned parts), and ONE NCCL all-gather
     per super-chunk hands every rank all records over NVLink/NVSwitch.  Three streams, double-buffered: the copy stream
-    uploads super-chunk i + 2 and the communication stream gathers super-chunk i + 1 while the caller's stream integrates
-    super-chunk i; the super-chunks ramp up (1, 2, 4, ... frames per rank) so the pipeline fills quickly.
+    and the communication stream run up to `slots` super-chunks ahead of the caller's stream, which integrates; the
+    super-chunks ramp up (1, 2, 4, ... frames per rank) so the pipeline fills quickly.
     `consume(depth_ptrs, color_ptrs, first_frame, n_valid)` receives device addresses in global frame order."""
 
-    def __init__(self, frame_shape, color_channels: int, per: int = 8, group=None, device=None, ramp: bool = True):
+    def __init__(self, frame_shape, color_channels: int, per: int = 8, group=None, device=None, ramp: bool = True, slots: int = 4):
         import torch.distributed as dist
         self.dist, self.group = dist, group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
@@ -219,11 +219,12 @@ class HostFrameExchange:
         # (each image padded to 256 bytes): two contiguous DMA copies fill it, one all-gather moves it
         self.dpad, self.cpad = al(self.dbytes), al(self.cbytes)
         self.rec = self.dpad + self.cpad
-        self.local = [torch.zeros((self.per * self.rec,), dtype=torch.uint8, device=device) for _ in range(2)]
-        self.gathered = [torch.zeros((self.world * self.per * self.rec,), dtype=torch.uint8, device=device) for _ in range(2)]
+        self.ns = max(2, int(slots))                    # ring depth: uploads / gathers run up to `slots` super-chunks ahead
+        self.local = [torch.zeros((self.per * self.rec,), dtype=torch.uint8, device=device) for _ in range(self.ns)]
+        self.gathered = [torch.zeros((self.world * self.per * self.rec,), dtype=torch.uint8, device=device) for _ in range(self.ns)]
         self.copy_stream = torch.cuda.Stream(device=device) if cuda else None
         self.comm_stream = torch.cuda.Stream(device=device) if cuda else None
-        ev = lambda: [torch.cuda.Event() for _ in range(2)] if cuda else None
+        ev = lambda: [torch.cuda.Event() for _ in range(self.ns)] if cuda else None
         self.uploaded, self.consumed = ev(), ev()       # local slot: filled by the copy stream / read by the gather
         self.gathered_ev, self.released = ev(), ev()    # gathered slot: filled by the gather / read by the consumer
         self.bytes_uploaded = 0
@@ -295,16 +296,27 @@ class HostFrameExchange:
             # the buffers may still be read by work the caller enqueued earlier (a previous run's last consumers)
             self.copy_stream.wait_stream(torch.cuda.current_stream())
             self.comm_stream.wait_stream(torch.cuda.current_stream())
-        self._upload(0, 0, depth_h, color_h, *plan[0][2][self.rank], cur_of(0))
-        if n > 1:
-            self._upload(1, 1, depth_h, color_h, *plan[1][2][self.rank], cur_of(1))
-        self._gather(0, 0, cur_of(0))
+        ns = self.ns
+        nxt = {"up": 0, "ga": 0}
+
+        def pump(i):
+            # enqueue everything whose predecessors are enqueued: upload j needs gather j - ns (it read the local slot), gather k
+            # needs upload k and integration k - ns (it read the gathered slot); the events order the actual execution
+            progress = True
+            while progress:
+                progress = False
+                while nxt["ga"] < n and nxt["ga"] < nxt["up"] and nxt["ga"] < i + ns:
+                    self._gather(nxt["ga"], nxt["ga"] % ns, cur_of(nxt["ga"]))
+                    nxt["ga"] += 1
+                    progress = True
+                while nxt["up"] < n and nxt["up"] < nxt["ga"] + ns:
+                    j = nxt["up"]
+                    self._upload(j, j % ns, depth_h, color_h, *plan[j][2][self.rank], cur_of(j))
+                    nxt["up"] += 1
+                    progress = True
         for i, (f_start, n_valid, _) in enumerate(plan):
-            slot = i & 1
-            if i + 1 < n:
-                self._gather(i + 1, slot ^ 1, cur_of(i + 1))           # overlaps the integration of super-chunk i
-            if i + 2 < n:
-                self._upload(i + 2, slot, depth_h, color_h, *plan[i + 2][2][self.rank], cur_of(i + 2))   # waits for gather i to have read the slot
+            slot = i % ns
+            pump(i)
             cur = cur_of(i)
             if self.comm_stream is not None:
                 torch.cuda.current_stream().wait_event(self.gathered_ev[slot])
