@@ -525,8 +525,9 @@ __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(con
 
 struct FuseParams {
     int nframes;
-    int q;                   // batch buffer being fused; (q+2)%3 = previous batch (its masks get cleared),
-                             // (q+1)%3 = next batch (its counter gets zeroed)
+    int q;                   // batch buffer being fused; (q+2)%3 = previous batch: its masks get cleared by this pass and its
+                             // counters are zeroed by the pass's last CTA (the buffer's next user is the batch after next --
+                             // (q+1)%3 may already be filling: the next batch's K1 can run beside this pass)
     int ring_rounds;         // passes with at least this many items per CTA run the prefetching ring
     int reverse;             // sweep direction (alternates per batch: the tail of the last sweep is still in L2)
     float vl, hv, trunc, inv_trunc;
@@ -560,11 +561,7 @@ __global__ void __launch_bounds__(64 * XL, FUSE_MIN_CTAS * 4 / XL) tsdf_fuse_ker
         const int qp = (P.q + 2) % 3;
         const int Tp = min(P.counters[B2R_C_TOUCHED0 + qp], P.cap_units);
         for (int i = blockIdx.x * FUSE_THREADS + tid; i < Tp; i += gridDim.x * FUSE_THREADS) P.slots[P.touched_prev[i]].mask[qp] = 0u;
-        if (blockIdx.x == 0 && tid == 0) {
-            P.counters[B2R_C_TOUCHED0 + (P.q + 1) % 3] = 0;
-            P.counters[B2R_C_WORK0 + (P.q + 1) % 3] = 0;   // the next pass draws its items from a fresh counter
-            P.counters[B2R_C_LAST_TOUCHED] = T;
-        }
+        if (blockIdx.x == 0 && tid == 0) P.counters[B2R_C_LAST_TOUCHED] = T;
     }
     if (tid == 0) {
         for (int s = 0; s < FUSE_STAGES; s++) mbar_init(&full_bar[s], 1);
@@ -759,6 +756,18 @@ __global__ void __launch_bounds__(64 * XL, FUSE_MIN_CTAS * 4 / XL) tsdf_fuse_ker
         if (upd) atomicAdd(reinterpret_cast<unsigned long long*>(&P.counters[B2R_C_UPDATED]), (unsigned long long)upd);
         if (tid == 0 && pairs) atomicAdd(reinterpret_cast<unsigned long long*>(&P.counters[B2R_C_TOUCHED_TOTAL]), (unsigned long long)pairs);
     }
+    // The last CTA out recycles the previous batch's buffer: every CTA has read its touched count (the mask-clearing loop
+    // above) before it takes a ticket.
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        if (atomicAdd(&P.counters[B2R_C_TICKET], 1) == (int)gridDim.x - 1) {
+            const int qp = (P.q + 2) % 3;
+            P.counters[B2R_C_TOUCHED0 + qp] = 0;
+            P.counters[B2R_C_WORK0 + qp] = 0;      // the pass after next draws its items from a fresh counter
+            P.counters[B2R_C_TICKET] = 0;
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -782,7 +791,10 @@ static void tsdf_free(b2r_tsdf* h) {
     cudaFree(h->hash.slots); cudaFree(h->unit_keys);
     cudaFree(h->pool); cudaFree(h->counters); cudaFree(h->scratch);
     for (int i = 0; i < 3; i++) cudaFree(h->touched[i]);
-    for (int i = 0; i < B2R_MAX_BATCH; i++) cudaFree(h->texel[i]);
+    for (int i = 0; i < B2R_MAX_BATCH; i++) { cudaFree(h->texel[0][i]); cudaFree(h->texel[1][i]); }
+    if (h->fuse_stream) cudaStreamDestroy(h->fuse_stream);
+    if (h->ev_k1) cudaEventDestroy(h->ev_k1);
+    for (int i = 0; i < 3; i++) if (h->ev_k2[i]) cudaEventDestroy(h->ev_k2[i]);
     cudaFree(h->mult);
     for (int i = 0; i < B2R_HOST_RING; i++) {
         if (h->ev_copied[i]) cudaEventDestroy(h->ev_copied[i]);
@@ -855,7 +867,18 @@ B2R_API b2r_tsdf* b2r_tsdf_create(double voxel_length, double sdf_trunc, int col
         if (e == cudaSuccess) e = cudaFuncSetAttribute(tsdf_pack_alloc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PACK_STAGES * PACK_TILE * 8 + 256);
         if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 64 * h->fuse_xl, h->fuse_smem);
         if (per_sm < 1) per_sm = 1;
+        // B2R_FUSE_CTAS_PER_SM: fewer resident fusion CTAs than fit leave registers / shared memory on every SM for what runs
+        // beside the pass (the next batch's K1 on the side stream, NCCL's gather kernels); default: all that fit
+        h->overlap = env_int("B2R_TSDF_OVERLAP", world > 1 ? 1 : 0, 0, 1);
+        // overlap mode keeps one CTA slot per SM free for what runs beside a pass (K1 of the next batch, NCCL's kernels):
+        // measured + 4 % on the pass, against K1 (a fifth of a sharded rank's frame time) disappearing behind it
+        per_sm = env_int("B2R_FUSE_CTAS_PER_SM", h->overlap && per_sm > 1 ? per_sm - 1 : per_sm, 1, per_sm);
         h->fuse_grid = nsm * per_sm;
+        if (h->overlap) {
+            if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->fuse_stream, cudaStreamNonBlocking);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_k1, cudaEventDisableTiming);
+            for (int i = 0; i < 3 && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(&h->ev_k2[i], cudaEventDisableTiming);
+        }
     }
     if (e == cudaSuccess && b2r_tsdf_reset(h, 0) != B2R_OK) e = cudaErrorUnknown;
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
@@ -897,6 +920,10 @@ B2R_API int b2r_tsdf_reset(b2r_tsdf* h, cudaStream_t stream) {
     B2RDeviceGuard g(h->device);
     int nsm = 148;
     cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, h->device);
+    if (h->overlap && h->unjoined) {     // passes still running on the internal stream read what is about to be cleared
+        B2R_CUDA(cudaStreamWaitEvent(stream, h->ev_k2[(h->batches + 2) % 3], 0));
+        h->unjoined = 0;
+    }
     tsdf_clear_pool_kernel<<<nsm * 8, 256, 0, stream>>>(reinterpret_cast<float4*>(h->pool), (int64_t)h->planes * (B2R_UNIT_VOX / 4), h->counters, (int)h->cap_units);
     B2R_CHECK_LAUNCH();
     tsdf_clear_slots_kernel<<<(h->nslots + 255) / 256, 256, 0, stream>>>(h->hash.slots, h->nslots);
@@ -932,7 +959,9 @@ static void prof_end(b2r_tsdf* h, bool on, cudaStream_t stream) {
 // ------------------------------------------------------------------------------------------------
 // K2 launch: fuse the pending batch
 // ------------------------------------------------------------------------------------------------
-int b2r_tsdf_flush_pending(b2r_tsdf* h, cudaStream_t stream) {
+// Launches the pass over the pending batch.  Overlap mode: on the internal stream, after everything the caller's stream has
+// queued so far (the batch's K1 launches); the caller's stream does NOT wait for it.
+static int tsdf_launch_fuse(b2r_tsdf* h, cudaStream_t stream) {
     if (!h->pending) return B2R_OK;
     FuseParams F;
     memset(&F, 0, sizeof(F));
@@ -946,13 +975,34 @@ int b2r_tsdf_flush_pending(b2r_tsdf* h, cudaStream_t stream) {
     F.counters = h->counters; F.cap_units = (int)h->cap_units;
     for (int i = 0; i < h->pending; i++) F.fr[i] = h->frames[i];
     const int stages = h->fuse_smem / (h->planes * 256 * h->fuse_xl * 4);
-    const bool prof = prof_begin(h, 2, stream);
-    fuse_fn(h->color_type, stages, h->fuse_xl)<<<h->fuse_grid, 64 * h->fuse_xl, h->fuse_smem, stream>>>(F);
+    cudaStream_t fs = stream;
+    if (h->overlap) {
+        fs = h->fuse_stream;
+        B2R_CUDA(cudaEventRecord(h->ev_k1, stream));
+        B2R_CUDA(cudaStreamWaitEvent(fs, h->ev_k1, 0));
+    }
+    const bool prof = prof_begin(h, 2, fs);
+    fuse_fn(h->color_type, stages, h->fuse_xl)<<<h->fuse_grid, 64 * h->fuse_xl, h->fuse_smem, fs>>>(F);
     B2R_CHECK_LAUNCH();
-    prof_end(h, prof, stream);
+    prof_end(h, prof, fs);
+    if (h->overlap) {
+        B2R_CUDA(cudaEventRecord(h->ev_k2[h->batches % 3], fs));
+        h->unjoined = 1;
+    }
     h->q = (h->q + 1) % 3;
     h->pending = 0;
     h->batches++;
+    return B2R_OK;
+}
+
+// Fuses whatever is pending AND makes `stream` wait for every pass in flight: what every reader of the volume calls first.
+int b2r_tsdf_flush_pending(b2r_tsdf* h, cudaStream_t stream) {
+    int rc = tsdf_launch_fuse(h, stream);
+    if (rc != B2R_OK) return rc;
+    if (h->overlap && h->unjoined) {
+        B2R_CUDA(cudaStreamWaitEvent(stream, h->ev_k2[(h->batches + 2) % 3], 0));   // passes run in order: the last one covers all
+        h->unjoined = 0;
+    }
     return B2R_OK;
 }
 
@@ -985,9 +1035,11 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
         int rc = b2r_tsdf_flush_pending(h, stream);
         if (rc != B2R_OK) return rc;
         B2R_CUDA(cudaStreamSynchronize(stream));
-        for (int i = 0; i < B2R_MAX_BATCH; i++) { if (h->texel[i]) cudaFree(h->texel[i]); h->texel[i] = nullptr; }
+        for (int t = 0; t < 2; t++)
+            for (int i = 0; i < B2R_MAX_BATCH; i++) { if (h->texel[t][i]) cudaFree(h->texel[t][i]); h->texel[t][i] = nullptr; }
         h->texel_px = 0;
-        for (int i = 0; i < h->max_batch; i++) B2R_CUDA(cudaMalloc((void**)&h->texel[i], npx * sizeof(float2)));
+        for (int t = 0; t < (h->overlap ? 2 : 1); t++)
+            for (int i = 0; i < h->max_batch; i++) B2R_CUDA(cudaMalloc((void**)&h->texel[t][i], npx * sizeof(float2)));
         h->texel_px = npx;
     }
     const float fcx = (float)cx, fcy = (float)cy, ifx = 1.0f / (float)fx, ify = 1.0f / (float)fy;
@@ -1011,10 +1063,15 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
     int done = 0;
     while (done < nf) {
         if (h->pending == h->max_batch) {
-            int rc = b2r_tsdf_flush_pending(h, stream);
+            int rc = tsdf_launch_fuse(h, stream);        // overlap mode: the caller's stream goes on to the next batch's K1
             if (rc != B2R_OK) return rc;
         }
         const int take = (nf - done < h->max_batch - h->pending) ? nf - done : h->max_batch - h->pending;
+        const int tset = h->overlap ? (int)(h->batches & 1) : 0;
+        if (h->overlap && h->pending == 0 && h->batches >= 2) {
+            // first K1 of batch n: its texel set and its touched buffer were last used by pass n - 2
+            B2R_CUDA(cudaStreamWaitEvent(stream, h->ev_k2[(h->batches + 1) % 3], 0));
+        }
         PackParams P;
         memset(&P, 0, sizeof(P));
         P.W = W; P.H = H; P.depth_is_u16 = depth_is_u16;
@@ -1044,7 +1101,7 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
             pf.color = (h->color_type == 1) ? (color_ptrs ? color_ptrs[done + f] : color + (size_t)(done + f) * cstep) : nullptr;
             if (!pf.depth || (h->color_type == 1 && !pf.color)) { b2r_set_error("b2r_tsdf_integrate_frames: null frame pointer"); return B2R_ERR_BAD_ARG; }
             pf.gray = (h->color_type == 2) ? gray + (size_t)(done + f) * npx : nullptr;
-            pf.texel = h->texel[slot];
+            pf.texel = h->texel[tset][slot];
             for (int i = 0; i < 12; i++) pf.pose[i] = pose[i];
             pf.bit = 1u << slot;
             B2RFrame& fr = h->frames[slot];
@@ -1053,7 +1110,7 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
             fr.Es02 = fr.E[2] * vl; fr.Es12 = fr.E[6] * vl; fr.Es22 = fr.E[10] * vl;
             fr.fx = (float)fx; fr.fy = (float)fy; fr.cx = (float)cx; fr.cy = (float)cy;
             fr.safe_w = (float)W - 0.0001f; fr.safe_h = (float)H - 0.0001f;
-            fr.W = W; fr.H = H; fr.texel = h->texel[slot]; fr.mult = h->mult;
+            fr.W = W; fr.H = H; fr.texel = h->texel[tset][slot]; fr.mult = h->mult;
         }
         {
             const void* cimg = (h->color_type == 1) ? (const void*)color : (h->color_type == 2 ? (const void*)gray : nullptr);
@@ -1242,8 +1299,9 @@ B2R_API int b2r_tsdf_set_batch(b2r_tsdf* h, int max_batch, cudaStream_t stream) 
     if (rc != B2R_OK) return rc;
     if (max_batch > h->max_batch && h->texel_px) {
         B2R_CUDA(cudaStreamSynchronize(stream));
-        for (int i = h->max_batch; i < max_batch; i++)
-            if (!h->texel[i]) B2R_CUDA(cudaMalloc((void**)&h->texel[i], h->texel_px * sizeof(float2)));
+        for (int t = 0; t < (h->overlap ? 2 : 1); t++)
+            for (int i = h->max_batch; i < max_batch; i++)
+                if (!h->texel[t][i]) B2R_CUDA(cudaMalloc((void**)&h->texel[t][i], h->texel_px * sizeof(float2)));
     }
     h->max_batch = max_batch;
     return B2R_OK;

@@ -11,6 +11,7 @@ enum {
     B2R_C_TOUCHED_TOTAL = 8,  // u64 (words 8,9): cumulative (unit, frame) pairs fused
     B2R_C_LAST_TOUCHED = 10,  // units touched by the most recent fused batch
     B2R_C_WORK0 = 11,         // K2 work-item counters of the three rotating batch buffers (words 11,12,13)
+    B2R_C_TICKET = 14,        // K2: CTAs that have finished the running pass (the last one recycles the previous batch's counters)
     B2R_C_WORDS = 16
 };
 
@@ -44,7 +45,7 @@ struct b2r_tsdf {
     int pending;           // frames in it
     int max_batch;         // <= B2R_MAX_BATCH
     B2RFrame frames[B2R_MAX_BATCH];
-    float2* texel[B2R_MAX_BATCH];
+    float2* texel[2][B2R_MAX_BATCH];   // overlap mode packs batch n + 1 into the other set while batch n is being fused
     size_t texel_px;
     float* mult;             // depth-to-camera-distance multiplier image of the cached intrinsics (shared by every frame)
     size_t mult_px;
@@ -55,6 +56,13 @@ struct b2r_tsdf {
     int fuse_smem;         // dynamic shared memory of the fusion kernel
     int fuse_xl;           // x-layers per K2 work item (4 or 2)
     int fuse_ring_rounds;  // K2 passes shorter than this many items per CTA claim one item at a time
+    // Overlap mode (B2R_TSDF_OVERLAP, default on for sharded handles): the fusion passes run on an INTERNAL stream, so the K1 of
+    // batch n + 1 (caller's stream) runs beside the K2 of batch n; K1 of batch n waits for K2 of batch n - 2 (texel set and
+    // touched buffer reuse), every reader of the volume joins the internal stream first.
+    int overlap;
+    cudaStream_t fuse_stream;
+    cudaEvent_t ev_k1, ev_k2[3];   // ev_k2[n % 3]: pass n has finished
+    int unjoined;                  // a pass was launched on fuse_stream that the caller's stream has not waited for yet
     // host-input pipeline (b2r_tsdf_integrate_host)
     cudaStream_t copy_stream;
     cudaEvent_t ev_copied[B2R_HOST_RING], ev_consumed[B2R_HOST_RING];
