@@ -791,6 +791,7 @@ static void tsdf_free(b2r_tsdf* h) {
     cudaFree(h->hash.slots); cudaFree(h->unit_keys);
     cudaFree(h->pool); cudaFree(h->counters); cudaFree(h->scratch);
     for (int i = 0; i < 3; i++) cudaFree(h->touched[i]);
+    cudaFree(h->touched_sorted);
     for (int i = 0; i < B2R_MAX_BATCH; i++) { cudaFree(h->texel[0][i]); cudaFree(h->texel[1][i]); }
     if (h->fuse_stream) cudaStreamDestroy(h->fuse_stream);
     if (h->ev_k1) cudaEventDestroy(h->ev_k1);
@@ -858,6 +859,8 @@ B2R_API b2r_tsdf* b2r_tsdf_create(double voxel_length, double sdf_trunc, int col
         // work quantum of K2: 4 x-layers per item; 2 (128-thread CTAs, 8 per SM) measured equal at every world size
         h->fuse_xl = env_int("B2R_FUSE_XL", 4, 2, 4) == 2 ? 2 : 4;
         h->fuse_ring_rounds = env_int("B2R_FUSE_RING_ROUNDS", 6, 0, 1 << 20);
+        h->sort_touched = env_int("B2R_FUSE_SORT", world > 1 ? 1 : 0, 0, 1);
+        if (h->sort_touched && e == cudaSuccess) e = cudaMalloc((void**)&h->touched_sorted, (size_t)capacity_units * 4);
         h->fuse_smem = stages * h->planes * 256 * h->fuse_xl * 4;
         fuse_fn_t fn = fuse_fn(color_type, stages, h->fuse_xl);
         e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fuse_smem);
@@ -869,9 +872,11 @@ B2R_API b2r_tsdf* b2r_tsdf_create(double voxel_length, double sdf_trunc, int col
         if (per_sm < 1) per_sm = 1;
         // B2R_FUSE_CTAS_PER_SM: fewer resident fusion CTAs than fit leave registers / shared memory on every SM for what runs
         // beside the pass (the next batch's K1 on the side stream, NCCL's gather kernels); default: all that fit
-        h->overlap = env_int("B2R_TSDF_OVERLAP", world > 1 ? 1 : 0, 0, 1);
-        // overlap mode keeps one CTA slot per SM free for what runs beside a pass (K1 of the next batch, NCCL's kernels):
-        // measured + 4 % on the pass, against K1 (a fifth of a sharded rank's frame time) disappearing behind it
+        // Overlap mode is OFF by default: measured (profiles/r2_overlap_probe.json) it loses -- the pass slows by more than K1
+        // costs (K1 streams 150 MB per batch through the L2 the pass gathers its texels from: 5.1 -> 6.5 us/frame on a rank of
+        // 8, 32.4 -> 35.6 at one GPU) -- so K1 and K2 stay back to back on the caller's stream.
+        h->overlap = env_int("B2R_TSDF_OVERLAP", 0, 0, 1);
+        // overlap mode keeps one CTA slot per SM free for what runs beside a pass (K1 of the next batch)
         per_sm = env_int("B2R_FUSE_CTAS_PER_SM", h->overlap && per_sm > 1 ? per_sm - 1 : per_sm, 1, per_sm);
         h->fuse_grid = nsm * per_sm;
         if (h->overlap) {
@@ -959,6 +964,29 @@ static void prof_end(b2r_tsdf* h, bool on, cudaStream_t stream) {
 // ------------------------------------------------------------------------------------------------
 // K2 launch: fuse the pending batch
 // ------------------------------------------------------------------------------------------------
+// Short passes (a sharded rank: 2 - 3 work items per fusion CTA, each costing 1 .. 32 frames) are bounded by the CTA that
+// happens to draw the heaviest items last.  One small CTA orders the touched list by the number of frames that touch the
+// unit, heaviest first (counting sort on popc(mask)), so the counter hands out the long items first and the short ones fill
+// the gaps (longest-processing-time-first list scheduling).
+__global__ void __launch_bounds__(1024) tsdf_sort_touched_kernel(const int32_t* __restrict__ touched, int32_t* __restrict__ sorted,
+                                                                 const B2RSlot* __restrict__ slots, const int32_t* __restrict__ counters, int q, int cap) {
+    __shared__ int hist[33], cursor[33];
+    const int T = min(counters[B2R_C_TOUCHED0 + q], cap);
+    if (threadIdx.x < 33) hist[threadIdx.x] = 0;
+    __syncthreads();
+    for (int t = threadIdx.x; t < T; t += blockDim.x) atomicAdd(&hist[32 - __popc(slots[touched[t]].mask[q])], 1);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int acc = 0;
+        for (int b = 0; b < 33; b++) { cursor[b] = acc; acc += hist[b]; }
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < T; t += blockDim.x) {
+        const int sl = touched[t];
+        sorted[atomicAdd(&cursor[32 - __popc(slots[sl].mask[q])], 1)] = sl;
+    }
+}
+
 // Launches the pass over the pending batch.  Overlap mode: on the internal stream, after everything the caller's stream has
 // queued so far (the batch's K1 launches); the caller's stream does NOT wait for it.
 static int tsdf_launch_fuse(b2r_tsdf* h, cudaStream_t stream) {
@@ -980,6 +1008,12 @@ static int tsdf_launch_fuse(b2r_tsdf* h, cudaStream_t stream) {
         fs = h->fuse_stream;
         B2R_CUDA(cudaEventRecord(h->ev_k1, stream));
         B2R_CUDA(cudaStreamWaitEvent(fs, h->ev_k1, 0));
+    }
+    if (h->sort_touched && h->pending > 1) {
+        tsdf_sort_touched_kernel<<<1, 1024, 0, fs>>>(h->touched[h->q], h->touched_sorted, h->hash.slots, h->counters, h->q, (int)h->cap_units);
+        B2R_CHECK_LAUNCH();
+        F.touched = h->touched_sorted;     // the same set, heaviest units first; the mask clearing of the pass after next uses either
+        F.reverse = 0;
     }
     const bool prof = prof_begin(h, 2, fs);
     fuse_fn(h->color_type, stages, h->fuse_xl)<<<h->fuse_grid, 64 * h->fuse_xl, h->fuse_smem, fs>>>(F);

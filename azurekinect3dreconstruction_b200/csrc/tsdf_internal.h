@@ -39,6 +39,8 @@ struct b2r_tsdf {
     int32_t* unit_keys;    // cap_units * 3
     float* pool;           // cap_units * planes * 4096 : planes = tsdf, weight[, r, g, b]
     int32_t* touched[3];   // cap_units each: hash slots touched by the batch using that buffer
+    int32_t* touched_sorted;   // short passes: the pending batch's list ordered heaviest unit first (sort_touched)
+    int sort_touched;
     int32_t* counters;     // B2R_C_WORDS
     // pending batch: frames packed + allocated (K1 done) but not yet fused (K2 runs at flush)
     int q;                 // rotating buffer index of the pending batch
