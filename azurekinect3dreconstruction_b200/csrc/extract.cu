@@ -370,7 +370,7 @@ __global__ void scatter_bases_kernel(const int32_t* order, const int32_t* scan, 
 __global__ void __launch_bounds__(256) mesh_fill_kernel(const VolView V, const int32_t* order, const uint32_t* vinfo,
                                                         const int32_t* vbase_by_unit, const int32_t* tbase,
                                                         double* vtx, double* vcol, int32_t* tri, int32_t* ids,
-                                                        int64_t capV, int64_t capF, int pos0, int64_t v0, int64_t t0) {
+                                                        int64_t capV, int64_t capF, int pos0, int64_t v0, int64_t t0, int vshift) {
     __shared__ float A[MD * MD * MD];
     __shared__ uint32_t NEG[MCOLS], VAL[MCOLS], CC[CCOLS];
     __shared__ uint16_t vlist[FILL_CAP];       // x << 10 | y << 6 | z << 2 | axis
@@ -480,7 +480,7 @@ __global__ void __launch_bounds__(256) mesh_fill_kernel(const VolView V, const i
                 if (oz >= 16) { oz -= 16; uz = 2; }
                 const int u = nb[(ux * 3 + uy) * 3 + uz];
                 const uint32_t info = vinfo[(int64_t)u * B2R_UNIT_VOX + (ox * 256 + oy * 16 + oz)];
-                vid[i] = vbase_by_unit[u] + (int)(info >> 3) + __popc(info & ((1u << axis) - 1u));
+                vid[i] = vbase_by_unit[u] + vshift + (int)(info >> 3) + __popc(info & ((1u << axis) - 1u));
             }
             int64_t to2 = tb + ctoff[t];
             for (int k = 0; k < nt; k++, to2++) {
@@ -549,51 +549,45 @@ VolView make_view(const b2r_tsdf* h) {
     return V;
 }
 
-__global__ void owner_of_sorted_kernel(const int32_t* order, const int32_t* unit_keys, int n, int world, uint32_t* owner, int32_t* id_out, int32_t* hist) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const int u = order[i];
-    const int o = b2r_owner(b2r_pack_key(unit_keys[3 * u], unit_keys[3 * u + 1], unit_keys[3 * u + 2]), world);
-    owner[i] = (uint32_t)o; id_out[i] = u;
-    atomicAdd(&hist[o], 1);
+// A slab handle (multi-GPU extraction, pipelines/sharded.py) holds the units with kx in [kx_lo, kx_hi] plus ghost layers
+// kx_lo - 1, kx_hi + 1, kx_hi + 2.  Packed keys sort kx-major, so in the sorted order the slab is [i0, i1) and the first
+// ghost layer above it [i1, i2).  out7 = {i0, i1, i2, vscan[i0], vscan[i1], tscan[i0], tscan[i1]} (scans may be null).
+__global__ void slab_bounds_kernel(const uint64_t* sorted_keys, int n, uint64_t k_lo, uint64_t k_hi1, uint64_t k_hi2,
+                                   const int32_t* vscan, const int32_t* tscan, int32_t* out7) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    auto lower = [&](uint64_t key) { int lo = 0, hi = n; while (lo < hi) { const int mid = (lo + hi) >> 1; if (sorted_keys[mid] < key) lo = mid + 1; else hi = mid; } return lo; };
+    const int i0 = lower(k_lo), i1 = lower(k_hi1), i2 = lower(k_hi2);
+    out7[0] = i0; out7[1] = i1; out7[2] = i2;
+    out7[3] = vscan ? vscan[i0] : 0; out7[4] = vscan ? vscan[i1] : 0;
+    out7[5] = tscan ? tscan[i0] : 0; out7[6] = tscan ? tscan[i1] : 0;
 }
 
-// Canonical unit order: by packed key; for a sharded handle (world > 1) by (owner rank, packed key), so that
-// the units -- and therefore the vertices -- of one rank are a contiguous range of the global numbering.
-// own[0], own[1]: the range of positions owned by h->rank (the whole range when world == 1).
-int sorted_order(b2r_tsdf* h, int n, Scratch& S, int* own, cudaStream_t stream) {
+struct Slab { int use, kx_lo, kx_hi; };
+
+// Canonical unit order: by packed key (kx-major).
+int sorted_order(b2r_tsdf* h, int n, Scratch& S, cudaStream_t stream) {
     pack_keys_kernel<<<(n + 255) / 256, 256, 0, stream>>>(h->unit_keys, n, S.k_in, S.id_in);
     B2R_CHECK_LAUNCH();
     size_t tmp = S.cub_bytes;
     B2R_CUDA(cub::DeviceRadixSort::SortPairs(S.cub_tmp, tmp, S.k_in, S.k_out, S.id_in, S.order, n, 0, 63, stream));
-    own[0] = 0; own[1] = n;
-    if (h->world <= 1) return B2R_OK;
-    // second, stable pass by owner (keys reuse the k_in buffer as uint32, values go order -> id_in -> order)
-    uint32_t* ow_in = reinterpret_cast<uint32_t*>(S.k_in);
-    uint32_t* ow_out = ow_in + n;
-    int32_t* hist = S.cnt_a;   // free until the count pass
-    B2R_CUDA(cudaMemsetAsync(hist, 0, 64 * 4, stream));
-    owner_of_sorted_kernel<<<(n + 255) / 256, 256, 0, stream>>>(S.order, h->unit_keys, n, h->world, ow_in, S.id_in, hist);
-    B2R_CHECK_LAUNCH();
-    tmp = S.cub_bytes;
-    B2R_CUDA(cub::DeviceRadixSort::SortPairs(S.cub_tmp, tmp, ow_in, ow_out, S.id_in, S.order, n, 0, 8, stream));
-    int32_t hh[64];
-    B2R_CUDA(cudaMemcpyAsync(hh, hist, 64 * 4, cudaMemcpyDeviceToHost, stream));
-    B2R_CUDA(cudaStreamSynchronize(stream));
-    int a = 0;
-    for (int r = 0; r < h->rank; r++) a += hh[r];
-    own[0] = a; own[1] = a + hh[h->rank];
     return B2R_OK;
 }
 
-}  // namespace
+int slab_bounds(int n, const Scratch& S, const Slab& sl, const int32_t* vscan, const int32_t* tscan, int32_t* host7, cudaStream_t stream) {
+    if (!sl.use) { host7[0] = 0; host7[1] = n; host7[2] = n; return 1; }   // 1: nothing was queued, the caller fills the scan values itself
+    auto clampk = [](long long k) { return (int)(k < -(long long)B2R_KEY_BIAS ? -(long long)B2R_KEY_BIAS : (k > (long long)B2R_KEY_BIAS - 1 ? (long long)B2R_KEY_BIAS - 1 : k)); };
+    const bool top = (long long)sl.kx_hi + 1 > (long long)B2R_KEY_BIAS - 1;
+    const uint64_t k_lo = b2r_pack_key(clampk(sl.kx_lo), -B2R_KEY_BIAS, -B2R_KEY_BIAS);
+    const uint64_t k_hi1 = top ? B2R_KEY_EMPTY : b2r_pack_key(clampk((long long)sl.kx_hi + 1), -B2R_KEY_BIAS, -B2R_KEY_BIAS);
+    const uint64_t k_hi2 = ((long long)sl.kx_hi + 2 > (long long)B2R_KEY_BIAS - 1) ? B2R_KEY_EMPTY : b2r_pack_key(clampk((long long)sl.kx_hi + 2), -B2R_KEY_BIAS, -B2R_KEY_BIAS);
+    int32_t* d7 = S.cnt_a + (size_t)n + 8;     // 64 spare words follow the counts
+    slab_bounds_kernel<<<1, 32, 0, stream>>>(S.k_out, n, k_lo, k_hi1, k_hi2, vscan, tscan, d7);
+    B2R_CHECK_LAUNCH();
+    B2R_CUDA(cudaMemcpyAsync(host7, d7, 7 * 4, cudaMemcpyDeviceToHost, stream));
+    return B2R_OK;
+}
 
-// volume.extract_point_cloud().  Outputs (DEVICE, f64): xyz/rgb/nrm [capacity*3]; ids (optional int32
-// [capacity*4]) = global voxel coordinate of the edge's lower end + axis (the canonical sort key).
-// Call with xyz == NULL (or too small a capacity) to get the required count in *count and
-// B2R_ERR_CAPACITY; a second call with enough room fills.  Synchronises `stream` to read counts.
-B2R_API int b2r_tsdf_extract_points(b2r_tsdf* h, double* xyz, double* rgb, double* nrm, int32_t* ids, int64_t capacity,
-                                    int64_t* count, cudaStream_t stream) {
+int extract_points_impl(b2r_tsdf* h, const Slab& sl, double* xyz, double* rgb, double* nrm, int32_t* ids, int64_t capacity, int64_t* count, cudaStream_t stream) {
     if (!h || !count) return B2R_ERR_BAD_ARG;
     B2RDeviceGuard g(h->device);
     int64_t st[5];
@@ -605,12 +599,15 @@ B2R_API int b2r_tsdf_extract_points(b2r_tsdf* h, double* xyz, double* rgb, doubl
     Scratch S;
     rc = carve(h, n, false, &S);
     if (rc != B2R_OK) return rc;
-    int own[2];
-    rc = sorted_order(h, n, S, own, stream);
+    rc = sorted_order(h, n, S, stream);
     if (rc != B2R_OK) return rc;
-    const int n_own = own[1] - own[0];
-    if (n_own == 0) return B2R_OK;
-    const int32_t* order = S.order + own[0];   // a sharded handle emits the points of its own units only
+    int32_t b7[7];
+    rc = slab_bounds(n, S, sl, nullptr, nullptr, b7, stream);
+    if (rc < 0) return rc;
+    if (rc == B2R_OK) B2R_CUDA(cudaStreamSynchronize(stream));
+    const int n_own = b7[1] - b7[0];
+    if (n_own <= 0) return B2R_OK;
+    const int32_t* order = S.order + b7[0];     // a slab handle emits the points of its own units only
     const VolView V = make_view(h);
     extract_points_kernel<false><<<n_own, 256, 0, stream>>>(V, order, S.cnt_a, nullptr, nullptr, nullptr, nullptr, nullptr, 0);
     B2R_CHECK_LAUNCH();
@@ -628,15 +625,8 @@ B2R_API int b2r_tsdf_extract_points(b2r_tsdf* h, double* xyz, double* rgb, doubl
     return B2R_OK;
 }
 
-// volume.extract_triangle_mesh().  Outputs (DEVICE): vtx/vcol f64 [capV*3], tri int32 [capF*3],
-// ids optional int32 [capV*4] = global integer edge id (X,Y,Z,axis) of each vertex.
-// Same two-call capacity protocol as extract_points (nV/nF always written).
-// Sharded form (handle created with world > 1 and holding the FULL volume: its own units plus the other ranks'
-// units imported as ghosts): emits the vertices owned by this rank's units and the triangles of their cubes.
-// Triangle vertex ids are GLOBAL in the (owner rank, unit key, voxel, axis) order, so the rank-order
-// concatenation of all ranks' outputs is the complete welded mesh; *vertex_base = this rank's first global id.
-B2R_API int b2r_tsdf_extract_mesh_sharded(b2r_tsdf* h, double* vtx, double* vcol, int32_t* tri, int32_t* ids, int64_t capV,
-                                          int64_t capF, int64_t* nV, int64_t* nF, int64_t* vertex_base, cudaStream_t stream) {
+int extract_mesh_impl(b2r_tsdf* h, const Slab& sl, int64_t vertex_base, double* vtx, double* vcol, int32_t* tri, int32_t* ids, int64_t capV,
+                      int64_t capF, int64_t* nV, int64_t* nF, cudaStream_t stream) {
     if (!h || !nV || !nF) return B2R_ERR_BAD_ARG;
     B2RDeviceGuard g(h->device);
     int64_t st[5];
@@ -651,15 +641,17 @@ B2R_API int b2r_tsdf_extract_mesh_sharded(b2r_tsdf* h, double* vtx, double* vcol
     int own[2];
     int32_t v01[2] = {0, 0}, t01[2] = {0, 0};
     const VolView V = make_view(h);
-    if (h->mesh_gen == h->generation && h->mesh_n == n) {
+    const uint64_t slab_tag = sl.use ? (((uint64_t)(uint32_t)sl.kx_lo << 32) | (uint32_t)sl.kx_hi) + 1 : 0;
+    if (h->mesh_gen == h->generation && h->mesh_n == n && h->mesh_slab == slab_tag) {
         // second call of the two-call protocol on an unchanged volume: order, vertex slots and scans are still in scratch
         own[0] = h->mesh_own[0]; own[1] = h->mesh_own[1];
         v01[0] = h->mesh_v01[0]; v01[1] = h->mesh_v01[1]; t01[0] = h->mesh_t01[0]; t01[1] = h->mesh_t01[1];
     } else {
-        rc = sorted_order(h, n, S, own, stream);
+        rc = sorted_order(h, n, S, stream);
         if (rc != B2R_OK) return rc;
-        // the count pass covers EVERY unit the handle holds (own + imported ghosts): it fixes the global vertex
-        // numbering, which a cube needs for edges owned by a neighbouring unit of another rank
+        // the count pass covers EVERY unit the handle holds: it fixes the vertex numbering (key order), which a cube needs for
+        // edges owned by the neighbouring units above it -- for a slab handle those are the first ghost layer, whose own
+        // neighbourhood is complete thanks to the second one (the counts of the outermost ghost layers are never used)
         mesh_count_kernel<<<n, 256, 0, stream>>>(V, S.order, S.vinfo, S.cnt_a, S.cnt_b);
         B2R_CHECK_LAUNCH();
         B2R_CUDA(cudaMemsetAsync(S.cnt_a + n, 0, 4, stream));
@@ -670,29 +662,72 @@ B2R_API int b2r_tsdf_extract_mesh_sharded(b2r_tsdf* h, double* vtx, double* vcol
         B2R_CUDA(cub::DeviceScan::ExclusiveSum(S.cub_tmp, tmp, S.cnt_b, S.scan_b, n + 1, stream));
         scatter_bases_kernel<<<(n + 255) / 256, 256, 0, stream>>>(S.order, S.scan_a, S.vbase_by_unit, n);
         B2R_CHECK_LAUNCH();
-        B2R_CUDA(cudaMemcpyAsync(&v01[0], S.scan_a + own[0], 4, cudaMemcpyDeviceToHost, stream));
-        B2R_CUDA(cudaMemcpyAsync(&v01[1], S.scan_a + own[1], 4, cudaMemcpyDeviceToHost, stream));
-        B2R_CUDA(cudaMemcpyAsync(&t01[0], S.scan_b + own[0], 4, cudaMemcpyDeviceToHost, stream));
-        B2R_CUDA(cudaMemcpyAsync(&t01[1], S.scan_b + own[1], 4, cudaMemcpyDeviceToHost, stream));
+        int32_t b7[7];
+        rc = slab_bounds(n, S, sl, S.scan_a, S.scan_b, b7, stream);
+        if (rc < 0) return rc;
+        if (rc == 1) {
+            B2R_CUDA(cudaMemcpyAsync(&b7[4], S.scan_a + n, 4, cudaMemcpyDeviceToHost, stream));
+            B2R_CUDA(cudaMemcpyAsync(&b7[6], S.scan_b + n, 4, cudaMemcpyDeviceToHost, stream));
+            b7[3] = 0; b7[5] = 0;
+        }
         B2R_CUDA(cudaStreamSynchronize(stream));
-        h->mesh_gen = h->generation; h->mesh_n = n;
+        own[0] = b7[0]; own[1] = b7[1];
+        v01[0] = b7[3]; v01[1] = b7[4]; t01[0] = b7[5]; t01[1] = b7[6];
+        h->mesh_gen = h->generation; h->mesh_n = n; h->mesh_slab = slab_tag;
         h->mesh_own[0] = own[0]; h->mesh_own[1] = own[1];
         h->mesh_v01[0] = v01[0]; h->mesh_v01[1] = v01[1]; h->mesh_t01[0] = t01[0]; h->mesh_t01[1] = t01[1];
     }
     const int32_t tv = v01[1] - v01[0], tf = t01[1] - t01[0];
     *nV = tv; *nF = tf;
-    if (vertex_base) *vertex_base = v01[0];
     if (!vtx || !tri || capV < tv || capF < tf) { b2r_set_error("extract_mesh: need capacity V=%d F=%d", tv, tf); return B2R_ERR_CAPACITY; }
     if (tv == 0 || own[1] == own[0]) return B2R_OK;
+    // triangle vertex ids: local key-order id - (ids before this slab) + the slab's global base
+    const long long vshift = vertex_base - (long long)v01[0];
+    if (vertex_base < 0 || vertex_base + (long long)tv > (long long)0x7fffffff) { b2r_set_error("extract_mesh: vertex ids exceed int32"); return B2R_ERR_RANGE; }
     mesh_fill_kernel<<<own[1] - own[0], 256, 0, stream>>>(V, S.order, S.vinfo, S.vbase_by_unit, S.scan_b, vtx, h->planes == 5 ? vcol : nullptr, tri, ids,
-                                                        capV, capF, own[0], (int64_t)v01[0], (int64_t)t01[0]);
+                                                        capV, capF, own[0], (int64_t)v01[0], (int64_t)t01[0], (int)vshift);
     B2R_CHECK_LAUNCH();
     return B2R_OK;
 }
 
+}  // namespace
+
+// volume.extract_point_cloud().  Outputs (DEVICE, f64): xyz/rgb/nrm [capacity*3]; ids (optional int32
+// [capacity*4]) = global voxel coordinate of the edge's lower end + axis (the canonical sort key).
+// Call with xyz == NULL (or too small a capacity) to get the required count in *count and
+// B2R_ERR_CAPACITY; a second call with enough room fills.  Synchronises `stream` to read counts.
+B2R_API int b2r_tsdf_extract_points(b2r_tsdf* h, double* xyz, double* rgb, double* nrm, int32_t* ids, int64_t capacity,
+                                    int64_t* count, cudaStream_t stream) {
+    const Slab sl = {0, 0, 0};
+    return extract_points_impl(h, sl, xyz, rgb, nrm, ids, capacity, count, stream);
+}
+
+// volume.extract_triangle_mesh().  Outputs (DEVICE): vtx/vcol f64 [capV*3], tri int32 [capF*3],
+// ids optional int32 [capV*4] = global integer edge id (X,Y,Z,axis) of each vertex.
+// Same two-call capacity protocol as extract_points (nV/nF always written).  Vertices come out in unit-key order
+// (kx-major), then voxel, then axis.
 B2R_API int b2r_tsdf_extract_mesh(b2r_tsdf* h, double* vtx, double* vcol, int32_t* tri, int32_t* ids, int64_t capV,
                                   int64_t capF, int64_t* nV, int64_t* nF, cudaStream_t stream) {
-    return b2r_tsdf_extract_mesh_sharded(h, vtx, vcol, tri, ids, capV, capF, nV, nF, nullptr, stream);
+    const Slab sl = {0, 0, 0};
+    return extract_mesh_impl(h, sl, 0, vtx, vcol, tri, ids, capV, capF, nV, nF, stream);
+}
+
+// Multi-GPU extraction: the handle holds ONE SLAB of the volume -- every unit with kx in [kx_lo, kx_hi] -- plus the
+// ghost layers kx_lo - 1, kx_hi + 1 and kx_hi + 2 (whatever of them exists).  Emitted: the vertices owned by the slab's units and
+// the triangles of their cubes.  Triangle vertex ids are GLOBAL: vertex_base (= the vertex count of all slabs below this one,
+// known after every rank's first call) + the slab's key-order numbering -- which continues seamlessly into the ghost layer
+// above, so the slab-order concatenation of all ranks' outputs is the single-GPU mesh, vertex for vertex.
+B2R_API int b2r_tsdf_extract_mesh_slab(b2r_tsdf* h, int kx_lo, int kx_hi, int64_t vertex_base, double* vtx, double* vcol, int32_t* tri,
+                                       int32_t* ids, int64_t capV, int64_t capF, int64_t* nV, int64_t* nF, cudaStream_t stream) {
+    if (kx_lo > kx_hi) { if (nV) *nV = 0; if (nF) *nF = 0; return B2R_OK; }
+    const Slab sl = {1, kx_lo, kx_hi};
+    return extract_mesh_impl(h, sl, vertex_base, vtx, vcol, tri, ids, capV, capF, nV, nF, stream);
+}
+B2R_API int b2r_tsdf_extract_points_slab(b2r_tsdf* h, int kx_lo, int kx_hi, double* xyz, double* rgb, double* nrm, int32_t* ids,
+                                         int64_t capacity, int64_t* count, cudaStream_t stream) {
+    if (kx_lo > kx_hi) { if (count) *count = 0; return B2R_OK; }
+    const Slab sl = {1, kx_lo, kx_hi};
+    return extract_points_impl(h, sl, xyz, rgb, nrm, ids, capacity, count, stream);
 }
 
 // ---- TriangleMesh.compute_vertex_normals() (GoodColorReconstruction.py:286) --------

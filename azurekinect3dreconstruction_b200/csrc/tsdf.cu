@@ -1366,6 +1366,34 @@ B2R_API int b2r_tsdf_export_units(b2r_tsdf* h, int64_t first, int64_t count, flo
     return B2R_OK;
 }
 
+// one CTA per (selected unit, plane): a unit's planes are gathered out of the pool into export layout
+__global__ void tsdf_export_selected_kernel(const float* __restrict__ pool, int64_t unit_stride, int planes, const int32_t* __restrict__ unit_keys,
+                                            const int32_t* __restrict__ ids, int32_t* keys3, float* tsdf, float* weight, float* rgb) {
+    const int u = blockIdx.x / planes, pl = blockIdx.x - u * planes;
+    const int id = ids[u];
+    if (pl == 0 && threadIdx.x < 3 && keys3) keys3[3 * u + threadIdx.x] = unit_keys[3 * id + threadIdx.x];
+    float* dst = pl == 0 ? tsdf + (int64_t)u * B2R_UNIT_VOX : (pl == 1 ? weight + (int64_t)u * B2R_UNIT_VOX : (rgb ? rgb + ((int64_t)u * 3 + (pl - 2)) * B2R_UNIT_VOX : nullptr));
+    if (!dst) return;
+    const float4* src = reinterpret_cast<const float4*>(pool + (int64_t)id * unit_stride + (int64_t)pl * B2R_UNIT_VOX);
+    float4* d4 = reinterpret_cast<float4*>(dst);
+    for (int v = threadIdx.x; v < B2R_UNIT_VOX / 4; v += blockDim.x) d4[v] = __ldg(src + v);
+}
+
+// Copies the units ids[0..n) (DEVICE int32 pool indices) out in export layout: keys3 [n][3], tsdf / weight [n][4096],
+// rgb [n][3][4096] (rgb may be null).  The multi-GPU extraction routes units to slab owners with it.
+B2R_API int b2r_tsdf_export_selected(b2r_tsdf* h, const int32_t* ids, int64_t n, int32_t* keys3, float* tsdf, float* weight, float* rgb,
+                                     cudaStream_t stream) {
+    if (!h || !ids || !tsdf || !weight || n < 0 || n > (1 << 26)) return B2R_ERR_BAD_ARG;
+    B2RDeviceGuard g(h->device);
+    int rc = b2r_tsdf_flush_pending(h, stream);
+    if (rc != B2R_OK) return rc;
+    if (n == 0) return B2R_OK;
+    tsdf_export_selected_kernel<<<(unsigned)(n * h->planes), 256, 0, stream>>>(h->pool, (int64_t)h->planes * B2R_UNIT_VOX, h->planes, h->unit_keys, ids,
+                                                                             keys3, tsdf, weight, h->planes == 5 ? rgb : nullptr);
+    B2R_CHECK_LAUNCH();
+    return B2R_OK;
+}
+
 __global__ void tsdf_import_keys_kernel(B2RHash hash, int32_t* unit_keys, int32_t* counters, const int32_t* keys3,
                                         int n, int cap, int32_t* out_ids) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;

@@ -78,7 +78,7 @@ struct b2r_tsdf {
     // The Open3D-shaped callers extract with a two-call protocol (sizes first, then the arrays).  generation counts
     // every change of the volume (integrate / reset / import); mesh_gen remembers for which generation the sorted
     // order, per-voxel vertex slots and scans in `scratch` are valid, so the second call only runs the fill pass.
-    uint64_t generation, mesh_gen;
+    uint64_t generation, mesh_gen, mesh_slab;
     int mesh_n, mesh_own[2];
     int32_t mesh_v01[2], mesh_t01[2];
     // optional per-kernel timing (b2r_tsdf_profile): event pairs around every K1 / K2 launch

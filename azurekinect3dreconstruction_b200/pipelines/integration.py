@@ -176,7 +176,24 @@ class ScalableTSDFVolume:
             _lib.check(self._lib.b2r_tsdf_export_units(self._h, first, count, _lib.ptr(tsdf), _lib.ptr(wgt), _lib.ptr(rgb), _lib.stream_ptr()))
         return self.unit_keys()[first:first + count], tsdf, wgt, rgb
 
-    def import_units(self, keys, tsdf, weight, rgb=None) -> None:
+    def capacity(self) -> int:
+        return int(self._lib.b2r_tsdf_capacity(self._h))
+
+    def export_selected(self, ids: torch.Tensor):
+        """Units by pool index (device int32 tensor) in export layout: (keys (n,3), tsdf (n,4096), weight (n,4096), rgb (n,3,4096) | None)."""
+        dev = _lib.require_cuda()
+        ids = ids.to(dev, dtype=torch.int32).contiguous()
+        n = int(ids.shape[0])
+        keys = torch.empty((n, 3), dtype=torch.int32, device=dev)
+        tsdf = torch.empty((n, 4096), dtype=torch.float32, device=dev)
+        wgt = torch.empty((n, 4096), dtype=torch.float32, device=dev)
+        rgb = torch.empty((n, 3, 4096), dtype=torch.float32, device=dev) if self.color_type != TSDFVolumeColorType.NoColor else None
+        if n:
+            _lib.check(self._lib.b2r_tsdf_export_selected(self._h, _lib.ptr(ids), n, _lib.ptr(keys), _lib.ptr(tsdf), _lib.ptr(wgt), _lib.ptr(rgb),
+                                                          _lib.stream_ptr()), "export_selected")
+        return keys, tsdf, wgt, rgb
+
+    def import_units(self, keys, tsdf, weight, rgb=None, sync: bool = True) -> None:
         dev = _lib.require_cuda()
         keys = (keys if torch.is_tensor(keys) else torch.as_tensor(np.asarray(keys))).to(dev, dtype=torch.int32).contiguous()
         tsdf = torch.as_tensor(tsdf, dtype=torch.float32).to(dev).contiguous()
@@ -185,7 +202,8 @@ class ScalableTSDFVolume:
             rgb = torch.as_tensor(rgb, dtype=torch.float32).to(dev).contiguous()
         _lib.check(self._lib.b2r_tsdf_import_units(self._h, _lib.ptr(keys), keys.shape[0], _lib.ptr(tsdf), _lib.ptr(weight),
                                                     _lib.ptr(rgb), _lib.stream_ptr()), "import_units")
-        torch.cuda.current_stream().synchronize()
+        if sync:
+            torch.cuda.current_stream().synchronize()
 
     # ---- extraction ---------------------------------------------------------------------------------
     def extract_point_cloud(self, with_ids: bool = False) -> PointCloud:

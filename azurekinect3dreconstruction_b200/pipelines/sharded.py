@@ -4,14 +4,15 @@ The reference is single-process (its only "many streams, one volume" precedent i
 CodeThatKindaWorks/BetterVisualizerD2camerasWORKSkinda.py:533-570).  Here the volume is sharded by unit key:
 ``owner(key) = mix64(key) >> 33 mod world`` (csrc/common.cuh b2r_owner).  Every rank sees every frame and
 allocates / fuses only the units it owns -- integration needs NO collective.  Extraction needs one exchange,
-because marching-cubes cubes and surface-point normals straddle unit borders:
+because marching-cubes cubes and surface-point normals straddle unit borders, and a hash shard's neighbours are
+almost all remote:
 
-  1. all-gather-v of the ranks' units (keys + voxel planes) over NCCL/NVLink -> every rank holds the full volume
-     in a scratch handle (own units + ghosts);
-  2. every rank extracts what ITS units own (b2r_tsdf_extract_mesh_sharded: vertices of its units' edges,
-     triangles of its units' cubes; vertex ids are global in (owner rank, key, voxel, axis) order, so no
-     cross-rank welding is needed);
-  3. all-gather-v of the parts; the rank-order concatenation is the complete mesh / cloud.
+  1. all-gather of the units' kx (4 bytes per unit) -> every rank derives the same balanced kx SLABS;
+  2. all-to-all-v: every unit goes to the rank whose slab holds it and, as a ghost, to the slabs one layer below /
+     two layers above -> a rank holds O(own slab + ghost layers), never the whole volume;
+  3. every rank extracts what its slab owns with the single-GPU kernels (b2r_tsdf_extract_mesh_slab: vertex ids are
+     global -- the key-order numbering continues across slab borders -- so no cross-rank welding is needed);
+  4. gather-v of the parts to rank 0 (all-gather on request); the slab-order concatenation is the single-GPU mesh.
 
 Odometry and ICP pairs are independent: one pair per GPU ("replicas only"), no collective.
 """
@@ -50,18 +51,23 @@ def unit_owner(key, world: int) -> int:
 
 
 class Comm:
-    """Variable-length all-gather over a torch.distributed group (NCCL on GPUs, gloo on CPU tensors)."""
+    """The collectives the multi-GPU path needs, over a torch.distributed group (NCCL on GPUs, gloo on CPU tensors)."""
 
     def __init__(self, group=None):
         import torch.distributed as dist
         self.dist, self.group = dist, group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.nccl = dist.get_backend(group) == "nccl"
 
     def all_gather_v(self, t: torch.Tensor) -> List[torch.Tensor]:
         n = torch.tensor([t.shape[0]], dtype=torch.int64, device=t.device)
         counts = [torch.zeros_like(n) for _ in range(self.world)]
         self.dist.all_gather(counts, n, group=self.group)
         counts = [int(c.item()) for c in counts]
+        if self.nccl:
+            out = [torch.empty((c,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device) for c in counts]
+            self.dist.all_gather(out, t.contiguous(), group=self.group)      # uneven sizes: grouped broadcasts, no padding
+            return out
         m = max(counts + [1])
         pad = torch.zeros((m,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
         pad[:t.shape[0]] = t
@@ -69,60 +75,185 @@ class Comm:
         self.dist.all_gather(out, pad, group=self.group)
         return [o[:c] for o, c in zip(out, counts)]
 
+    def all_to_all_v(self, parts: List[torch.Tensor]) -> List[torch.Tensor]:
+        """parts[d] goes to rank d (rows may differ per destination); returns what every rank sent here, by source rank."""
+        dev, tail, dt = parts[0].device, tuple(parts[0].shape[1:]), parts[0].dtype
+        mine = torch.tensor([int(p.shape[0]) for p in parts], dtype=torch.int64, device=dev)
+        rows = [torch.zeros_like(mine) for _ in range(self.world)]
+        self.dist.all_gather(rows, mine, group=self.group)
+        recv = [int(rows[src][self.rank].item()) for src in range(self.world)]
+        out = [torch.empty((c,) + tail, dtype=dt, device=dev) for c in recv]
+        if self.nccl:
+            self.dist.all_to_all(out, [p.contiguous() for p in parts], group=self.group)
+            return out
+        for d in range(self.world):            # gloo has no all-to-all: one ragged gather per destination (CPU tests only)
+            got = self.all_gather_v(parts[d])
+            if d == self.rank:
+                out = got
+        return out
+
+    def gather_v(self, t: torch.Tensor, dst: int = 0) -> Optional[List[torch.Tensor]]:
+        """Ragged gather to one rank (grouped send / recv on NCCL); None on the other ranks."""
+        n = torch.tensor([t.shape[0]], dtype=torch.int64, device=t.device)
+        counts = [torch.zeros_like(n) for _ in range(self.world)]
+        self.dist.all_gather(counts, n, group=self.group)
+        counts = [int(c.item()) for c in counts]
+        if not self.nccl:
+            got = self.all_gather_v(t)
+            return got if self.rank == dst else None
+        if self.rank == dst:
+            out = [torch.empty((c,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device) for c in counts]
+            out[dst] = t
+            ops = [self.dist.P2POp(self.dist.irecv, out[r], r, self.group) for r in range(self.world) if r != dst and counts[r] > 0]
+        else:
+            out = None
+            ops = [self.dist.P2POp(self.dist.isend, t.contiguous(), dst, self.group)] if counts[self.rank] > 0 else []
+        if ops:
+            for w in self.dist.batch_isend_irecv(ops):
+                w.wait()
+        return out
+
 
 class LocalComm:
     """In-process stand-in used to emulate `world` ranks on one GPU (tests): the caller runs a phase for every
-    rank, then hands the per-rank tensors to `exchange`, which returns what all_gather_v would."""
+    rank, then hands the per-rank results to the matching static exchange, which returns what the collective would."""
 
     def __init__(self, rank: int, world: int):
         self.rank, self.world = rank, world
 
+    @staticmethod
+    def all_gather_v(per_rank):                       # per_rank[r] = rank r's tensor -> what every rank receives
+        return list(per_rank)
 
-# ---- the three phases (local -> collective -> local -> collective -> local) ------------------------------
-def phase_export(vol: ScalableTSDFVolume):
-    keys, tsdf, wgt, rgb = vol.export_units()
-    return [keys.contiguous(), tsdf, wgt] + ([rgb] if rgb is not None else [])
+    @staticmethod
+    def all_to_all_v(per_rank_parts):                 # per_rank_parts[src][dst] -> result[dst][src]
+        world = len(per_rank_parts)
+        return [[per_rank_parts[src][dst] for src in range(world)] for dst in range(world)]
 
 
-def phase_extract(vol: ScalableTSDFVolume, gathered: List[List[torch.Tensor]], what: str = "mesh"):
-    """gathered[i] = list over ranks of tensor i of phase_export.  Returns this rank's part."""
-    cat = [torch.cat(g) for g in gathered]
-    total = int(cat[0].shape[0])
-    tmp = ScalableTSDFVolume(vol.voxel_length, vol.sdf_trunc, vol.color_type, capacity_units=max(total, 1) + 16,
-                             rank=vol.rank, world=vol.world)
-    if total:
-        tmp.import_units(cat[0], cat[1], cat[2], cat[3] if len(cat) > 3 else None)
-    if what == "points":
-        pc = tmp.extract_point_cloud()
+# ---- multi-GPU extraction: re-partition into kx slabs, extract locally, gather -------------------------------------------
+def slab_cuts(all_kx: np.ndarray, world: int):
+    """Balanced kx slabs from the kx of EVERY unit of the volume: [(lo, hi)] per rank, inclusive; (1, 0) = empty slab.
+    Cuts fall between distinct kx values (a slab is a set of whole unit layers), as close to equal unit counts as that allows."""
+    if all_kx.size == 0:
+        return [(1, 0)] * world
+    vals, cnt = np.unique(all_kx, return_counts=True)
+    cum = np.cumsum(cnt)
+    total = int(cum[-1])
+    bounds = [0]                                         # indices into vals where a new slab starts
+    for r in range(1, world):
+        j = int(np.searchsorted(cum, r * total / world, side="left")) + 1      # first layer of slab r
+        bounds.append(min(max(j, bounds[-1]), len(vals)))
+    bounds.append(len(vals))
+    out = []
+    for r in range(world):
+        a, b = bounds[r], bounds[r + 1]
+        out.append((int(vals[a]), int(vals[b - 1])) if b > a else (1, 0))
+    return out
+
+
+def slab_routes(kx: np.ndarray, slabs):
+    """Which of this rank's units (by pool index) each slab rank needs: its own layers plus the ghost layers lo - 1, hi + 1, hi + 2."""
+    return [np.nonzero((kx >= lo - 1) & (kx <= hi + 2))[0].astype(np.int32) if hi >= lo else np.zeros((0,), np.int32) for lo, hi in slabs]
+
+
+class SlabExtractor:
+    """The phases of the collective extraction for ONE rank; `ShardedTSDFVolume` strings them together with
+    real collectives, the tests with LocalComm.  Integration shards by unit-key hash (balance); a hash shard's neighbours are
+    almost all remote, so extraction first RE-PARTITIONS the volume into kx slabs: each unit goes to the rank whose slab holds
+    it and, as a ghost, to the slabs within one layer below / two layers above.  A rank then holds O(own + ghost layers)
+    units, extracts what its slab owns with the single-GPU kernels, and the slab-order concatenation of the parts IS the
+    single-GPU mesh (vertex numbering continues across slab borders, see b2r_tsdf_extract_mesh_slab)."""
+
+    def __init__(self, vol: ScalableTSDFVolume, rank: int, world: int):
+        self.vol, self.rank, self.world = vol, rank, world
+        self.slab: Optional[ScalableTSDFVolume] = None
+        self.range = (1, 0)
+        self.scratch_bytes = 0
+
+    # phase 1 (local): the kx of my units -> all_gather_v
+    def unit_kx(self) -> torch.Tensor:
+        self.keys = self.vol.unit_keys()
+        return self.keys[:, 0].contiguous()
+
+    # phase 2 (local): route my units -> all_to_all_v of each of the returned lists
+    def export_routes(self, gathered_kx: List[torch.Tensor]):
+        all_kx = torch.cat([g.reshape(-1) for g in gathered_kx]).cpu().numpy() if gathered_kx else np.zeros((0,), np.int32)
+        self.slabs = slab_cuts(all_kx, self.world)
+        self.range = self.slabs[self.rank]
+        routes = slab_routes(self.keys[:, 0].cpu().numpy(), self.slabs)
         dev = _lib.require_cuda()
-        e = lambda: torch.empty((0, 3), dtype=torch.float64, device=dev)
-        parts = [pc.points.tensor if len(pc.points) else e(), pc.normals.tensor if len(pc.points) else e()]
-        if vol.color_type != TSDFVolumeColorType.NoColor:
-            parts.append(pc.colors.tensor if len(pc.points) else e())
-        return parts
-    return _extract_mesh_part(tmp)
+        has_c = self.vol.color_type != TSDFVolumeColorType.NoColor
+        K, T, W, R = [], [], [], []
+        for ids in routes:
+            k, t, w, c = self.vol.export_selected(torch.as_tensor(ids, device=dev))
+            K.append(k); T.append(t); W.append(w); R.append(c)
+        return [K, T, W] + ([R] if has_c else [])
 
+    # phase 3 (local): import what arrived, size my part -> all_gather_v of the returned (1, 2) counts
+    def import_and_size(self, recv):
+        has_c = self.vol.color_type != TSDFVolumeColorType.NoColor
+        K, T, W = recv[:3]
+        R = recv[3] if has_c else [None] * len(K)
+        total = sum(int(k.shape[0]) for k in K)
+        if self.slab is None or self.slab.capacity() < total:
+            self.slab = None
+            self.slab = ScalableTSDFVolume(self.vol.voxel_length, self.vol.sdf_trunc, self.vol.color_type, capacity_units=max(int(total * 1.25), 64) + 16)
+        else:
+            self.slab.reset()
+        for k, t, w, c in zip(K, T, W, R):
+            if k.shape[0]:
+                self.slab.import_units(k, t, w, c if has_c else None, sync=False)
+        self.units_held = total
+        self.scratch_bytes = self.slab.capacity() * (5 if has_c else 2) * 4096 * 4
+        lib, dev = _lib.load(), _lib.require_cuda()
+        nV, nF = C.c_int64(0), C.c_int64(0)
+        lo, hi = self.range
+        rc = lib.b2r_tsdf_extract_mesh_slab(self.slab._h, lo, hi, 0, None, None, None, None, 0, 0, C.byref(nV), C.byref(nF), _lib.stream_ptr())
+        if rc not in (_lib.OK, _lib.ERR_CAPACITY):
+            _lib.check(rc, "extract_mesh_slab")
+        self.nV, self.nF = int(nV.value), int(nF.value)
+        return torch.tensor([[self.nV, self.nF]], dtype=torch.int64, device=dev)
 
-def _extract_mesh_part(tmp: ScalableTSDFVolume):
-    lib, dev = _lib.load(), _lib.require_cuda()
-    nV, nF, vb = C.c_int64(0), C.c_int64(0), C.c_int64(0)
-    rc = lib.b2r_tsdf_extract_mesh_sharded(tmp._h, None, None, None, None, 0, 0, C.byref(nV), C.byref(nF), C.byref(vb), _lib.stream_ptr())
-    if rc not in (_lib.OK, _lib.ERR_CAPACITY):
-        _lib.check(rc, "extract_mesh_sharded")
-    v, f = int(nV.value), int(nF.value)
-    has_c = tmp.color_type != TSDFVolumeColorType.NoColor
-    vtx = torch.empty((v, 3), dtype=torch.float64, device=dev)
-    vcol = torch.empty((v, 3), dtype=torch.float64, device=dev) if has_c else None
-    tri = torch.empty((f, 3), dtype=torch.int32, device=dev)
-    if v:
-        _lib.check(lib.b2r_tsdf_extract_mesh_sharded(tmp._h, _lib.ptr(vtx), _lib.ptr(vcol), _lib.ptr(tri) if f else _lib.ptr(torch.empty((1, 3), dtype=torch.int32, device=dev)),
-                                                      None, v, max(f, 1), C.byref(nV), C.byref(nF), C.byref(vb), _lib.stream_ptr()), "extract_mesh_sharded")
-    return [vtx, tri] + ([vcol] if has_c else [])
+    # phase 4 (local): fill with the global vertex base -> gather_v / all_gather_v of the returned tensors
+    def fill_mesh(self, gathered_counts: List[torch.Tensor]):
+        lib, dev = _lib.load(), _lib.require_cuda()
+        counts = torch.cat(gathered_counts).cpu().numpy().reshape(-1, 2)
+        vbase = int(counts[:self.rank, 0].sum())
+        has_c = self.vol.color_type != TSDFVolumeColorType.NoColor
+        v, f = self.nV, self.nF
+        vtx = torch.empty((v, 3), dtype=torch.float64, device=dev)
+        vcol = torch.empty((v, 3), dtype=torch.float64, device=dev) if has_c else None
+        tri = torch.empty((f, 3), dtype=torch.int32, device=dev)
+        if v:
+            nV, nF = C.c_int64(0), C.c_int64(0)
+            lo, hi = self.range
+            _lib.check(lib.b2r_tsdf_extract_mesh_slab(self.slab._h, lo, hi, vbase, _lib.ptr(vtx), _lib.ptr(vcol),
+                                                      _lib.ptr(tri) if f else _lib.ptr(torch.empty((1, 3), dtype=torch.int32, device=dev)),
+                                                      None, v, max(f, 1), C.byref(nV), C.byref(nF), _lib.stream_ptr()), "extract_mesh_slab")
+        return [vtx, tri] + ([vcol] if has_c else [])
+
+    def extract_points_part(self):
+        lib, dev = _lib.load(), _lib.require_cuda()
+        has_c = self.vol.color_type != TSDFVolumeColorType.NoColor
+        lo, hi = self.range
+        cnt = C.c_int64(0)
+        rc = lib.b2r_tsdf_extract_points_slab(self.slab._h, lo, hi, None, None, None, None, 0, C.byref(cnt), _lib.stream_ptr())
+        if rc not in (_lib.OK, _lib.ERR_CAPACITY):
+            _lib.check(rc, "extract_points_slab")
+        n = int(cnt.value)
+        xyz = torch.empty((n, 3), dtype=torch.float64, device=dev)
+        nrm = torch.empty((n, 3), dtype=torch.float64, device=dev)
+        rgb = torch.empty((n, 3), dtype=torch.float64, device=dev) if has_c else None
+        if n:
+            _lib.check(lib.b2r_tsdf_extract_points_slab(self.slab._h, lo, hi, _lib.ptr(xyz), _lib.ptr(rgb), _lib.ptr(nrm), None, n, C.byref(cnt),
+                                                        _lib.stream_ptr()), "extract_points_slab")
+        return [xyz, nrm] + ([rgb] if has_c else [])
 
 
 def merge_mesh_parts(parts: List[List[torch.Tensor]]) -> TriangleMesh:
-    """parts[i] = list over ranks of tensor i of _extract_mesh_part.  Triangle ids are already global and the
-    global vertex order is rank-major, so the mesh is the plain rank-order concatenation."""
+    """parts[i] = list over ranks of tensor i of SlabExtractor.fill_mesh.  Triangle ids are already global and the
+    global vertex order is slab-major, so the mesh is the plain rank-order concatenation."""
     mesh = TriangleMesh()
     vtx, tri = torch.cat(parts[0]), torch.cat(parts[1])
     if vtx.shape[0] == 0:
@@ -147,12 +278,17 @@ def merge_point_parts(parts: List[List[torch.Tensor]]) -> PointCloud:
 
 
 class ShardedTSDFVolume:
-    """One shard of a ScalableTSDFVolume per rank; same integrate / extract calls, collective extraction."""
+    """One shard of a ScalableTSDFVolume per rank; same integrate / extract calls, collective extraction.
+    ``gather="rank0"`` (default): the mesh / cloud is returned on rank 0, the other ranks get an empty geometry;
+    ``gather="all"``: every rank gets the whole result."""
 
     def __init__(self, voxel_length: float, sdf_trunc: float, color_type, *, group=None, capacity_units: Optional[int] = None):
         self.comm = Comm(group)
         self.local = ScalableTSDFVolume(voxel_length, sdf_trunc, color_type, capacity_units=capacity_units,
                                         rank=self.comm.rank, world=self.comm.world)
+        self._ex = SlabExtractor(self.local, self.comm.rank, self.comm.world)
+        self.last_extract_scratch_bytes = 0
+        self.last_extract_units_held = 0
 
     def integrate(self, image, intrinsic, extrinsic) -> None:
         self.local.integrate(image, intrinsic, extrinsic)          # every rank gets every frame; no collective
@@ -163,16 +299,29 @@ class ShardedTSDFVolume:
     def reset(self) -> None:
         self.local.reset()
 
-    def _gather(self, tensors):
-        return [self.comm.all_gather_v(t) for t in tensors]
+    def _repartition(self):
+        ex, c = self._ex, self.comm
+        routes = ex.export_routes(c.all_gather_v(ex.unit_kx()))
+        counts = ex.import_and_size([c.all_to_all_v(lst) for lst in routes])
+        self.last_extract_scratch_bytes, self.last_extract_units_held = ex.scratch_bytes, ex.units_held
+        return counts
 
-    def extract_triangle_mesh(self) -> TriangleMesh:
-        part = phase_extract(self.local, self._gather(phase_export(self.local)), "mesh")
-        return merge_mesh_parts(self._gather(part))
+    def _collect(self, tensors, gather):
+        if gather == "all":
+            return [self.comm.all_gather_v(t) for t in tensors]
+        got = [self.comm.gather_v(t, 0) for t in tensors]
+        return got if self.comm.rank == 0 else None
 
-    def extract_point_cloud(self) -> PointCloud:
-        part = phase_extract(self.local, self._gather(phase_export(self.local)), "points")
-        return merge_point_parts(self._gather(part))
+    def extract_triangle_mesh(self, gather: str = "rank0") -> TriangleMesh:
+        counts = self._repartition()
+        part = self._ex.fill_mesh(self.comm.all_gather_v(counts))
+        parts = self._collect(part, gather)
+        return merge_mesh_parts(parts) if parts is not None else TriangleMesh()
+
+    def extract_point_cloud(self, gather: str = "rank0") -> PointCloud:
+        self._repartition()
+        parts = self._collect(self._ex.extract_points_part(), gather)
+        return merge_point_parts(parts) if parts is not None else PointCloud()
 
 
 # ---- host-frame ingest at world > 1: upload 1/world per rank over PCIe, exchange over NVLink -----------------------

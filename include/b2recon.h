@@ -167,13 +167,18 @@ int b2r_tsdf_extract_points(b2r_tsdf* h, double* xyz, double* rgb, double* nrm, 
 /* ---- a11: volume.extract_triangle_mesh()  (GoodColorReconstruction.py:285,536) */
 int b2r_tsdf_extract_mesh(b2r_tsdf* h, double* vtx, double* vcol, int32_t* tri, int32_t* ids4, int64_t capV,
                           int64_t capF, int64_t* nV_host, int64_t* nF_host, cudaStream_t stream);
-/* Multi-GPU form: on a handle created with world > 1 that holds the full volume (own units + the
- * other ranks' units imported as ghosts), a10/a11 emit only what this rank's units own; triangle vertex ids
- * are global in (owner rank, unit key, voxel, axis) order, so concatenating the ranks' outputs in rank order
- * gives the complete welded mesh.  *vertex_base_host = this rank's first global vertex id. */
-int b2r_tsdf_extract_mesh_sharded(b2r_tsdf* h, double* vtx, double* vcol, int32_t* tri, int32_t* ids, int64_t capV,
-                                  int64_t capF, int64_t* nV_host, int64_t* nF_host, int64_t* vertex_base_host,
-                                  cudaStream_t stream);
+/* Multi-GPU extraction; integration shards by unit-key hash, extraction re-partitions by kx SLABS (cubes and
+ * normals straddle unit borders, and a slab has only thin ghost layers).  The handle holds every unit with kx in
+ * [kx_lo, kx_hi] plus the ghost layers kx_lo - 1, kx_hi + 1, kx_hi + 2; a10/a11 emit what the slab's units own.  Vertex ids are
+ * global: vertex_base (the vertex count of the slabs below, known after every rank's sizing call) + the key-order numbering,
+ * which runs on into the ghost layer above -- the slab-order concatenation of the ranks' outputs is the single-GPU mesh. */
+int b2r_tsdf_extract_mesh_slab(b2r_tsdf* h, int kx_lo, int kx_hi, int64_t vertex_base, double* vtx, double* vcol, int32_t* tri,
+                               int32_t* ids4, int64_t capV, int64_t capF, int64_t* nV_host, int64_t* nF_host, cudaStream_t stream);
+int b2r_tsdf_extract_points_slab(b2r_tsdf* h, int kx_lo, int kx_hi, double* xyz, double* rgb, double* nrm, int32_t* ids4,
+                                 int64_t capacity, int64_t* count_host, cudaStream_t stream);
+/* units ids[0..n) (DEVICE pool indices) in export layout (keys3 may be NULL): routes units to their slab ranks */
+int b2r_tsdf_export_selected(b2r_tsdf* h, const int32_t* ids, int64_t n, int32_t* keys3, float* tsdf, float* weight, float* rgb,
+                             cudaStream_t stream);
 /* mesh.compute_vertex_normals()  (GoodColorReconstruction.py:286) */
 int b2r_mesh_vertex_normals(const double* vtx, int64_t nV, const int32_t* tri, int64_t nF, double* out,
                             cudaStream_t stream);

@@ -50,6 +50,13 @@ def _worker(rank, world, port, q):
         cnt = torch.tensor([mine], dtype=torch.int64)
         dist.all_reduce(cnt)
         assert int(cnt.item()) == len(keys) and 0.35 * len(keys) < mine < 0.65 * len(keys)
+        # ragged all-to-all and gather-v (slab re-partition of the extraction): rank r sends r + d + 1 rows to rank d
+        parts = [torch.full((rank + d + 1, 2), 10 * rank + d, dtype=torch.float32) for d in range(world)]
+        got = comm.all_to_all_v(parts)
+        assert [g.shape[0] for g in got] == [src + rank + 1 for src in range(world)]
+        assert all(float(g[0, 0]) == 10 * src + rank for src, g in enumerate(got))
+        gv = comm.gather_v(torch.full((rank + 1,), float(rank)), 0)
+        assert (gv is None) if rank else ([g.shape[0] for g in gv] == [1, 2] and float(gv[1][0]) == 1.0)
         # host-frame exchange: each rank uploads its share, the all-gather returns every frame in global order
         F, H, W = 11, 4, 6                                                       # ragged: 11 frames, super-chunks of 2 x 3
         depth = (torch.arange(F * H * W, dtype=torch.int32) % 60000).to(torch.int16).reshape(F, H, W).view(torch.uint16)
@@ -140,3 +147,29 @@ def test_superchunk_plan_keeps_global_frame_order():
                 covered += list(range(f0, f1))
             assert covered[-n_valid:] == list(range(f_start, f_start + n_valid))
         assert covered == list(range(F))
+
+
+def test_slab_cuts_and_routes():
+    rng = np.random.default_rng(3)
+    for world in (1, 2, 3, 4, 8):
+        kx = rng.integers(-7, 9, size=500).astype(np.int32)
+        slabs = sharded.slab_cuts(kx, world)
+        assert len(slabs) == world
+        covered = np.zeros(kx.shape, np.int32)
+        prev_hi = None
+        for lo, hi in slabs:
+            if hi < lo:
+                continue
+            assert prev_hi is None or lo > prev_hi                            # disjoint, ascending
+            prev_hi = hi
+            covered += ((kx >= lo) & (kx <= hi))
+        assert np.all(covered == 1)                                           # every unit layer belongs to exactly one slab
+        sizes = [int(((kx >= lo) & (kx <= hi)).sum()) for lo, hi in slabs if hi >= lo]
+        assert max(sizes) <= 500 / min(world, 16) + 80                        # balanced up to one layer of units
+        routes = sharded.slab_routes(kx, slabs)
+        for (lo, hi), ids in zip(slabs, routes):
+            if hi < lo:
+                assert len(ids) == 0
+            else:
+                assert set(np.unique(kx[ids]).tolist()) == set(v for v in np.unique(kx).tolist() if lo - 1 <= v <= hi + 2)
+    assert sharded.slab_cuts(np.zeros((0,), np.int32), 3) == [(1, 0)] * 3

@@ -16,13 +16,6 @@ from azurekinect3dreconstruction_b200 import synthetic as syn  # noqa: E402
 from azurekinect3dreconstruction_b200.pipelines import sharded  # noqa: E402
 
 
-def canon(m):
-    v, t = np.asarray(m.vertices), np.asarray(m.triangles)
-    o = np.lexsort(v.T[::-1]); inv = np.empty_like(o); inv[o] = np.arange(len(o))
-    t = inv[t]
-    return v[o], t[np.lexsort(t.T[::-1])]
-
-
 def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -41,18 +34,24 @@ def main():
         vol.integrate(rgbd, K, E)
         if single is not None:
             single.integrate(rgbd, K, E)
-    mesh = vol.extract_triangle_mesh()
+    mesh = vol.extract_triangle_mesh()                      # gather to rank 0
+    held = vol.last_extract_units_held
     pcd = vol.extract_point_cloud()
+    mesh_all = vol.extract_triangle_mesh(gather="all")      # every rank gets the whole mesh
     n_local = vol.local.num_units()
     ok = True
     if rank == 0:
         ref = single.extract_triangle_mesh()
-        a, b = canon(mesh), canon(ref)
-        ok = np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+        # the slab-order concatenation IS the single-GPU mesh: same vertex order, same triangle order, same colours
+        ok = np.array_equal(np.asarray(mesh.vertices), np.asarray(ref.vertices)) and np.array_equal(np.asarray(mesh.triangles), np.asarray(ref.triangles)) \
+            and np.array_equal(np.asarray(mesh.vertex_colors), np.asarray(ref.vertex_colors))
         rp = single.extract_point_cloud()
-        ok = ok and len(pcd.points) == len(rp.points) and np.array_equal(np.sort(np.asarray(pcd.points), 0), np.sort(np.asarray(rp.points), 0))
-        print("sharded_check world=%d: units(rank0)=%d of %d, V=%d F=%d points=%d -> %s" % (world, n_local, single.num_units(), len(mesh.vertices),
-                                                                                        len(mesh.triangles), len(pcd.points), "OK" if ok else "MISMATCH"))
+        ok = ok and np.array_equal(np.asarray(pcd.points), np.asarray(rp.points)) and np.array_equal(np.asarray(pcd.normals), np.asarray(rp.normals))
+        ok = ok and np.array_equal(np.asarray(mesh_all.triangles), np.asarray(ref.triangles))
+        print("sharded_check world=%d: units(rank0 shard)=%d of %d, held by rank 0 during extraction=%d, V=%d F=%d points=%d -> %s" % (
+            world, n_local, single.num_units(), held, len(mesh.vertices), len(mesh.triangles), len(pcd.points), "OK" if ok else "MISMATCH"))
+    else:
+        ok = len(mesh.vertices) == 0 and len(mesh_all.vertices) > 0
     dist.barrier()
     dist.destroy_process_group()
     return 0 if ok else 1
