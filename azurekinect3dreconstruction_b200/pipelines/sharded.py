@@ -289,6 +289,16 @@ class ShardedTSDFVolume:
         self._ex = SlabExtractor(self.local, self.comm.rank, self.comm.world)
         self.last_extract_scratch_bytes = 0
         self.last_extract_units_held = 0
+        self.timing = None            # set to {} to collect per-phase wall times (each phase then ends with a device sync)
+
+    def _tick(self, name, t0):
+        import time
+        if self.timing is None:
+            return t0
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        self.timing[name] = self.timing.get(name, 0.0) + (t1 - t0)
+        return t1
 
     def integrate(self, image, intrinsic, extrinsic) -> None:
         self.local.integrate(image, intrinsic, extrinsic)          # every rank gets every frame; no collective
@@ -300,9 +310,17 @@ class ShardedTSDFVolume:
         self.local.reset()
 
     def _repartition(self):
+        import time
         ex, c = self._ex, self.comm
-        routes = ex.export_routes(c.all_gather_v(ex.unit_kx()))
-        counts = ex.import_and_size([c.all_to_all_v(lst) for lst in routes])
+        t = time.perf_counter()
+        kx = c.all_gather_v(ex.unit_kx())
+        t = self._tick("1_gather_kx", t)
+        routes = ex.export_routes(kx)
+        t = self._tick("2_route_export", t)
+        recv = [c.all_to_all_v(lst) for lst in routes]
+        t = self._tick("3_all_to_all_units", t)
+        counts = ex.import_and_size(recv)
+        t = self._tick("4_import_count_pass", t)
         self.last_extract_scratch_bytes, self.last_extract_units_held = ex.scratch_bytes, ex.units_held
         return counts
 
@@ -313,10 +331,16 @@ class ShardedTSDFVolume:
         return got if self.comm.rank == 0 else None
 
     def extract_triangle_mesh(self, gather: str = "rank0") -> TriangleMesh:
+        import time
         counts = self._repartition()
+        t = time.perf_counter()
         part = self._ex.fill_mesh(self.comm.all_gather_v(counts))
+        t = self._tick("5_fill", t)
         parts = self._collect(part, gather)
-        return merge_mesh_parts(parts) if parts is not None else TriangleMesh()
+        t = self._tick("6_gather_parts", t)
+        mesh = merge_mesh_parts(parts) if parts is not None else TriangleMesh()
+        self._tick("7_concat", t)
+        return mesh
 
     def extract_point_cloud(self, gather: str = "rank0") -> PointCloud:
         self._repartition()

@@ -232,6 +232,13 @@ def config5_record(dev, rank, world, ticks=64, n_streams=8, ticks_per_batch=4):
     mesh = extract()
     barrier()
     t_mesh = red(time.perf_counter() - t0, "max")
+    phases = None
+    if vol is not None:                                    # one more extraction with a device sync after every phase: where the time goes
+        vol.timing = {}
+        mesh = extract()
+        barrier()
+        phases = {k: round(1e3 * v, 3) for k, v in sorted(vol.timing.items())}
+        vol.timing = None
     nfr = ticks * n_streams
     algo = 40.0 * upd + 7.0 * W * H * nfr
     out = {"workload": "configs[4]: %d WFOV 1024x1024 streams x %d ticks, voxel 2 mm, trunc 1 cm, ONE volume sharded by unit-key hash over %d GPU(s); "
@@ -242,7 +249,7 @@ def config5_record(dev, rank, world, ticks=64, n_streams=8, ticks_per_batch=4):
            "nvlink_gathered_bytes_per_rank_per_step": ex.bytes_gathered // 2 if world > 1 else 0,
            "units_total": units, "updated_voxels_total": upd, "algorithmic_bytes_per_step": algo,
            "achieved_aggregate": algo / (ms * 1e-3) / 1e9, "unit": "GB/s",
-           "mesh_gather_s": t_mesh, "vertices": len(mesh.vertices), "triangles": len(mesh.triangles),
+           "mesh_gather_s": t_mesh, "mesh_phases_ms_rank0": phases, "vertices": len(mesh.vertices), "triangles": len(mesh.triangles),
            "extraction_scratch_bytes_rank0": getattr(vol, "last_extract_scratch_bytes", None) if vol is not None else None,
            "render_s": render_s}
     del packed, local, vol, ex
