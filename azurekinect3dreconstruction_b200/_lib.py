@@ -66,6 +66,7 @@ SIGNATURES = {
     "b2r_tsdf_export_selected": (_i, [_vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
     "b2r_mesh_vertex_normals": (_i, [_vp, _i64, _vp, _i64, _vp, _vp]),
     "b2r_odometry": (_i, [_vp, _vp, _vp, _vp, _i, _i, _d, _d, _d, _d, _pd, _i, _pi, _i, _d, _d, _d, _pd, _pd, _pi, _vp]),
+    "b2r_odometry_batch": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _d, _d, _d, _d, _pd, _i, _pi, _i, _d, _d, _d, _pd, _pd, _pi, _vp]),
     "b2r_image_filter": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "b2r_image_downsample": (_i, [_vp, _i, _i, _vp, _vp]),
     "b2r_knn_create": (_vp, [_vp, _i64, _d, _i, _vp]),

@@ -16,6 +16,7 @@
 //                      LDLT and left-multiplies the pose, all in one launch.
 // Image filters keep upstream's rounding points (f64 accumulate, f32 store after each separable pass).
 #include <mutex>
+#include <vector>
 #include "common.cuh"
 #include "host_math.h"
 #include <math.h>
@@ -27,6 +28,11 @@ namespace {
 #define OD_EMPTY 0xFFFFFFFFFFFFFFFFull
 
 struct KLevel { double fx, fy, cx, cy; };
+
+// Batched pairs (config 4: 300 independent consecutive pairs): every pair owns one contiguous workspace block, blockIdx.y is the
+// pair, and every workspace pointer a kernel receives is the FIRST pair's -- shifted by blockIdx.y * stride bytes at entry.
+template <class T>
+__device__ __forceinline__ T* pair_ptr(T* p, size_t stride) { return (T*)((const char*)p + (size_t)blockIdx.y * stride); }
 
 // device-resident iteration state
 struct OdoState {
@@ -54,8 +60,10 @@ __device__ __forceinline__ float pre_depth(float p, float dmin, float dmax) {
 
 // out = Filter(in) with clamp-to-edge; PRE applies PreprocessDepth to the loads first
 template <bool PRE>
-__global__ void __launch_bounds__(OD_THREADS) filter3_kernel(const float* __restrict__ in, float* __restrict__ out, int W, int H,
-                                                              int kind, float dmin, float dmax) {
+__global__ void __launch_bounds__(OD_THREADS) filter3_kernel(const float* __restrict__ in_, float* __restrict__ out_, int W, int H,
+                                                              int kind, float dmin, float dmax, size_t stride) {
+    const float* __restrict__ in = pair_ptr(in_, stride);
+    float* __restrict__ out = pair_ptr(out_, stride);
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= W * H) return;
     const int v = idx / W, u = idx - v * W;
@@ -79,7 +87,9 @@ __global__ void __launch_bounds__(OD_THREADS) filter3_kernel(const float* __rest
     out[idx] = (float)acc;
 }
 
-__global__ void __launch_bounds__(OD_THREADS) downsample_kernel(const float* __restrict__ in, float* __restrict__ out, int W, int H) {
+__global__ void __launch_bounds__(OD_THREADS) downsample_kernel(const float* __restrict__ in_, float* __restrict__ out_, int W, int H, size_t stride) {
+    const float* __restrict__ in = pair_ptr(in_, stride);
+    float* __restrict__ out = pair_ptr(out_, stride);
     const int Wo = W / 2, Ho = H / 2;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= Wo * Ho) return;
@@ -88,21 +98,28 @@ __global__ void __launch_bounds__(OD_THREADS) downsample_kernel(const float* __r
     out[idx] = xfdiv(xfadd(xfadd(xfadd(a, b), c), d), 4.0f);
 }
 
-__global__ void __launch_bounds__(OD_THREADS) scale_kernel(float* img, int n, const OdoState* st, int which) {
+__global__ void __launch_bounds__(OD_THREADS) scale_kernel(float* img_, int n, const OdoState* st_, int which, size_t stride) {
+    float* img = pair_ptr(img_, stride);
+    const OdoState* st = pair_ptr(st_, stride);
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= n) return;
     img[idx] = (float)xdmul(st->scale[which], (double)img[idx]);
 }
 
-__global__ void fill_u64_kernel(unsigned long long* p, int n) {
+__global__ void fill_u64_kernel(unsigned long long* p_, int n, size_t stride) {
+    unsigned long long* p = pair_ptr(p_, stride);
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx < n) p[idx] = OD_EMPTY;
 }
 
 // ---- correspondence (SURVEY A.6 ComputeCorrespondence) -------------------------------------------------
-__global__ void __launch_bounds__(OD_THREADS) corr_warp_kernel(const float* __restrict__ ds, const float* __restrict__ dt, int W, int H,
-                                                                const KLevel K, const OdoState* st, double depth_diff_max,
-                                                                unsigned long long* zbuf) {
+__global__ void __launch_bounds__(OD_THREADS) corr_warp_kernel(const float* __restrict__ ds_, const float* __restrict__ dt_, int W, int H,
+                                                                const KLevel K, const OdoState* st_, double depth_diff_max,
+                                                                unsigned long long* zbuf_, size_t stride) {
+    const float* __restrict__ ds = pair_ptr(ds_, stride);
+    const float* __restrict__ dt = pair_ptr(dt_, stride);
+    const OdoState* st = pair_ptr(st_, stride);
+    unsigned long long* zbuf = pair_ptr(zbuf_, stride);
     __shared__ double sM[9], sKt[3];
     if (threadIdx.x == 0) {
         const double Km[9] = {K.fx, 0, K.cx, 0, K.fy, K.cy, 0, 0, 1};
@@ -254,8 +271,14 @@ struct LevelImgs {
 // MODE 0: colour-term Jacobian, 1: hybrid-term Jacobian, 2: intensity means (NormalizeIntensity),
 //      3: information matrix (CreateInformationMatrix)
 template <int MODE>
-__global__ void __launch_bounds__(OD_THREADS) reduce_kernel(const LevelImgs L, const KLevel K, OdoState* st, unsigned long long* zbuf,
-                                                             double* partials) {
+__global__ void __launch_bounds__(OD_THREADS) reduce_kernel(const LevelImgs L_, const KLevel K, OdoState* st_, unsigned long long* zbuf_,
+                                                             double* partials_, size_t stride) {
+    LevelImgs L = L_;
+    L.sg = pair_ptr(L_.sg, stride); L.sd = pair_ptr(L_.sd, stride); L.tg = pair_ptr(L_.tg, stride); L.td = pair_ptr(L_.td, stride);
+    L.tgdx = pair_ptr(L_.tgdx, stride); L.tgdy = pair_ptr(L_.tgdy, stride); L.tddx = pair_ptr(L_.tddx, stride); L.tddy = pair_ptr(L_.tddy, stride);
+    OdoState* st = pair_ptr(st_, stride);
+    unsigned long long* zbuf = pair_ptr(zbuf_, stride);
+    double* partials = pair_ptr(partials_, stride);
     constexpr int NV = (MODE == 2) ? 3 : (MODE == 3 ? 22 : OD_NV);
     double acc[NV];
 #pragma unroll
@@ -432,7 +455,7 @@ int get_ws(size_t bytes, void** out) {
     return B2R_OK;
 }
 
-struct OdoGraphKey { int W, H, jac, n_levels, iters[8]; double k[7]; void* ws; };
+struct OdoGraphKey { int W, H, jac, n_levels, iters[8], batch; double k[7]; void* ws; };
 struct OdoGraph { OdoGraphKey key; cudaGraphExec_t exec = nullptr; cudaStream_t cap_stream = nullptr; };
 OdoGraph g_odo_graph[16];
 bool odo_graph_enabled() {
@@ -443,18 +466,18 @@ bool odo_graph_enabled() {
 
 inline unsigned nblk(int n) { return (unsigned)((n + OD_THREADS - 1) / OD_THREADS); }
 
-}  // namespace
-
-// compute_rgbd_odometry.  See include/b2recon.h.
-B2R_API int b2r_odometry(const float* src_gray, const float* src_depth, const float* tgt_gray, const float* tgt_depth, int W,
-                         int H, double fx, double fy, double cx, double cy, const double* init_host, int jac_kind,
-                         const int* iters_host, int n_levels, double depth_diff_max, double depth_min, double depth_max,
-                         double* out_T_host, double* out_info_host, int* success_host, cudaStream_t stream) {
-    if (!src_gray || !src_depth || !tgt_gray || !tgt_depth || !init_host || !iters_host || !out_T_host || !out_info_host ||
+// B independent pairs in one launch sequence: every kernel runs with grid.y = B over per-pair workspace blocks.
+int odometry_impl(int B, const float* const* src_gray, const float* const* src_depth, const float* const* tgt_gray, const float* const* tgt_depth,
+                  int W, int H, double fx, double fy, double cx, double cy, const double* init_host, int jac_kind,
+                  const int* iters_host, int n_levels, double depth_diff_max, double depth_min, double depth_max,
+                  double* out_T_host, double* out_info_host, int* success_host, cudaStream_t stream) {
+    if (B < 1 || B > 65535 || !src_gray || !src_depth || !tgt_gray || !tgt_depth || !iters_host || !out_T_host || !out_info_host ||
         !success_host || W < 4 || H < 4 || n_levels < 1 || n_levels > 8 || jac_kind < 0 || jac_kind > 1) {
         b2r_set_error("b2r_odometry: bad argument");
         return B2R_ERR_BAD_ARG;
     }
+    for (int p = 0; p < B; p++)
+        if (!src_gray[p] || !src_depth[p] || !tgt_gray[p] || !tgt_depth[p]) { b2r_set_error("b2r_odometry: null image"); return B2R_ERR_BAD_ARG; }
     int Wl[8], Hl[8];
     size_t off[8], total_px = 0;
     for (int l = 0; l < n_levels; l++) {
@@ -464,23 +487,24 @@ B2R_API int b2r_odometry(const float* src_gray, const float* src_depth, const fl
     }
     const size_t N0 = (size_t)W * H;
     // Workspace and graph cache are process-global per device and a ctypes call releases the GIL (the reference runs one
-    // thread per camera): one odometry at a time per device; the lock is held until the result has been read back.
+    // thread per camera): one odometry call at a time per device; the lock is held until the results have been read back.
     int cur_dev = 0;
     B2R_CUDA(cudaGetDevice(&cur_dev));
     static std::mutex odo_mu[16];
     std::lock_guard<std::mutex> odo_lock(odo_mu[cur_dev & 15]);
     int nsm = 148;
     cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, cur_dev);
+    // the per-pair reduction grid is part of the arithmetic (partial sums per block): it must not depend on the batch size
     const unsigned red_grid_max = (unsigned)nsm * 2;
-    // workspace: 8 pyramids + 1 temp image + 4 staged inputs + zbuf + partials + state
+    // one pair's workspace block: 8 pyramids + 1 temp image + 4 staged inputs + zbuf + partials + state
     const size_t N0p = (N0 + 63) & ~(size_t)63;
     const size_t bytes_imgs = (8 * total_px + N0p + 4 * N0p) * sizeof(float);
     const size_t o_z = (bytes_imgs + 255) & ~(size_t)255;
     const size_t o_p = o_z + ((N0 * 8 + 255) & ~(size_t)255);
     const size_t o_s = o_p + (((size_t)red_grid_max * OD_NV * 8 + 255) & ~(size_t)255);
-    const size_t total = o_s + sizeof(OdoState);
+    const size_t stride = (o_s + sizeof(OdoState) + 255) & ~(size_t)255;
     void* ws = nullptr;
-    int rc = get_ws(total, &ws);
+    int rc = get_ws(stride * (size_t)B, &ws);
     if (rc != B2R_OK) return rc;
     float* base = (float*)ws;
     float* pyr[8];
@@ -492,26 +516,30 @@ B2R_API int b2r_odometry(const float* src_gray, const float* src_depth, const fl
     double* partials = (double*)((char*)ws + o_p);
     OdoState* st = (OdoState*)((char*)ws + o_s);
 
-    OdoState h0;
-    memset(&h0, 0, sizeof(h0));
-    bool all_zero = true;
-    for (int i = 0; i < 16; i++) if (init_host[i] != 0.0) all_zero = false;
-    if (all_zero) b2r::m4_identity(h0.pose); else memcpy(h0.pose, init_host, sizeof(h0.pose));
-    h0.scale[0] = h0.scale[1] = 1.0;
-    B2R_CUDA(cudaMemcpyAsync(st, &h0, sizeof(h0), cudaMemcpyHostToDevice, stream));
+    for (int p = 0; p < B; p++) {
+        OdoState h0;
+        memset(&h0, 0, sizeof(h0));
+        bool all_zero = true;
+        if (init_host) for (int i = 0; i < 16; i++) if (init_host[16 * p + i] != 0.0) all_zero = false;
+        if (all_zero) b2r::m4_identity(h0.pose); else memcpy(h0.pose, init_host + 16 * p, sizeof(h0.pose));
+        h0.scale[0] = h0.scale[1] = 1.0;
+        B2R_CUDA(cudaMemcpyAsync((char*)st + (size_t)p * stride, &h0, sizeof(h0), cudaMemcpyHostToDevice, stream));
+    }
     // Everything between the state upload and the result read-back is ~105 small dependent launches with fixed
     // parameters (the iteration counts are fixed; upstream has no convergence break): it is captured ONCE into a CUDA
-    // graph per (shape, intrinsics, options, workspace) and replayed; the inputs are first copied into staging images
+    // graph per (shape, intrinsics, options, batch, workspace) and replayed; the inputs are first copied into staging images
     // inside the workspace so the graph's pointers never change.  B2R_ODO_GRAPH=0 launches the kernels directly.
-    auto enqueue = [&](cudaStream_t s, const float* in_sg, const float* in_sd, const float* in_tg, const float* in_td) -> bool {
-    fill_u64_kernel<<<nblk((int)N0), OD_THREADS, 0, s>>>(zbuf, (int)N0);
+    const dim3 blk(OD_THREADS);
+    auto G2 = [&](int n) { return dim3(nblk(n), (unsigned)B); };
+    auto enqueue = [&](cudaStream_t s) -> bool {
+    fill_u64_kernel<<<G2((int)N0), blk, 0, s>>>(zbuf, (int)N0, stride);
 
     // InitializeRGBDOdometry: Gaussian3 on grays; PreprocessDepth + Gaussian3 on depths
     const float dmin = (float)depth_min, dmax = (float)depth_max;
-    filter3_kernel<false><<<nblk((int)N0), OD_THREADS, 0, s>>>(in_sg, pyr[0], W, H, 0, 0.f, 0.f);
-    filter3_kernel<false><<<nblk((int)N0), OD_THREADS, 0, s>>>(in_tg, pyr[2], W, H, 0, 0.f, 0.f);
-    filter3_kernel<true><<<nblk((int)N0), OD_THREADS, 0, s>>>(in_sd, pyr[1], W, H, 0, dmin, dmax);
-    filter3_kernel<true><<<nblk((int)N0), OD_THREADS, 0, s>>>(in_td, pyr[3], W, H, 0, dmin, dmax);
+    filter3_kernel<false><<<G2((int)N0), blk, 0, s>>>(stage[0], pyr[0], W, H, 0, 0.f, 0.f, stride);
+    filter3_kernel<false><<<G2((int)N0), blk, 0, s>>>(stage[2], pyr[2], W, H, 0, 0.f, 0.f, stride);
+    filter3_kernel<true><<<G2((int)N0), blk, 0, s>>>(stage[1], pyr[1], W, H, 0, dmin, dmax, stride);
+    filter3_kernel<true><<<G2((int)N0), blk, 0, s>>>(stage[3], pyr[3], W, H, 0, dmin, dmax, stride);
     if (cudaGetLastError() != cudaSuccess) return false;
 
     KLevel K[8];
@@ -524,15 +552,15 @@ B2R_API int b2r_odometry(const float* src_gray, const float* src_depth, const fl
         L.W = Wl[l]; L.H = Hl[l];
         return L;
     };
-    auto red_grid = [&](int n) { unsigned g = nblk(n); return g < red_grid_max ? g : red_grid_max; };
+    auto RG = [&](int n) { unsigned g = nblk(n); return dim3(g < red_grid_max ? g : red_grid_max, (unsigned)B); };
 
     // NormalizeIntensity over the correspondences at the initial pose
     {
         const LevelImgs L = level(0);
-        corr_warp_kernel<<<nblk((int)N0), OD_THREADS, 0, s>>>(L.sd, L.td, W, H, K[0], st, depth_diff_max, zbuf);
-        reduce_kernel<2><<<red_grid((int)N0), OD_THREADS, 0, s>>>(L, K[0], st, zbuf, partials);
-        scale_kernel<<<nblk((int)N0), OD_THREADS, 0, s>>>(pyr[0], (int)N0, st, 0);
-        scale_kernel<<<nblk((int)N0), OD_THREADS, 0, s>>>(pyr[2], (int)N0, st, 1);
+        corr_warp_kernel<<<G2((int)N0), blk, 0, s>>>(L.sd, L.td, W, H, K[0], st, depth_diff_max, zbuf, stride);
+        reduce_kernel<2><<<RG((int)N0), blk, 0, s>>>(L, K[0], st, zbuf, partials, stride);
+        scale_kernel<<<G2((int)N0), blk, 0, s>>>(pyr[0], (int)N0, st, 0, stride);
+        scale_kernel<<<G2((int)N0), blk, 0, s>>>(pyr[2], (int)N0, st, 1, stride);
         if (cudaGetLastError() != cudaSuccess) return false;
     }
     // pyramids: colour = Downsample(Gaussian3(prev)), depth = Downsample(prev)
@@ -541,20 +569,20 @@ B2R_API int b2r_odometry(const float* src_gray, const float* src_depth, const fl
         for (int img = 0; img < 4; img++) {
             const float* prev = pyr[img] + off[l - 1];
             if (img == 0 || img == 2) {
-                filter3_kernel<false><<<nblk(n_prev), OD_THREADS, 0, s>>>(prev, tmp, Wl[l - 1], Hl[l - 1], 0, 0.f, 0.f);
-                downsample_kernel<<<nblk(n_cur), OD_THREADS, 0, s>>>(tmp, pyr[img] + off[l], Wl[l - 1], Hl[l - 1]);
+                filter3_kernel<false><<<G2(n_prev), blk, 0, s>>>(prev, tmp, Wl[l - 1], Hl[l - 1], 0, 0.f, 0.f, stride);
+                downsample_kernel<<<G2(n_cur), blk, 0, s>>>(tmp, pyr[img] + off[l], Wl[l - 1], Hl[l - 1], stride);
             } else {
-                downsample_kernel<<<nblk(n_cur), OD_THREADS, 0, s>>>(prev, pyr[img] + off[l], Wl[l - 1], Hl[l - 1]);
+                downsample_kernel<<<G2(n_cur), blk, 0, s>>>(prev, pyr[img] + off[l], Wl[l - 1], Hl[l - 1], stride);
             }
         }
     }
     // Sobel of the target colour and depth pyramids
     for (int l = 0; l < n_levels; l++) {
         const int n = Wl[l] * Hl[l];
-        filter3_kernel<false><<<nblk(n), OD_THREADS, 0, s>>>(pyr[2] + off[l], pyr[4] + off[l], Wl[l], Hl[l], 1, 0.f, 0.f);
-        filter3_kernel<false><<<nblk(n), OD_THREADS, 0, s>>>(pyr[2] + off[l], pyr[5] + off[l], Wl[l], Hl[l], 2, 0.f, 0.f);
-        filter3_kernel<false><<<nblk(n), OD_THREADS, 0, s>>>(pyr[3] + off[l], pyr[6] + off[l], Wl[l], Hl[l], 1, 0.f, 0.f);
-        filter3_kernel<false><<<nblk(n), OD_THREADS, 0, s>>>(pyr[3] + off[l], pyr[7] + off[l], Wl[l], Hl[l], 2, 0.f, 0.f);
+        filter3_kernel<false><<<G2(n), blk, 0, s>>>(pyr[2] + off[l], pyr[4] + off[l], Wl[l], Hl[l], 1, 0.f, 0.f, stride);
+        filter3_kernel<false><<<G2(n), blk, 0, s>>>(pyr[2] + off[l], pyr[5] + off[l], Wl[l], Hl[l], 2, 0.f, 0.f, stride);
+        filter3_kernel<false><<<G2(n), blk, 0, s>>>(pyr[3] + off[l], pyr[6] + off[l], Wl[l], Hl[l], 1, 0.f, 0.f, stride);
+        filter3_kernel<false><<<G2(n), blk, 0, s>>>(pyr[3] + off[l], pyr[7] + off[l], Wl[l], Hl[l], 2, 0.f, 0.f, stride);
     }
     if (cudaGetLastError() != cudaSuccess) return false;
     // coarse-to-fine Gauss-Newton, 2 launches per iteration, no host sync
@@ -563,38 +591,42 @@ B2R_API int b2r_odometry(const float* src_gray, const float* src_depth, const fl
         const int n = Wl[l] * Hl[l];
         const int n_it = iters_host[n_levels - 1 - l];
         for (int it = 0; it < n_it; it++) {
-            corr_warp_kernel<<<nblk(n), OD_THREADS, 0, s>>>(L.sd, L.td, L.W, L.H, K[l], st, depth_diff_max, zbuf);
-            if (jac_kind == 0) reduce_kernel<0><<<red_grid(n), OD_THREADS, 0, s>>>(L, K[l], st, zbuf, partials);
-            else reduce_kernel<1><<<red_grid(n), OD_THREADS, 0, s>>>(L, K[l], st, zbuf, partials);
+            corr_warp_kernel<<<G2(n), blk, 0, s>>>(L.sd, L.td, L.W, L.H, K[l], st, depth_diff_max, zbuf, stride);
+            if (jac_kind == 0) reduce_kernel<0><<<RG(n), blk, 0, s>>>(L, K[l], st, zbuf, partials, stride);
+            else reduce_kernel<1><<<RG(n), blk, 0, s>>>(L, K[l], st, zbuf, partials, stride);
         }
         if (cudaGetLastError() != cudaSuccess) return false;
     }
     // CreateInformationMatrix at the final pose
     {
         const LevelImgs L = level(0);
-        corr_warp_kernel<<<nblk((int)N0), OD_THREADS, 0, s>>>(L.sd, L.td, W, H, K[0], st, depth_diff_max, zbuf);
-        reduce_kernel<3><<<red_grid((int)N0), OD_THREADS, 0, s>>>(L, K[0], st, zbuf, partials);
+        corr_warp_kernel<<<G2((int)N0), blk, 0, s>>>(L.sd, L.td, W, H, K[0], st, depth_diff_max, zbuf, stride);
+        reduce_kernel<3><<<RG((int)N0), blk, 0, s>>>(L, K[0], st, zbuf, partials, stride);
         if (cudaGetLastError() != cudaSuccess) return false;
     }
         return true;
     };
+    // the inputs go into the workspace's staging images (one copy per image): the launch sequence then has fixed pointers
+    const size_t nb = N0 * sizeof(float);
+    for (int p = 0; p < B; p++) {
+        const float* in[4] = {src_gray[p], src_depth[p], tgt_gray[p], tgt_depth[p]};
+        for (int i = 0; i < 4; i++) B2R_CUDA(cudaMemcpyAsync((char*)stage[i] + (size_t)p * stride, in[i], nb, cudaMemcpyDeviceToDevice, stream));
+    }
     OdoGraphKey key;
     memset(&key, 0, sizeof(key));
-    key.W = W; key.H = H; key.jac = jac_kind; key.n_levels = n_levels;
+    key.W = W; key.H = H; key.jac = jac_kind; key.n_levels = n_levels; key.batch = B;
     for (int l = 0; l < n_levels; l++) key.iters[l] = iters_host[l];
     key.k[0] = fx; key.k[1] = fy; key.k[2] = cx; key.k[3] = cy; key.k[4] = depth_diff_max; key.k[5] = depth_min; key.k[6] = depth_max;
     key.ws = ws;
     bool launched = false;
     if (odo_graph_enabled()) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        OdoGraph& G = g_odo_graph[dev & 15];
+        OdoGraph& G = g_odo_graph[cur_dev & 15];
         if (!G.exec || memcmp(&G.key, &key, sizeof(key)) != 0) {
             if (G.exec) { cudaGraphExecDestroy(G.exec); G.exec = nullptr; }
             if (!G.cap_stream) cudaStreamCreateWithFlags(&G.cap_stream, cudaStreamNonBlocking);
             cudaGraph_t graph = nullptr;
             if (G.cap_stream && cudaStreamBeginCapture(G.cap_stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
-                const bool ok = enqueue(G.cap_stream, stage[0], stage[1], stage[2], stage[3]);
+                const bool ok = enqueue(G.cap_stream);
                 const cudaError_t e = cudaStreamEndCapture(G.cap_stream, &graph);
                 if (ok && e == cudaSuccess && graph && cudaGraphInstantiate(&G.exec, graph, 0) == cudaSuccess) G.key = key;
                 else G.exec = nullptr;
@@ -603,43 +635,66 @@ B2R_API int b2r_odometry(const float* src_gray, const float* src_depth, const fl
             cudaGetLastError();   // a failed capture must not poison the direct path below
         }
         if (G.exec) {
-            const size_t nb = N0 * sizeof(float);
-            B2R_CUDA(cudaMemcpyAsync(stage[0], src_gray, nb, cudaMemcpyDeviceToDevice, stream));
-            B2R_CUDA(cudaMemcpyAsync(stage[1], src_depth, nb, cudaMemcpyDeviceToDevice, stream));
-            B2R_CUDA(cudaMemcpyAsync(stage[2], tgt_gray, nb, cudaMemcpyDeviceToDevice, stream));
-            B2R_CUDA(cudaMemcpyAsync(stage[3], tgt_depth, nb, cudaMemcpyDeviceToDevice, stream));
             B2R_CUDA(cudaGraphLaunch(G.exec, stream));
             launched = true;
         }
     }
-    if (!launched && !enqueue(stream, src_gray, src_depth, tgt_gray, tgt_depth)) { B2R_CHECK_LAUNCH(); return B2R_ERR_CUDA; }
-    OdoState h1;
-    B2R_CUDA(cudaMemcpyAsync(&h1, st, sizeof(h1), cudaMemcpyDeviceToHost, stream));
+    if (!launched && !enqueue(stream)) { B2R_CHECK_LAUNCH(); return B2R_ERR_CUDA; }
+    static thread_local std::vector<OdoState> h1;
+    h1.resize((size_t)B);
+    B2R_CUDA(cudaMemcpy2DAsync(h1.data(), sizeof(OdoState), st, stride, sizeof(OdoState), (size_t)B, cudaMemcpyDeviceToHost, stream));
     B2R_CUDA(cudaStreamSynchronize(stream));
-    bool ok = !h1.failed;
-    for (int i = 0; i < 16; i++) ok = ok && std::isfinite(h1.pose[i]);
-    if (ok) {
-        memcpy(out_T_host, h1.pose, sizeof(h1.pose));
-        memcpy(out_info_host, h1.info, sizeof(h1.info));
-        *success_host = 1;
-    } else {
-        b2r::m4_identity(out_T_host);
-        for (int i = 0; i < 36; i++) out_info_host[i] = (i % 7 == 0) ? 1.0 : 0.0;
-        *success_host = 0;
+    for (int p = 0; p < B; p++) {
+        bool ok = !h1[p].failed;
+        for (int i = 0; i < 16; i++) ok = ok && std::isfinite(h1[p].pose[i]);
+        if (ok) {
+            memcpy(out_T_host + 16 * p, h1[p].pose, sizeof(h1[p].pose));
+            memcpy(out_info_host + 36 * p, h1[p].info, sizeof(h1[p].info));
+            success_host[p] = 1;
+        } else {
+            b2r::m4_identity(out_T_host + 16 * p);
+            for (int i = 0; i < 36; i++) out_info_host[36 * p + i] = (i % 7 == 0) ? 1.0 : 0.0;
+            success_host[p] = 0;
+        }
     }
     return B2R_OK;
+}
+
+}  // namespace
+
+// compute_rgbd_odometry.  See include/b2recon.h.
+B2R_API int b2r_odometry(const float* src_gray, const float* src_depth, const float* tgt_gray, const float* tgt_depth, int W,
+                         int H, double fx, double fy, double cx, double cy, const double* init_host, int jac_kind,
+                         const int* iters_host, int n_levels, double depth_diff_max, double depth_min, double depth_max,
+                         double* out_T_host, double* out_info_host, int* success_host, cudaStream_t stream) {
+    if (!init_host) { b2r_set_error("b2r_odometry: bad argument"); return B2R_ERR_BAD_ARG; }
+    return odometry_impl(1, &src_gray, &src_depth, &tgt_gray, &tgt_depth, W, H, fx, fy, cx, cy, init_host, jac_kind, iters_host, n_levels,
+                         depth_diff_max, depth_min, depth_max, out_T_host, out_info_host, success_host, stream);
+}
+
+// n independent pairs (config 4: the consecutive frames of a sequence, odo_init = I each, RGBD_Odometry.py:26-35) through ONE
+// launch sequence: images = HOST arrays of n DEVICE pointers; init_host = n x 16 (NULL: identity for every pair); outputs n x 16,
+// n x 36, n.  Pair p's result is bit-identical to b2r_odometry on that pair alone.
+B2R_API int b2r_odometry_batch(int n, const float* const* src_gray, const float* const* src_depth, const float* const* tgt_gray,
+                               const float* const* tgt_depth, int W, int H, double fx, double fy, double cx, double cy,
+                               const double* init_host, int jac_kind, const int* iters_host, int n_levels, double depth_diff_max,
+                               double depth_min, double depth_max, double* out_T_host, double* out_info_host, int* success_host,
+                               cudaStream_t stream) {
+    if (n == 0) return B2R_OK;
+    return odometry_impl(n, src_gray, src_depth, tgt_gray, tgt_depth, W, H, fx, fy, cx, cy, init_host, jac_kind, iters_host, n_levels,
+                         depth_diff_max, depth_min, depth_max, out_T_host, out_info_host, success_host, stream);
 }
 
 // Building blocks exposed for the parity tests of the image kernels (not part of the reference-facing API).
 B2R_API int b2r_image_filter(const float* in, int W, int H, int kind, float* out, cudaStream_t stream) {
     if (!in || !out || kind < 0 || kind > 2) return B2R_ERR_BAD_ARG;
-    filter3_kernel<false><<<nblk(W * H), OD_THREADS, 0, stream>>>(in, out, W, H, kind, 0.f, 0.f);
+    filter3_kernel<false><<<nblk(W * H), OD_THREADS, 0, stream>>>(in, out, W, H, kind, 0.f, 0.f, 0);
     B2R_CHECK_LAUNCH();
     return B2R_OK;
 }
 B2R_API int b2r_image_downsample(const float* in, int W, int H, float* out, cudaStream_t stream) {
     if (!in || !out) return B2R_ERR_BAD_ARG;
-    downsample_kernel<<<nblk((W / 2) * (H / 2)), OD_THREADS, 0, stream>>>(in, out, W, H);
+    downsample_kernel<<<nblk((W / 2) * (H / 2)), OD_THREADS, 0, stream>>>(in, out, W, H, 0);
     B2R_CHECK_LAUNCH();
     return B2R_OK;
 }

@@ -76,3 +76,48 @@ def compute_rgbd_odometry(rgbd_source: RGBDImage, rgbd_target: RGBDImage,
                                   _lib.stream_ptr())
     _lib.check(rc, "compute_rgbd_odometry")
     return bool(ok.value), np.array(T[:], dtype=np.float64).reshape(4, 4), np.array(info[:], dtype=np.float64).reshape(6, 6)
+
+
+def compute_rgbd_odometry_batch(rgbd_sources, rgbd_targets, pinhole_camera_intrinsic: PinholeCameraIntrinsic = None, odo_inits=None,
+                                jacobian: RGBDOdometryJacobian = None, option: OdometryOption = None, max_batch: int = 32):
+    """Build extension: ``compute_rgbd_odometry`` over independent pairs (the reference loops over the consecutive frames of a
+    sequence with ``odo_init = I``, RGBD_Odometry.py:26-35) through one launch sequence per ``max_batch`` pairs
+    (b2r_odometry_batch).  Returns ``[(success, T, info)]``; every entry is bit-identical to the per-pair call."""
+    intr = pinhole_camera_intrinsic or PinholeCameraIntrinsic()
+    jacobian = jacobian or RGBDOdometryJacobianFromHybridTerm()
+    option = option or OdometryOption()
+    n = len(rgbd_sources)
+    if len(rgbd_targets) != n:
+        raise RuntimeError("[ComputeRGBDOdometry] Two RGBD pairs should be same in size.")
+    if n == 0:
+        return []
+    shp = tuple(rgbd_sources[0].color.tensor.shape)
+    imgs = [[], [], [], []]
+    for s_, t_ in zip(rgbd_sources, rgbd_targets):
+        four = [s_.color.tensor, s_.depth.tensor, t_.color.tensor, t_.depth.tensor]
+        for k, t in enumerate(four):
+            if t.dim() != 2 or t.dtype != torch.float32 or tuple(t.shape) != shp:
+                raise RuntimeError("[ComputeRGBDOdometry] Two RGBD pairs should be same in size.")
+            imgs[k].append(t.contiguous())
+    _lib.require_cuda()
+    H, W = shp
+    iters = list(option.iteration_number_per_pyramid_level)
+    it_arr = (C.c_int * len(iters))(*iters)
+    fx, fy, cx, cy = intr.fxfycxcy()
+    out = []
+    for a in range(0, n, max_batch):
+        b = min(n, a + max_batch)
+        m = b - a
+        ptrs = [(C.c_void_p * m)(*[t.data_ptr() for t in imgs[k][a:b]]) for k in range(4)]
+        init = None
+        if odo_inits is not None:
+            init = _lib.dbl16(np.stack([np.asarray(x, dtype=np.float64) for x in odo_inits[a:b]]))
+        T = (C.c_double * (16 * m))()
+        info = (C.c_double * (36 * m))()
+        ok = (C.c_int * m)()
+        rc = _lib.load().b2r_odometry_batch(m, ptrs[0], ptrs[1], ptrs[2], ptrs[3], W, H, fx, fy, cx, cy, init, int(jacobian.kind), it_arr,
+                                            len(iters), option.depth_diff_max, option.depth_min, option.depth_max, T, info, ok, _lib.stream_ptr())
+        _lib.check(rc, "compute_rgbd_odometry_batch")
+        Ta, Ia = np.array(T[:], dtype=np.float64).reshape(m, 4, 4), np.array(info[:], dtype=np.float64).reshape(m, 6, 6)
+        out += [(bool(ok[i]), Ta[i], Ia[i]) for i in range(m)]
+    return out

@@ -192,6 +192,14 @@ int b2r_odometry(const float* src_gray, const float* src_depth, const float* tgt
                  int H, double fx, double fy, double cx, double cy, const double* init_host, int jac_kind,
                  const int* iters_host, int n_levels, double depth_diff_max, double depth_min, double depth_max,
                  double* out_T_host, double* out_info_host, int* success_host, cudaStream_t stream);
+/* n independent pairs through ONE launch sequence (config 4: the consecutive frames of a sequence, odo_init = I each,
+ * RGBD_Odometry.py:26-35 / capture_frames.py:148-151 in a loop): images = HOST arrays of n DEVICE pointers; init_host = n x 16
+ * or NULL (identity); outputs n x 16, n x 36, n.  Pair p's result is bit-identical to b2r_odometry on that pair alone. */
+int b2r_odometry_batch(int n, const float* const* src_gray, const float* const* src_depth, const float* const* tgt_gray,
+                       const float* const* tgt_depth, int W, int H, double fx, double fy, double cx, double cy,
+                       const double* init_host, int jac_kind, const int* iters_host, int n_levels, double depth_diff_max,
+                       double depth_min, double depth_max, double* out_T_host, double* out_info_host, int* success_host,
+                       cudaStream_t stream);
 
 /* image building blocks of a12, exposed for parity tests (Image::Filter Gaussian3/Sobel3Dx/Sobel3Dy =
  * kind 0/1/2, Image::Downsample) */

@@ -559,6 +559,29 @@ def test_odometry_parity(o3r, frames, small_kinect, jac):
         o3d.pipelines.odometry.compute_rgbd_odometry(bad, mk(ct, dt), intrinsic_of(intr), I4, J, opt)
 
 
+def test_odometry_batched_equals_per_pair_and_oracle(o3r, frames, small_kinect):
+    """config 4: the consecutive frames of a sequence are independent pairs (odo_init = I): the batched entry runs them through
+    one launch sequence; every pair's result is bit-identical to the per-pair call (and so within 1e-6 of the oracle)."""
+    intr = small_kinect.depth_intr
+    mk = lambda c, d: o3d.geometry.RGBDImage.create_from_color_and_depth(o3d.geometry.Image(c), o3d.geometry.Image(d), 1000.0, 3.0, True)
+    imgs = [mk(c, d) for d, c, _ in frames[:6]]
+    J = o3d.pipelines.odometry.RGBDOdometryJacobianFromHybridTerm()
+    opt = o3d.pipelines.odometry.OdometryOption(iteration_number_per_pyramid_level=o3d.utility.IntVector([20, 10, 5]), max_depth_diff=0.03,
+                                                min_depth=0.0, max_depth=4.0)
+    single = [o3d.pipelines.odometry.compute_rgbd_odometry(imgs[i + 1], imgs[i], intrinsic_of(intr), I4, J, opt) for i in range(5)]
+    for mb in (5, 2):                                                          # one launch sequence, and chunks of 2 + 2 + 1
+        batched = o3d.pipelines.odometry.compute_rgbd_odometry_batch(imgs[1:], imgs[:-1], intrinsic_of(intr), None, J, opt, max_batch=mb)
+        assert len(batched) == 5
+        for (ok, T, info), (ok_b, T_b, info_b) in zip(single, batched):
+            assert ok and ok_b and np.array_equal(T, T_b) and np.array_equal(info, info_b)
+    inits = [np.eye(4)] * 5
+    again = o3d.pipelines.odometry.compute_rgbd_odometry_batch(imgs[1:], imgs[:-1], intrinsic_of(intr), inits, J, opt)
+    assert all(np.array_equal(a[1], b[1]) for a, b in zip(again, single))
+    (ds, cs, _), (dt, ct, _) = frames[3], frames[2]
+    ok_r, T_r, info_r, _ = o3r.odometry(o3r.rgb_to_intensity(cs), o3r.depth_to_float(ds), o3r.rgb_to_intensity(ct), o3r.depth_to_float(dt), K_of(intr), jac_kind=1)
+    assert np.abs(batched[2][1][:3, 3] - T_r[:3, 3]).max() <= 1e-6 and rot_angle(batched[2][1][:3, :3] @ T_r[:3, :3].T) <= 1e-6
+
+
 def test_icp_parity(o3r, frames, small_kinect):
     intr = small_kinect.depth_intr
     (ds, _, ps), (dt, _, pt) = frames[2], frames[0]
