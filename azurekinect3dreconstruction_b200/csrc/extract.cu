@@ -328,8 +328,12 @@ __device__ __forceinline__ int cube_case_bits(const uint32_t* nn, int z) {
 }
 
 // pass 1: per-voxel vertex slots (written only where a vertex is owned) + per-unit vertex / triangle counts
+// The classification of a unit -- everything the fill pass needs besides the few voxels that carry a vertex -- is 3.8 KB of bit
+// words: the count pass stores it (record of UBITS words per unit, in sorted-unit order) so that the fill pass does not stage
+// the unit's 47 KB apron a second time.  Layout: NEG[324] | VAL[324] | CC[289] | neighbour unit ids [27].
+#define UBITS 968
 __global__ void __launch_bounds__(256) mesh_count_kernel(const VolView V, const int32_t* order, uint32_t* vinfo,
-                                                         int32_t* unit_vcount, int32_t* unit_tcount) {
+                                                         int32_t* unit_vcount, int32_t* unit_tcount, uint32_t* ubits) {
     __shared__ float A[MD * MD * MD];
     __shared__ uint32_t NEG[MCOLS], VAL[MCOLS], CC[CCOLS];
     __shared__ int nb[27];
@@ -338,6 +342,12 @@ __global__ void __launch_bounds__(256) mesh_count_kernel(const VolView V, const 
     const int unit = order[pos];
     stage_apron<-1, false>(V, unit, A, nb);
     stage_bits(A, NEG, VAL, CC);
+    {
+        uint32_t* rec = ubits + (size_t)pos * UBITS;
+        for (int i = threadIdx.x; i < MCOLS; i += blockDim.x) { rec[i] = NEG[i]; rec[MCOLS + i] = VAL[i]; }
+        for (int i = threadIdx.x; i < CCOLS; i += blockDim.x) rec[2 * MCOLS + i] = CC[i];
+        if (threadIdx.x < 27) rec[2 * MCOLS + CCOLS + threadIdx.x] = (uint32_t)nb[threadIdx.x];
+    }
     const int x = threadIdx.x >> 4, y = threadIdx.x & 15;
     uint32_t m[3], act, nn[4];
     column_masks(NEG, VAL, CC, x, y, m, &act, nn);
@@ -370,18 +380,23 @@ __global__ void scatter_bases_kernel(const int32_t* order, const int32_t* scan, 
 __global__ void __launch_bounds__(256) mesh_fill_kernel(const VolView V, const int32_t* order, const uint32_t* vinfo,
                                                         const int32_t* vbase_by_unit, const int32_t* tbase,
                                                         double* vtx, double* vcol, int32_t* tri, int32_t* ids,
-                                                        int64_t capV, int64_t capF, int pos0, int64_t v0, int64_t t0, int vshift) {
-    __shared__ float A[MD * MD * MD];
+                                                        int64_t capV, int64_t capF, int pos0, int64_t v0, int64_t t0, int vshift,
+                                                        const uint32_t* ubits) {
     __shared__ uint32_t NEG[MCOLS], VAL[MCOLS], CC[CCOLS];
     __shared__ uint16_t vlist[FILL_CAP];       // x << 10 | y << 6 | z << 2 | axis
     __shared__ uint16_t clist[FILL_CAP];       // x << 8 | y << 4 | z
     __shared__ uint16_t ctoff[FILL_CAP];       // triangle offset of the cube inside the unit (< 5 * 4096)
     __shared__ int nb[27];
     __shared__ int ws[9];
-    const int pos = blockIdx.x + pos0;   // a sharded handle fills its own contiguous range of the (owner, key) order
+    const int pos = blockIdx.x + pos0;   // a slab handle fills its own contiguous range of the key order
     const int unit = order[pos];
-    stage_apron<-1, false>(V, unit, A, nb);
-    stage_bits(A, NEG, VAL, CC);
+    {
+        const uint32_t* rec = ubits + (size_t)pos * UBITS;       // the count pass's classification of this unit
+        for (int i = threadIdx.x; i < MCOLS; i += blockDim.x) { NEG[i] = rec[i]; VAL[i] = rec[MCOLS + i]; }
+        for (int i = threadIdx.x; i < CCOLS; i += blockDim.x) CC[i] = rec[2 * MCOLS + i];
+        if (threadIdx.x < 27) nb[threadIdx.x] = (int)rec[2 * MCOLS + CCOLS + threadIdx.x];
+    }
+    __syncthreads();
     const int x = threadIdx.x >> 4, y = threadIdx.x & 15;
     uint32_t m[3], act, nn[4];
     column_masks(NEG, VAL, CC, x, y, m, &act, nn);
@@ -412,7 +427,15 @@ __global__ void __launch_bounds__(256) mesh_fill_kernel(const VolView V, const i
             const int px = it >> 10, py = (it >> 6) & 15, pz = (it >> 2) & 15, a = it & 3;
             int n[3] = {px, py, pz};
             n[a] += 1;
-            const float f0f = apron_m(A, px, py, pz), f1f = apron_m(A, n[0], n[1], n[2]);
+            // the two end voxels of an owned edge are valid by construction: their TSDF is read where it lies
+            int ux = 1, uy = 1, uz = 1, lx = n[0], ly = n[1], lz = n[2];
+            if (lx >= 16) { lx -= 16; ux = 2; }
+            if (ly >= 16) { ly -= 16; uy = 2; }
+            if (lz >= 16) { lz -= 16; uz = 2; }
+            const int u1 = nb[(ux * 3 + uy) * 3 + uz];
+            const float* p0 = V.pool + (int64_t)unit * V.unit_stride + (px * 256 + py * 16 + pz);
+            const float* p1 = V.pool + (int64_t)u1 * V.unit_stride + (lx * 256 + ly * 16 + lz);
+            const float f0f = __ldg(p0), f1f = __ldg(p1);
             const double f0 = fabs((double)f0f), f1 = fabs((double)f1f);
             const int e[3] = {kx * 16 + px, ky * 16 + py, kz * 16 + pz};
             double pt[3];
@@ -422,13 +445,6 @@ __global__ void __launch_bounds__(256) mesh_fill_kernel(const VolView V, const i
             if (a == 0) pt[0] = xdadd(pt[0], step); else if (a == 1) pt[1] = xdadd(pt[1], step); else pt[2] = xdadd(pt[2], step);
             vtx[3 * o] = pt[0]; vtx[3 * o + 1] = pt[1]; vtx[3 * o + 2] = pt[2];
             if (vcol && V.planes == 5) {
-                int ux = 1, uy = 1, uz = 1, lx = n[0], ly = n[1], lz = n[2];
-                if (lx >= 16) { lx -= 16; ux = 2; }
-                if (ly >= 16) { ly -= 16; uy = 2; }
-                if (lz >= 16) { lz -= 16; uz = 2; }
-                const int u1 = nb[(ux * 3 + uy) * 3 + uz];
-                const float* p0 = V.pool + (int64_t)unit * V.unit_stride + (px * 256 + py * 16 + pz);
-                const float* p1 = V.pool + (int64_t)u1 * V.unit_stride + (lx * 256 + ly * 16 + lz);
 #pragma unroll
                 for (int c = 0; c < 3; c++) {
                     const double c0 = xddiv((double)p0[(2 + c) * B2R_UNIT_VOX], 255.0), c1 = xddiv((double)p1[(2 + c) * B2R_UNIT_VOX], 255.0);
@@ -506,6 +522,7 @@ struct Scratch {
     int32_t *id_in, *order;
     int32_t *cnt_a, *cnt_b, *scan_a, *scan_b, *vbase_by_unit;
     uint32_t* vinfo;
+    uint32_t* ubits;
     void* cub_tmp;
     size_t cub_bytes;
 };
@@ -526,8 +543,10 @@ int carve(b2r_tsdf* h, int n, bool mesh, Scratch* S) {
     const size_t o_ca = take((size_t)(n + 65) * 4), o_cb = take((size_t)(n + 1) * 4), o_sa = take((size_t)(n + 1) * 4), o_sb = take((size_t)(n + 1) * 4);
     const size_t o_vb = take((size_t)n * 4);
     const size_t o_cub = take(cub_bytes);
+    const size_t o_ub = mesh ? take((size_t)n * UBITS * 4) : 0;
     const size_t o_vi = mesh ? take((size_t)n * B2R_UNIT_VOX * 4) : 0;
     if (!mesh || h->scratch_bytes < total) h->mesh_gen = 0;   // the scratch is about to be reused / reallocated
+    if (h->scratch_bytes < total) h->sort_n = -1;             // ... and a reallocation loses the cached unit order too
     int rc = b2r_tsdf_ensure_scratch(h, total);
     if (rc != B2R_OK) return rc;
     char* b = (char*)h->scratch;
@@ -538,6 +557,7 @@ int carve(b2r_tsdf* h, int n, bool mesh, Scratch* S) {
     S->vbase_by_unit = (int32_t*)(b + o_vb);
     S->cub_tmp = b + o_cub; S->cub_bytes = cub_bytes;
     S->vinfo = mesh ? (uint32_t*)(b + o_vi) : nullptr;
+    S->ubits = mesh ? (uint32_t*)(b + o_ub) : nullptr;
     return B2R_OK;
 }
 
@@ -566,6 +586,10 @@ struct Slab { int use, kx_lo, kx_hi; };
 
 // Canonical unit order: by packed key (kx-major).
 int sorted_order(b2r_tsdf* h, int n, Scratch& S, cudaStream_t stream) {
+    // units are only ever appended between resets / imports: with the same unit count in the same epoch, the order (and the
+    // sorted keys) left in the scratch by the last extraction still hold -- the steady state of a scan sorts nothing
+    if (h->sort_n == n && h->sort_epoch == h->unit_epoch) return B2R_OK;
+    h->sort_n = n; h->sort_epoch = h->unit_epoch;
     pack_keys_kernel<<<(n + 255) / 256, 256, 0, stream>>>(h->unit_keys, n, S.k_in, S.id_in);
     B2R_CHECK_LAUNCH();
     size_t tmp = S.cub_bytes;
@@ -652,7 +676,7 @@ int extract_mesh_impl(b2r_tsdf* h, const Slab& sl, int64_t vertex_base, double* 
         // the count pass covers EVERY unit the handle holds: it fixes the vertex numbering (key order), which a cube needs for
         // edges owned by the neighbouring units above it -- for a slab handle those are the first ghost layer, whose own
         // neighbourhood is complete thanks to the second one (the counts of the outermost ghost layers are never used)
-        mesh_count_kernel<<<n, 256, 0, stream>>>(V, S.order, S.vinfo, S.cnt_a, S.cnt_b);
+        mesh_count_kernel<<<n, 256, 0, stream>>>(V, S.order, S.vinfo, S.cnt_a, S.cnt_b, S.ubits);
         B2R_CHECK_LAUNCH();
         B2R_CUDA(cudaMemsetAsync(S.cnt_a + n, 0, 4, stream));
         B2R_CUDA(cudaMemsetAsync(S.cnt_b + n, 0, 4, stream));
@@ -685,7 +709,7 @@ int extract_mesh_impl(b2r_tsdf* h, const Slab& sl, int64_t vertex_base, double* 
     const long long vshift = vertex_base - (long long)v01[0];
     if (vertex_base < 0 || vertex_base + (long long)tv > (long long)0x7fffffff) { b2r_set_error("extract_mesh: vertex ids exceed int32"); return B2R_ERR_RANGE; }
     mesh_fill_kernel<<<own[1] - own[0], 256, 0, stream>>>(V, S.order, S.vinfo, S.vbase_by_unit, S.scan_b, vtx, h->planes == 5 ? vcol : nullptr, tri, ids,
-                                                        capV, capF, own[0], (int64_t)v01[0], (int64_t)t01[0], (int)vshift);
+                                                        capV, capF, own[0], (int64_t)v01[0], (int64_t)t01[0], (int)vshift, S.ubits);
     B2R_CHECK_LAUNCH();
     return B2R_OK;
 }

@@ -831,6 +831,7 @@ B2R_API b2r_tsdf* b2r_tsdf_create(double voxel_length, double sdf_trunc, int col
     if (!h) return nullptr;
     memset(h, 0, sizeof(*h));
     h->generation = 1;   // mesh_gen == 0 never matches: the extraction cache starts invalid
+    h->sort_n = -1;
     h->voxel_length = voxel_length; h->sdf_trunc = sdf_trunc;
     h->unit_length = voxel_length * unit_resolution;
     h->color_type = color_type; h->res = unit_resolution; h->stride = depth_sampling_stride;
@@ -935,7 +936,7 @@ B2R_API int b2r_tsdf_reset(b2r_tsdf* h, cudaStream_t stream) {
     B2R_CHECK_LAUNCH();
     B2R_CUDA(cudaMemsetAsync(h->counters, 0, B2R_C_WORDS * 4, stream));
     h->q = 0; h->pending = 0; h->batches = 0;
-    h->generation++;
+    h->generation++; h->unit_epoch++;
     return B2R_OK;
 }
 
@@ -1443,7 +1444,7 @@ B2R_API int b2r_tsdf_import_units(b2r_tsdf* h, const int32_t* keys3, int64_t n, 
     B2RDeviceGuard g(h->device);
     int rc = b2r_tsdf_flush_pending(h, stream);
     if (rc != B2R_OK) return rc;
-    h->generation++;
+    h->generation++; h->unit_epoch++;
     rc = b2r_tsdf_ensure_scratch(h, (size_t)n * 4);
     if (rc != B2R_OK) return rc;
     int32_t* ids = (int32_t*)h->scratch;

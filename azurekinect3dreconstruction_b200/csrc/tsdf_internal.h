@@ -79,6 +79,8 @@ struct b2r_tsdf {
     // every change of the volume (integrate / reset / import); mesh_gen remembers for which generation the sorted
     // order, per-voxel vertex slots and scans in `scratch` are valid, so the second call only runs the fill pass.
     uint64_t generation, mesh_gen, mesh_slab;
+    uint64_t unit_epoch, sort_epoch;   // unit_epoch: bumped by reset / import (anything but appends that changes the unit set)
+    int sort_n;                        // unit count the sorted order in scratch was built for (-1: none)
     int mesh_n, mesh_own[2];
     int32_t mesh_v01[2], mesh_t01[2];
     // optional per-kernel timing (b2r_tsdf_profile): event pairs around every K1 / K2 launch

@@ -232,28 +232,35 @@ class ScalableTSDFVolume:
         return pcd
 
     def extract_triangle_mesh(self, with_ids: bool = False) -> TriangleMesh:
-        """ScalableTSDFVolume::ExtractTriangleMesh (SURVEY A.5)."""
+        """ScalableTSDFVolume::ExtractTriangleMesh (SURVEY A.5).  The output arrays are sized from the previous extraction of this
+        volume (+ 12 % slack), so a scan that extracts after every integrate (GoodColorReconstruction.py:270,285) makes ONE library
+        call per mesh; only when the mesh outgrew the guess is the call repeated with the exact sizes it reported."""
         dev = _lib.require_cuda()
         nV, nF = C.c_int64(0), C.c_int64(0)
-        rc = self._lib.b2r_tsdf_extract_mesh(self._h, None, None, None, None, 0, 0, C.byref(nV), C.byref(nF), _lib.stream_ptr())
-        if rc not in (_lib.OK, _lib.ERR_CAPACITY):
-            _lib.check(rc, "extract_triangle_mesh")
-        v, f = int(nV.value), int(nF.value)
+        has_c = self.color_type != TSDFVolumeColorType.NoColor
+        capV, capF = getattr(self, "_mesh_cap", (0, 0))
         mesh = TriangleMesh()
+        for attempt in range(2):
+            vtx = torch.empty((capV, 3), dtype=torch.float64, device=dev) if capV else None
+            vcol = torch.empty((capV, 3), dtype=torch.float64, device=dev) if (has_c and capV) else None
+            tri = torch.empty((max(capF, 1), 3), dtype=torch.int32, device=dev) if capV else None
+            ids = torch.empty((capV, 4), dtype=torch.int32, device=dev) if (with_ids and capV) else None
+            rc = self._lib.b2r_tsdf_extract_mesh(self._h, _lib.ptr(vtx), _lib.ptr(vcol), _lib.ptr(tri), _lib.ptr(ids), capV, max(capF, 1) if capV else 0,
+                                                 C.byref(nV), C.byref(nF), _lib.stream_ptr())
+            v, f = int(nV.value), int(nF.value)
+            if rc == _lib.ERR_CAPACITY and attempt == 0:
+                capV, capF = v, f                                   # exact sizes; the count pass is cached, the second call only fills
+                continue
+            _lib.check(rc, "extract_triangle_mesh")
+            break
+        self._mesh_cap = (v + v // 8 + 1024, f + f // 8 + 2048) if v else (0, 0)
         if v == 0:
             return mesh
-        vtx = torch.empty((v, 3), dtype=torch.float64, device=dev)
-        has_c = self.color_type != TSDFVolumeColorType.NoColor
-        vcol = torch.empty((v, 3), dtype=torch.float64, device=dev) if has_c else None
-        tri = torch.empty((max(f, 1), 3), dtype=torch.int32, device=dev)
-        ids = torch.empty((v, 4), dtype=torch.int32, device=dev) if with_ids else None
-        _lib.check(self._lib.b2r_tsdf_extract_mesh(self._h, _lib.ptr(vtx), _lib.ptr(vcol), _lib.ptr(tri), _lib.ptr(ids), v, max(f, 1),
-                                                    C.byref(nV), C.byref(nF), _lib.stream_ptr()), "extract_triangle_mesh")
-        mesh.vertices = Vector3dVector(vtx)
+        mesh.vertices = Vector3dVector(vtx[:v])
         if has_c:
-            mesh.vertex_colors = Vector3dVector(vcol)
+            mesh.vertex_colors = Vector3dVector(vcol[:v])
         mesh.triangles = Vector3iVector(tri[:f])
-        mesh.edge_ids = ids
+        mesh.edge_ids = ids[:v] if ids is not None else None
         return mesh
 
     def __repr__(self):
