@@ -1368,13 +1368,16 @@ B2R_API int b2r_tsdf_export_units(b2r_tsdf* h, int64_t first, int64_t count, flo
     return B2R_OK;
 }
 
-// one CTA per (selected unit, plane): a unit's planes are gathered out of the pool into export layout
+// one CTA per (selected unit, plane): a unit's planes are gathered out of the pool.  units != null: unit-major records
+// [n][planes][4096] (the pool's own layout -- what a slab handle receives straight into its pool); else the export layout.
 __global__ void tsdf_export_selected_kernel(const float* __restrict__ pool, int64_t unit_stride, int planes, const int32_t* __restrict__ unit_keys,
-                                            const int32_t* __restrict__ ids, int32_t* keys3, float* tsdf, float* weight, float* rgb) {
+                                            const int32_t* __restrict__ ids, int32_t* keys3, float* tsdf, float* weight, float* rgb, float* units) {
     const int u = blockIdx.x / planes, pl = blockIdx.x - u * planes;
     const int id = ids[u];
     if (pl == 0 && threadIdx.x < 3 && keys3) keys3[3 * u + threadIdx.x] = unit_keys[3 * id + threadIdx.x];
-    float* dst = pl == 0 ? tsdf + (int64_t)u * B2R_UNIT_VOX : (pl == 1 ? weight + (int64_t)u * B2R_UNIT_VOX : (rgb ? rgb + ((int64_t)u * 3 + (pl - 2)) * B2R_UNIT_VOX : nullptr));
+    float* dst;
+    if (units) dst = units + ((int64_t)u * planes + pl) * B2R_UNIT_VOX;
+    else dst = pl == 0 ? tsdf + (int64_t)u * B2R_UNIT_VOX : (pl == 1 ? weight + (int64_t)u * B2R_UNIT_VOX : (rgb ? rgb + ((int64_t)u * 3 + (pl - 2)) * B2R_UNIT_VOX : nullptr));
     if (!dst) return;
     const float4* src = reinterpret_cast<const float4*>(pool + (int64_t)id * unit_stride + (int64_t)pl * B2R_UNIT_VOX);
     float4* d4 = reinterpret_cast<float4*>(dst);
@@ -1382,7 +1385,7 @@ __global__ void tsdf_export_selected_kernel(const float* __restrict__ pool, int6
 }
 
 // Copies the units ids[0..n) (DEVICE int32 pool indices) out in export layout: keys3 [n][3], tsdf / weight [n][4096],
-// rgb [n][3][4096] (rgb may be null).  The multi-GPU extraction routes units to slab owners with it.
+// rgb [n][3][4096] (rgb may be null).
 B2R_API int b2r_tsdf_export_selected(b2r_tsdf* h, const int32_t* ids, int64_t n, int32_t* keys3, float* tsdf, float* weight, float* rgb,
                                      cudaStream_t stream) {
     if (!h || !ids || !tsdf || !weight || n < 0 || n > (1 << 26)) return B2R_ERR_BAD_ARG;
@@ -1391,7 +1394,62 @@ B2R_API int b2r_tsdf_export_selected(b2r_tsdf* h, const int32_t* ids, int64_t n,
     if (rc != B2R_OK) return rc;
     if (n == 0) return B2R_OK;
     tsdf_export_selected_kernel<<<(unsigned)(n * h->planes), 256, 0, stream>>>(h->pool, (int64_t)h->planes * B2R_UNIT_VOX, h->planes, h->unit_keys, ids,
-                                                                             keys3, tsdf, weight, h->planes == 5 ? rgb : nullptr);
+                                                                             keys3, tsdf, weight, h->planes == 5 ? rgb : nullptr, nullptr);
+    B2R_CHECK_LAUNCH();
+    return B2R_OK;
+}
+
+// The same units as pool-layout records: units [n][planes * 4096] floats.  The multi-GPU extraction routes units to slab
+// ranks with it; the receiver lets the collective write them straight into its pool (b2r_tsdf_pool, b2r_tsdf_adopt_units).
+B2R_API int b2r_tsdf_export_records(b2r_tsdf* h, const int32_t* ids, int64_t n, int32_t* keys3, float* units, cudaStream_t stream) {
+    if (!h || !ids || !units || !keys3 || n < 0 || n > (1 << 26)) return B2R_ERR_BAD_ARG;
+    B2RDeviceGuard g(h->device);
+    int rc = b2r_tsdf_flush_pending(h, stream);
+    if (rc != B2R_OK) return rc;
+    if (n == 0) return B2R_OK;
+    tsdf_export_selected_kernel<<<(unsigned)(n * h->planes), 256, 0, stream>>>(h->pool, (int64_t)h->planes * B2R_UNIT_VOX, h->planes, h->unit_keys, ids,
+                                                                             keys3, nullptr, nullptr, nullptr, units);
+    B2R_CHECK_LAUNCH();
+    return B2R_OK;
+}
+
+// DEVICE address of the unit pool ([capacity][planes][4096] floats) and the floats per unit: a collective may deposit unit
+// records directly behind the units the handle already holds.
+B2R_API float* b2r_tsdf_pool(b2r_tsdf* h, int64_t* floats_per_unit) {
+    if (!h) return nullptr;
+    if (floats_per_unit) *floats_per_unit = (int64_t)h->planes * B2R_UNIT_VOX;
+    return h->pool;
+}
+
+__global__ void tsdf_adopt_keys_kernel(B2RHash hash, int32_t* unit_keys, int32_t* counters, const int32_t* keys3, int n, int base) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int kx = keys3[3 * i], ky = keys3[3 * i + 1], kz = keys3[3 * i + 2];
+    const int id = base + i;
+    unit_keys[3 * id] = kx; unit_keys[3 * id + 1] = ky; unit_keys[3 * id + 2] = kz;
+    if (i == 0) counters[B2R_C_NUM_UNITS] = base + n;
+    if (!b2r_key_in_range(kx, ky, kz)) { atomicOr(&counters[B2R_C_ERR], 2); return; }
+    const uint64_t key = b2r_pack_key(kx, ky, kz);
+    uint32_t s = (uint32_t)b2r_mix64(key) & hash.mask;
+    for (uint32_t probe = 0; probe <= hash.mask; probe++) {
+        unsigned long long k = atomicCAS((unsigned long long*)&hash.slots[s].key, (unsigned long long)B2R_KEY_EMPTY, (unsigned long long)key);
+        if (k == B2R_KEY_EMPTY) { hash.slots[s].val = id; return; }
+        if (k == key) { atomicOr(&counters[B2R_C_ERR], 8); return; }   // duplicate
+        s = (s + 1) & hash.mask;
+    }
+    atomicOr(&counters[B2R_C_ERR], 4);
+}
+
+// Registers n units whose records already lie in the pool at indices [first, first + n) (written there by the caller, e.g. as
+// the receive buffer of an all-to-all): keys3 = DEVICE int32 [n][3].  `first` must equal the handle's current unit count.
+B2R_API int b2r_tsdf_adopt_units(b2r_tsdf* h, const int32_t* keys3, int64_t first, int64_t n, cudaStream_t stream) {
+    if (!h || !keys3 || n < 0 || first < 0 || first + n > h->cap_units) return B2R_ERR_BAD_ARG;
+    if (n == 0) return B2R_OK;
+    B2RDeviceGuard g(h->device);
+    int rc = b2r_tsdf_flush_pending(h, stream);
+    if (rc != B2R_OK) return rc;
+    h->generation++; h->unit_epoch++;
+    tsdf_adopt_keys_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(h->hash, h->unit_keys, h->counters, keys3, (int)n, (int)first);
     B2R_CHECK_LAUNCH();
     return B2R_OK;
 }

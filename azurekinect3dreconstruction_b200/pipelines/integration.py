@@ -193,6 +193,37 @@ class ScalableTSDFVolume:
                                                           _lib.stream_ptr()), "export_selected")
         return keys, tsdf, wgt, rgb
 
+    def export_records(self, ids: torch.Tensor):
+        """Units by pool index as pool-layout records: (keys (n,3) i32, units (n, planes * 4096) f32)."""
+        dev = _lib.require_cuda()
+        ids = ids.to(dev, dtype=torch.int32).contiguous()
+        n = int(ids.shape[0])
+        keys = torch.empty((n, 3), dtype=torch.int32, device=dev)
+        units = torch.empty((n, self.unit_floats()), dtype=torch.float32, device=dev)
+        if n:
+            _lib.check(self._lib.b2r_tsdf_export_records(self._h, _lib.ptr(ids), n, _lib.ptr(keys), _lib.ptr(units), _lib.stream_ptr()), "export_records")
+        return keys, units
+
+    def unit_floats(self) -> int:
+        return (2 if self.color_type == TSDFVolumeColorType.NoColor else 5) * 4096
+
+    def pool_view(self) -> torch.Tensor:
+        """The handle's unit pool as a (capacity, planes * 4096) f32 tensor sharing its memory (no copy): a collective can write unit
+        records straight behind the units the handle holds; ``adopt_units`` then registers them."""
+        fpu = C.c_int64(0)
+        ptr = self._lib.b2r_tsdf_pool(self._h, C.byref(fpu))
+        cap = self.capacity()
+
+        class _Pool:
+            __cuda_array_interface__ = {"shape": (cap, int(fpu.value)), "typestr": "<f4", "data": (int(ptr), False), "version": 2, "strides": None}
+        t = torch.as_tensor(_Pool(), device=_lib.require_cuda())
+        t._b2r_owner = self            # the view must not outlive the handle
+        return t
+
+    def adopt_units(self, keys: torch.Tensor, first: int) -> None:
+        keys = keys.to(_lib.require_cuda(), dtype=torch.int32).contiguous()
+        _lib.check(self._lib.b2r_tsdf_adopt_units(self._h, _lib.ptr(keys), int(first), int(keys.shape[0]), _lib.stream_ptr()), "adopt_units")
+
     def import_units(self, keys, tsdf, weight, rgb=None, sync: bool = True) -> None:
         dev = _lib.require_cuda()
         keys = (keys if torch.is_tensor(keys) else torch.as_tensor(np.asarray(keys))).to(dev, dtype=torch.int32).contiguous()

@@ -75,35 +75,50 @@ class Comm:
         self.dist.all_gather(out, pad, group=self.group)
         return [o[:c] for o, c in zip(out, counts)]
 
-    def all_to_all_v(self, parts: List[torch.Tensor]) -> List[torch.Tensor]:
-        """parts[d] goes to rank d (rows may differ per destination); returns what every rank sent here, by source rank."""
-        dev, tail, dt = parts[0].device, tuple(parts[0].shape[1:]), parts[0].dtype
-        mine = torch.tensor([int(p.shape[0]) for p in parts], dtype=torch.int64, device=dev)
+    def recv_counts(self, parts: List[torch.Tensor]) -> List[int]:
+        """Rows every source rank is about to send here in an all_to_all_v of `parts`."""
+        mine = torch.tensor([int(p.shape[0]) for p in parts], dtype=torch.int64, device=parts[0].device)
         rows = [torch.zeros_like(mine) for _ in range(self.world)]
         self.dist.all_gather(rows, mine, group=self.group)
-        recv = [int(rows[src][self.rank].item()) for src in range(self.world)]
-        out = [torch.empty((c,) + tail, dtype=dt, device=dev) for c in recv]
+        m = torch.stack(rows).cpu()
+        return [int(m[src][self.rank]) for src in range(self.world)]
+
+    def all_to_all_v(self, parts: List[torch.Tensor], recv: Optional[List[int]] = None, out: Optional[List[torch.Tensor]] = None) -> List[torch.Tensor]:
+        """parts[d] goes to rank d (rows may differ per destination); returns what every rank sent here, by source rank.
+        `recv` (from recv_counts) saves the count exchange; `out` = caller-owned receive tensors (e.g. views of a unit pool)."""
+        dev, tail, dt = parts[0].device, tuple(parts[0].shape[1:]), parts[0].dtype
+        if recv is None:
+            recv = self.recv_counts(parts)
+        if out is None:
+            out = [torch.empty((c,) + tail, dtype=dt, device=dev) for c in recv]
         if self.nccl:
             self.dist.all_to_all(out, [p.contiguous() for p in parts], group=self.group)
             return out
         for d in range(self.world):            # gloo has no all-to-all: one ragged gather per destination (CPU tests only)
             got = self.all_gather_v(parts[d])
             if d == self.rank:
-                out = got
+                for o, g_ in zip(out, got):
+                    o.copy_(g_)
         return out
 
-    def gather_v(self, t: torch.Tensor, dst: int = 0) -> Optional[List[torch.Tensor]]:
-        """Ragged gather to one rank (grouped send / recv on NCCL); None on the other ranks."""
-        n = torch.tensor([t.shape[0]], dtype=torch.int64, device=t.device)
-        counts = [torch.zeros_like(n) for _ in range(self.world)]
-        self.dist.all_gather(counts, n, group=self.group)
-        counts = [int(c.item()) for c in counts]
+    def gather_v(self, t: torch.Tensor, dst: int = 0, counts: Optional[List[int]] = None) -> Optional[List[torch.Tensor]]:
+        """Ragged gather to one rank (grouped send / recv on NCCL); None on the other ranks.  On `dst` the parts are consecutive
+        row ranges of ONE tensor (the concatenation needs no further copy: ``torch.cat`` of views of one buffer is avoided by
+        ``merge_*_parts`` through ``_whole``)."""
+        if counts is None:
+            n = torch.tensor([t.shape[0]], dtype=torch.int64, device=t.device)
+            cl = [torch.zeros_like(n) for _ in range(self.world)]
+            self.dist.all_gather(cl, n, group=self.group)
+            counts = [int(c) for c in torch.cat(cl).cpu()]
         if not self.nccl:
             got = self.all_gather_v(t)
             return got if self.rank == dst else None
         if self.rank == dst:
-            out = [torch.empty((c,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device) for c in counts]
-            out[dst] = t
+            whole = torch.empty((sum(counts),) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+            offs = np.concatenate([[0], np.cumsum(counts)])
+            out = [whole[int(offs[r]):int(offs[r + 1])] for r in range(self.world)]
+            out[dst].copy_(t)
+            out[0]._b2r_whole = whole
             ops = [self.dist.P2POp(self.dist.irecv, out[r], r, self.group) for r in range(self.world) if r != dst and counts[r] > 0]
         else:
             out = None
@@ -176,36 +191,43 @@ class SlabExtractor:
         self.keys = self.vol.unit_keys()
         return self.keys[:, 0].contiguous()
 
-    # phase 2 (local): route my units -> all_to_all_v of each of the returned lists
+    # phase 2 (local): route my units -> per destination (keys, pool-layout records); exchanged by all_to_all_v
     def export_routes(self, gathered_kx: List[torch.Tensor]):
         all_kx = torch.cat([g.reshape(-1) for g in gathered_kx]).cpu().numpy() if gathered_kx else np.zeros((0,), np.int32)
         self.slabs = slab_cuts(all_kx, self.world)
         self.range = self.slabs[self.rank]
         routes = slab_routes(self.keys[:, 0].cpu().numpy(), self.slabs)
         dev = _lib.require_cuda()
-        has_c = self.vol.color_type != TSDFVolumeColorType.NoColor
-        K, T, W, R = [], [], [], []
+        K, U = [], []
         for ids in routes:
-            k, t, w, c = self.vol.export_selected(torch.as_tensor(ids, device=dev))
-            K.append(k); T.append(t); W.append(w); R.append(c)
-        return [K, T, W] + ([R] if has_c else [])
+            k, u = self.vol.export_records(torch.as_tensor(ids, device=dev))
+            K.append(k); U.append(u)
+        return [K, U]
 
-    # phase 3 (local): import what arrived, size my part -> all_gather_v of the returned (1, 2) counts
-    def import_and_size(self, recv):
+    # phase 3a (local, after the counts are known): make room; returns the receive tensors for the unit records -- views of the
+    # slab handle's own pool, so the collective deposits the units where they will live
+    def receive_buffers(self, recv_counts: List[int]):
+        total = int(sum(recv_counts))
         has_c = self.vol.color_type != TSDFVolumeColorType.NoColor
-        K, T, W = recv[:3]
-        R = recv[3] if has_c else [None] * len(K)
-        total = sum(int(k.shape[0]) for k in K)
         if self.slab is None or self.slab.capacity() < total:
             self.slab = None
+            self._pool = None
             self.slab = ScalableTSDFVolume(self.vol.voxel_length, self.vol.sdf_trunc, self.vol.color_type, capacity_units=max(int(total * 1.25), 64) + 16)
+            self._pool = self.slab.pool_view()
         else:
             self.slab.reset()
-        for k, t, w, c in zip(K, T, W, R):
-            if k.shape[0]:
-                self.slab.import_units(k, t, w, c if has_c else None, sync=False)
         self.units_held = total
         self.scratch_bytes = self.slab.capacity() * (5 if has_c else 2) * 4096 * 4
+        offs = np.concatenate([[0], np.cumsum(recv_counts)]).astype(np.int64)
+        return [self._pool[int(offs[r]):int(offs[r + 1])] for r in range(len(recv_counts))]
+
+    # phase 3b (local): register what arrived, size my part -> all_gather_v of the returned (1, 2) counts
+    def adopt_and_size(self, recv_keys: List[torch.Tensor]):
+        first = 0
+        for k in recv_keys:
+            if k.shape[0]:
+                self.slab.adopt_units(k, first)
+                first += int(k.shape[0])
         lib, dev = _lib.load(), _lib.require_cuda()
         nV, nF = C.c_int64(0), C.c_int64(0)
         lo, hi = self.range
@@ -251,29 +273,35 @@ class SlabExtractor:
         return [xyz, nrm] + ([rgb] if has_c else [])
 
 
+def _whole(part_list: List[torch.Tensor]) -> torch.Tensor:
+    """Rank-order concatenation of a gathered part list; gather_v hands out views of one buffer, which then IS the result."""
+    w = getattr(part_list[0], "_b2r_whole", None) if part_list else None
+    return w if w is not None else torch.cat(part_list)
+
+
 def merge_mesh_parts(parts: List[List[torch.Tensor]]) -> TriangleMesh:
     """parts[i] = list over ranks of tensor i of SlabExtractor.fill_mesh.  Triangle ids are already global and the
     global vertex order is slab-major, so the mesh is the plain rank-order concatenation."""
     mesh = TriangleMesh()
-    vtx, tri = torch.cat(parts[0]), torch.cat(parts[1])
+    vtx, tri = _whole(parts[0]), _whole(parts[1])
     if vtx.shape[0] == 0:
         return mesh
     mesh.vertices = Vector3dVector(vtx)
     mesh.triangles = Vector3iVector(tri)
     if len(parts) > 2:
-        mesh.vertex_colors = Vector3dVector(torch.cat(parts[2]))
+        mesh.vertex_colors = Vector3dVector(_whole(parts[2]))
     return mesh
 
 
 def merge_point_parts(parts: List[List[torch.Tensor]]) -> PointCloud:
     pcd = PointCloud()
-    pts = torch.cat(parts[0])
+    pts = _whole(parts[0])
     if pts.shape[0] == 0:
         return pcd
     pcd.points = Vector3dVector(pts)
-    pcd.normals = Vector3dVector(torch.cat(parts[1]))
+    pcd.normals = Vector3dVector(_whole(parts[1]))
     if len(parts) > 2:
-        pcd.colors = Vector3dVector(torch.cat(parts[2]))
+        pcd.colors = Vector3dVector(_whole(parts[2]))
     return pcd
 
 
@@ -315,12 +343,15 @@ class ShardedTSDFVolume:
         t = time.perf_counter()
         kx = c.all_gather_v(ex.unit_kx())
         t = self._tick("1_gather_kx", t)
-        routes = ex.export_routes(kx)
+        K, U = ex.export_routes(kx)
         t = self._tick("2_route_export", t)
-        recv = [c.all_to_all_v(lst) for lst in routes]
+        recv = c.recv_counts(K)
+        bufs = ex.receive_buffers(recv)
+        keys = c.all_to_all_v(K, recv)
+        c.all_to_all_v(U, recv, bufs)                 # unit records land in the slab handle's pool
         t = self._tick("3_all_to_all_units", t)
-        counts = ex.import_and_size(recv)
-        t = self._tick("4_import_count_pass", t)
+        counts = ex.adopt_and_size(keys)
+        t = self._tick("4_adopt_count_pass", t)
         self.last_extract_scratch_bytes, self.last_extract_units_held = ex.scratch_bytes, ex.units_held
         return counts
 

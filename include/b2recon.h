@@ -176,9 +176,14 @@ int b2r_tsdf_extract_mesh_slab(b2r_tsdf* h, int kx_lo, int kx_hi, int64_t vertex
                                int32_t* ids4, int64_t capV, int64_t capF, int64_t* nV_host, int64_t* nF_host, cudaStream_t stream);
 int b2r_tsdf_extract_points_slab(b2r_tsdf* h, int kx_lo, int kx_hi, double* xyz, double* rgb, double* nrm, int32_t* ids4,
                                  int64_t capacity, int64_t* count_host, cudaStream_t stream);
-/* units ids[0..n) (DEVICE pool indices) in export layout (keys3 may be NULL): routes units to their slab ranks */
+/* units ids[0..n) (DEVICE pool indices) in export layout (keys3 may be NULL) */
 int b2r_tsdf_export_selected(b2r_tsdf* h, const int32_t* ids, int64_t n, int32_t* keys3, float* tsdf, float* weight, float* rgb,
                              cudaStream_t stream);
+/* the same units as pool-layout records [n][planes * 4096] floats: what the re-partition sends; the receiver lets the
+ * all-to-all deposit them straight into its pool (b2r_tsdf_pool) and registers them with b2r_tsdf_adopt_units */
+int b2r_tsdf_export_records(b2r_tsdf* h, const int32_t* ids, int64_t n, int32_t* keys3, float* units, cudaStream_t stream);
+float* b2r_tsdf_pool(b2r_tsdf* h, int64_t* floats_per_unit);
+int b2r_tsdf_adopt_units(b2r_tsdf* h, const int32_t* keys3, int64_t first, int64_t n, cudaStream_t stream);
 /* mesh.compute_vertex_normals()  (GoodColorReconstruction.py:286) */
 int b2r_mesh_vertex_normals(const double* vtx, int64_t nV, const int32_t* tri, int64_t nF, double* out,
                             cudaStream_t stream);

@@ -413,9 +413,13 @@ def test_sharded_extraction_equals_single(o3r, frames, small_kinect, world):
     LC = sharded.LocalComm
     exs = [sharded.SlabExtractor(v, r, world) for r, v in enumerate(vols)]
     kx = LC.all_gather_v([e.unit_kx() for e in exs])                                   # collective 1
-    routes = [e.export_routes(kx) for e in exs]                                       # local
-    recv = [LC.all_to_all_v([routes[r][i] for r in range(world)]) for i in range(len(routes[0]))]   # collective 2 (per tensor kind)
-    counts = LC.all_gather_v([e.import_and_size([recv[i][r] for i in range(len(recv))]) for r, e in enumerate(exs)])   # local + collective 3
+    routes = [e.export_routes(kx) for e in exs]                                       # local: per destination (keys, unit records)
+    keys = LC.all_to_all_v([routes[r][0] for r in range(world)])                      # collective 2
+    units = LC.all_to_all_v([routes[r][1] for r in range(world)])
+    for r, e in enumerate(exs):
+        for buf, u in zip(e.receive_buffers([int(k.shape[0]) for k in keys[r]]), units[r]):
+            buf.copy_(u)                                                                # (the real all-to-all writes into these pool views)
+    counts = LC.all_gather_v([e.adopt_and_size(keys[r]) for r, e in enumerate(exs)])    # local + collective 3
     total_units = single.num_units()
     assert sum(e.units_held for e in exs) < 2.5 * total_units and (world < 3 or max(e.units_held for e in exs) < total_units)
     # ---- mesh
