@@ -228,10 +228,13 @@ def config5_record(dev, rank, world, ticks=64, n_streams=8, ticks_per_batch=4):
         return vol.extract_triangle_mesh() if vol is not None else local.extract_triangle_mesh()
     mesh = extract()
     barrier()
-    t0 = time.perf_counter()
-    mesh = extract()
-    barrier()
-    t_mesh = red(time.perf_counter() - t0, "max")
+    runs = []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        mesh = extract()
+        barrier()
+        runs.append(red(time.perf_counter() - t0, "max"))
+    t_mesh = min(runs)
     phases = None
     if vol is not None:                                    # one more extraction with a device sync after every phase: where the time goes
         vol.timing = {}
@@ -249,7 +252,7 @@ def config5_record(dev, rank, world, ticks=64, n_streams=8, ticks_per_batch=4):
            "nvlink_gathered_bytes_per_rank_per_step": ex.bytes_gathered // 2 if world > 1 else 0,
            "units_total": units, "updated_voxels_total": upd, "algorithmic_bytes_per_step": algo,
            "achieved_aggregate": algo / (ms * 1e-3) / 1e9, "unit": "GB/s",
-           "mesh_gather_s": t_mesh, "mesh_phases_ms_rank0": phases, "vertices": len(mesh.vertices), "triangles": len(mesh.triangles),
+           "mesh_gather_s": t_mesh, "mesh_gather_s_runs": runs, "mesh_phases_ms_rank0": phases, "vertices": len(mesh.vertices), "triangles": len(mesh.triangles),
            "extraction_scratch_bytes_rank0": getattr(vol, "last_extract_scratch_bytes", None) if vol is not None else None,
            "render_s": render_s}
     del packed, local, vol, ex
