@@ -129,6 +129,30 @@ class Comm:
         return out
 
 
+def _gather_v_multi(comm: "Comm", tensors: List[torch.Tensor], counts: List[List[int]], dst: int = 0):
+    """Several ragged gathers to one rank as ONE grouped send / recv (row counts per rank already known: no count exchange,
+    no host sync).  Returns [list over ranks of views of one preallocated tensor] per input on `dst`, None elsewhere."""
+    if not comm.nccl:
+        got = [comm.all_gather_v(t) for t in tensors]
+        return got if comm.rank == dst else None
+    ops, outs = [], []
+    for t, cnt in zip(tensors, counts):
+        if comm.rank == dst:
+            whole = torch.empty((int(sum(cnt)),) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+            offs = np.concatenate([[0], np.cumsum(cnt)]).astype(np.int64)
+            views = [whole[int(offs[r]):int(offs[r + 1])] for r in range(comm.world)]
+            views[dst].copy_(t)
+            views[0]._b2r_whole = whole
+            ops += [comm.dist.P2POp(comm.dist.irecv, views[r], r, comm.group) for r in range(comm.world) if r != dst and cnt[r] > 0]
+            outs.append(views)
+        elif cnt[comm.rank] > 0:
+            ops.append(comm.dist.P2POp(comm.dist.isend, t.contiguous(), dst, comm.group))
+    if ops:
+        for w in comm.dist.batch_isend_irecv(ops):
+            w.wait()
+    return outs if comm.rank == dst else None
+
+
 class LocalComm:
     """In-process stand-in used to emulate `world` ranks on one GPU (tests): the caller runs a phase for every
     rank, then hands the per-rank results to the matching static exchange, which returns what the collective would."""
@@ -355,19 +379,24 @@ class ShardedTSDFVolume:
         self.last_extract_scratch_bytes, self.last_extract_units_held = ex.scratch_bytes, ex.units_held
         return counts
 
-    def _collect(self, tensors, gather):
+    def _collect(self, tensors, gather, counts=None):
         if gather == "all":
             return [self.comm.all_gather_v(t) for t in tensors]
-        got = [self.comm.gather_v(t, 0) for t in tensors]
-        return got if self.comm.rank == 0 else None
+        if counts is None:
+            got = [self.comm.gather_v(t, 0) for t in tensors]
+            return got if self.comm.rank == 0 else None
+        return _gather_v_multi(self.comm, tensors, counts, 0)
 
     def extract_triangle_mesh(self, gather: str = "rank0") -> TriangleMesh:
         import time
         counts = self._repartition()
         t = time.perf_counter()
-        part = self._ex.fill_mesh(self.comm.all_gather_v(counts))
+        all_counts = self.comm.all_gather_v(counts)
+        part = self._ex.fill_mesh(all_counts)
         t = self._tick("5_fill", t)
-        parts = self._collect(part, gather)
+        vf = torch.cat(all_counts).cpu().numpy().reshape(-1, 2)
+        nv, nf = [int(x) for x in vf[:, 0]], [int(x) for x in vf[:, 1]]
+        parts = self._collect(part, gather, [nv, nf] + ([nv] if len(part) > 2 else []))
         t = self._tick("6_gather_parts", t)
         mesh = merge_mesh_parts(parts) if parts is not None else TriangleMesh()
         self._tick("7_concat", t)
