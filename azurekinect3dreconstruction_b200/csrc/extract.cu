@@ -151,7 +151,7 @@ __device__ double tsdf_at(const VolView& V, double px, double py, double pz) {
 // ------------------------------------------------------------------------------------------------
 #define POINTS_CAP 2048
 template <bool FILL>
-__global__ void __launch_bounds__(256) extract_points_kernel(const VolView V, const int32_t* order, int32_t* unit_counts,
+__global__ void __launch_bounds__(256, 4) extract_points_kernel(const VolView V, const int32_t* order, int32_t* unit_counts,
                                                              const int32_t* unit_offsets, double* xyz, double* rgb,
                                                              double* nrm, int32_t* ids, int64_t capacity) {
     constexpr int D = 17;
@@ -377,7 +377,7 @@ __global__ void scatter_bases_kernel(const int32_t* order, const int32_t* scan, 
 // work lists (block scans give every item its slot = its output rank), then consecutive threads process consecutive
 // items: full warps on the f64 interpolation instead of one or two live lanes per warp, and consecutive output rows.
 #define FILL_CAP 2048          // items per round (a unit holds at most 3 * 4096 vertices / 4096 cubes: processed in rounds)
-__global__ void __launch_bounds__(256) mesh_fill_kernel(const VolView V, const int32_t* order, const uint32_t* vinfo,
+__global__ void __launch_bounds__(256, 4) mesh_fill_kernel(const VolView V, const int32_t* order, const uint32_t* vinfo,
                                                         const int32_t* vbase_by_unit, const int32_t* tbase,
                                                         double* vtx, double* vcol, int32_t* tri, int32_t* ids,
                                                         int64_t capV, int64_t capF, int pos0, int64_t v0, int64_t t0, int vshift,
