@@ -68,6 +68,7 @@ SIGNATURES = {
     "b2r_tsdf_pool": (_vp, [_vp, _pi64]),
     "b2r_tsdf_adopt_units": (_i, [_vp, _vp, _i64, _i64, _vp]),
     "b2r_mesh_vertex_normals": (_i, [_vp, _i64, _vp, _i64, _vp, _vp]),
+    "b2r_mesh_vertex_normals_noalloc": (_i, [_vp, _i64, _vp, _i64, _vp, _vp]),
     "b2r_odometry": (_i, [_vp, _vp, _vp, _vp, _i, _i, _d, _d, _d, _d, _pd, _i, _pi, _i, _d, _d, _d, _pd, _pd, _pi, _vp]),
     "b2r_odometry_batch": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _d, _d, _d, _d, _pd, _i, _pi, _i, _d, _d, _d, _pd, _pd, _pi, _vp]),
     "b2r_image_filter": (_i, [_vp, _i, _i, _i, _vp, _vp]),

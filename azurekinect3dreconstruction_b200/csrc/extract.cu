@@ -15,6 +15,7 @@
 //   * compaction = per-thread popc over a z column + block scan (warp shuffles).
 #include "tsdf_internal.h"
 #include <cub/cub.cuh>
+#include <mutex>
 
 #define MC_TABLE_QUAL __device__ __constant__ const
 #include "mc_tables.h"
@@ -817,5 +818,128 @@ B2R_API int b2r_mesh_vertex_normals(const double* vtx, int64_t nV, const int32_t
     }
     cudaFreeAsync(buf, stream);
     if (e != cudaSuccess) { b2r_set_error("b2r_mesh_vertex_normals: %s", cudaGetErrorString(e)); return B2R_ERR_CUDA; }
+    return B2R_OK;
+}
+
+// ---- compute_vertex_normals without any allocation ------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as b2r_mesh_vertex_normals -- the
+// per-vertex sums run in ascending triangle order -- but the scratch (per-vertex incidence lists in CSR form) lives in a
+// file-scope device array of fixed size instead of a stream-ordered allocation, and no library routine is called:
+//   zero the counts -> count corners per vertex -> one-CTA exclusive scan -> fill the lists (atomic cursor; order arbitrary)
+//   -> one thread per vertex sorts its (short) list ascending and adds the un-normalised triangle normals in that order.
+// Limits: B2R_NOALLOC_MAX_VERTICES vertices, B2R_NOALLOC_MAX_TRIANGLES triangles (8.4 MB of scratch, held by every GPU that
+// loads the library until the process exits).  Every call on a device shares the array, which keeps the last call's contents:
+// the counts are cleared at the start of each call; calls that overlap on the GPU (two streams) race on it.
+#define B2R_NOALLOC_MAX_VERTICES 262144
+#define B2R_NOALLOC_MAX_TRIANGLES 524288
+namespace {
+struct NoAllocScratch {
+    int32_t offsets[B2R_NOALLOC_MAX_VERTICES + 1];   // corner counts, then their exclusive scan
+    int32_t cursor[B2R_NOALLOC_MAX_VERTICES + 1];
+    int32_t incident[3 * B2R_NOALLOC_MAX_TRIANGLES]; // triangle ids, grouped by vertex
+};
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];
+
+__global__ void na_zero_kernel(int32_t* p, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = 0;
+}
+__global__ void na_count_kernel(const int32_t* __restrict__ tri, int64_t n3, int nV, int32_t* counts) {
+    const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n3) return;
+    const int v = tri[c];
+    if (v >= 0 && v < nV) atomicAdd(&counts[v], 1);
+}
+// exclusive scan of counts[0 .. n] in place by ONE CTA of 1024 threads (n <= 262 145: 257 elements per thread); cursor = copy
+__global__ void __launch_bounds__(1024) na_scan_kernel(int32_t* counts, int32_t* cursor, int n) {
+    __shared__ int part[1024];
+    const int per = (n + 1023) / 1024;
+    const int lo = min(n, (int)threadIdx.x * per), hi = min(n, lo + per);
+    int s = 0;
+    for (int i = lo; i < hi; i++) s += counts[i];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        const int v = threadIdx.x >= o ? part[threadIdx.x - o] : 0;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    int run = part[threadIdx.x] - s;
+    for (int i = lo; i < hi; i++) { const int c = counts[i]; counts[i] = run; cursor[i] = run; run += c; }
+}
+__global__ void na_fill_kernel(const int32_t* __restrict__ tri, int64_t n3, int nV, int32_t* cursor, int32_t* incident) {
+    const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n3) return;
+    const int v = tri[c];
+    if (v >= 0 && v < nV) incident[atomicAdd(&cursor[v], 1)] = (int32_t)(c / 3);
+}
+__global__ void na_gather_kernel(const double* __restrict__ vtx, const int32_t* __restrict__ tri, const int32_t* __restrict__ offsets,
+                                 int32_t* incident, int nV, double* __restrict__ out) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nV) return;
+    const int a = offsets[v], b = offsets[v + 1];
+    for (int i = a + 1; i < b; i++) {                 // insertion sort: the list is this thread's own, a handful of entries
+        const int key = incident[i];
+        int j = i - 1;
+        while (j >= a && incident[j] > key) { incident[j + 1] = incident[j]; j--; }
+        incident[j + 1] = key;
+    }
+    double sx = 0.0, sy = 0.0, sz = 0.0;
+    for (int i = a; i < b; i++) {
+        const int t = incident[i];
+        const int i0 = tri[3 * t], i1 = tri[3 * t + 1], i2 = tri[3 * t + 2];
+        const double ax = vtx[3 * i0], ay = vtx[3 * i0 + 1], az = vtx[3 * i0 + 2];
+        const double e1x = xdsub(vtx[3 * i1], ax), e1y = xdsub(vtx[3 * i1 + 1], ay), e1z = xdsub(vtx[3 * i1 + 2], az);
+        const double e2x = xdsub(vtx[3 * i2], ax), e2y = xdsub(vtx[3 * i2 + 1], ay), e2z = xdsub(vtx[3 * i2 + 2], az);
+        sx = xdadd(sx, xdsub(xdmul(e1y, e2z), xdmul(e1z, e2y)));
+        sy = xdadd(sy, xdsub(xdmul(e1z, e2x), xdmul(e1x, e2z)));
+        sz = xdadd(sz, xdsub(xdmul(e1x, e2y), xdmul(e1y, e2x)));
+    }
+    const double z = xdadd(xdadd(xdmul(sx, sx), xdmul(sy, sy)), xdmul(sz, sz));
+    if (z > 0.0) { const double len = sqrt(z); sx = xddiv(sx, len); sy = xddiv(sy, len); sz = xddiv(sz, len); }
+    if (sx != sx) { sx = 0.0; sy = 0.0; sz = 1.0; }
+    out[3 * (int64_t)v] = sx; out[3 * (int64_t)v + 1] = sy; out[3 * (int64_t)v + 2] = sz;
+}
+
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the address a kernel may use comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+int noalloc_scratch(NoAllocScratch** out) {
+    static std::mutex mu;
+    static NoAllocScratch* ptr[64] = {nullptr};
+    int dev = 0;
+    B2R_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { b2r_set_error("b2r_mesh_vertex_normals_noalloc: device index %d out of range", dev); return B2R_ERR_BAD_ARG; }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptr[dev]) {
+        void* p = nullptr;
+        B2R_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        ptr[dev] = reinterpret_cast<NoAllocScratch*>(p);
+    }
+    *out = ptr[dev];
+    return B2R_OK;
+}
+}  // namespace
+
+B2R_API int b2r_mesh_vertex_normals_noalloc(const double* vtx, int64_t nV, const int32_t* tri, int64_t nF, double* out, cudaStream_t stream) {
+    if (!vtx || !tri || !out || nV < 0 || nF < 0) return B2R_ERR_BAD_ARG;
+    if (nV > B2R_NOALLOC_MAX_VERTICES || nF > B2R_NOALLOC_MAX_TRIANGLES) {
+        b2r_set_error("b2r_mesh_vertex_normals_noalloc: mesh of %lld vertices / %lld triangles exceeds the fixed scratch (max %d vertices, %d triangles); "
+                      "use b2r_mesh_vertex_normals", (long long)nV, (long long)nF, B2R_NOALLOC_MAX_VERTICES, B2R_NOALLOC_MAX_TRIANGLES);
+        return B2R_ERR_CAPACITY;
+    }
+    if (nV == 0) return B2R_OK;
+    NoAllocScratch* S = nullptr;
+    int rc = noalloc_scratch(&S);
+    if (rc != B2R_OK) return rc;
+    const int n = (int)nV;
+    const int64_t n3 = 3 * nF;
+    na_zero_kernel<<<(unsigned)((n + 1 + 255) / 256), 256, 0, stream>>>(S->offsets, n + 1);      // the last call's counts are stale
+    if (n3) na_count_kernel<<<(unsigned)((n3 + 255) / 256), 256, 0, stream>>>(tri, n3, n, S->offsets);
+    na_scan_kernel<<<1, 1024, 0, stream>>>(S->offsets, S->cursor, n + 1);
+    if (n3) na_fill_kernel<<<(unsigned)((n3 + 255) / 256), 256, 0, stream>>>(tri, n3, n, S->cursor, S->incident);
+    na_gather_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(vtx, tri, S->offsets, S->incident, n, out);
+    B2R_CHECK_LAUNCH();
     return B2R_OK;
 }

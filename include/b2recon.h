@@ -187,6 +187,17 @@ int b2r_tsdf_adopt_units(b2r_tsdf* h, const int32_t* keys3, int64_t first, int64
 /* mesh.compute_vertex_normals()  (GoodColorReconstruction.py:286) */
 int b2r_mesh_vertex_normals(const double* vtx, int64_t nV, const int32_t* tri, int64_t nF, double* out,
                             cudaStream_t stream);
+/* Allocation-free variant of b2r_mesh_vertex_normals.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same inputs, outputs and result (per-vertex sums in ascending triangle order); the scratch -- per-vertex
+ * incidence lists -- lives in a file-scope device array of 8.4 MB that every GPU loading the library holds until exit.
+ * Limits: nV <= B2R_NOALLOC_MAX_VERTICES, nF <= B2R_NOALLOC_MAX_TRIANGLES, else B2R_ERR_CAPACITY (-3) and a message.  Calls no
+ * cudaMalloc / cudaFree / allocating library routine.  All calls on a device share the array: calls that overlap on the GPU
+ * (different streams) race; calls on one stream are safe (the stale counts are cleared at the start of every call). */
+#define B2R_NOALLOC_MAX_VERTICES 262144
+#define B2R_NOALLOC_MAX_TRIANGLES 524288
+int b2r_mesh_vertex_normals_noalloc(const double* vtx, int64_t nV, const int32_t* tri, int64_t nF, double* out,
+                                    cudaStream_t stream);
 
 /* ---- a12: o3d.pipelines.odometry.compute_rgbd_odometry  (RGBD_Odometry.py:26-35,
  *      capture_frames.py:148-151, bundlefusion_reconstruction.py:224-227).
