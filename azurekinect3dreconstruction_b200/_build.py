@@ -14,7 +14,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libb2recon.so")
-SOURCES = ["tsdf.cu", "unproject.cu", "extract.cu", "odometry.cu", "icp.cu", "pointcloud.cu", "posegraph.cu", "features.cu"]
+SOURCES = ["tsdf.cu", "unproject.cu", "extract.cu", "odometry.cu", "icp.cu", "pointcloud.cu", "posegraph.cu", "features.cu", "peer.cu"]
 HEADERS = ["common.cuh", "host_math.h", "tsdf_internal.h", "mc_tables.h", "rigid_fit.cuh"]
 
 NVCC_FLAGS = [

@@ -63,6 +63,12 @@ SIGNATURES = {
     "b2r_tsdf_extract_mesh": (_i, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _pi64, _pi64, _vp]),
     "b2r_tsdf_extract_mesh_slab": (_i, [_vp, _i, _i, _i64, _vp, _vp, _vp, _vp, _i64, _i64, _pi64, _pi64, _vp]),
     "b2r_tsdf_extract_points_slab": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _i64, _pi64, _vp]),
+    "b2r_peer_alloc": (_i, [_i64, C.POINTER(_vp), _vp]),
+    "b2r_peer_free": (_i, [_vp]),
+    "b2r_peer_open": (_i, [_vp, C.POINTER(_vp)]),
+    "b2r_peer_close": (_i, [_vp]),
+    "b2r_stream_write32": (_i, [_vp, _vp, C.c_uint32]),
+    "b2r_stream_wait32_geq": (_i, [_vp, _vp, C.c_uint32]),
     "b2r_tsdf_export_selected": (_i, [_vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
     "b2r_tsdf_export_records": (_i, [_vp, _vp, _i64, _vp, _vp, _vp]),
     "b2r_tsdf_pool": (_vp, [_vp, _pi64]),

@@ -564,8 +564,146 @@ class HostFrameExchange:
                 self.released[slot].record(torch.cuda.current_stream())
 
 
+class PeerFrameExchange:
+    """HostFrameExchange without a collective: rank r uploads its 1/world share of every super-chunk (pinned host -> its own
+    device ring, copy engine) and the OTHER ranks read it where it lies -- the ring is mapped into every process through CUDA
+    IPC (b2r_peer_alloc / b2r_peer_open) and `consume` receives pointers into the peers' rings, so K1's TMA tile loads pull the
+    pixels over NVLink: the transfer is the pack kernel's load phase, and nothing has to be scheduled beside the persistent
+    fusion passes (an NCCL all-gather kernel cannot start while a pass holds every SM).  Ordering between ranks is two
+    monotonic counters per (rank, peer) in a small mapped flag block, written and awaited IN STREAM ORDER by stream memory
+    operations (b2r_stream_write32 / b2r_stream_wait32_geq: no kernel, no SM, no host round trip):
+      ready[src]  (in every rank's block)  = super-chunks src has uploaded  -> the consumer's stream waits for it before K1;
+      done[dst]   (in every rank's block)  = super-chunks dst has packed    -> the owner's copy stream waits for every peer
+                                             before it overwrites the ring slot `ring` chunks later.
+    Same plan / frame order as HostFrameExchange (the volume comes out bit-identical); needs NCCL only to hand the 64-byte
+    IPC handles round once."""
+
+    def __init__(self, frame_shape, color_channels: int, per: int = 8, group=None, device=None, ramp: bool = True, slots: int = 4):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.per, (self.H, self.W), self.ch, self.ramp = int(per), frame_shape, int(color_channels), bool(ramp)
+        self.device = torch.device(device)
+        self.lib = _lib.load()
+        al = lambda n: (n + 255) & ~255
+        self.dbytes, self.cbytes = self.H * self.W * 2, self.H * self.W * self.ch
+        self.dpad, self.cpad = al(self.dbytes), al(self.cbytes)
+        self.rec = self.dpad + self.cpad
+        self.ns = max(2, int(slots))
+        self.slot_bytes = self.per * self.rec
+        self.flag_bytes = 4096                                    # ready[world] at 0, done[world] at 2048 (uint32 each)
+        total = self.flag_bytes + self.ns * self.slot_bytes
+        mine, handle = C.c_void_p(0), (C.c_ubyte * 64)()
+        _lib.check(self.lib.b2r_peer_alloc(total, C.byref(mine), handle), "peer_alloc")
+        self.base_mine = int(mine.value)
+        h = torch.tensor(list(handle), dtype=torch.uint8, device=self.device)
+        hs = [torch.zeros_like(h) for _ in range(self.world)]
+        dist.all_gather(hs, h, group=group)
+        self.base = []
+        for r in range(self.world):
+            if r == self.rank:
+                self.base.append(self.base_mine)
+                continue
+            hb = (C.c_ubyte * 64)(*hs[r].cpu().tolist())
+            ptr = C.c_void_p(0)
+            _lib.check(self.lib.b2r_peer_open(hb, C.byref(ptr)), "peer_open")
+            self.base.append(int(ptr.value))
+        # my ring as a tensor (the upload target), without a copy
+        ring_ptr, n = self.base_mine + self.flag_bytes, self.ns * self.slot_bytes
+
+        class _Ring:
+            __cuda_array_interface__ = {"shape": (n,), "typestr": "|u1", "data": (ring_ptr, False), "version": 2, "strides": None}
+        self.ring = torch.as_tensor(_Ring(), device=self.device)
+        self.copy_stream = torch.cuda.Stream(device=self.device)
+        self.seq = 0                                              # super-chunks exchanged so far (monotonic across runs; same on every rank)
+        self.bytes_uploaded = 0
+        self.timeline = None
+        dist.barrier(group=group)                                 # every rank has mapped every ring before anyone writes a flag
+
+    def close(self):
+        if getattr(self, "base", None) is None:
+            return
+        torch.cuda.synchronize(self.device)
+        self.dist.barrier(group=self.group)
+        for r, b in enumerate(self.base):
+            if r != self.rank:
+                self.lib.b2r_peer_close(C.c_void_p(b))
+        self.ring = None
+        self.lib.b2r_peer_free(C.c_void_p(self.base_mine))
+        self.base = None
+
+    def _ready(self, holder, src):                                # address of ready[src] in `holder`'s flag block
+        return C.c_void_p(self.base[holder] + 4 * src)
+
+    def _done(self, holder, dst):
+        return C.c_void_p(self.base[holder] + 2048 + 4 * dst)
+
+    def _mark(self, stage, i, stream):
+        if self.timeline is None:
+            return
+        e = torch.cuda.Event(enable_timing=True)
+        e.record(stream)
+        self.timeline.append((stage, i, e))
+
+    def _upload(self, i, g, depth_h, color_h, f0, f1, cur):
+        n, slot = f1 - f0, g % self.ns
+        cs = C.c_void_p(self.copy_stream.cuda_stream)
+        if g >= self.ns:                                          # every rank has packed the chunk that lived in this slot
+            for p in range(self.world):
+                _lib.check(self.lib.b2r_stream_wait32_geq(cs, self._done(self.rank, p), g - self.ns + 1), "wait done")
+        loc = self.ring[slot * self.slot_bytes: slot * self.slot_bytes + cur * self.rec]
+        dblk = loc[: cur * self.dpad].view(cur, self.dpad)
+        cblk = loc[cur * self.dpad:].view(cur, self.cpad)
+        with torch.cuda.stream(self.copy_stream):
+            self._mark("upload_begin", i, self.copy_stream)
+            if n > 0:
+                if self.dpad == self.dbytes:
+                    dblk[:n].copy_(depth_h[f0:f1].reshape(n, -1).view(torch.uint8), non_blocking=True)
+                else:
+                    for k in range(n):
+                        dblk[k, :self.dbytes].copy_(depth_h[f0 + k].reshape(-1).view(torch.uint8), non_blocking=True)
+                if self.cpad == self.cbytes:
+                    cblk[:n].copy_(color_h[f0:f1].reshape(n, -1), non_blocking=True)
+                else:
+                    for k in range(n):
+                        cblk[k, :self.cbytes].copy_(color_h[f0 + k].reshape(-1), non_blocking=True)
+            self._mark("upload_end", i, self.copy_stream)
+        for p in range(self.world):                               # tell everyone (stream-ordered after the copies)
+            _lib.check(self.lib.b2r_stream_write32(cs, self._ready(p, self.rank), g + 1), "write ready")
+        self.bytes_uploaded += n * self.H * self.W * (2 + self.ch)
+
+    def run(self, depth_h: torch.Tensor, color_h: torch.Tensor, consume) -> None:
+        """depth_h (F,H,W) uint16, color_h (F,H,W,ch) uint8 -- pinned host tensors (identical on every rank)."""
+        plan = superchunk_plan(int(depth_h.shape[0]), self.world, self.per, self.ramp)
+        if not plan:
+            return
+        n = len(plan)
+        cur_of = lambda i: max(f1 - f0 for f0, f1 in plan[i][2])
+        cur_stream = torch.cuda.current_stream()
+        ms = C.c_void_p(cur_stream.cuda_stream)
+        self.copy_stream.wait_stream(cur_stream)
+        up = 0
+        for i, (f_start, n_valid, _) in enumerate(plan):
+            while up < n and up < i + self.ns:                    # uploads run up to `ring` chunks ahead; their real pacing is the done flags
+                self._upload(up, self.seq + up, depth_h, color_h, *plan[up][2][self.rank], cur_of(up))
+                up += 1
+            g, cur = self.seq + i, cur_of(i)
+            slot = g % self.ns
+            for p in range(self.world):
+                _lib.check(self.lib.b2r_stream_wait32_geq(ms, self._ready(self.rank, p), g + 1), "wait ready")
+            # frame f_start + k is image k % cur of rank k // cur's ring slot
+            dptr = [self.base[k // cur] + self.flag_bytes + slot * self.slot_bytes + (k % cur) * self.dpad for k in range(n_valid)]
+            cptr = [self.base[k // cur] + self.flag_bytes + slot * self.slot_bytes + cur * self.dpad + (k % cur) * self.cpad for k in range(n_valid)]
+            self._mark("integrate_begin", i, cur_stream)
+            consume(dptr, cptr, f_start, n_valid)
+            self._mark("integrate_end", i, cur_stream)
+            for p in range(self.world):                           # K1 has read the pixels (stream order): the owners may reuse the slot
+                _lib.check(self.lib.b2r_stream_write32(ms, self._done(p, self.rank), g + 1), "write done")
+        self.seq += n
+
+
 def integrate_host_frames(vol: ScalableTSDFVolume, depth_h: torch.Tensor, color_h: torch.Tensor, intrinsic, extrinsics,
-                          depth_scale: float = 1000.0, depth_trunc: float = 3.0, exchange: Optional[HostFrameExchange] = None) -> None:
+                          depth_scale: float = 1000.0, depth_trunc: float = 3.0, exchange=None) -> None:
     """integrate_raw for HOST frames on a sharded volume: PCIe carries each frame once per JOB (not once per rank)."""
     if exchange is None or exchange.world == 1:
         vol.integrate_raw(depth_h, color_h, intrinsic, extrinsics, depth_scale, depth_trunc)

@@ -318,8 +318,11 @@ def main():
     exchange = None
     if world > 1:
         from azurekinect3dreconstruction_b200.pipelines import sharded
-        exchange = sharded.HostFrameExchange((H, W), 3, per=int(os.environ.get("B2R_EXCHANGE_PER", "8")), device=dev,
-                                             ramp=os.environ.get("B2R_EXCHANGE_RAMP", "1") != "0")
+        ex_kind = os.environ.get("B2R_EXCHANGE", "peer")
+        ex_args = dict(per=int(os.environ.get("B2R_EXCHANGE_PER", "8")), device=dev, ramp=os.environ.get("B2R_EXCHANGE_RAMP", "1") != "0")
+        # "peer": K1 reads the other ranks' uploaded frames over NVLink through IPC-mapped rings (no collective);
+        # "nccl": one all-gather per super-chunk (the fallback, and what the CPU tests exercise over gloo)
+        exchange = sharded.PeerFrameExchange((H, W), 3, **ex_args) if ex_kind == "peer" else sharded.HostFrameExchange((H, W), 3, **ex_args)
 
     def step_e2e():
         vol.reset()
@@ -346,7 +349,7 @@ def main():
         if rank == 0:
             rows = [{"stage": st_, "superchunk": i, "t_ms": t_origin.elapsed_time(e)} for st_, i, e in exchange.timeline]
             with open(os.environ["B2R_E2E_TIMELINE"], "w") as f:
-                json.dump({"n_gpus": world, "frames": args.frames, "per": exchange.per, "ramp": exchange.ramp, "events": rows}, f)
+                json.dump({"n_gpus": world, "frames": args.frames, "per": exchange.per, "ramp": exchange.ramp, "exchange": type(exchange).__name__, "events": rows}, f)
         exchange.timeline = None
     # the end-to-end arm must leave this rank's shard exactly as the device-resident arm did (same units, same voxel updates)
     if (st_e2e["num_units"], st_e2e["updated_voxels"], st_e2e["errors"]) != (st["num_units"], st["updated_voxels"], st["errors"]):
@@ -409,8 +412,9 @@ def main():
                 "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes * world,
                         "ms_per_step": ms_e2e / args.steps,
                         "ingest": ("host frames -> one GPU over PCIe (6-deep ring of 8-frame chunks)" if world == 1 else
-                                   "each rank uploads 1/%d of the frames over its PCIe link; NCCL all-gather over NVLink hands every rank all frames "
-                                   "(h2d_bytes_per_step is the whole job's)" % world)},
+                                   "each rank uploads 1/%d of the frames over its PCIe link; %s (h2d_bytes_per_step is the whole job's)" % (
+                                       world, "the other ranks' K1 reads them over NVLink from IPC-mapped rings, ordered by stream memory operations"
+                                       if isinstance(exchange, sharded.PeerFrameExchange) else "one NCCL all-gather per super-chunk hands every rank all frames"))},
                 "gpu_launches": args.steps * n_launches_step, "clocks": clocks}
         print(json.dumps(line))
     if world > 1:

@@ -184,6 +184,18 @@ int b2r_tsdf_export_selected(b2r_tsdf* h, const int32_t* ids, int64_t n, int32_t
 int b2r_tsdf_export_records(b2r_tsdf* h, const int32_t* ids, int64_t n, int32_t* keys3, float* units, cudaStream_t stream);
 float* b2r_tsdf_pool(b2r_tsdf* h, int64_t* floats_per_unit);
 int b2r_tsdf_adopt_units(b2r_tsdf* h, const int32_t* keys3, int64_t first, int64_t n, cudaStream_t stream);
+/* ---- multi-GPU frame exchange over peer memory (one process per GPU; SURVEY 8(e) collective (1), north_star "each frame's
+ *      depth/color/pose is broadcast"; reference precedent for many cameras into one volume:
+ *      BetterVisualizerD2camerasWORKSkinda.py:546-551).  A rank keeps its uploaded frames in a b2r_peer_alloc buffer that the
+ *      other ranks map with b2r_peer_open; b2r_tsdf_integrate_frames then takes pointers INTO THE PEERS' BUFFERS and K1's TMA
+ *      loads pull the pixels over NVLink.  Ordering between ranks: 32-bit counters written / awaited in stream order
+ *      (cuStreamWriteValue32 / cuStreamWaitValue32 -- no kernel, no SM).  handle64: 64 bytes, exchanged by any transport. */
+int b2r_peer_alloc(int64_t bytes, void** dptr, unsigned char* handle64);
+int b2r_peer_free(void* dptr);
+int b2r_peer_open(const unsigned char* handle64, void** dptr);
+int b2r_peer_close(void* dptr);
+int b2r_stream_write32(cudaStream_t stream, void* addr, uint32_t value);
+int b2r_stream_wait32_geq(cudaStream_t stream, void* addr, uint32_t value);
 /* mesh.compute_vertex_normals()  (GoodColorReconstruction.py:286) */
 int b2r_mesh_vertex_normals(const double* vtx, int64_t nV, const int32_t* tri, int64_t nF, double* out,
                             cudaStream_t stream);

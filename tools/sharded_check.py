@@ -52,6 +52,32 @@ def main():
             world, n_local, single.num_units(), held, len(mesh.vertices), len(mesh.triangles), len(pcd.points), "OK" if ok else "MISMATCH"))
     else:
         ok = len(mesh.vertices) == 0 and len(mesh_all.vertices) > 0
+    # host-frame ingest: both exchanges must leave this rank's shard exactly as direct integration of device frames does
+    fr = [kin.render_depth_aligned_rgb(p) for p in syn.orbit_trajectory(21, yaw_sweep_deg=20.0)]
+    dh = torch.stack([f[0].view(torch.int16) for f in fr]).contiguous().pin_memory().view(torch.uint16)
+    ch = torch.stack([f[1] for f in fr]).contiguous().pin_memory()
+    Es = np.stack([np.linalg.inv(p) for p in syn.orbit_trajectory(21, yaw_sweep_deg=20.0)])
+    mk = lambda: o3d.pipelines.integration.ScalableTSDFVolume(0.01, 0.04, TT.RGB8, capacity_units=4096, rank=rank, world=world)
+    direct = mk()
+    direct.integrate_raw(dh.cuda(), ch.cuda(), K, Es, 1000.0, 3.0)
+    want = direct.export_units()
+    for kind in ("peer", "nccl"):
+        ex = (sharded.PeerFrameExchange if kind == "peer" else sharded.HostFrameExchange)((144, 160), 3, per=2, device=torch.device("cuda", local), slots=3)
+        for rep in range(2):                                  # twice: ring slots and counters are reused across runs
+            v = mk()
+            sharded.integrate_host_frames(v, dh, ch, K, Es, 1000.0, 3.0, exchange=ex)
+            got = v.export_units()
+            same = all(torch.equal(a, b) for a, b in zip(got, want))
+            ok = ok and same
+            if not same:
+                print("rank %d: %s exchange run %d differs from direct integration" % (rank, kind, rep))
+        if kind == "peer":
+            ex.close()
+    flag = torch.tensor([1 if ok else 0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    ok = bool(flag.item())
+    if rank == 0:
+        print("sharded_check world=%d: host-frame exchanges (peer, nccl) vs direct integration -> %s" % (world, "OK" if ok else "MISMATCH"))
     dist.barrier()
     dist.destroy_process_group()
     return 0 if ok else 1
