@@ -67,6 +67,7 @@ SIGNATURES = {
     "b2r_peer_free": (_i, [_vp]),
     "b2r_peer_open": (_i, [_vp, C.POINTER(_vp)]),
     "b2r_peer_close": (_i, [_vp]),
+    "b2r_peer_copy": (_i, [_vp, _vp, _i64, _vp]),
     "b2r_stream_write32": (_i, [_vp, _vp, C.c_uint32]),
     "b2r_stream_wait32_geq": (_i, [_vp, _vp, C.c_uint32]),
     "b2r_tsdf_export_selected": (_i, [_vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),

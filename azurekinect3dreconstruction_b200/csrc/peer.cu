@@ -63,6 +63,12 @@ B2R_API int b2r_peer_close(void* dptr) {
     if (dptr) B2R_CUDA(cudaIpcCloseMemHandle(dptr));
     return B2R_OK;
 }
+// Copy-engine copy between any two device addresses this process can see (own memory or mapped peer buffers): no SM involved.
+B2R_API int b2r_peer_copy(void* dst, const void* src, int64_t bytes, cudaStream_t stream) {
+    if (!dst || !src || bytes < 0) return B2R_ERR_BAD_ARG;
+    if (bytes) B2R_CUDA(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDefault, stream));
+    return B2R_OK;
+}
 // Stream-ordered 32-bit write (everything queued before it on `stream` is visible to whoever sees the value) and
 // stream-ordered wait until *addr >= value (wrap-safe comparison).  addr: device memory of this GPU or a mapped peer buffer.
 B2R_API int b2r_stream_write32(cudaStream_t stream, void* addr, uint32_t value) {

@@ -578,13 +578,18 @@ class PeerFrameExchange:
     Same plan / frame order as HostFrameExchange (the volume comes out bit-identical); needs NCCL only to hand the 64-byte
     IPC handles round once."""
 
-    def __init__(self, frame_shape, color_channels: int, per: int = 8, group=None, device=None, ramp: bool = True, slots: int = 4):
+    def __init__(self, frame_shape, color_channels: int, per: int = 8, group=None, device=None, ramp: bool = True, slots: int = 4,
+                 mode: str = "pull"):
+        """mode "direct": K1 reads the peers' rings itself (TMA loads over NVLink -- compute and transfer are one kernel, at
+        the price of NVLink latency inside K1); mode "pull": a pull stream first copies the peers' shares into a local buffer
+        with the COPY ENGINES (b2r_peer_copy, overlapping the fusion passes), K1 then reads local memory."""
         import torch.distributed as dist
         self.dist, self.group = dist, group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         self.per, (self.H, self.W), self.ch, self.ramp = int(per), frame_shape, int(color_channels), bool(ramp)
         self.device = torch.device(device)
         self.lib = _lib.load()
+        self.mode = mode
         al = lambda n: (n + 255) & ~255
         self.dbytes, self.cbytes = self.H * self.W * 2, self.H * self.W * self.ch
         self.dpad, self.cpad = al(self.dbytes), al(self.cbytes)
@@ -615,6 +620,11 @@ class PeerFrameExchange:
             __cuda_array_interface__ = {"shape": (n,), "typestr": "|u1", "data": (ring_ptr, False), "version": 2, "strides": None}
         self.ring = torch.as_tensor(_Ring(), device=self.device)
         self.copy_stream = torch.cuda.Stream(device=self.device)
+        if self.mode == "pull":
+            self.pull_stream = torch.cuda.Stream(device=self.device)
+            self.local = torch.zeros((self.ns, self.world * self.slot_bytes), dtype=torch.uint8, device=self.device)
+            self.ev_pulled = [torch.cuda.Event() for _ in range(self.ns)]
+            self.ev_packed = [torch.cuda.Event() for _ in range(self.ns)]
         self.seq = 0                                              # super-chunks exchanged so far (monotonic across runs; same on every rank)
         self.bytes_uploaded = 0
         self.timeline = None
@@ -682,24 +692,55 @@ class PeerFrameExchange:
         cur_stream = torch.cuda.current_stream()
         ms = C.c_void_p(cur_stream.cuda_stream)
         self.copy_stream.wait_stream(cur_stream)
-        up = 0
+        up = pulled = 0
         for i, (f_start, n_valid, _) in enumerate(plan):
             while up < n and up < i + self.ns:                    # uploads run up to `ring` chunks ahead; their real pacing is the done flags
                 self._upload(up, self.seq + up, depth_h, color_h, *plan[up][2][self.rank], cur_of(up))
                 up += 1
             g, cur = self.seq + i, cur_of(i)
             slot = g % self.ns
-            for p in range(self.world):
-                _lib.check(self.lib.b2r_stream_wait32_geq(ms, self._ready(self.rank, p), g + 1), "wait ready")
-            # frame f_start + k is image k % cur of rank k // cur's ring slot
-            dptr = [self.base[k // cur] + self.flag_bytes + slot * self.slot_bytes + (k % cur) * self.dpad for k in range(n_valid)]
-            cptr = [self.base[k // cur] + self.flag_bytes + slot * self.slot_bytes + cur * self.dpad + (k % cur) * self.cpad for k in range(n_valid)]
+            if self.mode == "pull":
+                while pulled < n and pulled < i + self.ns:        # pulls run ahead too; paced by ready flags and by K1 having freed the local slot
+                    self._pull(pulled, self.seq + pulled, cur_of(pulled), (pulled >= self.ns) or self.seq > 0)
+                    pulled += 1
+                cur_stream.wait_event(self.ev_pulled[slot])
+                _lib.check(self.lib.b2r_stream_wait32_geq(ms, self._ready(self.rank, self.rank), g + 1), "wait own upload")
+                lbase = self.local[slot].data_ptr()
+                src_base = [self.base_mine + self.flag_bytes + slot * self.slot_bytes if r == self.rank else lbase + r * self.slot_bytes for r in range(self.world)]
+            else:
+                for p in range(self.world):
+                    _lib.check(self.lib.b2r_stream_wait32_geq(ms, self._ready(self.rank, p), g + 1), "wait ready")
+                src_base = [self.base[r] + self.flag_bytes + slot * self.slot_bytes for r in range(self.world)]
+            # frame f_start + k is image k % cur of rank k // cur's share of the super-chunk
+            dptr = [src_base[k // cur] + (k % cur) * self.dpad for k in range(n_valid)]
+            cptr = [src_base[k // cur] + cur * self.dpad + (k % cur) * self.cpad for k in range(n_valid)]
             self._mark("integrate_begin", i, cur_stream)
             consume(dptr, cptr, f_start, n_valid)
             self._mark("integrate_end", i, cur_stream)
-            for p in range(self.world):                           # K1 has read the pixels (stream order): the owners may reuse the slot
-                _lib.check(self.lib.b2r_stream_write32(ms, self._done(p, self.rank), g + 1), "write done")
+            if self.mode == "pull":
+                self.ev_packed[slot].record(cur_stream)           # K1 has read the local slot and my own ring slot
+                _lib.check(self.lib.b2r_stream_write32(ms, self._done(self.rank, self.rank), g + 1), "write done")
+            else:
+                for p in range(self.world):                       # K1 has read the pixels (stream order): the owners may reuse the slot
+                    _lib.check(self.lib.b2r_stream_write32(ms, self._done(p, self.rank), g + 1), "write done")
         self.seq += n
+
+    def _pull(self, i, g, cur, reused):
+        """Copy-engine all-gather of super-chunk g: every peer's share -> my local slot; then the peers may reuse their ring slot."""
+        slot = g % self.ns
+        ps = C.c_void_p(self.pull_stream.cuda_stream)
+        if reused:
+            self.pull_stream.wait_event(self.ev_packed[slot])     # my K1 of the chunk that lived in this local slot
+        self._mark("gather_begin", i, self.pull_stream)
+        for p in range(self.world):
+            if p == self.rank:
+                continue
+            _lib.check(self.lib.b2r_stream_wait32_geq(ps, self._ready(self.rank, p), g + 1), "wait ready")
+            _lib.check(self.lib.b2r_peer_copy(C.c_void_p(self.local[slot].data_ptr() + p * self.slot_bytes),
+                                              C.c_void_p(self.base[p] + self.flag_bytes + slot * self.slot_bytes), cur * self.rec, ps), "peer_copy")
+            _lib.check(self.lib.b2r_stream_write32(ps, self._done(p, self.rank), g + 1), "write done")
+        self._mark("gather_end", i, self.pull_stream)
+        self.ev_pulled[slot].record(self.pull_stream)
 
 
 def integrate_host_frames(vol: ScalableTSDFVolume, depth_h: torch.Tensor, color_h: torch.Tensor, intrinsic, extrinsics,

@@ -194,6 +194,7 @@ int b2r_peer_alloc(int64_t bytes, void** dptr, unsigned char* handle64);
 int b2r_peer_free(void* dptr);
 int b2r_peer_open(const unsigned char* handle64, void** dptr);
 int b2r_peer_close(void* dptr);
+int b2r_peer_copy(void* dst, const void* src, int64_t bytes, cudaStream_t stream);   /* copy engine; either side may be a mapped peer buffer */
 int b2r_stream_write32(cudaStream_t stream, void* addr, uint32_t value);
 int b2r_stream_wait32_geq(cudaStream_t stream, void* addr, uint32_t value);
 /* mesh.compute_vertex_normals()  (GoodColorReconstruction.py:286) */

@@ -60,24 +60,29 @@ def main():
     mk = lambda: o3d.pipelines.integration.ScalableTSDFVolume(0.01, 0.04, TT.RGB8, capacity_units=4096, rank=rank, world=world)
     direct = mk()
     direct.integrate_raw(dh.cuda(), ch.cuda(), K, Es, 1000.0, 3.0)
-    want = direct.export_units()
-    for kind in ("peer", "nccl"):
-        ex = (sharded.PeerFrameExchange if kind == "peer" else sharded.HostFrameExchange)((144, 160), 3, per=2, device=torch.device("cuda", local), slots=3)
+    def state(v):                                            # pool order depends on allocation races: compare in key order
+        keys, t, w, c = v.export_units()
+        o = torch.as_tensor(np.lexsort(keys.cpu().numpy().T[::-1]), device=t.device)
+        return keys[o], t[o], w[o], c[o]
+    want = state(direct)
+    for kind in ("peer:pull", "peer:direct", "nccl"):
+        kw = dict(per=2, device=torch.device("cuda", local), slots=3)
+        ex = sharded.PeerFrameExchange((144, 160), 3, mode=kind.split(":")[1], **kw) if kind.startswith("peer") else sharded.HostFrameExchange((144, 160), 3, **kw)
         for rep in range(2):                                  # twice: ring slots and counters are reused across runs
             v = mk()
             sharded.integrate_host_frames(v, dh, ch, K, Es, 1000.0, 3.0, exchange=ex)
-            got = v.export_units()
+            got = state(v)
             same = all(torch.equal(a, b) for a, b in zip(got, want))
             ok = ok and same
             if not same:
                 print("rank %d: %s exchange run %d differs from direct integration" % (rank, kind, rep))
-        if kind == "peer":
+        if kind.startswith("peer"):
             ex.close()
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     ok = bool(flag.item())
     if rank == 0:
-        print("sharded_check world=%d: host-frame exchanges (peer, nccl) vs direct integration -> %s" % (world, "OK" if ok else "MISMATCH"))
+        print("sharded_check world=%d: host-frame exchanges (peer pull, peer direct, nccl) vs direct integration -> %s" % (world, "OK" if ok else "MISMATCH"))
     dist.barrier()
     dist.destroy_process_group()
     return 0 if ok else 1
