@@ -19,6 +19,7 @@ Odometry and ICP pairs are independent: one pair per GPU ("replicas only"), no c
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional
 
 import numpy as np
@@ -621,9 +622,11 @@ class PeerFrameExchange:
         self.ring = torch.as_tensor(_Ring(), device=self.device)
         self.copy_stream = torch.cuda.Stream(device=self.device)
         if self.mode == "pull":
-            self.pull_stream = torch.cuda.Stream(device=self.device)
+            # several pull streams: the peers' shares are copied by different copy engines side by side, and a peer whose
+            # upload is late holds up only the copies queued behind it on its own stream
+            self.pull_streams = [torch.cuda.Stream(device=self.device) for _ in range(max(1, min(int(os.environ.get("B2R_PULL_STREAMS", "4")), self.world - 1)))]
             self.local = torch.zeros((self.ns, self.world * self.slot_bytes), dtype=torch.uint8, device=self.device)
-            self.ev_pulled = [torch.cuda.Event() for _ in range(self.ns)]
+            self.ev_pulled = [[torch.cuda.Event() for _ in self.pull_streams] for _ in range(self.ns)]
             self.ev_packed = [torch.cuda.Event() for _ in range(self.ns)]
         self.seq = 0                                              # super-chunks exchanged so far (monotonic across runs; same on every rank)
         self.bytes_uploaded = 0
@@ -703,7 +706,8 @@ class PeerFrameExchange:
                 while pulled < n and pulled < i + self.ns:        # pulls run ahead too; paced by ready flags and by K1 having freed the local slot
                     self._pull(pulled, self.seq + pulled, cur_of(pulled), (pulled >= self.ns) or self.seq > 0)
                     pulled += 1
-                cur_stream.wait_event(self.ev_pulled[slot])
+                for e in self.ev_pulled[slot]:
+                    cur_stream.wait_event(e)
                 _lib.check(self.lib.b2r_stream_wait32_geq(ms, self._ready(self.rank, self.rank), g + 1), "wait own upload")
                 lbase = self.local[slot].data_ptr()
                 src_base = [self.base_mine + self.flag_bytes + slot * self.slot_bytes if r == self.rank else lbase + r * self.slot_bytes for r in range(self.world)]
@@ -728,19 +732,21 @@ class PeerFrameExchange:
     def _pull(self, i, g, cur, reused):
         """Copy-engine all-gather of super-chunk g: every peer's share -> my local slot; then the peers may reuse their ring slot."""
         slot = g % self.ns
-        ps = C.c_void_p(self.pull_stream.cuda_stream)
-        if reused:
-            self.pull_stream.wait_event(self.ev_packed[slot])     # my K1 of the chunk that lived in this local slot
-        self._mark("gather_begin", i, self.pull_stream)
-        for p in range(self.world):
-            if p == self.rank:
-                continue
-            _lib.check(self.lib.b2r_stream_wait32_geq(ps, self._ready(self.rank, p), g + 1), "wait ready")
-            _lib.check(self.lib.b2r_peer_copy(C.c_void_p(self.local[slot].data_ptr() + p * self.slot_bytes),
-                                              C.c_void_p(self.base[p] + self.flag_bytes + slot * self.slot_bytes), cur * self.rec, ps), "peer_copy")
-            _lib.check(self.lib.b2r_stream_write32(ps, self._done(p, self.rank), g + 1), "write done")
-        self._mark("gather_end", i, self.pull_stream)
-        self.ev_pulled[slot].record(self.pull_stream)
+        for j, st in enumerate(self.pull_streams):
+            ps = C.c_void_p(st.cuda_stream)
+            if reused:
+                st.wait_event(self.ev_packed[slot])               # my K1 of the chunk that lived in this local slot
+            if j == 0:
+                self._mark("gather_begin", i, st)
+            for k in range(j, self.world - 1, len(self.pull_streams)):
+                p = (self.rank + 1 + k) % self.world              # start with the next rank: the 8 readers spread over the 8 owners
+                _lib.check(self.lib.b2r_stream_wait32_geq(ps, self._ready(self.rank, p), g + 1), "wait ready")
+                _lib.check(self.lib.b2r_peer_copy(C.c_void_p(self.local[slot].data_ptr() + p * self.slot_bytes),
+                                                  C.c_void_p(self.base[p] + self.flag_bytes + slot * self.slot_bytes), cur * self.rec, ps), "peer_copy")
+                _lib.check(self.lib.b2r_stream_write32(ps, self._done(p, self.rank), g + 1), "write done")
+            if j == 0:
+                self._mark("gather_end", i, st)
+            self.ev_pulled[slot][j].record(st)
 
 
 def integrate_host_frames(vol: ScalableTSDFVolume, depth_h: torch.Tensor, color_h: torch.Tensor, intrinsic, extrinsics,
