@@ -319,7 +319,8 @@ def main():
     if world > 1:
         from azurekinect3dreconstruction_b200.pipelines import sharded
         ex_kind = os.environ.get("B2R_EXCHANGE", "peer")
-        ex_args = dict(per=int(os.environ.get("B2R_EXCHANGE_PER", "4")), device=dev, ramp=os.environ.get("B2R_EXCHANGE_RAMP", "1") != "0")
+        ex_args = dict(per=int(os.environ.get("B2R_EXCHANGE_PER", str(max(4, 32 // world)))), device=dev,   # one super-chunk = one 32-frame fusion pass
+                       ramp=os.environ.get("B2R_EXCHANGE_RAMP", "1") != "0")
         # "peer": K1 reads the other ranks' uploaded frames over NVLink through IPC-mapped rings (no collective);
         # "nccl": one all-gather per super-chunk (the fallback, and what the CPU tests exercise over gloo)
         exchange = sharded.PeerFrameExchange((H, W), 3, mode=os.environ.get("B2R_PEER_MODE", "pull"), **ex_args) if ex_kind == "peer" else sharded.HostFrameExchange((H, W), 3, **ex_args)
