@@ -70,6 +70,9 @@ SIGNATURES = {
     "b2r_peer_copy": (_i, [_vp, _vp, _i64, _vp]),
     "b2r_stream_write32": (_i, [_vp, _vp, C.c_uint32]),
     "b2r_stream_wait32_geq": (_i, [_vp, _vp, C.c_uint32]),
+    "b2r_stream_write32_multi": (_i, [_vp, _vp, _i, C.c_uint32]),
+    "b2r_stream_wait32_geq_multi": (_i, [_vp, _vp, _i, C.c_uint32]),
+    "b2r_peer_pull": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, C.c_uint32]),
     "b2r_tsdf_export_selected": (_i, [_vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
     "b2r_tsdf_export_records": (_i, [_vp, _vp, _i64, _vp, _vp, _vp]),
     "b2r_tsdf_pool": (_vp, [_vp, _pi64]),

@@ -78,6 +78,37 @@ B2R_API int b2r_stream_write32(cudaStream_t stream, void* addr, uint32_t value) 
     if (r != CUDA_SUCCESS) { b2r_set_error("cuStreamWriteValue32 failed (%d)", (int)r); return B2R_ERR_CUDA; }
     return B2R_OK;
 }
+// the same on n addresses (one call from the host language instead of n)
+B2R_API int b2r_stream_write32_multi(cudaStream_t stream, void* const* addrs, int n, uint32_t value) {
+    if (!addrs || n < 0) return B2R_ERR_BAD_ARG;
+    int rc = load_memops();
+    for (int i = 0; i < n && rc == B2R_OK; i++) {
+        const CUresult r = g_write32((CUstream)stream, (CUdeviceptr)(uintptr_t)addrs[i], value, CU_STREAM_WRITE_VALUE_DEFAULT);
+        if (r != CUDA_SUCCESS) { b2r_set_error("cuStreamWriteValue32 failed (%d)", (int)r); rc = B2R_ERR_CUDA; }
+    }
+    return rc;
+}
+B2R_API int b2r_stream_wait32_geq_multi(cudaStream_t stream, void* const* addrs, int n, uint32_t value) {
+    if (!addrs || n < 0) return B2R_ERR_BAD_ARG;
+    int rc = load_memops();
+    for (int i = 0; i < n && rc == B2R_OK; i++) {
+        const CUresult r = g_wait32((CUstream)stream, (CUdeviceptr)(uintptr_t)addrs[i], value, CU_STREAM_WAIT_VALUE_GEQ);
+        if (r != CUDA_SUCCESS) { b2r_set_error("cuStreamWaitValue32 failed (%d)", (int)r); rc = B2R_ERR_CUDA; }
+    }
+    return rc;
+}
+// One peer's share of a super-chunk, pulled by the copy engine: wait until *ready >= value, copy, then *done = value.
+B2R_API int b2r_peer_pull(cudaStream_t stream, void* ready, void* dst, const void* src, int64_t bytes, void* done, uint32_t value) {
+    if (!ready || !dst || !src || !done || bytes < 0) return B2R_ERR_BAD_ARG;
+    int rc = load_memops();
+    if (rc != B2R_OK) return rc;
+    CUresult r = g_wait32((CUstream)stream, (CUdeviceptr)(uintptr_t)ready, value, CU_STREAM_WAIT_VALUE_GEQ);
+    if (r != CUDA_SUCCESS) { b2r_set_error("cuStreamWaitValue32 failed (%d)", (int)r); return B2R_ERR_CUDA; }
+    if (bytes) B2R_CUDA(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDefault, stream));
+    r = g_write32((CUstream)stream, (CUdeviceptr)(uintptr_t)done, value, CU_STREAM_WRITE_VALUE_DEFAULT);
+    if (r != CUDA_SUCCESS) { b2r_set_error("cuStreamWriteValue32 failed (%d)", (int)r); return B2R_ERR_CUDA; }
+    return B2R_OK;
+}
 B2R_API int b2r_stream_wait32_geq(cudaStream_t stream, void* addr, uint32_t value) {
     int rc = load_memops();
     if (rc != B2R_OK) return rc;

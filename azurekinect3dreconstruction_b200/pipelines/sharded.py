@@ -624,10 +624,17 @@ class PeerFrameExchange:
         if self.mode == "pull":
             # several pull streams: the peers' shares are copied by different copy engines side by side, and a peer whose
             # upload is late holds up only the copies queued behind it on its own stream
-            self.pull_streams = [torch.cuda.Stream(device=self.device) for _ in range(max(1, min(int(os.environ.get("B2R_PULL_STREAMS", "4")), self.world - 1)))]
+            self.pull_streams = [torch.cuda.Stream(device=self.device) for _ in range(max(1, min(int(os.environ.get("B2R_PULL_STREAMS", "7")), self.world - 1)))]
             self.local = torch.zeros((self.ns, self.world * self.slot_bytes), dtype=torch.uint8, device=self.device)
             self.ev_pulled = [[torch.cuda.Event() for _ in self.pull_streams] for _ in range(self.ns)]
             self.ev_packed = [torch.cuda.Event() for _ in range(self.ns)]
+        arr = lambda xs: (C.c_void_p * len(xs))(*xs)
+        W_ = range(self.world)
+        self.a_ready_here = arr([self.base_mine + 4 * p for p in W_])                    # ready[p] in my block (all sources)
+        self.a_done_here = arr([self.base_mine + 2048 + 4 * p for p in W_])              # done[p] in my block (all consumers)
+        self.a_ready_everywhere = arr([self.base[p] + 4 * self.rank for p in W_])        # ready[me] in every block
+        self.a_done_everywhere = arr([self.base[p] + 2048 + 4 * self.rank for p in W_])  # done[me] in every block
+        self.lookahead = int(os.environ.get("B2R_EXCHANGE_LOOKAHEAD", "2"))
         self.seq = 0                                              # super-chunks exchanged so far (monotonic across runs; same on every rank)
         self.bytes_uploaded = 0
         self.timeline = None
@@ -661,9 +668,8 @@ class PeerFrameExchange:
     def _upload(self, i, g, depth_h, color_h, f0, f1, cur):
         n, slot = f1 - f0, g % self.ns
         cs = C.c_void_p(self.copy_stream.cuda_stream)
-        if g >= self.ns:                                          # every rank has packed the chunk that lived in this slot
-            for p in range(self.world):
-                _lib.check(self.lib.b2r_stream_wait32_geq(cs, self._done(self.rank, p), g - self.ns + 1), "wait done")
+        if g >= self.ns:                                          # every rank is done with the chunk that lived in this slot
+            _lib.check(self.lib.b2r_stream_wait32_geq_multi(cs, self.a_done_here, self.world, g - self.ns + 1), "wait done")
         loc = self.ring[slot * self.slot_bytes: slot * self.slot_bytes + cur * self.rec]
         dblk = loc[: cur * self.dpad].view(cur, self.dpad)
         cblk = loc[cur * self.dpad:].view(cur, self.cpad)
@@ -681,8 +687,8 @@ class PeerFrameExchange:
                     for k in range(n):
                         cblk[k, :self.cbytes].copy_(color_h[f0 + k].reshape(-1), non_blocking=True)
             self._mark("upload_end", i, self.copy_stream)
-        for p in range(self.world):                               # tell everyone (stream-ordered after the copies)
-            _lib.check(self.lib.b2r_stream_write32(cs, self._ready(p, self.rank), g + 1), "write ready")
+        # tell everyone (stream-ordered after the copies)
+        _lib.check(self.lib.b2r_stream_write32_multi(cs, self.a_ready_everywhere, self.world, g + 1), "write ready")
         self.bytes_uploaded += n * self.H * self.W * (2 + self.ch)
 
     def run(self, depth_h: torch.Tensor, color_h: torch.Tensor, consume) -> None:
@@ -697,13 +703,15 @@ class PeerFrameExchange:
         self.copy_stream.wait_stream(cur_stream)
         up = pulled = 0
         for i, (f_start, n_valid, _) in enumerate(plan):
-            while up < n and up < i + self.ns:                    # uploads run up to `ring` chunks ahead; their real pacing is the done flags
+            # the host stays `lookahead` chunks ahead of the consumer (enough to keep the copy engines fed; enqueuing a whole ring's
+            # worth first delayed the first pass by more than a millisecond of host time); the real pacing is the done flags
+            while up < n and up < i + min(self.ns, 1 + self.lookahead):
                 self._upload(up, self.seq + up, depth_h, color_h, *plan[up][2][self.rank], cur_of(up))
                 up += 1
             g, cur = self.seq + i, cur_of(i)
             slot = g % self.ns
             if self.mode == "pull":
-                while pulled < n and pulled < i + self.ns:        # pulls run ahead too; paced by ready flags and by K1 having freed the local slot
+                while pulled < n and pulled < i + min(self.ns, 1 + self.lookahead):   # pulls run ahead too; paced by ready flags and by K1 having freed the local slot
                     self._pull(pulled, self.seq + pulled, cur_of(pulled), (pulled >= self.ns) or self.seq > 0)
                     pulled += 1
                 for e in self.ev_pulled[slot]:
@@ -712,8 +720,7 @@ class PeerFrameExchange:
                 lbase = self.local[slot].data_ptr()
                 src_base = [self.base_mine + self.flag_bytes + slot * self.slot_bytes if r == self.rank else lbase + r * self.slot_bytes for r in range(self.world)]
             else:
-                for p in range(self.world):
-                    _lib.check(self.lib.b2r_stream_wait32_geq(ms, self._ready(self.rank, p), g + 1), "wait ready")
+                _lib.check(self.lib.b2r_stream_wait32_geq_multi(ms, self.a_ready_here, self.world, g + 1), "wait ready")
                 src_base = [self.base[r] + self.flag_bytes + slot * self.slot_bytes for r in range(self.world)]
             # frame f_start + k is image k % cur of rank k // cur's share of the super-chunk
             dptr = [src_base[k // cur] + (k % cur) * self.dpad for k in range(n_valid)]
@@ -725,13 +732,14 @@ class PeerFrameExchange:
                 self.ev_packed[slot].record(cur_stream)           # K1 has read the local slot and my own ring slot
                 _lib.check(self.lib.b2r_stream_write32(ms, self._done(self.rank, self.rank), g + 1), "write done")
             else:
-                for p in range(self.world):                       # K1 has read the pixels (stream order): the owners may reuse the slot
-                    _lib.check(self.lib.b2r_stream_write32(ms, self._done(p, self.rank), g + 1), "write done")
+                # K1 has read the pixels (stream order): the owners may reuse the slot
+                _lib.check(self.lib.b2r_stream_write32_multi(ms, self.a_done_everywhere, self.world, g + 1), "write done")
         self.seq += n
 
     def _pull(self, i, g, cur, reused):
         """Copy-engine all-gather of super-chunk g: every peer's share -> my local slot; then the peers may reuse their ring slot."""
         slot = g % self.ns
+        lbase = self.local[slot].data_ptr()
         for j, st in enumerate(self.pull_streams):
             ps = C.c_void_p(st.cuda_stream)
             if reused:
@@ -740,10 +748,9 @@ class PeerFrameExchange:
                 self._mark("gather_begin", i, st)
             for k in range(j, self.world - 1, len(self.pull_streams)):
                 p = (self.rank + 1 + k) % self.world              # start with the next rank: the 8 readers spread over the 8 owners
-                _lib.check(self.lib.b2r_stream_wait32_geq(ps, self._ready(self.rank, p), g + 1), "wait ready")
-                _lib.check(self.lib.b2r_peer_copy(C.c_void_p(self.local[slot].data_ptr() + p * self.slot_bytes),
-                                                  C.c_void_p(self.base[p] + self.flag_bytes + slot * self.slot_bytes), cur * self.rec, ps), "peer_copy")
-                _lib.check(self.lib.b2r_stream_write32(ps, self._done(p, self.rank), g + 1), "write done")
+                _lib.check(self.lib.b2r_peer_pull(ps, self._ready(self.rank, p), C.c_void_p(lbase + p * self.slot_bytes),
+                                                  C.c_void_p(self.base[p] + self.flag_bytes + slot * self.slot_bytes), cur * self.rec,
+                                                  self._done(p, self.rank), g + 1), "peer_pull")
             if j == 0:
                 self._mark("gather_end", i, st)
             self.ev_pulled[slot][j].record(st)

@@ -197,6 +197,10 @@ int b2r_peer_close(void* dptr);
 int b2r_peer_copy(void* dst, const void* src, int64_t bytes, cudaStream_t stream);   /* copy engine; either side may be a mapped peer buffer */
 int b2r_stream_write32(cudaStream_t stream, void* addr, uint32_t value);
 int b2r_stream_wait32_geq(cudaStream_t stream, void* addr, uint32_t value);
+int b2r_stream_write32_multi(cudaStream_t stream, void* const* addrs, int n, uint32_t value);
+int b2r_stream_wait32_geq_multi(cudaStream_t stream, void* const* addrs, int n, uint32_t value);
+/* wait *ready >= value, copy-engine copy, *done = value: one peer's share of a super-chunk */
+int b2r_peer_pull(cudaStream_t stream, void* ready, void* dst, const void* src, int64_t bytes, void* done, uint32_t value);
 /* mesh.compute_vertex_normals()  (GoodColorReconstruction.py:286) */
 int b2r_mesh_vertex_normals(const double* vtx, int64_t nV, const int32_t* tri, int64_t nF, double* out,
                             cudaStream_t stream);
