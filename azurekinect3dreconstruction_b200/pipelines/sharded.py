@@ -599,21 +599,35 @@ class PeerFrameExchange:
         self.slot_bytes = self.per * self.rec
         self.flag_bytes = 4096                                    # ready[world] at 0, done[world] at 2048 (uint32 each)
         total = self.flag_bytes + self.ns * self.slot_bytes
+        # Every step that can fail on one rank only (allocation, IPC export, mapping a peer) is followed by an agreement
+        # (all-reduce of a success flag), so that either every rank ends up with a working exchange or every rank raises --
+        # never some ranks waiting in a collective for one that has left.
+        def agree(ok: bool, what: str):
+            f = torch.tensor([1 if ok else 0], dtype=torch.int32, device=self.device)
+            dist.all_reduce(f, op=dist.ReduceOp.MIN, group=group)
+            if int(f.item()) == 0:
+                raise RuntimeError("PeerFrameExchange: %s failed on at least one rank%s" % (what, "" if ok else " (this one: %s)" % _lib.last_error()))
         mine, handle = C.c_void_p(0), (C.c_ubyte * 64)()
-        _lib.check(self.lib.b2r_peer_alloc(total, C.byref(mine), handle), "peer_alloc")
-        self.base_mine = int(mine.value)
+        rc = self.lib.b2r_peer_alloc(total, C.byref(mine), handle)
+        self.base_mine = int(mine.value) if rc == _lib.OK else 0
+        self.base = None
+        agree(rc == _lib.OK, "b2r_peer_alloc")
         h = torch.tensor(list(handle), dtype=torch.uint8, device=self.device)
         hs = [torch.zeros_like(h) for _ in range(self.world)]
         dist.all_gather(hs, h, group=group)
-        self.base = []
+        base, ok = [], True
         for r in range(self.world):
             if r == self.rank:
-                self.base.append(self.base_mine)
+                base.append(self.base_mine)
                 continue
             hb = (C.c_ubyte * 64)(*hs[r].cpu().tolist())
             ptr = C.c_void_p(0)
-            _lib.check(self.lib.b2r_peer_open(hb, C.byref(ptr)), "peer_open")
-            self.base.append(int(ptr.value))
+            ok = ok and self.lib.b2r_peer_open(hb, C.byref(ptr)) == _lib.OK
+            base.append(int(ptr.value or 0))
+        # stream memory operations must exist too (they are looked up through cudaGetDriverEntryPoint on first use)
+        ok = ok and self.lib.b2r_stream_write32(C.c_void_p(torch.cuda.current_stream().cuda_stream), C.c_void_p(self.base_mine + 4000), 1) == _lib.OK
+        agree(ok, "b2r_peer_open / stream memory operations")
+        self.base = base
         # my ring as a tensor (the upload target), without a copy
         ring_ptr, n = self.base_mine + self.flag_bytes, self.ns * self.slot_bytes
 
@@ -754,6 +768,20 @@ class PeerFrameExchange:
             if j == 0:
                 self._mark("gather_end", i, st)
             self.ev_pulled[slot][j].record(st)
+
+
+def make_frame_exchange(frame_shape, color_channels: int, kind: str = "peer", **kw):
+    """The host-frame exchange for this job: "peer" (IPC-mapped rings, copy-engine pulls; mode= "pull" | "direct") or "nccl" (one
+    all-gather per super-chunk).  If the peer form cannot be set up on this box -- decided collectively, see PeerFrameExchange --
+    every rank falls back to the NCCL form together."""
+    if kind == "peer":
+        try:
+            return PeerFrameExchange(frame_shape, color_channels, **kw)
+        except RuntimeError as e:
+            import sys
+            print("frame exchange: falling back to NCCL all-gathers (%s)" % e, file=sys.stderr)
+    kw.pop("mode", None)
+    return HostFrameExchange(frame_shape, color_channels, **kw)
 
 
 def integrate_host_frames(vol: ScalableTSDFVolume, depth_h: torch.Tensor, color_h: torch.Tensor, intrinsic, extrinsics,

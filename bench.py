@@ -323,7 +323,8 @@ def main():
                        ramp=os.environ.get("B2R_EXCHANGE_RAMP", "1") != "0")
         # "peer": K1 reads the other ranks' uploaded frames over NVLink through IPC-mapped rings (no collective);
         # "nccl": one all-gather per super-chunk (the fallback, and what the CPU tests exercise over gloo)
-        exchange = sharded.PeerFrameExchange((H, W), 3, mode=os.environ.get("B2R_PEER_MODE", "pull"), slots=int(os.environ.get("B2R_EXCHANGE_SLOTS", "8")), **ex_args) if ex_kind == "peer" else sharded.HostFrameExchange((H, W), 3, **ex_args)
+        exchange = sharded.make_frame_exchange((H, W), 3, ex_kind, mode=os.environ.get("B2R_PEER_MODE", "pull"),
+                                               slots=int(os.environ.get("B2R_EXCHANGE_SLOTS", "8")), **ex_args)
 
     def step_e2e():
         vol.reset()
