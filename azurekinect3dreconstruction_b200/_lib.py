@@ -100,6 +100,7 @@ SIGNATURES = {
     "b2r_ransac_correspondence": (_i, [_vp, _i64, _vp, _i64, _vp, _i64, _d, _i, _d, _d, _i64, _d, C.c_uint64, _pd, _pd, _pd, _pi64, _vp, _vp]),
     "b2r_knn_evaluate_transforms": (_i, [_vp, _vp, _i64, _vp, _i64, _d, _vp, _vp, _vp]),
     "b2r_posegraph_optimize": (_i, [_i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "b2r_correspondence_set": (_i, [_vp, _i64, _vp, _pi64, _vp]),
     "b2r_icp_point_to_plane": (_i, [_vp, _i64, _vp, _vp, _i64, _d, _pd, _i, _d, _d, _pd, _pd, _pd, _vp, _vp]),
 }
 

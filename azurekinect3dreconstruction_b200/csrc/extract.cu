@@ -161,6 +161,7 @@ __global__ void __launch_bounds__(256, 4) extract_points_kernel(const VolView V,
     __shared__ int ws[9];
     const int pos = blockIdx.x;
     const int unit = order[pos];
+    if (FILL && unit_offsets[pos + 1] == unit_offsets[pos]) return;     // the count pass found no surface point in this unit: nothing to stage
     stage_apron<0, true>(V, unit, A, nb);
     const int x = threadIdx.x >> 4, y = threadIdx.x & 15;
     unsigned masks[16];
@@ -382,7 +383,7 @@ __global__ void __launch_bounds__(256, 4) mesh_fill_kernel(const VolView V, cons
                                                         const int32_t* vbase_by_unit, const int32_t* tbase,
                                                         double* vtx, double* vcol, int32_t* tri, int32_t* ids,
                                                         int64_t capV, int64_t capF, int pos0, int64_t v0, int64_t t0, int vshift,
-                                                        const uint32_t* ubits) {
+                                                        const uint32_t* ubits, const int32_t* unit_vcount, const int32_t* unit_tcount) {
     __shared__ uint32_t NEG[MCOLS], VAL[MCOLS], CC[CCOLS];
     __shared__ uint16_t vlist[FILL_CAP];       // x << 10 | y << 6 | z << 2 | axis
     __shared__ uint16_t clist[FILL_CAP];       // x << 8 | y << 4 | z
@@ -390,6 +391,7 @@ __global__ void __launch_bounds__(256, 4) mesh_fill_kernel(const VolView V, cons
     __shared__ int nb[27];
     __shared__ int ws[9];
     const int pos = blockIdx.x + pos0;   // a slab handle fills its own contiguous range of the key order
+    if (unit_vcount[pos] == 0 && unit_tcount[pos] == 0) return;        // about half of the allocated units hold no part of the surface
     const int unit = order[pos];
     {
         const uint32_t* rec = ubits + (size_t)pos * UBITS;       // the count pass's classification of this unit
@@ -710,7 +712,7 @@ int extract_mesh_impl(b2r_tsdf* h, const Slab& sl, int64_t vertex_base, double* 
     const long long vshift = vertex_base - (long long)v01[0];
     if (vertex_base < 0 || vertex_base + (long long)tv > (long long)0x7fffffff) { b2r_set_error("extract_mesh: vertex ids exceed int32"); return B2R_ERR_RANGE; }
     mesh_fill_kernel<<<own[1] - own[0], 256, 0, stream>>>(V, S.order, S.vinfo, S.vbase_by_unit, S.scan_b, vtx, h->planes == 5 ? vcol : nullptr, tri, ids,
-                                                        capV, capF, own[0], (int64_t)v01[0], (int64_t)t01[0], (int)vshift, S.ubits);
+                                                        capV, capF, own[0], (int64_t)v01[0], (int64_t)t01[0], (int)vshift, S.ubits, S.cnt_a, S.cnt_b);
     B2R_CHECK_LAUNCH();
     return B2R_OK;
 }

@@ -682,6 +682,48 @@ B2R_API int b2r_pcd_gather_rows(const void* src, const int32_t* idx, int64_t m, 
     return B2R_OK;
 }
 
+// ---- RegistrationResult.correspondence_set: the (source, target) pairs of the matched source points, ascending by source ----
+namespace {
+__global__ void corr_flags_kernel(const int32_t* corr, int64_t n, int32_t* flags) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flags[i] = corr[i] >= 0 ? 1 : 0;
+    if (i == n) flags[i] = 0;
+}
+__global__ void corr_pairs_kernel(const int32_t* corr, const int32_t* scan, int64_t n, int32_t* pairs) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || corr[i] < 0) return;
+    pairs[2 * (int64_t)scan[i]] = (int32_t)i;
+    pairs[2 * (int64_t)scan[i] + 1] = corr[i];
+}
+}  // namespace
+// corr: DEVICE int32[n] (target index per source point, -1 = none, as b2r_icp_* write it); pairs_out: DEVICE int32[n][2] (room for
+// every point); *count_host = pairs written.  Synchronises `stream` to return the count.
+B2R_API int b2r_correspondence_set(const int32_t* corr, int64_t n, int32_t* pairs_out, int64_t* count_host, cudaStream_t stream) {
+    if (!corr || !pairs_out || !count_host || n < 0 || n > 0x7ffffff0) return B2R_ERR_BAD_ARG;
+    *count_host = 0;
+    if (n == 0) return B2R_OK;
+    size_t tmp_bytes = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, (int32_t*)nullptr, (int32_t*)nullptr, (int)(n + 1), stream);
+    int32_t *flags = nullptr, *scan = nullptr;
+    void* tmp = nullptr;
+    cudaError_t e = pcd_alloc(&flags, (size_t)(n + 1) * 4, stream);
+    if (e == cudaSuccess) e = pcd_alloc(&scan, (size_t)(n + 1) * 4, stream);
+    if (e == cudaSuccess) e = pcd_alloc(&tmp, tmp_bytes, stream);
+    int32_t total = 0;
+    if (e == cudaSuccess) {
+        const unsigned grid = (unsigned)((n + 1 + 255) / 256);
+        corr_flags_kernel<<<grid, 256, 0, stream>>>(corr, n, flags);
+        e = cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, flags, scan, (int)(n + 1), stream);
+        if (e == cudaSuccess) corr_pairs_kernel<<<grid, 256, 0, stream>>>(corr, scan, n, pairs_out);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&total, scan + n, 4, cudaMemcpyDeviceToHost, stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    }
+    pcd_free(flags, stream); pcd_free(scan, stream); pcd_free(tmp, stream);
+    if (e != cudaSuccess) { b2r_set_error("b2r_correspondence_set: %s", cudaGetErrorString(e)); return B2R_ERR_CUDA; }
+    *count_host = total;
+    return B2R_OK;
+}
+
 // ---- voxel_down_sample -------------------------------------------------------------------------------------------
 namespace {
 

@@ -183,7 +183,9 @@ __device__ __noinline__ void alloc_key(const PackParams& P, uint64_t key, uint32
 #define PACK_CTAS_PER_SM 2
 #endif
 #ifndef ALLOC_SPT
-#define ALLOC_SPT 4        // samples per thread of an allocation tile: 32 x (8 * ALLOC_SPT) samples per CTA
+#define ALLOC_SPT 4        // samples per thread of an allocation tile in batched launches: 32 x (8 * ALLOC_SPT) samples per CTA
+                           // (launches of one or two frames use 1: the GPU is empty then, and the CTA's dependent chain -- four f64
+                           // sample chains, a four times longer key list -- is what the call waits for)
 #endif
 #define ALLOC_LIST 2048  // compacted key list of an allocation tile (entries beyond it take the direct path)
 #define ALLOC_SMEM (4096 + ALLOC_LIST * 2)
@@ -238,6 +240,7 @@ B2R_API int b2r_debug_k1_trace(unsigned long long* out, int n) {
 #else
 #define K1_MARK(i) do { } while (0)
 #endif
+template <int SPT>
 __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(const __grid_constant__ PackParams P) {
     // One launch, two roles.  The first n_pack CTAs are PERSISTENT pack CTAs: each walks the launch's pixel tiles with stride
     // n_pack through a PACK_STAGES-deep ring of TMA bulk copies, so a tile's HBM latency is paid while the tiles before it
@@ -336,7 +339,7 @@ __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(con
     const int fidx = (int)(ridx / (unsigned)P.n_alloc_blocks), bidx = (int)(ridx - (unsigned)fidx * (unsigned)P.n_alloc_blocks);
     const PackFrame& F = P.fr[fidx];
     // ---- alloc role (a8): block allocation from the stride-sampled pixels (f64 chain).
-    // A CTA owns a 32 x 32 TILE of samples (128 x 128 pixels at stride 4; ALLOC_SPT samples per thread): a compact patch of the
+    // A CTA owns a 32 x 32 TILE of samples (128 x 128 pixels at stride 4; SPT samples per thread): a compact patch of the
     // surface touches a few dozen units, against the hundreds a raster strip of as many samples crosses, and the latency of
     // the tile's depth loads and of its hash round trips is paid once per 1024 samples.  Three stages:
     //   (1) per sample the upstream f64 chain -> integer key box;
@@ -350,24 +353,24 @@ __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(con
     const int tile_x = bidx % P.tiles_x, tile_y = bidx / P.tiles_x;
     const unsigned lane = threadIdx.x & 31u;
     const int warp = threadIdx.x >> 5;
-    // thread t takes samples (row 8 k + warp, column lane) of the tile, k = 0 .. ALLOC_SPT - 1: a warp holds 32 neighbours of
+    // thread t takes samples (row 8 k + warp, column lane) of the tile, k = 0 .. SPT - 1: a warp holds 32 neighbours of
     // one sample row.  All depth loads are issued before the first f64 chain starts.
     const int sj = tile_x * 32 + (int)lane;
-    float dpt[ALLOC_SPT];
+    float dpt[SPT];
 #pragma unroll
-    for (int k = 0; k < ALLOC_SPT; k++) {
-        const int si = tile_y * (8 * ALLOC_SPT) + 8 * k + warp;
+    for (int k = 0; k < SPT; k++) {
+        const int si = tile_y * (8 * SPT) + 8 * k + warp;
         dpt[k] = (sj < P.Ws && si < P.Hs) ? load_depth_m(P, F.depth, si * P.stride * P.W + sj * P.stride) : 0.0f;
     }
-    uint64_t bkey[ALLOC_SPT];      // packed lo corner of the sample's key box
-    uint32_t ecode[ALLOC_SPT];     // its extents, 10 bits each; 0 = the sample contributes nothing
+    uint64_t bkey[SPT];      // packed lo corner of the sample's key box
+    uint32_t ecode[SPT];     // its extents, 10 bits each; 0 = the sample contributes nothing
     int mn[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff};
 #pragma unroll
-    for (int k = 0; k < ALLOC_SPT; k++) {
+    for (int k = 0; k < SPT; k++) {
         bkey[k] = 0; ecode[k] = 0u;
         const float d = dpt[k];
         if (d > 0.0f) {
-            const int i = (tile_y * (8 * ALLOC_SPT) + 8 * k + warp) * P.stride, j = sj * P.stride;
+            const int i = (tile_y * (8 * SPT) + 8 * k + warp) * P.stride, j = sj * P.stride;
             const double z = (double)d;
             const double x = ddiv_const(xdmul(xdsub((double)j, P.cx), z), P.fx, P.rfx, P.ddiv_fast);
             const double y = ddiv_const(xdmul(xdsub((double)i, P.cy), z), P.fy, P.rfy, P.ddiv_fast);
@@ -420,7 +423,7 @@ __global__ void __launch_bounds__(256, PACK_MIN_CTAS) tsdf_pack_alloc_kernel(con
         org[a] = m;
     }
 #pragma unroll
-    for (int k = 0; k < ALLOC_SPT; k++) {
+    for (int k = 0; k < SPT; k++) {
         const uint64_t pk = __shfl_up_sync(0xffffffffu, bkey[k], 1);
         const uint32_t pe = __shfl_up_sync(0xffffffffu, ecode[k], 1);
         if (ecode[k] && (lane == 0 || pk != bkey[k] || pe != ecode[k])) {
@@ -869,7 +872,8 @@ B2R_API b2r_tsdf* b2r_tsdf_create(double voxel_length, double sdf_trunc, int col
         int nsm = 148, per_sm = 1;
         cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, h->device);
         h->n_sm = nsm;
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(tsdf_pack_alloc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PACK_STAGES * PACK_TILE * 8 + 256);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(tsdf_pack_alloc_kernel<ALLOC_SPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, PACK_STAGES * PACK_TILE * 8 + 256);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(tsdf_pack_alloc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, PACK_STAGES * PACK_TILE * 8 + 256);
         if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 64 * h->fuse_xl, h->fuse_smem);
         if (per_sm < 1) per_sm = 1;
         // B2R_FUSE_CTAS_PER_SM: fewer resident fusion CTAs than fit leave registers / shared memory on every SM for what runs
@@ -1123,7 +1127,8 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
         P.Ws = (W + h->stride - 1) / h->stride;
         P.Hs = (H + h->stride - 1) / h->stride;
         P.tiles_x = (P.Ws + 31) / 32;
-        P.n_alloc_blocks = P.tiles_x * ((P.Hs + 8 * ALLOC_SPT - 1) / (8 * ALLOC_SPT));
+        const int spt = take <= 2 ? 1 : ALLOC_SPT;
+        P.n_alloc_blocks = P.tiles_x * ((P.Hs + 8 * spt - 1) / (8 * spt));
         P.rank = h->rank; P.world = h->world; P.q = h->q;
         P.hash = h->hash; P.unit_keys = h->unit_keys; P.touched = h->touched[h->q];
         P.counters = h->counters; P.cap_units = (int)h->cap_units;
@@ -1171,7 +1176,8 @@ static int tsdf_integrate_impl(b2r_tsdf* h, int nf, const void* depth, int depth
         if (k1_smem < (size_t)ALLOC_SMEM) k1_smem = (size_t)ALLOC_SMEM;
         const unsigned grid = (unsigned)(P.n_pack + take * P.n_alloc_blocks);
         const bool prof = prof_begin(h, 1, stream);
-        tsdf_pack_alloc_kernel<<<grid, 256, k1_smem, stream>>>(P);
+        if (spt == 1) tsdf_pack_alloc_kernel<1><<<grid, 256, k1_smem, stream>>>(P);
+        else tsdf_pack_alloc_kernel<ALLOC_SPT><<<grid, 256, k1_smem, stream>>>(P);
         B2R_CHECK_LAUNCH();
         prof_end(h, prof, stream);
         h->pending += take;

@@ -26,6 +26,14 @@ class ICPConvergenceCriteria:
             self.relative_fitness, self.relative_rmse, self.max_iteration)
 
 
+def _correspondence_set(corr: torch.Tensor, n: int) -> "Vector2iVector":
+    """(source, target) pairs of the matched source points, ascending by source (b2r_correspondence_set)."""
+    pairs = torch.empty((max(n, 1), 2), dtype=torch.int32, device=corr.device)
+    cnt = C.c_int64(0)
+    _lib.check(_lib.load().b2r_correspondence_set(_lib.ptr(corr.contiguous()), n, _lib.ptr(pairs), C.byref(cnt), _lib.stream_ptr()), "correspondence_set")
+    return Vector2iVector(pairs[:int(cnt.value)])
+
+
 class TransformationEstimation:
     pass
 
@@ -88,9 +96,7 @@ def registration_icp(source: PointCloud, target: PointCloud, max_correspondence_
     res.transformation = np.array(T[:], dtype=np.float64).reshape(4, 4)
     res.fitness, res.inlier_rmse, res.num_iterations = float(fit.value), float(rmse.value), int(rc)
     if N and M:
-        c = corr[:N]
-        src_i = torch.nonzero(c >= 0).flatten().to(torch.int32)
-        res.correspondence_set = Vector2iVector(torch.stack([src_i, c[src_i.long()]], dim=1))
+        res.correspondence_set = _correspondence_set(corr, N)
     return res
 
 
@@ -144,9 +150,7 @@ def registration_colored_icp(source: PointCloud, target: PointCloud, max_corresp
     res.fitness, res.inlier_rmse, res.num_iterations = float(fit.value), float(rmse.value), int(rc)
     res.color_gradient = grad[:M]                    # build extension (parity hook)
     if N and M:
-        c = corr[:N]
-        src_i = torch.nonzero(c >= 0).flatten().to(torch.int32)
-        res.correspondence_set = Vector2iVector(torch.stack([src_i, c[src_i.long()]], dim=1))
+        res.correspondence_set = _correspondence_set(corr, N)
     return res
 
 
@@ -259,8 +263,7 @@ def registration_ransac_based_on_correspondence(source: PointCloud, target: Poin
         res.fitness, res.inlier_rmse = float(fit.value), float(rmse.value)
         if res.fitness > 0.0:
             cc = corr[:N]
-            src_i = torch.nonzero(cc >= 0).flatten().to(torch.int32)
-            res.correspondence_set = Vector2iVector(torch.stack([src_i, cc[src_i.long()]], dim=1))
+            res.correspondence_set = _correspondence_set(cc, int(cc.shape[0]))
     res.ransac_report = dict(iterations=int(rep[0]), validated=int(rep[1]), winning_iteration=int(rep[2]), inlier_correspondences=int(rep[3]))
     return res
 

@@ -247,6 +247,9 @@ int b2r_icp_point_to_plane(const double* src_xyz, int64_t N, const double* tgt_x
                            double max_dist, const double* init_host, int max_iter, double rel_fitness,
                            double rel_rmse, double* out_T_host, double* fitness_host, double* rmse_host,
                            int32_t* corr, cudaStream_t stream);
+/* result.correspondence_set (GoodColorReconstruction.py:200-204 reads the result's fields): the matched (source, target) index pairs,
+ * ascending by source, from the per-source target indices the ICP entry points write; pairs_out: DEVICE int32[n][2] */
+int b2r_correspondence_set(const int32_t* corr, int64_t n, int32_t* pairs_out, int64_t* count_host, cudaStream_t stream);
 
 /* registration_icp with TransformationEstimationPointToPoint(False) (Works2CamerasCOLORVisualizer.py:252-257): the same
  * on-device loop, update = closed-form rigid fit (Horn) of the correspondences.  No normals needed. */

@@ -439,6 +439,50 @@ def test_sharded_extraction_equals_single(o3r, frames, small_kinect, world):
     assert np.array_equal(np.asarray(pcd.colors), np.asarray(rp.colors))
 
 
+def test_peer_frame_exchange_rings_and_stream_memops(frames, small_kinect):
+    """The peer-memory host-frame exchange on ONE rank (a world-1 process group): IPC ring allocation, uploads into ring slots,
+    stream-ordered counters (cuStreamWriteValue32 / WaitValue32) pacing slot reuse over more chunks than the ring has slots, and
+    b2r_tsdf_integrate_frames on the slots -- the volume must equal direct integration.  (The cross-rank form is checked over
+    real IPC / NCCL by tools/sharded_check.py at N = 2 and N = 8.)"""
+    import socket
+    import torch.distributed as dist
+    from azurekinect3dreconstruction_b200.pipelines import sharded
+    intr = small_kinect.depth_intr
+    K = intrinsic_of(intr)
+    n = 9
+    depth = torch.from_numpy(np.stack([frames[i % len(frames)][0] for i in range(n)]).view(np.int16)).view(torch.uint16)
+    color = torch.stack([torch.from_numpy(frames[i % len(frames)][1]) for i in range(n)])
+    E = np.stack([np.linalg.inv(frames[i % len(frames)][2]) for i in range(n)])
+    TT = o3d.pipelines.integration.TSDFVolumeColorType
+    mk = lambda: o3d.pipelines.integration.ScalableTSDFVolume(0.01, 0.04, TT.RGB8, capacity_units=6000)
+    direct = mk()
+    direct.integrate_raw(depth.cuda(), color.cuda(), K, E)
+
+    def state(v):
+        keys, t, w, c = v.export_units()
+        o = torch.as_tensor(np.lexsort(keys.cpu().numpy().T[::-1]), device=t.device)
+        return keys[o], t[o], w[o], c[o]
+    want = state(direct)
+    own_group = not dist.is_initialized()
+    if own_group:
+        sk = socket.socket(); sk.bind(("127.0.0.1", 0)); port = sk.getsockname()[1]; sk.close()
+        dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % port, rank=0, world_size=1, device_id=torch.device("cuda", torch.cuda.current_device()))
+    try:
+        dh, ch = depth.view(torch.int16).pin_memory().view(torch.uint16), color.pin_memory()
+        for mode in ("pull", "direct"):
+            ex = sharded.PeerFrameExchange(tuple(depth.shape[1:]), 3, per=2, device=torch.device("cuda", torch.cuda.current_device()), slots=2, mode=mode)
+            for rep in range(2):                                              # 5 chunks through a 2-slot ring, twice (counters carry on)
+                v = mk()
+                sharded.integrate_host_frames(v, dh, ch, K, E, exchange=ex)
+                got = state(v)
+                assert all(torch.equal(a, b) for a, b in zip(got, want)), (mode, rep)
+            assert ex.seq == 2 * len(sharded.superchunk_plan(n, 1, 2, True)) and ex.bytes_uploaded == 2 * n * depth.shape[1] * depth.shape[2] * 5
+            ex.close()
+    finally:
+        if own_group:
+            dist.destroy_process_group()
+
+
 # ------------------------------------------------------------------------------------------------------
 # a10 / a11 extraction
 # ------------------------------------------------------------------------------------------------------
