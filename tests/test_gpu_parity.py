@@ -473,7 +473,8 @@ def test_peer_frame_exchange_rings_and_stream_memops(frames, small_kinect):
             ex = sharded.PeerFrameExchange(tuple(depth.shape[1:]), 3, per=2, device=torch.device("cuda", torch.cuda.current_device()), slots=2, mode=mode)
             for rep in range(2):                                              # 5 chunks through a 2-slot ring, twice (counters carry on)
                 v = mk()
-                sharded.integrate_host_frames(v, dh, ch, K, E, exchange=ex)
+                # (integrate_host_frames by-passes the exchange at world 1: drive it directly)
+                ex.run(dh, ch, lambda dp, cp, f0, m: v.integrate_frames(dp, cp, 3, K, E[f0:f0 + m], 1000.0, 3.0))
                 got = state(v)
                 assert all(torch.equal(a, b) for a, b in zip(got, want)), (mode, rep)
             assert ex.seq == 2 * len(sharded.superchunk_plan(n, 1, 2, True)) and ex.bytes_uploaded == 2 * n * depth.shape[1] * depth.shape[2] * 5
