@@ -264,7 +264,6 @@ __global__ void __launch_bounds__(256, 4) extract_points_kernel(const VolView V,
 #define MD 18   // apron [-1, 16]
 #define MC 17   // cube origins [-1, 15]
 
-__device__ __forceinline__ float apron_m(const float* A, int x, int y, int z) { return A[((x + 1) * MD + (y + 1)) * MD + (z + 1)]; }
 
 // ---- bit-parallel classification ----------------------------------------------------------------------------
 // Per (x, y) column of the staged apron (x, y in [-1, 16]) two 18-bit words over z in [-1, 16] (bit z + 1):
@@ -276,15 +275,54 @@ __device__ __forceinline__ float apron_m(const float* A, int x, int y, int z) { 
 #define MCOLS (MD * MD)        // 324 voxel columns
 #define CCOLS (MC * MC)        // 289 cube columns
 
-__device__ __forceinline__ void stage_bits(const float* A, uint32_t* NEG, uint32_t* VAL, uint32_t* CC) {
+// The words come straight from global memory, without a float apron in shared memory: a thread takes one (x, y) column of the
+// 18 x 18 apron columns, loads its 16 interior voxels (tsdf and weight: four 128-bit loads each) from the unit the column lies in
+// and the two caps z = -1 / z = 16 from the units below / above, and forms the column's VAL / NEG words in registers.
+__device__ __forceinline__ void neighbour_ids(const VolView& V, int unit, int* nb /*27*/) {
+    const int kx = V.unit_keys[3 * unit], ky = V.unit_keys[3 * unit + 1], kz = V.unit_keys[3 * unit + 2];
+    if (threadIdx.x < 27) {
+        const int dx = threadIdx.x / 9 - 1, dy = (threadIdx.x / 3) % 3 - 1, dz = threadIdx.x % 3 - 1;
+        nb[threadIdx.x] = (dx == 0 && dy == 0 && dz == 0) ? unit : find_unit(V, kx + dx, ky + dy, kz + dz);
+    }
+    __syncthreads();
+}
+__device__ __forceinline__ void stage_bits_direct(const VolView& V, const int* nb, uint32_t* NEG, uint32_t* VAL, uint32_t* CC) {
     for (int c = threadIdx.x; c < MCOLS; c += blockDim.x) {
-        const float* col = A + c * MD;
+        const int ax = c / MD, ay = c - ax * MD;
+        int x = ax - 1, y = ay - 1, ox = 1, oy = 1;
+        if (x < 0) { x += 16; ox = 0; } else if (x >= 16) { x -= 16; ox = 2; }
+        if (y < 0) { y += 16; oy = 0; } else if (y >= 16) { y -= 16; oy = 2; }
+        const int col = x * 256 + y * 16;
+        const int um = nb[(ox * 3 + oy) * 3 + 1], ub = nb[(ox * 3 + oy) * 3], ut = nb[(ox * 3 + oy) * 3 + 2];
         uint32_t n = 0, v = 0;
+        if (um >= 0) {
+            const float4* tp = reinterpret_cast<const float4*>(V.pool + (int64_t)um * V.unit_stride + col);
+            const float4* wp = reinterpret_cast<const float4*>(V.pool + (int64_t)um * V.unit_stride + B2R_UNIT_VOX + col);
+            float4 t[4], w[4];
 #pragma unroll
-        for (int z = 0; z < MD; z++) {
-            const float f = col[z];
-            v |= (f == f) ? (1u << z) : 0u;
-            n |= (f < 0.0f) ? (1u << z) : 0u;
+            for (int q = 0; q < 4; q++) { t[q] = __ldg(tp + q); w[q] = __ldg(wp + q); }
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const float tf[4] = {t[q].x, t[q].y, t[q].z, t[q].w}, wf[4] = {w[q].x, w[q].y, w[q].z, w[q].w};
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const bool ok = wf[k] != 0.0f;
+                    v |= ok ? (1u << (4 * q + k + 1)) : 0u;
+                    n |= (ok && tf[k] < 0.0f) ? (1u << (4 * q + k + 1)) : 0u;
+                }
+            }
+        }
+        if (ub >= 0) {
+            const float* b = V.pool + (int64_t)ub * V.unit_stride + col + 15;
+            const bool ok = __ldg(b + B2R_UNIT_VOX) != 0.0f;
+            v |= ok ? 1u : 0u;
+            n |= (ok && __ldg(b) < 0.0f) ? 1u : 0u;
+        }
+        if (ut >= 0) {
+            const float* b = V.pool + (int64_t)ut * V.unit_stride + col;
+            const bool ok = __ldg(b + B2R_UNIT_VOX) != 0.0f;
+            v |= ok ? (1u << 17) : 0u;
+            n |= (ok && __ldg(b) < 0.0f) ? (1u << 17) : 0u;
         }
         NEG[c] = n; VAL[c] = v;
     }
@@ -336,14 +374,13 @@ __device__ __forceinline__ int cube_case_bits(const uint32_t* nn, int z) {
 #define UBITS 968
 __global__ void __launch_bounds__(256) mesh_count_kernel(const VolView V, const int32_t* order, uint32_t* vinfo,
                                                          int32_t* unit_vcount, int32_t* unit_tcount, uint32_t* ubits) {
-    __shared__ float A[MD * MD * MD];
     __shared__ uint32_t NEG[MCOLS], VAL[MCOLS], CC[CCOLS];
     __shared__ int nb[27];
     __shared__ int ws[9];
     const int pos = blockIdx.x;
     const int unit = order[pos];
-    stage_apron<-1, false>(V, unit, A, nb);
-    stage_bits(A, NEG, VAL, CC);
+    neighbour_ids(V, unit, nb);
+    stage_bits_direct(V, nb, NEG, VAL, CC);
     {
         uint32_t* rec = ubits + (size_t)pos * UBITS;
         for (int i = threadIdx.x; i < MCOLS; i += blockDim.x) { rec[i] = NEG[i]; rec[MCOLS + i] = VAL[i]; }
