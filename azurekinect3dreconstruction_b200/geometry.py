@@ -28,9 +28,15 @@ class _PinnedRing:
     sent with an asynchronous H2D copy on the current stream; a slot is reused only after the copy that read it has completed."""
 
     def __init__(self, slots: int = 8):
+        import threading
         self.slots, self.buf, self.ev, self.i = slots, [None] * slots, [None] * slots, 0
+        self.lock = threading.Lock()          # the reference runs one capture thread per camera
 
     def upload(self, t_cpu: torch.Tensor, device) -> torch.Tensor:
+        with self.lock:
+            return self._upload(t_cpu, device)
+
+    def _upload(self, t_cpu: torch.Tensor, device) -> torch.Tensor:
         nbytes = t_cpu.numel() * t_cpu.element_size()
         k = self.i
         self.i = (self.i + 1) % self.slots
