@@ -693,10 +693,16 @@ int extract_mesh_impl(b2r_tsdf* h, const Slab& sl, int64_t vertex_base, double* 
                       int64_t capF, int64_t* nV, int64_t* nF, cudaStream_t stream) {
     if (!h || !nV || !nF) return B2R_ERR_BAD_ARG;
     B2RDeviceGuard g(h->device);
-    int64_t st[5];
-    int rc = b2r_tsdf_stats(h, st, stream);
-    if (rc != B2R_OK) return rc;
-    const int n = (int)st[0];
+    int rc = B2R_OK;
+    int n = h->mesh_n;
+    if (!(h->pending == 0 && h->mesh_gen == h->generation && h->mesh_n > 0)) {
+        // (an unchanged volume whose count pass is cached needs no read-back of the unit count: the fill pass is launched
+        //  without a host synchronisation)
+        int64_t st[5];
+        rc = b2r_tsdf_stats(h, st, stream);
+        if (rc != B2R_OK) return rc;
+        n = (int)st[0];
+    }
     *nV = 0; *nF = 0;
     if (n == 0) return B2R_OK;
     Scratch S;
