@@ -295,7 +295,7 @@ def main():
                 traffic = tj.get("dram_bytes_per_launch")
         except Exception:
             traffic = None
-    roofline = {"kernel": "tsdf_fuse_kernel<RGB8> (batch of %d frames per pass)" % batch, "bound": "hbm", "achieved": kp["achieved"],
+    roofline = {"kernel": "tsdf_fuse_kernel<RGB8, 2 stages, 2 x-layers per item> (batch of %d frames per pass)" % batch, "bound": "hbm", "achieved": kp["achieved"],
                 "peak": peak, "unit": "GB/s", "frac": kp["frac"], "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": kp["algorithmic_bytes_per_launch"], "avg_launch_ms": kp["avg_launch_ms"],
                 "frames_per_launch": kp["frames_per_launch"],

@@ -140,8 +140,8 @@ def test_tsdf_item_scheduling_modes_are_repeatable(nfov):
                     os.environ[k] = v
 
     ref, st = run({})
-    for env in ({"B2R_FUSE_RING_ROUNDS": "0"}, {"B2R_FUSE_RING_ROUNDS": "1000000"}, {"B2R_FUSE_XL": "2"},
-                {"B2R_FUSE_XL": "2", "B2R_FUSE_RING_ROUNDS": "1000000"}, {"B2R_FUSE_STAGES": "3"},
+    for env in ({"B2R_FUSE_RING_ROUNDS": "0"}, {"B2R_FUSE_RING_ROUNDS": "1000000"}, {"B2R_FUSE_XL": "4"},
+                {"B2R_FUSE_XL": "4", "B2R_FUSE_RING_ROUNDS": "1000000"}, {"B2R_FUSE_STAGES": "3"},
                 {"B2R_FUSE_SORT": "0"},                       # items in touched order instead of heaviest first
                 {"B2R_TSDF_OVERLAP": "1"},                    # passes on the internal stream beside the next batch's K1, double texel sets
                 {"B2R_TSDF_OVERLAP": "1", "B2R_TSDF_BATCH": "5"}):
