@@ -182,17 +182,20 @@ def config5_record(dev, rank, world, ticks=64, n_streams=8, ticks_per_batch=4):
     import torch.distributed as dist
     from azurekinect3dreconstruction_b200.pipelines import sharded
     intr = syn.WFOV_DEPTH
-    kin = syn.SyntheticKinect(depth_intrinsics=intr, seed=0, dropout=0.02, noise_sigma_mm=1.0, device=str(dev), max_range_m=syn.WFOV_MAX_RANGE_M)
     K = o3d.camera.PinholeCameraIntrinsic(intr["width"], intr["height"], intr["fx"], intr["fy"], intr["cx"], intr["cy"])
     H, W = intr["height"], intr["width"]
     ex = sharded.StreamTickExchange((H, W), 3, n_streams, ticks_per_batch=ticks_per_batch, device=dev)
     cams = syn.ring_cameras(n_streams, radius=1.5)
     mine = [s for s in range(n_streams) if s // ex.s_local == rank]
+    # one source per STREAM, seeded by the stream: a camera's noise / dropout sequence is the same whichever rank renders it, so the
+    # job fuses identical frames at every N (units_total / updated_voxels_total must then agree across N)
+    kins = {s: syn.SyntheticKinect(depth_intrinsics=intr, seed=100 + s, dropout=0.02, noise_sigma_mm=1.0, device=str(dev), max_range_m=syn.WFOV_MAX_RANGE_M)
+            for s in mine}
     packed = torch.zeros((ticks, ex.s_local, ex.rec), dtype=torch.uint8, device=dev)
     t_r0 = time.perf_counter()
     for t in range(ticks):
         drift = syn.make_pose(syn.rot_y(0.002 * t), (0.0, 0.001 * t, 0.0))      # the rig drifts: consecutive ticks are different frames
-        fr = [kin.render_depth_aligned_rgb(drift @ cams[s]) for s in mine]
+        fr = [kins[s].render_depth_aligned_rgb(drift @ cams[s]) for s in mine]
         ex.pack(torch.stack([f[0].view(torch.int16).to(dev) for f in fr]).view(torch.uint16), torch.stack([f[1].to(dev) for f in fr]),
                 np.stack([np.linalg.inv(drift @ cams[s]) for s in mine]), out=packed[t])
     torch.cuda.synchronize()
@@ -255,7 +258,7 @@ def config5_record(dev, rank, world, ticks=64, n_streams=8, ticks_per_batch=4):
            "mesh_gather_s": t_mesh, "mesh_gather_s_runs": runs, "mesh_phases_ms_rank0": phases, "vertices": len(mesh.vertices), "triangles": len(mesh.triangles),
            "extraction_scratch_bytes_rank0": getattr(vol, "last_extract_scratch_bytes", None) if vol is not None else None,
            "render_s": render_s}
-    del packed, local, vol, ex
+    del packed, local, vol, ex, kins
     torch.cuda.empty_cache()
     return out
 
