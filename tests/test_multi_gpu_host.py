@@ -63,7 +63,8 @@ def _worker(rank, world, port, q):
         color = (torch.arange(F * H * W * 3, dtype=torch.int64) % 251).to(torch.uint8).reshape(F, H, W, 3)
         import ctypes as C
         for ramp, expect in ((False, [(0, 6), (6, 5)]), (True, [(0, 2), (2, 4), (6, 5)])):
-            ex = sharded.HostFrameExchange((H, W), 3, per=3, device=None, ramp=ramp)
+            ex = sharded.make_frame_exchange((H, W), 3, "nccl", per=3, device=None, ramp=ramp, mode="pull")   # the collective form ("nccl" = torch.distributed: gloo here)
+            assert isinstance(ex, sharded.HostFrameExchange)
             seen = []
 
             def consume(dp, cp, f0, n):
